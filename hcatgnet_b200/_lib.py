@@ -1,0 +1,111 @@
+"""ctypes binding of libhcg.so (the C-ABI declared in include/hcg.h).
+
+There is no CPU implementation behind this module: if the library cannot be loaded (or built
+with nvcc), importing the product's compute path raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+from . import build as _build
+
+HCG_MAX_CONV = 8
+HCG_MAX_READOUT = 8
+HCG_COLLATE_TRANSPOSE = 1
+
+ERR_NAMES = {1: "INVALID_ARG", 2: "UNSUPPORTED", 3: "WORKSPACE", 4: "CUDA", 5: "BAD_INDEX", 6: "BAD_BATCH"}
+
+_fp = C.c_void_p  # device pointers travel as integers
+
+
+class HcgGraph(C.Structure):
+    _fields_ = [
+        ("N", C.c_int64), ("E", C.c_int64), ("B", C.c_int64),
+        ("rowptr", _fp), ("col", _fp), ("eid", _fp), ("dis", _fp), ("graph_ptr", _fp),
+        ("t_rowptr", _fp), ("t_col", _fp), ("t_eid", _fp),
+        ("fill", C.c_float),
+        ("ew0", _fp), ("t_ew0", _fp), ("selfw0", _fp), ("dis0", _fp),
+    ]
+
+
+class HcgParams(C.Structure):
+    _fields_ = [
+        ("F", C.c_int32), ("H", C.c_int32), ("L", C.c_int32), ("R", C.c_int32), ("C", C.c_int32),
+        ("slope", C.c_float),
+        ("conv_w", _fp * HCG_MAX_CONV), ("conv_b", _fp * HCG_MAX_CONV),
+        ("ro_w", _fp * HCG_MAX_READOUT), ("ro_b", _fp * HCG_MAX_READOUT),
+    ]
+
+
+class HcgGrads(C.Structure):
+    _fields_ = [
+        ("conv_w", _fp * HCG_MAX_CONV), ("conv_b", _fp * HCG_MAX_CONV),
+        ("ro_w", _fp * HCG_MAX_READOUT), ("ro_b", _fp * HCG_MAX_READOUT),
+    ]
+
+
+class HcgSaved(C.Structure):
+    _fields_ = [("acts", _fp * HCG_MAX_CONV), ("hid", _fp * HCG_MAX_READOUT)]
+
+
+class HcgError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"libhcg error {code} ({ERR_NAMES.get(code, '?')}): {msg}")
+        self.code = code
+
+
+_lock = threading.Lock()
+_lib = None
+
+# name -> (restype, argtypes); the test-suite checks this table against include/hcg.h
+SIGNATURES = {
+    "hcg_last_error": (C.c_char_p, []),
+    "hcg_version": (C.c_char_p, []),
+    "hcg_collate_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.c_int]),
+    "hcg_collate": (C.c_int, [_fp, C.c_int64, _fp, C.c_int64, C.c_int64, C.c_float, _fp, C.c_float, C.c_int,
+                              _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp,
+                              _fp, C.c_size_t, _fp]),
+    "hcg_collate_status": (C.c_int, [_fp, _fp]),
+    "hcg_forward_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.POINTER(HcgParams)]),
+    "hcg_gcn_forward": (C.c_int, [C.POINTER(HcgGraph), _fp, C.POINTER(HcgParams), _fp, _fp, C.POINTER(HcgSaved),
+                                  _fp, C.c_size_t, _fp]),
+    "hcg_backward_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.POINTER(HcgParams)]),
+    "hcg_gcn_backward": (C.c_int, [C.POINTER(HcgGraph), _fp, C.POINTER(HcgParams), C.POINTER(HcgSaved), _fp, _fp, _fp,
+                                   C.POINTER(HcgGrads), _fp, _fp, C.c_size_t, _fp]),
+}
+
+
+def lib_path() -> str:
+    return _build.LIB_PATH
+
+
+def load():
+    """Load (building first if the sources are newer and nvcc exists) and return the CDLL."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        path = _build.LIB_PATH
+        if _build.needs_build():
+            if _build.find_nvcc() is not None:
+                _build.build()
+            elif not os.path.exists(path):
+                raise RuntimeError(
+                    "hcatgnet_b200: libhcg.so is missing and nvcc is not available; the CUDA extension is "
+                    "required (there is no CPU fallback). Run `python -m hcatgnet_b200.build` on a box with nvcc.")
+        lib = C.CDLL(path)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError here = library/header mismatch: fail loudly
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def check(code: int) -> None:
+    if code != 0:
+        raise HcgError(code, load().hcg_last_error().decode("utf-8", "replace"))

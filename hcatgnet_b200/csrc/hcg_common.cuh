@@ -1,0 +1,65 @@
+// Shared helpers for libhcg (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/hcg.h"
+
+namespace hcg {
+
+constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+
+// thread-local error text behind hcg_last_error()
+char* err_buf();
+int set_err(int code, const char* fmt, ...);
+
+#define HCG_CUDA_OK(expr)                                                             \
+  do {                                                                                \
+    cudaError_t _e = (expr);                                                          \
+    if (_e != cudaSuccess)                                                            \
+      return ::hcg::set_err(HCG_ERR_CUDA, "%s failed: %s (%s:%d)", #expr,             \
+                            cudaGetErrorString(_e), __FILE__, __LINE__);              \
+  } while (0)
+
+#define HCG_LAUNCH_OK(name)                                                           \
+  do {                                                                                \
+    cudaError_t _e = cudaGetLastError();                                              \
+    if (_e != cudaSuccess)                                                            \
+      return ::hcg::set_err(HCG_ERR_CUDA, "launch of %s failed: %s", name,            \
+                            cudaGetErrorString(_e));                                  \
+  } while (0)
+
+#define HCG_REQUIRE(cond, code, ...)                                                  \
+  do {                                                                                \
+    if (!(cond)) return ::hcg::set_err(code, __VA_ARGS__);                            \
+  } while (0)
+
+inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// Carves aligned sub-buffers out of the caller's workspace.
+struct Carver {
+  char* base;
+  size_t off;
+  size_t cap;
+  Carver(void* p, size_t bytes) : base(static_cast<char*>(p)), off(0), cap(bytes) {}
+  template <typename T>
+  T* take(size_t count) {
+    size_t bytes = align_up(count * sizeof(T));
+    T* r = reinterpret_cast<T*>(base + off);
+    off += bytes;
+    return r;
+  }
+  bool ok() const { return off <= cap; }
+};
+
+__device__ __forceinline__ float lrelu(float v, float slope) { return v > 0.f ? v : v * slope; }
+// derivative of LeakyReLU recovered from the activation's OUTPUT (sign is preserved; 0 -> slope,
+// as torch's leaky_relu_backward does for input == 0)
+__device__ __forceinline__ float lrelu_grad_from_out(float h, float slope) { return h > 0.f ? 1.f : slope; }
+
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+}  // namespace hcg

@@ -1,0 +1,650 @@
+// General layer-wise path of the GCN hot path (any graph size, any H/F): forward and backward.
+//
+//   conv layer l :  T = h_in · W_l^T            k_gemm      (GCNConv.lin,  reference model/gcn.py:18-20,27-29)
+//                   h = lrelu(Â·T + b_l)         k_agg       (GCNConv.propagate + bias + LeakyReLU, :58-63)
+//   pooling      :  emb = [max ‖ mean]           k_pool      (global_max_pool / global_mean_pool, :65-66)
+//   readout      :  z = lrelu(z·W^T + b) ...     k_gemm      (readout MLP, :70-71)
+//
+// Â = D^-1/2 (A + I) D^-1/2 lives in the dst-sorted CSR built by hcg_collate; every reduction
+// (neighbour sum, segment max/mean, weight-gradient sums) walks its operands in a fixed order,
+// so there are no floating-point atomics and results are run-to-run identical.
+#include "hcg_common.cuh"
+
+namespace hcg {
+
+// ==========================================================================================
+// Dense tile GEMM:  C[M,Nc] = A[M,K] · op(B)  (+ epilogue)
+//   B_T = true : B is [Nc, K] row-major (a weight stored [out, in])      C = A · B^T
+//   B_T = false: B is [K, Nc] row-major                                    C = A · B
+// ==========================================================================================
+enum { EPI_NONE = 0, EPI_BIAS = 1, EPI_BIAS_LRELU = 2, EPI_MASK = 3, EPI_ADD = 4 };
+
+constexpr int GM = 128, GN = 64, GK = 32;
+
+template <bool B_T, int EPI>
+__global__ void __launch_bounds__(256)
+k_gemm(const float* __restrict__ A, const float* __restrict__ Bm, float* __restrict__ C,
+       int64_t M, int K, int Nc, const float* __restrict__ aux, float slope) {
+  __shared__ __align__(16) float As[GK][GM + 4];
+  __shared__ __align__(16) float Bs[GK][GN + 4];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;  // 16 x 16 threads, each 8 rows x 4 cols
+  const int64_t m0 = (int64_t)blockIdx.x * GM;
+  const int n0 = blockIdx.y * GN;
+
+  float acc[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < K; k0 += GK) {
+    const int kmax = min(GK, K - k0);
+    // A tile: a warp reads one row's GK consecutive k (rows of A are contiguous)
+#pragma unroll 4
+    for (int idx = tid; idx < GM * GK; idx += 256) {
+      int r = idx / GK, c = idx % GK;
+      float v = 0.f;
+      if (m0 + r < M && c < kmax) v = A[(m0 + r) * K + k0 + c];
+      As[c][r] = v;
+    }
+    if (B_T) {
+#pragma unroll 4
+      for (int idx = tid; idx < GN * GK; idx += 256) {
+        int n = idx / GK, c = idx % GK;
+        float v = 0.f;
+        if (n0 + n < Nc && c < kmax) v = Bm[(int64_t)(n0 + n) * K + k0 + c];
+        Bs[c][n] = v;
+      }
+    } else {
+#pragma unroll 4
+      for (int idx = tid; idx < GN * GK; idx += 256) {
+        int c = idx / GN, n = idx % GN;
+        float v = 0.f;
+        if (n0 + n < Nc && c < kmax) v = Bm[(int64_t)(k0 + c) * Nc + n0 + n];
+        Bs[c][n] = v;
+      }
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int kk = 0; kk < kmax; ++kk) {
+      float4 a0 = *reinterpret_cast<const float4*>(&As[kk][ty * 8]);
+      float4 a1 = *reinterpret_cast<const float4*>(&As[kk][ty * 8 + 4]);
+      float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+      float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    int64_t m = m0 + ty * 8 + i;
+    if (m >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int n = n0 + tx * 4 + j;
+      if (n >= Nc) continue;
+      float v = acc[i][j];
+      if (EPI == EPI_BIAS) v += aux[n];
+      if (EPI == EPI_BIAS_LRELU) v = lrelu(v + aux[n], slope);
+      if (EPI == EPI_MASK) v *= lrelu_grad_from_out(aux[m * Nc + n], slope);
+      if (EPI == EPI_ADD) v += aux[m * Nc + n];
+      C[m * Nc + n] = v;
+    }
+  }
+}
+
+template <bool B_T>
+static int launch_gemm(const float* A, const float* Bm, float* C, int64_t M, int K, int Nc, int epi,
+                       const float* aux, float slope, cudaStream_t st) {
+  if (M == 0 || Nc == 0) return HCG_OK;
+  dim3 grid((unsigned)cdiv(M, GM), (unsigned)cdiv(Nc, GN));
+  switch (epi) {
+    case EPI_NONE: k_gemm<B_T, EPI_NONE><<<grid, 256, 0, st>>>(A, Bm, C, M, K, Nc, aux, slope); break;
+    case EPI_BIAS: k_gemm<B_T, EPI_BIAS><<<grid, 256, 0, st>>>(A, Bm, C, M, K, Nc, aux, slope); break;
+    case EPI_BIAS_LRELU: k_gemm<B_T, EPI_BIAS_LRELU><<<grid, 256, 0, st>>>(A, Bm, C, M, K, Nc, aux, slope); break;
+    case EPI_MASK: k_gemm<B_T, EPI_MASK><<<grid, 256, 0, st>>>(A, Bm, C, M, K, Nc, aux, slope); break;
+    case EPI_ADD: k_gemm<B_T, EPI_ADD><<<grid, 256, 0, st>>>(A, Bm, C, M, K, Nc, aux, slope); break;
+    default: return set_err(HCG_ERR_INVALID_ARG, "bad gemm epilogue %d", epi);
+  }
+  HCG_LAUNCH_OK("k_gemm");
+  return HCG_OK;
+}
+
+// ==========================================================================================
+// Sparse aggregation  out[i] = act( bias + sum_{k in row i} norm_k · T[col[k]] + selfnorm_i · T[i] )
+// A group of `lpr` lanes owns one destination row; each lane VEC consecutive features.
+// Neighbours are visited in CSR order (= original edge order), the self-loop last, exactly the
+// order in which the reference's index_add_ accumulates.
+// ==========================================================================================
+template <int VEC>
+struct Vec;
+template <>
+struct Vec<4> {
+  float4 v;
+  __device__ __forceinline__ void zero() { v = make_float4(0.f, 0.f, 0.f, 0.f); }
+  __device__ __forceinline__ void load(const float* p) { v = ldg4(p); }
+  __device__ __forceinline__ void fma(float w, const Vec<4>& o) {
+    v.x = fmaf(w, o.v.x, v.x); v.y = fmaf(w, o.v.y, v.y); v.z = fmaf(w, o.v.z, v.z); v.w = fmaf(w, o.v.w, v.w);
+  }
+  __device__ __forceinline__ float get(int i) const { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
+  __device__ __forceinline__ void set(int i, float f) { if (i == 0) v.x = f; else if (i == 1) v.y = f; else if (i == 2) v.z = f; else v.w = f; }
+  __device__ __forceinline__ void store(float* p) const { *reinterpret_cast<float4*>(p) = v; }
+};
+template <>
+struct Vec<1> {
+  float v;
+  __device__ __forceinline__ void zero() { v = 0.f; }
+  __device__ __forceinline__ void load(const float* p) { v = __ldg(p); }
+  __device__ __forceinline__ void fma(float w, const Vec<1>& o) { v = fmaf(w, o.v, v); }
+  __device__ __forceinline__ float get(int) const { return v; }
+  __device__ __forceinline__ void set(int, float f) { v = f; }
+  __device__ __forceinline__ void store(float* p) const { *p = v; }
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+k_agg(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ dis,
+      const float* __restrict__ ew, const float* __restrict__ selfw, float fill,
+      const float* __restrict__ T, const float* __restrict__ bias, float* __restrict__ out,
+      int64_t N, int H, int lpr, int act, float slope) {
+  const int rows_per_block = 256 / lpr;
+  const int64_t i = (int64_t)blockIdx.x * rows_per_block + threadIdx.x / lpr;
+  const int sub = threadIdx.x % lpr;
+  if (i >= N) return;
+  const int beg = rowptr[i], end = rowptr[i + 1];
+  const float di = dis[i];
+  const float sw = selfw ? selfw[i] : fill;
+  const float self_norm = (di * sw) * di;
+  for (int c = sub * VEC; c < H; c += lpr * VEC) {
+    Vec<VEC> acc;
+    acc.zero();
+    int k = beg;
+    for (; k + 4 <= end; k += 4) {  // 4 independent gathers in flight
+      int j0 = col[k], j1 = col[k + 1], j2 = col[k + 2], j3 = col[k + 3];
+      float w0 = dis[j0], w1 = dis[j1], w2 = dis[j2], w3 = dis[j3];
+      if (ew) { w0 *= ew[k]; w1 *= ew[k + 1]; w2 *= ew[k + 2]; w3 *= ew[k + 3]; }
+      Vec<VEC> t0, t1, t2, t3;
+      t0.load(T + (int64_t)j0 * H + c); t1.load(T + (int64_t)j1 * H + c);
+      t2.load(T + (int64_t)j2 * H + c); t3.load(T + (int64_t)j3 * H + c);
+      acc.fma(w0 * di, t0); acc.fma(w1 * di, t1); acc.fma(w2 * di, t2); acc.fma(w3 * di, t3);
+    }
+    for (; k < end; ++k) {
+      int j = col[k];
+      float w = dis[j];
+      if (ew) w *= ew[k];
+      Vec<VEC> t;
+      t.load(T + (int64_t)j * H + c);
+      acc.fma(w * di, t);
+    }
+    Vec<VEC> ts;
+    ts.load(T + i * H + c);
+    acc.fma(self_norm, ts);
+#pragma unroll
+    for (int q = 0; q < VEC; ++q) {
+      float v = acc.get(q);
+      if (bias) v += bias[c + q];
+      if (act) v = lrelu(v, slope);
+      acc.set(q, v);
+    }
+    acc.store(out + i * H + c);
+  }
+}
+
+static int lanes_per_row(int H, int vec) {
+  int need = (H + vec - 1) / vec;
+  int l = 1;
+  while (l < need && l < 32) l <<= 1;
+  return l;
+}
+
+static int launch_agg(const int32_t* rowptr, const int32_t* col, const float* dis, const float* ew,
+                      const float* selfw, float fill, const float* T, const float* bias, float* out,
+                      int64_t N, int H, int act, float slope, cudaStream_t st) {
+  if (N == 0) return HCG_OK;
+  const bool vec4 = (H % 4 == 0) && ((reinterpret_cast<uintptr_t>(T) | reinterpret_cast<uintptr_t>(out)) % 16 == 0);
+  if (vec4) {
+    int lpr = lanes_per_row(H, 4);
+    k_agg<4><<<(unsigned)cdiv(N, 256 / lpr), 256, 0, st>>>(rowptr, col, dis, ew, selfw, fill, T, bias, out, N, H, lpr, act, slope);
+  } else {
+    int lpr = lanes_per_row(H, 1);
+    k_agg<1><<<(unsigned)cdiv(N, 256 / lpr), 256, 0, st>>>(rowptr, col, dis, ew, selfw, fill, T, bias, out, N, H, lpr, act, slope);
+  }
+  HCG_LAUNCH_OK("k_agg");
+  return HCG_OK;
+}
+
+// ==========================================================================================
+// Segmented pooling: emb[g] = [ max_i h[i] ‖ mean_i h[i] ] over the nodes of graph g
+// (a lane group per graph, nodes walked in order: the mean's sum order is the node order).
+// ==========================================================================================
+__global__ void __launch_bounds__(256)
+k_pool(const float* __restrict__ h, const int32_t* __restrict__ graph_ptr, int64_t B, int H, int lpr,
+       float* __restrict__ emb) {
+  const int gpb = 256 / lpr;
+  const int64_t g = (int64_t)blockIdx.x * gpb + threadIdx.x / lpr;
+  const int sub = threadIdx.x % lpr;
+  if (g >= B) return;
+  const int beg = graph_ptr[g], end = graph_ptr[g + 1];
+  const int n = end - beg;
+  for (int c = sub; c < H; c += lpr) {
+    float mx = -INFINITY, sum = 0.f;
+    int i = beg;
+    for (; i + 4 <= end; i += 4) {
+      float v0 = __ldg(h + (int64_t)i * H + c), v1 = __ldg(h + (int64_t)(i + 1) * H + c);
+      float v2 = __ldg(h + (int64_t)(i + 2) * H + c), v3 = __ldg(h + (int64_t)(i + 3) * H + c);
+      mx = fmaxf(fmaxf(mx, v0), fmaxf(v1, fmaxf(v2, v3)));
+      sum += v0; sum += v1; sum += v2; sum += v3;
+    }
+    for (; i < end; ++i) {
+      float v = __ldg(h + (int64_t)i * H + c);
+      mx = fmaxf(mx, v);
+      sum += v;
+    }
+    // an empty graph cannot come out of PyG collate; define it as zeros rather than -inf / NaN
+    emb[g * 2 * H + c] = n > 0 ? mx : 0.f;
+    emb[g * 2 * H + H + c] = n > 0 ? sum / (float)n : 0.f;
+  }
+}
+
+// Backward of pooling fused with the LeakyReLU derivative of the last conv layer:
+//   gA[i][c] = ( g_mean[g][c] / n_g + [h[i][c] == max] · g_max[g][c] / ties ) · lrelu'(h[i][c])
+// Ties share the gradient evenly, as torch's scatter_reduce(amax) backward does.
+__global__ void __launch_bounds__(256)
+k_pool_bwd(const float* __restrict__ h, const float* __restrict__ emb, const float* __restrict__ g_emb,
+           const int32_t* __restrict__ graph_ptr, int64_t B, int H, int lpr, float slope,
+           float* __restrict__ gA) {
+  const int gpb = 256 / lpr;
+  const int64_t g = (int64_t)blockIdx.x * gpb + threadIdx.x / lpr;
+  const int sub = threadIdx.x % lpr;
+  if (g >= B) return;
+  const int beg = graph_ptr[g], end = graph_ptr[g + 1];
+  const int n = end - beg;
+  if (n <= 0) return;
+  for (int c = sub; c < H; c += lpr) {
+    const float mx = emb[g * 2 * H + c];
+    const float gmax = g_emb[g * 2 * H + c];
+    const float gmean = g_emb[g * 2 * H + H + c] / (float)n;
+    int ties = 0;
+    for (int i = beg; i < end; ++i) ties += (__ldg(h + (int64_t)i * H + c) == mx) ? 1 : 0;
+    const float gm = ties > 0 ? gmax / (float)ties : 0.f;
+    for (int i = beg; i < end; ++i) {
+      float v = __ldg(h + (int64_t)i * H + c);
+      float gg = gmean + (v == mx ? gm : 0.f);
+      gA[(int64_t)i * H + c] = gg * lrelu_grad_from_out(v, slope);
+    }
+  }
+}
+
+// ==========================================================================================
+// Deterministic reduction over rows:  out[P,Q] = sum_n X[n][p] · Y[n][q]   (weight gradients)
+// stage 1: each block owns a contiguous chunk of rows and one 64x64 tile of [P,Q] -> partials
+// stage 2: partials summed in chunk order.
+// ==========================================================================================
+constexpr int XR = 32;  // rows staged per step
+
+__global__ void __launch_bounds__(256)
+k_xty_partial(const float* __restrict__ X, const float* __restrict__ Y, int64_t Nrows, int P, int Q,
+              int64_t rows_per_chunk, float* __restrict__ partial) {
+  __shared__ __align__(16) float Xs[XR][64 + 4];
+  __shared__ __align__(16) float Ys[XR][64 + 4];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int p0 = blockIdx.y * 64, q0 = blockIdx.z * 64;
+  const int64_t r_beg = (int64_t)blockIdx.x * rows_per_chunk;
+  const int64_t r_end = min(Nrows, r_beg + rows_per_chunk);
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int64_t r0 = r_beg; r0 < r_end; r0 += XR) {
+    for (int idx = tid; idx < XR * 64; idx += 256) {
+      int r = idx >> 6, c = idx & 63;
+      int64_t row = r0 + r;
+      Xs[r][c] = (row < r_end && p0 + c < P) ? X[row * P + p0 + c] : 0.f;
+      Ys[r][c] = (row < r_end && q0 + c < Q) ? Y[row * Q + q0 + c] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int r = 0; r < XR; ++r) {
+      float4 a = *reinterpret_cast<const float4*>(&Xs[r][ty * 4]);
+      float4 b = *reinterpret_cast<const float4*>(&Ys[r][tx * 4]);
+      float aa[4] = {a.x, a.y, a.z, a.w}, bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(aa[i], bb[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  float* dst = partial + (int64_t)blockIdx.x * P * Q;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    int p = p0 + ty * 4 + i;
+    if (p >= P) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int q = q0 + tx * 4 + j;
+      if (q < Q) dst[(int64_t)p * Q + q] = acc[i][j];
+    }
+  }
+}
+
+// column sums of X[n][p] over a chunk of rows (bias gradients)
+__global__ void __launch_bounds__(256)
+k_colsum_partial(const float* __restrict__ X, int64_t Nrows, int P, int64_t rows_per_chunk,
+                 float* __restrict__ partial) {
+  const int64_t r_beg = (int64_t)blockIdx.x * rows_per_chunk;
+  const int64_t r_end = min(Nrows, r_beg + rows_per_chunk);
+  for (int p = threadIdx.x; p < P; p += blockDim.x) {
+    float s = 0.f;
+    for (int64_t r = r_beg; r < r_end; ++r) s += X[r * P + p];
+    partial[(int64_t)blockIdx.x * P + p] = s;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_reduce_partials(const float* __restrict__ partial, int chunks, int64_t elems, float* __restrict__ out) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= elems) return;
+  float s = 0.f;
+  for (int c = 0; c < chunks; ++c) s += partial[(int64_t)c * elems + e];
+  out[e] = s;
+}
+
+constexpr int kMaxChunks = kNumSMs * 4;
+
+static int64_t pick_chunks(int64_t rows, int tiles) {
+  int64_t want = kMaxChunks / (tiles > 0 ? tiles : 1);
+  if (want < 1) want = 1;
+  int64_t by_rows = cdiv(rows, 256);  // at least 256 rows per chunk
+  if (by_rows < 1) by_rows = 1;
+  return want < by_rows ? want : by_rows;
+}
+
+static size_t xty_partial_elems(int64_t rows, int P, int Q) {
+  int tiles = (int)(cdiv(P, 64) * cdiv(Q, 64));
+  return (size_t)pick_chunks(rows, tiles) * P * Q;
+}
+
+static int launch_xty(const float* X, const float* Y, int64_t rows, int P, int Q, float* partial, float* out,
+                      cudaStream_t st) {
+  int tiles = (int)(cdiv(P, 64) * cdiv(Q, 64));
+  int64_t chunks = pick_chunks(rows, tiles);
+  int64_t rpc = cdiv(rows > 0 ? rows : 1, chunks);
+  dim3 grid((unsigned)chunks, (unsigned)cdiv(P, 64), (unsigned)cdiv(Q, 64));
+  k_xty_partial<<<grid, 256, 0, st>>>(X, Y, rows, P, Q, rpc, partial);
+  HCG_LAUNCH_OK("k_xty_partial");
+  k_reduce_partials<<<(unsigned)cdiv((int64_t)P * Q, 256), 256, 0, st>>>(partial, (int)chunks, (int64_t)P * Q, out);
+  HCG_LAUNCH_OK("k_reduce_partials");
+  return HCG_OK;
+}
+
+static int launch_colsum(const float* X, int64_t rows, int P, float* partial, float* out, cudaStream_t st) {
+  int64_t chunks = pick_chunks(rows, 1);
+  int64_t rpc = cdiv(rows > 0 ? rows : 1, chunks);
+  k_colsum_partial<<<(unsigned)chunks, 256, 0, st>>>(X, rows, P, rpc, partial);
+  HCG_LAUNCH_OK("k_colsum_partial");
+  k_reduce_partials<<<(unsigned)cdiv(P, 256), 256, 0, st>>>(partial, (int)chunks, P, out);
+  HCG_LAUNCH_OK("k_reduce_partials");
+  return HCG_OK;
+}
+
+// elementwise helpers of the readout backward
+__global__ void __launch_bounds__(256)
+k_mask_mul(const float* __restrict__ g, const float* __restrict__ act_out, int64_t n, float slope,
+           float* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = g[i] * lrelu_grad_from_out(act_out[i], slope);
+}
+
+// ------------------------------------------------------------------------------------------
+// argument checking shared by forward / backward
+// ------------------------------------------------------------------------------------------
+static int check_params(const HcgParams* p) {
+  HCG_REQUIRE(p != nullptr, HCG_ERR_INVALID_ARG, "params is NULL");
+  HCG_REQUIRE(p->F >= 1 && p->H >= 1 && p->C >= 1, HCG_ERR_INVALID_ARG, "bad dims F=%d H=%d C=%d", p->F, p->H, p->C);
+  HCG_REQUIRE(p->L >= 1 && p->L <= HCG_MAX_CONV, HCG_ERR_UNSUPPORTED, "n_convolutions=%d outside [1,%d]", p->L, HCG_MAX_CONV);
+  HCG_REQUIRE(p->R >= 1 && p->R <= HCG_MAX_READOUT, HCG_ERR_UNSUPPORTED, "readout_layers=%d outside [1,%d]", p->R, HCG_MAX_READOUT);
+  int d = 2 * p->H;
+  for (int k = 0; k < p->R - 1; ++k) {
+    d /= 2;
+    HCG_REQUIRE(d >= 1, HCG_ERR_UNSUPPORTED, "readout width reaches 0 at layer %d", k);
+  }
+  for (int l = 0; l < p->L; ++l)
+    HCG_REQUIRE(p->conv_w[l] && p->conv_b[l], HCG_ERR_INVALID_ARG, "conv layer %d parameter pointer is NULL", l);
+  for (int k = 0; k < p->R; ++k)
+    HCG_REQUIRE(p->ro_w[k] && p->ro_b[k], HCG_ERR_INVALID_ARG, "readout layer %d parameter pointer is NULL", k);
+  return HCG_OK;
+}
+
+static int check_graph(const HcgGraph* g, bool need_transpose) {
+  HCG_REQUIRE(g != nullptr, HCG_ERR_INVALID_ARG, "graph is NULL");
+  HCG_REQUIRE(g->N >= 0 && g->E >= 0 && g->B >= 0, HCG_ERR_INVALID_ARG, "negative graph sizes");
+  HCG_REQUIRE(g->rowptr && g->dis && g->graph_ptr, HCG_ERR_INVALID_ARG, "graph rowptr/dis/graph_ptr is NULL");
+  HCG_REQUIRE(g->E == 0 || g->col, HCG_ERR_INVALID_ARG, "graph col is NULL");
+  if (need_transpose)
+    HCG_REQUIRE(g->t_rowptr && (g->E == 0 || g->t_col), HCG_ERR_INVALID_ARG,
+                "backward needs the transposed CSR (collate with HCG_COLLATE_TRANSPOSE)");
+  if (g->ew0) HCG_REQUIRE(g->selfw0 && g->dis0, HCG_ERR_INVALID_ARG, "weighted layer-0 override is incomplete");
+  return HCG_OK;
+}
+
+static inline int ro_in_dim(const HcgParams* p, int k) {
+  int d = 2 * p->H;
+  for (int i = 0; i < k; ++i) d /= 2;
+  return d;
+}
+static inline int ro_out_dim(const HcgParams* p, int k) { return k == p->R - 1 ? p->C : ro_in_dim(p, k) / 2; }
+static inline int max_ro_dim(const HcgParams* p) {
+  int m = 2 * p->H;
+  return m > p->C ? m : p->C;
+}
+
+struct FwdWs {
+  float* T;
+  float* act[2];
+  float* hid[HCG_MAX_READOUT];
+  size_t bytes;
+};
+
+static FwdWs carve_fwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
+  Carver c(ws, (size_t)-1);
+  FwdWs w{};
+  w.T = c.take<float>((size_t)N * p->H + 4);
+  w.act[0] = c.take<float>((size_t)N * p->H + 4);
+  w.act[1] = c.take<float>((size_t)N * p->H + 4);
+  for (int k = 0; k < p->R - 1; ++k) w.hid[k] = c.take<float>((size_t)B * ro_out_dim(p, k) + 4);
+  w.bytes = c.off;
+  return w;
+}
+
+struct BwdWs {
+  float *gA, *gT, *partial, *gz[2], *gemb;
+  size_t bytes;
+};
+
+static BwdWs carve_bwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
+  Carver c(ws, (size_t)-1);
+  BwdWs w{};
+  w.gA = c.take<float>((size_t)N * p->H + 4);
+  w.gT = c.take<float>((size_t)N * p->H + 4);
+  size_t pe = 0;
+  for (int l = 0; l < p->L; ++l) {
+    size_t e = xty_partial_elems(N, p->H, l == 0 ? p->F : p->H);
+    pe = e > pe ? e : pe;
+  }
+  for (int k = 0; k < p->R; ++k) {
+    size_t e = xty_partial_elems(B, ro_out_dim(p, k), ro_in_dim(p, k));
+    pe = e > pe ? e : pe;
+  }
+  size_t cs = (size_t)kMaxChunks * (size_t)(p->H > max_ro_dim(p) ? p->H : max_ro_dim(p));
+  pe = cs > pe ? cs : pe;
+  w.partial = c.take<float>(pe + 4);
+  w.gz[0] = c.take<float>((size_t)B * max_ro_dim(p) + 4);
+  w.gz[1] = c.take<float>((size_t)B * max_ro_dim(p) + 4);
+  w.gemb = c.take<float>((size_t)B * 2 * p->H + 4);
+  w.bytes = c.off;
+  return w;
+}
+
+}  // namespace hcg
+
+using namespace hcg;
+
+extern "C" size_t hcg_forward_workspace_bytes(int64_t N, int64_t E, int64_t B, const HcgParams* p) {
+  (void)E;
+  if (!p || check_params(p)) return 0;
+  return carve_fwd(nullptr, N, B, p).bytes;
+}
+
+extern "C" size_t hcg_backward_workspace_bytes(int64_t N, int64_t E, int64_t B, const HcgParams* p) {
+  (void)E;
+  if (!p || check_params(p)) return 0;
+  return carve_bwd(nullptr, N, B, p).bytes;
+}
+
+extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParams* p, float* out, float* emb,
+                               const HcgSaved* saved, void* ws, size_t ws_bytes, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = check_params(p);
+  if (rc) return rc;
+  rc = check_graph(g, false);
+  if (rc) return rc;
+  HCG_REQUIRE(out && emb && ws, HCG_ERR_INVALID_ARG, "NULL out/emb/workspace");
+  HCG_REQUIRE(g->N == 0 || x, HCG_ERR_INVALID_ARG, "x is NULL");
+  FwdWs w = carve_fwd(ws, g->N, g->B, p);
+  HCG_REQUIRE(ws_bytes >= w.bytes, HCG_ERR_WORKSPACE, "forward workspace too small: %zu < %zu", ws_bytes, w.bytes);
+  const int64_t N = g->N, B = g->B;
+  const int H = p->H;
+
+  const float* h_in = x;
+  int k_in = p->F;
+  float* h_out = nullptr;
+  for (int l = 0; l < p->L; ++l) {
+    rc = launch_gemm<true>(h_in, p->conv_w[l], w.T, N, k_in, H, EPI_NONE, nullptr, p->slope, st);
+    if (rc) return rc;
+    h_out = saved ? saved->acts[l] : w.act[l & 1];
+    HCG_REQUIRE(h_out != nullptr, HCG_ERR_INVALID_ARG, "saved->acts[%d] is NULL", l);
+    const bool weighted0 = (l == 0 && g->ew0 != nullptr);
+    rc = launch_agg(g->rowptr, g->col, weighted0 ? g->dis0 : g->dis, weighted0 ? g->ew0 : nullptr,
+                    weighted0 ? g->selfw0 : nullptr, g->fill, w.T, p->conv_b[l], h_out, N, H, 1, p->slope, st);
+    if (rc) return rc;
+    h_in = h_out;
+    k_in = H;
+  }
+  if (B > 0) {
+    int lpr = lanes_per_row(H, 1);
+    k_pool<<<(unsigned)cdiv(B, 256 / lpr), 256, 0, st>>>(h_out, g->graph_ptr, B, H, lpr, emb);
+    HCG_LAUNCH_OK("k_pool");
+  }
+  const float* z = emb;
+  for (int k = 0; k < p->R; ++k) {
+    const bool last = k == p->R - 1;
+    float* zo = last ? out : (saved ? saved->hid[k] : w.hid[k]);
+    HCG_REQUIRE(zo != nullptr, HCG_ERR_INVALID_ARG, "saved->hid[%d] is NULL", k);
+    rc = launch_gemm<true>(z, p->ro_w[k], zo, B, ro_in_dim(p, k), ro_out_dim(p, k),
+                           last ? EPI_BIAS : EPI_BIAS_LRELU, p->ro_b[k], p->slope, st);
+    if (rc) return rc;
+    z = zo;
+  }
+  return HCG_OK;
+}
+
+extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgParams* p, const HcgSaved* saved,
+                                const float* emb, const float* g_out, const float* g_emb,
+                                const HcgGrads* grads, float* g_x, void* ws, size_t ws_bytes, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = check_params(p);
+  if (rc) return rc;
+  rc = check_graph(g, true);
+  if (rc) return rc;
+  HCG_REQUIRE(saved && emb && grads && ws, HCG_ERR_INVALID_ARG, "NULL saved/emb/grads/workspace");
+  HCG_REQUIRE(g_out || g_emb, HCG_ERR_INVALID_ARG, "both g_out and g_emb are NULL");
+  for (int l = 0; l < p->L; ++l)
+    HCG_REQUIRE(saved->acts[l] && grads->conv_w[l] && grads->conv_b[l], HCG_ERR_INVALID_ARG, "NULL saved act / grad pointer at conv %d", l);
+  for (int k = 0; k < p->R; ++k)
+    HCG_REQUIRE(grads->ro_w[k] && grads->ro_b[k] && (k == p->R - 1 || saved->hid[k]), HCG_ERR_INVALID_ARG,
+                "NULL saved hid / grad pointer at readout %d", k);
+  BwdWs w = carve_bwd(ws, g->N, g->B, p);
+  HCG_REQUIRE(ws_bytes >= w.bytes, HCG_ERR_WORKSPACE, "backward workspace too small: %zu < %zu", ws_bytes, w.bytes);
+  const int64_t N = g->N, B = g->B;
+  const int H = p->H;
+
+  // ---- readout MLP backward -------------------------------------------------------------
+  const float* gemb_total = g_emb;
+  if (g_out) {
+    const float* gz = g_out;  // gradient w.r.t. the (post-activation) output of layer k
+    int pp = 0;
+    for (int k = p->R - 1; k >= 0; --k) {
+      const int din = ro_in_dim(p, k), dout = ro_out_dim(p, k);
+      const float* zin = k == 0 ? emb : saved->hid[k - 1];
+      const float* gpre = gz;
+      if (k != p->R - 1) {  // through the LeakyReLU of this hidden layer
+        float* buf = w.gz[pp]; pp ^= 1;
+        if (B * dout > 0) {
+          k_mask_mul<<<(unsigned)cdiv(B * dout, 256), 256, 0, st>>>(gz, saved->hid[k], B * dout, p->slope, buf);
+          HCG_LAUNCH_OK("k_mask_mul");
+        }
+        gpre = buf;
+      }
+      rc = launch_xty(gpre, zin, B, dout, din, w.partial, grads->ro_w[k], st);
+      if (rc) return rc;
+      rc = launch_colsum(gpre, B, dout, w.partial, grads->ro_b[k], st);
+      if (rc) return rc;
+      // gradient w.r.t. this layer's input
+      float* gin = k == 0 ? w.gemb : w.gz[pp];
+      if (k != 0) pp ^= 1;
+      if (k == 0 && g_emb)
+        rc = launch_gemm<false>(gpre, p->ro_w[k], gin, B, dout, din, EPI_ADD, g_emb, p->slope, st);
+      else
+        rc = launch_gemm<false>(gpre, p->ro_w[k], gin, B, dout, din, EPI_NONE, nullptr, p->slope, st);
+      if (rc) return rc;
+      gz = gin;
+    }
+    gemb_total = w.gemb;
+  } else {
+    for (int k = 0; k < p->R; ++k) {
+      HCG_CUDA_OK(cudaMemsetAsync(grads->ro_w[k], 0, sizeof(float) * (size_t)ro_in_dim(p, k) * ro_out_dim(p, k), st));
+      HCG_CUDA_OK(cudaMemsetAsync(grads->ro_b[k], 0, sizeof(float) * (size_t)ro_out_dim(p, k), st));
+    }
+  }
+
+  // ---- pooling backward (+ LeakyReLU' of the last conv layer) -----------------------------
+  if (N > 0) HCG_CUDA_OK(cudaMemsetAsync(w.gA, 0, sizeof(float) * (size_t)N * H, st));  // nodes of no graph
+  if (B > 0) {
+    int lpr = lanes_per_row(H, 1);
+    k_pool_bwd<<<(unsigned)cdiv(B, 256 / lpr), 256, 0, st>>>(saved->acts[p->L - 1], emb, gemb_total, g->graph_ptr,
+                                                              B, H, lpr, p->slope, w.gA);
+    HCG_LAUNCH_OK("k_pool_bwd");
+  }
+
+  // ---- conv layers backward ---------------------------------------------------------------
+  for (int l = p->L - 1; l >= 0; --l) {
+    const float* h_in = l == 0 ? x : saved->acts[l - 1];
+    const int k_in = l == 0 ? p->F : H;
+    rc = launch_colsum(w.gA, N, H, w.partial, grads->conv_b[l], st);
+    if (rc) return rc;
+    const bool weighted0 = (l == 0 && g->ew0 != nullptr);
+    // gT = Â^T · gA  (transposed CSR; no bias, no activation)
+    rc = launch_agg(g->t_rowptr, g->t_col, weighted0 ? g->dis0 : g->dis, weighted0 ? g->t_ew0 : nullptr,
+                    weighted0 ? g->selfw0 : nullptr, g->fill, w.gA, nullptr, w.gT, N, H, 0, p->slope, st);
+    if (rc) return rc;
+    rc = launch_xty(w.gT, h_in, N, H, k_in, w.partial, grads->conv_w[l], st);
+    if (rc) return rc;
+    if (l > 0) {
+      rc = launch_gemm<false>(w.gT, p->conv_w[l], w.gA, N, H, k_in, EPI_MASK, saved->acts[l - 1], p->slope, st);
+      if (rc) return rc;
+    } else if (g_x) {
+      rc = launch_gemm<false>(w.gT, p->conv_w[0], g_x, N, H, k_in, EPI_NONE, nullptr, p->slope, st);
+      if (rc) return rc;
+    }
+  }
+  return HCG_OK;
+}

@@ -1,0 +1,283 @@
+"""Host-side glue between torch tensors and the C-ABI (include/hcg.h).
+
+Nothing here computes: tensors are only allocated, their device pointers handed to libhcg.so
+on torch's current CUDA stream.  Inputs living in host memory are staged to the GPU first
+(that is the end-to-end path bench.py times); without a CUDA device every call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import torch
+
+from . import _lib
+
+LEAKY_SLOPE = 0.01  # nn.LeakyReLU() default used throughout reference model/gcn.py
+
+
+def _require_cuda() -> torch.device:
+    if not torch.cuda.is_available():
+        raise RuntimeError("hcatgnet_b200 needs a CUDA device (B200): there is no CPU implementation of the GCN path")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def to_device(t: torch.Tensor | None, device: torch.device, dtype=None) -> torch.Tensor | None:
+    if t is None:
+        return None
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    if t.device != device:
+        t = t.to(device, non_blocking=True)
+    return t.contiguous()
+
+
+def _ptr(t: torch.Tensor | None) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+def _stream(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _workspace(nbytes: int, device) -> torch.Tensor:
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+@dataclass
+class GraphPlan:
+    """Device-resident batch topology (the HcgGraph of include/hcg.h) built once per batch."""
+    N: int
+    E: int
+    B: int
+    rowptr: torch.Tensor
+    col: torch.Tensor
+    eid: torch.Tensor
+    dis: torch.Tensor
+    graph_ptr: torch.Tensor
+    fill: float = 1.0
+    t_rowptr: torch.Tensor | None = None
+    t_col: torch.Tensor | None = None
+    t_eid: torch.Tensor | None = None
+    ew0: torch.Tensor | None = None
+    t_ew0: torch.Tensor | None = None
+    selfw0: torch.Tensor | None = None
+    dis0: torch.Tensor | None = None
+    _keep: list = field(default_factory=list, repr=False)
+
+    @property
+    def has_transpose(self) -> bool:
+        return self.t_rowptr is not None
+
+    @property
+    def device(self):
+        return self.rowptr.device
+
+    def c_struct(self) -> _lib.HcgGraph:
+        return _lib.HcgGraph(
+            self.N, self.E, self.B, _ptr(self.rowptr), _ptr(self.col), _ptr(self.eid), _ptr(self.dis),
+            _ptr(self.graph_ptr), _ptr(self.t_rowptr), _ptr(self.t_col), _ptr(self.t_eid), self.fill,
+            _ptr(self.ew0), _ptr(self.t_ew0), _ptr(self.selfw0), _ptr(self.dis0))
+
+
+def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int, num_graphs: int,
+            edge_weight: torch.Tensor | None = None, improved: bool = False, transpose: bool = False,
+            fill: float = 1.0, validate: bool = True) -> GraphPlan:
+    """COO ``edge_index`` [2,E] int64 + sorted ``batch`` [N] int64 -> :class:`GraphPlan`.
+
+    Runs ``hcg_collate``.  ``improved`` only matters together with ``edge_weight`` (self-loop
+    fill 2.0), mirroring the behaviour of the reference's PyG path.
+    ``validate`` reads back one status word (a stream sync) and raises on bad indices / unsorted
+    batch; the kernels are memory-safe either way.
+    """
+    device = _require_cuda() if not edge_index.is_cuda else edge_index.device
+    lib = _lib.load()
+    if edge_index.dim() != 2 or edge_index.shape[0] != 2:
+        raise ValueError(f"edge_index must have shape [2, E], got {tuple(edge_index.shape)}")
+    ei = to_device(edge_index, device, torch.int64)
+    bt = to_device(batch, device, torch.int64)
+    ew = to_device(edge_weight, device, torch.float32)
+    N, E, B = int(num_nodes), int(ei.shape[1]), int(num_graphs)
+    if bt is not None and bt.numel() != N:
+        raise ValueError(f"batch has {bt.numel()} entries for {N} nodes")
+    if ew is not None and ew.numel() != E:
+        raise ValueError(f"edge_weight has {ew.numel()} entries for {E} edges")
+    if bt is None and B > 1:
+        raise ValueError("batch vector required when num_graphs > 1")
+    i32 = dict(dtype=torch.int32, device=device)
+    f32 = dict(dtype=torch.float32, device=device)
+    with torch.cuda.device(device):
+        plan = GraphPlan(N, E, B, torch.empty(N + 1, **i32), torch.empty(max(E, 1), **i32),
+                         torch.empty(max(E, 1), **i32), torch.empty(max(N, 1), **f32), torch.empty(B + 1, **i32),
+                         fill=float(fill))
+        flags = 0
+        if transpose:
+            flags |= _lib.HCG_COLLATE_TRANSPOSE
+            plan.t_rowptr = torch.empty(N + 1, **i32)
+            plan.t_col = torch.empty(max(E, 1), **i32)
+            plan.t_eid = torch.empty(max(E, 1), **i32)
+        if ew is not None:
+            plan.ew0 = torch.empty(max(E, 1), **f32)
+            plan.selfw0 = torch.empty(max(N, 1), **f32)
+            plan.dis0 = torch.empty(max(N, 1), **f32)
+            if transpose:
+                plan.t_ew0 = torch.empty(max(E, 1), **f32)
+        ws = _workspace(lib.hcg_collate_workspace_bytes(N, E, B, flags), device)
+        st = _stream(device)
+        _lib.check(lib.hcg_collate(
+            _ptr(ei), E, _ptr(bt), N, B, float(fill), _ptr(ew), 2.0 if improved else 1.0, flags,
+            _ptr(plan.rowptr), _ptr(plan.col), _ptr(plan.eid), _ptr(plan.dis), _ptr(plan.graph_ptr),
+            _ptr(plan.t_rowptr), _ptr(plan.t_col), _ptr(plan.t_eid),
+            _ptr(plan.ew0), _ptr(plan.t_ew0), _ptr(plan.selfw0), _ptr(plan.dis0),
+            _ptr(ws), ws.numel(), st))
+        if validate:
+            _lib.check(lib.hcg_collate_status(_ptr(ws), st))
+        else:
+            ws.record_stream(torch.cuda.current_stream(device))
+    return plan
+
+
+@dataclass
+class NetDims:
+    F: int
+    H: int
+    L: int
+    R: int
+    C: int
+    slope: float = LEAKY_SLOPE
+
+    def ro_in(self, k: int) -> int:
+        d = 2 * self.H
+        for _ in range(k):
+            d //= 2
+        return d
+
+    def ro_out(self, k: int) -> int:
+        return self.C if k == self.R - 1 else self.ro_in(k) // 2
+
+
+def _params_struct(dims: NetDims, tensors) -> _lib.HcgParams:
+    """tensors: conv_w0, conv_b0, ..., ro_w0, ro_b0, ... (contiguous fp32 on the GPU)."""
+    p = _lib.HcgParams()
+    p.F, p.H, p.L, p.R, p.C, p.slope = dims.F, dims.H, dims.L, dims.R, dims.C, dims.slope
+    for l in range(dims.L):
+        p.conv_w[l] = tensors[2 * l].data_ptr()
+        p.conv_b[l] = tensors[2 * l + 1].data_ptr()
+    for k in range(dims.R):
+        p.ro_w[k] = tensors[2 * dims.L + 2 * k].data_ptr()
+        p.ro_b[k] = tensors[2 * dims.L + 2 * k + 1].data_ptr()
+    return p
+
+
+def _check_param_shapes(dims: NetDims, tensors) -> None:
+    if len(tensors) != 2 * (dims.L + dims.R):
+        raise ValueError(f"expected {2 * (dims.L + dims.R)} parameter tensors, got {len(tensors)}")
+    for l in range(dims.L):
+        want = (dims.H, dims.F if l == 0 else dims.H)
+        if tuple(tensors[2 * l].shape) != want or tuple(tensors[2 * l + 1].shape) != (dims.H,):
+            raise ValueError(f"conv layer {l}: weight {tuple(tensors[2 * l].shape)} / bias "
+                             f"{tuple(tensors[2 * l + 1].shape)} do not match {want} / {(dims.H,)}")
+    for k in range(dims.R):
+        w, b = tensors[2 * dims.L + 2 * k], tensors[2 * dims.L + 2 * k + 1]
+        want = (dims.ro_out(k), dims.ro_in(k))
+        if tuple(w.shape) != want or tuple(b.shape) != (want[0],):
+            raise ValueError(f"readout layer {k}: weight {tuple(w.shape)} / bias {tuple(b.shape)} do not match {want}")
+
+
+def forward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, save: bool):
+    """One ``hcg_gcn_forward`` call.  Returns (out[B,C], emb[B,2H], saved tensors or None)."""
+    lib = _lib.load()
+    device = plan.device
+    if x.shape != (plan.N, dims.F):
+        raise ValueError(f"x has shape {tuple(x.shape)}, expected {(plan.N, dims.F)}")
+    f32 = dict(dtype=torch.float32, device=device)
+    with torch.cuda.device(device):
+        out = torch.empty(plan.B, dims.C, **f32)
+        emb = torch.empty(plan.B, 2 * dims.H, **f32)
+        pstruct = _params_struct(dims, params)
+        saved_t = None
+        saved_c = None
+        if save:
+            acts = [torch.empty(plan.N, dims.H, **f32) for _ in range(dims.L)]
+            hid = [torch.empty(plan.B, dims.ro_out(k), **f32) for k in range(dims.R - 1)]
+            saved_t = (acts, hid)
+            saved_c = _lib.HcgSaved()
+            for l, a in enumerate(acts):
+                saved_c.acts[l] = a.data_ptr()
+            for k, h in enumerate(hid):
+                saved_c.hid[k] = h.data_ptr()
+        ws = _workspace(lib.hcg_forward_workspace_bytes(plan.N, plan.E, plan.B, C.byref(pstruct)), device)
+        g = plan.c_struct()
+        _lib.check(lib.hcg_gcn_forward(C.byref(g), _ptr(x), C.byref(pstruct), _ptr(out), _ptr(emb),
+                                       C.byref(saved_c) if saved_c is not None else None,
+                                       _ptr(ws), ws.numel(), _stream(device)))
+        ws.record_stream(torch.cuda.current_stream(device))
+    return out, emb, saved_t
+
+
+def backward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, saved_t, emb, g_out, g_emb, need_gx: bool):
+    """One ``hcg_gcn_backward`` call.  Returns (g_x or None, list of parameter grads)."""
+    lib = _lib.load()
+    device = plan.device
+    f32 = dict(dtype=torch.float32, device=device)
+    with torch.cuda.device(device):
+        pstruct = _params_struct(dims, params)
+        acts, hid = saved_t
+        saved_c = _lib.HcgSaved()
+        for l, a in enumerate(acts):
+            saved_c.acts[l] = a.data_ptr()
+        for k, h in enumerate(hid):
+            saved_c.hid[k] = h.data_ptr()
+        # one flat slab for all parameter gradients (a single all-reduce buffer for data parallelism)
+        sizes = [p.numel() for p in params]
+        flat = torch.empty(sum(sizes), **f32)
+        grads, off = [], 0
+        for p_, n in zip(params, sizes):
+            grads.append(flat[off:off + n].view_as(p_))
+            off += n
+        gc = _lib.HcgGrads()
+        for l in range(dims.L):
+            gc.conv_w[l] = grads[2 * l].data_ptr()
+            gc.conv_b[l] = grads[2 * l + 1].data_ptr()
+        for k in range(dims.R):
+            gc.ro_w[k] = grads[2 * dims.L + 2 * k].data_ptr()
+            gc.ro_b[k] = grads[2 * dims.L + 2 * k + 1].data_ptr()
+        g_x = torch.empty(plan.N, dims.F, **f32) if need_gx else None
+        ws = _workspace(lib.hcg_backward_workspace_bytes(plan.N, plan.E, plan.B, C.byref(pstruct)), device)
+        g = plan.c_struct()
+        _lib.check(lib.hcg_gcn_backward(C.byref(g), _ptr(x), C.byref(pstruct), C.byref(saved_c), _ptr(emb),
+                                        _ptr(g_out), _ptr(g_emb), C.byref(gc), _ptr(g_x),
+                                        _ptr(ws), ws.numel(), _stream(device)))
+        ws.record_stream(torch.cuda.current_stream(device))
+    return g_x, grads
+
+
+class _GCNFunction(torch.autograd.Function):
+    """autograd node whose forward/backward are single C-ABI calls."""
+
+    @staticmethod
+    def forward(ctx, x, plan, dims, *params):
+        params = tuple(p.contiguous() for p in params)
+        need_grad = any(ctx.needs_input_grad)
+        if need_grad and not plan.has_transpose:
+            raise RuntimeError("this GraphPlan was collated without the transposed CSR; backward needs transpose=True")
+        out, emb, saved_t = forward_raw(plan, x, dims, params, save=need_grad)
+        if need_grad:
+            ctx.plan, ctx.dims, ctx.saved_t = plan, dims, saved_t
+            ctx.save_for_backward(x, emb, *params)
+        return out, emb
+
+    @staticmethod
+    def backward(ctx, g_out, g_emb):
+        x, emb, *params = ctx.saved_tensors
+        g_out = g_out.contiguous() if g_out is not None else None
+        g_emb = g_emb.contiguous() if g_emb is not None else None
+        g_x, grads = backward_raw(ctx.plan, x, ctx.dims, params, ctx.saved_t, emb, g_out, g_emb,
+                                  need_gx=ctx.needs_input_grad[0])
+        return (g_x, None, None, *grads)
+
+
+def gcn_apply(x: torch.Tensor, plan: GraphPlan, dims: NetDims, params):
+    """Differentiable GCN hot path: returns (out[B,C], emb[B,2H])."""
+    _check_param_shapes(dims, params)
+    return _GCNFunction.apply(x, plan, dims, *params)

@@ -1,0 +1,175 @@
+/*
+ * hcg.h — C-ABI of libhcg.so, the B200 (sm_100a) implementation of HCat-GNet's GCN hot path.
+ *
+ * The reference (EdAguilarB/hcatgnet) has no FFI of its own: its boundary is the Python
+ * torch.nn.Module `GCN` (reference model/gcn.py:9-76) whose arithmetic is delegated to
+ * torch_geometric.  Each entry point below replaces one group of PyG/ATen calls made on that
+ * path; the host-side mirror of the reference interface (hcatgnet_b200/model/gcn.py) binds
+ * them through ctypes.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every pointer is a DEVICE pointer unless the name ends
+ *    in `_host`;
+ *  - nothing is allocated inside: the caller supplies outputs and one scratch workspace whose
+ *    size comes from the matching `*_workspace_bytes` query;
+ *  - every call is asynchronous on `stream` (a cudaStream_t passed as void*) and returns 0
+ *    (HCG_OK) or an error code; `hcg_last_error()` gives the thread-local message;
+ *  - input-dependent errors (bad node index, unsorted batch vector) are recorded in a device
+ *    status word and surfaced by `hcg_collate_status` (one 4-byte read-back, synchronises);
+ *    the kernels themselves stay memory-safe by skipping offending entries;
+ *  - all reductions are atomic-free in floating point and therefore run-to-run deterministic.
+ */
+#ifndef HCG_H_
+#define HCG_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HCG_MAX_CONV 8
+#define HCG_MAX_READOUT 8
+
+enum {
+  HCG_OK = 0,
+  HCG_ERR_INVALID_ARG = 1,
+  HCG_ERR_UNSUPPORTED = 2,
+  HCG_ERR_WORKSPACE = 3,
+  HCG_ERR_CUDA = 4,
+  HCG_ERR_BAD_INDEX = 5,      /* edge_index entry outside [0, N) */
+  HCG_ERR_BAD_BATCH = 6       /* batch vector not sorted / outside [0, B) */
+};
+
+/* flags of hcg_collate */
+enum {
+  HCG_COLLATE_TRANSPOSE = 1   /* also build the src-sorted (transposed) CSR for the backward pass */
+};
+
+/*
+ * Batch topology produced by hcg_collate and consumed by forward/backward.
+ * Replaces what PyG recomputes in every GCNConv call: add_remaining_self_loops + scatter
+ * degree + deg^-1/2 + per-edge norm (gcn_norm; call sites reference model/gcn.py:58,62), and
+ * the implicit `batch`->segment bookkeeping of global_max_pool / global_mean_pool
+ * (reference model/gcn.py:65-66).
+ */
+typedef struct HcgGraph {
+  int64_t N;                 /* nodes in the batch */
+  int64_t E;                 /* edges as stored in edge_index (self-loops included) */
+  int64_t B;                 /* graphs in the batch */
+  const int32_t* rowptr;     /* [N+1] dst-sorted CSR over kept (non self-loop) edges */
+  const int32_t* col;        /* [E]   src of each CSR slot, stable in original edge order */
+  const int32_t* eid;        /* [E]   original edge id of each CSR slot */
+  const float* dis;          /* [N]   (in-degree + fill)^-1/2 of the UNWEIGHTED graph, 0 where infinite */
+  const int32_t* graph_ptr;  /* [B+1] first node of each graph (PyG Batch.ptr) */
+  const int32_t* t_rowptr;   /* [N+1] transposed (src-sorted) CSR, or NULL if not built */
+  const int32_t* t_col;      /* [E]   dst of each transposed slot */
+  const int32_t* t_eid;      /* [E] */
+  float fill;                /* self-loop weight of the unweighted graph (1.0) */
+  /* Layer-0 override, all NULL unless an explicit edge_weight was collated.  The reference
+   * hands edge_weight to conv1 only (model/gcn.py:127 vs :131), so conv layers >= 1 always
+   * use the unweighted normalisation above. */
+  const float* ew0;          /* [E] edge weight per CSR slot */
+  const float* t_ew0;        /* [E] edge weight per transposed slot */
+  const float* selfw0;       /* [N] self-loop weight per node */
+  const float* dis0;         /* [N] weighted-degree^-1/2 */
+} HcgGraph;
+
+/*
+ * Network parameters, laid out exactly as the reference state_dict tensors
+ * (reference model/gcn.py:18-45): conv weights [H, F_l] (out,in) row-major, conv biases [H],
+ * readout weights [d_out, d_in], readout biases [d_out]; d_0 = 2H, d_{k+1} = d_k / 2,
+ * last layer -> C.
+ */
+typedef struct HcgParams {
+  int32_t F;                 /* n_node_features */
+  int32_t H;                 /* embedding_dim */
+  int32_t L;                 /* n_convolutions (>= 1) */
+  int32_t R;                 /* readout_layers (>= 1) */
+  int32_t C;                 /* n_classes */
+  float slope;               /* LeakyReLU negative slope (0.01) */
+  const float* conv_w[HCG_MAX_CONV];
+  const float* conv_b[HCG_MAX_CONV];
+  const float* ro_w[HCG_MAX_READOUT];
+  const float* ro_b[HCG_MAX_READOUT];
+} HcgParams;
+
+/* Same shape as HcgParams' pointer arrays; receives d(loss)/d(param).  Written, not accumulated. */
+typedef struct HcgGrads {
+  float* conv_w[HCG_MAX_CONV];
+  float* conv_b[HCG_MAX_CONV];
+  float* ro_w[HCG_MAX_READOUT];
+  float* ro_b[HCG_MAX_READOUT];
+} HcgGrads;
+
+/*
+ * Activations kept by the forward pass for the backward pass (what autograd would save).
+ * acts: L buffers of [N, H] (post-LeakyReLU output of each conv layer);
+ * emb:  [B, 2H] graph embedding (max || mean)  — also a forward output;
+ * hid:  R-1 buffers [B, d_{k+1}] (post-LeakyReLU readout hidden layers).
+ */
+typedef struct HcgSaved {
+  float* acts[HCG_MAX_CONV];
+  float* hid[HCG_MAX_READOUT];
+} HcgSaved;
+
+const char* hcg_last_error(void);
+const char* hcg_version(void);
+
+/* ---- collate (replaces gcn_norm index work; north_star "batch-collate kernel") ------------ */
+
+size_t hcg_collate_workspace_bytes(int64_t N, int64_t E, int64_t B, int flags);
+
+/*
+ * edge_index: int64 [2, E] row-major (row 0 = src j, row 1 = dst i), as PyG stores it;
+ * batch:      int64 [N], sorted node->graph ids (PyG Batch.batch); may be NULL when B <= 1;
+ * fill:       self-loop weight of the unweighted normalisation (1.0 reproduces the reference);
+ * edge_weight: float [E] in original edge order or NULL.  With weights, `fill_w` is the weight
+ *             of added self-loops (2.0 when improved) and an existing self-loop edge keeps its
+ *             own weight (add_remaining_self_loops semantics).
+ * Outputs: rowptr[N+1], col[E], eid[E], dis[N], graph_ptr[B+1]; t_rowptr/t_col/t_eid only with
+ * HCG_COLLATE_TRANSPOSE; ew0[E], selfw0[N], dis0[N] (and t_ew0[E]) only when edge_weight != NULL.
+ * The first 4 bytes of `ws` hold the device status word read by hcg_collate_status.
+ */
+int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* batch, int64_t N, int64_t B,
+                float fill, const float* edge_weight, float fill_w, int flags,
+                int32_t* rowptr, int32_t* col, int32_t* eid, float* dis, int32_t* graph_ptr,
+                int32_t* t_rowptr, int32_t* t_col, int32_t* t_eid,
+                float* ew0, float* t_ew0, float* selfw0, float* dis0,
+                void* ws, size_t ws_bytes, void* stream);
+
+/* Synchronises `stream`, reads the status word of the last hcg_collate that used `ws`. */
+int hcg_collate_status(const void* ws, void* stream);
+
+/* ---- forward (replaces GCNConv x L, LeakyReLU, global max/mean pool, readout MLP) ---------- */
+
+size_t hcg_forward_workspace_bytes(int64_t N, int64_t E, int64_t B, const HcgParams* p);
+
+/*
+ * x: [N, F] fp32 row-major.  out: [B, C].  emb: [B, 2H] (max first, then mean).
+ * saved: NULL for inference; otherwise its buffers are filled for hcg_gcn_backward.
+ */
+int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParams* p,
+                    float* out, float* emb, const HcgSaved* saved,
+                    void* ws, size_t ws_bytes, void* stream);
+
+/* ---- backward (replaces autograd over the ops above) -------------------------------------- */
+
+size_t hcg_backward_workspace_bytes(int64_t N, int64_t E, int64_t B, const HcgParams* p);
+
+/*
+ * g_out: [B, C] gradient w.r.t. the network output, or NULL (= 0);
+ * g_emb: [B, 2H] extra gradient flowing into the graph embedding, or NULL;
+ * grads: receives parameter gradients;  g_x: [N, F] gradient w.r.t. x, or NULL to skip it.
+ * Needs the transposed CSR in `g` (HCG_COLLATE_TRANSPOSE).
+ */
+int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgParams* p, const HcgSaved* saved,
+                     const float* emb, const float* g_out, const float* g_emb,
+                     const HcgGrads* grads, float* g_x,
+                     void* ws, size_t ws_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HCG_H_ */
