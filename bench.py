@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""Benchmark of the GCN hot path: reaction graphs/s on synthetic screening batches.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--mode infer|train] [--batch B]
+    python bench.py --impl reference ...      # the CPU restatement of the reference's PyG path
+
+A step = one pass of the hot path over one synthetic batch delivered as PyG would deliver it
+(x fp32 [N,25], edge_index int64 [2,E], batch int64 [N]): hcg_collate (dst-sorted CSR, deg^-1/2,
+graph offsets) + hcg_gcn_forward (2 x GCNConv + LeakyReLU, max||mean pooling, readout MLP); in
+--mode train additionally hcg_gcn_backward, the NCCL all-reduce of the flat gradient (N > 1)
+and the Adam step.  Default workload = BASELINE.json configs[1]: screening inference, ~80-atom
+graphs, batch 16384 per GPU, 62 steps ~ 1 M graphs.
+
+`value` times the device-resident path with CUDA events (barrier + synchronize on both sides,
+max over ranks); `e2e` times the public nn.Module call with pinned HOST buffers, host->device
+copies and the device->host read of the predictions inside the timed region.  Prints ONE JSON
+line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = "reaction_graphs_per_sec"
+UNIT = "graphs/s"
+F_IN, HID, N_CONV, N_RO, N_CLS = 25, 64, 2, 2, 1
+POOL = 4  # distinct synthetic batches cycled through (4 x ~205 MB of inputs >> 126 MB L2)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=62)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--mode", default="infer", choices=["infer", "train"])
+    ap.add_argument("--batch", type=int, default=None, help="graphs per GPU per step (16384 infer, 4096 train)")
+    ap.add_argument("--hidden", type=int, default=HID)
+    ap.add_argument("--convs", type=int, default=N_CONV)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-profile", action="store_true")
+    a = ap.parse_args()
+    if a.batch is None:
+        a.batch = 16384 if a.mode == "infer" else 4096
+    a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
+    return a
+
+
+def workload_name(a):
+    kind = "screening inference" if a.mode == "infer" else "data-parallel training (fwd+bwd+allreduce+Adam)"
+    return (f"synthetic reaction graphs n~U[40,120] e=3n F={F_IN} H={a.hidden} L={a.convs}; {kind}; "
+            f"batch {a.batch}/GPU")
+
+
+def config_of(a, extra=None):
+    c = {"workload": workload_name(a), "mode": a.mode, "batch_per_gpu": a.batch, "hidden": a.hidden,
+         "n_convolutions": a.convs, "n_node_features": F_IN, "graphs_per_gpu_in_timed_region": a.batch * a.steps,
+         "l2_policy": f"inputs larger than L2: {POOL} distinct batches cycled", "parallelism": f"dp{a.gpus} (graphs sharded)"}
+    if extra:
+        c.update(extra)
+    return c
+
+
+# ----------------------------------------------------------------------------------------------
+# clocks sampling (nvidia-smi in a side process during the timed region)
+# ----------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU arm: the oracle (plain-torch restatement of the reference's PyG path) on the host cores
+# ----------------------------------------------------------------------------------------------
+def cpu_oracle_rate(a, sample_graphs: int, budget_s: float, mode: str):
+    """graphs/s of oracle/ref_gcn on `sample_graphs` synthetic graphs, all host threads."""
+    from hcatgnet_b200.synth import synth_batch
+    from oracle import ref_gcn
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    b = synth_batch(sample_graphs, F_IN, seed=20232023)
+    sd = ref_gcn.init_state_dict(F_IN, a.hidden, a.convs, N_RO, N_CLS)
+    if mode == "train":
+        sd = {k: v.requires_grad_(True) for k, v in sd.items()}
+        opt = torch.optim.Adam(list(sd.values()), lr=0.01, eps=1e-9)
+
+    def one():
+        if mode == "train":
+            opt.zero_grad()
+            out, _ = ref_gcn.forward(sd, b.x, b.edge_index, b.batch, b.num_graphs)
+            ref_gcn.rmse_loss(out, b.y).backward()
+            opt.step()
+        else:
+            with torch.no_grad():
+                ref_gcn.forward(sd, b.x, b.edge_index, b.batch, b.num_graphs)
+
+    one()
+    t0 = time.perf_counter(); one(); dt1 = time.perf_counter() - t0
+    iters = int(max(2, min(50, budget_s / max(dt1, 1e-3))))
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        one()
+    dt = (time.perf_counter() - t0) / iters
+    return sample_graphs / dt, cores, f"{iters} x {sample_graphs} graphs of the same generator (collated batch in RAM), torch {torch.__version__}, {cores} threads"
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample = min(a.batch, 2048)
+    from hcatgnet_b200.synth import synth_batch
+    from oracle import ref_gcn
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    b = synth_batch(sample, F_IN, seed=20232023)
+    sd = ref_gcn.init_state_dict(F_IN, a.hidden, a.convs, N_RO, N_CLS)
+    if a.mode == "train":
+        sd = {k: v.requires_grad_(True) for k, v in sd.items()}
+        opt = torch.optim.Adam(list(sd.values()), lr=0.01, eps=1e-9)
+
+    def one():
+        if a.mode == "train":
+            opt.zero_grad()
+            out, _ = ref_gcn.forward(sd, b.x, b.edge_index, b.batch, b.num_graphs)
+            ref_gcn.rmse_loss(out, b.y).backward()
+            opt.step()
+        else:
+            with torch.no_grad():
+                ref_gcn.forward(sd, b.x, b.edge_index, b.batch, b.num_graphs)
+
+    for _ in range(a.warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        one()
+    dt = time.perf_counter() - t0
+    v = sample * a.steps / dt
+    sample_txt = (f"each step = {sample} graphs (bounded sample of the {a.batch}-graph batch), oracle/ref_gcn.py "
+                  f"(plain-torch restatement of the PyG path; torch_geometric not installable), {cores} threads")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": dt / a.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_of(a),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample_txt},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ----------------------------------------------------------------------------------------------
+# algorithmic bytes per launch of each kernel (SURVEY.md §8d formulas)
+# ----------------------------------------------------------------------------------------------
+def algorithmic_bytes(name: str, N: int, E: int, B: int, F: int, H: int, layer_in: int | None = None):
+    csr = 4 * (N + 1) + 4 * E
+    table = {
+        "k_agg": 4 * N * H + csr + 4 * N + 4 * N * H,        # read T once, CSR, dis, write h
+        "k_gemm": None,                                        # depends on the layer; see below
+        "k_pool": 4 * N * H + 4 * (B + 1) + 8 * B * H,
+        "k_count": 16 * E + 0,                                 # + integer atomics into cnt (L2-resident)
+        "k_fill": 16 * E + 4 * (N + 1) + 8 * E,
+        "k_rowsort": 4 * (N + 1) + 8 * E + 8 * E,
+    }
+    return table.get(name)
+
+
+# ----------------------------------------------------------------------------------------------
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+        return
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product has no CPU path (use --impl reference for the CPU arm)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    else:
+        dist = None
+
+    import hcatgnet_b200 as pkg
+    from hcatgnet_b200 import _lib, ops
+    from hcatgnet_b200.synth import synth_batch
+    from hcatgnet_b200 import parallel
+
+    _lib.load()
+    opt = pkg.default_options(embedding_dim=a.hidden, n_convolutions=a.convs)
+    model = pkg.make_network("GCN", opt, F_IN).to(dev)
+    model.eval() if a.mode == "infer" else model.train()
+    dims = model._dims()
+    params = [p.detach() for p in model._flat_params()]
+
+    # synthetic pool: pinned host copies (e2e) and device-resident copies (value)
+    host = [synth_batch(a.batch, F_IN, seed=20232023 + 1000 * rank + i, pin=True) for i in range(POOL)]
+    devb = [pkg.Batch(b.x.to(dev), b.edge_index.to(dev), b.batch.to(dev), None, b.y.to(dev), None, b.num_graphs)
+            for b in host]
+    Ns = [b.num_nodes for b in host]
+    Es = [int(b.edge_index.shape[1]) for b in host]
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device(i):
+        b = devb[i % POOL]
+        if a.mode == "infer":
+            plan = ops.collate(b.edge_index, b.batch, b.num_nodes, b.num_graphs, validate=False)
+            with torch.no_grad():
+                out, _ = ops.gcn_apply(b.x, plan, dims, params)
+            return out
+        return parallel.dp_train_step(model, b, validate=False)
+
+    def step_e2e(i):
+        h = host[i % POOL]
+        b = pkg.Batch(h.x.to(dev, non_blocking=True), h.edge_index.to(dev, non_blocking=True),
+                      h.batch.to(dev, non_blocking=True), None, h.y.to(dev, non_blocking=True), None, h.num_graphs)
+        if a.mode == "infer":
+            with torch.no_grad():
+                out = model(b)
+            return out.cpu()
+        return parallel.dp_train_step(model, b).cpu()  # loss read back
+
+    def timed(fn, steps):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ev0.record()
+        for i in range(steps):
+            fn(i)
+        ev1.record()
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        if dist is not None:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    # ---- device-resident number --------------------------------------------------------------
+    for i in range(a.warmup):
+        step_device(i)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = _lib.launch_count()
+    ms = timed(step_device, a.steps)
+    launches = _lib.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    graphs_total = a.batch * a.steps * world
+    value = graphs_total / (ms * 1e-3)
+
+    # ---- end to end through the nn.Module API with host buffers ------------------------------
+    for i in range(a.warmup):
+        step_e2e(i)
+    t0 = time.perf_counter()
+    ms_e2e_dev = timed(step_e2e, a.steps)
+    wall_e2e = (time.perf_counter() - t0) * 1e3
+    ms_e2e = max(ms_e2e_dev, 0.0)
+    e2e_value = graphs_total / (ms_e2e * 1e-3)
+    h2d = int(np.mean([h.x.numel() * 4 + h.edge_index.numel() * 8 + h.batch.numel() * 8 + h.y.numel() * 4 for h in host]))
+    d2h = a.batch * N_CLS * 4 if a.mode == "infer" else 4
+
+    # ---- per-kernel device time (separate pass, same inputs) + roofline of the dominant kernel -
+    roofline, kernels = None, None
+    if rank == 0 and not a.no_profile:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+        torch.cuda.synchronize()
+        _lib.profile_enable(True)
+        for i in range(a.steps):
+            step_device(i)
+        torch.cuda.synchronize()
+        prof = _lib.profile_read()
+        _lib.profile_enable(False)
+        tot = sum(v[0] for v in prof.values()) or 1.0
+        kernels = {k: {"ms_per_launch": v[0] / v[1], "launches_per_step": v[1] / a.steps, "share": v[0] / tot}
+                   for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}
+        top = next(iter(kernels))
+        N, E = int(np.mean(Ns)), int(np.mean(Es))
+        ab = algorithmic_bytes(top, N, E, a.batch, F_IN, a.hidden)
+        if ab is not None:
+            sec = kernels[top]["ms_per_launch"] * 1e-3
+            ach = ab / sec / 1e9
+            roofline = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s",
+                        "frac": ach / peak, "traffic": None, "algorithmic_bytes_per_launch": ab,
+                        "ms_per_launch": kernels[top]["ms_per_launch"], "peak_source": peak_src,
+                        "share_of_step": kernels[top]["share"]}
+
+    cpu_baseline = None
+    if rank == 0 and not a.no_cpu_baseline:
+        v, cores, sample = cpu_oracle_rate(a, 2048, 12.0, a.mode)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": config_of(a, {"mean_nodes_per_batch": int(np.mean(Ns)), "mean_edges_per_batch": int(np.mean(Es))}),
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / a.steps, "wall_ms_per_step": wall_e2e / a.steps},
+            "gpu_launches": int(launches),
+            "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline,
+        }
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,13 @@
+"""hcatgnet_b200 — B200-native (sm_100a) implementation of HCat-GNet's GCN hot path.
+
+Public surface mirrors the reference: ``GCN(opt, n_node_features)`` / ``GCN_explain`` with the
+reference's forward signatures and state_dict layout, ``make_network``; plus ``Batch`` /
+``DataLoader`` (what the reference takes from torch_geometric) and ``default_options``.
+All arithmetic runs in libhcg.so (include/hcg.h); there is no CPU implementation.
+"""
+from .call_methods import make_network  # noqa: F401
+from .data import Batch, DataLoader  # noqa: F401
+from .model import GCN, GCN_explain  # noqa: F401
+from .options import default_options  # noqa: F401
+
+__version__ = "0.1.0"

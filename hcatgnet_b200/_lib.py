@@ -63,6 +63,13 @@ _lib = None
 SIGNATURES = {
     "hcg_last_error": (C.c_char_p, []),
     "hcg_version": (C.c_char_p, []),
+    "hcg_launch_count": (C.c_uint64, []),
+    "hcg_profile_enable": (C.c_int, [C.c_int]),
+    "hcg_profile_read": (C.c_int, [C.c_char_p, C.POINTER(C.c_float), C.POINTER(C.c_int64), C.c_int]),
+    "hcg_sizeof_graph": (C.c_size_t, []),
+    "hcg_sizeof_params": (C.c_size_t, []),
+    "hcg_sizeof_grads": (C.c_size_t, []),
+    "hcg_sizeof_saved": (C.c_size_t, []),
     "hcg_collate_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.c_int]),
     "hcg_collate": (C.c_int, [_fp, C.c_int64, _fp, C.c_int64, C.c_int64, C.c_float, _fp, C.c_float, C.c_int,
                               _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp,
@@ -109,3 +116,25 @@ def load():
 def check(code: int) -> None:
     if code != 0:
         raise HcgError(code, load().hcg_last_error().decode("utf-8", "replace"))
+
+
+def launch_count() -> int:
+    return int(load().hcg_launch_count())
+
+
+def profile_enable(on: bool) -> None:
+    check(load().hcg_profile_enable(1 if on else 0))
+
+
+def profile_read(cap: int = 64) -> dict:
+    """{kernel name: (total device ms, launches)} since the last profile_enable(True)."""
+    names = C.create_string_buffer(cap * 64)
+    ms = (C.c_float * cap)()
+    cnt = (C.c_int64 * cap)()
+    rc = load().hcg_profile_read(names, ms, cnt, cap)
+    if rc > 0:
+        check(rc)
+    out = {}
+    for i in range(-rc):
+        out[names.raw[i * 64:(i + 1) * 64].split(b"\0", 1)[0].decode()] = (float(ms[i]), int(cnt[i]))
+    return out

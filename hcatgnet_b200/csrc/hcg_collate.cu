@@ -6,27 +6,9 @@
 // Integer contract (bit-exact vs oracle/ref_collate.py): self-loop edges dropped, kept edges
 // ordered by (dst, original edge id).  Histogram and slot claiming use INTEGER atomics (their
 // results are order-independent once each row is re-sorted by edge id); no float atomics.
-#include <stdarg.h>
-
 #include "hcg_common.cuh"
 
 namespace hcg {
-
-// ------------------------------------------------------------------------------------------
-// error plumbing (shared by all translation units)
-// ------------------------------------------------------------------------------------------
-char* err_buf() {
-  static thread_local char buf[512] = {0};
-  return buf;
-}
-
-int set_err(int code, const char* fmt, ...) {
-  va_list ap;
-  va_start(ap, fmt);
-  vsnprintf(err_buf(), 512, fmt, ap);
-  va_end(ap);
-  return code;
-}
 
 constexpr int kStatusBadIndex = 1;
 constexpr int kStatusBadBatch = 2;
@@ -278,11 +260,11 @@ static int scan_i32(const int32_t* in, int64_t n, int32_t* out, int32_t* sums, c
   // out has n+1 entries; out[n] = total
   int64_t nblk = cdiv(n > 0 ? n : 1, kScanTile);
   k_scan_tile<<<(unsigned)nblk, kScanThreads, 0, st>>>(in, n, out, sums);
-  HCG_LAUNCH_OK("k_scan_tile");
+  HCG_LAUNCH_OK(st, "k_scan_tile");
   k_scan_sums<<<1, kScanThreads, 0, st>>>(sums, nblk, sums + nblk);
-  HCG_LAUNCH_OK("k_scan_sums");
+  HCG_LAUNCH_OK(st, "k_scan_sums");
   k_scan_add<<<(unsigned)cdiv(n + 1, 256), 256, 0, st>>>(out, n, sums, sums + nblk);
-  HCG_LAUNCH_OK("k_scan_add");
+  HCG_LAUNCH_OK(st, "k_scan_add");
   return HCG_OK;
 }
 
@@ -314,9 +296,6 @@ static CollateWs carve_collate(void* ws, int64_t N, int64_t E, int flags) {
 
 using namespace hcg;
 
-extern "C" const char* hcg_last_error(void) { return err_buf(); }
-extern "C" const char* hcg_version(void) { return "hcg 0.1 (sm_100a)"; }
-
 extern "C" size_t hcg_collate_workspace_bytes(int64_t N, int64_t E, int64_t B, int flags) {
   (void)B;
   return carve_collate(nullptr, N, E, flags).bytes;
@@ -347,6 +326,7 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
   HCG_REQUIRE(ws_bytes >= need, HCG_ERR_WORKSPACE, "collate workspace too small: %zu < %zu", ws_bytes, need);
 
   CollateWs w = carve_collate(ws, N, E, flags);
+  note_region(st);
   const int64_t* src = edge_index;
   const int64_t* dst = edge_index + E;
 
@@ -356,6 +336,7 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
   HCG_CUDA_OK(cudaMemsetAsync(w.status, 0, zero_bytes, st));
   if (weighted) HCG_CUDA_OK(cudaMemsetAsync(w.loop_eid, 0xff, (size_t)(N + 1) * sizeof(int32_t), st));
   HCG_CUDA_OK(cudaMemsetAsync(graph_ptr, 0, (size_t)(B + 1) * sizeof(int32_t), st));
+  note_other("memset(collate)", st);
 
   int64_t eb = cdiv(E, 256);
   if (eb > (int64_t)kNumSMs * 16) eb = (int64_t)kNumSMs * 16;
@@ -363,7 +344,7 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
   if (E > 0) {
     k_count<<<eblocks, 256, 0, st>>>(src, dst, E, N, w.cnt_dst, transpose ? w.cnt_src : nullptr,
                                      weighted ? w.loop_eid : nullptr, w.status);
-    HCG_LAUNCH_OK("k_count");
+    HCG_LAUNCH_OK(st, "k_count");
   }
   int rc = scan_i32(w.cnt_dst, N, rowptr, w.sums, st);
   if (rc) return rc;
@@ -375,23 +356,23 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
     k_fill<<<eblocks, 256, 0, st>>>(src, dst, E, N, rowptr, w.cnt_dst, w.tmp,
                                     transpose ? t_rowptr : nullptr, transpose ? w.cnt_src : nullptr,
                                     transpose ? w.t_tmp : nullptr);
-    HCG_LAUNCH_OK("k_fill");
+    HCG_LAUNCH_OK(st, "k_fill");
   }
   if (N > 0) {
     const unsigned nb = (unsigned)cdiv(N, 256);
     if (E > 0) {
       k_rowsort<<<nb, 256, 0, st>>>(rowptr, N, w.tmp, col, eid, edge_weight, weighted ? ew0 : nullptr);
-      HCG_LAUNCH_OK("k_rowsort");
+      HCG_LAUNCH_OK(st, "k_rowsort");
       if (transpose) {
         k_rowsort<<<nb, 256, 0, st>>>(t_rowptr, N, w.t_tmp, t_col, t_eid, edge_weight, weighted ? t_ew0 : nullptr);
-        HCG_LAUNCH_OK("k_rowsort(t)");
+        HCG_LAUNCH_OK(st, "k_rowsort(t)");
       }
     }
     k_dis<<<nb, 256, 0, st>>>(rowptr, N, fill, dis, weighted ? 1 : 0, fill_w, ew0, w.loop_eid, edge_weight, selfw0, dis0);
-    HCG_LAUNCH_OK("k_dis");
+    HCG_LAUNCH_OK(st, "k_dis");
   }
   k_graph_ptr<<<(unsigned)cdiv(N + 1, 256), 256, 0, st>>>(batch, N, B, graph_ptr, w.status);
-  HCG_LAUNCH_OK("k_graph_ptr");
+  HCG_LAUNCH_OK(st, "k_graph_ptr");
   return HCG_OK;
 }
 

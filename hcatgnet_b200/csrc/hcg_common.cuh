@@ -15,6 +15,11 @@ constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 char* err_buf();
 int set_err(int code, const char* fmt, ...);
 
+// hcg_runtime.cu: launch counter + event profiler hooks (cheap no-ops unless profiling is on)
+void note_launch(const char* name, cudaStream_t st);   // a kernel of ours was launched
+void note_region(cudaStream_t st);                     // an API call starts issuing work
+void note_other(const char* name, cudaStream_t st);    // non-kernel stream work (memset)
+
 #define HCG_CUDA_OK(expr)                                                             \
   do {                                                                                \
     cudaError_t _e = (expr);                                                          \
@@ -23,12 +28,14 @@ int set_err(int code, const char* fmt, ...);
                             cudaGetErrorString(_e), __FILE__, __LINE__);              \
   } while (0)
 
-#define HCG_LAUNCH_OK(name)                                                           \
+// after every kernel launch: error check, launch counter, optional profiler mark
+#define HCG_LAUNCH_OK(stream, name)                                                   \
   do {                                                                                \
     cudaError_t _e = cudaGetLastError();                                              \
     if (_e != cudaSuccess)                                                            \
       return ::hcg::set_err(HCG_ERR_CUDA, "launch of %s failed: %s", name,            \
                             cudaGetErrorString(_e));                                  \
+    ::hcg::note_launch(name, stream);                                                 \
   } while (0)
 
 #define HCG_REQUIRE(cond, code, ...)                                                  \

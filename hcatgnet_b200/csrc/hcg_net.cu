@@ -112,7 +112,7 @@ static int launch_gemm(const float* A, const float* Bm, float* C, int64_t M, int
     case EPI_ADD: k_gemm<B_T, EPI_ADD><<<grid, 256, 0, st>>>(A, Bm, C, M, K, Nc, aux, slope); break;
     default: return set_err(HCG_ERR_INVALID_ARG, "bad gemm epilogue %d", epi);
   }
-  HCG_LAUNCH_OK("k_gemm");
+  HCG_LAUNCH_OK(st, "k_gemm");
   return HCG_OK;
 }
 
@@ -215,7 +215,7 @@ static int launch_agg(const int32_t* rowptr, const int32_t* col, const float* di
     int lpr = lanes_per_row(H, 1);
     k_agg<1><<<(unsigned)cdiv(N, 256 / lpr), 256, 0, st>>>(rowptr, col, dis, ew, selfw, fill, T, bias, out, N, H, lpr, act, slope);
   }
-  HCG_LAUNCH_OK("k_agg");
+  HCG_LAUNCH_OK(st, "k_agg");
   return HCG_OK;
 }
 
@@ -380,9 +380,9 @@ static int launch_xty(const float* X, const float* Y, int64_t rows, int P, int Q
   int64_t rpc = cdiv(rows > 0 ? rows : 1, chunks);
   dim3 grid((unsigned)chunks, (unsigned)cdiv(P, 64), (unsigned)cdiv(Q, 64));
   k_xty_partial<<<grid, 256, 0, st>>>(X, Y, rows, P, Q, rpc, partial);
-  HCG_LAUNCH_OK("k_xty_partial");
+  HCG_LAUNCH_OK(st, "k_xty_partial");
   k_reduce_partials<<<(unsigned)cdiv((int64_t)P * Q, 256), 256, 0, st>>>(partial, (int)chunks, (int64_t)P * Q, out);
-  HCG_LAUNCH_OK("k_reduce_partials");
+  HCG_LAUNCH_OK(st, "k_reduce_partials");
   return HCG_OK;
 }
 
@@ -390,9 +390,9 @@ static int launch_colsum(const float* X, int64_t rows, int P, float* partial, fl
   int64_t chunks = pick_chunks(rows, 1);
   int64_t rpc = cdiv(rows > 0 ? rows : 1, chunks);
   k_colsum_partial<<<(unsigned)chunks, 256, 0, st>>>(X, rows, P, rpc, partial);
-  HCG_LAUNCH_OK("k_colsum_partial");
+  HCG_LAUNCH_OK(st, "k_colsum_partial");
   k_reduce_partials<<<(unsigned)cdiv(P, 256), 256, 0, st>>>(partial, (int)chunks, P, out);
-  HCG_LAUNCH_OK("k_reduce_partials");
+  HCG_LAUNCH_OK(st, "k_reduce_partials");
   return HCG_OK;
 }
 
@@ -523,6 +523,7 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
   HCG_REQUIRE(ws_bytes >= w.bytes, HCG_ERR_WORKSPACE, "forward workspace too small: %zu < %zu", ws_bytes, w.bytes);
   const int64_t N = g->N, B = g->B;
   const int H = p->H;
+  note_region(st);
 
   const float* h_in = x;
   int k_in = p->F;
@@ -542,7 +543,7 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
   if (B > 0) {
     int lpr = lanes_per_row(H, 1);
     k_pool<<<(unsigned)cdiv(B, 256 / lpr), 256, 0, st>>>(h_out, g->graph_ptr, B, H, lpr, emb);
-    HCG_LAUNCH_OK("k_pool");
+    HCG_LAUNCH_OK(st, "k_pool");
   }
   const float* z = emb;
   for (int k = 0; k < p->R; ++k) {
@@ -576,6 +577,7 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
   HCG_REQUIRE(ws_bytes >= w.bytes, HCG_ERR_WORKSPACE, "backward workspace too small: %zu < %zu", ws_bytes, w.bytes);
   const int64_t N = g->N, B = g->B;
   const int H = p->H;
+  note_region(st);
 
   // ---- readout MLP backward -------------------------------------------------------------
   const float* gemb_total = g_emb;
@@ -590,7 +592,7 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
         float* buf = w.gz[pp]; pp ^= 1;
         if (B * dout > 0) {
           k_mask_mul<<<(unsigned)cdiv(B * dout, 256), 256, 0, st>>>(gz, saved->hid[k], B * dout, p->slope, buf);
-          HCG_LAUNCH_OK("k_mask_mul");
+          HCG_LAUNCH_OK(st, "k_mask_mul");
         }
         gpre = buf;
       }
@@ -617,12 +619,15 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
   }
 
   // ---- pooling backward (+ LeakyReLU' of the last conv layer) -----------------------------
-  if (N > 0) HCG_CUDA_OK(cudaMemsetAsync(w.gA, 0, sizeof(float) * (size_t)N * H, st));  // nodes of no graph
+  if (N > 0) {  // nodes of no graph
+    HCG_CUDA_OK(cudaMemsetAsync(w.gA, 0, sizeof(float) * (size_t)N * H, st));
+    note_other("memset(gA)", st);
+  }
   if (B > 0) {
     int lpr = lanes_per_row(H, 1);
     k_pool_bwd<<<(unsigned)cdiv(B, 256 / lpr), 256, 0, st>>>(saved->acts[p->L - 1], emb, gemb_total, g->graph_ptr,
                                                               B, H, lpr, p->slope, w.gA);
-    HCG_LAUNCH_OK("k_pool_bwd");
+    HCG_LAUNCH_OK(st, "k_pool_bwd");
   }
 
   // ---- conv layers backward ---------------------------------------------------------------

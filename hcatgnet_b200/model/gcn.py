@@ -1,0 +1,162 @@
+"""GCN / GCN_explain — drop-in mirror of reference model/gcn.py:9-139.
+
+Same constructor options, same ``forward`` signatures, same ``state_dict`` keys, shapes and
+order (``conv1.bias``, ``conv1.lin.weight``, ``conv_layers.{i}.bias``,
+``conv_layers.{i}.lin.weight``, ``readout.{k}.0.weight|bias``, ``readout.{R-1}.weight|bias``),
+so the shipped ``model_params.pth`` load with ``strict=True``.  The sub-modules below only
+HOLD parameters; the arithmetic of the whole network (GCNConv × L, LeakyReLU, global max‖mean
+pooling, readout MLP; forward and backward) runs in libhcg.so (include/hcg.h) on the GPU.
+There is no CPU implementation: tensors that arrive in host memory are staged to the current
+CUDA device, computed there, and the results returned on the device the inputs came from
+(that keeps reference utils/utils_model.py:82-111 ``predict_network``, which forces
+``.to('cpu')``, working unchanged).
+"""
+from __future__ import annotations
+
+import argparse
+import math
+
+import torch
+import torch.nn as nn
+
+from .. import ops
+from .networks import BaseNetwork
+
+
+class _DenseLin(nn.Module):
+    """Parameter holder with the layout of PyG's bias-free ``Linear`` inside GCNConv
+    (key ``weight`` [out, in], glorot-uniform init)."""
+
+    def __init__(self, in_channels: int, out_channels: int):
+        super().__init__()
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.weight = nn.Parameter(torch.empty(out_channels, in_channels))
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        a = math.sqrt(6.0 / (self.in_channels + self.out_channels))
+        with torch.no_grad():
+            self.weight.uniform_(-a, a)
+
+
+class GCNConv(nn.Module):
+    """Parameter holder for one graph convolution (replaces ``torch_geometric.nn.GCNConv`` as
+    used at reference model/gcn.py:18-20,27-29).  Registration order gives the state_dict order
+    ``bias`` then ``lin.weight``.  Like PyG, the weight is drawn twice at construction (once by
+    the Linear's own init, once by GCNConv.reset_parameters), which keeps the global RNG stream
+    in step with the reference for seeded from-scratch training."""
+
+    def __init__(self, in_channels: int, out_channels: int, improved: bool = False):
+        super().__init__()
+        self.in_channels, self.out_channels, self.improved = in_channels, out_channels, improved
+        self.bias = nn.Parameter(torch.empty(out_channels))
+        self.lin = _DenseLin(in_channels, out_channels)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        self.lin.reset_parameters()
+        with torch.no_grad():
+            self.bias.zero_()
+
+    def forward(self, *args, **kwargs):
+        raise RuntimeError("hcatgnet_b200.GCNConv only holds parameters; the fused network kernel is "
+                           "invoked by GCN.forward / GCN_explain.forward")
+
+    def extra_repr(self):
+        return f"{self.in_channels}, {self.out_channels}, improved={self.improved}"
+
+
+def _num_graphs_of(graph, batch, n_nodes: int) -> int:
+    ng = getattr(graph, "num_graphs", None) if graph is not None else None
+    if ng is not None:
+        return int(ng)
+    if batch is None:
+        return 1 if n_nodes > 0 else 0
+    return int(batch.max().item()) + 1 if batch.numel() else 0  # one sync, as PyG's pooling does
+
+
+class _GCNBase(BaseNetwork):
+    """Everything reference GCN and GCN_explain share (their constructors are identical,
+    reference model/gcn.py:11-50 and :81-120)."""
+
+    def __init__(self, opt: argparse.Namespace, n_node_features: int):
+        super().__init__(opt=opt, n_node_features=n_node_features)
+        self._name = "GCN"
+        self.improved = opt.improved
+        # read back hcg_collate's status word for every new batch (one stream sync): bad node ids or
+        # an unsorted batch vector raise instead of being skipped
+        self.validate_inputs = True
+
+        self.conv1 = GCNConv(self.n_node_features, self.embedding_dim, improved=self.improved)
+        self.relu1 = nn.LeakyReLU()
+
+        self.conv_layers = nn.ModuleList([])
+        for _ in range(self.n_convolutions - 1):
+            self.conv_layers.append(GCNConv(self.embedding_dim, self.embedding_dim, self.improved))
+
+        graph_embedding = self.embedding_dim * 2
+        self.readout = nn.ModuleList([])
+        for _ in range(self.readout_layers - 1):
+            reduced_dim = int(graph_embedding / 2)
+            self.readout.append(nn.Sequential(nn.Linear(graph_embedding, reduced_dim), nn.LeakyReLU()))
+            graph_embedding = reduced_dim
+        self.readout.append(nn.Linear(graph_embedding, self._n_classes))
+
+        self._make_loss(opt.problem_type)
+        self._make_optimizer(opt.optimizer, opt.lr)
+        self._make_scheduler(scheduler=opt.scheduler, step_size=opt.step_size, gamma=opt.gamma, min_lr=opt.min_lr)
+
+    # -- plumbing --------------------------------------------------------------------------
+    def _dims(self) -> ops.NetDims:
+        return ops.NetDims(F=self.n_node_features, H=self.embedding_dim, L=self.n_convolutions,
+                           R=self.readout_layers, C=self._n_classes, slope=self.relu1.negative_slope)
+
+    def _flat_params(self):
+        ps = [self.conv1.lin.weight, self.conv1.bias]
+        for conv in self.conv_layers:
+            ps += [conv.lin.weight, conv.bias]
+        for k in range(self.readout_layers - 1):
+            ps += [self.readout[k][0].weight, self.readout[k][0].bias]
+        ps += [self.readout[-1].weight, self.readout[-1].bias]
+        return ps
+
+    def _run(self, x, edge_index, batch, num_graphs, edge_weight=None, cache_on=None):
+        """Stage to the GPU if needed, collate (cached on ``cache_on``), run the fused network."""
+        home = x.device
+        device = ops.compute_device(x)
+        params = self._flat_params()
+        need_grad = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params))
+        if edge_weight is not None and edge_weight.requires_grad and torch.is_grad_enabled():
+            raise NotImplementedError("gradients w.r.t. edge_weight are not provided by libhcg yet")
+        plan = ops.cached_collate(cache_on, edge_index, batch, x.shape[0], num_graphs, device,
+                                  edge_weight=edge_weight, improved=bool(self.improved), transpose=need_grad,
+                                  validate=self.validate_inputs)
+        xd = ops.to_device(x, device, torch.float32)
+        pd = [ops.to_device(p, device, torch.float32) for p in params]
+        out, emb = ops.gcn_apply(xd, plan, self._dims(), pd)
+        if home != device:
+            out, emb = out.to(home), emb.to(home)
+        return out, emb
+
+
+class GCN(_GCNBase):
+    """reference model/gcn.py:9-76."""
+
+    def forward(self, reaction_graph, return_graph_embedding=False):
+        x, edge_index, batch = reaction_graph.x, reaction_graph.edge_index, reaction_graph.batch
+        # edge_weight is None on this path, so `improved` does not change the normalisation
+        # (self-loop weight 1.0) — the behaviour the shipped golden outputs pin
+        out, graph_emb = self._run(x, edge_index, batch, _num_graphs_of(reaction_graph, batch, x.shape[0]),
+                                   cache_on=reaction_graph)
+        if return_graph_embedding == True:  # noqa: E712  (same test as the reference, model/gcn.py:73)
+            return out, graph_emb
+        return out
+
+
+class GCN_explain(_GCNBase):
+    """reference model/gcn.py:79-139: tensor-level entry; ``edge_weight`` reaches conv1 only."""
+
+    def forward(self, x=None, edge_index=None, batch_index=None, edge_weight=None):
+        out, _ = self._run(x, edge_index, batch_index, _num_graphs_of(None, batch_index, x.shape[0]),
+                           edge_weight=edge_weight)
+        return out

@@ -22,6 +22,12 @@ def _require_cuda() -> torch.device:
     return torch.device("cuda", torch.cuda.current_device())
 
 
+def compute_device(t: torch.Tensor) -> torch.device:
+    """The GPU the work runs on: the tensor's own device if it is a CUDA tensor, else the
+    current CUDA device (host tensors get staged there)."""
+    return t.device if t.is_cuda else _require_cuda()
+
+
 def to_device(t: torch.Tensor | None, device: torch.device, dtype=None) -> torch.Tensor | None:
     if t is None:
         return None
@@ -134,6 +140,34 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
             _lib.check(lib.hcg_collate_status(_ptr(ws), st))
         else:
             ws.record_stream(torch.cuda.current_stream(device))
+    return plan
+
+
+def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edge_weight=None,
+                   improved=False, transpose=False, validate=True) -> GraphPlan:
+    """``collate`` memoised on ``holder`` (the batch object the caller passed to ``forward``).
+
+    The reference recomputes the normalisation inside every GCNConv call of every forward
+    (``cached=False``); here the topology is built once per batch object and reused by all
+    layers, by the backward pass and by later epochs that present the same batch again.
+    Weighted calls (explainer masks change every step) are never cached.
+    """
+    key = None
+    if holder is not None and edge_weight is None:
+        key = (edge_index.data_ptr(), edge_index._version, tuple(edge_index.shape),
+               None if batch is None else batch.data_ptr(), int(num_nodes), int(num_graphs), str(device))
+        hit = getattr(holder, "_hcg_plan", None)
+        if hit is not None and hit[0] == key and (hit[1].has_transpose or not transpose):
+            return hit[1]
+    with torch.cuda.device(device):
+        plan = collate(to_device(edge_index, device, torch.int64), to_device(batch, device, torch.int64),
+                       num_nodes, num_graphs, edge_weight=to_device(edge_weight, device, torch.float32),
+                       improved=improved, transpose=transpose, validate=validate)
+    if key is not None:
+        try:
+            object.__setattr__(holder, "_hcg_plan", (key, plan))
+        except (AttributeError, TypeError):
+            pass
     return plan
 
 

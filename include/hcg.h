@@ -117,6 +117,24 @@ typedef struct HcgSaved {
 const char* hcg_last_error(void);
 const char* hcg_version(void);
 
+/*
+ * Instrumentation (used by bench.py; never on the product's critical path).
+ * hcg_launch_count: kernels this library has launched in this process so far.
+ * hcg_profile_enable(1) starts recording a CUDA event after every kernel launch on the launch
+ * stream, hcg_profile_enable(0) stops; hcg_profile_read synchronises and aggregates device time
+ * per kernel name into name_buf (cap rows of 64 bytes), total_ms and counts.  It returns
+ * -(rows written) on success (<= 0) or a positive HCG_ERR_* code.
+ */
+uint64_t hcg_launch_count(void);
+int hcg_profile_enable(int on);
+int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts, int cap);
+
+/* sizeof() of the structs above, for bindings that mirror them (ctypes, cgo, JNI ...) */
+size_t hcg_sizeof_graph(void);
+size_t hcg_sizeof_params(void);
+size_t hcg_sizeof_grads(void);
+size_t hcg_sizeof_saved(void);
+
 /* ---- collate (replaces gcn_norm index work; north_star "batch-collate kernel") ------------ */
 
 size_t hcg_collate_workspace_bytes(int64_t N, int64_t E, int64_t B, int flags);
