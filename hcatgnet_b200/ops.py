@@ -290,9 +290,10 @@ class _GCNFunction(torch.autograd.Function):
     """autograd node whose forward/backward are single C-ABI calls."""
 
     @staticmethod
-    def forward(ctx, x, plan, dims, *params):
+    def forward(ctx, x, plan, dims, need_grad, *params):
+        # `need_grad` is decided by the caller: grad mode is always off inside Function.forward and
+        # ctx.needs_input_grad reports requires_grad flags even under torch.no_grad()
         params = tuple(p.contiguous() for p in params)
-        need_grad = any(ctx.needs_input_grad)
         if need_grad and not plan.has_transpose:
             raise RuntimeError("this GraphPlan was collated without the transposed CSR; backward needs transpose=True")
         out, emb, saved_t = forward_raw(plan, x, dims, params, save=need_grad)
@@ -308,10 +309,11 @@ class _GCNFunction(torch.autograd.Function):
         g_emb = g_emb.contiguous() if g_emb is not None else None
         g_x, grads = backward_raw(ctx.plan, x, ctx.dims, params, ctx.saved_t, emb, g_out, g_emb,
                                   need_gx=ctx.needs_input_grad[0])
-        return (g_x, None, None, *grads)
+        return (g_x, None, None, None, *grads)
 
 
 def gcn_apply(x: torch.Tensor, plan: GraphPlan, dims: NetDims, params):
     """Differentiable GCN hot path: returns (out[B,C], emb[B,2H])."""
     _check_param_shapes(dims, params)
-    return _GCNFunction.apply(x, plan, dims, *params)
+    need_grad = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params))
+    return _GCNFunction.apply(x, plan, dims, need_grad, *params)

@@ -224,11 +224,47 @@ def test_backward_matches_oracle_autograd(hcg, rset, outer, inner, count):
     sd, graphs, _, _ = golden_io.rows_with_graphs(rset, outer, inner)
     b = ref_gcn.collate(graphs[:count])
     args = (sd, b["x"], b["edge_index"], b["batch"], b["num_graphs"], b["y"])
-    l_ref, g_ref, gx_ref = _oracle_grads(*args, x_grad=True)
-    l_cuda, g_cuda, gx_cuda = _cuda_grads(hcg, *args, x_grad=True)
+    l_ref, g_ref, _ = _oracle_grads(*args)
+    l_cuda, g_cuda, _ = _cuda_grads(hcg, *args)
     assert abs(l_cuda - l_ref) <= 1e-5 * max(abs(l_ref), 1)
     _assert_grads(g_cuda, g_ref)
+    # d/dx: symmetry-equivalent atoms of the real molecules are (near-)ties of the max pooling;
+    # which of them carries the max gradient is decided by rounding noise and differs between the
+    # fp64 oracle and any fp32 run (weight gradients are unaffected: the tied atoms are
+    # equivalent).  The node-level gradient is therefore compared on de-symmetrised inputs;
+    # exact ties are covered by test_backward_exact_ties_split_evenly.
+    xj = b["x"] + 0.05 * torch.rand(b["x"].shape, generator=torch.Generator().manual_seed(3))
+    args = (sd, xj, b["edge_index"], b["batch"], b["num_graphs"], b["y"])
+    _, g_ref, gx_ref = _oracle_grads(*args, x_grad=True)
+    _, g_cuda, gx_cuda = _cuda_grads(hcg, *args, x_grad=True)
+    _assert_grads(g_cuda, g_ref)
     _assert_grads({"x": gx_cuda}, {"x": gx_ref})
+
+
+def test_backward_exact_ties_split_evenly(hcg):
+    """Two identical copies of a molecule inside ONE graph (same edge order): every pooled maximum
+    is attained twice, bit-identically.  torch's scatter_reduce(amax) backward — what the
+    restated reference path runs — shares the gradient evenly among ties; so must the kernel."""
+    sd, graphs, _, _ = golden_io.rows_with_graphs("learning", 1, 2)
+    gs = []
+    for g in graphs[:6]:
+        n = g["x"].shape[0]
+        gs.append({"x": torch.cat([g["x"], g["x"]]), "y": g["y"], "idx": g["idx"],
+                   "edge_index": torch.cat([g["edge_index"], g["edge_index"] + n], 1)})
+    b = ref_gcn.collate(gs)
+    args = (sd, b["x"], b["edge_index"], b["batch"], b["num_graphs"], b["y"])
+    _, g_ref, gx_ref = _oracle_grads(*args, x_grad=True)
+    _, g_cuda, gx_cuda = _cuda_grads(hcg, *args, x_grad=True)
+    _assert_grads(g_cuda, g_ref)
+    n0 = gs[0]["x"].shape[0] // 2
+    assert torch.equal(gx_cuda[:n0], gx_cuda[n0:2 * n0])      # the two copies get identical gradients
+    # vs the fp64 oracle the copies are exact ties too, but ties BETWEEN symmetry-equivalent atoms of
+    # one copy stay rounding-dependent: compare the per-copy SUM over equivalent candidates instead,
+    # i.e. the total gradient mass per graph and feature
+    ptr = b["ptr"].tolist()
+    for g in range(len(gs)):
+        a, r = gx_cuda[ptr[g]:ptr[g + 1]].double().sum(0), gx_ref[ptr[g]:ptr[g + 1]].sum(0)
+        assert float((a - r).abs().max()) <= 1e-4 * max(float(r.abs().max()), 1e-6)
 
 
 @pytest.mark.parametrize("H,L,R,F,C", [(256, 4, 2, 25, 1), (48, 3, 3, 7, 3), (64, 1, 1, 32, 1)])
