@@ -14,6 +14,7 @@ from . import build as _build
 HCG_MAX_CONV = 8
 HCG_MAX_READOUT = 8
 HCG_COLLATE_TRANSPOSE = 1
+HCG_GRAPH_CROSS_EDGES = 1
 
 ERR_NAMES = {1: "INVALID_ARG", 2: "UNSUPPORTED", 3: "WORKSPACE", 4: "CUDA", 5: "BAD_INDEX", 6: "BAD_BATCH"}
 
@@ -27,6 +28,7 @@ class HcgGraph(C.Structure):
         ("t_rowptr", _fp), ("t_col", _fp), ("t_eid", _fp),
         ("fill", C.c_float),
         ("ew0", _fp), ("t_ew0", _fp), ("selfw0", _fp), ("dis0", _fp),
+        ("max_graph_nodes", C.c_int32), ("flags", C.c_int32),
     ]
 
 
@@ -66,6 +68,9 @@ SIGNATURES = {
     "hcg_launch_count": (C.c_uint64, []),
     "hcg_profile_enable": (C.c_int, [C.c_int]),
     "hcg_profile_read": (C.c_int, [C.c_char_p, C.POINTER(C.c_float), C.POINTER(C.c_int64), C.c_int]),
+    "hcg_config_set": (C.c_int, [C.c_int, C.c_int]),
+    "hcg_config_get": (C.c_int, [C.c_int]),
+    "hcg_selftest_tc_gemm": (C.c_int, [_fp, _fp, C.c_int, _fp, _fp]),
     "hcg_sizeof_graph": (C.c_size_t, []),
     "hcg_sizeof_params": (C.c_size_t, []),
     "hcg_sizeof_grads": (C.c_size_t, []),
@@ -74,7 +79,7 @@ SIGNATURES = {
     "hcg_collate": (C.c_int, [_fp, C.c_int64, _fp, C.c_int64, C.c_int64, C.c_float, _fp, C.c_float, C.c_int,
                               _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp,
                               _fp, C.c_size_t, _fp]),
-    "hcg_collate_status": (C.c_int, [_fp, _fp]),
+    "hcg_collate_status": (C.c_int, [_fp, _fp, C.POINTER(C.c_int32)]),
     "hcg_forward_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.POINTER(HcgParams)]),
     "hcg_gcn_forward": (C.c_int, [C.POINTER(HcgGraph), _fp, C.POINTER(HcgParams), _fp, _fp, C.POINTER(HcgSaved),
                                   _fp, C.c_size_t, _fp]),
@@ -116,6 +121,18 @@ def load():
 def check(code: int) -> None:
     if code != 0:
         raise HcgError(code, load().hcg_last_error().decode("utf-8", "replace"))
+
+
+HCG_CFG_FORWARD_PATH = 0
+PATH_AUTO, PATH_LAYERWISE, PATH_GRAPH_RESIDENT = 0, 1, 2
+
+
+def config_set(key: int, value: int) -> int:
+    """Library-wide switch (tests / benchmarks); returns the previous value."""
+    prev = load().hcg_config_set(key, value)
+    if prev < 0:
+        raise ValueError(f"unknown libhcg config key {key}")
+    return prev
 
 
 def launch_count() -> int:

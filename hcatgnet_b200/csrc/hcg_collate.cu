@@ -12,6 +12,7 @@ namespace hcg {
 
 constexpr int kStatusBadIndex = 1;
 constexpr int kStatusBadBatch = 2;
+constexpr int kStatusCrossEdge = 4;
 
 constexpr int kScanThreads = 256;
 constexpr int kScanItems = 8;
@@ -21,8 +22,8 @@ constexpr int kScanTile = kScanThreads * kScanItems;  // 2048 elements per block
 // 1. in-degree (and out-degree) histogram over kept edges
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-k_count(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, int64_t E, int64_t N,
-        int32_t* __restrict__ cnt_dst, int32_t* __restrict__ cnt_src, int32_t* __restrict__ loop_eid,
+k_count(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, const int64_t* __restrict__ batch,
+        int64_t E, int64_t N, int32_t* __restrict__ cnt_dst, int32_t* __restrict__ cnt_src, int32_t* __restrict__ loop_eid,
         int* __restrict__ status) {
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E; e += stride) {
@@ -35,6 +36,7 @@ k_count(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, int64_
       if (loop_eid) atomicMax(&loop_eid[s], (int32_t)e);  // "last one wins" like index assignment
       continue;
     }
+    if (batch && batch[s] != batch[d]) atomicOr(status, kStatusCrossEdge);
     atomicAdd(&cnt_dst[d], 1);
     if (cnt_src) atomicAdd(&cnt_src[s], 1);
   }
@@ -342,7 +344,7 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
   if (eb > (int64_t)kNumSMs * 16) eb = (int64_t)kNumSMs * 16;
   const unsigned eblocks = (unsigned)eb;
   if (E > 0) {
-    k_count<<<eblocks, 256, 0, st>>>(src, dst, E, N, w.cnt_dst, transpose ? w.cnt_src : nullptr,
+    k_count<<<eblocks, 256, 0, st>>>(src, dst, batch, E, N, w.cnt_dst, transpose ? w.cnt_src : nullptr,
                                      weighted ? w.loop_eid : nullptr, w.status);
     HCG_LAUNCH_OK(st, "k_count");
   }
@@ -376,12 +378,14 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
   return HCG_OK;
 }
 
-extern "C" int hcg_collate_status(const void* ws, void* stream) {
+extern "C" int hcg_collate_status(const void* ws, void* stream, int32_t* graph_flags) {
   int status = 0;
+  if (graph_flags) *graph_flags = 0;
   HCG_REQUIRE(ws != nullptr, HCG_ERR_INVALID_ARG, "NULL workspace");
   HCG_CUDA_OK(cudaMemcpyAsync(&status, ws, sizeof(int), cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
   HCG_CUDA_OK(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
   if (status & kStatusBadIndex) return set_err(HCG_ERR_BAD_INDEX, "edge_index holds a node index outside [0, N)");
   if (status & kStatusBadBatch) return set_err(HCG_ERR_BAD_BATCH, "batch vector is not sorted or holds an id outside [0, B)");
+  if (graph_flags && (status & kStatusCrossEdge)) *graph_flags |= HCG_GRAPH_CROSS_EDGES;
   return HCG_OK;
 }

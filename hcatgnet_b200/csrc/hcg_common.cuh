@@ -19,6 +19,7 @@ int set_err(int code, const char* fmt, ...);
 void note_launch(const char* name, cudaStream_t st);   // a kernel of ours was launched
 void note_region(cudaStream_t st);                     // an API call starts issuing work
 void note_other(const char* name, cudaStream_t st);    // non-kernel stream work (memset)
+int config_get(int key);                               // hcg_config_get
 
 #define HCG_CUDA_OK(expr)                                                             \
   do {                                                                                \

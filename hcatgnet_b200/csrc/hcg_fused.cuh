@@ -1,0 +1,40 @@
+// Declarations shared between hcg_net.cu (dispatch) and hcg_fused.cu (graph-resident kernels).
+#pragma once
+
+#include "hcg_common.cuh"
+
+namespace hcg {
+
+constexpr int kFusedH = 64;        // hidden width the graph-resident kernels are specialised for
+constexpr int kFusedThreads = 256; // 8 warps per CTA
+constexpr int kFusedWarps = kFusedThreads / 32;
+constexpr int kTileRows = 16;      // node rows per warp tile
+constexpr int kTileStride = 68;    // floats per tile row (64 + 4: adjacent rows land 4 banks apart)
+constexpr int kMaxFusedF = 64;     // widest input feature vector kept in shared memory
+
+// Everything the graph-resident forward needs, passed by value (fits the 4 KB parameter space).
+struct FusedFwdArgs {
+  const int32_t* rowptr;
+  const int32_t* col;
+  const float* dis;
+  const int32_t* graph_ptr;
+  const float* x;
+  const float* conv_w[HCG_MAX_CONV];
+  const float* conv_b[HCG_MAX_CONV];
+  float* save_act[HCG_MAX_CONV];  // optional: post-activation output of every conv layer, [N, H]
+  float* emb;                     // [B, 2H]
+  float* scratch_a;               // [N, H] global scratch for graphs that exceed the smem capacity
+  float* scratch_b;               // [N, H]
+  int* status;                    // device status word (may be NULL)
+  int64_t B;
+  int F, Fp, L;
+  int ncap, ecap;                 // per-graph node / edge capacity of the shared-memory path
+  float slope, fill;
+};
+
+// bytes of dynamic shared memory the kernel needs for a given capacity
+size_t fused_fwd_smem_bytes(int F, int L, int ncap, int ecap);
+// launches the kernel; grid sized from the SM count and the achievable residency
+int launch_fused_fwd(const FusedFwdArgs& a, size_t smem, cudaStream_t st);
+
+}  // namespace hcg

@@ -9,6 +9,7 @@
 // (neighbour sum, segment max/mean, weight-gradient sums) walks its operands in a fixed order,
 // so there are no floating-point atomics and results are run-to-run identical.
 #include "hcg_common.cuh"
+#include "hcg_fused.cuh"
 
 namespace hcg {
 
@@ -525,10 +526,45 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
   const int H = p->H;
   note_region(st);
 
+  // ---- graph-resident path: conv layers + pooling in one kernel, then the readout --------------
+  const int path = config_get(HCG_CFG_FORWARD_PATH);
+  const bool fusable = H == kFusedH && p->F <= kMaxFusedF && g->ew0 == nullptr && B > 0 && N > 0 &&
+                       !(g->flags & HCG_GRAPH_CROSS_EDGES);
+  // molecule-sized graphs only: one CTA walks a graph, so a batch of few huge graphs stays layer-wise
+  const bool molecule_like = N / (B > 0 ? B : 1) <= 512;
+  if (path == 2 && !fusable)
+    return set_err(HCG_ERR_UNSUPPORTED, "graph-resident forward needs H == %d, F <= %d and no edge weights", kFusedH, kMaxFusedF);
+  bool fused_done = false;
+  if (path == 2 || (path == 0 && fusable && molecule_like)) {
+    FusedFwdArgs a{};
+    a.rowptr = g->rowptr; a.col = g->col; a.dis = g->dis; a.graph_ptr = g->graph_ptr; a.x = x;
+    for (int l = 0; l < p->L; ++l) {
+      a.conv_w[l] = p->conv_w[l]; a.conv_b[l] = p->conv_b[l];
+      a.save_act[l] = saved ? saved->acts[l] : nullptr;
+      if (saved) HCG_REQUIRE(saved->acts[l] != nullptr, HCG_ERR_INVALID_ARG, "saved->acts[%d] is NULL", l);
+    }
+    a.emb = emb; a.scratch_a = w.act[0]; a.scratch_b = w.act[1]; a.status = nullptr;
+    a.B = B; a.F = p->F; a.Fp = (p->F + 3) / 4 * 4; a.L = p->L; a.slope = p->slope; a.fill = g->fill;
+    // capacity: 128 nodes covers RhCAA (max 127) and the synthetic screening graphs (<= 120) with two
+    // CTAs per SM; a hint above that selects 256 (biaryl: max 184) if it fits, at one CTA per SM
+    int ncap = 128;
+    if (g->max_graph_nodes > 128) ncap = 256;
+    size_t smem = fused_fwd_smem_bytes(p->F, p->L, ncap, 6 * ncap);
+    if (smem > 227 * 1024 && ncap > 128) { ncap = 128; smem = fused_fwd_smem_bytes(p->F, p->L, ncap, 6 * ncap); }
+    if (smem <= 227 * 1024) {
+      a.ncap = ncap; a.ecap = 6 * ncap;
+      rc = launch_fused_fwd(a, smem, st);
+      if (rc) return rc;
+      fused_done = true;
+    } else if (path == 2) {
+      return set_err(HCG_ERR_UNSUPPORTED, "graph-resident forward: %d conv layers do not fit in shared memory", p->L);
+    }
+  }
+
   const float* h_in = x;
   int k_in = p->F;
   float* h_out = nullptr;
-  for (int l = 0; l < p->L; ++l) {
+  for (int l = 0; l < p->L && !fused_done; ++l) {
     rc = launch_gemm<true>(h_in, p->conv_w[l], w.T, N, k_in, H, EPI_NONE, nullptr, p->slope, st);
     if (rc) return rc;
     h_out = saved ? saved->acts[l] : w.act[l & 1];
@@ -540,7 +576,7 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
     h_in = h_out;
     k_in = H;
   }
-  if (B > 0) {
+  if (B > 0 && !fused_done) {
     int lpr = lanes_per_row(H, 1);
     k_pool<<<(unsigned)cdiv(B, 256 / lpr), 256, 0, st>>>(h_out, g->graph_ptr, B, H, lpr, emb);
     HCG_LAUNCH_OK(st, "k_pool");

@@ -126,6 +126,18 @@ extern "C" int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts
   return n < 0 ? 0 : -n;  // non-positive: -(rows written); positive values are error codes
 }
 
+static std::atomic<int> g_cfg[HCG_CFG_COUNT_];
+
+namespace hcg {
+int config_get(int key) { return (key >= 0 && key < HCG_CFG_COUNT_) ? g_cfg[key].load() : -1; }
+}  // namespace hcg
+
+extern "C" int hcg_config_set(int key, int value) {
+  if (key < 0 || key >= HCG_CFG_COUNT_) return -1;
+  return g_cfg[key].exchange(value);
+}
+extern "C" int hcg_config_get(int key) { return hcg::config_get(key); }
+
 // struct sizes, so that a foreign-language binding can verify its mirror of include/hcg.h
 extern "C" size_t hcg_sizeof_graph(void) { return sizeof(HcgGraph); }
 extern "C" size_t hcg_sizeof_params(void) { return sizeof(HcgParams); }

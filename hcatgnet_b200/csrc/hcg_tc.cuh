@@ -1,0 +1,79 @@
+// Building blocks of the tensor-core (tcgen05, TF32 x 3 split) dense product used inside the
+// graph-resident kernel:  D[128 x 64] = A[128 x K] . W[64 x K]^T  with fp32-level accuracy.
+//
+// fp32 operands are split  v = hi + lo,  hi = v with the 13 low mantissa bits cleared (exactly a
+// TF32 number), lo = (v - hi) cleared the same way; D accumulates hi.hi + hi.lo + lo.hi in fp32.
+// The dropped lo.lo term and the truncation of lo are O(2^-22) relative per product — the same
+// order as fp32 rounding — which is what the 1e-5 parity bound of the GCN path needs; plain TF32
+// (2^-11) would miss it by two orders of magnitude.
+//
+// A lives in tensor memory (thread r of the 128-thread group owns row r = TMEM lane r; column k
+// holds A[r][k]), written with tcgen05.st straight from the registers that produced the row.
+// W^T tiles live in shared memory in the K-major / 128-byte-swizzle layout the MMA reads.
+#pragma once
+
+#include "hcg_ptx.cuh"
+
+namespace hcg {
+namespace tc {
+
+constexpr int kRows = 128;       // M of the MMA = rows (nodes) per tile = threads per group
+constexpr int kN = 64;           // N of the MMA = hidden width
+constexpr int kChunkFloats = kN * 32;  // one K-chunk (32 floats = 128 B per row) of a W tile
+
+__device__ __forceinline__ uint32_t tf32_hi(float v) { return __float_as_uint(v) & 0xffffe000u; }
+__device__ __forceinline__ uint32_t tf32_lo(float v, uint32_t hi) {
+  return __float_as_uint(v - __uint_as_float(hi)) & 0xffffe000u;
+}
+
+// float offset of element (n, k) inside a W tile of [K/32 chunks][64 rows][32 floats], swizzled
+__device__ __forceinline__ int w_tile_offset(int n, int k) {
+  const int chunk = k >> 5, kk = k & 31;
+  return chunk * kChunkFloats + (n >> 3) * 256 + (n & 7) * 32 + ((((kk >> 2) ^ (n & 7)) << 2) | (kk & 3));
+}
+
+// W: global [64][Kin] row-major (state_dict layout [out][in]).  Writes the hi / lo tiles for K
+// padded to Kpad (32 or 64).  Cooperative over `nthreads` threads; tiles must be 1024-B aligned.
+__device__ __forceinline__ void prep_weight_tiles(const float* __restrict__ W, int Kin, int Kpad, float* s_hi,
+                                                  float* s_lo, int tid, int nthreads) {
+  for (int idx = tid; idx < kN * Kpad; idx += nthreads) {
+    const int n = idx / Kpad, k = idx - n * Kpad;
+    const float v = k < Kin ? __ldg(W + n * Kin + k) : 0.f;
+    const uint32_t hi = tf32_hi(v), lo = tf32_lo(v, hi);
+    const int off = w_tile_offset(n, k);
+    s_hi[off] = __uint_as_float(hi);
+    s_lo[off] = __uint_as_float(lo);
+  }
+}
+
+// One layer's product: ksteps = K/8 MMAs of K = 8 for each of the three split terms.  Issued by a
+// single thread; the caller commits.  a_*: TMEM addresses (lane 0 of the group, first column).
+__device__ __forceinline__ void issue_split_mma(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi_smem,
+                                                uint32_t b_lo_smem, int ksteps) {
+  constexpr uint32_t idesc = ptx::make_idesc_tf32(kRows, kN);
+  for (int s = 0; s < ksteps; ++s) {
+    const uint32_t boff = (uint32_t)(s >> 2) * (kChunkFloats * 4) + (uint32_t)(s & 3) * 32;
+    const uint64_t bh = ptx::make_kmajor_sw128_desc(b_hi_smem + boff);
+    const uint64_t bl = ptx::make_kmajor_sw128_desc(b_lo_smem + boff);
+    const uint32_t acol = (uint32_t)s * 8;
+    ptx::mma_tf32_ts(d_tmem, a_lo + acol, bh, idesc, s > 0 ? 1u : 0u);
+    ptx::mma_tf32_ts(d_tmem, a_hi + acol, bl, idesc, 1u);
+    ptx::mma_tf32_ts(d_tmem, a_hi + acol, bh, idesc, 1u);
+  }
+}
+
+// Splits 16 consecutive values of this thread's row and stores them to tensor memory columns
+// [col, col+16) of the hi and lo operands.  `trow` = TMEM lane base of this warp (32 * warp-in-group) << 16.
+__device__ __forceinline__ void store_split16(const float (&v)[16], uint32_t a_hi, uint32_t a_lo, uint32_t trow, int col) {
+  uint32_t h[16], l[16];
+#pragma unroll
+  for (int q = 0; q < 16; ++q) {
+    h[q] = tf32_hi(v[q]);
+    l[q] = tf32_lo(v[q], h[q]);
+  }
+  ptx::tmem_st16(a_hi + trow + col, h);
+  ptx::tmem_st16(a_lo + trow + col, l);
+}
+
+}  // namespace tc
+}  // namespace hcg

@@ -29,6 +29,10 @@ class Batch:
         if num_graphs is None:
             num_graphs = (int(ptr.numel()) - 1) if ptr is not None else (int(batch.max()) + 1 if batch.numel() else 0)
         self.num_graphs = int(num_graphs)
+        # size of the largest graph, kept as a host integer (it survives .to(device)); 0 = unknown
+        self.max_graph_nodes = 0
+        if ptr is not None and not ptr.is_cuda and ptr.numel() >= 2:
+            self.max_graph_nodes = int((ptr[1:] - ptr[:-1]).max())
 
     @classmethod
     def from_data_list(cls, graphs: Sequence) -> "Batch":

@@ -75,6 +75,20 @@ def _num_graphs_of(graph, batch, n_nodes: int) -> int:
     return int(batch.max().item()) + 1 if batch.numel() else 0  # one sync, as PyG's pooling does
 
 
+def _max_nodes_hint(graph) -> int:
+    """Largest graph of the batch when that is known without touching the device (a host-side
+    ``ptr``); 0 = unknown.  Only sizes a kernel's shared-memory capacity."""
+    if graph is None:
+        return 0
+    known = int(getattr(graph, "max_graph_nodes", 0) or 0)
+    if known:
+        return known
+    ptr = getattr(graph, "ptr", None)
+    if ptr is None or ptr.is_cuda or ptr.numel() < 2:
+        return 0
+    return int((ptr[1:] - ptr[:-1]).max())
+
+
 class _GCNBase(BaseNetwork):
     """Everything reference GCN and GCN_explain share (their constructors are identical,
     reference model/gcn.py:11-50 and :81-120)."""
@@ -130,7 +144,7 @@ class _GCNBase(BaseNetwork):
             raise NotImplementedError("gradients w.r.t. edge_weight are not provided by libhcg yet")
         plan = ops.cached_collate(cache_on, edge_index, batch, x.shape[0], num_graphs, device,
                                   edge_weight=edge_weight, improved=bool(self.improved), transpose=need_grad,
-                                  validate=self.validate_inputs)
+                                  validate=self.validate_inputs, max_graph_nodes=_max_nodes_hint(cache_on))
         xd = ops.to_device(x, device, torch.float32)
         pd = [ops.to_device(p, device, torch.float32) for p in params]
         out, emb = ops.gcn_apply(xd, plan, self._dims(), pd)

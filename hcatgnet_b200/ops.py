@@ -69,6 +69,8 @@ class GraphPlan:
     t_ew0: torch.Tensor | None = None
     selfw0: torch.Tensor | None = None
     dis0: torch.Tensor | None = None
+    flags: int = 0             # HCG_GRAPH_* bits reported by hcg_collate_status
+    max_graph_nodes: int = 0   # hint (0 = unknown): sizes the smem capacity of the graph-resident kernel
     _keep: list = field(default_factory=list, repr=False)
 
     @property
@@ -83,12 +85,12 @@ class GraphPlan:
         return _lib.HcgGraph(
             self.N, self.E, self.B, _ptr(self.rowptr), _ptr(self.col), _ptr(self.eid), _ptr(self.dis),
             _ptr(self.graph_ptr), _ptr(self.t_rowptr), _ptr(self.t_col), _ptr(self.t_eid), self.fill,
-            _ptr(self.ew0), _ptr(self.t_ew0), _ptr(self.selfw0), _ptr(self.dis0))
+            _ptr(self.ew0), _ptr(self.t_ew0), _ptr(self.selfw0), _ptr(self.dis0), int(self.max_graph_nodes), int(self.flags))
 
 
 def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int, num_graphs: int,
             edge_weight: torch.Tensor | None = None, improved: bool = False, transpose: bool = False,
-            fill: float = 1.0, validate: bool = True) -> GraphPlan:
+            fill: float = 1.0, validate: bool = True, max_graph_nodes: int = 0) -> GraphPlan:
     """COO ``edge_index`` [2,E] int64 + sorted ``batch`` [N] int64 -> :class:`GraphPlan`.
 
     Runs ``hcg_collate``.  ``improved`` only matters together with ``edge_weight`` (self-loop
@@ -115,7 +117,7 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
     with torch.cuda.device(device):
         plan = GraphPlan(N, E, B, torch.empty(N + 1, **i32), torch.empty(max(E, 1), **i32),
                          torch.empty(max(E, 1), **i32), torch.empty(max(N, 1), **f32), torch.empty(B + 1, **i32),
-                         fill=float(fill))
+                         fill=float(fill), max_graph_nodes=int(max_graph_nodes))
         flags = 0
         if transpose:
             flags |= _lib.HCG_COLLATE_TRANSPOSE
@@ -137,14 +139,16 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
             _ptr(plan.ew0), _ptr(plan.t_ew0), _ptr(plan.selfw0), _ptr(plan.dis0),
             _ptr(ws), ws.numel(), st))
         if validate:
-            _lib.check(lib.hcg_collate_status(_ptr(ws), st))
+            gflags = C.c_int32(0)
+            _lib.check(lib.hcg_collate_status(_ptr(ws), st, C.byref(gflags)))
+            plan.flags = int(gflags.value)
         else:
             ws.record_stream(torch.cuda.current_stream(device))
     return plan
 
 
 def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edge_weight=None,
-                   improved=False, transpose=False, validate=True) -> GraphPlan:
+                   improved=False, transpose=False, validate=True, max_graph_nodes=0) -> GraphPlan:
     """``collate`` memoised on ``holder`` (the batch object the caller passed to ``forward``).
 
     The reference recomputes the normalisation inside every GCNConv call of every forward
@@ -162,7 +166,8 @@ def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edg
     with torch.cuda.device(device):
         plan = collate(to_device(edge_index, device, torch.int64), to_device(batch, device, torch.int64),
                        num_nodes, num_graphs, edge_weight=to_device(edge_weight, device, torch.float32),
-                       improved=improved, transpose=transpose, validate=validate)
+                       improved=improved, transpose=transpose, validate=validate,
+                       max_graph_nodes=max_graph_nodes)
     if key is not None:
         try:
             object.__setattr__(holder, "_hcg_plan", (key, plan))

@@ -42,6 +42,12 @@ enum {
   HCG_ERR_BAD_BATCH = 6       /* batch vector not sorted / outside [0, B) */
 };
 
+/* HcgGraph.flags */
+enum {
+  HCG_GRAPH_CROSS_EDGES = 1   /* some edge joins two different graphs (reported by hcg_collate_status):
+                                 the batch is not a disjoint union, use the layer-wise kernels */
+};
+
 /* flags of hcg_collate */
 enum {
   HCG_COLLATE_TRANSPOSE = 1   /* also build the src-sorted (transposed) CSR for the backward pass */
@@ -74,6 +80,11 @@ typedef struct HcgGraph {
   const float* t_ew0;        /* [E] edge weight per transposed slot */
   const float* selfw0;       /* [N] self-loop weight per node */
   const float* dis0;         /* [N] weighted-degree^-1/2 */
+  /* Optional hint: node count of the largest graph of the batch (0 = unknown).  Only used to size
+   * the shared-memory capacity of the graph-resident kernels; a wrong hint costs speed, never
+   * correctness (graphs above the capacity run on global scratch). */
+  int32_t max_graph_nodes;
+  int32_t flags;             /* HCG_GRAPH_* bits */
 } HcgGraph;
 
 /*
@@ -129,6 +140,23 @@ uint64_t hcg_launch_count(void);
 int hcg_profile_enable(int on);
 int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts, int cap);
 
+/*
+ * Library-wide switches (tests and benchmarks; defaults are what production uses).
+ * HCG_CFG_FORWARD_PATH: 0 = auto (graph-resident kernel when H == 64, F <= 64, no edge weights and
+ * the batch looks like molecules; layer-wise kernels otherwise), 1 = force layer-wise,
+ * 2 = force graph-resident (HCG_ERR_UNSUPPORTED if not applicable).
+ * Both are CUDA paths; there is no CPU path.  Returns the previous value, or -1 for a bad key.
+ */
+enum { HCG_CFG_FORWARD_PATH = 0, HCG_CFG_COUNT_ = 1 };
+int hcg_config_set(int key, int value);
+int hcg_config_get(int key);
+
+/*
+ * Self-test of the tensor-core building block (split-TF32 tcgen05.mma with the A operand in tensor
+ * memory): D[128,64] = A[128,K] . W[64,K]^T, 1 <= K <= 64, fp32 in / fp32 out.  Test-suite only.
+ */
+int hcg_selftest_tc_gemm(const float* A, const float* W, int K, float* D, void* stream);
+
 /* sizeof() of the structs above, for bindings that mirror them (ctypes, cgo, JNI ...) */
 size_t hcg_sizeof_graph(void);
 size_t hcg_sizeof_params(void);
@@ -157,8 +185,10 @@ int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* batch, int6
                 float* ew0, float* t_ew0, float* selfw0, float* dis0,
                 void* ws, size_t ws_bytes, void* stream);
 
-/* Synchronises `stream`, reads the status word of the last hcg_collate that used `ws`. */
-int hcg_collate_status(const void* ws, void* stream);
+/* Synchronises `stream`, reads the status word of the last hcg_collate that used `ws`.  Returns
+ * HCG_ERR_BAD_INDEX / HCG_ERR_BAD_BATCH for unusable input; `graph_flags` (may be NULL) receives
+ * the HCG_GRAPH_* bits to put into HcgGraph.flags. */
+int hcg_collate_status(const void* ws, void* stream, int32_t* graph_flags);
 
 /* ---- forward (replaces GCNConv x L, LeakyReLU, global max/mean pool, readout MLP) ---------- */
 

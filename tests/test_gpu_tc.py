@@ -1,0 +1,28 @@
+"""The tensor-core building block (split-TF32 tcgen05.mma, A operand in tensor memory) against an
+fp64 matmul: the accuracy the GCN parity bound (1e-5 relative) relies on."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("K", [64, 32, 25, 8, 57])
+def test_tc_split_tf32_tile_product(K):
+    from hcatgnet_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(K)
+    A = (torch.randn(128, K, generator=g) * 3).cuda()
+    W = torch.randn(64, K, generator=g).cuda()
+    D = torch.full((128, 64), float("nan"), device="cuda")
+    _lib.check(lib.hcg_selftest_tc_gemm(A.data_ptr(), W.data_ptr(), K, D.data_ptr(),
+                                         torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    ref = A.double().cpu() @ W.double().cpu().t()
+    scale = (A.double().abs().cpu() @ W.double().abs().cpu().t()).clamp(min=1e-30)   # condition-free error measure
+    err = ((D.double().cpu() - ref).abs() / scale).max().item()
+    assert err <= 2e-6, err
+    # and it really is better than one plain TF32 pass would be (2^-11 ~ 5e-4)
+    assert err < 1e-5
