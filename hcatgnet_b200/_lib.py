@@ -124,7 +124,7 @@ def check(code: int) -> None:
 
 
 HCG_CFG_FORWARD_PATH = 0
-PATH_AUTO, PATH_LAYERWISE, PATH_GRAPH_RESIDENT = 0, 1, 2
+PATH_AUTO, PATH_LAYERWISE, PATH_GRAPH_RESIDENT, PATH_TENSOR_CORE = 0, 1, 2, 3
 
 
 def config_set(key: int, value: int) -> int:

@@ -223,6 +223,8 @@ __global__ void __launch_bounds__(kFusedThreads, 2)
 k_fused_fwd(const FusedFwdArgs a) {
   extern __shared__ __align__(16) float smem_f[];
   const int tid = threadIdx.x;
+  const int64_t total = a.list ? (int64_t)*a.list_count : a.B;
+  if ((int64_t)blockIdx.x >= total) return;  // nothing for this CTA (an empty overflow list costs ~nothing)
   Smem s;
   {
     float* p = smem_f;
@@ -252,7 +254,8 @@ k_fused_fwd(const FusedFwdArgs a) {
     s.bias[idx] = __ldg(a.conv_b[idx / kFusedH] + idx % kFusedH);
   __syncthreads();
 
-  for (int64_t gid = blockIdx.x; gid < a.B; gid += gridDim.x) {
+  for (int64_t it = blockIdx.x; it < total; it += gridDim.x) {
+    const int64_t gid = a.list ? (int64_t)a.list[it] : it;
     GraphCtx g;
     g.n0 = a.graph_ptr[gid];
     g.n = a.graph_ptr[gid + 1] - g.n0;

@@ -26,6 +26,8 @@ struct FusedFwdArgs {
   float* scratch_a;               // [N, H] global scratch for graphs that exceed the smem capacity
   float* scratch_b;               // [N, H]
   int* status;                    // device status word (may be NULL)
+  const int* list;                // optional: only these graph ids are processed ...
+  const int* list_count;          // ... (device-resident count), e.g. the tensor-core kernel's overflow list
   int64_t B;
   int F, Fp, L;
   int ncap, ecap;                 // per-graph node / edge capacity of the shared-memory path
@@ -36,5 +38,12 @@ struct FusedFwdArgs {
 size_t fused_fwd_smem_bytes(int F, int L, int ncap, int ecap);
 // launches the kernel; grid sized from the SM count and the achievable residency
 int launch_fused_fwd(const FusedFwdArgs& a, size_t smem, cudaStream_t st);
+
+// tensor-core graph-resident forward (hcg_tc.cu): H == 64, F <= 32
+size_t tc_fwd_smem_bytes(int F, int L);
+size_t tc_fwd_workspace_bytes(int64_t B);
+// `a.scratch_*`, `a.ncap/ecap` describe the FMA kernel that picks up the overflow list; ws holds
+// the per-graph descriptors and that list
+int launch_tc_fwd(const FusedFwdArgs& a, int64_t N, int64_t E, void* ws, cudaStream_t st);
 
 }  // namespace hcg

@@ -452,6 +452,7 @@ struct FwdWs {
   float* T;
   float* act[2];
   float* hid[HCG_MAX_READOUT];
+  char* tc;
   size_t bytes;
 };
 
@@ -462,6 +463,7 @@ static FwdWs carve_fwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
   w.act[0] = c.take<float>((size_t)N * p->H + 4);
   w.act[1] = c.take<float>((size_t)N * p->H + 4);
   for (int k = 0; k < p->R - 1; ++k) w.hid[k] = c.take<float>((size_t)B * ro_out_dim(p, k) + 4);
+  w.tc = c.take<char>(tc_fwd_workspace_bytes(B));
   w.bytes = c.off;
   return w;
 }
@@ -532,10 +534,10 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
                        !(g->flags & HCG_GRAPH_CROSS_EDGES);
   // molecule-sized graphs only: one CTA walks a graph, so a batch of few huge graphs stays layer-wise
   const bool molecule_like = N / (B > 0 ? B : 1) <= 512;
-  if (path == 2 && !fusable)
-    return set_err(HCG_ERR_UNSUPPORTED, "graph-resident forward needs H == %d, F <= %d and no edge weights", kFusedH, kMaxFusedF);
+  if (path >= 2 && !fusable)
+    return set_err(HCG_ERR_UNSUPPORTED, "graph-resident forward needs H == %d, F <= %d, no edge weights and a disjoint batch", kFusedH, kMaxFusedF);
   bool fused_done = false;
-  if (path == 2 || (path == 0 && fusable && molecule_like)) {
+  if (path >= 2 || (path == 0 && fusable && molecule_like)) {
     FusedFwdArgs a{};
     a.rowptr = g->rowptr; a.col = g->col; a.dis = g->dis; a.graph_ptr = g->graph_ptr; a.x = x;
     for (int l = 0; l < p->L; ++l) {
@@ -545,18 +547,29 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
     }
     a.emb = emb; a.scratch_a = w.act[0]; a.scratch_b = w.act[1]; a.status = nullptr;
     a.B = B; a.F = p->F; a.Fp = (p->F + 3) / 4 * 4; a.L = p->L; a.slope = p->slope; a.fill = g->fill;
-    // capacity: 128 nodes covers RhCAA (max 127) and the synthetic screening graphs (<= 120) with two
-    // CTAs per SM; a hint above that selects 256 (biaryl: max 184) if it fits, at one CTA per SM
+    // FMA kernel capacity: 128 nodes covers RhCAA (max 127) and the synthetic screening graphs (<= 120)
+    // with two CTAs per SM; a hint above that selects 256 (biaryl: max 184) if it fits, at one CTA per SM
     int ncap = 128;
     if (g->max_graph_nodes > 128) ncap = 256;
     size_t smem = fused_fwd_smem_bytes(p->F, p->L, ncap, 6 * ncap);
     if (smem > 227 * 1024 && ncap > 128) { ncap = 128; smem = fused_fwd_smem_bytes(p->F, p->L, ncap, 6 * ncap); }
-    if (smem <= 227 * 1024) {
-      a.ncap = ncap; a.ecap = 6 * ncap;
+    const bool fma_fits = smem <= 227 * 1024;
+    a.ncap = ncap; a.ecap = 6 * ncap;
+    // tensor-core kernel: F <= 32, its smem must fit, the FMA kernel must exist for the overflow list,
+    // and the batch should mostly fit the 128-node slots
+    const bool tc_ok = p->F <= 32 && tc_fwd_smem_bytes(p->F, p->L) <= 227 * 1024 && fma_fits;
+    if (path == 3 && !tc_ok)
+      return set_err(HCG_ERR_UNSUPPORTED, "tensor-core forward needs F <= 32 and %d conv layers to fit in shared memory", p->L);
+    const bool want_tc = path == 3 || (path == 0 && tc_ok && (g->max_graph_nodes == 0 || g->max_graph_nodes <= 128));
+    if (want_tc) {
+      rc = launch_tc_fwd(a, N, g->E, w.tc, st);
+      if (rc) return rc;
+      fused_done = true;
+    } else if (fma_fits) {
       rc = launch_fused_fwd(a, smem, st);
       if (rc) return rc;
       fused_done = true;
-    } else if (path == 2) {
+    } else if (path >= 2) {
       return set_err(HCG_ERR_UNSUPPORTED, "graph-resident forward: %d conv layers do not fit in shared memory", p->L);
     }
   }

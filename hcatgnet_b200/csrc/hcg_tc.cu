@@ -28,7 +28,7 @@ k_tc_selftest(const float* __restrict__ A, const float* __restrict__ W, int K, f
   __syncthreads();
   ptx::tc_fence_after_sync();
   const uint32_t tbase = tmem_base_s;
-  const uint32_t d_t = tbase, a_hi = tbase + 64, a_lo = tbase + 128;
+  const uint32_t d_t = tbase, a_hi = tbase + 128, a_lo = tbase + 192;
   const uint32_t trow = (uint32_t)(warp * 32) << 16;
 
   for (int c0 = 0; c0 < Kpad; c0 += 16) {
@@ -48,11 +48,10 @@ k_tc_selftest(const float* __restrict__ A, const float* __restrict__ W, int K, f
   ptx::mbar_wait(&bar_mma, 0);
   ptx::tc_fence_after_sync();
   for (int c0 = 0; c0 < tc::kN; c0 += 16) {
-    uint32_t r[16];
-    ptx::tmem_ld16(d_t + trow + c0, r);
-    ptx::tmem_wait_ld();
+    float r[16];
+    tc::load_acc16(d_t, trow, c0, r);
 #pragma unroll
-    for (int q = 0; q < 16; ++q) D[tid * tc::kN + c0 + q] = __uint_as_float(r[q]);
+    for (int q = 0; q < 16; ++q) D[tid * tc::kN + c0 + q] = r[q];
   }
   ptx::tc_fence_before_sync();
   __syncthreads();
@@ -73,3 +72,423 @@ extern "C" int hcg_selftest_tc_gemm(const float* A, const float* W, int K, float
   HCG_LAUNCH_OK(st, "k_tc_selftest");
   return HCG_OK;
 }
+
+// =================================================================================================
+// Graph-resident forward on the tensor cores.
+//
+// A CTA holds two independent "slots" of 128 threads; a slot walks its share of the batch one graph
+// at a time with thread r of the slot owning node r of the graph (= row r of the MMA tile = lane r
+// of tensor memory):
+//
+//   prefetch   x rows, rowptr/col slice, deg^-1/2 of the NEXT graph: four bulk async copies
+//              (cp.async.bulk -> mbarrier), issued one graph ahead, double-buffered
+//   layer l    thread r gathers  a_r = sum_j norm_rj * h_j  (neighbours' rows from shared memory),
+//              splits it into TF32 hi/lo and stores it as row r of the A operand in tensor memory;
+//              one elected thread issues the split-TF32 tcgen05.mma chain against W_l^T (shared
+//              memory, swizzled) and commits to an mbarrier; every thread then pulls row r of the
+//              fp32 accumulator back (tcgen05.ld), adds bias, applies LeakyReLU and writes h_r to
+//              the slot's activation buffer (16-byte chunks XOR-swizzled by row: conflict-free for
+//              row-owner stores, column readers and neighbour gathers alike)
+//   pooling    column owners scan the last layer's rows: emb[g] = [max || mean]
+//
+// The two slots of a CTA run out of phase, so one slot's gathers overlap the other's MMAs.
+// Nothing of size [N,H] touches HBM unless the caller wants the activations (training forward).
+// Graphs above the slot capacity (128 nodes / kTcEcap CSR slots) are appended to an overflow list
+// that the FMA graph-resident kernel processes afterwards.
+// =================================================================================================
+namespace hcg {
+
+constexpr int kTcThreads = 256;
+constexpr int kTcSlots = 2;
+constexpr int kTcNcap = 128;
+constexpr int kTcEcap = 640;
+constexpr int kTcMaxF = 32;
+constexpr int kStatusCrossEdgeTc = 4;
+
+struct TcSlotMeta {
+  int n0, n, e0, e;
+  int lead_x, lead_rp, lead_cl, lead_ds;  // element offsets of the data inside the 16-byte aligned copies
+  int skip, pad0, pad1, pad2;
+};
+
+struct TcStage {
+  float* x;       // [ncap*F + 4]
+  int32_t* rp;    // [ncap + 1 + 4]
+  int32_t* cl;    // [ecap + 4]
+  float* ds;      // [ncap + 4]
+};
+
+__device__ __forceinline__ int h_off(int r, int c) {  // float offset of (row, col) in a swizzled [128][64] buffer
+  const int q = c >> 2;
+  return r * 64 + ((((q ^ r) & 7) | (q & 8)) << 2) + (c & 3);
+}
+
+// one contiguous slice global -> shared through the bulk-copy engine; returns the bytes in flight.
+// `count` elements of 4 bytes starting at `src`; data lands at dst + lead (elements).  A tail the
+// 16-byte granularity would read past `src_end` is fetched with ordinary loads instead.
+__device__ __forceinline__ uint32_t bulk_slice(void* dst, const void* src, int count, const void* src_end, int* lead,
+                                               uint64_t* bar) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(src);
+  const uintptr_t a_al = a & ~uintptr_t(15);
+  *lead = (int)((a - a_al) >> 2);
+  if (count <= 0) return 0;
+  uint32_t bytes = (uint32_t)(((a - a_al) + (uintptr_t)count * 4 + 15) & ~uintptr_t(15));
+  const uintptr_t avail = (reinterpret_cast<uintptr_t>(src_end) - a_al) & ~uintptr_t(15);
+  if (bytes > avail) {  // last elements of the array: copy them by hand
+    const int done = (int)((avail - (a - a_al)) >> 2);
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(dst) + *lead;
+    for (int i = done < 0 ? 0 : done; i < count; ++i) d32[i] = __ldg(s32 + i);
+    bytes = (uint32_t)avail;
+  }
+  if (bytes) ptx::bulk_g2s(dst, reinterpret_cast<const void*>(a_al), bytes, bar);
+  return bytes;
+}
+
+struct TcArgs {
+  FusedFwdArgs f;
+  const int4* gdesc;     // [B] {n0, n, e0, e}
+  int* overflow_count;
+  int* overflow_list;    // [B]
+  const void* x_end;
+  const void* rp_end;
+  const void* cl_end;
+  const void* ds_end;
+};
+
+__global__ void __launch_bounds__(256)
+k_graph_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ rowptr, int64_t B, int4* __restrict__ gdesc) {
+  int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= B) return;
+  int n0 = graph_ptr[g], n1 = graph_ptr[g + 1];
+  int e0 = rowptr[n0], e1 = rowptr[n1];
+  gdesc[g] = make_int4(n0, n1 - n0, e0, e1 - e0);
+}
+
+// thread 0 of a slot: start the copies of one graph into a stage (or mark it skipped / overflowed)
+__device__ __forceinline__ void tc_prefetch(const TcArgs& a, int64_t gid, int4 d, const TcStage& st, TcSlotMeta* meta,
+                                            uint64_t* bar) {
+  meta->n0 = d.x; meta->n = d.y; meta->e0 = d.z; meta->e = d.w;
+  if (d.y > kTcNcap || d.w > kTcEcap) {
+    meta->skip = 1;
+    const int pos = atomicAdd(a.overflow_count, 1);
+    a.overflow_list[pos] = (int)gid;
+    ptx::mbar_arrive(bar);
+    return;
+  }
+  meta->skip = 0;
+  uint32_t bytes = 0;
+  bytes += bulk_slice(st.x, a.f.x + (int64_t)d.x * a.f.F, d.y * a.f.F, a.x_end, &meta->lead_x, bar);
+  bytes += bulk_slice(st.rp, a.f.rowptr + d.x, d.y + 1, a.rp_end, &meta->lead_rp, bar);
+  bytes += bulk_slice(st.cl, a.f.col + d.z, d.w, a.cl_end, &meta->lead_cl, bar);
+  bytes += bulk_slice(st.ds, a.f.dis + d.x, d.y, a.ds_end, &meta->lead_ds, bar);
+  ptx::mbar_expect_tx(bar, bytes);  // the slot's single arrival for this phase + the bytes in flight
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+k_tc_fwd(const TcArgs a) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  __shared__ uint64_t bar_stage[kTcSlots][2];
+  __shared__ uint64_t bar_mma[kTcSlots];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ TcSlotMeta metas[kTcSlots][2];
+
+  const int tid = threadIdx.x;
+  const int slot = tid >> 7, gt = tid & 127, gw = gt >> 5;
+  const int F = a.f.F, L = a.f.L;
+
+  // ---- carve shared memory ---------------------------------------------------------------------
+  unsigned char* p = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* w0_hi = reinterpret_cast<float*>(p); p += tc::kN * 32 * 4;
+  float* w0_lo = reinterpret_cast<float*>(p); p += tc::kN * 32 * 4;
+  float* wl_base = reinterpret_cast<float*>(p); p += (size_t)(L - 1) * 2 * tc::kN * 64 * 4;  // per layer: hi, lo
+  float* s_bias = reinterpret_cast<float*>(p); p += (size_t)L * 64 * 4;
+  float* Hbuf = reinterpret_cast<float*>(p) + (size_t)slot * kTcNcap * 64; p += (size_t)kTcSlots * kTcNcap * 64 * 4;
+  float* s_pool = reinterpret_cast<float*>(p) + slot * 128; p += kTcSlots * 128 * 4;
+  const size_t x_bytes = ((size_t)kTcNcap * F * 4 + 16 + 15) & ~size_t(15);
+  const size_t rp_bytes = ((size_t)(kTcNcap + 1) * 4 + 16 + 15) & ~size_t(15);
+  const size_t cl_bytes = ((size_t)kTcEcap * 4 + 16 + 15) & ~size_t(15);
+  const size_t ds_bytes = ((size_t)kTcNcap * 4 + 16 + 15) & ~size_t(15);
+  const size_t stage_bytes = x_bytes + rp_bytes + cl_bytes + ds_bytes;
+  TcStage stg[2];
+#pragma unroll
+  for (int s = 0; s < 2; ++s) {
+    unsigned char* q = p + ((size_t)slot * 2 + s) * stage_bytes;
+    stg[s].x = reinterpret_cast<float*>(q); q += x_bytes;
+    stg[s].rp = reinterpret_cast<int32_t*>(q); q += rp_bytes;
+    stg[s].cl = reinterpret_cast<int32_t*>(q); q += cl_bytes;
+    stg[s].ds = reinterpret_cast<float*>(q);
+  }
+
+  // ---- one-time setup ----------------------------------------------------------------------------
+  if (tid < 32) ptx::tmem_alloc(&tmem_base_s, 512);
+  if (tid == 0) {
+    for (int s = 0; s < kTcSlots; ++s) {
+      ptx::mbar_init(&bar_stage[s][0], 1);
+      ptx::mbar_init(&bar_stage[s][1], 1);
+      ptx::mbar_init(&bar_mma[s], 1);
+    }
+    ptx::fence_mbar_init();
+  }
+  tc::prep_weight_tiles(a.f.conv_w[0], F, 32, w0_hi, w0_lo, tid, kTcThreads);
+  for (int l = 1; l < L; ++l)
+    tc::prep_weight_tiles(a.f.conv_w[l], 64, 64, wl_base + (size_t)(l - 1) * 2 * tc::kN * 64,
+                          wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64, tid, kTcThreads);
+  for (int idx = tid; idx < L * 64; idx += kTcThreads) s_bias[idx] = __ldg(a.f.conv_b[idx >> 6] + (idx & 63));
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  ptx::tc_fence_after_sync();
+
+  const uint32_t tbase = tmem_base_s + (uint32_t)slot * 256;  // big acc | small acc | A hi | A lo, 64 columns each
+  const uint32_t d_t = tbase, a_hi = tbase + 128, a_lo = tbase + 192;
+  const uint32_t trow = (uint32_t)(gw * 32) << 16;
+  const int bar_id = 1 + slot;
+  const int ksteps0 = (F + 7) >> 3;
+  const int xstride = (F & 1) ? F : F + 1;  // odd row stride: row-owner reads hit distinct banks
+
+  const int64_t first = (int64_t)blockIdx.x * kTcSlots + slot;
+  const int64_t stride = (int64_t)gridDim.x * kTcSlots;
+  int4 d_next = make_int4(0, 0, 0, 0);
+  if (gt == 0 && first < a.f.B) {
+    tc_prefetch(a, first, a.gdesc[first], stg[0], &metas[slot][0], &bar_stage[slot][0]);
+    if (first + stride < a.f.B) d_next = a.gdesc[first + stride];
+  }
+  uint32_t mma_phase = 0;
+  int k = 0;
+  for (int64_t gid = first; gid < a.f.B; gid += stride, ++k) {
+    const int s = k & 1;
+    if (gt == 0 && gid + stride < a.f.B) {  // next graph -> the other stage (its readers finished last iteration)
+      tc_prefetch(a, gid + stride, d_next, stg[s ^ 1], &metas[slot][s ^ 1], &bar_stage[slot][s ^ 1]);
+      if (gid + 2 * stride < a.f.B) d_next = a.gdesc[gid + 2 * stride];
+    }
+    ptx::mbar_wait(&bar_stage[slot][s], (uint32_t)(k >> 1) & 1u);
+    const TcSlotMeta m = metas[slot][s];
+    if (m.skip) continue;  // slot-uniform
+    const int n = m.n, n0 = m.n0, e0 = m.e0;
+    const float* xs = stg[s].x + m.lead_x;
+    const int32_t* rp = stg[s].rp + m.lead_rp;
+    const int32_t* cl = stg[s].cl + m.lead_cl;
+    const float* ds = stg[s].ds + m.lead_ds;
+    const int i = gt;
+    const bool row_ok = i < n;
+
+    if (!(F & 1)) {  // even F: re-pitch the rows to F + 1 floats inside the (idle) activation buffer
+      for (int idx = gt; idx < n * F; idx += 128) {
+        const int r = idx / F;
+        Hbuf[r * xstride + (idx - r * F)] = xs[idx];
+      }
+      ptx::named_bar_sync(bar_id, 128);
+      xs = Hbuf;
+    }
+    int beg = 0, end = 0;
+    float di = 0.f;
+    if (row_ok) { beg = rp[i] - e0; end = rp[i + 1] - e0; di = ds[i]; }
+    const float wself = (di * a.f.fill) * di;
+
+    // ---- layer 0: a_r = sum_j norm_rj x_j  (F <= 32 columns) ------------------------------------
+    {
+      float acc[32];
+#pragma unroll
+      for (int c = 0; c < 32; ++c) acc[c] = 0.f;
+      if (row_ok) {
+        for (int kk = beg; kk < end; ++kk) {
+          int j = cl[kk] - n0;
+          const bool ok = (unsigned)j < (unsigned)n;
+          if (!ok) { if (a.f.status) atomicOr(a.f.status, kStatusCrossEdgeTc); j = i; }
+          const float w = ok ? ds[j] * di : 0.f;
+          const float* xr = xs + j * xstride;
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            if (c < F) acc[c] = fmaf(w, xr[c], acc[c]);
+        }
+        const float* xr = xs + i * xstride;
+#pragma unroll
+        for (int c = 0; c < 32; ++c)
+          if (c < F) acc[c] = fmaf(wself, xr[c], acc[c]);
+      }
+      float v[16];
+#pragma unroll
+      for (int q = 0; q < 16; ++q) v[q] = acc[q];
+      tc::store_split16(v, a_hi, a_lo, trow, 0);
+#pragma unroll
+      for (int q = 0; q < 16; ++q) v[q] = acc[16 + q];
+      tc::store_split16(v, a_hi, a_lo, trow, 16);
+    }
+
+    for (int l = 0; l < L; ++l) {
+      const bool last = l == L - 1;
+      ptx::tmem_wait_st();
+      ptx::tc_fence_before_sync();
+      ptx::named_bar_sync(bar_id, 128);  // A operand complete; previous readers of Hbuf / D are done
+      if (gt == 0) {
+        ptx::tc_fence_after_sync();
+        if (l == 0)
+          tc::issue_split_mma(d_t, a_hi, a_lo, ptx::smem_u32(w0_hi), ptx::smem_u32(w0_lo), ksteps0);
+        else
+          tc::issue_split_mma(d_t, a_hi, a_lo, ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64),
+                              ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64), 8);
+        ptx::mma_commit(&bar_mma[slot]);
+      }
+      ptx::mbar_wait(&bar_mma[slot], mma_phase);
+      mma_phase ^= 1u;
+      ptx::tc_fence_after_sync();
+
+      // ---- epilogue: h_r = lrelu(D_r + b_l) -> swizzled activation buffer (+ optional save) ------
+      float* save = a.f.save_act[l];
+#pragma unroll
+      for (int c0 = 0; c0 < 64; c0 += 16) {
+        float r[16];
+        tc::load_acc16(d_t, trow, c0, r);
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+          const float4 b4 = *reinterpret_cast<const float4*>(s_bias + l * 64 + c0 + 4 * q4);
+          float4 v;
+          v.x = lrelu(r[4 * q4 + 0] + b4.x, a.f.slope);
+          v.y = lrelu(r[4 * q4 + 1] + b4.y, a.f.slope);
+          v.z = lrelu(r[4 * q4 + 2] + b4.z, a.f.slope);
+          v.w = lrelu(r[4 * q4 + 3] + b4.w, a.f.slope);
+          *reinterpret_cast<float4*>(Hbuf + h_off(i, c0 + 4 * q4)) = v;
+          if (save && row_ok) *reinterpret_cast<float4*>(save + ((int64_t)n0 + i) * 64 + c0 + 4 * q4) = v;
+        }
+      }
+      ptx::tc_fence_before_sync();
+      ptx::named_bar_sync(bar_id, 128);  // h complete in shared memory; D may be overwritten
+
+      if (!last) {
+        // ---- next layer's A operand: a_r = sum_j norm_rj h_j  (64 columns) ------------------------
+        float acc[64];
+#pragma unroll
+        for (int c = 0; c < 64; ++c) acc[c] = 0.f;
+        if (row_ok) {
+          for (int kk = beg; kk <= end; ++kk) {  // kk == end: the self-loop, last as in the reference
+            int j = i;
+            float w = wself;
+            if (kk < end) {
+              j = cl[kk] - n0;
+              const bool ok = (unsigned)j < (unsigned)n;
+              if (!ok) j = i;
+              w = ok ? ds[j] * di : 0.f;
+            }
+            const float* hr = Hbuf + j * 64;
+            const int sw = j & 7;
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+              const float4 h4 = *reinterpret_cast<const float4*>(hr + ((((q ^ sw) & 7) | (q & 8)) << 2));
+              acc[4 * q + 0] = fmaf(w, h4.x, acc[4 * q + 0]);
+              acc[4 * q + 1] = fmaf(w, h4.y, acc[4 * q + 1]);
+              acc[4 * q + 2] = fmaf(w, h4.z, acc[4 * q + 2]);
+              acc[4 * q + 3] = fmaf(w, h4.w, acc[4 * q + 3]);
+            }
+          }
+        }
+#pragma unroll
+        for (int c0 = 0; c0 < 64; c0 += 16) {
+          float v[16];
+#pragma unroll
+          for (int q = 0; q < 16; ++q) v[q] = acc[c0 + q];
+          tc::store_split16(v, a_hi, a_lo, trow, c0);
+        }
+      }
+    }
+
+    // ---- pooling over the graph's rows (column owners; two halves of the rows) -------------------
+    {
+      const int c = gt & 63, half = gt >> 6;
+      float mx = -INFINITY, sm = 0.f;
+      int r = half;
+      for (; r + 6 < n; r += 8) {
+        const float v0 = Hbuf[h_off(r, c)], v1 = Hbuf[h_off(r + 2, c)];
+        const float v2 = Hbuf[h_off(r + 4, c)], v3 = Hbuf[h_off(r + 6, c)];
+        mx = fmaxf(fmaxf(mx, v0), fmaxf(v1, fmaxf(v2, v3)));
+        sm += v0; sm += v1; sm += v2; sm += v3;
+      }
+      for (; r < n; r += 2) {
+        const float v0 = Hbuf[h_off(r, c)];
+        mx = fmaxf(mx, v0);
+        sm += v0;
+      }
+      if (half == 1) { s_pool[c] = mx; s_pool[64 + c] = sm; }
+      ptx::named_bar_sync(bar_id, 128);
+      if (half == 0) {
+        mx = fmaxf(mx, s_pool[c]);
+        sm += s_pool[64 + c];
+        a.f.emb[gid * 128 + c] = n > 0 ? mx : 0.f;
+        a.f.emb[gid * 128 + 64 + c] = n > 0 ? sm / (float)n : 0.f;
+      }
+    }
+  }
+
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  if (tid < 32) ptx::tmem_dealloc(tmem_base_s, 512);
+}
+
+size_t tc_fwd_smem_bytes(int F, int L) {
+  const size_t x_bytes = ((size_t)kTcNcap * F * 4 + 16 + 15) & ~size_t(15);
+  const size_t rp_bytes = ((size_t)(kTcNcap + 1) * 4 + 16 + 15) & ~size_t(15);
+  const size_t cl_bytes = ((size_t)kTcEcap * 4 + 16 + 15) & ~size_t(15);
+  const size_t ds_bytes = ((size_t)kTcNcap * 4 + 16 + 15) & ~size_t(15);
+  return 1024 + 2 * tc::kN * 32 * 4 + (size_t)(L - 1) * 2 * tc::kN * 64 * 4 + (size_t)L * 64 * 4 +
+         (size_t)kTcSlots * kTcNcap * 64 * 4 + kTcSlots * 128 * 4 + (size_t)kTcSlots * 2 * (x_bytes + rp_bytes + cl_bytes + ds_bytes);
+}
+
+}  // namespace hcg
+
+namespace hcg {
+
+struct TcWs {
+  int4* gdesc;
+  int* overflow_count;
+  int* overflow_list;
+  size_t bytes;
+};
+
+static TcWs carve_tc(void* ws, int64_t B) {
+  Carver c(ws, (size_t)-1);
+  TcWs w{};
+  w.gdesc = c.take<int4>((size_t)B + 1);
+  w.overflow_count = c.take<int>(64);
+  w.overflow_list = c.take<int>((size_t)B + 1);
+  w.bytes = c.off;
+  return w;
+}
+
+size_t tc_fwd_workspace_bytes(int64_t B) { return carve_tc(nullptr, B).bytes; }
+
+int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStream_t st) {
+  if (f.B <= 0) return HCG_OK;
+  TcWs w = carve_tc(ws, f.B);
+  const size_t smem = tc_fwd_smem_bytes(f.F, f.L);
+  static thread_local size_t configured = 0;
+  if (smem > configured) {
+    HCG_CUDA_OK(cudaFuncSetAttribute(k_tc_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  HCG_CUDA_OK(cudaMemsetAsync(w.overflow_count, 0, sizeof(int), st));
+  k_graph_desc<<<(unsigned)cdiv(f.B, 256), 256, 0, st>>>(f.graph_ptr, f.rowptr, f.B, w.gdesc);
+  HCG_LAUNCH_OK(st, "k_graph_desc");
+
+  TcArgs a{};
+  a.f = f;
+  a.gdesc = w.gdesc;
+  a.overflow_count = w.overflow_count;
+  a.overflow_list = w.overflow_list;
+  a.x_end = f.x + N * f.F;
+  a.rp_end = f.rowptr + N + 1;
+  a.cl_end = f.col + E;
+  a.ds_end = f.dis + N;
+  int64_t grid = cdiv(f.B, kTcSlots);
+  if (grid > kNumSMs) grid = kNumSMs;
+  k_tc_fwd<<<(unsigned)grid, kTcThreads, smem, st>>>(a);
+  HCG_LAUNCH_OK(st, "k_tc_fwd");
+
+  // graphs above the slot capacity: the FMA graph-resident kernel walks the overflow list
+  FusedFwdArgs o = f;
+  o.list = w.overflow_list;
+  o.list_count = w.overflow_count;
+  const size_t osmem = fused_fwd_smem_bytes(f.F, f.L, o.ncap, o.ecap);
+  return launch_fused_fwd(o, osmem, st);
+}
+
+}  // namespace hcg

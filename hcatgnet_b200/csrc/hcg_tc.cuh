@@ -1,8 +1,8 @@
 // Building blocks of the tensor-core (tcgen05, TF32 x 3 split) dense product used inside the
 // graph-resident kernel:  D[128 x 64] = A[128 x K] . W[64 x K]^T  with fp32-level accuracy.
 //
-// fp32 operands are split  v = hi + lo,  hi = v with the 13 low mantissa bits cleared (exactly a
-// TF32 number), lo = (v - hi) cleared the same way; D accumulates hi.hi + hi.lo + lo.hi in fp32.
+// fp32 operands are split  v = hi + lo,  hi = v rounded to TF32 (13 low mantissa bits zero),
+// lo = (v - hi) rounded to TF32 as well; D accumulates hi.hi + hi.lo + lo.hi in fp32.
 // The dropped lo.lo term and the truncation of lo are O(2^-22) relative per product — the same
 // order as fp32 rounding — which is what the 1e-5 parity bound of the GCN path needs; plain TF32
 // (2^-11) would miss it by two orders of magnitude.
@@ -21,9 +21,10 @@ constexpr int kRows = 128;       // M of the MMA = rows (nodes) per tile = threa
 constexpr int kN = 64;           // N of the MMA = hidden width
 constexpr int kChunkFloats = kN * 32;  // one K-chunk (32 floats = 128 B per row) of a W tile
 
-__device__ __forceinline__ uint32_t tf32_hi(float v) { return __float_as_uint(v) & 0xffffe000u; }
+// round-to-nearest on the magnitude (bit pattern + half an ulp of TF32, then clear): |lo| <= 2^-12 |v|
+__device__ __forceinline__ uint32_t tf32_hi(float v) { return (__float_as_uint(v) + 0x1000u) & 0xffffe000u; }
 __device__ __forceinline__ uint32_t tf32_lo(float v, uint32_t hi) {
-  return __float_as_uint(v - __uint_as_float(hi)) & 0xffffe000u;
+  return (__float_as_uint(v - __uint_as_float(hi)) + 0x1000u) & 0xffffe000u;  // rounded too: |err| <= 2^-24 |v|
 }
 
 // float offset of element (n, k) inside a W tile of [K/32 chunks][64 rows][32 floats], swizzled
@@ -48,18 +49,34 @@ __device__ __forceinline__ void prep_weight_tiles(const float* __restrict__ W, i
 
 // One layer's product: ksteps = K/8 MMAs of K = 8 for each of the three split terms.  Issued by a
 // single thread; the caller commits.  a_*: TMEM addresses (lane 0 of the group, first column).
-__device__ __forceinline__ void issue_split_mma(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi_smem,
+// The tensor core truncates (rounds toward zero) when it adds into its accumulator, a bias that grows
+// with the number of accumulation steps at the accumulator's magnitude.  The large hi.hi chain and
+// the small cross terms therefore go to two separate accumulators (d_big: `ksteps` steps instead of
+// 3 x ksteps; d_small: its truncation is relative to values 2^-11 smaller); the epilogue adds the
+// two in fp32 round-to-nearest.  d_small = d_big + 64 columns.
+__device__ __forceinline__ void issue_split_mma(uint32_t d_big, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi_smem,
                                                 uint32_t b_lo_smem, int ksteps) {
   constexpr uint32_t idesc = ptx::make_idesc_tf32(kRows, kN);
+  const uint32_t d_small = d_big + kN;
   for (int s = 0; s < ksteps; ++s) {
     const uint32_t boff = (uint32_t)(s >> 2) * (kChunkFloats * 4) + (uint32_t)(s & 3) * 32;
     const uint64_t bh = ptx::make_kmajor_sw128_desc(b_hi_smem + boff);
     const uint64_t bl = ptx::make_kmajor_sw128_desc(b_lo_smem + boff);
     const uint32_t acol = (uint32_t)s * 8;
-    ptx::mma_tf32_ts(d_tmem, a_lo + acol, bh, idesc, s > 0 ? 1u : 0u);
-    ptx::mma_tf32_ts(d_tmem, a_hi + acol, bl, idesc, 1u);
-    ptx::mma_tf32_ts(d_tmem, a_hi + acol, bh, idesc, 1u);
+    ptx::mma_tf32_ts(d_small, a_lo + acol, bh, idesc, s > 0 ? 1u : 0u);
+    ptx::mma_tf32_ts(d_small, a_hi + acol, bl, idesc, 1u);
+    ptx::mma_tf32_ts(d_big, a_hi + acol, bh, idesc, s > 0 ? 1u : 0u);
   }
+}
+
+// Row r's 16 accumulator columns [c0, c0+16): big + small, as floats.
+__device__ __forceinline__ void load_acc16(uint32_t d_big, uint32_t trow, int c0, float (&out)[16]) {
+  uint32_t rb[16], rs[16];
+  ptx::tmem_ld16(d_big + trow + c0, rb);
+  ptx::tmem_ld16(d_big + kN + trow + c0, rs);
+  ptx::tmem_wait_ld();
+#pragma unroll
+  for (int q = 0; q < 16; ++q) out[q] = __uint_as_float(rb[q]) + __uint_as_float(rs[q]);
 }
 
 // Splits 16 consecutive values of this thread's row and stores them to tensor memory columns

@@ -142,9 +142,10 @@ int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts, int cap);
 
 /*
  * Library-wide switches (tests and benchmarks; defaults are what production uses).
- * HCG_CFG_FORWARD_PATH: 0 = auto (graph-resident kernel when H == 64, F <= 64, no edge weights and
- * the batch looks like molecules; layer-wise kernels otherwise), 1 = force layer-wise,
- * 2 = force graph-resident (HCG_ERR_UNSUPPORTED if not applicable).
+ * HCG_CFG_FORWARD_PATH: 0 = auto (graph-resident kernels when H == 64, no edge weights and the batch
+ * looks like molecules: the tensor-core kernel for F <= 32, the FMA kernel for F <= 64; layer-wise
+ * kernels otherwise), 1 = force layer-wise, 2 = force graph-resident FMA, 3 = force graph-resident
+ * tensor-core (HCG_ERR_UNSUPPORTED if not applicable).
  * Both are CUDA paths; there is no CPU path.  Returns the previous value, or -1 for a bad key.
  */
 enum { HCG_CFG_FORWARD_PATH = 0, HCG_CFG_COUNT_ = 1 };

@@ -23,6 +23,6 @@ def test_tc_split_tf32_tile_product(K):
     ref = A.double().cpu() @ W.double().cpu().t()
     scale = (A.double().abs().cpu() @ W.double().abs().cpu().t()).clamp(min=1e-30)   # condition-free error measure
     err = ((D.double().cpu() - ref).abs() / scale).max().item()
-    assert err <= 2e-6, err
-    # and it really is better than one plain TF32 pass would be (2^-11 ~ 5e-4)
-    assert err < 1e-5
+    print(f"K={K}: max |D - ref| / (|A| |W|^T) = {err:.3e}")
+    # fp32-class accuracy (a plain TF32 pass would sit at 2^-11 ~ 5e-4)
+    assert err <= 5e-7, err
