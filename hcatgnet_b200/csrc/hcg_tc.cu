@@ -98,8 +98,9 @@ extern "C" int hcg_selftest_tc_gemm(const float* A, const float* W, int K, float
 // =================================================================================================
 namespace hcg {
 
-constexpr int kTcThreads = 256;
-constexpr int kTcSlots = 2;
+constexpr int kTcSlots = 2;           // independent graph pipelines per CTA (tensor memory: 256 columns each)
+constexpr int kTcSlotThreads = 256;  // two threads per node row: each owns half of the columns
+constexpr int kTcThreads = kTcSlots * kTcSlotThreads;
 constexpr int kTcNcap = 128;
 constexpr int kTcEcap = 640;
 constexpr int kTcMaxF = 32;
@@ -185,8 +186,65 @@ __device__ __forceinline__ void tc_prefetch(const TcArgs& a, int64_t gid, int4 d
   ptx::mbar_expect_tx(bar, bytes);  // the slot's single arrival for this phase + the bytes in flight
 }
 
+// shared-memory carve-up, identical on host (size query) and device
+struct TcSmemLayout {
+  uint32_t w0_hi, w0_lo, wl, bias, hbuf, pool, stage;  // byte offsets from the 1024-aligned base
+  uint32_t x_bytes, rp_bytes, cl_bytes, ds_bytes, stage_bytes, total;
+};
+__host__ __device__ inline TcSmemLayout tc_layout(int F, int L) {
+  TcSmemLayout y;
+  uint32_t p = 0;
+  y.w0_hi = p; p += tc::kN * 32 * 4;
+  y.w0_lo = p; p += tc::kN * 32 * 4;
+  y.wl = p; p += (uint32_t)(L - 1) * 2 * tc::kN * 64 * 4;  // per layer: hi tile, lo tile
+  y.bias = p; p += (uint32_t)L * 64 * 4;
+  y.hbuf = p; p += (uint32_t)kTcSlots * kTcNcap * 64 * 4;
+  y.pool = p; p += (uint32_t)kTcSlots * 4 * 128 * 4;
+  y.x_bytes = ((uint32_t)kTcNcap * F * 4 + 16 + 15) & ~15u;
+  y.rp_bytes = ((uint32_t)(kTcNcap + 1) * 4 + 16 + 15) & ~15u;
+  y.cl_bytes = ((uint32_t)kTcEcap * 4 + 16 + 15) & ~15u;
+  y.ds_bytes = ((uint32_t)kTcNcap * 4 + 16 + 15) & ~15u;
+  y.stage_bytes = y.x_bytes + y.rp_bytes + y.cl_bytes + y.ds_bytes;
+  y.stage = p; p += (uint32_t)kTcSlots * 2 * y.stage_bytes;
+  y.total = p + 1024;  // slack for the 1024-byte alignment of the base
+  return y;
+}
+
+// Layer-0 gather of one thread: NCH 16-byte chunks of the rows of `xp` (pitch P floats), starting at
+// chunk `q0`: acc += w * x_j for every neighbour, then the self-loop.
+template <int NCH, int P>
+__device__ __forceinline__ void gather_x(float (&acc)[16], const float* xp, const int32_t* cl, const float* ds,
+                                         int beg, int end, int i, int n, int n0, float di, float wself, int q0,
+                                         int* status) {
+#pragma unroll
+  for (int c = 0; c < 16; ++c) acc[c] = 0.f;
+  for (int kk = beg; kk <= end; ++kk) {  // kk == end: the self-loop, last as in the reference
+    int j = i;
+    float w = wself;
+    if (kk < end) {
+      j = cl[kk] - n0;
+      const bool ok = (unsigned)j < (unsigned)n;
+      if (!ok) { if (status) atomicOr(status, kStatusCrossEdgeTc); j = i; }
+      w = ok ? ds[j] * di : 0.f;
+    }
+    const float4* xr = reinterpret_cast<const float4*>(xp + j * P) + q0;
+#pragma unroll
+    for (int q = 0; q < NCH; ++q) {
+      const float4 v = xr[q];
+      acc[4 * q + 0] = fmaf(w, v.x, acc[4 * q + 0]);
+      acc[4 * q + 1] = fmaf(w, v.y, acc[4 * q + 1]);
+      acc[4 * q + 2] = fmaf(w, v.z, acc[4 * q + 2]);
+      acc[4 * q + 3] = fmaf(w, v.w, acc[4 * q + 3]);
+    }
+  }
+}
+
+// NQ = 16-byte chunks per re-pitched x row (7: F <= 28, 8: F <= 32); the pitch P keeps P/4 odd so that
+// eight consecutive rows cover all 32 banks for 128-bit reads.
+template <int NQ>
 __global__ void __launch_bounds__(kTcThreads, 1)
 k_tc_fwd(const TcArgs a) {
+  constexpr int P = (NQ & 1) ? 4 * NQ : 4 * NQ + 4;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ uint64_t bar_stage[kTcSlots][2];
   __shared__ uint64_t bar_mma[kTcSlots];
@@ -194,31 +252,30 @@ k_tc_fwd(const TcArgs a) {
   __shared__ TcSlotMeta metas[kTcSlots][2];
 
   const int tid = threadIdx.x;
-  const int slot = tid >> 7, gt = tid & 127, gw = gt >> 5;
+  const int slot = tid / kTcSlotThreads, gt = tid % kTcSlotThreads;
+  const int half = gt >> 7;          // which half of the columns this thread works on
+  const int i = gt & 127;            // node (row) of the graph = TMEM lane
   const int F = a.f.F, L = a.f.L;
 
-  // ---- carve shared memory ---------------------------------------------------------------------
-  unsigned char* p = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  float* w0_hi = reinterpret_cast<float*>(p); p += tc::kN * 32 * 4;
-  float* w0_lo = reinterpret_cast<float*>(p); p += tc::kN * 32 * 4;
-  float* wl_base = reinterpret_cast<float*>(p); p += (size_t)(L - 1) * 2 * tc::kN * 64 * 4;  // per layer: hi, lo
-  float* s_bias = reinterpret_cast<float*>(p); p += (size_t)L * 64 * 4;
-  float* Hbuf = reinterpret_cast<float*>(p) + (size_t)slot * kTcNcap * 64; p += (size_t)kTcSlots * kTcNcap * 64 * 4;
-  float* s_pool = reinterpret_cast<float*>(p) + slot * 128; p += kTcSlots * 128 * 4;
-  const size_t x_bytes = ((size_t)kTcNcap * F * 4 + 16 + 15) & ~size_t(15);
-  const size_t rp_bytes = ((size_t)(kTcNcap + 1) * 4 + 16 + 15) & ~size_t(15);
-  const size_t cl_bytes = ((size_t)kTcEcap * 4 + 16 + 15) & ~size_t(15);
-  const size_t ds_bytes = ((size_t)kTcNcap * 4 + 16 + 15) & ~size_t(15);
-  const size_t stage_bytes = x_bytes + rp_bytes + cl_bytes + ds_bytes;
-  TcStage stg[2];
-#pragma unroll
-  for (int s = 0; s < 2; ++s) {
-    unsigned char* q = p + ((size_t)slot * 2 + s) * stage_bytes;
-    stg[s].x = reinterpret_cast<float*>(q); q += x_bytes;
-    stg[s].rp = reinterpret_cast<int32_t*>(q); q += rp_bytes;
-    stg[s].cl = reinterpret_cast<int32_t*>(q); q += cl_bytes;
-    stg[s].ds = reinterpret_cast<float*>(q);
-  }
+  // ---- carve shared memory (pointer arithmetic on the shared array only: keeps the address space) --
+  const TcSmemLayout lay = tc_layout(F, L);
+  unsigned char* base = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
+  float* w0_hi = reinterpret_cast<float*>(base + lay.w0_hi);
+  float* w0_lo = reinterpret_cast<float*>(base + lay.w0_lo);
+  float* wl_base = reinterpret_cast<float*>(base + lay.wl);
+  float* s_bias = reinterpret_cast<float*>(base + lay.bias);
+  float* Hbuf = reinterpret_cast<float*>(base + lay.hbuf) + (size_t)slot * kTcNcap * 64;
+  float* s_pool = reinterpret_cast<float*>(base + lay.pool) + slot * 4 * 128;
+  unsigned char* stage0 = base + lay.stage + (size_t)slot * 2 * lay.stage_bytes;
+  auto stage_of = [&](int s) {
+    TcStage t;
+    unsigned char* q = stage0 + (size_t)s * lay.stage_bytes;
+    t.x = reinterpret_cast<float*>(q); q += lay.x_bytes;
+    t.rp = reinterpret_cast<int32_t*>(q); q += lay.rp_bytes;
+    t.cl = reinterpret_cast<int32_t*>(q); q += lay.cl_bytes;
+    t.ds = reinterpret_cast<float*>(q);
+    return t;
+  };
 
   // ---- one-time setup ----------------------------------------------------------------------------
   if (tid < 32) ptx::tmem_alloc(&tmem_base_s, 512);
@@ -242,16 +299,15 @@ k_tc_fwd(const TcArgs a) {
 
   const uint32_t tbase = tmem_base_s + (uint32_t)slot * 256;  // big acc | small acc | A hi | A lo, 64 columns each
   const uint32_t d_t = tbase, a_hi = tbase + 128, a_lo = tbase + 192;
-  const uint32_t trow = (uint32_t)(gw * 32) << 16;
+  const uint32_t trow = (uint32_t)(((gt >> 5) & 3) * 32) << 16;  // warps w and w+4 share a lane quadrant
   const int bar_id = 1 + slot;
   const int ksteps0 = (F + 7) >> 3;
-  const int xstride = (F & 1) ? F : F + 1;  // odd row stride: row-owner reads hit distinct banks
 
   const int64_t first = (int64_t)blockIdx.x * kTcSlots + slot;
   const int64_t stride = (int64_t)gridDim.x * kTcSlots;
   int4 d_next = make_int4(0, 0, 0, 0);
   if (gt == 0 && first < a.f.B) {
-    tc_prefetch(a, first, a.gdesc[first], stg[0], &metas[slot][0], &bar_stage[slot][0]);
+    tc_prefetch(a, first, a.gdesc[first], stage_of(0), &metas[slot][0], &bar_stage[slot][0]);
     if (first + stride < a.f.B) d_next = a.gdesc[first + stride];
   }
   uint32_t mma_phase = 0;
@@ -259,68 +315,45 @@ k_tc_fwd(const TcArgs a) {
   for (int64_t gid = first; gid < a.f.B; gid += stride, ++k) {
     const int s = k & 1;
     if (gt == 0 && gid + stride < a.f.B) {  // next graph -> the other stage (its readers finished last iteration)
-      tc_prefetch(a, gid + stride, d_next, stg[s ^ 1], &metas[slot][s ^ 1], &bar_stage[slot][s ^ 1]);
+      tc_prefetch(a, gid + stride, d_next, stage_of(s ^ 1), &metas[slot][s ^ 1], &bar_stage[slot][s ^ 1]);
       if (gid + 2 * stride < a.f.B) d_next = a.gdesc[gid + 2 * stride];
     }
     ptx::mbar_wait(&bar_stage[slot][s], (uint32_t)(k >> 1) & 1u);
     const TcSlotMeta m = metas[slot][s];
     if (m.skip) continue;  // slot-uniform
     const int n = m.n, n0 = m.n0, e0 = m.e0;
-    const float* xs = stg[s].x + m.lead_x;
-    const int32_t* rp = stg[s].rp + m.lead_rp;
-    const int32_t* cl = stg[s].cl + m.lead_cl;
-    const float* ds = stg[s].ds + m.lead_ds;
-    const int i = gt;
+    const TcStage st = stage_of(s);
+    const float* xs = st.x + m.lead_x;
+    const int32_t* rp = st.rp + m.lead_rp;
+    const int32_t* cl = st.cl + m.lead_cl;
+    const float* ds = st.ds + m.lead_ds;
     const bool row_ok = i < n;
+    const bool warp_ok = (i & ~31) < n;  // this warp owns at least one node of the graph
 
-    if (!(F & 1)) {  // even F: re-pitch the rows to F + 1 floats inside the (idle) activation buffer
-      for (int idx = gt; idx < n * F; idx += 128) {
-        const int r = idx / F;
-        Hbuf[r * xstride + (idx - r * F)] = xs[idx];
-      }
-      ptx::named_bar_sync(bar_id, 128);
-      xs = Hbuf;
+    // ---- re-pitch the x rows to P floats (zero padded) inside the idle activation buffer ----------
+    for (int idx = gt; idx < n * P; idx += kTcSlotThreads) {
+      const int r = idx / P, c = idx - r * P;
+      Hbuf[idx] = c < F ? xs[r * F + c] : 0.f;
     }
-    int beg = 0, end = 0;
+    int beg = 0, end = -1;
     float di = 0.f;
     if (row_ok) { beg = rp[i] - e0; end = rp[i + 1] - e0; di = ds[i]; }
     const float wself = (di * a.f.fill) * di;
+    ptx::named_bar_sync(bar_id, kTcSlotThreads);
 
-    // ---- layer 0: a_r = sum_j norm_rj x_j  (F <= 32 columns) ------------------------------------
-    {
-      float acc[32];
-#pragma unroll
-      for (int c = 0; c < 32; ++c) acc[c] = 0.f;
-      if (row_ok) {
-        for (int kk = beg; kk < end; ++kk) {
-          int j = cl[kk] - n0;
-          const bool ok = (unsigned)j < (unsigned)n;
-          if (!ok) { if (a.f.status) atomicOr(a.f.status, kStatusCrossEdgeTc); j = i; }
-          const float w = ok ? ds[j] * di : 0.f;
-          const float* xr = xs + j * xstride;
-#pragma unroll
-          for (int c = 0; c < 32; ++c)
-            if (c < F) acc[c] = fmaf(w, xr[c], acc[c]);
-        }
-        const float* xr = xs + i * xstride;
-#pragma unroll
-        for (int c = 0; c < 32; ++c)
-          if (c < F) acc[c] = fmaf(wself, xr[c], acc[c]);
-      }
-      float v[16];
-#pragma unroll
-      for (int q = 0; q < 16; ++q) v[q] = acc[q];
-      tc::store_split16(v, a_hi, a_lo, trow, 0);
-#pragma unroll
-      for (int q = 0; q < 16; ++q) v[q] = acc[16 + q];
-      tc::store_split16(v, a_hi, a_lo, trow, 16);
+    // ---- layer 0: a_r = sum_j norm_rj x_j ; this thread's 16 of the (up to) 32 columns ---------------
+    if (warp_ok && half * 16 < ksteps0 * 8) {
+      float acc[16];
+      if (half == 0) gather_x<(NQ < 4 ? NQ : 4), P>(acc, Hbuf, cl, ds, beg, end, i, n, n0, di, wself, 0, a.f.status);
+      else           gather_x<(NQ > 4 ? NQ - 4 : 0), P>(acc, Hbuf, cl, ds, beg, end, i, n, n0, di, wself, 4, nullptr);
+      tc::store_split16(acc, a_hi, a_lo, trow, half * 16);
     }
 
     for (int l = 0; l < L; ++l) {
       const bool last = l == L - 1;
       ptx::tmem_wait_st();
       ptx::tc_fence_before_sync();
-      ptx::named_bar_sync(bar_id, 128);  // A operand complete; previous readers of Hbuf / D are done
+      ptx::named_bar_sync(bar_id, kTcSlotThreads);  // A operand complete; previous readers of Hbuf / D are done
       if (gt == 0) {
         ptx::tc_fence_after_sync();
         if (l == 0)
@@ -335,84 +368,86 @@ k_tc_fwd(const TcArgs a) {
       ptx::tc_fence_after_sync();
 
       // ---- epilogue: h_r = lrelu(D_r + b_l) -> swizzled activation buffer (+ optional save) ------
-      float* save = a.f.save_act[l];
+      if (warp_ok) {
+        float* save = a.f.save_act[l];
 #pragma unroll
-      for (int c0 = 0; c0 < 64; c0 += 16) {
-        float r[16];
-        tc::load_acc16(d_t, trow, c0, r);
+        for (int cc = 0; cc < 32; cc += 16) {
+          const int c0 = half * 32 + cc;
+          float r[16];
+          tc::load_acc16(d_t, trow, c0, r);
 #pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          const float4 b4 = *reinterpret_cast<const float4*>(s_bias + l * 64 + c0 + 4 * q4);
-          float4 v;
-          v.x = lrelu(r[4 * q4 + 0] + b4.x, a.f.slope);
-          v.y = lrelu(r[4 * q4 + 1] + b4.y, a.f.slope);
-          v.z = lrelu(r[4 * q4 + 2] + b4.z, a.f.slope);
-          v.w = lrelu(r[4 * q4 + 3] + b4.w, a.f.slope);
-          *reinterpret_cast<float4*>(Hbuf + h_off(i, c0 + 4 * q4)) = v;
-          if (save && row_ok) *reinterpret_cast<float4*>(save + ((int64_t)n0 + i) * 64 + c0 + 4 * q4) = v;
+          for (int q4 = 0; q4 < 4; ++q4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(s_bias + l * 64 + c0 + 4 * q4);
+            float4 v;
+            v.x = lrelu(r[4 * q4 + 0] + b4.x, a.f.slope);
+            v.y = lrelu(r[4 * q4 + 1] + b4.y, a.f.slope);
+            v.z = lrelu(r[4 * q4 + 2] + b4.z, a.f.slope);
+            v.w = lrelu(r[4 * q4 + 3] + b4.w, a.f.slope);
+            *reinterpret_cast<float4*>(Hbuf + h_off(i, c0 + 4 * q4)) = v;
+            if (save && row_ok) *reinterpret_cast<float4*>(save + ((int64_t)n0 + i) * 64 + c0 + 4 * q4) = v;
+          }
         }
       }
       ptx::tc_fence_before_sync();
-      ptx::named_bar_sync(bar_id, 128);  // h complete in shared memory; D may be overwritten
+      ptx::named_bar_sync(bar_id, kTcSlotThreads);  // h complete in shared memory; D may be overwritten
 
-      if (!last) {
-        // ---- next layer's A operand: a_r = sum_j norm_rj h_j  (64 columns) ------------------------
-        float acc[64];
+      if (!last && warp_ok) {
+        // ---- next layer's A operand: a_r = sum_j norm_rj h_j ; this thread's 32 of the 64 columns ----
+        float acc[32];
 #pragma unroll
-        for (int c = 0; c < 64; ++c) acc[c] = 0.f;
-        if (row_ok) {
-          for (int kk = beg; kk <= end; ++kk) {  // kk == end: the self-loop, last as in the reference
-            int j = i;
-            float w = wself;
-            if (kk < end) {
-              j = cl[kk] - n0;
-              const bool ok = (unsigned)j < (unsigned)n;
-              if (!ok) j = i;
-              w = ok ? ds[j] * di : 0.f;
-            }
-            const float* hr = Hbuf + j * 64;
-            const int sw = j & 7;
+        for (int c = 0; c < 32; ++c) acc[c] = 0.f;
+        for (int kk = beg; kk <= end; ++kk) {  // kk == end: the self-loop, last as in the reference
+          int j = i;
+          float w = wself;
+          if (kk < end) {
+            j = cl[kk] - n0;
+            const bool ok = (unsigned)j < (unsigned)n;
+            if (!ok) j = i;
+            w = ok ? ds[j] * di : 0.f;
+          }
+          const float* hr = Hbuf + j * 64 + half * 32;
+          const int sw = j & 7;
 #pragma unroll
-            for (int q = 0; q < 16; ++q) {
-              const float4 h4 = *reinterpret_cast<const float4*>(hr + ((((q ^ sw) & 7) | (q & 8)) << 2));
-              acc[4 * q + 0] = fmaf(w, h4.x, acc[4 * q + 0]);
-              acc[4 * q + 1] = fmaf(w, h4.y, acc[4 * q + 1]);
-              acc[4 * q + 2] = fmaf(w, h4.z, acc[4 * q + 2]);
-              acc[4 * q + 3] = fmaf(w, h4.w, acc[4 * q + 3]);
-            }
+          for (int q = 0; q < 8; ++q) {
+            const float4 h4 = *reinterpret_cast<const float4*>(hr + ((q ^ sw) << 2));
+            acc[4 * q + 0] = fmaf(w, h4.x, acc[4 * q + 0]);
+            acc[4 * q + 1] = fmaf(w, h4.y, acc[4 * q + 1]);
+            acc[4 * q + 2] = fmaf(w, h4.z, acc[4 * q + 2]);
+            acc[4 * q + 3] = fmaf(w, h4.w, acc[4 * q + 3]);
           }
         }
 #pragma unroll
-        for (int c0 = 0; c0 < 64; c0 += 16) {
+        for (int cc = 0; cc < 32; cc += 16) {
           float v[16];
 #pragma unroll
-          for (int q = 0; q < 16; ++q) v[q] = acc[c0 + q];
-          tc::store_split16(v, a_hi, a_lo, trow, c0);
+          for (int q = 0; q < 16; ++q) v[q] = acc[cc + q];
+          tc::store_split16(v, a_hi, a_lo, trow, half * 32 + cc);
         }
       }
     }
 
-    // ---- pooling over the graph's rows (column owners; two halves of the rows) -------------------
+    // ---- pooling over the graph's rows (column owners; four interleaved quarters of the rows) ------
     {
-      const int c = gt & 63, half = gt >> 6;
+      const int c = gt & 63, quarter = gt >> 6;
       float mx = -INFINITY, sm = 0.f;
-      int r = half;
-      for (; r + 6 < n; r += 8) {
-        const float v0 = Hbuf[h_off(r, c)], v1 = Hbuf[h_off(r + 2, c)];
-        const float v2 = Hbuf[h_off(r + 4, c)], v3 = Hbuf[h_off(r + 6, c)];
+      int r = quarter;
+      for (; r + 12 < n; r += 16) {
+        const float v0 = Hbuf[h_off(r, c)], v1 = Hbuf[h_off(r + 4, c)];
+        const float v2 = Hbuf[h_off(r + 8, c)], v3 = Hbuf[h_off(r + 12, c)];
         mx = fmaxf(fmaxf(mx, v0), fmaxf(v1, fmaxf(v2, v3)));
         sm += v0; sm += v1; sm += v2; sm += v3;
       }
-      for (; r < n; r += 2) {
+      for (; r < n; r += 4) {
         const float v0 = Hbuf[h_off(r, c)];
         mx = fmaxf(mx, v0);
         sm += v0;
       }
-      if (half == 1) { s_pool[c] = mx; s_pool[64 + c] = sm; }
-      ptx::named_bar_sync(bar_id, 128);
-      if (half == 0) {
-        mx = fmaxf(mx, s_pool[c]);
-        sm += s_pool[64 + c];
+      s_pool[quarter * 128 + c] = mx;
+      s_pool[quarter * 128 + 64 + c] = sm;
+      ptx::named_bar_sync(bar_id, kTcSlotThreads);
+      if (gt < 64) {
+        mx = fmaxf(fmaxf(s_pool[c], s_pool[128 + c]), fmaxf(s_pool[256 + c], s_pool[384 + c]));
+        sm = ((s_pool[64 + c] + s_pool[192 + c]) + s_pool[320 + c]) + s_pool[448 + c];
         a.f.emb[gid * 128 + c] = n > 0 ? mx : 0.f;
         a.f.emb[gid * 128 + 64 + c] = n > 0 ? sm / (float)n : 0.f;
       }
@@ -424,14 +459,7 @@ k_tc_fwd(const TcArgs a) {
   if (tid < 32) ptx::tmem_dealloc(tmem_base_s, 512);
 }
 
-size_t tc_fwd_smem_bytes(int F, int L) {
-  const size_t x_bytes = ((size_t)kTcNcap * F * 4 + 16 + 15) & ~size_t(15);
-  const size_t rp_bytes = ((size_t)(kTcNcap + 1) * 4 + 16 + 15) & ~size_t(15);
-  const size_t cl_bytes = ((size_t)kTcEcap * 4 + 16 + 15) & ~size_t(15);
-  const size_t ds_bytes = ((size_t)kTcNcap * 4 + 16 + 15) & ~size_t(15);
-  return 1024 + 2 * tc::kN * 32 * 4 + (size_t)(L - 1) * 2 * tc::kN * 64 * 4 + (size_t)L * 64 * 4 +
-         (size_t)kTcSlots * kTcNcap * 64 * 4 + kTcSlots * 128 * 4 + (size_t)kTcSlots * 2 * (x_bytes + rp_bytes + cl_bytes + ds_bytes);
-}
+size_t tc_fwd_smem_bytes(int F, int L) { return tc_layout(F, L).total; }
 
 }  // namespace hcg
 
@@ -460,10 +488,11 @@ int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStr
   if (f.B <= 0) return HCG_OK;
   TcWs w = carve_tc(ws, f.B);
   const size_t smem = tc_fwd_smem_bytes(f.F, f.L);
-  static thread_local size_t configured = 0;
-  if (smem > configured) {
-    HCG_CUDA_OK(cudaFuncSetAttribute(k_tc_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+  static thread_local size_t configured[2] = {0, 0};
+  const int v = f.F <= 28 ? 0 : 1;
+  if (smem > configured[v]) {
+    HCG_CUDA_OK(cudaFuncSetAttribute(v == 0 ? k_tc_fwd<7> : k_tc_fwd<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[v] = smem;
   }
   HCG_CUDA_OK(cudaMemsetAsync(w.overflow_count, 0, sizeof(int), st));
   k_graph_desc<<<(unsigned)cdiv(f.B, 256), 256, 0, st>>>(f.graph_ptr, f.rowptr, f.B, w.gdesc);
@@ -480,7 +509,8 @@ int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStr
   a.ds_end = f.dis + N;
   int64_t grid = cdiv(f.B, kTcSlots);
   if (grid > kNumSMs) grid = kNumSMs;
-  k_tc_fwd<<<(unsigned)grid, kTcThreads, smem, st>>>(a);
+  if (v == 0) k_tc_fwd<7><<<(unsigned)grid, kTcThreads, smem, st>>>(a);
+  else k_tc_fwd<8><<<(unsigned)grid, kTcThreads, smem, st>>>(a);
   HCG_LAUNCH_OK(st, "k_tc_fwd");
 
   // graphs above the slot capacity: the FMA graph-resident kernel walks the overflow list

@@ -86,7 +86,9 @@ __device__ __forceinline__ void store_split16(const float (&v)[16], uint32_t a_h
 #pragma unroll
   for (int q = 0; q < 16; ++q) {
     h[q] = tf32_hi(v[q]);
-    l[q] = tf32_lo(v[q], h[q]);
+    // the residual goes in unrounded: the tensor core reads only the TF32 bits of an operand (the 13 low
+    // mantissa bits are ignored), i.e. truncates it: |err| <= 2^-10 |lo| <= 2^-21 |v|, typically 2^-23
+    l[q] = __float_as_uint(v[q] - __uint_as_float(h[q]));
   }
   ptx::tmem_st16(a_hi + trow + col, h);
   ptx::tmem_st16(a_lo + trow + col, l);
