@@ -101,14 +101,20 @@ def load():
     with _lock:
         if _lib is not None:
             return _lib
-        path = _build.LIB_PATH
-        if _build.needs_build():
+        path = os.environ.get("HCG_LIB_PATH")  # an explicitly chosen build (e.g. an instrumented one)
+        if path:
+            if not os.path.exists(path):
+                raise RuntimeError(f"HCG_LIB_PATH={path} does not exist")
+        elif _build.needs_build():
+            path = _build.LIB_PATH
             if _build.find_nvcc() is not None:
                 _build.build()
             elif not os.path.exists(path):
                 raise RuntimeError(
                     "hcatgnet_b200: libhcg.so is missing and nvcc is not available; the CUDA extension is "
                     "required (there is no CPU fallback). Run `python -m hcatgnet_b200.build` on a box with nvcc.")
+        else:
+            path = _build.LIB_PATH
         lib = C.CDLL(path)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(lib, name)  # AttributeError here = library/header mismatch: fail loudly

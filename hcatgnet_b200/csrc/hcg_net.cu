@@ -557,7 +557,8 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
     a.ncap = ncap; a.ecap = 6 * ncap;
     // tensor-core kernel: F <= 32, its smem must fit, the FMA kernel must exist for the overflow list,
     // and the batch should mostly fit the 128-node slots
-    const bool tc_ok = p->F <= 32 && tc_fwd_smem_bytes(p->F, p->L) <= 227 * 1024 && fma_fits;
+    const bool tc_ok = p->F <= 32 && tc_fwd_smem_bytes(p->F, p->L) <= 227 * 1024 && fma_fits &&
+                       p->slope >= 0.f && p->slope <= 1.f;  // its LeakyReLU is max(v, slope * v)
     if (path == 3 && !tc_ok)
       return set_err(HCG_ERR_UNSUPPORTED, "tensor-core forward needs F <= 32 and %d conv layers to fit in shared memory", p->L);
     const bool want_tc = path == 3 || (path == 0 && tc_ok && (g->max_graph_nodes == 0 || g->max_graph_nodes <= 128));

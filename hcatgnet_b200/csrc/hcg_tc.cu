@@ -42,7 +42,8 @@ k_tc_selftest(const float* __restrict__ A, const float* __restrict__ W, int K, f
   __syncthreads();
   if (tid == 0) {
     ptx::tc_fence_after_sync();
-    tc::issue_split_mma(d_t, a_hi, a_lo, ptx::smem_u32(s_hi), ptx::smem_u32(s_lo), Kpad / 8);
+    if (Kpad == 32) tc::issue_split_mma<4>(d_t, a_hi, a_lo, ptx::smem_u32(s_hi), ptx::smem_u32(s_lo));
+    else tc::issue_split_mma<8>(d_t, a_hi, a_lo, ptx::smem_u32(s_hi), ptx::smem_u32(s_lo));
     ptx::mma_commit(&bar_mma);
   }
   ptx::mbar_wait(&bar_mma, 0);
@@ -103,7 +104,7 @@ constexpr int kTcSlotThreads = 256;  // two threads per node row: each owns half
 constexpr int kTcThreads = kTcSlots * kTcSlotThreads;
 constexpr int kTcNcap = 128;
 constexpr int kTcEcap = 640;
-constexpr int kTcMaxF = 32;
+constexpr int kTcHPitch = 68;        // floats per activation row: 8 consecutive rows cover all banks for 128-bit access
 constexpr int kStatusCrossEdgeTc = 4;
 
 struct TcSlotMeta {
@@ -119,76 +120,75 @@ struct TcStage {
   float* ds;      // [ncap + 4]
 };
 
-__device__ __forceinline__ int h_off(int r, int c) {  // float offset of (row, col) in a swizzled [128][64] buffer
-  const int q = c >> 2;
-  return r * 64 + ((((q ^ r) & 7) | (q & 8)) << 2) + (c & 3);
-}
-
-// one contiguous slice global -> shared through the bulk-copy engine; returns the bytes in flight.
-// `count` elements of 4 bytes starting at `src`; data lands at dst + lead (elements).  A tail the
-// 16-byte granularity would read past `src_end` is fetched with ordinary loads instead.
-__device__ __forceinline__ uint32_t bulk_slice(void* dst, const void* src, int count, const void* src_end, int* lead,
-                                               uint64_t* bar) {
-  const uintptr_t a = reinterpret_cast<uintptr_t>(src);
-  const uintptr_t a_al = a & ~uintptr_t(15);
-  *lead = (int)((a - a_al) >> 2);
-  if (count <= 0) return 0;
-  uint32_t bytes = (uint32_t)(((a - a_al) + (uintptr_t)count * 4 + 15) & ~uintptr_t(15));
-  const uintptr_t avail = (reinterpret_cast<uintptr_t>(src_end) - a_al) & ~uintptr_t(15);
-  if (bytes > avail) {  // last elements of the array: copy them by hand
-    const int done = (int)((avail - (a - a_al)) >> 2);
-    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
-    uint32_t* d32 = reinterpret_cast<uint32_t*>(dst) + *lead;
-    for (int i = done < 0 ? 0 : done; i < count; ++i) d32[i] = __ldg(s32 + i);
-    bytes = (uint32_t)avail;
-  }
-  if (bytes) ptx::bulk_g2s(dst, reinterpret_cast<const void*>(a_al), bytes, bar);
-  return bytes;
-}
-
 struct TcArgs {
   FusedFwdArgs f;
-  const int4* gdesc;     // [B] {n0, n, e0, e}
-  int* overflow_count;
-  int* overflow_list;    // [B]
-  const void* x_end;
-  const void* rp_end;
-  const void* cl_end;
-  const void* ds_end;
+  const int4* gdesc;     // [B] {n0, n, e0, e}; e < 0: not for this kernel (on the overflow list)
 };
 
-__global__ void __launch_bounds__(256)
-k_graph_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ rowptr, int64_t B, int4* __restrict__ gdesc) {
-  int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= B) return;
-  int n0 = graph_ptr[g], n1 = graph_ptr[g + 1];
-  int e0 = rowptr[n0], e1 = rowptr[n1];
-  gdesc[g] = make_int4(n0, n1 - n0, e0, e1 - e0);
+// The 16-byte granular window [lo, lo + bytes) the bulk copy of `count` 4-byte elements at `p` reads.
+__host__ __device__ __forceinline__ void copy_window(uintptr_t p, int count, uintptr_t* lo, uint32_t* bytes, int* lead) {
+  *lo = p & ~uintptr_t(15);
+  *lead = (int)((p - *lo) >> 2);
+  *bytes = (uint32_t)(((p - *lo) + (uintptr_t)count * 4 + 15) & ~uintptr_t(15));
 }
 
-// thread 0 of a slot: start the copies of one graph into a stage (or mark it skipped / overflowed)
-__device__ __forceinline__ void tc_prefetch(const TcArgs& a, int64_t gid, int4 d, const TcStage& st, TcSlotMeta* meta,
-                                            uint64_t* bar) {
-  meta->n0 = d.x; meta->n = d.y; meta->e0 = d.z; meta->e = d.w;
-  if (d.y > kTcNcap || d.w > kTcEcap) {
-    meta->skip = 1;
-    const int pos = atomicAdd(a.overflow_count, 1);
-    a.overflow_list[pos] = (int)gid;
+// Per-graph descriptor + routing: graphs above the slot capacity and graphs without nodes or edges go to
+// the overflow list (the FMA graph-resident kernel); everything else runs on the tensor-core kernel.
+// A graph whose 16-byte granular copy windows would reach past the end of an input array (the last
+// graph of a batch) is flagged (n stored negated): its slot fetches it with ordinary loads.
+__global__ void __launch_bounds__(256)
+k_graph_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+             const float* __restrict__ dis, const float* __restrict__ x, int F, int64_t N, int64_t E, int64_t B,
+             int4* __restrict__ gdesc, int* __restrict__ overflow_count, int* __restrict__ overflow_list) {
+  int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= B) return;
+  const int n0 = graph_ptr[g], n = graph_ptr[g + 1] - n0;
+  const int e0 = rowptr[n0], e = rowptr[n0 + n] - e0;
+  const bool skip = n <= 0 || e <= 0 || n > kTcNcap || e > kTcEcap;
+  bool manual = false;  // a 16-byte granular copy window would reach past the end of an input array
+  if (!skip) {
+    uintptr_t lo; uint32_t bytes; int lead;
+    copy_window(reinterpret_cast<uintptr_t>(x + (int64_t)n0 * F), n * F, &lo, &bytes, &lead);
+    manual |= lo + bytes > reinterpret_cast<uintptr_t>(x + N * F);
+    copy_window(reinterpret_cast<uintptr_t>(rowptr + n0), n + 1, &lo, &bytes, &lead);
+    manual |= lo + bytes > reinterpret_cast<uintptr_t>(rowptr + N + 1);
+    copy_window(reinterpret_cast<uintptr_t>(col + e0), e, &lo, &bytes, &lead);
+    manual |= lo + bytes > reinterpret_cast<uintptr_t>(col + E);
+    copy_window(reinterpret_cast<uintptr_t>(dis + n0), n, &lo, &bytes, &lead);
+    manual |= lo + bytes > reinterpret_cast<uintptr_t>(dis + N);
+  }
+  if (skip) overflow_list[atomicAdd(overflow_count, 1)] = (int)g;
+  gdesc[g] = make_int4(n0, manual ? -n : n, e0, skip ? -1 : e);
+}
+
+// thread 0 of a slot: start the four copies of one graph into a stage (branch-free for routed graphs)
+__device__ __forceinline__ void tc_prefetch(const TcArgs& a, int4 d, const TcStage& st, TcSlotMeta* meta, uint64_t* bar) {
+  meta->n0 = d.x; meta->n = d.y < 0 ? -d.y : d.y; meta->e0 = d.z; meta->e = d.w;
+  meta->skip = d.w < 0 ? 1 : (d.y < 0 ? 2 : 0);
+  meta->lead_x = meta->lead_rp = meta->lead_cl = meta->lead_ds = 0;
+  if (d.w < 0 || d.y < 0) {
     ptx::mbar_arrive(bar);
     return;
   }
-  meta->skip = 0;
-  uint32_t bytes = 0;
-  bytes += bulk_slice(st.x, a.f.x + (int64_t)d.x * a.f.F, d.y * a.f.F, a.x_end, &meta->lead_x, bar);
-  bytes += bulk_slice(st.rp, a.f.rowptr + d.x, d.y + 1, a.rp_end, &meta->lead_rp, bar);
-  bytes += bulk_slice(st.cl, a.f.col + d.z, d.w, a.cl_end, &meta->lead_cl, bar);
-  bytes += bulk_slice(st.ds, a.f.dis + d.x, d.y, a.ds_end, &meta->lead_ds, bar);
-  ptx::mbar_expect_tx(bar, bytes);  // the slot's single arrival for this phase + the bytes in flight
+  uintptr_t lo0, lo1, lo2, lo3;
+  uint32_t b0, b1, b2, b3;
+  int l0, l1, l2, l3;
+  copy_window(reinterpret_cast<uintptr_t>(a.f.x + (int64_t)d.x * a.f.F), d.y * a.f.F, &lo0, &b0, &l0);
+  copy_window(reinterpret_cast<uintptr_t>(a.f.rowptr + d.x), d.y + 1, &lo1, &b1, &l1);
+  copy_window(reinterpret_cast<uintptr_t>(a.f.col + d.z), d.w, &lo2, &b2, &l2);
+  copy_window(reinterpret_cast<uintptr_t>(a.f.dis + d.x), d.y, &lo3, &b3, &l3);
+  // the metadata must be in place before the arrival that can complete the phase (release/acquire)
+  meta->lead_x = l0; meta->lead_rp = l1; meta->lead_cl = l2; meta->lead_ds = l3;
+  ptx::mbar_expect_tx(bar, b0 + b1 + b2 + b3);  // the slot's single arrival for this phase + the bytes in flight
+  ptx::bulk_g2s(st.x, reinterpret_cast<const void*>(lo0), b0, bar);
+  ptx::bulk_g2s(st.rp, reinterpret_cast<const void*>(lo1), b1, bar);
+  ptx::bulk_g2s(st.cl, reinterpret_cast<const void*>(lo2), b2, bar);
+  ptx::bulk_g2s(st.ds, reinterpret_cast<const void*>(lo3), b3, bar);
 }
 
 // shared-memory carve-up, identical on host (size query) and device
 struct TcSmemLayout {
-  uint32_t w0_hi, w0_lo, wl, bias, hbuf, pool, stage;  // byte offsets from the 1024-aligned base
+  uint32_t w0_hi, w0_lo, wl, bias, hbuf, wbuf, pool, stage;  // byte offsets from the 1024-aligned base
   uint32_t x_bytes, rp_bytes, cl_bytes, ds_bytes, stage_bytes, total;
 };
 __host__ __device__ inline TcSmemLayout tc_layout(int F, int L) {
@@ -198,7 +198,8 @@ __host__ __device__ inline TcSmemLayout tc_layout(int F, int L) {
   y.w0_lo = p; p += tc::kN * 32 * 4;
   y.wl = p; p += (uint32_t)(L - 1) * 2 * tc::kN * 64 * 4;  // per layer: hi tile, lo tile
   y.bias = p; p += (uint32_t)L * 64 * 4;
-  y.hbuf = p; p += (uint32_t)kTcSlots * kTcNcap * 64 * 4;
+  y.hbuf = p; p += (uint32_t)kTcSlots * kTcNcap * kTcHPitch * 4;
+  y.wbuf = p; p += (uint32_t)kTcSlots * kTcEcap * 4;
   y.pool = p; p += (uint32_t)kTcSlots * 4 * 128 * 4;
   y.x_bytes = ((uint32_t)kTcNcap * F * 4 + 16 + 15) & ~15u;
   y.rp_bytes = ((uint32_t)(kTcNcap + 1) * 4 + 16 + 15) & ~15u;
@@ -210,27 +211,22 @@ __host__ __device__ inline TcSmemLayout tc_layout(int F, int L) {
   return y;
 }
 
-// Layer-0 gather of one thread: NCH 16-byte chunks of the rows of `xp` (pitch P floats), starting at
-// chunk `q0`: acc += w * x_j for every neighbour, then the self-loop.
-template <int NCH, int P>
-__device__ __forceinline__ void gather_x(float (&acc)[16], const float* xp, const int32_t* cl, const float* ds,
-                                         int beg, int end, int i, int n, int n0, float di, float wself, int q0,
-                                         int* status) {
+// One thread's share of a gather: NCH 16-byte chunks, starting at chunk q0, of the rows of `src` (pitch
+// P floats):  acc = sum_k w_k * src[j_k] over the row's CSR slots, then the self-loop (last, as in the
+// reference).  `jl` holds graph-local neighbour ids, `wn` the matching norm_ij (both per CSR slot).
+template <int NCH, int P, int NACC>
+__device__ __forceinline__ void gather_rows(float (&acc)[NACC], const float* src, const int32_t* jl,
+                                            const float* wn, int beg, int end, int i, float wself, int q0) {
 #pragma unroll
-  for (int c = 0; c < 16; ++c) acc[c] = 0.f;
-  for (int kk = beg; kk <= end; ++kk) {  // kk == end: the self-loop, last as in the reference
+  for (int c = 0; c < NACC; ++c) acc[c] = 0.f;
+  for (int kk = beg; kk <= end; ++kk) {
     int j = i;
     float w = wself;
-    if (kk < end) {
-      j = cl[kk] - n0;
-      const bool ok = (unsigned)j < (unsigned)n;
-      if (!ok) { if (status) atomicOr(status, kStatusCrossEdgeTc); j = i; }
-      w = ok ? ds[j] * di : 0.f;
-    }
-    const float4* xr = reinterpret_cast<const float4*>(xp + j * P) + q0;
+    if (kk < end) { j = jl[kk]; w = wn[kk]; }
+    const float4* row = reinterpret_cast<const float4*>(src + j * P) + q0;
 #pragma unroll
     for (int q = 0; q < NCH; ++q) {
-      const float4 v = xr[q];
+      const float4 v = row[q];
       acc[4 * q + 0] = fmaf(w, v.x, acc[4 * q + 0]);
       acc[4 * q + 1] = fmaf(w, v.y, acc[4 * q + 1]);
       acc[4 * q + 2] = fmaf(w, v.z, acc[4 * q + 2]);
@@ -239,12 +235,23 @@ __device__ __forceinline__ void gather_x(float (&acc)[16], const float* xp, cons
   }
 }
 
+#ifdef HCG_TC_TIMING
+__device__ unsigned long long g_tc_timing[16];
+#define TC_TICK(slot_) do { if (tid == 0) { long long t_ = clock64(); g_tc_timing[slot_] += (unsigned long long)(t_ - t_prev); t_prev = t_; } } while (0)
+#else
+#define TC_TICK(slot_) do { } while (0)
+#endif
+
 // NQ = 16-byte chunks per re-pitched x row (7: F <= 28, 8: F <= 32); the pitch P keeps P/4 odd so that
 // eight consecutive rows cover all 32 banks for 128-bit reads.
 template <int NQ>
 __global__ void __launch_bounds__(kTcThreads, 1)
 k_tc_fwd(const TcArgs a) {
+#ifdef HCG_TC_TIMING
+  long long t_prev = clock64();
+#endif
   constexpr int P = (NQ & 1) ? 4 * NQ : 4 * NQ + 4;
+  constexpr int HP = kTcHPitch;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ uint64_t bar_stage[kTcSlots][2];
   __shared__ uint64_t bar_mma[kTcSlots];
@@ -255,6 +262,7 @@ k_tc_fwd(const TcArgs a) {
   const int slot = tid / kTcSlotThreads, gt = tid % kTcSlotThreads;
   const int half = gt >> 7;          // which half of the columns this thread works on
   const int i = gt & 127;            // node (row) of the graph = TMEM lane
+  const int lane = tid & 31;
   const int F = a.f.F, L = a.f.L;
 
   // ---- carve shared memory (pointer arithmetic on the shared array only: keeps the address space) --
@@ -264,7 +272,8 @@ k_tc_fwd(const TcArgs a) {
   float* w0_lo = reinterpret_cast<float*>(base + lay.w0_lo);
   float* wl_base = reinterpret_cast<float*>(base + lay.wl);
   float* s_bias = reinterpret_cast<float*>(base + lay.bias);
-  float* Hbuf = reinterpret_cast<float*>(base + lay.hbuf) + (size_t)slot * kTcNcap * 64;
+  float* Hbuf = reinterpret_cast<float*>(base + lay.hbuf) + (size_t)slot * kTcNcap * HP;
+  float* wn = reinterpret_cast<float*>(base + lay.wbuf) + (size_t)slot * kTcEcap;
   float* s_pool = reinterpret_cast<float*>(base + lay.pool) + slot * 4 * 128;
   unsigned char* stage0 = base + lay.stage + (size_t)slot * 2 * lay.stage_bytes;
   auto stage_of = [&](int s) {
@@ -297,17 +306,17 @@ k_tc_fwd(const TcArgs a) {
   __syncthreads();
   ptx::tc_fence_after_sync();
 
-  const uint32_t tbase = tmem_base_s + (uint32_t)slot * 256;  // big acc | small acc | A hi | A lo, 64 columns each
+  const uint32_t tbase = tmem_base_s + (uint32_t)slot * 256;  // accumulator | (free) | A hi | A lo, 64 columns each
   const uint32_t d_t = tbase, a_hi = tbase + 128, a_lo = tbase + 192;
   const uint32_t trow = (uint32_t)(((gt >> 5) & 3) * 32) << 16;  // warps w and w+4 share a lane quadrant
   const int bar_id = 1 + slot;
-  const int ksteps0 = (F + 7) >> 3;
+  const float slope = a.f.slope;
 
   const int64_t first = (int64_t)blockIdx.x * kTcSlots + slot;
   const int64_t stride = (int64_t)gridDim.x * kTcSlots;
-  int4 d_next = make_int4(0, 0, 0, 0);
+  int4 d_next = make_int4(0, 0, 0, -1);
   if (gt == 0 && first < a.f.B) {
-    tc_prefetch(a, first, a.gdesc[first], stage_of(0), &metas[slot][0], &bar_stage[slot][0]);
+    tc_prefetch(a, a.gdesc[first], stage_of(0), &metas[slot][0], &bar_stage[slot][0]);
     if (first + stride < a.f.B) d_next = a.gdesc[first + stride];
   }
   uint32_t mma_phase = 0;
@@ -315,107 +324,124 @@ k_tc_fwd(const TcArgs a) {
   for (int64_t gid = first; gid < a.f.B; gid += stride, ++k) {
     const int s = k & 1;
     if (gt == 0 && gid + stride < a.f.B) {  // next graph -> the other stage (its readers finished last iteration)
-      tc_prefetch(a, gid + stride, d_next, stage_of(s ^ 1), &metas[slot][s ^ 1], &bar_stage[slot][s ^ 1]);
+      tc_prefetch(a, d_next, stage_of(s ^ 1), &metas[slot][s ^ 1], &bar_stage[slot][s ^ 1]);
       if (gid + 2 * stride < a.f.B) d_next = a.gdesc[gid + 2 * stride];
     }
+    TC_TICK(0);
     ptx::mbar_wait(&bar_stage[slot][s], (uint32_t)(k >> 1) & 1u);
+    TC_TICK(1);
     const TcSlotMeta m = metas[slot][s];
-    if (m.skip) continue;  // slot-uniform
+    if (m.skip == 1) continue;  // slot-uniform: this graph is on the overflow list
     const int n = m.n, n0 = m.n0, e0 = m.e0;
     const TcStage st = stage_of(s);
+    if (m.skip == 2) {  // flagged graph: fetch the four slices with ordinary loads
+      for (int idx = gt; idx < n * F; idx += kTcSlotThreads) st.x[idx] = __ldg(a.f.x + (int64_t)n0 * F + idx);
+      for (int idx = gt; idx <= n; idx += kTcSlotThreads) st.rp[idx] = __ldg(a.f.rowptr + n0 + idx);
+      for (int idx = gt; idx < m.e; idx += kTcSlotThreads) st.cl[idx] = __ldg(a.f.col + e0 + idx);
+      for (int idx = gt; idx < n; idx += kTcSlotThreads) st.ds[idx] = __ldg(a.f.dis + n0 + idx);
+      ptx::named_bar_sync(bar_id, kTcSlotThreads);
+    }
     const float* xs = st.x + m.lead_x;
     const int32_t* rp = st.rp + m.lead_rp;
-    const int32_t* cl = st.cl + m.lead_cl;
+    int32_t* cl = st.cl + m.lead_cl;
     const float* ds = st.ds + m.lead_ds;
     const bool row_ok = i < n;
     const bool warp_ok = (i & ~31) < n;  // this warp owns at least one node of the graph
 
-    // ---- re-pitch the x rows to P floats (zero padded) inside the idle activation buffer ----------
-    for (int idx = gt; idx < n * P; idx += kTcSlotThreads) {
-      const int r = idx / P, c = idx - r * P;
-      Hbuf[idx] = c < F ? xs[r * F + c] : 0.f;
+    // ---- re-pitch the x rows to P floats (zero padded) inside the idle activation buffer: a warp per
+    //      row, a lane per column ------------------------------------------------------------------------
+    for (int r0 = gt >> 5; r0 < n; r0 += 4 * (kTcSlotThreads / 32)) {  // four rows in flight per warp
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int r = r0 + u * (kTcSlotThreads / 32);
+        v[u] = (r < n && lane < F) ? xs[r * F + lane] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int r = r0 + u * (kTcSlotThreads / 32);
+        if (r < n && lane < (P < 32 ? P : 32)) Hbuf[r * P + lane] = v[u];
+      }
     }
+    // ---- per CSR slot: graph-local neighbour id (in place) and norm_ij; the two threads of a row take
+    //      alternate slots --------------------------------------------------------------------------------
     int beg = 0, end = -1;
     float di = 0.f;
-    if (row_ok) { beg = rp[i] - e0; end = rp[i + 1] - e0; di = ds[i]; }
+    if (row_ok) {
+      beg = rp[i] - e0; end = rp[i + 1] - e0; di = ds[i];
+      for (int kk = beg + half; kk < end; kk += 2) {
+        int j = cl[kk] - n0;
+        const bool ok = (unsigned)j < (unsigned)n;
+        if (!ok) { if (a.f.status) atomicOr(a.f.status, kStatusCrossEdgeTc); j = i; }
+        cl[kk] = j;
+        wn[kk] = ok ? ds[j] * di : 0.f;
+      }
+    }
     const float wself = (di * a.f.fill) * di;
+    TC_TICK(2);
     ptx::named_bar_sync(bar_id, kTcSlotThreads);
+    TC_TICK(3);
 
     // ---- layer 0: a_r = sum_j norm_rj x_j ; this thread's 16 of the (up to) 32 columns ---------------
-    if (warp_ok && half * 16 < ksteps0 * 8) {
+    if (warp_ok) {
       float acc[16];
-      if (half == 0) gather_x<(NQ < 4 ? NQ : 4), P>(acc, Hbuf, cl, ds, beg, end, i, n, n0, di, wself, 0, a.f.status);
-      else           gather_x<(NQ > 4 ? NQ - 4 : 0), P>(acc, Hbuf, cl, ds, beg, end, i, n, n0, di, wself, 4, nullptr);
+      if (half == 0) gather_rows<(NQ < 4 ? NQ : 4), P, 16>(acc, Hbuf, cl, wn, beg, end, i, wself, 0);
+      else           gather_rows<(NQ > 4 ? NQ - 4 : 0), P, 16>(acc, Hbuf, cl, wn, beg, end, i, wself, 4);
       tc::store_split16(acc, a_hi, a_lo, trow, half * 16);
     }
 
     for (int l = 0; l < L; ++l) {
       const bool last = l == L - 1;
+      TC_TICK(4);
       ptx::tmem_wait_st();
+      TC_TICK(5);
       ptx::tc_fence_before_sync();
       ptx::named_bar_sync(bar_id, kTcSlotThreads);  // A operand complete; previous readers of Hbuf / D are done
       if (gt == 0) {
         ptx::tc_fence_after_sync();
         if (l == 0)
-          tc::issue_split_mma(d_t, a_hi, a_lo, ptx::smem_u32(w0_hi), ptx::smem_u32(w0_lo), ksteps0);
+          tc::issue_split_mma<4>(d_t, a_hi, a_lo, ptx::smem_u32(w0_hi), ptx::smem_u32(w0_lo));  // K = 32, zero padded
         else
-          tc::issue_split_mma(d_t, a_hi, a_lo, ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64),
-                              ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64), 8);
+          tc::issue_split_mma<8>(d_t, a_hi, a_lo, ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64),
+                                 ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64));
         ptx::mma_commit(&bar_mma[slot]);
       }
+      TC_TICK(6);
       ptx::mbar_wait(&bar_mma[slot], mma_phase);
       mma_phase ^= 1u;
       ptx::tc_fence_after_sync();
+      TC_TICK(7);
 
-      // ---- epilogue: h_r = lrelu(D_r + b_l) -> swizzled activation buffer (+ optional save) ------
+      // ---- epilogue: h_r = lrelu(D_r + b_l) -> activation buffer (+ optional save) ------------------
       if (warp_ok) {
         float* save = a.f.save_act[l];
+        uint32_t r0[16], r1[16];
+        ptx::tmem_ld16(d_t + trow + half * 32, r0);
+        ptx::tmem_ld16(d_t + trow + half * 32 + 16, r1);
+        ptx::tmem_wait_ld();
 #pragma unroll
-        for (int cc = 0; cc < 32; cc += 16) {
-          const int c0 = half * 32 + cc;
-          float r[16];
-          tc::load_acc16(d_t, trow, c0, r);
-#pragma unroll
-          for (int q4 = 0; q4 < 4; ++q4) {
-            const float4 b4 = *reinterpret_cast<const float4*>(s_bias + l * 64 + c0 + 4 * q4);
-            float4 v;
-            v.x = lrelu(r[4 * q4 + 0] + b4.x, a.f.slope);
-            v.y = lrelu(r[4 * q4 + 1] + b4.y, a.f.slope);
-            v.z = lrelu(r[4 * q4 + 2] + b4.z, a.f.slope);
-            v.w = lrelu(r[4 * q4 + 3] + b4.w, a.f.slope);
-            *reinterpret_cast<float4*>(Hbuf + h_off(i, c0 + 4 * q4)) = v;
-            if (save && row_ok) *reinterpret_cast<float4*>(save + ((int64_t)n0 + i) * 64 + c0 + 4 * q4) = v;
-          }
+        for (int q4 = 0; q4 < 8; ++q4) {
+          const int c0 = half * 32 + 4 * q4;
+          const float4 b4 = *reinterpret_cast<const float4*>(s_bias + l * 64 + c0);
+          const uint32_t* rr = q4 < 4 ? &r0[4 * q4] : &r1[4 * (q4 - 4)];
+          float4 v;
+          v.x = __uint_as_float(rr[0]) + b4.x; v.x = fmaxf(v.x, v.x * slope);  // LeakyReLU, 0 <= slope <= 1
+          v.y = __uint_as_float(rr[1]) + b4.y; v.y = fmaxf(v.y, v.y * slope);
+          v.z = __uint_as_float(rr[2]) + b4.z; v.z = fmaxf(v.z, v.z * slope);
+          v.w = __uint_as_float(rr[3]) + b4.w; v.w = fmaxf(v.w, v.w * slope);
+          *reinterpret_cast<float4*>(Hbuf + i * HP + c0) = v;
+          if (save && row_ok) *reinterpret_cast<float4*>(save + ((int64_t)n0 + i) * 64 + c0) = v;
         }
       }
+      TC_TICK(8);
       ptx::tc_fence_before_sync();
       ptx::named_bar_sync(bar_id, kTcSlotThreads);  // h complete in shared memory; D may be overwritten
+      TC_TICK(9);
 
       if (!last && warp_ok) {
         // ---- next layer's A operand: a_r = sum_j norm_rj h_j ; this thread's 32 of the 64 columns ----
         float acc[32];
-#pragma unroll
-        for (int c = 0; c < 32; ++c) acc[c] = 0.f;
-        for (int kk = beg; kk <= end; ++kk) {  // kk == end: the self-loop, last as in the reference
-          int j = i;
-          float w = wself;
-          if (kk < end) {
-            j = cl[kk] - n0;
-            const bool ok = (unsigned)j < (unsigned)n;
-            if (!ok) j = i;
-            w = ok ? ds[j] * di : 0.f;
-          }
-          const float* hr = Hbuf + j * 64 + half * 32;
-          const int sw = j & 7;
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float4 h4 = *reinterpret_cast<const float4*>(hr + ((q ^ sw) << 2));
-            acc[4 * q + 0] = fmaf(w, h4.x, acc[4 * q + 0]);
-            acc[4 * q + 1] = fmaf(w, h4.y, acc[4 * q + 1]);
-            acc[4 * q + 2] = fmaf(w, h4.z, acc[4 * q + 2]);
-            acc[4 * q + 3] = fmaf(w, h4.w, acc[4 * q + 3]);
-          }
-        }
+        gather_rows<8, HP, 32>(acc, Hbuf, cl, wn, beg, end, i, wself, half * 8);
 #pragma unroll
         for (int cc = 0; cc < 32; cc += 16) {
           float v[16];
@@ -430,27 +456,29 @@ k_tc_fwd(const TcArgs a) {
     {
       const int c = gt & 63, quarter = gt >> 6;
       float mx = -INFINITY, sm = 0.f;
+      const float* hp = Hbuf + c;
       int r = quarter;
       for (; r + 12 < n; r += 16) {
-        const float v0 = Hbuf[h_off(r, c)], v1 = Hbuf[h_off(r + 4, c)];
-        const float v2 = Hbuf[h_off(r + 8, c)], v3 = Hbuf[h_off(r + 12, c)];
+        const float v0 = hp[r * HP], v1 = hp[(r + 4) * HP], v2 = hp[(r + 8) * HP], v3 = hp[(r + 12) * HP];
         mx = fmaxf(fmaxf(mx, v0), fmaxf(v1, fmaxf(v2, v3)));
         sm += v0; sm += v1; sm += v2; sm += v3;
       }
       for (; r < n; r += 4) {
-        const float v0 = Hbuf[h_off(r, c)];
+        const float v0 = hp[r * HP];
         mx = fmaxf(mx, v0);
         sm += v0;
       }
+      TC_TICK(10);
       s_pool[quarter * 128 + c] = mx;
       s_pool[quarter * 128 + 64 + c] = sm;
       ptx::named_bar_sync(bar_id, kTcSlotThreads);
       if (gt < 64) {
         mx = fmaxf(fmaxf(s_pool[c], s_pool[128 + c]), fmaxf(s_pool[256 + c], s_pool[384 + c]));
         sm = ((s_pool[64 + c] + s_pool[192 + c]) + s_pool[320 + c]) + s_pool[448 + c];
-        a.f.emb[gid * 128 + c] = n > 0 ? mx : 0.f;
-        a.f.emb[gid * 128 + 64 + c] = n > 0 ? sm / (float)n : 0.f;
+        a.f.emb[gid * 128 + c] = mx;
+        a.f.emb[gid * 128 + 64 + c] = sm / (float)n;
       }
+      TC_TICK(11);
     }
   }
 
@@ -495,18 +523,13 @@ int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStr
     configured[v] = smem;
   }
   HCG_CUDA_OK(cudaMemsetAsync(w.overflow_count, 0, sizeof(int), st));
-  k_graph_desc<<<(unsigned)cdiv(f.B, 256), 256, 0, st>>>(f.graph_ptr, f.rowptr, f.B, w.gdesc);
+  k_graph_desc<<<(unsigned)cdiv(f.B, 256), 256, 0, st>>>(f.graph_ptr, f.rowptr, f.col, f.dis, f.x, f.F, N, E, f.B, w.gdesc,
+                                                         w.overflow_count, w.overflow_list);
   HCG_LAUNCH_OK(st, "k_graph_desc");
 
   TcArgs a{};
   a.f = f;
   a.gdesc = w.gdesc;
-  a.overflow_count = w.overflow_count;
-  a.overflow_list = w.overflow_list;
-  a.x_end = f.x + N * f.F;
-  a.rp_end = f.rowptr + N + 1;
-  a.cl_end = f.col + E;
-  a.ds_end = f.dis + N;
   int64_t grid = cdiv(f.B, kTcSlots);
   if (grid > kNumSMs) grid = kNumSMs;
   if (v == 0) k_tc_fwd<7><<<(unsigned)grid, kTcThreads, smem, st>>>(a);
@@ -522,3 +545,11 @@ int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStr
 }
 
 }  // namespace hcg
+
+#ifdef HCG_TC_TIMING
+extern "C" int hcg_debug_tc_timing(unsigned long long* out16, int reset) {
+  if (out16) cudaMemcpyFromSymbol(out16, hcg::g_tc_timing, sizeof(unsigned long long) * 16);
+  if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(hcg::g_tc_timing, z, sizeof(z)); }
+  return 0;
+}
+#endif

@@ -47,36 +47,40 @@ __device__ __forceinline__ void prep_weight_tiles(const float* __restrict__ W, i
   }
 }
 
-// One layer's product: ksteps = K/8 MMAs of K = 8 for each of the three split terms.  Issued by a
-// single thread; the caller commits.  a_*: TMEM addresses (lane 0 of the group, first column).
-// The tensor core truncates (rounds toward zero) when it adds into its accumulator, a bias that grows
-// with the number of accumulation steps at the accumulator's magnitude.  The large hi.hi chain and
-// the small cross terms therefore go to two separate accumulators (d_big: `ksteps` steps instead of
-// 3 x ksteps; d_small: its truncation is relative to values 2^-11 smaller); the epilogue adds the
-// two in fp32 round-to-nearest.  d_small = d_big + 64 columns.
-__device__ __forceinline__ void issue_split_mma(uint32_t d_big, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi_smem,
-                                                uint32_t b_lo_smem, int ksteps) {
+// One layer's product: ksteps = K/8 MMAs of K = 8 for each of the three split terms, all into ONE fp32
+// accumulator.  Issued by a single thread; the caller commits.  a_*: TMEM addresses (lane 0 of the
+// group, first column).  The tensor core truncates (rounds toward zero) when it adds into its
+// accumulator, a bias that grows with the number of accumulation steps at the accumulator's magnitude.
+// The small cross terms (hi.lo + lo.hi, 2^-11 of the result) are therefore accumulated FIRST, while the
+// accumulator is still small, and the hi.hi chain goes on top: the truncation bias is that of `ksteps`
+// steps at full magnitude, not of 3 x ksteps.
+template <int KSTEPS>
+__device__ __forceinline__ void issue_split_mma(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi_smem,
+                                                uint32_t b_lo_smem) {
   constexpr uint32_t idesc = ptx::make_idesc_tf32(kRows, kN);
-  const uint32_t d_small = d_big + kN;
-  for (int s = 0; s < ksteps; ++s) {
-    const uint32_t boff = (uint32_t)(s >> 2) * (kChunkFloats * 4) + (uint32_t)(s & 3) * 32;
-    const uint64_t bh = ptx::make_kmajor_sw128_desc(b_hi_smem + boff);
-    const uint64_t bl = ptx::make_kmajor_sw128_desc(b_lo_smem + boff);
-    const uint32_t acol = (uint32_t)s * 8;
-    ptx::mma_tf32_ts(d_small, a_lo + acol, bh, idesc, s > 0 ? 1u : 0u);
-    ptx::mma_tf32_ts(d_small, a_hi + acol, bl, idesc, 1u);
-    ptx::mma_tf32_ts(d_big, a_hi + acol, bh, idesc, s > 0 ? 1u : 0u);
+  // descriptors of K-step s = descriptor of step 0 + a compile-time offset in its 14-bit address field
+  // (16-byte units; shared-memory addresses are below 2^18, so the field never carries)
+  const uint64_t bh = ptx::make_kmajor_sw128_desc(b_hi_smem), bl = ptx::make_kmajor_sw128_desc(b_lo_smem);
+#pragma unroll
+  for (int s = 0; s < KSTEPS; ++s) {
+    const uint64_t boff = (uint64_t)(((s >> 2) * (kChunkFloats * 4) + (s & 3) * 32) >> 4);
+    ptx::mma_tf32_ts(d, a_lo + s * 8, bh + boff, idesc, s > 0 ? 1u : 0u);
+    ptx::mma_tf32_ts(d, a_hi + s * 8, bl + boff, idesc, 1u);
+  }
+#pragma unroll
+  for (int s = 0; s < KSTEPS; ++s) {
+    const uint64_t boff = (uint64_t)(((s >> 2) * (kChunkFloats * 4) + (s & 3) * 32) >> 4);
+    ptx::mma_tf32_ts(d, a_hi + s * 8, bh + boff, idesc, 1u);
   }
 }
 
-// Row r's 16 accumulator columns [c0, c0+16): big + small, as floats.
-__device__ __forceinline__ void load_acc16(uint32_t d_big, uint32_t trow, int c0, float (&out)[16]) {
-  uint32_t rb[16], rs[16];
-  ptx::tmem_ld16(d_big + trow + c0, rb);
-  ptx::tmem_ld16(d_big + kN + trow + c0, rs);
+// Row r's 16 accumulator columns [c0, c0+16), as floats.
+__device__ __forceinline__ void load_acc16(uint32_t d, uint32_t trow, int c0, float (&out)[16]) {
+  uint32_t rb[16];
+  ptx::tmem_ld16(d + trow + c0, rb);
   ptx::tmem_wait_ld();
 #pragma unroll
-  for (int q = 0; q < 16; ++q) out[q] = __uint_as_float(rb[q]) + __uint_as_float(rs[q]);
+  for (int q = 0; q < 16; ++q) out[q] = __uint_as_float(rb[q]);
 }
 
 // Splits 16 consecutive values of this thread's row and stores them to tensor memory columns

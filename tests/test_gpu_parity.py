@@ -340,7 +340,7 @@ def test_graph_resident_forward_shapes(hcg, forward_path, path, L, F):
     """H = 64 networks of 1..4 conv layers, odd feature widths, tiny (1-node) and edge-less graphs,
     pre-existing self-loops and duplicate edges; saved activations (training forward) included."""
     from hcatgnet_b200.synth import synth_batch
-    if path == 3 and (F > 32 or L > 3):
+    if path == 3 and (F > 32 or L > 3 or (L == 3 and F > 28)):
         pytest.skip("outside the tensor-core kernel's shared-memory budget (the dispatcher picks the FMA kernel)")
     forward_path(path)
     b = synth_batch(61, n_features=F, seed=9 + L, n_min=1, n_max=140)
