@@ -202,17 +202,31 @@ def run_reference(a):
 # ----------------------------------------------------------------------------------------------
 # algorithmic bytes per launch of each kernel (SURVEY.md §8d formulas)
 # ----------------------------------------------------------------------------------------------
-def algorithmic_bytes(name: str, N: int, E: int, B: int, F: int, H: int, layer_in: int | None = None):
+def algorithmic_bytes(name: str, N: int, E: int, B: int, F: int, H: int):
+    """Bytes one launch of `name` must move (each tensor once)."""
     csr = 4 * (N + 1) + 4 * E
     table = {
+        # whole conv stack + pooling of a batch: x, CSR, deg^-1/2 in; embedding + per-graph descriptor out/in
+        "k_tc_fwd": 4 * N * F + csr + 4 * N + 8 * B * H + 16 * B,
+        "k_fused_fwd": 4 * N * F + csr + 4 * N + 8 * B * H + 4 * (B + 1),
         "k_agg": 4 * N * H + csr + 4 * N + 4 * N * H,        # read T once, CSR, dis, write h
-        "k_gemm": None,                                        # depends on the layer; see below
         "k_pool": 4 * N * H + 4 * (B + 1) + 8 * B * H,
-        "k_count": 16 * E + 0,                                 # + integer atomics into cnt (L2-resident)
+        "k_count": 16 * E,                                     # + integer atomics into cnt (L2-resident)
         "k_fill": 16 * E + 4 * (N + 1) + 8 * E,
         "k_rowsort": 4 * (N + 1) + 8 * E + 8 * E,
     }
     return table.get(name)
+
+
+def measured_traffic(name: str, a):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full`
+    capture of this kernel on this workload (profiles/ncu_traffic.json), or None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except (OSError, ValueError):
+        return None
+    rec = t.get(f"{name}|{a.mode}|batch{a.batch}|H{a.hidden}|L{a.convs}")
+    return None if rec is None else rec["dram_bytes"]
 
 
 # ----------------------------------------------------------------------------------------------
@@ -339,12 +353,12 @@ def main():
                    for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}
         top = next(iter(kernels))
         N, E = int(np.mean(Ns)), int(np.mean(Es))
-        ab = algorithmic_bytes(top, N, E, a.batch, F_IN, a.hidden)
+        ab = algorithmic_bytes(top.split("<")[0], N, E, a.batch, F_IN, a.hidden)
         if ab is not None:
             sec = kernels[top]["ms_per_launch"] * 1e-3
             ach = ab / sec / 1e9
             roofline = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s",
-                        "frac": ach / peak, "traffic": None, "algorithmic_bytes_per_launch": ab,
+                        "frac": ach / peak, "traffic": measured_traffic(top.split("<")[0], a), "algorithmic_bytes_per_launch": ab,
                         "ms_per_launch": kernels[top]["ms_per_launch"], "peak_source": peak_src,
                         "share_of_step": kernels[top]["share"]}
 

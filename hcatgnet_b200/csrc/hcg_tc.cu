@@ -261,7 +261,13 @@ k_tc_fwd(const TcArgs a) {
   const int tid = threadIdx.x;
   const int slot = tid / kTcSlotThreads, gt = tid % kTcSlotThreads;
   const int half = gt >> 7;          // which half of the columns this thread works on
-  const int i = gt & 127;            // node (row) of the graph = TMEM lane
+  // Node (row of the graph) owned by this thread.  Its TMEM lane is fixed by the hardware (lane quadrant
+  // = warp id % 4 = the warp scheduler), and graphs fill rows from 0 up, so slot 1 maps its nodes in
+  // reverse: slot 0 loads schedulers 0,1 the most, slot 1 schedulers 3,2.
+  const int i = slot == 0 ? (gt & 127) : 127 - (gt & 127);
+  const int i_warp_min = slot == 0 ? (gt & 96) : 96 - (gt & 96);  // smallest node id owned by this warp
+  // the warp of each slot whose quadrant is filled last does the waiting and the MMA issue for the slot
+  const bool ctl_warp = (gt >> 5) == (slot == 0 ? 3 : 0);
   const int lane = tid & 31;
   const int F = a.f.F, L = a.f.L;
 
@@ -346,7 +352,7 @@ k_tc_fwd(const TcArgs a) {
     int32_t* cl = st.cl + m.lead_cl;
     const float* ds = st.ds + m.lead_ds;
     const bool row_ok = i < n;
-    const bool warp_ok = (i & ~31) < n;  // this warp owns at least one node of the graph
+    const bool warp_ok = i_warp_min < n;  // this warp owns at least one node of the graph
 
     // ---- re-pitch the x rows to P floats (zero padded) inside the idle activation buffer: a warp per
     //      row, a lane per column ------------------------------------------------------------------------
@@ -397,7 +403,8 @@ k_tc_fwd(const TcArgs a) {
       TC_TICK(5);
       ptx::tc_fence_before_sync();
       ptx::named_bar_sync(bar_id, kTcSlotThreads);  // A operand complete; previous readers of Hbuf / D are done
-      if (gt == 0) {
+      if (ctl_warp) {
+       if (lane == 0) {
         ptx::tc_fence_after_sync();
         if (l == 0)
           tc::issue_split_mma<4>(d_t, a_hi, a_lo, ptx::smem_u32(w0_hi), ptx::smem_u32(w0_lo));  // K = 32, zero padded
@@ -405,10 +412,13 @@ k_tc_fwd(const TcArgs a) {
           tc::issue_split_mma<8>(d_t, a_hi, a_lo, ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64),
                                  ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64));
         ptx::mma_commit(&bar_mma[slot]);
+       }
+       __syncwarp();
+       ptx::mbar_wait(&bar_mma[slot], mma_phase);  // one warp polls; the others sleep in the barrier below
       }
-      TC_TICK(6);
-      ptx::mbar_wait(&bar_mma[slot], mma_phase);
       mma_phase ^= 1u;
+      TC_TICK(6);
+      ptx::named_bar_sync(bar_id, kTcSlotThreads);
       ptx::tc_fence_after_sync();
       TC_TICK(7);
 
