@@ -1,0 +1,120 @@
+"""Streaming screening / prediction driver: the working counterpart of the reference's
+``scripts_experiments/predict.py:11-60`` (dead code there) and of ``predict_network``
+(reference utils/utils_model.py:82-111), for batches that live in HOST memory.
+
+``DevicePrefetcher`` stages batch i+1 to the GPU on a side stream while batch i computes, so the
+PCIe copy (the bound of end-to-end screening: ~12.5 KB per 80-atom graph) overlaps the kernels;
+``predict_stream`` runs a model over such a stream and hands back host results one batch late, so
+the host never waits on the step it has just queued.
+"""
+from __future__ import annotations
+
+from collections import deque
+from typing import Iterable, Iterator
+
+import torch
+
+from . import ops
+from .data import Batch
+
+
+class DevicePrefetcher:
+    """Iterates an iterable of host ``Batch`` objects as device batches, ``depth`` copies ahead.
+
+    Copies are issued on a private stream (pinned host memory makes them truly asynchronous);
+    the consumer's current stream is made to wait on each batch's copy event when it is handed
+    out, and the device tensors are marked as used by that stream for the caching allocator.
+    """
+
+    def __init__(self, batches: Iterable[Batch], device=None, depth: int = 2):
+        self.device = torch.device(device) if device is not None else ops._require_cuda()
+        self.batches = iter(batches)
+        self.depth = max(1, int(depth))
+        self.copy_stream = torch.cuda.Stream(self.device)
+        self.queue: deque = deque()
+
+    def _stage_one(self) -> bool:
+        try:
+            h = next(self.batches)
+        except StopIteration:
+            return False
+        with torch.cuda.stream(self.copy_stream):
+            mv = lambda t: None if t is None else t.to(self.device, non_blocking=True)  # noqa: E731
+            d = Batch(mv(h.x), mv(h.edge_index), mv(h.batch), None, mv(h.y), h.idx, h.num_graphs)
+            d.max_graph_nodes = getattr(h, "max_graph_nodes", 0)
+            ev = torch.cuda.Event()
+            ev.record(self.copy_stream)
+        self.queue.append((d, ev, h))
+        return True
+
+    def __iter__(self) -> Iterator[Batch]:
+        while len(self.queue) < self.depth and self._stage_one():
+            pass
+        while self.queue:
+            d, ev, h = self.queue.popleft()
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(ev)
+            for t in (d.x, d.edge_index, d.batch, d.y):
+                if t is not None and t.is_cuda:
+                    t.record_stream(cur)
+            self._stage_one()  # refill behind the batch being handed out
+            d._host = h
+            yield d
+
+
+def predict_stream(model, batches: Iterable[Batch], return_embedding: bool = False, device=None,
+                   depth: int = 2, validate: bool = False):
+    """Yields ``(out, emb_or_None, host_batch)`` per batch, ``out``/``emb`` as pinned HOST tensors.
+
+    Inference only (``torch.no_grad``).  ``validate=True`` keeps the per-batch status read-back of
+    ``hcg_collate`` (one stream sync per batch; bad indices raise); with ``False`` the kernels stay
+    memory-safe but malformed input is not reported.
+    """
+    prev_validate = getattr(model, "validate_inputs", True)
+    model.validate_inputs = bool(validate)
+    was_training = model.training
+    model.eval()
+    pending: deque = deque()
+    try:
+        with torch.no_grad():
+            for d in DevicePrefetcher(batches, device=device, depth=depth):
+                out, emb = model(d, True)
+                o_h = torch.empty(out.shape, dtype=out.dtype, pin_memory=True)
+                o_h.copy_(out, non_blocking=True)
+                e_h = None
+                if return_embedding:
+                    e_h = torch.empty(emb.shape, dtype=emb.dtype, pin_memory=True)
+                    e_h.copy_(emb, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+                pending.append((o_h, e_h, d._host, ev, (out, emb)))
+                if len(pending) > 1:  # hand back the previous batch: the GPU queue stays one step ahead
+                    o, e, h, pev, _keep = pending.popleft()
+                    pev.synchronize()
+                    yield o, e, h
+            while pending:
+                o, e, h, pev, _keep = pending.popleft()
+                pev.synchronize()
+                yield o, e, h
+    finally:
+        model.validate_inputs = prev_validate
+        model.train(was_training)
+
+
+def predict_network_stream(model, loader: Iterable[Batch], return_emb: bool = False, **kw):
+    """``predict_network`` (reference utils/utils_model.py:82-111) on the GPU: returns numpy arrays
+    ``(y_pred, y_true, idx[, embeddings])`` concatenated over the loader."""
+    import numpy as np
+    y_pred, y_true, idx, embs = [], [], [], []
+    for out, emb, h in predict_stream(model, loader, return_embedding=return_emb, **kw):
+        y_pred.append(out.numpy().ravel().copy() if out.shape[1] == 1 else out.numpy().copy())
+        if h.y is not None:
+            y_true.append(h.y.cpu().numpy())
+        if h.idx is not None:
+            idx.append(h.idx.cpu().numpy())
+        if return_emb:
+            embs.append(emb.numpy().copy())
+    cat = lambda xs: np.concatenate(xs, 0) if xs else np.empty((0,))  # noqa: E731
+    if return_emb:
+        return cat(y_pred), cat(y_true), cat(idx), cat(embs)
+    return cat(y_pred), cat(y_true), cat(idx)

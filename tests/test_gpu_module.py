@@ -103,3 +103,21 @@ def test_explain_signature_and_pickle(pkg):
     buf.seek(0)
     m2 = torch.load(buf, weights_only=False)
     assert torch.equal(m2(x=g["x"].cuda(), edge_index=g["edge_index"].cuda()), out)
+
+
+def test_predict_stream_matches_blocking_forward():
+    """hcatgnet_b200.predict_stream (host batches, copies overlapped on a side stream) returns, batch
+    by batch and in order, exactly what the blocking model(batch) call returns."""
+    import hcatgnet_b200 as pkg
+    from hcatgnet_b200.synth import synth_batch
+    model = pkg.make_network("GCN", pkg.default_options(), 25).to("cuda:0").eval()
+    host = [synth_batch(200 + 17 * i, 25, seed=100 + i, pin=True) for i in range(5)]
+    got = list(pkg.predict_stream(model, host, return_embedding=True))
+    assert len(got) == len(host)
+    for (o, e, h), hb in zip(got, host):
+        assert h is hb and not o.is_cuda and o.shape == (hb.num_graphs, 1)
+        with torch.no_grad():
+            o2, e2 = model(pkg.Batch(hb.x.cuda(), hb.edge_index.cuda(), hb.batch.cuda(), None, None, None, hb.num_graphs), True)
+        assert torch.equal(o, o2.cpu()) and torch.equal(e, e2.cpu())
+    yp, yt, idx, emb = pkg.predict_network_stream(model, host, return_emb=True)
+    assert yp.shape == (sum(h.num_graphs for h in host),) and emb.shape[1] == 128 and yt.shape == yp.shape
