@@ -264,8 +264,8 @@ def main():
 
     # synthetic pool: pinned host copies (e2e) and device-resident copies (value)
     host = [synth_batch(a.batch, F_IN, seed=20232023 + 1000 * rank + i, pin=True) for i in range(POOL)]
-    devb = [pkg.Batch(b.x.to(dev), b.edge_index.to(dev), b.batch.to(dev), None, b.y.to(dev), None, b.num_graphs)
-            for b in host]
+    devb = [pkg.Batch(b.x.to(dev), b.edge_index.to(dev), b.batch.to(dev), None, b.y.to(dev), None, b.num_graphs,
+                      edges_grouped=True) for b in host]
     Ns = [b.num_nodes for b in host]
     Es = [int(b.edge_index.shape[1]) for b in host]
 
@@ -277,12 +277,12 @@ def main():
     def step_device(i):
         b = devb[i % POOL]
         if a.mode == "infer":
-            plan = ops.collate(b.edge_index, b.batch, b.num_nodes, b.num_graphs, validate=False)
+            plan = ops.collate(b.edge_index, b.batch, b.num_nodes, b.num_graphs, validate=False, grouped=True)
             with torch.no_grad():
                 out, _ = ops.gcn_apply(b.x, plan, dims, params)
             return out
         # a fresh batch object every step: the collate runs inside the step (no topology cache hit)
-        fresh = pkg.Batch(b.x, b.edge_index, b.batch, None, b.y, None, b.num_graphs)
+        fresh = pkg.Batch(b.x, b.edge_index, b.batch, None, b.y, None, b.num_graphs, edges_grouped=True)
         return parallel.dp_train_step(model, fresh, validate=False)
 
     def run_e2e(steps):

@@ -14,9 +14,11 @@ from . import build as _build
 HCG_MAX_CONV = 8
 HCG_MAX_READOUT = 8
 HCG_COLLATE_TRANSPOSE = 1
+HCG_COLLATE_GROUPED = 2
+HCG_ERR_NOT_GROUPED = 7
 HCG_GRAPH_CROSS_EDGES = 1
 
-ERR_NAMES = {1: "INVALID_ARG", 2: "UNSUPPORTED", 3: "WORKSPACE", 4: "CUDA", 5: "BAD_INDEX", 6: "BAD_BATCH"}
+ERR_NAMES = {1: "INVALID_ARG", 2: "UNSUPPORTED", 3: "WORKSPACE", 4: "CUDA", 5: "BAD_INDEX", 6: "BAD_BATCH", 7: "NOT_GROUPED"}
 
 _fp = C.c_void_p  # device pointers travel as integers
 

@@ -258,6 +258,255 @@ k_graph_ptr(const int64_t* __restrict__ batch, int64_t N, int64_t B, int32_t* __
   for (int64_t g = prev + 1; g <= b; ++g) graph_ptr[g] = (int32_t)i;
 }
 
+// ==========================================================================================
+// Graph-local fast path (HCG_COLLATE_GROUPED).  PyG's collate concatenates the edge lists graph
+// by graph, so the edges of graph g are one contiguous slice of edge_index: find the slices
+// (k_edge_ranges), then build each graph's CSR entirely in shared memory (k_collate_graph) and write
+// it out coalesced.  Without dropped self-loops the CSR slots of graph g are exactly its edge slice,
+// so no batch-wide scan is needed.  Every precondition is checked on the device.
+// ==========================================================================================
+constexpr int kStatusNotGrouped = 8;
+constexpr int kGrpNodes = 1024;  // per-graph capacity of the shared-memory CSR build
+constexpr int kGrpEdges = 2048;
+constexpr int kGrpThreads = 128;
+
+// eptr[g] = first edge of graph g (graph of an edge = graph of its dst); eptr[B] = E
+__global__ void __launch_bounds__(256)
+k_edge_ranges(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, const int64_t* __restrict__ batch,
+              int64_t E, int64_t N, int64_t B, int32_t* __restrict__ eptr, int* __restrict__ status) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E; e += stride) {
+    const int64_t s = src[e], d = dst[e];
+    if (s < 0 || s >= N || d < 0 || d >= N) { atomicOr(status, kStatusBadIndex | kStatusNotGrouped); continue; }
+    if (s == d) { atomicOr(status, kStatusNotGrouped); continue; }  // dropped self-loops shift the slots
+    int64_t g = batch[d];
+    if (g < 0 || g >= B) { atomicOr(status, kStatusBadBatch | kStatusNotGrouped); continue; }
+    if (batch[s] != g) atomicOr(status, kStatusCrossEdge | kStatusNotGrouped);
+    int64_t gp = -1;
+    if (e > 0) {
+      const int64_t dp = dst[e - 1];
+      gp = (dp >= 0 && dp < N) ? batch[dp] : -1;
+      if (gp >= B) gp = -1;
+    }
+    if (g < gp) atomicOr(status, kStatusNotGrouped);
+    for (int64_t q = gp + 1; q <= g; ++q) eptr[q] = (int32_t)e;  // graphs without edges share the boundary
+    if (e == E - 1)
+      for (int64_t q = g + 1; q <= B; ++q) eptr[q] = (int32_t)E;
+  }
+}
+
+// block-wide exclusive scan of v[0..n) in shared memory (n <= kGrpNodes), kGrpThreads threads;
+// out[0..n] receives the offsets, out[n] the total.  `warp_tot` is scratch of kGrpThreads/32 ints.
+__device__ __forceinline__ void grp_scan(const int* v, int n, int* out, int* warp_tot) {
+  constexpr int PER = kGrpNodes / kGrpThreads;  // 8 consecutive items per thread
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  int local[PER], sum = 0;
+#pragma unroll
+  for (int q = 0; q < PER; ++q) {
+    const int idx = t * PER + q;
+    local[q] = idx < n ? v[idx] : 0;
+    sum += local[q];
+  }
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += u;
+  }
+  if (lane == 31) warp_tot[w] = incl;
+  __syncthreads();
+  int base = 0;
+  for (int q = 0; q < w; ++q) base += warp_tot[q];
+  int run = base + incl - sum;
+#pragma unroll
+  for (int q = 0; q < PER; ++q) {
+    const int idx = t * PER + q;
+    if (idx < n) out[idx] = run;
+    run += local[q];
+  }
+  if (t == kGrpThreads - 1) out[n] = run;  // the last thread's running sum is the total
+  __syncthreads();
+}
+
+// One CSR (by_dst = rows are dst, values src) or its transpose (rows src, values dst) of one graph,
+// built in shared memory; slots of a row end up in original edge order.
+__device__ __forceinline__ void grp_build(const int64_t* __restrict__ rowkey, const int64_t* __restrict__ val,
+                                          int e_lo, int e_cnt, int n0, int n, int* cnt, int* rp, int* slot_eid,
+                                          int* slot_val, int* warp_tot, int32_t* __restrict__ rowptr_out,
+                                          int32_t* __restrict__ col_out, int32_t* __restrict__ eid_out,
+                                          float* __restrict__ dis_out, float fill) {
+  const int t = threadIdx.x;
+  for (int i = t; i < n; i += kGrpThreads) cnt[i] = 0;
+  __syncthreads();
+  for (int k = t; k < e_cnt; k += kGrpThreads) {
+    const int r = (int)(rowkey[e_lo + k] - n0);
+    if ((unsigned)r < (unsigned)n) atomicAdd(&cnt[r], 1);  // out-of-graph keys were flagged by k_edge_ranges
+  }
+  __syncthreads();
+  grp_scan(cnt, n, rp, warp_tot);
+  for (int i = t; i < n; i += kGrpThreads) {
+    rowptr_out[n0 + i] = e_lo + rp[i];
+    if (dis_out) {
+      const float r = __fdiv_rn(1.0f, __fsqrt_rn((float)cnt[i] + fill));
+      dis_out[n0 + i] = isinf(r) ? 0.f : r;
+    }
+  }
+  __syncthreads();
+  for (int i = t; i < n; i += kGrpThreads) cnt[i] = rp[i];  // cursors
+  __syncthreads();
+  for (int k = t; k < e_cnt; k += kGrpThreads) {
+    const int r = (int)(rowkey[e_lo + k] - n0);
+    if ((unsigned)r >= (unsigned)n) continue;
+    const int pos = atomicAdd(&cnt[r], 1);
+    slot_eid[pos] = e_lo + k;
+    slot_val[pos] = (int)val[e_lo + k];
+  }
+  __syncthreads();
+  for (int i = t; i < n; i += kGrpThreads) {  // insertion sort by edge id (rows are a handful of slots)
+    const int b = rp[i], e = rp[i + 1];
+    for (int a = b + 1; a < e; ++a) {
+      const int ke = slot_eid[a], kv = slot_val[a];
+      int c = a - 1;
+      while (c >= b && slot_eid[c] > ke) { slot_eid[c + 1] = slot_eid[c]; slot_val[c + 1] = slot_val[c]; --c; }
+      slot_eid[c + 1] = ke; slot_val[c + 1] = kv;
+    }
+  }
+  __syncthreads();
+  const int kept = rp[n];
+  for (int k = t; k < e_cnt; k += kGrpThreads) {  // kept == e_cnt unless the batch was flagged
+    eid_out[e_lo + k] = k < kept ? slot_eid[k] : 0;
+    col_out[e_lo + k] = k < kept ? slot_val[k] : 0;
+  }
+  __syncthreads();
+}
+
+// ---- warp-per-graph variant for molecule-sized graphs (<= kWgNodes nodes, <= kWgEdges edges): no
+//      block-wide barriers, eight graphs in flight per CTA ----------------------------------------
+constexpr int kWgNodes = 256, kWgEdges = 512, kWgWarps = 4;
+
+__device__ __forceinline__ void wg_build(const int64_t* __restrict__ rowkey, const int64_t* __restrict__ val, int e_lo,
+                                         int e_cnt, int n0, int n, int* cnt, int* rp, int* slot_eid, int* slot_val,
+                                         int32_t* __restrict__ rowptr_out, int32_t* __restrict__ col_out,
+                                         int32_t* __restrict__ eid_out, float* __restrict__ dis_out, float fill) {
+  const int lane = threadIdx.x & 31;
+  constexpr int PER = kWgNodes / 32;
+  for (int i = lane; i < n; i += 32) cnt[i] = 0;
+  __syncwarp();
+  for (int k = lane; k < e_cnt; k += 32) {
+    const int r = (int)(rowkey[e_lo + k] - n0);
+    if ((unsigned)r < (unsigned)n) atomicAdd(&cnt[r], 1);
+  }
+  __syncwarp();
+  int local[PER], sum = 0;
+#pragma unroll
+  for (int q = 0; q < PER; ++q) {
+    const int idx = lane * PER + q;
+    local[q] = idx < n ? cnt[idx] : 0;
+    sum += local[q];
+  }
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += u;
+  }
+  int run = incl - sum;
+#pragma unroll
+  for (int q = 0; q < PER; ++q) {
+    const int idx = lane * PER + q;
+    if (idx < n) rp[idx] = run;
+    run += local[q];
+  }
+  if (lane == 31) rp[n] = run;
+  __syncwarp();
+  for (int i = lane; i < n; i += 32) {
+    const int b = rp[i];
+    rowptr_out[n0 + i] = e_lo + b;
+    if (dis_out) {
+      const float r = __fdiv_rn(1.0f, __fsqrt_rn((float)cnt[i] + fill));
+      dis_out[n0 + i] = isinf(r) ? 0.f : r;
+    }
+  }
+  __syncwarp();
+  for (int i = lane; i < n; i += 32) cnt[i] = rp[i];  // cursors
+  __syncwarp();
+  for (int k = lane; k < e_cnt; k += 32) {
+    const int r = (int)(rowkey[e_lo + k] - n0);
+    if ((unsigned)r >= (unsigned)n) continue;
+    const int pos = atomicAdd(&cnt[r], 1);
+    slot_eid[pos] = e_lo + k;
+    slot_val[pos] = (int)val[e_lo + k];
+  }
+  __syncwarp();
+  for (int i = lane; i < n; i += 32) {  // insertion sort by edge id inside each row
+    const int b = rp[i], e = rp[i + 1];
+    for (int a = b + 1; a < e; ++a) {
+      const int ke = slot_eid[a], kv = slot_val[a];
+      int c = a - 1;
+      while (c >= b && slot_eid[c] > ke) { slot_eid[c + 1] = slot_eid[c]; slot_val[c + 1] = slot_val[c]; --c; }
+      slot_eid[c + 1] = ke; slot_val[c + 1] = kv;
+    }
+  }
+  __syncwarp();
+  const int kept = rp[n];
+  for (int k = lane; k < e_cnt; k += 32) {
+    eid_out[e_lo + k] = k < kept ? slot_eid[k] : 0;
+    col_out[e_lo + k] = k < kept ? slot_val[k] : 0;
+  }
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(kWgWarps * 32)
+k_collate_graph_warp(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, int64_t E, int64_t N, int64_t B,
+                     const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ eptr, float fill,
+                     int32_t* __restrict__ rowptr, int32_t* __restrict__ col, int32_t* __restrict__ eid,
+                     float* __restrict__ dis, int32_t* __restrict__ t_rowptr, int32_t* __restrict__ t_col,
+                     int32_t* __restrict__ t_eid, int* __restrict__ big_count) {
+  __shared__ int cnt[kWgWarps][kWgNodes], rp[kWgWarps][kWgNodes + 1], slot_eid[kWgWarps][kWgEdges], slot_val[kWgWarps][kWgEdges];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t stride = (int64_t)gridDim.x * kWgWarps;
+  for (int64_t g = (int64_t)blockIdx.x * kWgWarps + w; g < B; g += stride) {
+    const int n0 = graph_ptr[g], n = graph_ptr[g + 1] - n0;
+    const int e_lo = eptr[g], e_cnt = eptr[g + 1] - e_lo;
+    if (g == B - 1 && lane == 0) {
+      rowptr[N] = (int32_t)E;
+      if (t_rowptr) t_rowptr[N] = (int32_t)E;
+    }
+    if (n <= 0) continue;
+    if (n > kWgNodes || e_cnt > kWgEdges || e_cnt < 0 || e_lo < 0 || (int64_t)e_lo + e_cnt > E) {
+      if (lane == 0) atomicAdd(big_count, 1);  // left to the block-per-graph kernel
+      continue;
+    }
+    wg_build(dst, src, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot_eid[w], slot_val[w], rowptr, col, eid, dis, fill);
+    if (t_rowptr)
+      wg_build(src, dst, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot_eid[w], slot_val[w], t_rowptr, t_col, t_eid, nullptr, fill);
+  }
+}
+
+__global__ void __launch_bounds__(kGrpThreads)
+k_collate_graph(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, int64_t E, int64_t N, int64_t B,
+                const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ eptr, float fill,
+                int32_t* __restrict__ rowptr, int32_t* __restrict__ col, int32_t* __restrict__ eid,
+                float* __restrict__ dis, int32_t* __restrict__ t_rowptr, int32_t* __restrict__ t_col,
+                int32_t* __restrict__ t_eid, int* __restrict__ status) {
+  __shared__ int cnt[kGrpNodes + 1], rp[kGrpNodes + 1], slot_eid[kGrpEdges], slot_val[kGrpEdges];
+  __shared__ int warp_tot[kGrpThreads / 32];
+  if (status[1] == 0) return;  // k_collate_graph_warp left nothing behind
+  for (int64_t g = blockIdx.x; g < B; g += gridDim.x) {
+    const int n0 = graph_ptr[g], n = graph_ptr[g + 1] - n0;
+    int e_lo = eptr[g], e_cnt = eptr[g + 1] - e_lo;
+    if (n <= 0) continue;
+    if (n <= kWgNodes && e_cnt <= kWgEdges && e_cnt >= 0 && e_lo >= 0 && (int64_t)e_lo + e_cnt <= E) continue;  // done by a warp
+    if (n > kGrpNodes || e_cnt > kGrpEdges || e_cnt < 0 || e_lo < 0 || (int64_t)e_lo + e_cnt > E) {
+      if (threadIdx.x == 0) atomicOr(status, kStatusNotGrouped);
+      continue;
+    }
+    grp_build(dst, src, e_lo, e_cnt, n0, n, cnt, rp, slot_eid, slot_val, warp_tot, rowptr, col, eid, dis, fill);
+    if (t_rowptr)
+      grp_build(src, dst, e_lo, e_cnt, n0, n, cnt, rp, slot_eid, slot_val, warp_tot, t_rowptr, t_col, t_eid, nullptr, fill);
+  }
+}
+
 static int scan_i32(const int32_t* in, int64_t n, int32_t* out, int32_t* sums, cudaStream_t st) {
   // out has n+1 entries; out[n] = total
   int64_t nblk = cdiv(n > 0 ? n : 1, kScanTile);
@@ -272,17 +521,18 @@ static int scan_i32(const int32_t* in, int64_t n, int32_t* out, int32_t* sums, c
 
 struct CollateWs {
   int* status;
-  int32_t *cnt_dst, *cnt_src, *loop_eid, *sums, *t_sums;
+  int32_t *cnt_dst, *cnt_src, *loop_eid, *sums, *t_sums, *eptr;
   int2 *tmp, *t_tmp;
   size_t bytes;
 };
 
 // one carving routine for both the size query (base == nullptr) and the real call
-static CollateWs carve_collate(void* ws, int64_t N, int64_t E, int flags) {
+static CollateWs carve_collate(void* ws, int64_t N, int64_t E, int64_t B, int flags) {
   Carver c(ws, (size_t)-1);
   CollateWs w{};
   int64_t nblk = cdiv(N > 0 ? N : 1, kScanTile) + 1;
   w.status = c.take<int>(64);
+  w.eptr = c.take<int32_t>(B + 2);   // status and eptr are adjacent: one memset clears both
   w.cnt_dst = c.take<int32_t>(N + 1);   // status, cnt_dst, cnt_src are adjacent: one memset clears them
   w.cnt_src = c.take<int32_t>(N + 1);
   w.loop_eid = c.take<int32_t>(N + 1);
@@ -299,8 +549,7 @@ static CollateWs carve_collate(void* ws, int64_t N, int64_t E, int flags) {
 using namespace hcg;
 
 extern "C" size_t hcg_collate_workspace_bytes(int64_t N, int64_t E, int64_t B, int flags) {
-  (void)B;
-  return carve_collate(nullptr, N, E, flags).bytes;
+  return carve_collate(nullptr, N, E, B, flags).bytes;
 }
 
 extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* batch, int64_t N, int64_t B,
@@ -327,10 +576,35 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
   const size_t need = hcg_collate_workspace_bytes(N, E, B, flags);
   HCG_REQUIRE(ws_bytes >= need, HCG_ERR_WORKSPACE, "collate workspace too small: %zu < %zu", ws_bytes, need);
 
-  CollateWs w = carve_collate(ws, N, E, flags);
+  CollateWs w = carve_collate(ws, N, E, B, flags);
   note_region(st);
   const int64_t* src = edge_index;
   const int64_t* dst = edge_index + E;
+
+  // ---- graph-local fast path (checked on the device; see HCG_COLLATE_GROUPED in hcg.h) -----------
+  if ((flags & HCG_COLLATE_GROUPED) && batch != nullptr && !weighted && B > 0 && N > 0) {
+    HCG_CUDA_OK(cudaMemsetAsync(w.status, 0, (size_t)((char*)w.cnt_dst - (char*)w.status), st));
+    HCG_CUDA_OK(cudaMemsetAsync(graph_ptr, 0, (size_t)(B + 1) * sizeof(int32_t), st));
+    note_other("memset(collate)", st);
+    k_graph_ptr<<<(unsigned)cdiv(N + 1, 256), 256, 0, st>>>(batch, N, B, graph_ptr, w.status);
+    HCG_LAUNCH_OK(st, "k_graph_ptr");
+    if (E > 0) {
+      int64_t eb = cdiv(E, 256);
+      if (eb > (int64_t)kNumSMs * 16) eb = (int64_t)kNumSMs * 16;
+      k_edge_ranges<<<(unsigned)eb, 256, 0, st>>>(src, dst, batch, E, N, B, w.eptr, w.status);
+      HCG_LAUNCH_OK(st, "k_edge_ranges");
+    }
+    int64_t wb = cdiv(B, kWgWarps);
+    if (wb > (int64_t)kNumSMs * 9) wb = (int64_t)kNumSMs * 9;
+    k_collate_graph_warp<<<(unsigned)wb, kWgWarps * 32, 0, st>>>(src, dst, E, N, B, graph_ptr, w.eptr, fill, rowptr, col, eid, dis,
+                                                                transpose ? t_rowptr : nullptr, t_col, t_eid, w.status + 1);
+    HCG_LAUNCH_OK(st, "k_collate_graph_warp");
+    int64_t gb = B < (int64_t)kNumSMs * 8 ? B : (int64_t)kNumSMs * 8;
+    k_collate_graph<<<(unsigned)gb, kGrpThreads, 0, st>>>(src, dst, E, N, B, graph_ptr, w.eptr, fill, rowptr, col, eid, dis,
+                                                        transpose ? t_rowptr : nullptr, t_col, t_eid, w.status);
+    HCG_LAUNCH_OK(st, "k_collate_graph");
+    return HCG_OK;
+  }
 
   // status + both histograms are adjacent: one memset; loop_eid = -1; graph_ptr = 0 so that a
   // rejected batch vector still leaves memory-safe offsets behind
@@ -386,6 +660,9 @@ extern "C" int hcg_collate_status(const void* ws, void* stream, int32_t* graph_f
   HCG_CUDA_OK(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
   if (status & kStatusBadIndex) return set_err(HCG_ERR_BAD_INDEX, "edge_index holds a node index outside [0, N)");
   if (status & kStatusBadBatch) return set_err(HCG_ERR_BAD_BATCH, "batch vector is not sorted or holds an id outside [0, B)");
+  if (status & kStatusNotGrouped)
+    return set_err(HCG_ERR_NOT_GROUPED, "HCG_COLLATE_GROUPED: edges are not grouped by graph, or self-loops / cross-graph edges / "
+                                        "a graph above %d nodes or %d edges are present; collate again without the flag", kGrpNodes, kGrpEdges);
   if (graph_flags && (status & kStatusCrossEdge)) *graph_flags |= HCG_GRAPH_CROSS_EDGES;
   return HCG_OK;
 }

@@ -24,8 +24,11 @@ def _field(g, name, default=None):
 class Batch:
     """A disjoint union of graphs: nodes concatenated, edge indices offset per graph."""
 
-    def __init__(self, x, edge_index, batch, ptr=None, y=None, idx=None, num_graphs=None):
+    def __init__(self, x, edge_index, batch, ptr=None, y=None, idx=None, num_graphs=None, edges_grouped=None):
         self.x, self.edge_index, self.batch, self.ptr, self.y, self.idx = x, edge_index, batch, ptr, y, idx
+        # True when edge_index is known to list the edges graph by graph (this module's own collate
+        # does); lets hcg_collate take its graph-local path without a status read-back
+        self.edges_grouped = edges_grouped
         if num_graphs is None:
             num_graphs = (int(ptr.numel()) - 1) if ptr is not None else (int(batch.max()) + 1 if batch.numel() else 0)
         self.num_graphs = int(num_graphs)
@@ -51,7 +54,7 @@ class Batch:
             [torch.as_tensor(v, dtype=torch.float32).reshape(-1) for v in ys], 0)
         ids = [_field(g, "idx") for g in graphs]
         idx = None if any(v is None for v in ids) else torch.tensor([int(v) for v in ids], dtype=torch.int64)
-        return cls(x, edge_index, batch, ptr, y, idx, len(graphs))
+        return cls(x, edge_index, batch, ptr, y, idx, len(graphs), edges_grouped=True)
 
     @property
     def num_nodes(self) -> int:

@@ -144,7 +144,8 @@ class _GCNBase(BaseNetwork):
             raise NotImplementedError("gradients w.r.t. edge_weight are not provided by libhcg yet")
         plan = ops.cached_collate(cache_on, edge_index, batch, x.shape[0], num_graphs, device,
                                   edge_weight=edge_weight, improved=bool(self.improved), transpose=need_grad,
-                                  validate=self.validate_inputs, max_graph_nodes=_max_nodes_hint(cache_on))
+                                  validate=self.validate_inputs, max_graph_nodes=_max_nodes_hint(cache_on),
+                                  grouped=getattr(cache_on, "edges_grouped", None))
         xd = ops.to_device(x, device, torch.float32)
         pd = [ops.to_device(p, device, torch.float32) for p in params]
         out, emb = ops.gcn_apply(xd, plan, self._dims(), pd)

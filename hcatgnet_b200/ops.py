@@ -90,13 +90,18 @@ class GraphPlan:
 
 def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int, num_graphs: int,
             edge_weight: torch.Tensor | None = None, improved: bool = False, transpose: bool = False,
-            fill: float = 1.0, validate: bool = True, max_graph_nodes: int = 0) -> GraphPlan:
+            fill: float = 1.0, validate: bool = True, max_graph_nodes: int = 0,
+            grouped: bool | None = None) -> GraphPlan:
     """COO ``edge_index`` [2,E] int64 + sorted ``batch`` [N] int64 -> :class:`GraphPlan`.
 
     Runs ``hcg_collate``.  ``improved`` only matters together with ``edge_weight`` (self-loop
     fill 2.0), mirroring the behaviour of the reference's PyG path.
     ``validate`` reads back one status word (a stream sync) and raises on bad indices / unsorted
     batch; the kernels are memory-safe either way.
+    ``grouped`` selects the graph-local fast path of ``hcg_collate`` (HCG_COLLATE_GROUPED: edges listed
+    graph by graph, as ``Batch.from_data_list`` / PyG's collate produce them; same outputs bit for bit):
+    ``True`` = the caller vouches for it, ``None`` = try it when the status word is read back anyway
+    (``validate``) and fall back to the general kernels if the device check refuses, ``False`` = never.
     """
     device = _require_cuda() if not edge_index.is_cuda else edge_index.device
     lib = _lib.load()
@@ -119,6 +124,10 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
                          torch.empty(max(E, 1), **i32), torch.empty(max(N, 1), **f32), torch.empty(B + 1, **i32),
                          fill=float(fill), max_graph_nodes=int(max_graph_nodes))
         flags = 0
+        use_grouped = bt is not None and ew is None and B > 0 and N > 0 and E > 0 and \
+            (grouped is True or (grouped is None and validate))
+        if use_grouped:
+            flags |= _lib.HCG_COLLATE_GROUPED
         if transpose:
             flags |= _lib.HCG_COLLATE_TRANSPOSE
             plan.t_rowptr = torch.empty(N + 1, **i32)
@@ -140,7 +149,11 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
             _ptr(ws), ws.numel(), st))
         if validate:
             gflags = C.c_int32(0)
-            _lib.check(lib.hcg_collate_status(_ptr(ws), st, C.byref(gflags)))
+            rc = lib.hcg_collate_status(_ptr(ws), st, C.byref(gflags))
+            if rc == _lib.HCG_ERR_NOT_GROUPED and use_grouped:  # the device check refused the fast path
+                return collate(ei, bt, N, B, edge_weight=ew, improved=improved, transpose=transpose, fill=fill,
+                               validate=True, max_graph_nodes=max_graph_nodes, grouped=False)
+            _lib.check(rc)
             plan.flags = int(gflags.value)
         else:
             ws.record_stream(torch.cuda.current_stream(device))
@@ -148,7 +161,7 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
 
 
 def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edge_weight=None,
-                   improved=False, transpose=False, validate=True, max_graph_nodes=0) -> GraphPlan:
+                   improved=False, transpose=False, validate=True, max_graph_nodes=0, grouped=None) -> GraphPlan:
     """``collate`` memoised on ``holder`` (the batch object the caller passed to ``forward``).
 
     The reference recomputes the normalisation inside every GCNConv call of every forward
@@ -167,7 +180,7 @@ def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edg
         plan = collate(to_device(edge_index, device, torch.int64), to_device(batch, device, torch.int64),
                        num_nodes, num_graphs, edge_weight=to_device(edge_weight, device, torch.float32),
                        improved=improved, transpose=transpose, validate=validate,
-                       max_graph_nodes=max_graph_nodes)
+                       max_graph_nodes=max_graph_nodes, grouped=grouped)
     if key is not None:
         try:
             object.__setattr__(holder, "_hcg_plan", (key, plan))

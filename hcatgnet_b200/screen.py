@@ -40,7 +40,8 @@ class DevicePrefetcher:
             return False
         with torch.cuda.stream(self.copy_stream):
             mv = lambda t: None if t is None else t.to(self.device, non_blocking=True)  # noqa: E731
-            d = Batch(mv(h.x), mv(h.edge_index), mv(h.batch), None, mv(h.y), h.idx, h.num_graphs)
+            d = Batch(mv(h.x), mv(h.edge_index), mv(h.batch), None, mv(h.y), h.idx, h.num_graphs,
+                      edges_grouped=getattr(h, "edges_grouped", None))
             d.max_graph_nodes = getattr(h, "max_graph_nodes", 0)
             ev = torch.cuda.Event()
             ev.record(self.copy_stream)

@@ -67,5 +67,5 @@ def synth_batch(num_graphs: int, n_features: int = 25, seed: int = 20232023, pin
     d = synth_batch_numpy(num_graphs, n_features, seed, **kw)
     b = Batch(torch.from_numpy(d["x"]), torch.from_numpy(d["edge_index"]), torch.from_numpy(d["batch"]),
               torch.from_numpy(d["ptr"]), torch.from_numpy(d["y"]),
-              torch.arange(num_graphs, dtype=torch.int64), num_graphs)
+              torch.arange(num_graphs, dtype=torch.int64), num_graphs, edges_grouped=True)
     return b.pin_memory() if pin else b

@@ -39,7 +39,8 @@ enum {
   HCG_ERR_WORKSPACE = 3,
   HCG_ERR_CUDA = 4,
   HCG_ERR_BAD_INDEX = 5,      /* edge_index entry outside [0, N) */
-  HCG_ERR_BAD_BATCH = 6       /* batch vector not sorted / outside [0, B) */
+  HCG_ERR_BAD_BATCH = 6,      /* batch vector not sorted / outside [0, B) */
+  HCG_ERR_NOT_GROUPED = 7     /* HCG_COLLATE_GROUPED was requested but the batch does not qualify: call again without it */
 };
 
 /* HcgGraph.flags */
@@ -50,7 +51,13 @@ enum {
 
 /* flags of hcg_collate */
 enum {
-  HCG_COLLATE_TRANSPOSE = 1   /* also build the src-sorted (transposed) CSR for the backward pass */
+  HCG_COLLATE_TRANSPOSE = 1,  /* also build the src-sorted (transposed) CSR for the backward pass */
+  HCG_COLLATE_GROUPED = 2     /* graph-local fast path: the caller expects edge_index to list the edges graph by
+                                 graph in batch order (what PyG's Batch.from_data_list produces), without self-loop
+                                 edges, graphs of at most 1024 nodes / 2048 edges, no edge weights.  Same outputs,
+                                 bit for bit.  The expectation is CHECKED on the device: if it does not hold the
+                                 status word says so (hcg_collate_status returns HCG_ERR_NOT_GROUPED), the outputs
+                                 are unusable but every access stayed in bounds; call again without the flag. */
 };
 
 /*
