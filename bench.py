@@ -209,6 +209,8 @@ def algorithmic_bytes(name: str, N: int, E: int, B: int, F: int, H: int):
         # whole conv stack + pooling of a batch: x, CSR, deg^-1/2 in; embedding + per-graph descriptor out/in
         "k_tc_fwd": 4 * N * F + csr + 4 * N + 8 * B * H + 16 * B,
         "k_fused_fwd": 4 * N * F + csr + 4 * N + 8 * B * H + 4 * (B + 1),
+        # graph-resident backward: saved h1, h2, x, transposed CSR, dis, emb + its gradient in; per-CTA partials out
+        "k_fused_bwd": 8 * N * H + 4 * N * F + csr + 4 * N + 16 * B * H + 296 * 4 * (H * H + H * F + 2 * H),
         "k_agg": 4 * N * H + csr + 4 * N + 4 * N * H,        # read T once, CSR, dis, write h
         "k_pool": 4 * N * H + 4 * (B + 1) + 8 * B * H,
         "k_count": 16 * E,                                     # + integer atomics into cnt (L2-resident)

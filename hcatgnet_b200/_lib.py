@@ -132,6 +132,7 @@ def check(code: int) -> None:
 
 
 HCG_CFG_FORWARD_PATH = 0
+HCG_CFG_BACKWARD_PATH = 1
 PATH_AUTO, PATH_LAYERWISE, PATH_GRAPH_RESIDENT, PATH_TENSOR_CORE = 0, 1, 2, 3
 
 

@@ -46,4 +46,29 @@ size_t tc_fwd_workspace_bytes(int64_t B);
 // the per-graph descriptors and that list
 int launch_tc_fwd(const FusedFwdArgs& a, int64_t N, int64_t E, void* ws, cudaStream_t st);
 
+// ---- graph-resident backward (hcg_fused_bwd.cu): H == 64, two conv layers, F <= 32 ---------------
+struct FusedBwdArgs {
+  const int32_t* t_rowptr;        // transposed (src-sorted) CSR
+  const int32_t* t_col;
+  const float* dis;
+  const int32_t* graph_ptr;
+  const float* x;                 // [N, F]
+  const float* h1;                // [N, 64] saved output of conv layer 0
+  const float* h2;                // [N, 64] saved output of conv layer 1
+  const float* emb;               // [B, 128] forward embedding (max || mean)
+  const float* gemb;              // [B, 128] gradient flowing into the embedding
+  const float* w2;                // conv_w[1], [64, 64] (out, in)
+  float* scratch;                 // 3 planes of [(N + 16 B + 16), 64] for graphs above the smem capacity
+  int64_t scratch_stride;         // floats between the planes (set by launch_fused_bwd)
+  float* partial;                 // [grid][64*64 + 64*F + 128] per-CTA partial parameter gradients
+  int64_t B;
+  int F;
+  float slope, fill;
+};
+int fused_bwd_grid(int64_t B);
+size_t fused_bwd_partial_elems(int64_t B, int F);
+size_t fused_bwd_scratch_elems(int64_t N, int64_t B);
+// writes g_w2 [64,64], g_w1 [64,F], g_b2 [64], g_b1 [64]
+int launch_fused_bwd(FusedBwdArgs a, int64_t N, float* g_w2, float* g_w1, float* g_b2, float* g_b1, cudaStream_t st);
+
 }  // namespace hcg

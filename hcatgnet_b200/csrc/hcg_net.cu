@@ -532,14 +532,31 @@ static FwdWs carve_fwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
 
 struct BwdWs {
   float *gA, *gT, *partial, *gz[2], *gemb;
+  float *fpartial, *fscratch;  // graph-resident backward: per-CTA partials, oversize-graph scratch
   size_t bytes;
 };
+
+// the graph-resident backward applies (hcg_fused_bwd.cu); g_x and the config switch are checked by the caller
+static bool fused_bwd_shape_ok(const HcgGraph* g, const HcgParams* p) {
+  return p->H == kFusedH && p->L == 2 && p->F <= 32 && g->ew0 == nullptr && g->B > 0 && g->N > 0 &&
+         !(g->flags & HCG_GRAPH_CROSS_EDGES) && g->N / g->B <= 512;
+}
 
 static BwdWs carve_bwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
   Carver c(ws, (size_t)-1);
   BwdWs w{};
-  w.gA = c.take<float>((size_t)N * p->H + 4);
-  w.gT = c.take<float>((size_t)N * p->H + 4);
+  // graph-resident scratch: three [N + 16 B + 16, 64] planes; gA / gT of the layer-wise path alias the
+  // first two when the shape allows the graph-resident kernel (only one of the two paths runs per call)
+  const bool fshape = p->H == kFusedH && p->L == 2 && p->F <= 32 && B > 0 && N > 0;
+  if (fshape) {
+    w.fscratch = c.take<float>(fused_bwd_scratch_elems(N, B) + 4);
+    w.fpartial = c.take<float>(fused_bwd_partial_elems(B, p->F) + 4);
+    w.gA = w.fscratch;
+    w.gT = w.fscratch + (size_t)N * p->H + 64;
+  } else {
+    w.gA = c.take<float>((size_t)N * p->H + 4);
+    w.gT = c.take<float>((size_t)N * p->H + 4);
+  }
   size_t pe = 0;
   for (int l = 0; l < p->L; ++l) {
     size_t e = xty_partial_elems(N, p->H, l == 0 ? p->F : p->H);
@@ -735,6 +752,22 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
     for (int k = 0; k < p->R; ++k) {
       HCG_CUDA_OK(cudaMemsetAsync(grads->ro_w[k], 0, sizeof(float) * (size_t)ro_in_dim(p, k) * ro_out_dim(p, k), st));
       HCG_CUDA_OK(cudaMemsetAsync(grads->ro_b[k], 0, sizeof(float) * (size_t)ro_out_dim(p, k), st));
+    }
+  }
+
+  // ---- graph-resident path: pooling backward + both conv layers in one kernel ----------------
+  {
+    const int bpath = config_get(HCG_CFG_BACKWARD_PATH);
+    const bool ok = fused_bwd_shape_ok(g, p) && g_x == nullptr && w.fscratch != nullptr;
+    if (bpath == 2 && !ok)
+      return set_err(HCG_ERR_UNSUPPORTED, "graph-resident backward needs H == %d, L == 2, F <= 32, no edge weights, a disjoint batch and g_x == NULL", kFusedH);
+    if (ok && bpath != 1) {
+      FusedBwdArgs a{};
+      a.t_rowptr = g->t_rowptr; a.t_col = g->t_col; a.dis = g->dis; a.graph_ptr = g->graph_ptr;
+      a.x = x; a.h1 = saved->acts[0]; a.h2 = saved->acts[1]; a.emb = emb; a.gemb = gemb_total;
+      a.w2 = p->conv_w[1]; a.scratch = w.fscratch; a.partial = w.fpartial;
+      a.B = B; a.F = p->F; a.slope = p->slope; a.fill = g->fill;
+      return launch_fused_bwd(a, N, grads->conv_w[1], grads->conv_w[0], grads->conv_b[1], grads->conv_b[0], st);
     }
   }
 

@@ -153,9 +153,12 @@ int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts, int cap);
  * looks like molecules: the tensor-core kernel for F <= 32, the FMA kernel for F <= 64; layer-wise
  * kernels otherwise), 1 = force layer-wise, 2 = force graph-resident FMA, 3 = force graph-resident
  * tensor-core (HCG_ERR_UNSUPPORTED if not applicable).
- * Both are CUDA paths; there is no CPU path.  Returns the previous value, or -1 for a bad key.
+ * HCG_CFG_BACKWARD_PATH: 0 = auto (the graph-resident backward kernel when H == 64, L == 2, F <= 32, no
+ * edge weights, a disjoint molecule-like batch and no gradient w.r.t. x is wanted; layer-wise kernels
+ * otherwise), 1 = force layer-wise, 2 = force graph-resident (HCG_ERR_UNSUPPORTED if not applicable).
+ * All are CUDA paths; there is no CPU path.  Returns the previous value, or -1 for a bad key.
  */
-enum { HCG_CFG_FORWARD_PATH = 0, HCG_CFG_COUNT_ = 1 };
+enum { HCG_CFG_FORWARD_PATH = 0, HCG_CFG_BACKWARD_PATH = 1, HCG_CFG_COUNT_ = 2 };
 int hcg_config_set(int key, int value);
 int hcg_config_get(int key);
 

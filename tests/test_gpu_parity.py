@@ -410,3 +410,61 @@ def test_cross_graph_edges(hcg, forward_path):
         o2, _ = hcg.gcn_apply(b.x.cuda(), plan2, _dims(hcg, sd), params)
     torch.cuda.synchronize()
     assert torch.isfinite(o2).all()
+
+
+# ------------------------------------------------------------------------------------------
+# the two CUDA backward paths (graph-resident kernel / layer-wise kernels) against the fp64 oracle
+# ------------------------------------------------------------------------------------------
+@pytest.fixture
+def backward_path(hcg):
+    from hcatgnet_b200 import _lib
+    prev = []
+
+    def set_path(v):
+        prev.append(_lib.config_set(_lib.HCG_CFG_BACKWARD_PATH, v))
+
+    yield set_path
+    if prev:
+        _lib.config_set(_lib.HCG_CFG_BACKWARD_PATH, prev[0])
+
+
+@pytest.mark.parametrize("path", [1, 2])
+@pytest.mark.parametrize("rset,outer,inner,count", [("learning", 1, 2, 668), ("biaryl", 5, 6, 485), ("final_test", 8, 10, 52)])
+def test_backward_paths_match_oracle(hcg, backward_path, path, rset, outer, inner, count):
+    """Whole datasets in one batch: more graphs than CTAs (each CTA accumulates several graphs), biaryl
+    graphs above the 128-node shared-memory capacity (global scratch path) and isolated atoms."""
+    backward_path(path)
+    sd, graphs, _, _ = golden_io.rows_with_graphs(rset, outer, inner)
+    b = ref_gcn.collate(graphs[:count])
+    args = (sd, b["x"], b["edge_index"], b["batch"], b["num_graphs"], b["y"])
+    l_ref, g_ref, _ = _oracle_grads(*args)
+    l_cuda, g_cuda, _ = _cuda_grads(hcg, *args)
+    assert abs(l_cuda - l_ref) <= 1e-5 * max(abs(l_ref), 1)
+    _assert_grads(g_cuda, g_ref)
+
+
+@pytest.mark.parametrize("F,nmin,nmax,B", [(25, 40, 120, 3000), (32, 1, 9, 700), (3, 100, 300, 50), (8, 128, 128, 40), (25, 1, 1, 10)])
+def test_graph_resident_backward_shapes(hcg, backward_path, F, nmin, nmax, B):
+    from hcatgnet_b200.synth import synth_batch
+    b = synth_batch(B, n_features=F, seed=11, n_min=nmin, n_max=nmax)
+    sd = ref_gcn.init_state_dict(F, 64, 2, 2, 1, seed=5)
+    args = (sd, b.x, b.edge_index, b.batch, b.num_graphs, b.y)
+    _, g_ref, _ = _oracle_grads(*args)
+    backward_path(2)
+    _, g_fused, _ = _cuda_grads(hcg, *args)
+    _assert_grads(g_fused, g_ref)
+    _, g_again, _ = _cuda_grads(hcg, *args)
+    for k in g_fused:  # no floating-point atomics: run-to-run identical bits
+        assert torch.equal(g_fused[k], g_again[k]), k
+    backward_path(1)
+    _, g_layer, _ = _cuda_grads(hcg, *args)
+    _assert_grads(g_layer, g_ref)
+
+
+def test_graph_resident_backward_refuses_unsupported(hcg, backward_path):
+    from hcatgnet_b200.synth import synth_batch
+    b = synth_batch(5, n_features=7, seed=1, n_min=3, n_max=9)
+    sd = ref_gcn.init_state_dict(7, 48, 3, 2, 1, seed=5)
+    backward_path(2)
+    with pytest.raises(RuntimeError):
+        _cuda_grads(hcg, sd, b.x, b.edge_index, b.batch, b.num_graphs, b.y)
