@@ -262,6 +262,8 @@ def main():
     model = pkg.make_network("GCN", opt, F_IN).to(dev)
     model.eval() if a.mode == "infer" else model.train()
     dims = model._dims()
+    # training: the device-resident step (collate, forward, loss seed, backward, all-reduce, Adam)
+    trainer = pkg.FusedTrainer(model) if a.mode == "train" else None
     params = [p.detach() for p in model._flat_params()]
 
     # synthetic pool: pinned host copies (e2e) and device-resident copies (value)
@@ -285,7 +287,7 @@ def main():
             return out
         # a fresh batch object every step: the collate runs inside the step (no topology cache hit)
         fresh = pkg.Batch(b.x, b.edge_index, b.batch, None, b.y, None, b.num_graphs, edges_grouped=True)
-        return parallel.dp_train_step(model, fresh, validate=False)
+        return trainer.step(fresh)
 
     def run_e2e(steps):
         """The public streaming API on HOST batches: every step's inputs cross PCIe from pinned memory
@@ -298,7 +300,7 @@ def main():
             return n
         prev = None
         for d in pkg.DevicePrefetcher(stream, device=dev):
-            loss = parallel.dp_train_step(model, d, validate=False)
+            loss = trainer.step(d)
             l_h = torch.empty((), dtype=loss.dtype, pin_memory=True)
             l_h.copy_(loss, non_blocking=True)
             ev = torch.cuda.Event(); ev.record()
@@ -399,7 +401,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / a.steps, "wall_ms_per_step": wall_e2e / a.steps,
                     "api": "hcatgnet_b200.predict_stream (H2D of batch i+1 overlaps the kernels of batch i)"
-                    if a.mode == "infer" else "hcatgnet_b200.DevicePrefetcher + parallel.dp_train_step"},
+                    if a.mode == "infer" else "hcatgnet_b200.DevicePrefetcher + FusedTrainer.step"},
             "gpu_launches": int(launches),
             "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline,
         }

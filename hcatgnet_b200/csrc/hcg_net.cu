@@ -315,6 +315,161 @@ k_readout2(const float* __restrict__ emb, const float* __restrict__ W1, const fl
   }
 }
 
+// ==========================================================================================
+// Backward of the default two-layer readout head in one launch (+ one reduce):
+//   gpre1 = (g_out . W2) * lrelu'(hid)                      [B,64]
+//   g_emb = gpre1 . W1 (+ extra gradient into emb)          [B,128]  -> feeds the pooling backward
+//   gW1 = gpre1^T emb, gb1 = colsum(gpre1), gW2 = g_out^T hid, gb2 = colsum(g_out)
+// A block owns 64 graphs and writes its partial parameter gradients; k_readout2_bwd_reduce sums the
+// blocks in order (deterministic).  Replaces 11 launches of the general chain.
+// ==========================================================================================
+constexpr int RB_P = 68;  // pitch of the 64-wide shared tiles
+
+__host__ __device__ inline int ro2_partial_elems(int C) { return RO_HID * RO_IN + RO_HID + C * RO_HID + C; }
+__host__ __device__ inline int ro2_partial_stride(int C) { return (ro2_partial_elems(C) + 3) & ~3; }  // 16-byte aligned blocks
+static inline size_t ro2_bwd_smem_bytes(int C) {
+  return sizeof(float) * (size_t)(RO_HID * RO_IN + RO_G * RO_IN + 2 * RO_G * RB_P + RO_G * C);
+}
+
+__global__ void __launch_bounds__(256)
+k_readout2_bwd(const float* __restrict__ emb, const float* __restrict__ hid, const float* __restrict__ g_out,
+               const float* __restrict__ g_emb_extra, const float* __restrict__ W1, const float* __restrict__ W2,
+               int64_t B, int C, float slope, float* __restrict__ g_emb, float* __restrict__ partial) {
+  extern __shared__ __align__(16) float ro_smem[];
+  float* W1s = ro_smem;                    // [64][128]  (unit j, input k)
+  float* Es = W1s + RO_HID * RO_IN;        // [64][128]  (graph g, input k)
+  float* G = Es + RO_G * RO_IN;            // [64][68]   gpre1[g][j]
+  float* GT = G + RO_G * RB_P;             // [64][68]   gpre1[j][g]
+  float* Go = GT + RO_G * RB_P;            // [64][C]    g_out tile
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int64_t g0 = (int64_t)blockIdx.x * RO_G;
+  float* part = partial + (int64_t)blockIdx.x * ro2_partial_stride(C);
+
+  for (int idx = tid; idx < RO_HID * RO_IN / 4; idx += 256)
+    reinterpret_cast<float4*>(W1s)[idx] = ldg4(W1 + 4 * idx);
+  for (int idx = tid; idx < RO_G * RO_IN / 4; idx += 256) {
+    const int g = idx / (RO_IN / 4);
+    reinterpret_cast<float4*>(Es)[idx] = g0 + g < B ? ldg4(emb + g0 * RO_IN + 4 * (int64_t)idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int idx = tid; idx < RO_G * C; idx += 256) Go[idx] = g0 + idx / C < B ? g_out[g0 * C + idx] : 0.f;
+  __syncthreads();
+
+  // gpre1 (both orientations)
+  for (int idx = tid; idx < RO_G * RO_HID; idx += 256) {
+    const int g = idx >> 6, j = idx & 63;
+    float s = 0.f;
+    for (int c = 0; c < C; ++c) s = fmaf(Go[g * C + c], __ldg(W2 + c * RO_HID + j), s);
+    const float h = g0 + g < B ? hid[(g0 + g) * RO_HID + j] : 0.f;
+    s *= lrelu_grad_from_out(h, slope);
+    G[g * RB_P + j] = s;
+    GT[j * RB_P + g] = s;
+  }
+  __syncthreads();
+
+  // small gradients: gb1[j], gW2[c][j], gb2[c]
+  if (tid < RO_HID) {
+    float s = 0.f;
+    for (int g = 0; g < RO_G; ++g) s += G[g * RB_P + tid];
+    part[RO_HID * RO_IN + tid] = s;
+    for (int c = 0; c < C; ++c) {
+      float w = 0.f;
+      for (int g = 0; g < RO_G; ++g)
+        if (g0 + g < B) w = fmaf(Go[g * C + c], hid[(g0 + g) * RO_HID + tid], w);
+      part[RO_HID * RO_IN + RO_HID + c * RO_HID + tid] = w;
+    }
+  } else if (tid < RO_HID + C) {
+    const int c = tid - RO_HID;
+    float s = 0.f;
+    for (int g = 0; g < RO_G; ++g) s += Go[g * C + c];
+    part[RO_HID * RO_IN + RO_HID + C * RO_HID + c] = s;
+  }
+
+  // g_emb[g][k] = sum_j gpre1[g][j] W1[j][k]   ; thread: graphs 4 ty .. +4, inputs 8 tx .. +8
+  {
+    float acc[4][8];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 8; ++b) acc[a][b] = 0.f;
+#pragma unroll 4
+    for (int j = 0; j < RO_HID; ++j) {
+      const float4 a4 = *reinterpret_cast<const float4*>(GT + j * RB_P + 4 * ty);
+      const float4 w0 = *reinterpret_cast<const float4*>(W1s + j * RO_IN + 8 * tx);
+      const float4 w1 = *reinterpret_cast<const float4*>(W1s + j * RO_IN + 8 * tx + 4);
+      const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+      const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 8; ++b) acc[a][b] = fmaf(av[a], wv[b], acc[a][b]);
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      const int64_t g = g0 + 4 * ty + a;
+      if (g >= B) continue;
+      float* dst = g_emb + g * RO_IN + 8 * tx;
+      float4 o0 = make_float4(acc[a][0], acc[a][1], acc[a][2], acc[a][3]);
+      float4 o1 = make_float4(acc[a][4], acc[a][5], acc[a][6], acc[a][7]);
+      if (g_emb_extra) {
+        const float4 e0 = ldg4(g_emb_extra + g * RO_IN + 8 * tx), e1 = ldg4(g_emb_extra + g * RO_IN + 8 * tx + 4);
+        o0.x += e0.x; o0.y += e0.y; o0.z += e0.z; o0.w += e0.w;
+        o1.x += e1.x; o1.y += e1.y; o1.z += e1.z; o1.w += e1.w;
+      }
+      *reinterpret_cast<float4*>(dst) = o0;
+      *reinterpret_cast<float4*>(dst + 4) = o1;
+    }
+  }
+  // gW1[j][k] = sum_g gpre1[g][j] emb[g][k]     ; thread: units 4 ty .. +4, inputs 8 tx .. +8
+  {
+    float acc[4][8];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 8; ++b) acc[a][b] = 0.f;
+#pragma unroll 4
+    for (int g = 0; g < RO_G; ++g) {
+      const float4 a4 = *reinterpret_cast<const float4*>(G + g * RB_P + 4 * ty);
+      const float4 e0 = *reinterpret_cast<const float4*>(Es + g * RO_IN + 8 * tx);
+      const float4 e1 = *reinterpret_cast<const float4*>(Es + g * RO_IN + 8 * tx + 4);
+      const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+      const float ev[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 8; ++b) acc[a][b] = fmaf(av[a], ev[b], acc[a][b]);
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      float* dst = part + (4 * ty + a) * RO_IN + 8 * tx;
+      *reinterpret_cast<float4*>(dst) = make_float4(acc[a][0], acc[a][1], acc[a][2], acc[a][3]);
+      *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[a][4], acc[a][5], acc[a][6], acc[a][7]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_readout2_bwd_reduce(const float* __restrict__ partial, int blocks, int C, float* __restrict__ gW1, float* __restrict__ gb1,
+                      float* __restrict__ gW2, float* __restrict__ gb2) {
+  const int pe = ro2_partial_stride(C);
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= ro2_partial_elems(C)) return;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  int k = 0;
+  for (; k + 4 <= blocks; k += 4) {
+    s0 += partial[(int64_t)k * pe + e];
+    s1 += partial[(int64_t)(k + 1) * pe + e];
+    s2 += partial[(int64_t)(k + 2) * pe + e];
+    s3 += partial[(int64_t)(k + 3) * pe + e];
+  }
+  for (; k < blocks; ++k) s0 += partial[(int64_t)k * pe + e];
+  const float v = (s0 + s1) + (s2 + s3);
+  const int n1 = RO_HID * RO_IN;
+  if (e < n1) gW1[e] = v;
+  else if (e < n1 + RO_HID) gb1[e - n1] = v;
+  else if (e < n1 + RO_HID + C * RO_HID) gW2[e - n1 - RO_HID] = v;
+  else gb2[e - n1 - RO_HID - C * RO_HID] = v;
+}
+
 // Backward of pooling fused with the LeakyReLU derivative of the last conv layer:
 //   gA[i][c] = ( g_mean[g][c] / n_g + [h[i][c] == max] · g_max[g][c] / ties ) · lrelu'(h[i][c])
 // Ties share the gradient evenly, as torch's scatter_reduce(amax) backward does.
@@ -533,6 +688,7 @@ static FwdWs carve_fwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
 struct BwdWs {
   float *gA, *gT, *partial, *gz[2], *gemb;
   float *fpartial, *fscratch;  // graph-resident backward: per-CTA partials, oversize-graph scratch
+  float *ropartial;            // fused readout backward: per-block partials
   size_t bytes;
 };
 
@@ -572,6 +728,8 @@ static BwdWs carve_bwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
   w.gz[0] = c.take<float>((size_t)B * max_ro_dim(p) + 4);
   w.gz[1] = c.take<float>((size_t)B * max_ro_dim(p) + 4);
   w.gemb = c.take<float>((size_t)B * 2 * p->H + 4);
+  if (p->R == 2 && 2 * p->H == RO_IN && p->C <= 16 && B > 0)
+    w.ropartial = c.take<float>((size_t)cdiv(B, RO_G) * ro2_partial_stride(p->C) + 4);
   w.bytes = c.off;
   return w;
 }
@@ -718,7 +876,23 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
 
   // ---- readout MLP backward -------------------------------------------------------------
   const float* gemb_total = g_emb;
-  if (g_out) {
+  if (g_out && w.ropartial != nullptr && config_get(HCG_CFG_BACKWARD_PATH) != 1) {
+    // default head (128 -> 64 -> C): one kernel + one reduce
+    const size_t smem = ro2_bwd_smem_bytes(p->C);
+    static thread_local size_t configured = 0;
+    if (smem > configured) {
+      HCG_CUDA_OK(cudaFuncSetAttribute(k_readout2_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      configured = smem;
+    }
+    const int blocks = (int)cdiv(B, RO_G);
+    k_readout2_bwd<<<blocks, 256, smem, st>>>(emb, saved->hid[0], g_out, g_emb, p->ro_w[0], p->ro_w[1], B, p->C, p->slope,
+                                             w.gemb, w.ropartial);
+    HCG_LAUNCH_OK(st, "k_readout2_bwd");
+    k_readout2_bwd_reduce<<<(unsigned)cdiv(ro2_partial_elems(p->C), 256), 256, 0, st>>>(
+        w.ropartial, blocks, p->C, grads->ro_w[0], grads->ro_b[0], grads->ro_w[1], grads->ro_b[1]);
+    HCG_LAUNCH_OK(st, "k_readout2_bwd_reduce");
+    gemb_total = w.gemb;
+  } else if (g_out) {
     const float* gz = g_out;  // gradient w.r.t. the (post-activation) output of layer k
     int pp = 0;
     for (int k = p->R - 1; k >= 0; --k) {

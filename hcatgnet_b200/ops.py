@@ -267,8 +267,10 @@ def forward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, save: b
     return out, emb, saved_t
 
 
-def backward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, saved_t, emb, g_out, g_emb, need_gx: bool):
-    """One ``hcg_gcn_backward`` call.  Returns (g_x or None, list of parameter grads)."""
+def backward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, saved_t, emb, g_out, g_emb, need_gx: bool,
+                 flat_out: torch.Tensor | None = None):
+    """One ``hcg_gcn_backward`` call.  Returns (g_x or None, list of parameter grads).
+    ``flat_out``: an existing fp32 slab (>= sum of parameter sizes) to write the gradients into."""
     lib = _lib.load()
     device = plan.device
     f32 = dict(dtype=torch.float32, device=device)
@@ -282,7 +284,7 @@ def backward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, saved_
             saved_c.hid[k] = h.data_ptr()
         # one flat slab for all parameter gradients (a single all-reduce buffer for data parallelism)
         sizes = [p.numel() for p in params]
-        flat = torch.empty(sum(sizes), **f32)
+        flat = flat_out if flat_out is not None else torch.empty(sum(sizes), **f32)
         grads, off = [], 0
         for p_, n in zip(params, sizes):
             grads.append(flat[off:off + n].view_as(p_))

@@ -1,0 +1,90 @@
+"""Device-resident training step — the body of the reference's ``train_network``
+(reference utils/utils_model.py:55-70: zero_grad, forward, ``sqrt(MSELoss)``, backward,
+``optimizer.step()``) as six asynchronous C-ABI calls and no autograd graph:
+
+    hcg_collate -> hcg_gcn_forward -> hcg_rmse_seed -> hcg_gcn_backward -> [all-reduce] -> hcg_adam_step
+
+The parameters of the module are re-pointed at views of ONE flat fp32 slab (``state_dict`` keys, shapes
+and order are unchanged), the gradients land in one flat slab whose two tail slots carry
+``(sum of squared errors, count)``; with several ranks that slab is the single NCCL all-reduce of the
+step, and the ``1 / (2 count rmse)`` factor of ``d sqrt(MSE)`` is applied inside the Adam kernel, so
+every rank takes exactly the single-device step on the concatenated batch.
+Nothing here synchronises with the host: the returned loss is a 0-dim device tensor.
+
+Learning rate, betas and eps are read from ``model.optimizer.param_groups[0]`` at every step, so the
+reference's schedulers (``model.scheduler.step(val_loss)``, reference scripts_experiments/train_GNN.py:88)
+keep working on the module's own optimizer object; its moment buffers live here.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import _lib, ops
+
+
+class FusedTrainer:
+    def __init__(self, model, group=None, validate: bool = False):
+        if not isinstance(model.optimizer, torch.optim.Adam):
+            raise NotImplementedError("FusedTrainer implements the reference's default optimizer (Adam) only; "
+                                      "use parallel.dp_train_step for SGD / RMSprop")
+        pg = model.optimizer.param_groups[0]
+        if pg.get("weight_decay", 0) != 0 or pg.get("amsgrad", False) or pg.get("maximize", False):
+            raise NotImplementedError("FusedTrainer: Adam with weight_decay / amsgrad / maximize is not implemented")
+        if getattr(model.loss, "__class__", None) is not torch.nn.MSELoss:
+            raise NotImplementedError("FusedTrainer implements the regression loss sqrt(MSELoss) only")
+        self.model, self.group, self.validate = model, group, bool(validate)
+        self.params = model._flat_params()
+        dev = self.params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("FusedTrainer: move the model to a CUDA device first (there is no CPU path)")
+        self.device, self.dims = dev, model._dims()
+        sizes = [p.numel() for p in self.params]
+        self.n = sum(sizes)
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.flat = torch.empty(self.n, **f32)
+        off = 0
+        with torch.no_grad():
+            for p, k in zip(self.params, sizes):
+                self.flat[off:off + k].copy_(p.detach().reshape(-1))
+                p.data = self.flat[off:off + k].view(p.shape)   # same Parameter objects, storage = the slab
+                off += k
+        self.grad = torch.zeros(self.n + 2, **f32)              # [gradients | sse | count]
+        self.exp_avg = torch.zeros(self.n, **f32)
+        self.exp_avg_sq = torch.zeros(self.n, **f32)
+        self.losses = torch.zeros(16, **f32)                    # ring of loss slots: a returned loss stays valid for 15 more steps
+        self.steps = 0
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+
+    def step(self, batch) -> torch.Tensor:
+        """One optimisation step on ``batch`` (a device ``Batch``); returns the global RMSE (device scalar)."""
+        m, dev, dims = self.model, self.device, self.dims
+        lib = _lib.load()
+        x = ops.to_device(batch.x, dev, torch.float32)
+        y = ops.to_device(batch.y, dev, torch.float32)
+        B = int(batch.num_graphs)
+        plan = ops.cached_collate(batch, batch.edge_index, batch.batch, x.shape[0], B, dev, transpose=True,
+                                  validate=self.validate, max_graph_nodes=int(getattr(batch, "max_graph_nodes", 0) or 0),
+                                  grouped=getattr(batch, "edges_grouped", None))
+        params = [p.data for p in self.params]
+        out, emb, saved = ops.forward_raw(plan, x, dims, params, save=True)
+        with torch.cuda.device(dev):
+            st = torch.cuda.current_stream(dev).cuda_stream
+            g_out = torch.empty_like(out)
+            tail = self.grad[self.n:]
+            _lib.check(lib.hcg_rmse_seed(out.data_ptr(), y.data_ptr(), B, dims.C, g_out.data_ptr(), tail.data_ptr(), st))
+            ops.backward_raw(plan, x, dims, params, saved, emb, g_out, None, need_gx=False, flat_out=self.grad)
+            if self.world > 1:
+                dist.all_reduce(self.grad, op=dist.ReduceOp.SUM, group=self.group)
+            pg = m.optimizer.param_groups[0]
+            b1, b2 = pg["betas"]
+            self.steps += 1
+            loss = self.losses[self.steps % 16]
+            _lib.check(lib.hcg_adam_step(self.flat.data_ptr(), self.grad.data_ptr(), self.exp_avg.data_ptr(),
+                                         self.exp_avg_sq.data_ptr(), self.n, tail.data_ptr(), float(pg["lr"]), float(b1),
+                                         float(b2), float(pg["eps"]), self.steps, loss.data_ptr(), st))
+        return loss
+
+    def checksum(self) -> torch.Tensor:
+        """Sum of the parameter slab (replicas of a data-parallel job must agree bit for bit)."""
+        return self.flat.double().sum()

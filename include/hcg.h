@@ -228,6 +228,28 @@ int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgParams* p, cons
                      const HcgGrads* grads, float* g_x,
                      void* ws, size_t ws_bytes, void* stream);
 
+/* ---- training step around forward/backward (replaces the loss / optimizer lines of the reference's
+ *      train loop, utils/utils_model.py:64-66, and torch.optim.Adam of model/networks.py:36-44) ------ */
+
+/*
+ * Seeds the backward pass of loss = sqrt(MSELoss(out, y.unsqueeze(1))) in its shard-additive form:
+ * g_out[B,C] = 2 (out - y)  and  tail[0] = sum (out - y)^2, tail[1] = B*C.   y: [B] (broadcast over C).
+ * The 1 / (2 count rmse) factor of d sqrt(sse/count) is applied by hcg_adam_step after the (optional)
+ * all-reduce of gradient slab + tail, so data-parallel ranks take exactly the single-device step on the
+ * concatenated batch.
+ */
+int hcg_rmse_seed(const float* out, const float* y, int64_t B, int C, float* g_out, float* tail, void* stream);
+
+/*
+ * One Adam step (torch.optim.Adam semantics: amsgrad off, weight_decay 0) over a flat parameter slab.
+ * tail: NULL, or the [sse, count] pair written by hcg_rmse_seed (summed over ranks): the gradient is then
+ * scaled by 1 / (2 count sqrt(sse / count)) and the RMSE is written to loss_out (may be NULL).
+ * step: 1-based step number (bias correction).
+ */
+int hcg_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n,
+                  const float* tail, float lr, float beta1, float beta2, float eps, int64_t step,
+                  float* loss_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -121,3 +121,47 @@ def test_predict_stream_matches_blocking_forward():
         assert torch.equal(o, o2.cpu()) and torch.equal(e, e2.cpu())
     yp, yt, idx, emb = pkg.predict_network_stream(model, host, return_emb=True)
     assert yp.shape == (sum(h.num_graphs for h in host),) and emb.shape[1] == 128 and yt.shape == yp.shape
+
+
+def test_fused_trainer_tracks_oracle_and_autograd_path(pkg):
+    """FusedTrainer.step (collate, forward, rmse seed, backward, Adam kernel; no autograd) against the
+    plain-torch oracle + torch.optim.Adam, and against this package's own autograd path."""
+    graphs = golden_io.load_graphs("rhcaa_learning")[:120]
+    opt = pkg.default_options()
+    model = pkg.make_network("GCN", opt, 25).to("cuda")
+    twin = pkg.make_network("GCN", opt, 25).to("cuda")
+    twin.load_state_dict(model.state_dict())
+    sd0 = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+    keys = list(sd0.keys())
+    ref = {k: v.clone().requires_grad_(True) for k, v in sd0.items()}
+    ref_opt = torch.optim.Adam(list(ref.values()), lr=opt.lr, eps=1e-9)
+    trainer = pkg.FusedTrainer(model)
+    assert list(model.state_dict().keys()) == keys          # flattening keeps the state_dict layout
+    model.train(); twin.train()
+    for epoch in range(2):
+        for batch in _batches(pkg, graphs):
+            batch = batch.to("cuda")
+            loss = trainer.step(batch)
+            twin.optimizer.zero_grad()
+            l_twin = torch.sqrt(twin.loss(twin(batch), torch.unsqueeze(batch.y, dim=1)))
+            l_twin.backward()
+            twin.optimizer.step()
+            b = batch.to("cpu")
+            ref_opt.zero_grad()
+            o_ref, _ = ref_gcn.forward(ref, b.x, b.edge_index, b.batch, b.num_graphs)
+            l_ref = ref_gcn.rmse_loss(o_ref, b.y)
+            l_ref.backward()
+            ref_opt.step()
+            assert abs(loss.item() - l_ref.item()) <= 2e-3 * max(1.0, abs(l_ref.item()))
+            assert abs(loss.item() - l_twin.item()) <= 2e-3 * max(1.0, abs(l_twin.item()))
+    for k, v in model.state_dict().items():
+        assert torch.allclose(v.cpu(), ref[k].detach(), rtol=0, atol=5e-3), k
+        assert torch.allclose(v, twin.state_dict()[k], rtol=0, atol=5e-3), k
+    # a scheduler acting on the module's optimizer object changes the trainer's learning rate
+    model.optimizer.param_groups[0]["lr"] = 0.0
+    before = trainer.flat.clone()
+    trainer.step(_batches(pkg, graphs)[0].to("cuda"))
+    assert torch.equal(before, trainer.flat)
+    # state_dict round trip keeps the parameters inside the slab
+    model.load_state_dict({k: v.cuda() for k, v in sd0.items()})
+    assert torch.allclose(trainer.flat[:64 * 25].view(64, 25).cpu(), sd0["conv1.lin.weight"])
