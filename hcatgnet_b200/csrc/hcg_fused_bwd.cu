@@ -81,7 +81,7 @@ __device__ __forceinline__ void agg_rows(const float* __restrict__ src, float* _
         const bool ok = (unsigned)j < (unsigned)n;  // an edge leaving its graph: skipped (cannot come out of PyG collate)
         if (!ok) j = i;
         const float w = ok ? ds[j] * di : 0.f;
-        const float4 v = *reinterpret_cast<const float4*>(src + j * 64 + (c0 ^ swz(j)));
+        const float4 v = *reinterpret_cast<const float4*>(src + (((j << 6) | swz(j)) ^ c0));
         acc.x = fmaf(w, v.x, acc.x); acc.y = fmaf(w, v.y, acc.y); acc.z = fmaf(w, v.z, acc.z); acc.w = fmaf(w, v.w, acc.w);
       }
       const float ws = (di * fill) * di;
@@ -102,20 +102,30 @@ __device__ __forceinline__ void xty_tiles(const float* __restrict__ Q, const flo
   for (int j = 0; j < NT; ++j)
 #pragma unroll
     for (int q = 0; q < 4; ++q) d[j][q] = 0.f;
-  const int oc = 16 * mt + g8;
+  // fragment rows are r0 + t4 (swizzle t4 << 3) and r0 + t4 + 4 (swizzle (t4 << 3) | 4) with r0 a multiple of 8:
+  // every offset is a per-thread constant plus r0 * 64
+  const int s0 = t4 << 3, s1 = s0 | 4, oc = 16 * mt + g8;
+  const float* qa = Q + t4 * 64 + (oc ^ s0);
+  const float* qb = Q + t4 * 64 + ((oc + 8) ^ s0);
+  const float* qc = Q + (t4 + 4) * 64 + (oc ^ s1);
+  const float* qd = Q + (t4 + 4) * 64 + ((oc + 8) ^ s1);
+  const float* yr0 = Y + t4 * 64;
+  const float* yr1 = Y + (t4 + 4) * 64;
+  int off[NT];
+#pragma unroll
+  for (int j = 0; j < NT; ++j) off[j] = (8 * (nb + j) + g8) ^ s0;  // column of tile j in row r0 + t4; row + 4: ^ 4
   for (int r0 = 0; r0 < npad; r0 += 8) {
-    const int ra = r0 + t4, rb = ra + 4;
+    const int o = r0 * 64;
     uint32_t ah[4], al[4];
-    split_tf32(Q[at(ra, oc)], ah[0], al[0]);
-    split_tf32(Q[at(ra, oc + 8)], ah[1], al[1]);
-    split_tf32(Q[at(rb, oc)], ah[2], al[2]);
-    split_tf32(Q[at(rb, oc + 8)], ah[3], al[3]);
+    split_tf32(qa[o], ah[0], al[0]);
+    split_tf32(qb[o], ah[1], al[1]);
+    split_tf32(qc[o], ah[2], al[2]);
+    split_tf32(qd[o], ah[3], al[3]);
 #pragma unroll
     for (int j = 0; j < NT; ++j) {
-      const int ic = 8 * (nb + j) + g8;
       uint32_t bh0, bl0, bh1, bl1;
-      split_tf32(Y[at(ra, ic)], bh0, bl0);
-      split_tf32(Y[at(rb, ic)], bh1, bl1);
+      split_tf32(yr0[o + off[j]], bh0, bl0);
+      split_tf32(yr1[o + (off[j] ^ 4)], bh1, bl1);
       mma_split(d[j], ah, al, bh0, bh1, bl0, bl1);
     }
   }
@@ -187,17 +197,22 @@ __device__ __forceinline__ void bwd_graph(const FusedBwdArgs& a, BwdState& s, fl
   {
     const int i0 = 8 * warp;
     const int mtiles = (n + 15) >> 4;
+    // element (16 mt + g8 (+8), 8 ks + t4 (+4)) sits at row * 64 + ((8 ks) ^ v), v = t4 ^ swz(g8) (^ 4):
+    // with ks = j + 4 h that is (v ^ 8 j) + 32 h — four per-thread constants and immediates
+    const int v0 = t4 ^ swz(g8), v1 = v0 ^ 4;
     for (int mt = 0; mt < mtiles; ++mt) {
       const int ra = 16 * mt + g8, rb = ra + 8;
+      const float* qrow = Q + ra * 64;
       float d[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int ks = 0; ks < 8; ++ks) {
-        const int ko = 8 * ks + t4;
+        const float* pa = qrow + (v0 ^ (8 * (ks & 3))) + 32 * (ks >> 2);
+        const float* pb = qrow + (v1 ^ (8 * (ks & 3))) + 32 * (ks >> 2);
         uint32_t ah[4], al[4], bh0, bl0, bh1, bl1;
-        split_tf32(Q[at(ra, ko)], ah[0], al[0]);
-        split_tf32(Q[at(rb, ko)], ah[1], al[1]);
-        split_tf32(Q[at(ra, ko + 4)], ah[2], al[2]);
-        split_tf32(Q[at(rb, ko + 4)], ah[3], al[3]);
+        split_tf32(pa[0], ah[0], al[0]);
+        split_tf32(pa[512], ah[1], al[1]);
+        split_tf32(pb[0], ah[2], al[2]);
+        split_tf32(pb[512], ah[3], al[3]);
         split_tf32(s.wreg[ks][0], bh0, bl0);
         split_tf32(s.wreg[ks][1], bh1, bl1);
         mma_split(d, ah, al, bh0, bh1, bl0, bl1);

@@ -119,3 +119,53 @@ def predict_network_stream(model, loader: Iterable[Batch], return_emb: bool = Fa
     if return_emb:
         return cat(y_pred), cat(y_true), cat(idx), cat(embs)
     return cat(y_pred), cat(y_true), cat(idx)
+
+
+def predict_ensemble_stream(models, batches: Iterable[Batch], device=None, depth: int = 2, validate: bool = False):
+    """Ensemble screening — the intended ``scripts_experiments/predict.py`` (reference :11-60, dead code
+    there): every model of ``models`` (e.g. the 90 ``model_params.pth`` of a nested cross-validation,
+    reference scripts_experiments/train_GNN.py:48-137) is run over every batch of the stream.
+
+    A batch crosses PCIe ONCE and is collated ONCE (the topology plan is shared by all models); only the
+    network kernel runs per model, so the screen is bound by the device, not by the host link.
+    Yields ``(pred[M, B, C], mean[B, C], std[B, C], host_batch)`` per batch as pinned HOST tensors
+    (``std`` is the population standard deviation over the ensemble)."""
+    models = list(models)
+    if not models:
+        raise ValueError("predict_ensemble_stream needs at least one model")
+    dims0 = models[0]._dims()
+    for m in models[1:]:
+        if m._dims() != dims0:
+            raise ValueError("all models of an ensemble must share one architecture")
+    dev = torch.device(device) if device is not None else ops._require_cuda()
+    params = [[ops.to_device(p.detach(), dev, torch.float32) for p in m._flat_params()] for m in models]
+    pending: deque = deque()
+
+    def finish(item):
+        p_h, m_h, s_h, h, ev, _keep = item
+        ev.synchronize()
+        return p_h, m_h, s_h, h
+
+    with torch.no_grad():
+        for d in DevicePrefetcher(batches, device=dev, depth=depth):
+            plan = ops.cached_collate(d, d.edge_index, d.batch, d.x.shape[0], d.num_graphs, dev, transpose=False,
+                                      validate=validate, max_graph_nodes=int(getattr(d, "max_graph_nodes", 0) or 0),
+                                      grouped=getattr(d, "edges_grouped", None))
+            x = ops.to_device(d.x, dev, torch.float32)
+            pred = torch.empty(len(models), d.num_graphs, dims0.C, dtype=torch.float32, device=dev)
+            for k, ps in enumerate(params):
+                out, _, _ = ops.forward_raw(plan, x, dims0, ps, save=False)
+                pred[k].copy_(out)
+            mean, std = pred.mean(0), pred.std(0, unbiased=False)
+            hosts = []
+            for t in (pred, mean, std):
+                t_h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+                t_h.copy_(t, non_blocking=True)
+                hosts.append(t_h)
+            ev = torch.cuda.Event()
+            ev.record()
+            pending.append((*hosts, d._host, ev, (pred, mean, std, plan, x)))
+            if len(pending) > 1:
+                yield finish(pending.popleft())
+        while pending:
+            yield finish(pending.popleft())

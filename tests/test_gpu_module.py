@@ -165,3 +165,34 @@ def test_fused_trainer_tracks_oracle_and_autograd_path(pkg):
     # state_dict round trip keeps the parameters inside the slab
     model.load_state_dict({k: v.cuda() for k, v in sd0.items()})
     assert torch.allclose(trainer.flat[:64 * 25].view(64, 25).cpu(), sd0["conv1.lin.weight"])
+
+
+def test_predict_ensemble_stream_matches_per_model_golden(pkg):
+    """Three shipped RhCAA models over one stream of host batches: every model's predictions equal the
+    reference's own golden CSV rows, mean / std are those of the stack."""
+    models, golds = [], []
+    graphs = None
+    for outer, inner in [(1, 2), (8, 10), (10, 9)]:
+        sd, gs, _, pred_gold = golden_io.rows_with_graphs("learning", outer, inner)
+        m = pkg.make_network("GCN", pkg.default_options(), 25)
+        m.load_state_dict(sd, strict=True)
+        models.append(m.to("cuda").eval())
+        if graphs is None:
+            graphs = gs
+        golds.append((gs, pred_gold))
+    # the golden rows of each model cover different reactions (its own test folds): screen the union of the
+    # first model's graphs and compare model 0 to its golden rows, the others to the blocking forward
+    gs0, gold0 = golds[0]
+    loader = pkg.DataLoader(gs0, batch_size=37, shuffle=False)
+    preds, means, stds = [], [], []
+    for p, mean, std, h in pkg.predict_ensemble_stream(models, loader):
+        assert p.shape == (3, h.num_graphs, 1)
+        preds.append(p.clone()); means.append(mean.clone()); stds.append(std.clone())
+    pred = torch.cat(preds, 1)
+    assert np.abs(pred[0].numpy().ravel() - gold0).max() <= 2e-5
+    with torch.no_grad():
+        for k, m in enumerate(models):
+            ref = torch.cat([m(b.to("cuda")).cpu() for b in pkg.DataLoader(gs0, batch_size=37, shuffle=False)], 0)
+            assert torch.equal(ref, pred[k])      # same kernels, same batches: identical bits
+    assert torch.allclose(torch.cat(means, 0), pred.mean(0), atol=1e-6)
+    assert torch.allclose(torch.cat(stds, 0), pred.std(0, unbiased=False), atol=1e-6)
