@@ -100,10 +100,25 @@ k_gemm(const float* __restrict__ A, const float* __restrict__ Bm, float* __restr
   }
 }
 
+// hcg_tcgemm.cu: the same product on the tensor cores (split-TF32 tcgen05.mma), Nc in {64,128,192,256}
+size_t tc_gemm_image_floats(int K, int Nc);
+bool tc_gemm_applicable(int64_t M, int K, int Nc);
+int launch_tc_gemm(const float* A, const float* W, float* C, int64_t M, int K, int Nc, bool transposed, int epi,
+                   const float* aux, float slope, float* img, cudaStream_t st);
+
+// wimg: scratch for the tensor-core path's operand image (NULL = fp32 FMA tiles only)
 template <bool B_T>
 static int launch_gemm(const float* A, const float* Bm, float* C, int64_t M, int K, int Nc, int epi,
-                       const float* aux, float slope, cudaStream_t st) {
+                       const float* aux, float slope, cudaStream_t st, float* wimg = nullptr) {
   if (M == 0 || Nc == 0) return HCG_OK;
+  {
+    // HCG_CFG_GEMM_PATH: 0 = tensor cores for wide layers on batches with enough row tiles, 1 = never, 2 = whenever applicable
+    const int gp = config_get(HCG_CFG_GEMM_PATH);
+    const bool shape_ok = wimg != nullptr && (epi == EPI_NONE || epi == EPI_MASK) && tc_gemm_applicable(M, K, Nc) &&
+                          (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (epi != EPI_MASK || (reinterpret_cast<uintptr_t>(aux) & 15) == 0);
+    if (shape_ok && (gp == 2 || (gp == 0 && Nc >= 128 && M >= 128 * 64)))
+      return launch_tc_gemm(A, Bm, C, M, K, Nc, !B_T, epi == EPI_MASK ? 1 : 0, aux, slope, wimg, st);
+  }
   dim3 grid((unsigned)cdiv(M, GM), (unsigned)cdiv(Nc, GN));
   switch (epi) {
     case EPI_NONE: k_gemm<B_T, EPI_NONE><<<grid, 256, 0, st>>>(A, Bm, C, M, K, Nc, aux, slope); break;
@@ -670,6 +685,7 @@ struct FwdWs {
   float* act[2];
   float* hid[HCG_MAX_READOUT];
   char* tc;
+  float* wimg;  // operand image of the tensor-core GEMM (layer-wise path, wide layers)
   size_t bytes;
 };
 
@@ -681,6 +697,7 @@ static FwdWs carve_fwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
   w.act[1] = c.take<float>((size_t)N * p->H + 4);
   for (int k = 0; k < p->R - 1; ++k) w.hid[k] = c.take<float>((size_t)B * ro_out_dim(p, k) + 4);
   w.tc = c.take<char>(tc_fwd_workspace_bytes(B));
+  if (p->H % 64 == 0 && p->H <= 256) w.wimg = c.take<float>(tc_gemm_image_floats(p->F > p->H ? p->F : p->H, p->H) + 4);
   w.bytes = c.off;
   return w;
 }
@@ -689,6 +706,7 @@ struct BwdWs {
   float *gA, *gT, *partial, *gz[2], *gemb;
   float *fpartial, *fscratch;  // graph-resident backward: per-CTA partials, oversize-graph scratch
   float *ropartial;            // fused readout backward: per-block partials
+  float *wimg;                 // operand image of the tensor-core GEMM
   size_t bytes;
 };
 
@@ -728,6 +746,7 @@ static BwdWs carve_bwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
   w.gz[0] = c.take<float>((size_t)B * max_ro_dim(p) + 4);
   w.gz[1] = c.take<float>((size_t)B * max_ro_dim(p) + 4);
   w.gemb = c.take<float>((size_t)B * 2 * p->H + 4);
+  if (p->H % 64 == 0 && p->H <= 256) w.wimg = c.take<float>(tc_gemm_image_floats(p->H, p->H) + 4);
   if (p->R == 2 && 2 * p->H == RO_IN && p->C <= 16 && B > 0)
     w.ropartial = c.take<float>((size_t)cdiv(B, RO_G) * ro2_partial_stride(p->C) + 4);
   w.bytes = c.off;
@@ -816,7 +835,7 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
   int k_in = p->F;
   float* h_out = nullptr;
   for (int l = 0; l < p->L && !fused_done; ++l) {
-    rc = launch_gemm<true>(h_in, p->conv_w[l], w.T, N, k_in, H, EPI_NONE, nullptr, p->slope, st);
+    rc = launch_gemm<true>(h_in, p->conv_w[l], w.T, N, k_in, H, EPI_NONE, nullptr, p->slope, st, w.wimg);
     if (rc) return rc;
     h_out = saved ? saved->acts[l] : w.act[l & 1];
     HCG_REQUIRE(h_out != nullptr, HCG_ERR_INVALID_ARG, "saved->acts[%d] is NULL", l);
@@ -971,7 +990,7 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
     rc = launch_xty(w.gT, h_in, N, H, k_in, w.partial, grads->conv_w[l], st);
     if (rc) return rc;
     if (l > 0) {
-      rc = launch_gemm<false>(w.gT, p->conv_w[l], w.gA, N, H, k_in, EPI_MASK, saved->acts[l - 1], p->slope, st);
+      rc = launch_gemm<false>(w.gT, p->conv_w[l], w.gA, N, H, k_in, EPI_MASK, saved->acts[l - 1], p->slope, st, w.wimg);
       if (rc) return rc;
     } else if (g_x) {
       rc = launch_gemm<false>(w.gT, p->conv_w[0], g_x, N, H, k_in, EPI_NONE, nullptr, p->slope, st);

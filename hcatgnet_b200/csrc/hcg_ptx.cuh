@@ -42,6 +42,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity, ui
 // suspended polls and surfaces as a CUDA error instead of hanging the device.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
+  if (mbar_try_wait(bar, parity, 0u)) return;  // the common case for a prefetched stage: already complete
   while (!mbar_try_wait(bar, parity, 1000u)) {
     if (++spins > (1u << 24)) __trap();
   }

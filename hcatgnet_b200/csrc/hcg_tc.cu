@@ -269,6 +269,9 @@ k_tc_fwd(const TcArgs a) {
   // the warp of each slot whose quadrant is filled last does the waiting and the MMA issue for the slot
   const bool ctl_warp = (gt >> 5) == (slot == 0 ? 3 : 0);
   const int lane = tid & 31;
+  // the control warp's first lane also feeds the slot: it issues the next graph's bulk copies while the
+  // layer-0 MMAs run (it would only be polling their mbarrier), off the other warps' critical path
+  const bool pf_thread = ctl_warp && lane == 0;
   const int F = a.f.F, L = a.f.L;
 
   // ---- carve shared memory (pointer arithmetic on the shared array only: keeps the address space) --
@@ -321,7 +324,7 @@ k_tc_fwd(const TcArgs a) {
   const int64_t first = (int64_t)blockIdx.x * kTcSlots + slot;
   const int64_t stride = (int64_t)gridDim.x * kTcSlots;
   int4 d_next = make_int4(0, 0, 0, -1);
-  if (gt == 0 && first < a.f.B) {
+  if (pf_thread && first < a.f.B) {
     tc_prefetch(a, a.gdesc[first], stage_of(0), &metas[slot][0], &bar_stage[slot][0]);
     if (first + stride < a.f.B) d_next = a.gdesc[first + stride];
   }
@@ -329,15 +332,22 @@ k_tc_fwd(const TcArgs a) {
   int k = 0;
   for (int64_t gid = first; gid < a.f.B; gid += stride, ++k) {
     const int s = k & 1;
-    if (gt == 0 && gid + stride < a.f.B) {  // next graph -> the other stage (its readers finished last iteration)
-      tc_prefetch(a, d_next, stage_of(s ^ 1), &metas[slot][s ^ 1], &bar_stage[slot][s ^ 1]);
-      if (gid + 2 * stride < a.f.B) d_next = a.gdesc[gid + 2 * stride];
-    }
+    // next graph -> the other stage; its readers finished with the previous iteration.  Issued by pf_thread
+    // either right here (this graph is skipped) or after the layer-0 MMAs have been committed.
+    auto issue_next = [&]() {
+      if (gid + stride < a.f.B) {
+        tc_prefetch(a, d_next, stage_of(s ^ 1), &metas[slot][s ^ 1], &bar_stage[slot][s ^ 1]);
+        if (gid + 2 * stride < a.f.B) d_next = a.gdesc[gid + 2 * stride];
+      }
+    };
     TC_TICK(0);
     ptx::mbar_wait(&bar_stage[slot][s], (uint32_t)(k >> 1) & 1u);
     TC_TICK(1);
     const TcSlotMeta m = metas[slot][s];
-    if (m.skip == 1) continue;  // slot-uniform: this graph is on the overflow list
+    if (m.skip == 1) {  // slot-uniform: this graph is on the overflow list
+      if (pf_thread) issue_next();
+      continue;
+    }
     const int n = m.n, n0 = m.n0, e0 = m.e0;
     const TcStage st = stage_of(s);
     if (m.skip == 2) {  // flagged graph: fetch the four slices with ordinary loads
@@ -412,6 +422,7 @@ k_tc_fwd(const TcArgs a) {
           tc::issue_split_mma<8>(d_t, a_hi, a_lo, ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64),
                                  ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64));
         ptx::mma_commit(&bar_mma[slot]);
+        if (l == 0) issue_next();
        }
        __syncwarp();
        ptx::mbar_wait(&bar_mma[slot], mma_phase);  // one warp polls; the others sleep in the barrier below

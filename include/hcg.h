@@ -156,9 +156,12 @@ int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts, int cap);
  * HCG_CFG_BACKWARD_PATH: 0 = auto (the graph-resident backward kernel when H == 64, L == 2, F <= 32, no
  * edge weights, a disjoint molecule-like batch and no gradient w.r.t. x is wanted; layer-wise kernels
  * otherwise), 1 = force layer-wise, 2 = force graph-resident (HCG_ERR_UNSUPPORTED if not applicable).
+ * HCG_CFG_GEMM_PATH (dense X.W products of the layer-wise kernels): 0 = auto (split-TF32 tcgen05 kernel for
+ * output widths 128/192/256 on batches of >= 8192 rows, fp32 FMA tiles otherwise), 1 = FMA tiles only,
+ * 2 = the tensor-core kernel wherever its shape constraints hold (output width a multiple of 64, <= 256).
  * All are CUDA paths; there is no CPU path.  Returns the previous value, or -1 for a bad key.
  */
-enum { HCG_CFG_FORWARD_PATH = 0, HCG_CFG_BACKWARD_PATH = 1, HCG_CFG_COUNT_ = 2 };
+enum { HCG_CFG_FORWARD_PATH = 0, HCG_CFG_BACKWARD_PATH = 1, HCG_CFG_GEMM_PATH = 2, HCG_CFG_COUNT_ = 3 };
 int hcg_config_set(int key, int value);
 int hcg_config_get(int key);
 

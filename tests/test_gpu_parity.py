@@ -468,3 +468,47 @@ def test_graph_resident_backward_refuses_unsupported(hcg, backward_path):
     backward_path(2)
     with pytest.raises(RuntimeError):
         _cuda_grads(hcg, sd, b.x, b.edge_index, b.batch, b.num_graphs, b.y)
+
+
+# ------------------------------------------------------------------------------------------
+# the tensor-core dense product of the layer-wise path (wide hidden layers) against the oracle
+# ------------------------------------------------------------------------------------------
+@pytest.fixture
+def gemm_path(hcg):
+    from hcatgnet_b200 import _lib
+    prev = []
+
+    def set_path(v):
+        prev.append(_lib.config_set(_lib.HCG_CFG_GEMM_PATH, v))
+
+    yield set_path
+    if prev:
+        _lib.config_set(_lib.HCG_CFG_GEMM_PATH, prev[0])
+
+
+@pytest.mark.parametrize("H,L,F,B,nmax", [(256, 4, 25, 33, 50), (128, 2, 32, 700, 60), (192, 3, 7, 64, 40),
+                                          (64, 2, 40, 300, 120), (256, 2, 25, 1, 3)])
+def test_tensor_core_gemm_forward_backward(hcg, gemm_path, forward_path, backward_path, H, L, F, B, nmax):
+    """Layer-wise kernels with every X.W product (forward T = h W^T, backward g_in = gT W with the
+    LeakyReLU' mask) forced onto the split-TF32 tcgen05 GEMM: partial row tiles, K = F < 32, several
+    K chunks, 1..4 column tiles."""
+    from hcatgnet_b200.synth import synth_batch
+    b = synth_batch(B, n_features=F, seed=21, n_min=1, n_max=nmax)
+    sd = ref_gcn.init_state_dict(F, H, L, 2, 1, seed=9)
+    forward_path(1)
+    backward_path(1)
+    gemm_path(2)
+    params, _, _ = _sd_params(sd, "cuda")
+    plan = hcg.collate(b.edge_index.cuda(), b.batch.cuda(), b.num_nodes, b.num_graphs)
+    with torch.no_grad():
+        o, e = hcg.gcn_apply(b.x.cuda(), plan, _dims(hcg, sd), params)
+    o_ref, e_ref = ref_gcn.forward(sd, b.x, b.edge_index, b.batch, b.num_graphs)
+    assert _close(e.cpu(), e_ref) <= TOL and _close(o.cpu(), o_ref) <= TOL
+    args = (sd, b.x, b.edge_index, b.batch, b.num_graphs, b.y)
+    _, g_ref, _ = _oracle_grads(*args)
+    _, g_tc, _ = _cuda_grads(hcg, *args)
+    _assert_grads(g_tc, g_ref)
+    gemm_path(1)
+    with torch.no_grad():
+        o_fma, e_fma = hcg.gcn_apply(b.x.cuda(), plan, _dims(hcg, sd), params)
+    assert _close(e.cpu(), e_fma.cpu()) <= TOL and _close(o.cpu(), o_fma.cpu()) <= TOL
