@@ -11,15 +11,21 @@
 // TF32 hi + lo, D accumulates lo.hi + hi.lo + hi.hi in fp32 (fp32-grade accuracy; plain TF32 misses the
 // 1e-5 parity bound by two orders of magnitude).
 //
-//  * k_w_image turns W into the exact shared-memory image the MMA reads — per 32-wide K chunk and per
-//    64-row N tile a hi and a lo tile in the K-major / 128-byte-swizzle layout — once per call;
+//  * k_w_image turns W into the exact shared-memory image the MMA reads — per 32-wide K chunk a hi and a lo
+//    plane of all Nc rows in the K-major / 128-byte-swizzle layout — once per call;
 //  * k_tc_gemm: one persistent CTA of 128 threads per SM walks 128-row tiles.  Thread r owns row r: it
 //    loads the row's K chunk from global memory (one chunk ahead, in registers), splits it and stores it
-//    as lane r of the A operand in tensor memory (tcgen05.st); the W chunk image (up to 64 KB) arrives by
-//    ONE bulk async copy into a double-buffered shared-memory slot (cp.async.bulk -> mbarrier, issued two
-//    chunks ahead); one thread issues the Nc/64 x 12 tcgen05.mma of the chunk into the [128 x Nc] fp32
-//    accumulator in tensor memory and commits them to an mbarrier that frees the A operand and the W slot.
-//    Epilogue: tcgen05.ld of the accumulator row, optional LeakyReLU' mask, row store.
+//    as lane r of the A operand in tensor memory (tcgen05.st, double-buffered); the W chunk image (up to
+//    64 KB) arrives by ONE bulk async copy into one of three shared-memory slots (cp.async.bulk ->
+//    mbarrier, issued as soon as the slot's previous MMAs have completed); one thread issues the 12
+//    tcgen05.mma (M = 128, N = Nc, K = 8; three split terms x four K steps) of the chunk into the
+//    [128 x Nc] fp32 accumulator in tensor memory and commits them to the mbarrier that frees the A buffer
+//    and the W slot two chunks later.  Epilogue: tcgen05.ld of the accumulator row, optional LeakyReLU'
+//    mask, row store.
+// Measured (B200, N = 1.31 M rows, K = Nc = 256): 0.99 ms = 173 TFLOP/s fp32-equivalent, 3 x 173 = 520 TFLOP/s
+// on the TF32 pipe (fp32 FMA tiles: 3.96 ms).  Every 128-row tile streams the whole 512 KB hi|lo image of W
+// from L2 (5.3 TB/s across the chip): that, not the tensor pipe, is the bound; sharing W chunks across a
+// 2-CTA cluster by multicast is the next step.
 #include "hcg_common.cuh"
 #include "hcg_tc.cuh"
 
@@ -27,13 +33,11 @@ namespace hcg {
 
 constexpr int kGemmThreads = 128;
 constexpr int kGemmKC = 32;                      // K chunk
-constexpr int kGemmTile = 64 * kGemmKC;          // floats of one [64 x 32] operand tile
-constexpr int kGemmMaxNT = 4;                    // Nc <= 256
+constexpr int kGemmMaxNc = 256;                  // fp32 accumulator columns in tensor memory (+ 128 for the A operand)
 
-// ---- W -> per-chunk image: [kc][nt][hi | lo][64 x 32 swizzled] -------------------------------------------
+// ---- W -> per-chunk image: [kc][hi | lo][Nc x 32 swizzled] -----------------------------------------------
 __global__ void __launch_bounds__(256)
 k_w_image(const float* __restrict__ W, int Nc, int K, int transposed, int nkc, float* __restrict__ img) {
-  const int NT = Nc >> 6;
   const int Kpad = nkc * kGemmKC;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= Nc * Kpad) return;
@@ -41,16 +45,16 @@ k_w_image(const float* __restrict__ W, int Nc, int K, int transposed, int nkc, f
   float v = 0.f;
   if (k < K) v = transposed ? __ldg(W + (int64_t)k * Nc + n) : __ldg(W + (int64_t)n * K + k);
   const uint32_t hi = tc::tf32_hi(v), lo = tc::tf32_lo(v, hi);
-  const int kc = k >> 5, kk = k & 31, nt = n >> 6, nn = n & 63;
-  const int off = ((kc * NT + nt) * 2) * kGemmTile + tc::w_tile_offset(nn, kk);
+  const int kc = k >> 5, kk = k & 31;
+  const int off = kc * 2 * Nc * kGemmKC + tc::w_tile_offset(n, kk);  // 8-row groups 1024 bytes apart, all Nc rows in one plane
   img[off] = __uint_as_float(hi);
-  img[off + kGemmTile] = __uint_as_float(lo);
+  img[off + Nc * kGemmKC] = __uint_as_float(lo);
 }
 
-// one chunk's MMAs for one 64-column N tile: K = 32, accumulate on top of D unless `fresh`
+// one chunk's MMAs (M = 128, N = Nc, K = 32 in four steps of 8 per split term), accumulated on top of D unless `fresh`
 __device__ __forceinline__ void issue_chunk_mma(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi_smem, uint32_t b_lo_smem,
-                                                bool fresh) {
-  constexpr uint32_t idesc = ptx::make_idesc_tf32(tc::kRows, tc::kN);
+                                                bool fresh, int Nc) {
+  const uint32_t idesc = ptx::make_idesc_tf32(tc::kRows, Nc);
   const uint64_t bh = ptx::make_kmajor_sw128_desc(b_hi_smem), bl = ptx::make_kmajor_sw128_desc(b_lo_smem);
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
@@ -89,28 +93,27 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 k_tc_gemm(const float* __restrict__ A, const float* __restrict__ img, float* __restrict__ C, int64_t M, int K, int Nc,
           int nkc, const float* __restrict__ aux, float slope) {
   extern __shared__ __align__(1024) unsigned char gemm_smem[];
-  __shared__ uint64_t bar_w[2];
-  __shared__ uint64_t bar_mma;
+  __shared__ uint64_t bar_w[3];
+  __shared__ uint64_t bar_mma[2];
   __shared__ uint32_t tmem_base_s;
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int NT = Nc >> 6;
-  const uint32_t chunk_bytes = (uint32_t)NT * 2u * kGemmTile * 4u;
+  const uint32_t chunk_bytes = 2u * (uint32_t)Nc * kGemmKC * 4u;  // hi + lo plane of one K chunk
   unsigned char* base = gemm_smem + ((1024u - (ptx::smem_u32(gemm_smem) & 1023u)) & 1023u);
-  float* wbuf0 = reinterpret_cast<float*>(base);
-  float* wbuf1 = reinterpret_cast<float*>(base + chunk_bytes);
 
   if (warp == 0) ptx::tmem_alloc(&tmem_base_s, 512);
   if (tid == 0) {
     ptx::mbar_init(&bar_w[0], 1);
     ptx::mbar_init(&bar_w[1], 1);
-    ptx::mbar_init(&bar_mma, 1);
+    ptx::mbar_init(&bar_w[2], 1);
+    ptx::mbar_init(&bar_mma[0], 1);
+    ptx::mbar_init(&bar_mma[1], 1);
     ptx::fence_mbar_init();
   }
   ptx::tc_fence_before_sync();
   __syncthreads();
   ptx::tc_fence_after_sync();
   const uint32_t tbase = tmem_base_s;
-  const uint32_t d_t = tbase, a_hi = tbase + 256, a_lo = tbase + 288;
+  const uint32_t d_t = tbase;  // A operand of chunk g: columns 256 + 64 (g & 1): hi (32) | lo (32)
   const uint32_t trow = (uint32_t)(warp * 32) << 16;
   const bool vec4 = (K & 3) == 0 && (reinterpret_cast<uintptr_t>(A) & 15) == 0;
 
@@ -118,15 +121,14 @@ k_tc_gemm(const float* __restrict__ A, const float* __restrict__ img, float* __r
   const int64_t my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
   const int64_t total_chunks = my_tiles * nkc;
 
-  // W chunk g (image chunk g % nkc) -> slot g & 1
+  // W chunk g (image chunk g % nkc) -> slot g % 3
   auto copy_chunk = [&](int64_t g) {
-    const int b = (int)(g & 1);
+    const int b = (int)(g % 3);
     ptx::mbar_expect_tx(&bar_w[b], chunk_bytes);
-    ptx::bulk_g2s(b ? wbuf1 : wbuf0, img + (size_t)(g % nkc) * (chunk_bytes / 4), chunk_bytes, &bar_w[b]);
+    ptx::bulk_g2s(base + (size_t)b * chunk_bytes, img + (size_t)(g % nkc) * (chunk_bytes / 4), chunk_bytes, &bar_w[b]);
   };
   if (tid == 0) {
-    if (total_chunks > 0) copy_chunk(0);
-    if (total_chunks > 1) copy_chunk(1);
+    for (int64_t c = 0; c < 3 && c < total_chunks; ++c) copy_chunk(c);
   }
 
   int64_t g = 0;
@@ -136,9 +138,10 @@ k_tc_gemm(const float* __restrict__ A, const float* __restrict__ img, float* __r
     const int64_t row = tile * 128 + tid;
     const bool valid = row < M;
     for (int kc = 0; kc < nkc; ++kc, ++g) {
-      if (g > 0) {
-        // the previous chunk's MMAs are done: the A operand and W slot (g - 1) & 1 are free again
-        ptx::mbar_wait(&bar_mma, (uint32_t)((g - 1) & 1));
+      const uint32_t a_hi = tbase + 256 + 64 * (uint32_t)(g & 1), a_lo = a_hi + 32;
+      if (g >= 2) {
+        // the MMAs of chunk g - 2 are done: this A operand buffer and W slot (g + 1) % 3 are free again
+        ptx::mbar_wait(&bar_mma[g & 1], (uint32_t)(((g - 2) >> 1) & 1));
         if (tid == 0 && g + 1 < total_chunks) copy_chunk(g + 1);
       }
       ptx::tc_fence_after_sync();
@@ -163,16 +166,14 @@ k_tc_gemm(const float* __restrict__ A, const float* __restrict__ img, float* __r
       __syncthreads();
       if (tid == 0) {
         ptx::tc_fence_after_sync();
-        ptx::mbar_wait(&bar_w[g & 1], (uint32_t)((g >> 1) & 1));
-        const float* wb = (g & 1) ? wbuf1 : wbuf0;
-        for (int nt = 0; nt < NT; ++nt)
-          issue_chunk_mma(d_t + 64 * nt, a_hi, a_lo, ptx::smem_u32(wb + (size_t)nt * 2 * kGemmTile),
-                          ptx::smem_u32(wb + (size_t)nt * 2 * kGemmTile + kGemmTile), kc == 0);
-        ptx::mma_commit(&bar_mma);
+        ptx::mbar_wait(&bar_w[g % 3], (uint32_t)((g / 3) & 1));
+        const uint32_t wb = ptx::smem_u32(base + (size_t)(g % 3) * chunk_bytes);
+        issue_chunk_mma(d_t, a_hi, a_lo, wb, wb + chunk_bytes / 2, kc == 0, Nc);
+        ptx::mma_commit(&bar_mma[g & 1]);
       }
     }
     // ---- epilogue of the tile: accumulator row -> C ------------------------------------------------
-    ptx::mbar_wait(&bar_mma, (uint32_t)((g - 1) & 1));
+    ptx::mbar_wait(&bar_mma[(g - 1) & 1], (uint32_t)(((g - 1) >> 1) & 1));  // the last chunk's commit covers all before it
     ptx::tc_fence_after_sync();
     for (int c0 = 0; c0 < Nc; c0 += 16) {
       float r[16];
@@ -202,11 +203,11 @@ k_tc_gemm(const float* __restrict__ A, const float* __restrict__ img, float* __r
 
 size_t tc_gemm_image_floats(int K, int Nc) {
   const int nkc = (K + kGemmKC - 1) / kGemmKC;
-  return (size_t)nkc * (size_t)(Nc >> 6) * 2 * kGemmTile;
+  return (size_t)nkc * 2 * (size_t)Nc * kGemmKC;
 }
 
 bool tc_gemm_applicable(int64_t M, int K, int Nc) {
-  return M >= 1 && K >= 1 && Nc >= 64 && (Nc & 63) == 0 && Nc <= 64 * kGemmMaxNT && K <= 4096;
+  return M >= 1 && K >= 1 && Nc >= 64 && (Nc & 63) == 0 && Nc <= kGemmMaxNc && K <= 4096;
 }
 
 // C = A . B^T with the B operand taken from W as described at the top.  `img`: tc_gemm_image_floats(K, Nc)
@@ -221,7 +222,7 @@ int launch_tc_gemm(const float* A, const float* W, float* C, int64_t M, int K, i
   const int nkc = (K + kGemmKC - 1) / kGemmKC;
   k_w_image<<<(unsigned)cdiv((int64_t)Nc * nkc * kGemmKC, 256), 256, 0, st>>>(W, Nc, K, transposed ? 1 : 0, nkc, img);
   HCG_LAUNCH_OK(st, "k_w_image");
-  const size_t smem = 2 * (size_t)(Nc >> 6) * 2 * kGemmTile * 4 + 1024;
+  const size_t smem = 3 * 2 * (size_t)Nc * kGemmKC * 4 + 1024;
   static thread_local size_t configured[2] = {0, 0};
   const int e = epi == TCG_EPI_MASK ? 1 : 0;
   if (smem > configured[e]) {
