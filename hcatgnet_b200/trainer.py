@@ -88,3 +88,67 @@ class FusedTrainer:
     def checksum(self) -> torch.Tensor:
         """Sum of the parameter slab (replicas of a data-parallel job must agree bit for bit)."""
         return self.flat.double().sum()
+
+    # ---- the reference's epoch functions, with the per-batch .item() syncs replaced by device sums ----------
+    def train_network(self, train_loader, device=None) -> float:
+        """reference utils/utils_model.py:55-70: one epoch; returns sum(loss_b * num_graphs_b) / len(dataset).
+        The per-batch RMSE values are accumulated on the device; the host reads one number per epoch."""
+        dev = self.device if device is None else torch.device(device)
+        self.model.train()
+        acc = torch.zeros((), dtype=torch.float32, device=self.device)
+        n = 0
+        for batch in train_loader:
+            batch = batch.to(dev)
+            acc += self.step(batch) * float(batch.num_graphs)
+            n += int(batch.num_graphs)
+        total = len(train_loader.dataset) if hasattr(train_loader, "dataset") else n
+        return float(acc.item()) / max(total, 1)
+
+    @torch.no_grad()
+    def eval_network(self, loader, device=None) -> float:
+        """reference utils/utils_model.py:72-79 (which runs without no_grad and syncs per batch): same number,
+        inference kernels only, one host read."""
+        dev = self.device if device is None else torch.device(device)
+        self.model.eval()
+        acc = torch.zeros((), dtype=torch.float32, device=self.device)
+        n = 0
+        prev_validate = getattr(self.model, "validate_inputs", True)
+        self.model.validate_inputs = self.validate   # no per-batch status read-back unless asked for
+        try:
+            for batch in loader:
+                batch = batch.to(dev)
+                out = self.model(batch)
+                acc += torch.sqrt(self.model.loss(out, torch.unsqueeze(batch.y, dim=1))) * float(batch.num_graphs)
+                n += int(batch.num_graphs)
+        finally:
+            self.model.validate_inputs = prev_validate
+        total = len(loader.dataset) if hasattr(loader, "dataset") else n
+        return float(acc.item()) / max(total, 1)
+
+    def fit(self, train_loader, val_loader, test_loader=None, epochs: int = 250, early_stopping: int = 6, log=None):
+        """The epoch loop of reference scripts_experiments/train_GNN.py:73-111: train every epoch, every 5th
+        epoch step the scheduler on the validation loss, keep the best parameters, stop after
+        ``early_stopping`` evaluations without improvement.  Returns a dict with the loss curves, the best
+        epoch and the best ``state_dict``; the module is left at its last epoch, as in the reference."""
+        from copy import deepcopy
+        m = self.model
+        hist = {"train": [], "val": [], "test": [], "best_epoch": 0, "best_val": float("inf"), "best_state_dict": None}
+        strikes = 0
+        for epoch in range(epochs):
+            if strikes > early_stopping:
+                break
+            train_loss = self.train_network(train_loader)
+            val_loss = self.eval_network(val_loader)
+            test_loss = self.eval_network(test_loader) if test_loader is not None else float("nan")
+            if log is not None:
+                log(epoch, train_loss, val_loss, test_loss)
+            if epoch % 5 == 0:
+                m.scheduler.step(val_loss)
+                hist["train"].append(train_loss); hist["val"].append(val_loss); hist["test"].append(test_loss)
+                if val_loss < hist["best_val"]:
+                    hist["best_val"], hist["best_epoch"] = val_loss, epoch
+                    strikes = 0
+                    hist["best_state_dict"] = deepcopy(m.state_dict())
+                else:
+                    strikes += 1
+        return hist

@@ -196,3 +196,38 @@ def test_predict_ensemble_stream_matches_per_model_golden(pkg):
             assert torch.equal(ref, pred[k])      # same kernels, same batches: identical bits
     assert torch.allclose(torch.cat(means, 0), pred.mean(0), atol=1e-6)
     assert torch.allclose(torch.cat(stds, 0), pred.std(0, unbiased=False), atol=1e-6)
+
+
+def test_trainer_epoch_functions_match_reference_loop(pkg):
+    """FusedTrainer.train_network / eval_network / fit against the reference's loop bodies
+    (utils/utils_model.py:55-79, train_GNN.py:73-111) run through the module's autograd path."""
+    graphs = golden_io.load_graphs("rhcaa_learning")
+    tr, va = graphs[:200], graphs[200:280]
+    opt = pkg.default_options()
+    model = pkg.make_network("GCN", opt, 25).to("cuda")
+    twin = pkg.make_network("GCN", opt, 25).to("cuda")
+    twin.load_state_dict(model.state_dict())
+    trainer = pkg.FusedTrainer(model)
+    tl, vl = pkg.DataLoader(tr, batch_size=40), pkg.DataLoader(va, batch_size=40)
+    for epoch in range(2):
+        got_train = trainer.train_network(tl)
+        got_val = trainer.eval_network(vl)
+        # the reference's functions, verbatim semantics
+        twin.train(); ref_train = 0.0
+        for batch in tl:
+            batch = batch.to("cuda")
+            twin.optimizer.zero_grad()
+            loss = torch.sqrt(twin.loss(twin(batch), torch.unsqueeze(batch.y, dim=1)))
+            loss.backward(); twin.optimizer.step()
+            ref_train += loss.item() * batch.num_graphs
+        ref_train /= len(tl.dataset)
+        twin.eval(); ref_val = 0.0
+        for batch in vl:
+            batch = batch.to("cuda")
+            ref_val += torch.sqrt(twin.loss(twin(batch), torch.unsqueeze(batch.y, dim=1))).item() * batch.num_graphs
+        ref_val /= len(vl.dataset)
+        assert abs(got_train - ref_train) <= 2e-3 * max(1.0, abs(ref_train))
+        assert abs(got_val - ref_val) <= 2e-3 * max(1.0, abs(ref_val))
+    hist = trainer.fit(tl, vl, epochs=6, early_stopping=6)
+    assert len(hist["val"]) == 2 and hist["best_state_dict"] is not None      # epochs 0 and 5 are evaluated
+    assert list(hist["best_state_dict"].keys()) == list(model.state_dict().keys())
