@@ -31,6 +31,7 @@ class HcgGraph(C.Structure):
         ("fill", C.c_float),
         ("ew0", _fp), ("t_ew0", _fp), ("selfw0", _fp), ("dis0", _fp),
         ("max_graph_nodes", C.c_int32), ("flags", C.c_int32),
+        ("edge_mask", _fp),
     ]
 
 
@@ -47,6 +48,7 @@ class HcgGrads(C.Structure):
     _fields_ = [
         ("conv_w", _fp * HCG_MAX_CONV), ("conv_b", _fp * HCG_MAX_CONV),
         ("ro_w", _fp * HCG_MAX_READOUT), ("ro_b", _fp * HCG_MAX_READOUT),
+        ("edge_mask", _fp),
     ]
 
 

@@ -168,7 +168,8 @@ __global__ void __launch_bounds__(256)
 k_agg(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ dis,
       const float* __restrict__ ew, const float* __restrict__ selfw, float fill,
       const float* __restrict__ T, const float* __restrict__ bias, float* __restrict__ out,
-      int64_t N, int H, int lpr, int act, float slope) {
+      int64_t N, int H, int lpr, int act, float slope, const int32_t* __restrict__ eid,
+      const float* __restrict__ mask) {
   const int rows_per_block = 256 / lpr;
   const int64_t i = (int64_t)blockIdx.x * rows_per_block + threadIdx.x / lpr;
   const int sub = threadIdx.x % lpr;
@@ -185,6 +186,7 @@ k_agg(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const
       int j0 = col[k], j1 = col[k + 1], j2 = col[k + 2], j3 = col[k + 3];
       float w0 = dis[j0], w1 = dis[j1], w2 = dis[j2], w3 = dis[j3];
       if (ew) { w0 *= ew[k]; w1 *= ew[k + 1]; w2 *= ew[k + 2]; w3 *= ew[k + 3]; }
+      if (mask) { w0 *= mask[eid[k]]; w1 *= mask[eid[k + 1]]; w2 *= mask[eid[k + 2]]; w3 *= mask[eid[k + 3]]; }
       Vec<VEC> t0, t1, t2, t3;
       t0.load(T + (int64_t)j0 * H + c); t1.load(T + (int64_t)j1 * H + c);
       t2.load(T + (int64_t)j2 * H + c); t3.load(T + (int64_t)j3 * H + c);
@@ -194,6 +196,7 @@ k_agg(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const
       int j = col[k];
       float w = dis[j];
       if (ew) w *= ew[k];
+      if (mask) w *= mask[eid[k]];
       Vec<VEC> t;
       t.load(T + (int64_t)j * H + c);
       acc.fma(w * di, t);
@@ -212,6 +215,34 @@ k_agg(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const
   }
 }
 
+// Gradient w.r.t. the soft edge mask of one conv layer:  g_mask[e] (+)= norm_e <gA[dst_e], T[src_e]>
+// (out_i = sum_e mask_e norm_e T_src(e) + ...).  A warp per destination row, lanes over the features, fixed
+// shuffle tree; every edge owns exactly one CSR slot, so the accumulation over layers needs no atomics.
+__global__ void __launch_bounds__(256)
+k_edge_dot(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const int32_t* __restrict__ eid,
+           const float* __restrict__ dis, const float* __restrict__ ew, const float* __restrict__ gA,
+           const float* __restrict__ T, int64_t N, int H, int accumulate, float* __restrict__ g_mask) {
+  const int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (i >= N) return;
+  const int beg = rowptr[i], end = rowptr[i + 1];
+  const float di = dis[i];
+  for (int k = beg; k < end; ++k) {
+    const int j = col[k];
+    float s = 0.f;
+    for (int c = lane; c < H; c += 32) s = fmaf(gA[i * H + c], __ldg(T + (int64_t)j * H + c), s);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) {
+      float w = dis[j] * di;
+      if (ew) w *= ew[k];
+      const float v = w * s;
+      const int e = eid[k];
+      g_mask[e] = accumulate ? g_mask[e] + v : v;
+    }
+  }
+}
+
 static int lanes_per_row(int H, int vec) {
   int need = (H + vec - 1) / vec;
   int l = 1;
@@ -221,15 +252,16 @@ static int lanes_per_row(int H, int vec) {
 
 static int launch_agg(const int32_t* rowptr, const int32_t* col, const float* dis, const float* ew,
                       const float* selfw, float fill, const float* T, const float* bias, float* out,
-                      int64_t N, int H, int act, float slope, cudaStream_t st) {
+                      int64_t N, int H, int act, float slope, cudaStream_t st, const int32_t* eid = nullptr,
+                      const float* mask = nullptr) {
   if (N == 0) return HCG_OK;
   const bool vec4 = (H % 4 == 0) && ((reinterpret_cast<uintptr_t>(T) | reinterpret_cast<uintptr_t>(out)) % 16 == 0);
   if (vec4) {
     int lpr = lanes_per_row(H, 4);
-    k_agg<4><<<(unsigned)cdiv(N, 256 / lpr), 256, 0, st>>>(rowptr, col, dis, ew, selfw, fill, T, bias, out, N, H, lpr, act, slope);
+    k_agg<4><<<(unsigned)cdiv(N, 256 / lpr), 256, 0, st>>>(rowptr, col, dis, ew, selfw, fill, T, bias, out, N, H, lpr, act, slope, eid, mask);
   } else {
     int lpr = lanes_per_row(H, 1);
-    k_agg<1><<<(unsigned)cdiv(N, 256 / lpr), 256, 0, st>>>(rowptr, col, dis, ew, selfw, fill, T, bias, out, N, H, lpr, act, slope);
+    k_agg<1><<<(unsigned)cdiv(N, 256 / lpr), 256, 0, st>>>(rowptr, col, dis, ew, selfw, fill, T, bias, out, N, H, lpr, act, slope, eid, mask);
   }
   HCG_LAUNCH_OK(st, "k_agg");
   return HCG_OK;
@@ -666,6 +698,8 @@ static int check_graph(const HcgGraph* g, bool need_transpose) {
     HCG_REQUIRE(g->t_rowptr && (g->E == 0 || g->t_col), HCG_ERR_INVALID_ARG,
                 "backward needs the transposed CSR (collate with HCG_COLLATE_TRANSPOSE)");
   if (g->ew0) HCG_REQUIRE(g->selfw0 && g->dis0, HCG_ERR_INVALID_ARG, "weighted layer-0 override is incomplete");
+  if (g->edge_mask && g->E > 0)
+    HCG_REQUIRE(g->eid && (!need_transpose || g->t_eid), HCG_ERR_INVALID_ARG, "edge_mask needs the eid / t_eid arrays of hcg_collate");
   return HCG_OK;
 }
 
@@ -712,7 +746,7 @@ struct BwdWs {
 
 // the graph-resident backward applies (hcg_fused_bwd.cu); g_x and the config switch are checked by the caller
 static bool fused_bwd_shape_ok(const HcgGraph* g, const HcgParams* p) {
-  return p->H == kFusedH && p->L == 2 && p->F <= 32 && g->ew0 == nullptr && g->B > 0 && g->N > 0 &&
+  return p->H == kFusedH && p->L == 2 && p->F <= 32 && g->ew0 == nullptr && g->edge_mask == nullptr && g->B > 0 && g->N > 0 &&
          !(g->flags & HCG_GRAPH_CROSS_EDGES) && g->N / g->B <= 512;
 }
 
@@ -786,7 +820,7 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
 
   // ---- graph-resident path: conv layers + pooling in one kernel, then the readout --------------
   const int path = config_get(HCG_CFG_FORWARD_PATH);
-  const bool fusable = H == kFusedH && p->F <= kMaxFusedF && g->ew0 == nullptr && B > 0 && N > 0 &&
+  const bool fusable = H == kFusedH && p->F <= kMaxFusedF && g->ew0 == nullptr && g->edge_mask == nullptr && B > 0 && N > 0 &&
                        !(g->flags & HCG_GRAPH_CROSS_EDGES);
   // molecule-sized graphs only: one CTA walks a graph, so a batch of few huge graphs stays layer-wise
   const bool molecule_like = N / (B > 0 ? B : 1) <= 512;
@@ -841,7 +875,8 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
     HCG_REQUIRE(h_out != nullptr, HCG_ERR_INVALID_ARG, "saved->acts[%d] is NULL", l);
     const bool weighted0 = (l == 0 && g->ew0 != nullptr);
     rc = launch_agg(g->rowptr, g->col, weighted0 ? g->dis0 : g->dis, weighted0 ? g->ew0 : nullptr,
-                    weighted0 ? g->selfw0 : nullptr, g->fill, w.T, p->conv_b[l], h_out, N, H, 1, p->slope, st);
+                    weighted0 ? g->selfw0 : nullptr, g->fill, w.T, p->conv_b[l], h_out, N, H, 1, p->slope, st,
+                    g->eid, g->edge_mask);
     if (rc) return rc;
     h_in = h_out;
     k_in = H;
@@ -977,15 +1012,26 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
   }
 
   // ---- conv layers backward ---------------------------------------------------------------
+  if (grads->edge_mask && g->E > 0)  // dropped self-loop edges and a call without a mask leave zeros
+    HCG_CUDA_OK(cudaMemsetAsync(grads->edge_mask, 0, sizeof(float) * (size_t)g->E, st));
   for (int l = p->L - 1; l >= 0; --l) {
     const float* h_in = l == 0 ? x : saved->acts[l - 1];
     const int k_in = l == 0 ? p->F : H;
     rc = launch_colsum(w.gA, N, H, w.partial, grads->conv_b[l], st);
     if (rc) return rc;
     const bool weighted0 = (l == 0 && g->ew0 != nullptr);
+    if (grads->edge_mask && g->edge_mask && g->E > 0 && N > 0) {
+      // T_l = h_in W_l^T again (the forward does not keep it), into the not yet used gT buffer
+      rc = launch_gemm<true>(h_in, p->conv_w[l], w.gT, N, k_in, H, EPI_NONE, nullptr, p->slope, st, w.wimg);
+      if (rc) return rc;
+      k_edge_dot<<<(unsigned)cdiv(N, 8), 256, 0, st>>>(g->rowptr, g->col, g->eid, weighted0 ? g->dis0 : g->dis,
+                                                     weighted0 ? g->ew0 : nullptr, w.gA, w.gT, N, H, 1, grads->edge_mask);
+      HCG_LAUNCH_OK(st, "k_edge_dot");
+    }
     // gT = Â^T · gA  (transposed CSR; no bias, no activation)
     rc = launch_agg(g->t_rowptr, g->t_col, weighted0 ? g->dis0 : g->dis, weighted0 ? g->t_ew0 : nullptr,
-                    weighted0 ? g->selfw0 : nullptr, g->fill, w.gA, nullptr, w.gT, N, H, 0, p->slope, st);
+                    weighted0 ? g->selfw0 : nullptr, g->fill, w.gA, nullptr, w.gT, N, H, 0, p->slope, st,
+                    g->t_eid, g->edge_mask);
     if (rc) return rc;
     rc = launch_xty(w.gT, h_in, N, H, k_in, w.partial, grads->conv_w[l], st);
     if (rc) return rc;

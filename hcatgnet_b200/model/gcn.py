@@ -89,6 +89,13 @@ def _max_nodes_hint(graph) -> int:
     return int((ptr[1:] - ptr[:-1]).max())
 
 
+class _PlanHolder:
+    """Carries a cached topology plan for tensor-level calls; pickles empty (``torch.save(model)``)."""
+
+    def __getstate__(self):
+        return {}
+
+
 class _GCNBase(BaseNetwork):
     """Everything reference GCN and GCN_explain share (their constructors are identical,
     reference model/gcn.py:11-50 and :81-120)."""
@@ -134,12 +141,13 @@ class _GCNBase(BaseNetwork):
         ps += [self.readout[-1].weight, self.readout[-1].bias]
         return ps
 
-    def _run(self, x, edge_index, batch, num_graphs, edge_weight=None, cache_on=None):
+    def _run(self, x, edge_index, batch, num_graphs, edge_weight=None, cache_on=None, edge_mask=None):
         """Stage to the GPU if needed, collate (cached on ``cache_on``), run the fused network."""
         home = x.device
         device = ops.compute_device(x)
         params = self._flat_params()
-        need_grad = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params))
+        need_grad = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params) or
+                                                 (edge_mask is not None and edge_mask.requires_grad))
         if edge_weight is not None and edge_weight.requires_grad and torch.is_grad_enabled():
             raise NotImplementedError("gradients w.r.t. edge_weight are not provided by libhcg yet")
         plan = ops.cached_collate(cache_on, edge_index, batch, x.shape[0], num_graphs, device,
@@ -148,7 +156,8 @@ class _GCNBase(BaseNetwork):
                                   grouped=getattr(cache_on, "edges_grouped", None))
         xd = ops.to_device(x, device, torch.float32)
         pd = [ops.to_device(p, device, torch.float32) for p in params]
-        out, emb = ops.gcn_apply(xd, plan, self._dims(), pd)
+        md = ops.to_device(edge_mask, device, torch.float32)
+        out, emb = ops.gcn_apply(xd, plan, self._dims(), pd, edge_mask=md)
         if home != device:
             out, emb = out.to(home), emb.to(home)
         return out, emb
@@ -171,7 +180,21 @@ class GCN(_GCNBase):
 class GCN_explain(_GCNBase):
     """reference model/gcn.py:79-139: tensor-level entry; ``edge_weight`` reaches conv1 only."""
 
-    def forward(self, x=None, edge_index=None, batch_index=None, edge_weight=None):
+    def forward(self, x=None, edge_index=None, batch_index=None, edge_weight=None, edge_mask=None):
+        """``edge_mask`` ([E], optional, differentiable) is this package's stand-in for the hooks PyG's
+        Explainer installs on every MessagePassing layer: it multiplies the messages of ALL conv layers,
+        leaves added self-loops and the normalisation alone (see hcatgnet_b200/explain.py)."""
         out, _ = self._run(x, edge_index, batch_index, _num_graphs_of(None, batch_index, x.shape[0]),
-                           edge_weight=edge_weight)
+                           edge_weight=edge_weight, cache_on=self._plan_cache(edge_index, edge_weight), edge_mask=edge_mask)
         return out
+
+    def _plan_cache(self, edge_index, edge_weight):
+        """An explainer calls forward hundreds of times on one graph: keep the topology plan on a small holder
+        keyed by the edge_index tensor (cached_collate re-checks pointer, version and shape)."""
+        if edge_weight is not None:
+            return None
+        holder = getattr(self, "_explain_holder", None)
+        if holder is None:
+            holder = _PlanHolder()
+            object.__setattr__(self, "_explain_holder", holder)
+        return holder

@@ -81,11 +81,12 @@ class GraphPlan:
     def device(self):
         return self.rowptr.device
 
-    def c_struct(self) -> _lib.HcgGraph:
+    def c_struct(self, edge_mask: torch.Tensor | None = None) -> _lib.HcgGraph:
         return _lib.HcgGraph(
             self.N, self.E, self.B, _ptr(self.rowptr), _ptr(self.col), _ptr(self.eid), _ptr(self.dis),
             _ptr(self.graph_ptr), _ptr(self.t_rowptr), _ptr(self.t_col), _ptr(self.t_eid), self.fill,
-            _ptr(self.ew0), _ptr(self.t_ew0), _ptr(self.selfw0), _ptr(self.dis0), int(self.max_graph_nodes), int(self.flags))
+            _ptr(self.ew0), _ptr(self.t_ew0), _ptr(self.selfw0), _ptr(self.dis0), int(self.max_graph_nodes), int(self.flags),
+            _ptr(edge_mask))
 
 
 def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int, num_graphs: int,
@@ -236,8 +237,15 @@ def _check_param_shapes(dims: NetDims, tensors) -> None:
             raise ValueError(f"readout layer {k}: weight {tuple(w.shape)} / bias {tuple(b.shape)} do not match {want}")
 
 
-def forward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, save: bool):
-    """One ``hcg_gcn_forward`` call.  Returns (out[B,C], emb[B,2H], saved tensors or None)."""
+def _check_mask(plan: GraphPlan, edge_mask):
+    if edge_mask is not None and (edge_mask.numel() != plan.E or edge_mask.dtype != torch.float32 or not edge_mask.is_cuda):
+        raise ValueError(f"edge_mask must be a CUDA float32 tensor with one entry per edge ({plan.E})")
+
+
+def forward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, save: bool, edge_mask=None):
+    """One ``hcg_gcn_forward`` call.  Returns (out[B,C], emb[B,2H], saved tensors or None).
+    ``edge_mask``: optional [E] multiplier of every message of every conv layer (original edge order)."""
+    _check_mask(plan, edge_mask)
     lib = _lib.load()
     device = plan.device
     if x.shape != (plan.N, dims.F):
@@ -259,7 +267,7 @@ def forward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, save: b
             for k, h in enumerate(hid):
                 saved_c.hid[k] = h.data_ptr()
         ws = _workspace(lib.hcg_forward_workspace_bytes(plan.N, plan.E, plan.B, C.byref(pstruct)), device)
-        g = plan.c_struct()
+        g = plan.c_struct(edge_mask)
         _lib.check(lib.hcg_gcn_forward(C.byref(g), _ptr(x), C.byref(pstruct), _ptr(out), _ptr(emb),
                                        C.byref(saved_c) if saved_c is not None else None,
                                        _ptr(ws), ws.numel(), _stream(device)))
@@ -268,9 +276,11 @@ def forward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, save: b
 
 
 def backward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, saved_t, emb, g_out, g_emb, need_gx: bool,
-                 flat_out: torch.Tensor | None = None):
-    """One ``hcg_gcn_backward`` call.  Returns (g_x or None, list of parameter grads).
+                 flat_out: torch.Tensor | None = None, edge_mask=None, need_gmask: bool = False):
+    """One ``hcg_gcn_backward`` call.  Returns (g_x or None, list of parameter grads) — and the gradient
+    w.r.t. ``edge_mask`` as a third element when ``need_gmask``.
     ``flat_out``: an existing fp32 slab (>= sum of parameter sizes) to write the gradients into."""
+    _check_mask(plan, edge_mask)
     lib = _lib.load()
     device = plan.device
     f32 = dict(dtype=torch.float32, device=device)
@@ -297,12 +307,18 @@ def backward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, saved_
             gc.ro_w[k] = grads[2 * dims.L + 2 * k].data_ptr()
             gc.ro_b[k] = grads[2 * dims.L + 2 * k + 1].data_ptr()
         g_x = torch.empty(plan.N, dims.F, **f32) if need_gx else None
+        g_mask = None
+        if need_gmask and edge_mask is not None:
+            g_mask = torch.empty(max(plan.E, 1), **f32)
+            gc.edge_mask = g_mask.data_ptr()
         ws = _workspace(lib.hcg_backward_workspace_bytes(plan.N, plan.E, plan.B, C.byref(pstruct)), device)
-        g = plan.c_struct()
+        g = plan.c_struct(edge_mask)
         _lib.check(lib.hcg_gcn_backward(C.byref(g), _ptr(x), C.byref(pstruct), C.byref(saved_c), _ptr(emb),
                                         _ptr(g_out), _ptr(g_emb), C.byref(gc), _ptr(g_x),
                                         _ptr(ws), ws.numel(), _stream(device)))
         ws.record_stream(torch.cuda.current_stream(device))
+    if need_gmask:
+        return g_x, grads, (None if g_mask is None else g_mask[:plan.E])
     return g_x, grads
 
 
@@ -310,30 +326,45 @@ class _GCNFunction(torch.autograd.Function):
     """autograd node whose forward/backward are single C-ABI calls."""
 
     @staticmethod
-    def forward(ctx, x, plan, dims, need_grad, *params):
+    def forward(ctx, x, plan, dims, need_grad, edge_mask, *params):
         # `need_grad` is decided by the caller: grad mode is always off inside Function.forward and
         # ctx.needs_input_grad reports requires_grad flags even under torch.no_grad()
         params = tuple(p.contiguous() for p in params)
         if need_grad and not plan.has_transpose:
             raise RuntimeError("this GraphPlan was collated without the transposed CSR; backward needs transpose=True")
-        out, emb, saved_t = forward_raw(plan, x, dims, params, save=need_grad)
+        if edge_mask is not None:
+            edge_mask = edge_mask.contiguous()
+        out, emb, saved_t = forward_raw(plan, x, dims, params, save=need_grad, edge_mask=edge_mask)
         if need_grad:
             ctx.plan, ctx.dims, ctx.saved_t = plan, dims, saved_t
-            ctx.save_for_backward(x, emb, *params)
+            ctx.has_mask = edge_mask is not None
+            if edge_mask is not None:
+                ctx.save_for_backward(x, emb, edge_mask, *params)
+            else:
+                ctx.save_for_backward(x, emb, *params)
         return out, emb
 
     @staticmethod
     def backward(ctx, g_out, g_emb):
-        x, emb, *params = ctx.saved_tensors
+        if ctx.has_mask:
+            x, emb, edge_mask, *params = ctx.saved_tensors
+        else:
+            x, emb, *params = ctx.saved_tensors
+            edge_mask = None
         g_out = g_out.contiguous() if g_out is not None else None
         g_emb = g_emb.contiguous() if g_emb is not None else None
-        g_x, grads = backward_raw(ctx.plan, x, ctx.dims, params, ctx.saved_t, emb, g_out, g_emb,
-                                  need_gx=ctx.needs_input_grad[0])
-        return (g_x, None, None, None, *grads)
+        want_gmask = bool(ctx.has_mask and ctx.needs_input_grad[4])
+        res = backward_raw(ctx.plan, x, ctx.dims, params, ctx.saved_t, emb, g_out, g_emb,
+                           need_gx=ctx.needs_input_grad[0], edge_mask=edge_mask, need_gmask=want_gmask)
+        g_x, grads = res[0], res[1]
+        g_mask = res[2] if want_gmask else None
+        return (g_x, None, None, None, g_mask, *grads)
 
 
-def gcn_apply(x: torch.Tensor, plan: GraphPlan, dims: NetDims, params):
-    """Differentiable GCN hot path: returns (out[B,C], emb[B,2H])."""
+def gcn_apply(x: torch.Tensor, plan: GraphPlan, dims: NetDims, params, edge_mask: torch.Tensor | None = None):
+    """Differentiable GCN hot path: returns (out[B,C], emb[B,2H]).  ``edge_mask`` ([E], original edge order)
+    multiplies every message of every conv layer and is differentiable (explainers)."""
     _check_param_shapes(dims, params)
-    need_grad = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params))
-    return _GCNFunction.apply(x, plan, dims, need_grad, *params)
+    need_grad = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params) or
+                                             (edge_mask is not None and edge_mask.requires_grad))
+    return _GCNFunction.apply(x, plan, dims, need_grad, edge_mask, *params)

@@ -92,6 +92,12 @@ typedef struct HcgGraph {
    * correctness (graphs above the capacity run on global scratch). */
   int32_t max_graph_nodes;
   int32_t flags;             /* HCG_GRAPH_* bits */
+  /* Optional soft edge mask, [E] in ORIGINAL edge order (indexed through eid / t_eid), NULL = none: every
+   * message of every conv layer is multiplied by its edge's mask value, added self-loops are not masked and
+   * the degree normalisation is unchanged — what PyG's Explainer hooks do to a MessagePassing layer
+   * (edge_mask_type='object'; reference scripts_experiments/explain_gnn.py:39-50).  Masked calls run on the
+   * layer-wise kernels. */
+  const float* edge_mask;
 } HcgGraph;
 
 /*
@@ -119,6 +125,7 @@ typedef struct HcgGrads {
   float* conv_b[HCG_MAX_CONV];
   float* ro_w[HCG_MAX_READOUT];
   float* ro_b[HCG_MAX_READOUT];
+  float* edge_mask;          /* [E] d(loss)/d(HcgGraph.edge_mask) in original edge order, or NULL to skip it */
 } HcgGrads;
 
 /*

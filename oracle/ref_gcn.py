@@ -62,10 +62,17 @@ def gcn_norm(edge_index: torch.Tensor, num_nodes: int, edge_weight=None, improve
     return row2, col2, norm, deg, dis
 
 
-def gcn_conv(h, edge_index, weight, bias, edge_weight=None, improved=False):
-    """One GCNConv: transform first (no bias), weighted sum to dst in edge order, bias last."""
+def gcn_conv(h, edge_index, weight, bias, edge_weight=None, improved=False, edge_mask=None):
+    """One GCNConv: transform first (no bias), weighted sum to dst in edge order, bias last.
+
+    ``edge_mask`` ([E], already in (0,1)) restates what PyG's Explainer hooks do inside
+    ``MessagePassing.propagate`` (explain mode, ``edge_mask_type='object'``): every message is multiplied
+    by its edge's mask, the self-loops GCNConv added get mask 1, the normalisation is untouched."""
     n = h.shape[0]
     row, col, norm, _, _ = gcn_norm(edge_index, n, edge_weight, improved, dtype=h.dtype)
+    if edge_mask is not None:
+        keep = edge_index[0] != edge_index[1]
+        norm = norm * torch.cat([edge_mask[keep].to(h.dtype), torch.ones(n, dtype=h.dtype)])
     t = h @ weight.t()
     out = torch.zeros(n, weight.shape[0], dtype=h.dtype).index_add_(0, col, t[row] * norm[:, None])
     return out + bias
@@ -101,7 +108,7 @@ def infer_arch(sd) -> tuple[int, int]:
 
 
 def forward(sd, x, edge_index, batch, num_graphs=None, edge_weight=None, improved=True,
-            return_all=False):
+            return_all=False, edge_mask=None):
     """Whole network on a state_dict-like mapping of tensors (reference model/gcn.py:54-76).
 
     Returns ``(out[B,C], emb[B,2H])`` (and the per-layer activations when ``return_all``).
@@ -112,11 +119,12 @@ def forward(sd, x, edge_index, batch, num_graphs=None, edge_weight=None, improve
         num_graphs = int(batch.max()) + 1 if batch.numel() else 0
     acts = []
     h = torch.nn.functional.leaky_relu(
-        gcn_conv(x, edge_index, sd["conv1.lin.weight"], sd["conv1.bias"], edge_weight, improved), LEAKY_SLOPE)
+        gcn_conv(x, edge_index, sd["conv1.lin.weight"], sd["conv1.bias"], edge_weight, improved, edge_mask), LEAKY_SLOPE)
     acts.append(h)
     for i in range(n_conv - 1):
         h = torch.nn.functional.leaky_relu(
-            gcn_conv(h, edge_index, sd[f"conv_layers.{i}.lin.weight"], sd[f"conv_layers.{i}.bias"]), LEAKY_SLOPE)
+            gcn_conv(h, edge_index, sd[f"conv_layers.{i}.lin.weight"], sd[f"conv_layers.{i}.bias"],
+                     edge_mask=edge_mask), LEAKY_SLOPE)
         acts.append(h)
     emb = torch.cat([segment_max(h, batch, num_graphs), segment_mean(h, batch, num_graphs)], dim=1)
     z = emb

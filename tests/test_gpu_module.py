@@ -231,3 +231,31 @@ def test_trainer_epoch_functions_match_reference_loop(pkg):
     hist = trainer.fit(tl, vl, epochs=6, early_stopping=6)
     assert len(hist["val"]) == 2 and hist["best_state_dict"] is not None      # epochs 0 and 5 are evaluated
     assert list(hist["best_state_dict"].keys()) == list(model.state_dict().keys())
+
+
+def test_gnn_explainer_tracks_oracle_run(pkg):
+    """hcatgnet_b200.explain.gnn_explainer (masks trained through the CUDA forward/backward) against the same
+    loop driven by the CPU oracle, from identical initial masks."""
+    from hcatgnet_b200 import explain
+    sd, graphs, _, _ = golden_io.rows_with_graphs("learning", 1, 2)
+    g = graphs[3]
+    x, ei = g["x"], g["edge_index"]
+    batch = torch.zeros(x.shape[0], dtype=torch.int64)
+    from hcatgnet_b200.model.gcn import GCN_explain
+    model = GCN_explain(pkg.default_options(), 25)
+    model.load_state_dict(sd, strict=True)
+    model = model.to("cuda")
+    gen = torch.Generator().manual_seed(11)
+    nm0, em0 = explain.init_masks(x.shape[0], x.shape[1], ei.shape[1], "cpu", gen)
+    got = explain.gnn_explainer(model, x, ei, batch, epochs=12,
+                                masks=(nm0.detach().clone().cuda().requires_grad_(True),
+                                       em0.detach().clone().cuda().requires_grad_(True)))
+    ref_nm, ref_em = explain.run_gnnexplainer(
+        lambda h, m: ref_gcn.forward(sd, h, ei, batch, 1, edge_mask=m)[0], x, ei.shape[1], epochs=12,
+        masks=(nm0.detach().clone().requires_grad_(True), em0.detach().clone().requires_grad_(True)))
+    assert got["node_mask"].shape == x.shape and got["edge_mask"].shape == (ei.shape[1],)
+    assert float((got["node_mask"].cpu() - ref_nm).abs().max()) <= 2e-3
+    assert float((got["edge_mask"].cpu() - ref_em).abs().max()) <= 2e-3
+    # what the reference consumes: masks / max(masks.sum(dim=1))  (utils/other_utils.py:66-68)
+    nm = got["node_mask"].cpu()
+    assert torch.isfinite(nm / torch.max(nm.sum(dim=1))).all()

@@ -512,3 +512,34 @@ def test_tensor_core_gemm_forward_backward(hcg, gemm_path, forward_path, backwar
     with torch.no_grad():
         o_fma, e_fma = hcg.gcn_apply(b.x.cuda(), plan, _dims(hcg, sd), params)
     assert _close(e.cpu(), e_fma.cpu()) <= TOL and _close(o.cpu(), o_fma.cpu()) <= TOL
+
+
+# ------------------------------------------------------------------------------------------
+# soft edge mask on every conv layer (explainers): forward and gradients against the fp64 oracle
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("rset,outer,inner,count", [("learning", 1, 2, 5), ("biaryl", 1, 2, 3)])
+def test_edge_mask_forward_and_gradients(hcg, rset, outer, inner, count):
+    sd, graphs, _, _ = golden_io.rows_with_graphs(rset, outer, inner)
+    b = ref_gcn.collate(graphs[:count])
+    E = b["edge_index"].shape[1]
+    gen = torch.Generator().manual_seed(5)
+    mask = torch.rand(E, generator=gen) * 0.9 + 0.05
+    xj = b["x"] + 0.05 * torch.rand(b["x"].shape, generator=gen)     # de-symmetrised (see the x-gradient test above)
+    # oracle, fp64
+    sd64 = {k: v.double() for k, v in sd.items()}
+    x64, m64 = xj.double().requires_grad_(True), mask.double().requires_grad_(True)
+    o_ref, e_ref = ref_gcn.forward(sd64, x64, b["edge_index"], b["batch"], b["num_graphs"], edge_mask=m64)
+    (o_ref.pow(2).sum() + 0.01 * e_ref.sum()).backward()
+    # CUDA
+    params, _, _ = _sd_params(sd, "cuda")
+    plan = hcg.collate(b["edge_index"].cuda(), b["batch"].cuda(), xj.shape[0], b["num_graphs"], transpose=True)
+    xc, mc = xj.cuda().requires_grad_(True), mask.cuda().requires_grad_(True)
+    o, e = hcg.gcn_apply(xc, plan, _dims(hcg, sd), params, edge_mask=mc)
+    assert _close(o.detach().cpu(), o_ref.detach()) <= TOL and _close(e.detach().cpu(), e_ref.detach()) <= TOL
+    (o.pow(2).sum() + 0.01 * e.sum()).backward()
+    _assert_grads({"mask": mc.grad.cpu(), "x": xc.grad.cpu()}, {"mask": m64.grad, "x": x64.grad}, rtol=1e-3)
+    # a mask of ones is the unmasked network
+    with torch.no_grad():
+        o1, _ = hcg.gcn_apply(xj.cuda(), plan, _dims(hcg, sd), params, edge_mask=torch.ones(E, device="cuda"))
+        o0, _ = hcg.gcn_apply(xj.cuda(), plan, _dims(hcg, sd), params)
+    assert _close(o1.cpu(), o0.cpu()) <= TOL
