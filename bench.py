@@ -220,6 +220,14 @@ def algorithmic_bytes(name: str, N: int, E: int, B: int, F: int, H: int):
     return table.get(name)
 
 
+def algorithmic_flops(name: str, N: int, F: int, H: int, L: int):
+    """FLOPs one launch of a tensor-bound kernel must perform (fp32-equivalent: 2 M K Nc), averaged over
+    the launches of a step."""
+    if name == "k_tc_gemm":  # forward: layer 0 has K = F, the others K = H (inference: one launch per layer)
+        return (2.0 * N * F * H + (L - 1) * 2.0 * N * H * H) / L
+    return None
+
+
 def measured_traffic(name: str, a):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full`
     capture of this kernel on this workload (profiles/ncu_traffic.json), or None."""
@@ -378,7 +386,21 @@ def main():
         top = next(iter(kernels))
         N, E = int(np.mean(Ns)), int(np.mean(Es))
         ab = algorithmic_bytes(top.split("<")[0], N, E, a.batch, F_IN, a.hidden)
-        if ab is not None:
+        af = algorithmic_flops(top.split("<")[0], N, F_IN, a.hidden, a.convs) if a.mode == "infer" else None
+        if af is not None:
+            # dense contraction on the tensor cores: achieved fp32-equivalent TFLOP/s against the measured dense
+            # bf16 peak (sustained figure: the kernel is timed inside a long step).  The split-TF32 scheme
+            # issues 3 TF32 MMAs per product and TF32 runs at half the bf16 rate, so frac <= 1/6 by construction.
+            tpeak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1500.0)))
+            sec = kernels[top]["ms_per_launch"] * 1e-3
+            ach = af / sec / 1e12
+            roofline = {"bound": "tensor", "kernel": top, "achieved": ach, "peak": tpeak, "unit": "TFLOP/s",
+                        "frac": ach / tpeak, "traffic": measured_traffic(top.split("<")[0], a),
+                        "algorithmic_flops_per_launch": af, "ms_per_launch": kernels[top]["ms_per_launch"],
+                        "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (cuBLAS bf16)" if "bf16_tflops_sustained" in peaks
+                        else "fallback 1500 TFLOP/s", "share_of_step": kernels[top]["share"],
+                        "note": "fp32-equivalent FLOPs; 3 TF32 MMAs per product at half the bf16 rate: frac <= 0.167"}
+        elif ab is not None:
             sec = kernels[top]["ms_per_launch"] * 1e-3
             ach = ab / sec / 1e9
             roofline = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s",
