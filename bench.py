@@ -356,7 +356,9 @@ def main():
     wall_e2e = (time.perf_counter() - t0) * 1e3
     ms_e2e = max(ms_e2e_dev, 0.0)
     e2e_value = graphs_total / (ms_e2e * 1e-3)
-    h2d = int(np.mean([h.x.numel() * 4 + h.edge_index.numel() * 8 + h.batch.numel() * 8 + h.y.numel() * 4 for h in host]))
+    # what DevicePrefetcher copies per batch: x, edge_index, ptr (the batch vector is rebuilt on the device), y
+    h2d = int(np.mean([h.x.numel() * 4 + h.edge_index.numel() * 8 + (h.ptr.numel() * 8 if h.ptr is not None else h.batch.numel() * 8)
+                       + h.y.numel() * 4 for h in host]))
     d2h = a.batch * N_CLS * 4 if a.mode == "infer" else 4
 
     # ---- per-kernel device time (separate pass, same inputs) + roofline of the dominant kernel -

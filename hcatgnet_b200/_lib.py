@@ -90,6 +90,7 @@ SIGNATURES = {
     "hcg_backward_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.POINTER(HcgParams)]),
     "hcg_gcn_backward": (C.c_int, [C.POINTER(HcgGraph), _fp, C.POINTER(HcgParams), C.POINTER(HcgSaved), _fp, _fp, _fp,
                                    C.POINTER(HcgGrads), _fp, _fp, C.c_size_t, _fp]),
+    "hcg_batch_from_ptr": (C.c_int, [_fp, C.c_int64, C.c_int64, _fp, _fp]),
     "hcg_rmse_seed": (C.c_int, [_fp, _fp, C.c_int64, C.c_int, _fp, _fp, _fp]),
     "hcg_adam_step": (C.c_int, [_fp, _fp, _fp, _fp, C.c_int64, _fp, C.c_float, C.c_float, C.c_float, C.c_float,
                                 C.c_int64, _fp, _fp]),

@@ -666,3 +666,31 @@ extern "C" int hcg_collate_status(const void* ws, void* stream, int32_t* graph_f
   if (graph_flags && (status & kStatusCrossEdge)) *graph_flags |= HCG_GRAPH_CROSS_EDGES;
   return HCG_OK;
 }
+
+// ---- batch vector from graph offsets ------------------------------------------------------------------
+// PyG's Batch carries both `batch` [N] and `ptr` [B+1]; they hold the same information.  A host batch can
+// therefore cross PCIe without its `batch` vector (8 bytes per node, 5 % of the bytes of a reaction graph)
+// and have it rebuilt here.
+namespace hcg {
+__global__ void __launch_bounds__(256)
+k_batch_from_ptr(const int64_t* __restrict__ ptr, int64_t B, int64_t N, int64_t* __restrict__ batch) {
+  // a warp per graph: lanes stride over the graph's node range
+  const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (g >= B) return;
+  int64_t lo = ptr[g], hi = ptr[g + 1];
+  lo = lo < 0 ? 0 : lo;
+  hi = hi > N ? N : hi;
+  for (int64_t i = lo + lane; i < hi; i += 32) batch[i] = g;
+}
+}  // namespace hcg
+
+extern "C" int hcg_batch_from_ptr(const int64_t* ptr, int64_t B, int64_t N, int64_t* batch, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  HCG_REQUIRE(ptr && (batch || N == 0), HCG_ERR_INVALID_ARG, "NULL pointer");
+  HCG_REQUIRE(B >= 0 && N >= 0, HCG_ERR_INVALID_ARG, "negative sizes");
+  if (B == 0 || N == 0) return HCG_OK;
+  hcg::k_batch_from_ptr<<<(unsigned)hcg::cdiv(B * 32, 256), 256, 0, st>>>(ptr, B, N, batch);
+  HCG_LAUNCH_OK(st, "k_batch_from_ptr");
+  return HCG_OK;
+}

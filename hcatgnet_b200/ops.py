@@ -161,6 +161,17 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
     return plan
 
 
+def batch_from_ptr(ptr: torch.Tensor, num_nodes: int) -> torch.Tensor:
+    """PyG's ``Batch.batch`` [N] rebuilt on the GPU from ``Batch.ptr`` [B+1] (``hcg_batch_from_ptr``)."""
+    if not ptr.is_cuda:
+        raise RuntimeError("batch_from_ptr expects the ptr tensor on a CUDA device")
+    ptr = ptr.to(torch.int64).contiguous()
+    out = torch.empty(int(num_nodes), dtype=torch.int64, device=ptr.device)
+    with torch.cuda.device(ptr.device):
+        _lib.check(_lib.load().hcg_batch_from_ptr(_ptr(ptr), int(ptr.numel()) - 1, int(num_nodes), _ptr(out), _stream(ptr.device)))
+    return out
+
+
 def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edge_weight=None,
                    improved=False, transpose=False, validate=True, max_graph_nodes=0, grouped=None) -> GraphPlan:
     """``collate`` memoised on ``holder`` (the batch object the caller passed to ``forward``).

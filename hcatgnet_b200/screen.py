@@ -40,7 +40,15 @@ class DevicePrefetcher:
             return False
         with torch.cuda.stream(self.copy_stream):
             mv = lambda t: None if t is None else t.to(self.device, non_blocking=True)  # noqa: E731
-            d = Batch(mv(h.x), mv(h.edge_index), mv(h.batch), None, mv(h.y), h.idx, h.num_graphs,
+            ptr = getattr(h, "ptr", None)
+            if ptr is not None and not ptr.is_cuda and ptr.numel() == h.num_graphs + 1 and h.x is not None:
+                # `batch` and `ptr` carry the same information: ship the (B+1)-entry ptr and rebuild the
+                # N-entry batch vector on the device (5 % fewer bytes over PCIe for a reaction graph)
+                ptr_d = mv(ptr)
+                bt = ops.batch_from_ptr(ptr_d, int(h.x.shape[0]))
+            else:
+                ptr_d, bt = None, mv(h.batch)
+            d = Batch(mv(h.x), mv(h.edge_index), bt, ptr_d, mv(h.y), h.idx, h.num_graphs,
                       edges_grouped=getattr(h, "edges_grouped", None))
             d.max_graph_nodes = getattr(h, "max_graph_nodes", 0)
             ev = torch.cuda.Event()
@@ -55,7 +63,7 @@ class DevicePrefetcher:
             d, ev, h = self.queue.popleft()
             cur = torch.cuda.current_stream(self.device)
             cur.wait_event(ev)
-            for t in (d.x, d.edge_index, d.batch, d.y):
+            for t in (d.x, d.edge_index, d.batch, d.ptr, d.y):
                 if t is not None and t.is_cuda:
                     t.record_stream(cur)
             self._stage_one()  # refill behind the batch being handed out

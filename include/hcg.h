@@ -206,6 +206,12 @@ int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* batch, int6
                 float* ew0, float* t_ew0, float* selfw0, float* dis0,
                 void* ws, size_t ws_bytes, void* stream);
 
+/*
+ * batch[i] = g for ptr[g] <= i < ptr[g+1]: rebuilds PyG's `Batch.batch` [N] from `Batch.ptr` [B+1] on the
+ * device, so that a host batch need not carry the redundant vector across PCIe.
+ */
+int hcg_batch_from_ptr(const int64_t* ptr, int64_t B, int64_t N, int64_t* batch, void* stream);
+
 /* Synchronises `stream`, reads the status word of the last hcg_collate that used `ws`.  Returns
  * HCG_ERR_BAD_INDEX / HCG_ERR_BAD_BATCH for unusable input; `graph_flags` (may be NULL) receives
  * the HCG_GRAPH_* bits to put into HcgGraph.flags. */

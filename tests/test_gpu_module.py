@@ -259,3 +259,14 @@ def test_gnn_explainer_tracks_oracle_run(pkg):
     # what the reference consumes: masks / max(masks.sum(dim=1))  (utils/other_utils.py:66-68)
     nm = got["node_mask"].cpu()
     assert torch.isfinite(nm / torch.max(nm.sum(dim=1))).all()
+
+
+def test_prefetcher_rebuilds_batch_vector_from_ptr(pkg):
+    from hcatgnet_b200 import ops
+    from hcatgnet_b200.synth import synth_batch
+    h = synth_batch(300, 25, seed=3, n_min=1, n_max=60, pin=True)
+    d = next(iter(pkg.DevicePrefetcher([h])))
+    torch.cuda.synchronize()
+    assert torch.equal(d.batch.cpu(), h.batch) and torch.equal(d.ptr.cpu(), h.ptr)
+    ptr = torch.tensor([0, 3, 3, 7], dtype=torch.int64, device="cuda")      # an empty graph in the middle
+    assert ops.batch_from_ptr(ptr, 7).tolist() == [0, 0, 0, 2, 2, 2, 2]
