@@ -23,9 +23,9 @@
 //    and the W slot two chunks later.  Epilogue: tcgen05.ld of the accumulator row, optional LeakyReLU'
 //    mask, row store.
 // Measured (B200, N = 1.31 M rows, K = Nc = 256): 0.99 ms = 173 TFLOP/s fp32-equivalent, 3 x 173 = 520 TFLOP/s
-// on the TF32 pipe (fp32 FMA tiles: 3.96 ms).  Every 128-row tile streams the whole 512 KB hi|lo image of W
-// from L2 (5.3 TB/s across the chip): that, not the tensor pipe, is the bound; sharing W chunks across a
-// 2-CTA cluster by multicast is the next step.
+// on the TF32 pipe (fp32 FMA tiles: 3.96 ms).  Sharing the W stream across 2-CTA clusters (multicast) and a
+// deeper A prefetch were both measured without gain (profiles/experiments/README.md): the kernel runs at the
+// TF32 rate the tensor pipe sustains for this shape; what is left is the arithmetic of the 3-term split.
 #include "hcg_common.cuh"
 #include "hcg_tc.cuh"
 
