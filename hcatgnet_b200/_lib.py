@@ -140,6 +140,7 @@ def check(code: int) -> None:
 HCG_CFG_FORWARD_PATH = 0
 HCG_CFG_BACKWARD_PATH = 1
 HCG_CFG_GEMM_PATH = 2
+HCG_CFG_AGG_PATH = 3
 PATH_AUTO, PATH_LAYERWISE, PATH_GRAPH_RESIDENT, PATH_TENSOR_CORE = 0, 1, 2, 3
 
 

@@ -250,6 +250,166 @@ static int lanes_per_row(int H, int vec) {
   return l;
 }
 
+// ------------------------------------------------------------------------------------------
+// Wide-row aggregation (H >= 128, unweighted, unmasked): k_agg above spends ~400 instructions per 256-wide
+// row (the neighbour list is walked once per 128-column pass, runtime switches inside the loops, scalar
+// bias loads) and is issue-bound at ~40 % of the HBM rate.  Here a warp owns a whole row: the neighbour
+// list is walked ONCE, each lane carries NV float4 accumulators (columns 4 lane + 128 v), the weights are
+// formed once per neighbour, bias / LeakyReLU / store are vector operations.  Same weights, same order of
+// the sums as k_agg: bit-identical rows.
+// POOL: a block owns one graph (rows round-robin over its 8 warps) and also produces emb = [max || mean]
+// of the finished rows (reference model/gcn.py:65-66) - the last layer's k_pool pass over [N, H] disappears,
+// and in inference (out == NULL) so does the last layer's [N, H] store.
+// ------------------------------------------------------------------------------------------
+template <int NV>
+__device__ __forceinline__ void agg_wide_row(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                                             const float* __restrict__ dis, float fill, const float* __restrict__ T,
+                                             int64_t i, int H, int lane, const float4 (&b4)[NV], int act, float slope,
+                                             float4 (&acc)[NV]) {
+  const int beg = __ldg(rowptr + i), end = __ldg(rowptr + i + 1);
+  const float di = __ldg(dis + i);
+#pragma unroll
+  for (int v = 0; v < NV; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float* Tl = T + 4 * lane;
+  int k = beg;
+  for (; k + 2 <= end; k += 2) {  // two neighbours' rows in flight
+    const int j0 = __ldg(col + k), j1 = __ldg(col + k + 1);
+    const float w0 = __ldg(dis + j0) * di, w1 = __ldg(dis + j1) * di;
+    const float* p0 = Tl + (int64_t)j0 * H;
+    const float* p1 = Tl + (int64_t)j1 * H;
+    float4 t0[NV], t1[NV];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      if (128 * v + 4 * lane < H) { t0[v] = ldg4(p0 + 128 * v); t1[v] = ldg4(p1 + 128 * v); }
+      else { t0[v] = make_float4(0.f, 0.f, 0.f, 0.f); t1[v] = t0[v]; }
+    }
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      acc[v].x = fmaf(w0, t0[v].x, acc[v].x); acc[v].y = fmaf(w0, t0[v].y, acc[v].y);
+      acc[v].z = fmaf(w0, t0[v].z, acc[v].z); acc[v].w = fmaf(w0, t0[v].w, acc[v].w);
+    }
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      acc[v].x = fmaf(w1, t1[v].x, acc[v].x); acc[v].y = fmaf(w1, t1[v].y, acc[v].y);
+      acc[v].z = fmaf(w1, t1[v].z, acc[v].z); acc[v].w = fmaf(w1, t1[v].w, acc[v].w);
+    }
+  }
+  if (k < end) {
+    const int j0 = __ldg(col + k);
+    const float w0 = __ldg(dis + j0) * di;
+    const float* p0 = Tl + (int64_t)j0 * H;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+      if (128 * v + 4 * lane < H) {
+        const float4 t = ldg4(p0 + 128 * v);
+        acc[v].x = fmaf(w0, t.x, acc[v].x); acc[v].y = fmaf(w0, t.y, acc[v].y);
+        acc[v].z = fmaf(w0, t.z, acc[v].z); acc[v].w = fmaf(w0, t.w, acc[v].w);
+      }
+  }
+  const float ws = (di * fill) * di;
+  const float* ps = Tl + i * H;
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+    if (128 * v + 4 * lane < H) {
+      const float4 t = ldg4(ps + 128 * v);
+      acc[v].x = fmaf(ws, t.x, acc[v].x) + b4[v].x; acc[v].y = fmaf(ws, t.y, acc[v].y) + b4[v].y;
+      acc[v].z = fmaf(ws, t.z, acc[v].z) + b4[v].z; acc[v].w = fmaf(ws, t.w, acc[v].w) + b4[v].w;
+      if (act) {
+        acc[v].x = lrelu(acc[v].x, slope); acc[v].y = lrelu(acc[v].y, slope);
+        acc[v].z = lrelu(acc[v].z, slope); acc[v].w = lrelu(acc[v].w, slope);
+      }
+    }
+}
+
+template <int NV, bool POOL>
+__global__ void __launch_bounds__(256)
+k_agg_wide(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ dis, float fill,
+           const float* __restrict__ T, const float* __restrict__ bias, float* __restrict__ out, int64_t N, int H, int act,
+           float slope, const int32_t* __restrict__ graph_ptr, float* __restrict__ emb) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float4 b4[NV], acc[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+    b4[v] = (bias && 128 * v + 4 * lane < H) ? ldg4(bias + 128 * v + 4 * lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+  if (!POOL) {
+    const int64_t i = (int64_t)blockIdx.x * 8 + warp;
+    if (i >= N) return;
+    agg_wide_row<NV>(rowptr, col, dis, fill, T, i, H, lane, b4, act, slope, acc);
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+      if (128 * v + 4 * lane < H) *reinterpret_cast<float4*>(out + i * H + 128 * v + 4 * lane) = acc[v];
+    return;
+  }
+  __shared__ float4 s_max[8][NV][32], s_sum[8][NV][32];
+  const int64_t gid = blockIdx.x;
+  const int n0 = graph_ptr[gid], n1 = graph_ptr[gid + 1];
+  float4 pmax[NV], psum[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) {
+    pmax[v] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    psum[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int64_t i = n0 + warp; i < n1; i += 8) {
+    agg_wide_row<NV>(rowptr, col, dis, fill, T, i, H, lane, b4, act, slope, acc);
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+      if (128 * v + 4 * lane < H) {
+        if (out) *reinterpret_cast<float4*>(out + i * H + 128 * v + 4 * lane) = acc[v];
+        pmax[v].x = fmaxf(pmax[v].x, acc[v].x); pmax[v].y = fmaxf(pmax[v].y, acc[v].y);
+        pmax[v].z = fmaxf(pmax[v].z, acc[v].z); pmax[v].w = fmaxf(pmax[v].w, acc[v].w);
+        psum[v].x += acc[v].x; psum[v].y += acc[v].y; psum[v].z += acc[v].z; psum[v].w += acc[v].w;
+      }
+  }
+#pragma unroll
+  for (int v = 0; v < NV; ++v) { s_max[warp][v][lane] = pmax[v]; s_sum[warp][v][lane] = psum[v]; }
+  __syncthreads();
+  // thread t combines column t of every 128-column chunk over the 8 warps in warp order (fixed order)
+  const int n = n1 - n0;
+  for (int c = threadIdx.x; c < NV * 128; c += 256) {
+    const int v = c >> 7, cc = c & 127;
+    if (128 * v + cc >= H) continue;
+    float mx = -INFINITY, sm = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      mx = fmaxf(mx, reinterpret_cast<const float*>(&s_max[w][v][0])[cc]);
+      sm += reinterpret_cast<const float*>(&s_sum[w][v][0])[cc];
+    }
+    emb[gid * 2 * H + 128 * v + cc] = n > 0 ? mx : 0.f;
+    emb[gid * 2 * H + H + 128 * v + cc] = n > 0 ? sm / (float)n : 0.f;
+  }
+}
+
+// HCG_CFG_AGG_PATH: 0 = wide-row kernels when H >= 128, 1 = k_agg / k_pool only, 2 = wide-row kernels for any H % 4 == 0
+static bool agg_wide_ok(const HcgGraph* g, int H, const float* T, const float* out) {
+  const int ap = config_get(HCG_CFG_AGG_PATH);
+  if (ap == 1 || (H & 3) != 0 || H > 512 || g->edge_mask != nullptr) return false;
+  if ((reinterpret_cast<uintptr_t>(T) | reinterpret_cast<uintptr_t>(out)) % 16 != 0) return false;
+  return ap == 2 || H >= 128;
+}
+
+// out may be NULL only with emb (pooling variant: grid = graphs); emb == NULL: grid = rows / 8
+static int launch_agg_wide(const int32_t* rowptr, const int32_t* col, const float* dis, float fill, const float* T,
+                           const float* bias, float* out, int64_t N, int H, int act, float slope,
+                           const int32_t* graph_ptr, int64_t B, float* emb, cudaStream_t st) {
+  if (N == 0 || (emb && B == 0)) return HCG_OK;
+  const int nv = (H + 127) / 128;
+  const unsigned grid = (unsigned)(emb ? B : cdiv(N, 8));
+#define HCG_AGG_WIDE(NVV)                                                                                              \
+  do {                                                                                                                 \
+    if (emb) k_agg_wide<NVV, true><<<grid, 256, 0, st>>>(rowptr, col, dis, fill, T, bias, out, N, H, act, slope, graph_ptr, emb); \
+    else k_agg_wide<NVV, false><<<grid, 256, 0, st>>>(rowptr, col, dis, fill, T, bias, out, N, H, act, slope, graph_ptr, emb);    \
+  } while (0)
+  switch (nv) {
+    case 1: HCG_AGG_WIDE(1); break;
+    case 2: HCG_AGG_WIDE(2); break;
+    case 3: HCG_AGG_WIDE(3); break;
+    default: HCG_AGG_WIDE(4); break;
+  }
+#undef HCG_AGG_WIDE
+  HCG_LAUNCH_OK(st, "k_agg_wide");
+  return HCG_OK;
+}
+
 static int launch_agg(const int32_t* rowptr, const int32_t* col, const float* dis, const float* ew,
                       const float* selfw, float fill, const float* T, const float* bias, float* out,
                       int64_t N, int H, int act, float slope, cudaStream_t st, const int32_t* eid = nullptr,
@@ -868,20 +1028,29 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
   const float* h_in = x;
   int k_in = p->F;
   float* h_out = nullptr;
+  bool pooled = false;
   for (int l = 0; l < p->L && !fused_done; ++l) {
     rc = launch_gemm<true>(h_in, p->conv_w[l], w.T, N, k_in, H, EPI_NONE, nullptr, p->slope, st, w.wimg);
     if (rc) return rc;
     h_out = saved ? saved->acts[l] : w.act[l & 1];
     HCG_REQUIRE(h_out != nullptr, HCG_ERR_INVALID_ARG, "saved->acts[%d] is NULL", l);
     const bool weighted0 = (l == 0 && g->ew0 != nullptr);
-    rc = launch_agg(g->rowptr, g->col, weighted0 ? g->dis0 : g->dis, weighted0 ? g->ew0 : nullptr,
-                    weighted0 ? g->selfw0 : nullptr, g->fill, w.T, p->conv_b[l], h_out, N, H, 1, p->slope, st,
-                    g->eid, g->edge_mask);
+    if (!weighted0 && agg_wide_ok(g, H, w.T, h_out)) {
+      // whole-row kernel; the last layer pools in its epilogue and keeps its rows only for a backward
+      const bool last = l == p->L - 1 && B > 0;
+      rc = launch_agg_wide(g->rowptr, g->col, g->dis, g->fill, w.T, p->conv_b[l], last && !saved ? nullptr : h_out, N, H, 1,
+                           p->slope, g->graph_ptr, B, last ? emb : nullptr, st);
+      pooled = last;
+    } else {
+      rc = launch_agg(g->rowptr, g->col, weighted0 ? g->dis0 : g->dis, weighted0 ? g->ew0 : nullptr,
+                      weighted0 ? g->selfw0 : nullptr, g->fill, w.T, p->conv_b[l], h_out, N, H, 1, p->slope, st,
+                      g->eid, g->edge_mask);
+    }
     if (rc) return rc;
     h_in = h_out;
     k_in = H;
   }
-  if (B > 0 && !fused_done) {
+  if (B > 0 && !fused_done && !pooled) {
     int lpr = lanes_per_row(H, 1);
     k_pool<<<(unsigned)cdiv(B, 256 / lpr), 256, 0, st>>>(h_out, g->graph_ptr, B, H, lpr, emb);
     HCG_LAUNCH_OK(st, "k_pool");
@@ -1029,9 +1198,13 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
       HCG_LAUNCH_OK(st, "k_edge_dot");
     }
     // gT = Â^T · gA  (transposed CSR; no bias, no activation)
-    rc = launch_agg(g->t_rowptr, g->t_col, weighted0 ? g->dis0 : g->dis, weighted0 ? g->t_ew0 : nullptr,
-                    weighted0 ? g->selfw0 : nullptr, g->fill, w.gA, nullptr, w.gT, N, H, 0, p->slope, st,
-                    g->t_eid, g->edge_mask);
+    if (!weighted0 && agg_wide_ok(g, H, w.gA, w.gT))
+      rc = launch_agg_wide(g->t_rowptr, g->t_col, g->dis, g->fill, w.gA, nullptr, w.gT, N, H, 0, p->slope, g->graph_ptr, B,
+                           nullptr, st);
+    else
+      rc = launch_agg(g->t_rowptr, g->t_col, weighted0 ? g->dis0 : g->dis, weighted0 ? g->t_ew0 : nullptr,
+                      weighted0 ? g->selfw0 : nullptr, g->fill, w.gA, nullptr, w.gT, N, H, 0, p->slope, st,
+                      g->t_eid, g->edge_mask);
     if (rc) return rc;
     rc = launch_xty(w.gT, h_in, N, H, k_in, w.partial, grads->conv_w[l], st);
     if (rc) return rc;

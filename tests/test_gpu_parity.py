@@ -515,6 +515,59 @@ def test_tensor_core_gemm_forward_backward(hcg, gemm_path, forward_path, backwar
 
 
 # ------------------------------------------------------------------------------------------
+# whole-row aggregation of the layer-wise path (wide hidden layers), pooling in its last epilogue
+# ------------------------------------------------------------------------------------------
+@pytest.fixture
+def agg_path(hcg):
+    from hcatgnet_b200 import _lib
+    prev = []
+
+    def set_path(v):
+        prev.append(_lib.config_set(_lib.HCG_CFG_AGG_PATH, v))
+
+    yield set_path
+    if prev:
+        _lib.config_set(_lib.HCG_CFG_AGG_PATH, prev[0])
+
+
+@pytest.mark.parametrize("H,L,F,B,nmin,nmax", [(256, 4, 25, 33, 1, 50), (128, 2, 32, 700, 2, 60), (192, 3, 7, 64, 1, 40),
+                                               (64, 2, 25, 300, 1, 120), (136, 2, 9, 5, 1, 8), (256, 2, 25, 6, 100, 300)])
+def test_wide_row_aggregation_forward_backward(hcg, agg_path, gemm_path, forward_path, backward_path, H, L, F, B,
+                                                     nmin, nmax):
+    """k_agg_wide (a warp per whole row, pooled per graph in the last layer's epilogue, transposed CSR in the
+    backward) against k_agg + k_pool (same summation order: identical activations) and the oracle; 1..2
+    column chunks, partial chunks (H = 192, 136, 64), graphs from 1 to 300 nodes."""
+    from hcatgnet_b200.synth import synth_batch
+    b = synth_batch(B, n_features=F, seed=33, n_min=nmin, n_max=nmax)
+    sd = ref_gcn.init_state_dict(F, H, L, 2, 1, seed=4)
+    forward_path(1)
+    backward_path(1)
+    gemm_path(1)
+    params, _, _ = _sd_params(sd, "cuda")
+    dims = _dims(hcg, sd)
+    plan = hcg.collate(b.edge_index.cuda(), b.batch.cuda(), b.num_nodes, b.num_graphs, transpose=True)
+    x = b.x.cuda()
+    res = {}
+    for path in (1, 2):
+        agg_path(path)
+        with torch.no_grad():
+            o, e = hcg.gcn_apply(x, plan, dims, params)
+        o_s, e_s, saved = hcg.forward_raw(plan, x, dims, params, save=True)
+        res[path] = (o, e, o_s, e_s, [a.clone() for a in saved[0]])
+    o_ref, e_ref = ref_gcn.forward(sd, b.x, b.edge_index, b.batch, b.num_graphs)
+    assert _close(res[2][1].cpu(), e_ref) <= TOL and _close(res[2][0].cpu(), o_ref) <= TOL
+    assert _close(res[2][3].cpu(), e_ref) <= TOL and _close(res[2][2].cpu(), o_ref) <= TOL
+    for a1, a2 in zip(res[1][4], res[2][4]):
+        assert torch.equal(a1, a2)                       # same weights, same order of the sums
+    assert torch.equal(res[1][1][:, :H], res[2][1][:, :H])   # max pooling is order independent
+    assert _close(res[2][1].cpu(), res[1][1].cpu()) <= TOL
+    args = (sd, b.x, b.edge_index, b.batch, b.num_graphs, b.y)
+    _, g_ref, _ = _oracle_grads(*args)
+    _, g_res, _ = _cuda_grads(hcg, *args)
+    _assert_grads(g_res, g_ref)
+
+
+# ------------------------------------------------------------------------------------------
 # soft edge mask on every conv layer (explainers): forward and gradients against the fp64 oracle
 # ------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("rset,outer,inner,count", [("learning", 1, 2, 5), ("biaryl", 1, 2, 3)])
