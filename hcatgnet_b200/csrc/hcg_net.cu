@@ -261,105 +261,101 @@ static int lanes_per_row(int H, int vec) {
 // of the finished rows (reference model/gcn.py:65-66) - the last layer's k_pool pass over [N, H] disappears,
 // and in inference (out == NULL) so does the last layer's [N, H] store.
 // ------------------------------------------------------------------------------------------
-template <int NV>
-__device__ __forceinline__ void agg_wide_row(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
-                                             const float* __restrict__ dis, float fill, const float* __restrict__ T,
-                                             int64_t i, int H, int lane, const float4 (&b4)[NV], int act, float slope,
-                                             float4 (&acc)[NV]) {
-  const int beg = __ldg(rowptr + i), end = __ldg(rowptr + i + 1);
-  const float di = __ldg(dis + i);
+template <int NV, bool EXACT>
+__device__ __forceinline__ void agg_wide_fma(float4 (&acc)[NV], float w, const float* __restrict__ p, int H, int lane) {
+  float4 t[NV];
 #pragma unroll
-  for (int v = 0; v < NV; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-  const float* Tl = T + 4 * lane;
-  int k = beg;
-  for (; k + 2 <= end; k += 2) {  // two neighbours' rows in flight
-    const int j0 = __ldg(col + k), j1 = __ldg(col + k + 1);
-    const float w0 = __ldg(dis + j0) * di, w1 = __ldg(dis + j1) * di;
-    const float* p0 = Tl + (int64_t)j0 * H;
-    const float* p1 = Tl + (int64_t)j1 * H;
-    float4 t0[NV], t1[NV];
+  for (int v = 0; v < NV; ++v) t[v] = (EXACT || 128 * v + 4 * lane < H) ? ldg4(p + 128 * v) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-    for (int v = 0; v < NV; ++v) {
-      if (128 * v + 4 * lane < H) { t0[v] = ldg4(p0 + 128 * v); t1[v] = ldg4(p1 + 128 * v); }
-      else { t0[v] = make_float4(0.f, 0.f, 0.f, 0.f); t1[v] = t0[v]; }
-    }
-#pragma unroll
-    for (int v = 0; v < NV; ++v) {
-      acc[v].x = fmaf(w0, t0[v].x, acc[v].x); acc[v].y = fmaf(w0, t0[v].y, acc[v].y);
-      acc[v].z = fmaf(w0, t0[v].z, acc[v].z); acc[v].w = fmaf(w0, t0[v].w, acc[v].w);
-    }
-#pragma unroll
-    for (int v = 0; v < NV; ++v) {
-      acc[v].x = fmaf(w1, t1[v].x, acc[v].x); acc[v].y = fmaf(w1, t1[v].y, acc[v].y);
-      acc[v].z = fmaf(w1, t1[v].z, acc[v].z); acc[v].w = fmaf(w1, t1[v].w, acc[v].w);
-    }
+  for (int v = 0; v < NV; ++v) {
+    acc[v].x = fmaf(w, t[v].x, acc[v].x); acc[v].y = fmaf(w, t[v].y, acc[v].y);
+    acc[v].z = fmaf(w, t[v].z, acc[v].z); acc[v].w = fmaf(w, t[v].w, acc[v].w);
   }
-  if (k < end) {
-    const int j0 = __ldg(col + k);
-    const float w0 = __ldg(dis + j0) * di;
-    const float* p0 = Tl + (int64_t)j0 * H;
-#pragma unroll
-    for (int v = 0; v < NV; ++v)
-      if (128 * v + 4 * lane < H) {
-        const float4 t = ldg4(p0 + 128 * v);
-        acc[v].x = fmaf(w0, t.x, acc[v].x); acc[v].y = fmaf(w0, t.y, acc[v].y);
-        acc[v].z = fmaf(w0, t.z, acc[v].z); acc[v].w = fmaf(w0, t.w, acc[v].w);
-      }
-  }
-  const float ws = (di * fill) * di;
-  const float* ps = Tl + i * H;
-#pragma unroll
-  for (int v = 0; v < NV; ++v)
-    if (128 * v + 4 * lane < H) {
-      const float4 t = ldg4(ps + 128 * v);
-      acc[v].x = fmaf(ws, t.x, acc[v].x) + b4[v].x; acc[v].y = fmaf(ws, t.y, acc[v].y) + b4[v].y;
-      acc[v].z = fmaf(ws, t.z, acc[v].z) + b4[v].z; acc[v].w = fmaf(ws, t.w, acc[v].w) + b4[v].w;
-      if (act) {
-        acc[v].x = lrelu(acc[v].x, slope); acc[v].y = lrelu(acc[v].y, slope);
-        acc[v].z = lrelu(acc[v].z, slope); acc[v].w = lrelu(acc[v].w, slope);
-      }
-    }
 }
 
-template <int NV, bool POOL>
+// A warp finishes `rows` (1..R) consecutive rows starting at i0.  The rows' CSR slots are contiguous, so the
+// row pointers, the first 32 column indices and their dis[] values are fetched by ONE coalesced load each and
+// handed out by shuffles: three dependent memory latencies per tile instead of three per row.
+template <int NV, int R, bool EXACT, bool POOL>
+__device__ __forceinline__ void agg_wide_tile(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                                              const float* __restrict__ dis, float fill, const float* __restrict__ T,
+                                              int64_t i0, int rows, int H, int lane, const float4 (&b4)[NV], int act,
+                                              float slope, float* __restrict__ out, float4 (&pmax)[NV], float4 (&psum)[NV]) {
+  constexpr unsigned kFull = 0xffffffffu;
+  int rp = 0;
+  float drow = 0.f;
+  if (lane <= rows) rp = __ldg(rowptr + i0 + lane);
+  if (lane < rows) drow = __ldg(dis + i0 + lane);
+  const int beg0 = __shfl_sync(kFull, rp, 0), end_all = __shfl_sync(kFull, rp, rows);
+  int jl = 0;
+  float wl = 0.f;
+  if (beg0 + lane < end_all) { jl = __ldg(col + beg0 + lane); wl = __ldg(dis + jl); }
+  const float* Tl = T + 4 * lane;
+#pragma unroll 1
+  for (int r = 0; r < rows; ++r) {
+    const int beg = __shfl_sync(kFull, rp, r), end = __shfl_sync(kFull, rp, r + 1);
+    const float di = __shfl_sync(kFull, drow, r);
+    float4 acc[NV];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+    for (int k = beg; k < end; ++k) {
+      const int sl = k - beg0;
+      int j;
+      float w;
+      if (sl < 32) { j = __shfl_sync(kFull, jl, sl); w = __shfl_sync(kFull, wl, sl); }   // warp-uniform branch
+      else { j = __ldg(col + k); w = __ldg(dis + j); }
+      agg_wide_fma<NV, EXACT>(acc, w * di, Tl + (int64_t)j * H, H, lane);
+    }
+    const int64_t i = i0 + r;
+    agg_wide_fma<NV, EXACT>(acc, (di * fill) * di, Tl + i * H, H, lane);
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+      if (EXACT || 128 * v + 4 * lane < H) {
+        acc[v].x += b4[v].x; acc[v].y += b4[v].y; acc[v].z += b4[v].z; acc[v].w += b4[v].w;
+        if (act) {
+          acc[v].x = lrelu(acc[v].x, slope); acc[v].y = lrelu(acc[v].y, slope);
+          acc[v].z = lrelu(acc[v].z, slope); acc[v].w = lrelu(acc[v].w, slope);
+        }
+        if (!POOL || out) *reinterpret_cast<float4*>(out + i * H + 128 * v + 4 * lane) = acc[v];
+        if (POOL) {
+          pmax[v].x = fmaxf(pmax[v].x, acc[v].x); pmax[v].y = fmaxf(pmax[v].y, acc[v].y);
+          pmax[v].z = fmaxf(pmax[v].z, acc[v].z); pmax[v].w = fmaxf(pmax[v].w, acc[v].w);
+          psum[v].x += acc[v].x; psum[v].y += acc[v].y; psum[v].z += acc[v].z; psum[v].w += acc[v].w;
+        }
+      }
+  }
+}
+
+constexpr int kAggTileRows = 8;   // rows per warp tile, row-parallel variant
+constexpr int kAggPoolRows = 4;   // rows per warp tile inside one graph (pooling variant: finer, for balance)
+
+template <int NV, bool EXACT, bool POOL>
 __global__ void __launch_bounds__(256)
 k_agg_wide(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ dis, float fill,
            const float* __restrict__ T, const float* __restrict__ bias, float* __restrict__ out, int64_t N, int H, int act,
            float slope, const int32_t* __restrict__ graph_ptr, float* __restrict__ emb) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float4 b4[NV], acc[NV];
+  float4 b4[NV], pmax[NV], psum[NV];
 #pragma unroll
-  for (int v = 0; v < NV; ++v)
+  for (int v = 0; v < NV; ++v) {
     b4[v] = (bias && 128 * v + 4 * lane < H) ? ldg4(bias + 128 * v + 4 * lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+    pmax[v] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    psum[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   if (!POOL) {
-    const int64_t i = (int64_t)blockIdx.x * 8 + warp;
-    if (i >= N) return;
-    agg_wide_row<NV>(rowptr, col, dis, fill, T, i, H, lane, b4, act, slope, acc);
-#pragma unroll
-    for (int v = 0; v < NV; ++v)
-      if (128 * v + 4 * lane < H) *reinterpret_cast<float4*>(out + i * H + 128 * v + 4 * lane) = acc[v];
+    const int64_t i0 = ((int64_t)blockIdx.x * 8 + warp) * kAggTileRows;
+    if (i0 >= N) return;
+    const int rows = (int)min((int64_t)kAggTileRows, N - i0);
+    agg_wide_tile<NV, kAggTileRows, EXACT, false>(rowptr, col, dis, fill, T, i0, rows, H, lane, b4, act, slope, out, pmax, psum);
     return;
   }
   __shared__ float4 s_max[8][NV][32], s_sum[8][NV][32];
   const int64_t gid = blockIdx.x;
   const int n0 = graph_ptr[gid], n1 = graph_ptr[gid + 1];
-  float4 pmax[NV], psum[NV];
-#pragma unroll
-  for (int v = 0; v < NV; ++v) {
-    pmax[v] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
-    psum[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  for (int64_t i = n0 + warp; i < n1; i += 8) {
-    agg_wide_row<NV>(rowptr, col, dis, fill, T, i, H, lane, b4, act, slope, acc);
-#pragma unroll
-    for (int v = 0; v < NV; ++v)
-      if (128 * v + 4 * lane < H) {
-        if (out) *reinterpret_cast<float4*>(out + i * H + 128 * v + 4 * lane) = acc[v];
-        pmax[v].x = fmaxf(pmax[v].x, acc[v].x); pmax[v].y = fmaxf(pmax[v].y, acc[v].y);
-        pmax[v].z = fmaxf(pmax[v].z, acc[v].z); pmax[v].w = fmaxf(pmax[v].w, acc[v].w);
-        psum[v].x += acc[v].x; psum[v].y += acc[v].y; psum[v].z += acc[v].z; psum[v].w += acc[v].w;
-      }
-  }
+  for (int i0 = n0 + warp * kAggPoolRows; i0 < n1; i0 += 8 * kAggPoolRows)
+    agg_wide_tile<NV, kAggPoolRows, EXACT, true>(rowptr, col, dis, fill, T, i0, min(kAggPoolRows, n1 - i0), H, lane, b4, act,
+                                                 slope, out, pmax, psum);
 #pragma unroll
   for (int v = 0; v < NV; ++v) { s_max[warp][v][lane] = pmax[v]; s_sum[warp][v][lane] = psum[v]; }
   __syncthreads();
@@ -393,11 +389,16 @@ static int launch_agg_wide(const int32_t* rowptr, const int32_t* col, const floa
                            const int32_t* graph_ptr, int64_t B, float* emb, cudaStream_t st) {
   if (N == 0 || (emb && B == 0)) return HCG_OK;
   const int nv = (H + 127) / 128;
-  const unsigned grid = (unsigned)(emb ? B : cdiv(N, 8));
+  const unsigned grid = (unsigned)(emb ? B : cdiv(N, 8 * kAggTileRows));
+  const bool exact = H % 128 == 0;
+#define HCG_AGG_WIDE2(NVV, EX)                                                                                          \
+  do {                                                                                                                 \
+    if (emb) k_agg_wide<NVV, EX, true><<<grid, 256, 0, st>>>(rowptr, col, dis, fill, T, bias, out, N, H, act, slope, graph_ptr, emb); \
+    else k_agg_wide<NVV, EX, false><<<grid, 256, 0, st>>>(rowptr, col, dis, fill, T, bias, out, N, H, act, slope, graph_ptr, emb);    \
+  } while (0)
 #define HCG_AGG_WIDE(NVV)                                                                                              \
   do {                                                                                                                 \
-    if (emb) k_agg_wide<NVV, true><<<grid, 256, 0, st>>>(rowptr, col, dis, fill, T, bias, out, N, H, act, slope, graph_ptr, emb); \
-    else k_agg_wide<NVV, false><<<grid, 256, 0, st>>>(rowptr, col, dis, fill, T, bias, out, N, H, act, slope, graph_ptr, emb);    \
+    if (exact) HCG_AGG_WIDE2(NVV, true); else HCG_AGG_WIDE2(NVV, false);                                               \
   } while (0)
   switch (nv) {
     case 1: HCG_AGG_WIDE(1); break;
@@ -405,6 +406,7 @@ static int launch_agg_wide(const int32_t* rowptr, const int32_t* col, const floa
     case 3: HCG_AGG_WIDE(3); break;
     default: HCG_AGG_WIDE(4); break;
   }
+#undef HCG_AGG_WIDE2
 #undef HCG_AGG_WIDE
   HCG_LAUNCH_OK(st, "k_agg_wide");
   return HCG_OK;
