@@ -361,6 +361,33 @@ def main():
                        + h.y.numel() * 4 for h in host]))
     d2h = a.batch * N_CLS * 4 if a.mode == "infer" else 4
 
+    # ---- the same, with the batches in the packed wire format ----------------
+    # Node features with the block structure of the reference featuriser (24 one-hot / binary columns -> u8,
+    # temperature -> f32), endpoints local to their graph in u8: ~4x fewer bytes over PCIe, expanded on the
+    # device by hcg_unpack_batch into the very tensors PyG's collate would produce.  Same graphs as `host`.
+    e2e_packed = None
+    if a.mode == "infer":
+        packed = []
+        for i in range(POOL):
+            pb = synth_batch(a.batch, F_IN, seed=20232023 + 1000 * rank + i, features="featuriser")
+            packed.append(pkg.PackedDataset.from_arrays(pb.x.numpy(), pb.edge_index.numpy(), pb.ptr.numpy(), pb.y.numpy(),
+                                                        pinned=True))
+
+        def run_packed(steps):
+            n = 0
+            for out, _, _ in pkg.predict_stream(model, (packed[i % POOL] for i in range(steps))):
+                n += out.shape[0]
+            return n
+
+        run_packed(a.warmup)
+        ms_p = timed(run_packed, a.steps, whole=True)
+        e2e_packed = {"value": graphs_total / (ms_p * 1e-3), "unit": UNIT, "ms_per_step": ms_p / a.steps,
+                      "h2d_bytes_per_step": int(np.mean([p.nbytes for p in packed])) + 3 * 8 * (a.batch + 1),
+                      "d2h_bytes_per_step": d2h,
+                      "api": "hcatgnet_b200.predict_stream over PackedDataset chunks (one image copy + hcg_unpack_batch per step)",
+                      "x": "featuriser-shaped: 24 one-hot/binary columns as u8 + 1 f32 column (lossless)"}
+        del packed
+
     # ---- per-kernel device time (separate pass, same inputs) + roofline of the dominant kernel -
     roofline, kernels = None, None
     if world > 1 and a.mode == "train" and not a.no_profile and rank != 0:
@@ -426,6 +453,7 @@ def main():
                     "ms_per_step": ms_e2e / a.steps, "wall_ms_per_step": wall_e2e / a.steps,
                     "api": "hcatgnet_b200.predict_stream (H2D of batch i+1 overlaps the kernels of batch i)"
                     if a.mode == "infer" else "hcatgnet_b200.DevicePrefetcher + FusedTrainer.step"},
+            "e2e_packed": e2e_packed,
             "gpu_launches": int(launches),
             "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline,
         }

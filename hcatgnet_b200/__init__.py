@@ -9,6 +9,7 @@ from .call_methods import make_network  # noqa: F401
 from .data import Batch, DataLoader  # noqa: F401
 from .model import GCN, GCN_explain  # noqa: F401
 from .options import default_options  # noqa: F401
+from .packed import DeviceGraphStore, PackedDataset, convert_processed_dir  # noqa: F401
 from .screen import DevicePrefetcher, predict_ensemble_stream, predict_network_stream, predict_stream  # noqa: F401
 from .trainer import FusedTrainer  # noqa: F401
 

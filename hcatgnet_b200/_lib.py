@@ -63,6 +63,13 @@ class HcgError(RuntimeError):
 
 
 _lock = threading.Lock()
+class HcgPackedStore(C.Structure):
+    _fields_ = [("G", C.c_int64), ("N", C.c_int64), ("E", C.c_int64),
+                ("F", C.c_int32), ("Fu", C.c_int32), ("Ff", C.c_int32), ("edge_kind", C.c_int32),
+                ("col_slot", _fp), ("node_ptr", _fp), ("edge_ptr", _fp), ("y", _fp), ("xu8", _fp), ("xf32", _fp),
+                ("edges", _fp)]
+
+
 _lib = None
 
 # name -> (restype, argtypes); the test-suite checks this table against include/hcg.h
@@ -91,6 +98,8 @@ SIGNATURES = {
     "hcg_gcn_backward": (C.c_int, [C.POINTER(HcgGraph), _fp, C.POINTER(HcgParams), C.POINTER(HcgSaved), _fp, _fp, _fp,
                                    C.POINTER(HcgGrads), _fp, _fp, C.c_size_t, _fp]),
     "hcg_batch_from_ptr": (C.c_int, [_fp, C.c_int64, C.c_int64, _fp, _fp]),
+    "hcg_unpack_batch": (C.c_int, [C.POINTER(HcgPackedStore), _fp, C.c_int64, C.c_int64, _fp, _fp, _fp, _fp, C.c_int64,
+                                   _fp, _fp, _fp]),
     "hcg_rmse_seed": (C.c_int, [_fp, _fp, C.c_int64, C.c_int, _fp, _fp, _fp]),
     "hcg_adam_step": (C.c_int, [_fp, _fp, _fp, _fp, C.c_int64, _fp, C.c_float, C.c_float, C.c_float, C.c_float,
                                 C.c_int64, _fp, _fp]),

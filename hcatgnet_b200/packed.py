@@ -1,0 +1,315 @@
+"""Packed on-disk / on-wire graph format and its device-side loader.
+
+The reference keeps one pickled ``Data`` object per reaction (``reaction_<i>.pt``, reference
+data/datasets.py:74-78, data/rhcaa.py:90-92) and collates with Python per batch
+(``DataLoader``, reference call_methods.py:15-47): 668 file opens + unpickles per pass, and a host
+batch of 100 B per node + 16 B per directed edge.  Here the whole set is ONE binary image:
+
+    header (128 B) | col_slot i32[F] | node_ptr i64[G+1] | edge_ptr i64[G+1] | y f32[G] | idx i64[G] |
+    fold i32[G] | xu8 u8[N, Fu] | xf32 f32[N, Ff] | edges uK[E, 2]          (every section 64-byte aligned)
+
+* node features are split per COLUMN: a column whose values are all integers in 0..255 (the one-hot / count
+  columns of the featuriser, reference data/rhcaa.py:112-150) is stored as u8, the others (temperature)
+  stay f32 — lossless by construction, checked at pack time;
+* edges are (src, dst) pairs LOCAL to their graph in u8 (graphs <= 256 nodes), u16 or i32, graph by graph.
+
+RhCAA-shaped graphs take ~2.7 KB instead of ~11.9 KB.  The image is consumed on the GPU:
+``DeviceGraphStore`` keeps it resident (the 10 M-graph screening set is ~27 GB of 180 GB HBM) and
+``batch(ids)`` assembles any selection of graphs — a shuffled mini-batch, a cross-validation fold — with one
+kernel (``hcg_unpack_batch``, csrc/hcg_packed.cu) into exactly the tensors PyG's collate would have produced
+(x f32, edge_index i64 with node offsets, batch, ptr, y): no host collate, no per-step PCIe traffic beyond
+the id list.  For sets larger than HBM the same image format is the wire format: ship a chunk, unpack it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import glob
+import os
+import re
+import sys
+import types
+from typing import Sequence
+
+import numpy as np
+import torch
+
+from . import _lib
+from .data import Batch, _field
+
+MAGIC = b"HCGPACK1"
+HEADER_BYTES = 128
+_ALIGN = 64
+_EDGE_DTYPES = {1: np.uint8, 2: np.uint16, 4: np.int32}
+
+
+def _aligned(n: int) -> int:
+    return (n + _ALIGN - 1) // _ALIGN * _ALIGN
+
+
+def _sections(G: int, N: int, E: int, F: int, Fu: int, Ff: int, ek: int):
+    """(name, dtype, shape) in file order."""
+    return [("col_slot", np.int32, (F,)), ("node_ptr", np.int64, (G + 1,)), ("edge_ptr", np.int64, (G + 1,)),
+            ("y", np.float32, (G,)), ("idx", np.int64, (G,)), ("fold", np.int32, (G,)),
+            ("xu8", np.uint8, (N, Fu)), ("xf32", np.float32, (N, Ff)), ("edges", _EDGE_DTYPES[ek], (E, 2))]
+
+
+def _layout(G, N, E, F, Fu, Ff, ek):
+    off, out = HEADER_BYTES, {}
+    for name, dt, shape in _sections(G, N, E, F, Fu, Ff, ek):
+        nbytes = int(np.prod(shape, dtype=np.int64)) * np.dtype(dt).itemsize
+        out[name] = (off, dt, shape, nbytes)
+        off = _aligned(off + nbytes)
+    return out, off
+
+
+class PackedDataset:
+    """The packed image as typed numpy views over one byte buffer (in memory or memory-mapped)."""
+
+    def __init__(self, blob: np.ndarray):
+        assert blob.dtype == np.uint8 and blob.ndim == 1
+        if bytes(blob[:8]) != MAGIC:
+            raise ValueError("not a packed graph image (bad magic)")
+        h = blob[8:8 + 8 * 8].view(np.int64)
+        self.G, self.N, self.E, self.F, self.Fu, self.Ff, self.edge_kind, self.max_graph_nodes = (int(v) for v in h)
+        self.layout, total = _layout(self.G, self.N, self.E, self.F, self.Fu, self.Ff, self.edge_kind)
+        if blob.size < total:
+            raise ValueError(f"packed graph image truncated: {blob.size} of {total} bytes")
+        self.blob = blob[:total]
+        for name, (off, dt, shape, nbytes) in self.layout.items():
+            setattr(self, name, self.blob[off:off + nbytes].view(dt).reshape(shape))
+
+    # ------------------------------------------------------------------ construction
+    @classmethod
+    def from_arrays(cls, x, edge_index, ptr, y=None, idx=None, fold=None, pinned: bool = False) -> "PackedDataset":
+        """From a collated set: ``x[N,F]`` f32, ``edge_index[2,E]`` with GLOBAL node numbers listed graph by
+        graph (what ``Batch.from_data_list`` / PyG's collate produce), ``ptr[G+1]``."""
+        x = np.ascontiguousarray(np.asarray(x, dtype=np.float32))
+        ei = np.asarray(edge_index, dtype=np.int64)
+        ptr = np.asarray(ptr, dtype=np.int64)
+        G, N, E, F = ptr.size - 1, x.shape[0], ei.shape[1], x.shape[1]
+        assert ptr[0] == 0 and ptr[-1] == N, "ptr does not cover x"
+        gsrc = np.searchsorted(ptr, ei[0], side="right") - 1 if E else np.zeros(0, np.int64)
+        gdst = np.searchsorted(ptr, ei[1], side="right") - 1 if E else np.zeros(0, np.int64)
+        if E and (np.any(gsrc != gdst) or np.any(np.diff(gsrc) < 0) or ei.min() < 0 or ei.max() >= N):
+            raise ValueError("edges must stay inside their graph and be listed graph by graph")
+        edge_ptr = np.zeros(G + 1, np.int64)
+        np.cumsum(np.bincount(gsrc, minlength=G), out=edge_ptr[1:])
+        sizes = np.diff(ptr)
+        nmax = int(sizes.max()) if G else 0
+        ek = 1 if nmax <= 256 else 2 if nmax <= 65536 else 4
+        # lossless column split
+        as_u8 = np.array([bool(np.all((x[:, c] >= 0) & (x[:, c] <= 255) & (x[:, c] == np.floor(x[:, c])))) for c in range(F)],
+                         dtype=bool) if N else np.ones(F, bool)
+        Fu, Ff = int(as_u8.sum()), int((~as_u8).sum())
+        col_slot = np.empty(F, np.int32)
+        col_slot[as_u8] = np.arange(Fu, dtype=np.int32)
+        col_slot[~as_u8] = ~np.arange(Ff, dtype=np.int32)      # negative: ~slot in the f32 block
+        layout, total = _layout(G, N, E, F, Fu, Ff, ek)
+        blob_t = torch.zeros(total, dtype=torch.uint8)
+        if pinned:
+            blob_t = blob_t.pin_memory()
+        blob = blob_t.numpy()
+        blob[:8] = np.frombuffer(MAGIC, np.uint8)
+        blob[8:72].view(np.int64)[:] = [G, N, E, F, Fu, Ff, ek, nmax]
+        self = cls(blob)
+        self._owner = blob_t
+        self.col_slot[:] = col_slot
+        self.node_ptr[:] = ptr
+        self.edge_ptr[:] = edge_ptr
+        self.y[:] = 0 if y is None else np.asarray(y, np.float32).reshape(-1)
+        self.idx[:] = np.arange(G) if idx is None else np.asarray(idx, np.int64).reshape(-1)
+        self.fold[:] = -1 if fold is None else np.asarray(fold, np.int32).reshape(-1)
+        self.xu8[:] = x[:, as_u8].astype(np.uint8)
+        self.xf32[:] = x[:, ~as_u8]
+        if E:
+            self.edges[:, 0] = (ei[0] - ptr[gsrc]).astype(self.edges.dtype)
+            self.edges[:, 1] = (ei[1] - ptr[gsrc]).astype(self.edges.dtype)
+        return self
+
+    @classmethod
+    def from_graphs(cls, graphs: Sequence, pinned: bool = False) -> "PackedDataset":
+        """From a list of per-graph records (``x``, ``edge_index`` local, optional ``y`` / ``idx`` / ``fold``)."""
+        b = Batch.from_data_list(graphs)
+        folds = [_field(g, "fold") for g in graphs]
+        fold = None if any(f is None for f in folds) else [int(f) for f in folds]
+        return cls.from_arrays(b.x.numpy(), b.edge_index.numpy(), b.ptr.numpy(), None if b.y is None else b.y.numpy(),
+                               None if b.idx is None else b.idx.numpy(), fold, pinned=pinned)
+
+    # ------------------------------------------------------------------ file I/O
+    def save(self, path: str) -> None:
+        with open(path, "wb") as f:
+            f.write(self.blob.tobytes())
+
+    @classmethod
+    def load(cls, path: str, mmap: bool = True) -> "PackedDataset":
+        return cls(np.memmap(path, dtype=np.uint8, mode="r") if mmap else np.fromfile(path, dtype=np.uint8))
+
+    @property
+    def nbytes(self) -> int:
+        return int(self.blob.size)
+
+    # ------------------------------------------------------------------ host decoder (format reference)
+    def unpack_host(self, ids=None) -> Batch:
+        """numpy decoder of the format: the batch ``Batch.from_data_list`` would build from graphs ``ids``."""
+        ids = np.arange(self.G, dtype=np.int64) if ids is None else np.asarray(ids, dtype=np.int64).reshape(-1)
+        n = self.node_ptr[ids + 1] - self.node_ptr[ids]
+        e = self.edge_ptr[ids + 1] - self.edge_ptr[ids]
+        ptr = np.zeros(ids.size + 1, np.int64)
+        np.cumsum(n, out=ptr[1:])
+        rows = np.concatenate([np.arange(self.node_ptr[g], self.node_ptr[g + 1]) for g in ids]) if ids.size else np.zeros(0, np.int64)
+        slots = np.concatenate([np.arange(self.edge_ptr[g], self.edge_ptr[g + 1]) for g in ids]) if ids.size else np.zeros(0, np.int64)
+        x = np.empty((rows.size, self.F), np.float32)
+        u8c = self.col_slot >= 0
+        x[:, u8c] = self.xu8[rows][:, self.col_slot[u8c]]
+        x[:, ~u8c] = self.xf32[rows][:, ~self.col_slot[~u8c]]
+        ei = self.edges[slots].astype(np.int64).T + np.repeat(ptr[:-1], e)[None, :]
+        batch = np.repeat(np.arange(ids.size, dtype=np.int64), n)
+        return Batch(torch.from_numpy(x), torch.from_numpy(np.ascontiguousarray(ei)), torch.from_numpy(batch),
+                     torch.from_numpy(ptr), torch.from_numpy(self.y[ids].copy()), torch.from_numpy(self.idx[ids].copy()),
+                     ids.size, edges_grouped=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+# converter from the reference's processed directory (one torch zip-pickle per reaction)
+# ---------------------------------------------------------------------------------------------------
+class _Stub:
+    """Stand-in for the torch_geometric classes inside the pickles: keeps whatever state arrives."""
+
+    def __init__(self, *a, **k):
+        pass
+
+    def __setstate__(self, state):
+        self.__dict__["_state"] = state
+        if isinstance(state, dict):
+            self.__dict__.update(state)
+
+
+_PYG_CLASSES = {"torch_geometric.data.data": ("Data", "DataEdgeAttr", "DataTensorAttr"),
+                "torch_geometric.data.storage": ("GlobalStorage", "BaseStorage", "NodeStorage", "EdgeStorage")}
+
+
+def load_reaction_file(path: str) -> dict:
+    """One ``reaction_<i>.pt`` -> its field dict (x, edge_index, y, idx, fold, ...), without torch_geometric:
+    the pickles' only foreign globals are PyG's Data / storage classes, replaced by stubs while loading."""
+    added = []
+    try:
+        for mod, names in _PYG_CLASSES.items():
+            parts = mod.split(".")
+            for k in range(1, len(parts) + 1):
+                name = ".".join(parts[:k])
+                if name not in sys.modules:
+                    sys.modules[name] = types.ModuleType(name)
+                    added.append(name)
+            for n in names:
+                if not hasattr(sys.modules[mod], n):
+                    setattr(sys.modules[mod], n, type(n, (_Stub,), {"__module__": mod}))
+        obj = torch.load(path, map_location="cpu", weights_only=False)
+    finally:
+        for name in added:
+            sys.modules.pop(name, None)
+    store = getattr(obj, "_store", obj)
+    mapping = getattr(store, "_mapping", None)
+    if mapping is None and isinstance(getattr(store, "_state", None), dict):
+        mapping = store._state.get("_mapping")
+    if not isinstance(mapping, dict):
+        raise ValueError(f"{path}: no field mapping found in the pickled Data object")
+    return mapping
+
+
+def convert_processed_dir(processed_dir: str, out_path: str | None = None) -> PackedDataset:
+    """All ``reaction_<i>.pt`` of a reference ``processed/`` directory, in index order (stray copies such as
+    ``reaction_12 2.pt`` are skipped), into one packed image (optionally written to ``out_path``)."""
+    files = []
+    for f in glob.glob(os.path.join(processed_dir, "reaction_*.pt")):
+        m = re.fullmatch(r"reaction_(\d+)\.pt", os.path.basename(f))
+        if m:
+            files.append((int(m.group(1)), f))
+    if not files:
+        raise FileNotFoundError(f"no reaction_<i>.pt under {processed_dir}")
+    graphs = []
+    for i, f in sorted(files):
+        d = load_reaction_file(f)
+        graphs.append({"x": d["x"], "edge_index": d["edge_index"], "y": d.get("y"), "idx": d.get("idx", i),
+                       "fold": d.get("fold", -1)})
+    ds = PackedDataset.from_graphs(graphs)
+    if out_path:
+        ds.save(out_path)
+    return ds
+
+
+# ---------------------------------------------------------------------------------------------------
+# device side
+# ---------------------------------------------------------------------------------------------------
+class DeviceGraphStore:
+    """A packed image resident in device memory + ``batch(ids)``: any selection of its graphs as a collated
+    device ``Batch`` (one ``hcg_unpack_batch`` launch; the only host->device traffic is the id / offset lists).
+
+    ``from_blob`` wraps an image that is ALREADY on the device (a chunk shipped with one ``copy_``), with the
+    host copy supplying the sizes."""
+
+    def __init__(self, ds: PackedDataset, device=None, blob_dev: torch.Tensor | None = None):
+        self.ds = ds
+        self.device = torch.device(device if device is not None else "cuda")
+        _lib.load()     # raises if libhcg.so is missing: there is no host fallback for the loader
+        if blob_dev is None:
+            host = torch.from_numpy(np.ascontiguousarray(ds.blob))
+            blob_dev = host.to(self.device)
+        assert blob_dev.dtype == torch.uint8 and blob_dev.numel() >= ds.nbytes and blob_dev.data_ptr() % _ALIGN == 0
+        self.blob_dev = blob_dev
+        self._bind()
+
+    @classmethod
+    def from_blob(cls, ds: PackedDataset, blob_dev: torch.Tensor) -> "DeviceGraphStore":
+        return cls(ds, blob_dev.device, blob_dev)
+
+    def _bind(self):
+        base = self.blob_dev.data_ptr()
+        s = _lib.HcgPackedStore()
+        s.G, s.N, s.E = self.ds.G, self.ds.N, self.ds.E
+        s.F, s.Fu, s.Ff, s.edge_kind = self.ds.F, self.ds.Fu, self.ds.Ff, self.ds.edge_kind
+        for name in ("col_slot", "node_ptr", "edge_ptr", "y", "xu8", "xf32", "edges"):
+            setattr(s, name, base + self.ds.layout[name][0])
+        self.c_store = s
+
+    def rebind(self, ds: PackedDataset, blob_dev: torch.Tensor | None = None) -> "DeviceGraphStore":
+        """Point the store at another image of the stream (same device buffer refilled, or a new one)."""
+        self.ds = ds
+        if blob_dev is not None:
+            self.blob_dev = blob_dev
+        self._bind()
+        return self
+
+    def batch(self, ids=None, with_batch_vector: bool = True) -> Batch:
+        """``ids``: sequence / numpy / CPU tensor of graph numbers (repeats allowed); None = all, in order."""
+        ds, dev = self.ds, self.device
+        if ids is None:
+            ids_np, n, e = None, np.diff(ds.node_ptr), np.diff(ds.edge_ptr)
+        else:
+            ids_np = np.ascontiguousarray(np.asarray(ids, dtype=np.int64).reshape(-1))
+            if ids_np.size and (ids_np.min() < 0 or ids_np.max() >= ds.G):
+                raise IndexError(f"graph id out of range [0, {ds.G})")
+            n = ds.node_ptr[ids_np + 1] - ds.node_ptr[ids_np]
+            e = ds.edge_ptr[ids_np + 1] - ds.edge_ptr[ids_np]
+        B = int(n.size)
+        meta = torch.empty(3, B + 1, dtype=torch.int64).pin_memory() if dev.type == "cuda" else torch.empty(3, B + 1, dtype=torch.int64)
+        m = meta.numpy()
+        m[0, 0] = m[1, 0] = 0
+        np.cumsum(n, out=m[0, 1:])
+        np.cumsum(e, out=m[1, 1:])
+        m[2, :B] = ids_np if ids_np is not None else 0
+        N_out, E_out = int(m[0, B]), int(m[1, B])
+        meta_d = meta.to(dev, non_blocking=True)
+        x = torch.empty(N_out, ds.F, dtype=torch.float32, device=dev)
+        ei = torch.empty(2, E_out, dtype=torch.int64, device=dev)
+        bvec = torch.empty(N_out, dtype=torch.int64, device=dev) if with_batch_vector else None
+        y = torch.empty(B, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.load().hcg_unpack_batch(
+                C.byref(self.c_store), meta_d[2].data_ptr() if ids_np is not None else None, 0, B,
+                meta_d[0].data_ptr(), meta_d[1].data_ptr(), x.data_ptr(), ei.data_ptr(), E_out,
+                bvec.data_ptr() if bvec is not None else None, y.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+        idx = torch.from_numpy(ds.idx[ids_np].copy() if ids_np is not None else np.array(ds.idx))
+        out = Batch(x, ei, bvec, meta_d[0], y, idx, B, edges_grouped=True)
+        out.max_graph_nodes = int(n.max()) if B else 0
+        out._keepalive = meta_d
+        return out

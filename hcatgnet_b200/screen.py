@@ -16,10 +16,13 @@ import torch
 
 from . import ops
 from .data import Batch
+from .packed import DeviceGraphStore, PackedDataset
 
 
 class DevicePrefetcher:
     """Iterates an iterable of host ``Batch`` objects as device batches, ``depth`` copies ahead.
+    An item may also be a ``PackedDataset`` chunk (packed wire format, ~4x fewer bytes per graph): its image
+    crosses PCIe as ONE copy and is expanded on the device by ``hcg_unpack_batch``.
 
     Copies are issued on a private stream (pinned host memory makes them truly asynchronous);
     the consumer's current stream is made to wait on each batch's copy event when it is handed
@@ -38,6 +41,17 @@ class DevicePrefetcher:
             h = next(self.batches)
         except StopIteration:
             return False
+        if isinstance(h, PackedDataset):
+            with torch.cuda.stream(self.copy_stream):
+                owner = getattr(h, "_owner", None)     # the pinned torch buffer behind an image packed with pinned=True
+                blob_h = owner[:h.nbytes] if owner is not None else torch.from_numpy(h.blob)
+                store = DeviceGraphStore.from_blob(h, blob_h.to(self.device, non_blocking=True))
+                d = store.batch(None)
+                d._store = store
+                ev = torch.cuda.Event()
+                ev.record(self.copy_stream)
+            self.queue.append((d, ev, h))
+            return True
         with torch.cuda.stream(self.copy_stream):
             mv = lambda t: None if t is None else t.to(self.device, non_blocking=True)  # noqa: E731
             ptr = getattr(h, "ptr", None)
@@ -63,7 +77,9 @@ class DevicePrefetcher:
             d, ev, h = self.queue.popleft()
             cur = torch.cuda.current_stream(self.device)
             cur.wait_event(ev)
-            for t in (d.x, d.edge_index, d.batch, d.ptr, d.y):
+            store = getattr(d, "_store", None)
+            for t in (d.x, d.edge_index, d.batch, d.ptr, d.y, getattr(d, "_keepalive", None),
+                      store.blob_dev if store is not None else None):
                 if t is not None and t.is_cuda:
                     t.record_stream(cur)
             self._stage_one()  # refill behind the batch being handed out
@@ -118,9 +134,9 @@ def predict_network_stream(model, loader: Iterable[Batch], return_emb: bool = Fa
     for out, emb, h in predict_stream(model, loader, return_embedding=return_emb, **kw):
         y_pred.append(out.numpy().ravel().copy() if out.shape[1] == 1 else out.numpy().copy())
         if h.y is not None:
-            y_true.append(h.y.cpu().numpy())
+            y_true.append(np.asarray(h.y.cpu() if torch.is_tensor(h.y) else h.y))
         if h.idx is not None:
-            idx.append(h.idx.cpu().numpy())
+            idx.append(np.asarray(h.idx.cpu() if torch.is_tensor(h.idx) else h.idx))
         if return_emb:
             embs.append(emb.numpy().copy())
     cat = lambda xs: np.concatenate(xs, 0) if xs else np.empty((0,))  # noqa: E731

@@ -18,7 +18,7 @@ from .data import Batch
 
 
 def synth_batch_numpy(num_graphs: int, n_features: int = 25, seed: int = 20232023,
-                      n_min: int = 40, n_max: int = 120, bonds_per_atom: float = 1.5):
+                      n_min: int = 40, n_max: int = 120, bonds_per_atom: float = 1.5, features: str = "uniform"):
     rng = np.random.default_rng(seed)
     B = int(num_graphs)
     n = rng.integers(n_min, n_max + 1, size=B).astype(np.int64)
@@ -59,6 +59,26 @@ def synth_batch_numpy(num_graphs: int, n_features: int = 25, seed: int = 2023202
     edge_index[0, 1::2], edge_index[1, 1::2] = b, a
 
     x = rng.random((N, n_features), dtype=np.float32)
+    if features == "featuriser":
+        # the block structure of the reference's node features (reference data/rhcaa.py:112-150): one-hot
+        # element / degree / hybridisation blocks, binary flags, and the reaction temperature (one value per
+        # graph, normalised) in the last column.  Drawn AFTER the uniform matrix so that the graphs, targets and
+        # the generator state of the default variant do not change.
+        widths = [10, 4, 4] + [1] * max(n_features - 19, 0)
+        r2 = np.random.default_rng(seed + 1)
+        x = np.zeros((N, n_features), dtype=np.float32)
+        c = 0
+        for w in widths:
+            if c + w > n_features - 1:
+                break
+            if w > 1:
+                x[np.arange(N), c + r2.integers(0, w, size=N)] = 1.0
+            else:
+                x[:, c] = (r2.random(N) < 0.3).astype(np.float32)
+            c += w
+        x[:, -1] = (r2.integers(1, 6, size=B).astype(np.float32) / 5.0)[gid]
+    elif features != "uniform":
+        raise ValueError(f"unknown feature style {features!r}")
     y = (rng.standard_normal(B) * 8.0).astype(np.float32)
     return {"x": x, "edge_index": edge_index, "batch": gid, "ptr": ptr, "y": y, "num_graphs": B}
 

@@ -216,6 +216,34 @@ int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* batch, int6
  */
 int hcg_batch_from_ptr(const int64_t* ptr, int64_t B, int64_t N, int64_t* batch, void* stream);
 
+/*
+ * Packed graph image resident in device memory (layout: hcatgnet_b200/packed.py).  Replaces the reference's
+ * one-pickle-per-reaction store + Python collate (reference data/datasets.py:74-78, call_methods.py:41-46).
+ * All pointers are device pointers into the image.
+ */
+typedef struct HcgPackedStore {
+  int64_t G, N, E;            /* graphs, nodes, directed edges in the image */
+  int32_t F, Fu, Ff;          /* feature columns: total, stored as u8, stored as f32 (Fu + Ff == F) */
+  int32_t edge_kind;          /* bytes per local edge endpoint: 1, 2 or 4 */
+  const int32_t* col_slot;    /* [F]  >= 0: column of xu8;  < 0: ~column of xf32 */
+  const int64_t* node_ptr;    /* [G+1] */
+  const int64_t* edge_ptr;    /* [G+1] */
+  const float* y;             /* [G] */
+  const uint8_t* xu8;         /* [N, Fu] */
+  const float* xf32;          /* [N, Ff] */
+  const void* edges;          /* [E, 2] (src, dst) local to the graph */
+} HcgPackedStore;
+
+/*
+ * Assemble the batch of graphs graph_ids[0..B) (device int64; NULL = first, first+1, ...) exactly as PyG's
+ * collate would: x f32 [N_out, F], edge_index i64 [2, E_out] (row 0 at edge_index, row 1 at edge_index +
+ * E_out) with node offsets added, batch i64 [N_out] (may be NULL), y f32 [B] (may be NULL).  out_ptr /
+ * out_eptr: device int64 [B+1] exclusive prefix sums of the selected graphs' node / edge counts.
+ */
+int hcg_unpack_batch(const HcgPackedStore* store, const int64_t* graph_ids, int64_t first, int64_t B,
+                     const int64_t* out_ptr, const int64_t* out_eptr, float* x, int64_t* edge_index, int64_t E_out,
+                     int64_t* batch, float* y, void* stream);
+
 /* Synchronises `stream`, reads the status word of the last hcg_collate that used `ws`.  Returns
  * HCG_ERR_BAD_INDEX / HCG_ERR_BAD_BATCH for unusable input; `graph_flags` (may be NULL) receives
  * the HCG_GRAPH_* bits to put into HcgGraph.flags. */

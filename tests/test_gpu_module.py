@@ -270,3 +270,63 @@ def test_prefetcher_rebuilds_batch_vector_from_ptr(pkg):
     assert torch.equal(d.batch.cpu(), h.batch) and torch.equal(d.ptr.cpu(), h.ptr)
     ptr = torch.tensor([0, 3, 3, 7], dtype=torch.int64, device="cuda")      # an empty graph in the middle
     assert ops.batch_from_ptr(ptr, 7).tolist() == [0, 0, 0, 2, 2, 2, 2]
+
+
+# ------------------------------------------------------------------------------------------
+# packed graph image on the device: hcg_unpack_batch against PyG-style collate
+# ------------------------------------------------------------------------------------------
+def _assert_same_batch(dev_b, host_b):
+    assert torch.equal(dev_b.x.cpu(), host_b.x) and torch.equal(dev_b.edge_index.cpu(), host_b.edge_index)
+    assert torch.equal(dev_b.batch.cpu(), host_b.batch) and torch.equal(dev_b.ptr.cpu(), host_b.ptr)
+    assert torch.equal(dev_b.y.cpu(), host_b.y) and dev_b.num_graphs == host_b.num_graphs
+    assert torch.equal(dev_b.idx, host_b.idx)
+
+
+@pytest.mark.gpu
+def test_device_graph_store_assembles_pyg_batches_bit_exact():
+    import hcatgnet_b200 as pkg
+    sd, graphs, _, pred = golden_io.rows_with_graphs("learning", 1, 2)
+    ds = pkg.PackedDataset.from_graphs(graphs)
+    store = pkg.DeviceGraphStore(ds, "cuda")
+    _assert_same_batch(store.batch(), pkg.Batch.from_data_list(graphs))
+    gen = np.random.default_rng(3)
+    for ids in ([5], [4, 4, 4], list(gen.permutation(len(graphs))[:37]), list(range(len(graphs) - 1, -1, -1))):
+        _assert_same_batch(store.batch(ids), pkg.Batch.from_data_list([graphs[i] for i in ids]))
+    assert store.batch([]).num_graphs == 0 and store.batch([]).x.shape == (0, ds.F)
+    with pytest.raises(IndexError):
+        store.batch([len(graphs)])
+    # the assembled batch feeds the model like any other: golden predictions of the shipped run
+    model = pkg.make_network("GCN", pkg.default_options(), ds.F)
+    model.load_state_dict(sd, strict=True)
+    model.cuda().eval()
+    with torch.no_grad():
+        out = model(store.batch())
+    assert np.abs(out.cpu().numpy().ravel() - pred).max() <= 2e-5
+
+
+@pytest.mark.gpu
+def test_device_graph_store_large_and_wire_format():
+    """A 3000-graph synthetic image: shuffled selections against the host decoder (u8 endpoints, one f32
+    column), u16 endpoints, and the wire path (pinned image -> one copy -> unpack) through predict_stream."""
+    import hcatgnet_b200 as pkg
+    from hcatgnet_b200.synth import synth_batch
+    b = synth_batch(3000, n_features=25, seed=77)
+    x = torch.floor(b.x * 3)            # integer-valued columns, as the featuriser's one-hot blocks are
+    x[:, -1] = b.x[:, -1]               # ... and one real-valued column (temperature)
+    ds = pkg.PackedDataset.from_arrays(x.numpy(), b.edge_index.numpy(), b.ptr.numpy(), b.y.numpy(), pinned=True)
+    assert ds.Fu == 24 and ds.Ff == 1 and ds.edge_kind == 1
+    store = pkg.DeviceGraphStore(ds, "cuda")
+    ids = np.random.default_rng(1).permutation(3000)[:1111]
+    _assert_same_batch(store.batch(ids), ds.unpack_host(ids))
+    big = synth_batch(3, n_features=7, seed=5, n_min=250, n_max=400)
+    ds16 = pkg.PackedDataset.from_arrays(big.x.numpy(), big.edge_index.numpy(), big.ptr.numpy(), big.y.numpy())
+    assert ds16.edge_kind == 2 and ds16.Fu == 0
+    _assert_same_batch(pkg.DeviceGraphStore(ds16, "cuda").batch([2, 0]), ds16.unpack_host([2, 0]))
+    # wire format: the same predictions as the f32 / i64 host batch
+    opt = pkg.default_options()
+    torch.manual_seed(0)
+    model = pkg.make_network("GCN", opt, 25).cuda().eval()
+    host_b = ds.unpack_host()
+    want = [o.clone() for o, _, _ in pkg.predict_stream(model, [host_b])]
+    got = [o.clone() for o, _, _ in pkg.predict_stream(model, [ds, ds])]
+    assert len(got) == 2 and torch.equal(got[0], want[0]) and torch.equal(got[1], want[0])

@@ -137,3 +137,82 @@ def test_synthetic_generator_shape():
     assert n.min() >= 40 and n.max() <= 120
     d2 = synth_batch_numpy(256, seed=1)
     assert np.array_equal(d2["edge_index"], ei) and np.array_equal(d2["x"], d["x"])
+
+
+# ------------------------------------------------------------------------------------------
+# packed graph image: format round trips and the host decoder
+# ------------------------------------------------------------------------------------------
+def _real_graphs(count=40):
+    from tests import golden_io
+    g = golden_io.graphs_by_idx("rhcaa_learning")
+    return [g[k] for k in sorted(g)[:count]]
+
+
+def _same_batch(a, b):
+    assert torch.equal(a.x, b.x) and torch.equal(a.edge_index, b.edge_index) and torch.equal(a.batch, b.batch)
+    assert torch.equal(a.ptr, b.ptr) and torch.equal(a.y, b.y) and a.num_graphs == b.num_graphs
+
+
+def test_packed_image_round_trip_real_graphs(tmp_path):
+    from hcatgnet_b200.data import Batch
+    from hcatgnet_b200.packed import PackedDataset
+    graphs = _real_graphs()
+    ds = PackedDataset.from_graphs(graphs)
+    assert ds.G == len(graphs) and ds.edge_kind == 1
+    # the featuriser's one-hot columns go to u8, lossless: the image is several times smaller than the tensors
+    full = Batch.from_data_list(graphs)
+    assert ds.Fu >= ds.F - 2
+    assert ds.nbytes * 3 < full.x.numel() * 4 + full.edge_index.numel() * 8
+    _same_batch(ds.unpack_host(), full)
+    ids = [7, 3, 3, 39, 0, 12]
+    _same_batch(ds.unpack_host(ids), Batch.from_data_list([graphs[i] for i in ids]))
+    path = str(tmp_path / "set.hcgp")
+    ds.save(path)
+    for mmap in (True, False):
+        back = PackedDataset.load(path, mmap=mmap)
+        assert back.G == ds.G and np.array_equal(np.asarray(back.blob), ds.blob)
+        _same_batch(back.unpack_host(ids), ds.unpack_host(ids))
+    with pytest.raises(ValueError):
+        PackedDataset(np.zeros(256, np.uint8))
+
+
+def test_packed_image_column_and_edge_kinds():
+    from hcatgnet_b200.packed import PackedDataset
+    gen = np.random.default_rng(0)
+    # graph sizes above 256 force u16 endpoints; column 1 non-integer, column 2 negative, column 3 above 255 -> f32
+    sizes = [300, 1, 17]
+    graphs = []
+    for n in sizes:
+        x = gen.integers(0, 3, size=(n, 5)).astype(np.float32)
+        x[:, 1] += 0.5
+        x[0, 2] = -1.0
+        x[0, 3] = 256.0
+        e = gen.integers(0, n, size=(2, 2 * n)) if n > 1 else np.zeros((2, 0), np.int64)
+        graphs.append({"x": torch.from_numpy(x), "edge_index": torch.from_numpy(e.astype(np.int64)), "y": torch.tensor([float(n)]),
+                       "idx": n, "fold": n % 3})
+    ds = PackedDataset.from_graphs(graphs)
+    assert ds.edge_kind == 2 and ds.Fu == 2 and ds.Ff == 3 and ds.max_graph_nodes == 300
+    assert list(ds.fold) == [0, 1, 2] and list(ds.idx) == sizes
+    from hcatgnet_b200.data import Batch
+    _same_batch(ds.unpack_host([2, 0, 1, 0]), Batch.from_data_list([graphs[i] for i in (2, 0, 1, 0)]))
+    bad = {"x": torch.zeros(3, 5), "edge_index": torch.tensor([[0, 1], [1, 5]]), "y": torch.tensor([0.0])}
+    with pytest.raises(ValueError):
+        PackedDataset.from_graphs([bad, bad])      # an endpoint outside its own graph
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/data/datasets/rhcaa_final_test/processed"),
+                    reason="reference data set not present")
+def test_packed_converter_reads_the_reference_pickles():
+    """convert_processed_dir against the golden fixtures (which were made by importing the reference)."""
+    from tests import golden_io
+    from hcatgnet_b200.packed import convert_processed_dir
+    ds = convert_processed_dir("/root/reference/data/datasets/rhcaa_final_test/processed")
+    want = golden_io.graphs_by_idx("rhcaa_final_test")
+    assert ds.G == len(want)
+    got = ds.unpack_host()
+    for b in range(ds.G):
+        g = want[int(ds.idx[b])]
+        lo, hi = int(got.ptr[b]), int(got.ptr[b + 1])
+        assert torch.equal(got.x[lo:hi], torch.as_tensor(g["x"]))
+        sel = (got.edge_index[0] >= lo) & (got.edge_index[0] < hi)
+        assert torch.equal(got.edge_index[:, sel] - lo, torch.as_tensor(g["edge_index"]).to(torch.int64))
