@@ -313,3 +313,60 @@ class DeviceGraphStore:
         out.max_graph_nodes = int(n.max()) if B else 0
         out._keepalive = meta_d
         return out
+
+
+class StoreLoader:
+    """``DataLoader`` over graphs of a ``DeviceGraphStore`` (reference call_methods.py:41-46 builds these with
+    PyG's DataLoader over lists of Data): yields collated DEVICE batches assembled by ``store.batch``.
+    ``len(loader.dataset)`` is the number of graphs, as the reference's loops expect
+    (reference utils/utils_model.py:70,79).  Shuffling uses python ``random`` like ``data.DataLoader``.
+    A loader that does not shuffle yields the same batches every epoch: they (and the collate plans the model
+    caches on them) are assembled once and kept."""
+
+    def __init__(self, store: DeviceGraphStore, ids, batch_size: int = 1, shuffle: bool = False, cache: bool | None = None):
+        self.store = store
+        self.dataset = [int(i) for i in ids]
+        self.batch_size = int(batch_size)
+        self.shuffle = bool(shuffle)
+        self.cache = (not self.shuffle) if cache is None else bool(cache) and not self.shuffle
+        self._kept = None
+
+    def __len__(self):
+        return (len(self.dataset) + self.batch_size - 1) // self.batch_size
+
+    def __iter__(self):
+        if self._kept is not None:
+            yield from self._kept
+            return
+        import random
+        order = list(self.dataset)
+        if self.shuffle:
+            random.shuffle(order)
+        kept = []
+        for s in range(0, len(order), self.batch_size):
+            b = self.store.batch(order[s:s + self.batch_size])
+            if self.cache:
+                kept.append(b)
+            yield b
+        if self.cache:
+            self._kept = kept
+
+
+def create_store_loaders(store: DeviceGraphStore, opt):
+    """The nested cross-validation generator of reference call_methods.py:15-47 over a device-resident store:
+    for every outer fold (test set) and every remaining inner fold (validation set) yields
+    ``(train_loader, val_loader, test_loader)``; graphs keep the reference's order inside each fold and the
+    training set is the remaining folds concatenated in fold order, reshuffled every epoch."""
+    n_folds = int(opt.folds)
+    fold = np.asarray(store.ds.fold)
+    if fold.size and (fold.min() < 0 or fold.max() >= n_folds):
+        raise ValueError(f"fold labels outside [0, {n_folds}) in the packed image")
+    folds = [np.nonzero(fold == f)[0].tolist() for f in range(n_folds)]
+    for outer in range(n_folds):
+        proxy = folds[:outer] + folds[outer + 1:]
+        for inner in range(len(proxy)):
+            rest = proxy[:inner] + proxy[inner + 1:]
+            train = [i for sub in rest for i in sub]
+            yield (StoreLoader(store, train, opt.batch_size, shuffle=True),
+                   StoreLoader(store, proxy[inner], opt.batch_size, shuffle=False),
+                   StoreLoader(store, folds[outer], opt.batch_size, shuffle=False))

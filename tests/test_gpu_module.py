@@ -330,3 +330,35 @@ def test_device_graph_store_large_and_wire_format():
     want = [o.clone() for o, _, _ in pkg.predict_stream(model, [host_b])]
     got = [o.clone() for o, _, _ in pkg.predict_stream(model, [ds, ds])]
     assert len(got) == 2 and torch.equal(got[0], want[0]) and torch.equal(got[1], want[0])
+
+
+@pytest.mark.gpu
+def test_store_loaders_match_host_loaders_in_nested_cv():
+    """create_loaders over a DeviceGraphStore: the same graphs in the same order as the host loaders of the
+    reference's generator, an identical training epoch, and cached evaluation batches."""
+    import random
+    import hcatgnet_b200 as pkg
+    graphs = golden_io.load_graphs("rhcaa_learning")[:200]
+    opt = pkg.default_options()
+    store = pkg.DeviceGraphStore(pkg.PackedDataset.from_graphs(graphs), "cuda")
+    host_it, dev_it = pkg.create_loaders(graphs, opt), pkg.create_loaders(store, opt)
+    for n in range(12):
+        (htr, hva, hte), (dtr, dva, dte) = next(host_it), next(dev_it)
+        for hl, dl in ((htr, dtr), (hva, dva), (hte, dte)):
+            assert [int(g["idx"]) for g in hl.dataset] == [int(store.ds.idx[i]) for i in dl.dataset]
+            assert len(hl) == len(dl) and len(hl.dataset) == len(dl.dataset)
+    losses = []
+    for loaders in ((htr, hva), (dtr, dva)):
+        torch.manual_seed(1)
+        model = pkg.make_network("GCN", opt, 25).cuda()
+        tr = pkg.FusedTrainer(model)
+        random.seed(5)
+        l_train = tr.train_network(loaders[0])
+        l_val = tr.eval_network(loaders[1])
+        l_val2 = tr.eval_network(loaders[1])
+        assert l_val == l_val2
+        losses.append((l_train, l_val))
+    assert losses[0] == losses[1]          # same batches, same kernels, same order: identical numbers
+    assert dva._kept is not None and dtr._kept is None
+    first = [id(b) for b in dva]
+    assert first == [id(b) for b in dva]

@@ -216,3 +216,22 @@ def test_packed_converter_reads_the_reference_pickles():
         assert torch.equal(got.x[lo:hi], torch.as_tensor(g["x"]))
         sel = (got.edge_index[0] >= lo) & (got.edge_index[0] < hi)
         assert torch.equal(got.edge_index[:, sel] - lo, torch.as_tensor(g["edge_index"]).to(torch.int64))
+
+
+def test_create_loaders_nested_cv_partitions():
+    """reference call_methods.py:15-47: folds x (folds - 1) triples; test = outer fold, val = inner-th of the
+    remaining folds, train = the rest in fold order."""
+    import hcatgnet_b200 as pkg
+    graphs = _real_graphs(120)
+    opt = pkg.default_options()
+    triples = list(pkg.create_loaders(graphs, opt))
+    assert len(triples) == opt.folds * (opt.folds - 1)
+    all_idx = sorted(int(g["idx"]) for g in graphs)
+    for n, (tr, va, te) in enumerate(triples):
+        outer, inner = divmod(n, opt.folds - 1)
+        rest = [f for f in range(opt.folds) if f != outer]
+        assert all(int(g["fold"]) == outer for g in te.dataset)
+        assert all(int(g["fold"]) == rest[inner] for g in va.dataset)
+        want_train = [int(g["idx"]) for f in rest if f != rest[inner] for g in graphs if int(g["fold"]) == f]
+        assert [int(g["idx"]) for g in tr.dataset] == want_train and tr.shuffle and not va.shuffle and not te.shuffle
+        assert sorted([int(g["idx"]) for l in (tr, va, te) for g in l.dataset]) == all_idx
