@@ -32,6 +32,7 @@
 // point atomics, run-to-run identical.  Graphs above the shared-memory capacity run the same code on a
 // private slice of a global scratch buffer.
 #include "hcg_fused.cuh"
+#include "hcg_mma.cuh"
 
 namespace hcg {
 
@@ -41,28 +42,6 @@ constexpr int kBwdThreads = 256;
 constexpr int kBwdNcap = 128;   // nodes per graph held in shared memory
 constexpr int kBwdEcap = 640;   // transposed-CSR slots per graph held in shared memory
 constexpr int kBwdSlack = 16;   // rows of slack per graph in the global scratch (pad rows of the MMA tiles)
-
-__device__ __forceinline__ int swz(int r) { return ((r & 3) << 3) | (r & 4); }
-__device__ __forceinline__ int at(int r, int c) { return r * 64 + (c ^ swz(r)); }
-
-__device__ __forceinline__ void split_tf32(float v, uint32_t& hi, uint32_t& lo) {
-  hi = (__float_as_uint(v) + 0x1000u) & 0xffffe000u;  // round to nearest TF32 on the magnitude
-  lo = __float_as_uint(v - __uint_as_float(hi));      // exact residual; the tensor core reads its TF32 bits
-}
-
-// D[16x8] += A[16x8] . B[8x8]   (A row-major fragment, B column-major fragment, fp32 accumulators)
-__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-__device__ __forceinline__ void mma_split(float (&d)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4],
-                                          uint32_t bh0, uint32_t bh1, uint32_t bl0, uint32_t bl1) {
-  mma_tf32(d, al, bh0, bh1);  // small cross terms first
-  mma_tf32(d, ah, bl0, bl1);
-  mma_tf32(d, ah, bh0, bh1);
-}
 
 // dst[i] = sum_k norm_ik src[k] over the transposed CSR row of i, self-loop last; rows n..npad-1 := 0.
 // A half-warp per row, a lane per 16-byte chunk.
@@ -90,49 +69,6 @@ __device__ __forceinline__ void agg_rows(const float* __restrict__ src, float* _
     }
     *reinterpret_cast<float4*>(dst + i * 64 + (c0 ^ swz(i))) = acc;
   }
-}
-
-// acc[j] += (Q^T . Y)[16 mt .. +16][8 (nb + j) .. +8]  over rows 0..npad-1 (pad rows of Q are zero)
-template <int NT>
-__device__ __forceinline__ void xty_tiles(const float* __restrict__ Q, const float* __restrict__ Y, int npad, int mt,
-                                          int nb, float (&acc)[NT][4]) {
-  const int lane = threadIdx.x & 31, g8 = lane >> 2, t4 = lane & 3;
-  float d[NT][4];
-#pragma unroll
-  for (int j = 0; j < NT; ++j)
-#pragma unroll
-    for (int q = 0; q < 4; ++q) d[j][q] = 0.f;
-  // fragment rows are r0 + t4 (swizzle t4 << 3) and r0 + t4 + 4 (swizzle (t4 << 3) | 4) with r0 a multiple of 8:
-  // every offset is a per-thread constant plus r0 * 64
-  const int s0 = t4 << 3, s1 = s0 | 4, oc = 16 * mt + g8;
-  const float* qa = Q + t4 * 64 + (oc ^ s0);
-  const float* qb = Q + t4 * 64 + ((oc + 8) ^ s0);
-  const float* qc = Q + (t4 + 4) * 64 + (oc ^ s1);
-  const float* qd = Q + (t4 + 4) * 64 + ((oc + 8) ^ s1);
-  const float* yr0 = Y + t4 * 64;
-  const float* yr1 = Y + (t4 + 4) * 64;
-  int off[NT];
-#pragma unroll
-  for (int j = 0; j < NT; ++j) off[j] = (8 * (nb + j) + g8) ^ s0;  // column of tile j in row r0 + t4; row + 4: ^ 4
-  for (int r0 = 0; r0 < npad; r0 += 8) {
-    const int o = r0 * 64;
-    uint32_t ah[4], al[4];
-    split_tf32(qa[o], ah[0], al[0]);
-    split_tf32(qb[o], ah[1], al[1]);
-    split_tf32(qc[o], ah[2], al[2]);
-    split_tf32(qd[o], ah[3], al[3]);
-#pragma unroll
-    for (int j = 0; j < NT; ++j) {
-      uint32_t bh0, bl0, bh1, bl1;
-      split_tf32(yr0[o + off[j]], bh0, bl0);
-      split_tf32(yr1[o + (off[j] ^ 4)], bh1, bl1);
-      mma_split(d[j], ah, al, bh0, bh1, bl0, bl1);
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < NT; ++j)
-#pragma unroll
-    for (int q = 0; q < 4; ++q) acc[j][q] += d[j][q];
 }
 
 struct BwdState {       // per-thread running sums over the graphs this CTA walks

@@ -10,6 +10,7 @@
 // so there are no floating-point atomics and results are run-to-run identical.
 #include "hcg_common.cuh"
 #include "hcg_fused.cuh"
+#include "hcg_mma.cuh"
 
 namespace hcg {
 
@@ -763,6 +764,104 @@ k_xty_partial(const float* __restrict__ X, const float* __restrict__ Y, int64_t 
   }
 }
 
+// The same contract on the tensor cores (warp-level mma.sync m16n8k8, TF32 with the 3-term split: fp32-grade
+// accuracy, see hcg_mma.cuh).  The reduction dimension is the ROW index, which is the row of the staged planes:
+// fragments come straight out of shared memory.  32 rows are staged per step, split into TF32 hi / lo parts
+// by the staging thread (once per element, not once per consuming warp) into four XOR-swizzled [32][64] planes
+// (32 KB, several CTAs per SM overlap staging and MMAs): the inner loop is LDS + MMA.  Each slab's product
+// starts from a zero accumulator and is added to the thread's running fp32 sums.  At P = Q = 256 (stress configuration) the fp32
+// FMA kernel above is 63 % of the training step.
+constexpr int XM = 32;
+
+__device__ __forceinline__ void split4(const float4 v, float4& hi, float4& lo) {
+  uint32_t h, l;
+  split_tf32(v.x, h, l); hi.x = __uint_as_float(h); lo.x = __uint_as_float(l);
+  split_tf32(v.y, h, l); hi.y = __uint_as_float(h); lo.y = __uint_as_float(l);
+  split_tf32(v.z, h, l); hi.z = __uint_as_float(h); lo.z = __uint_as_float(l);
+  split_tf32(v.w, h, l); hi.w = __uint_as_float(h); lo.w = __uint_as_float(l);
+}
+
+__global__ void __launch_bounds__(256)
+k_xty_mma(const float* __restrict__ X, const float* __restrict__ Y, int64_t Nrows, int P, int Q,
+          int64_t rows_per_chunk, float* __restrict__ partial) {
+  __shared__ __align__(16) float Xh[XM * 64], Xl[XM * 64], Yh[XM * 64], Yl[XM * 64];  // TF32 hi / lo planes
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int p0 = blockIdx.y * 64, q0 = blockIdx.z * 64;
+  const int64_t r_beg = (int64_t)blockIdx.x * rows_per_chunk;
+  const int64_t r_end = min(Nrows, r_beg + rows_per_chunk);
+  const bool vecX = (P & 3) == 0, vecY = (Q & 3) == 0;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  // this thread stages float4 (r, c4) and (r + 16, c4) of both planes
+  const int sr = tid >> 4, c4 = (tid & 15) * 4;
+  const bool xin = vecX && p0 + c4 + 3 < P, yin = vecY && q0 + c4 + 3 < Q;
+
+  for (int64_t r0 = r_beg; r0 < r_end; r0 += XM) {
+    const int rows = (int)min((int64_t)XM, r_end - r0);
+    const int npad = (rows + 7) & ~7;
+    float4 xv[2], yv[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int r = sr + 16 * h;
+      xv[h] = make_float4(0.f, 0.f, 0.f, 0.f);
+      yv[h] = xv[h];
+      if (r < rows) {
+        const float* xp = X + (r0 + r) * P + p0 + c4;
+        const float* yp = Y + (r0 + r) * Q + q0 + c4;
+        if (xin) xv[h] = ldg4(xp);
+        else {
+          if (p0 + c4 < P) xv[h].x = __ldg(xp);
+          if (p0 + c4 + 1 < P) xv[h].y = __ldg(xp + 1);
+          if (p0 + c4 + 2 < P) xv[h].z = __ldg(xp + 2);
+          if (p0 + c4 + 3 < P) xv[h].w = __ldg(xp + 3);
+        }
+        if (yin) yv[h] = ldg4(yp);
+        else {
+          if (q0 + c4 < Q) yv[h].x = __ldg(yp);
+          if (q0 + c4 + 1 < Q) yv[h].y = __ldg(yp + 1);
+          if (q0 + c4 + 2 < Q) yv[h].z = __ldg(yp + 2);
+          if (q0 + c4 + 3 < Q) yv[h].w = __ldg(yp + 3);
+        }
+      }
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int r = sr + 16 * h;
+      if (r < npad) {
+        const int o = r * 64 + (c4 ^ swz(r));
+        float4 hi, lo;
+        split4(xv[h], hi, lo);
+        *reinterpret_cast<float4*>(Xh + o) = hi;
+        *reinterpret_cast<float4*>(Xl + o) = lo;
+        split4(yv[h], hi, lo);
+        *reinterpret_cast<float4*>(Yh + o) = hi;
+        *reinterpret_cast<float4*>(Yl + o) = lo;
+      }
+    }
+    __syncthreads();
+    xty_tiles_presplit<4>(Xh, Xl, Yh, Yl, npad, warp & 3, (warp >> 2) * 4, acc);
+    __syncthreads();
+  }
+  // fragment of tile j: rows 16 mt + g8 (+8), columns 8 (nb + j) + 2 t4 (+1)
+  float* dst = partial + (int64_t)blockIdx.x * P * Q;
+  const int g8 = lane >> 2, t4 = lane & 3;
+  const int pr = p0 + 16 * (warp & 3) + g8;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int qc = q0 + 8 * ((warp >> 2) * 4 + j) + 2 * t4;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int p = pr + 8 * h;
+      if (p >= P) continue;
+      if (qc < Q) dst[(int64_t)p * Q + qc] = acc[j][2 * h];
+      if (qc + 1 < Q) dst[(int64_t)p * Q + qc + 1] = acc[j][2 * h + 1];
+    }
+  }
+}
+
 // column sums of X[n][p] over a chunk of rows (bias gradients)
 __global__ void __launch_bounds__(256)
 k_colsum_partial(const float* __restrict__ X, int64_t Nrows, int P, int64_t rows_per_chunk,
@@ -806,8 +905,14 @@ static int launch_xty(const float* X, const float* Y, int64_t rows, int P, int Q
   int64_t chunks = pick_chunks(rows, tiles);
   int64_t rpc = cdiv(rows > 0 ? rows : 1, chunks);
   dim3 grid((unsigned)chunks, (unsigned)cdiv(P, 64), (unsigned)cdiv(Q, 64));
-  k_xty_partial<<<grid, 256, 0, st>>>(X, Y, rows, P, Q, rpc, partial);
-  HCG_LAUNCH_OK(st, "k_xty_partial");
+  // HCG_CFG_GEMM_PATH = 1 keeps every dense product on the fp32 FMA pipe (A/B reference for the tests)
+  if (config_get(HCG_CFG_GEMM_PATH) != 1 && P >= 32) {
+    k_xty_mma<<<grid, 256, 0, st>>>(X, Y, rows, P, Q, rpc, partial);
+    HCG_LAUNCH_OK(st, "k_xty_mma");
+  } else {
+    k_xty_partial<<<grid, 256, 0, st>>>(X, Y, rows, P, Q, rpc, partial);
+    HCG_LAUNCH_OK(st, "k_xty_partial");
+  }
   k_reduce_partials<<<(unsigned)cdiv((int64_t)P * Q, 256), 256, 0, st>>>(partial, (int)chunks, (int64_t)P * Q, out);
   HCG_LAUNCH_OK(st, "k_reduce_partials");
   return HCG_OK;
