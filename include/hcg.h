@@ -166,6 +166,7 @@ int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts, int cap);
  * HCG_CFG_GEMM_PATH (dense X.W products of the layer-wise kernels): 0 = auto (split-TF32 tcgen05 kernel for
  * output widths 128/192/256 on batches of >= 8192 rows, fp32 FMA tiles otherwise), 1 = FMA tiles only,
  * 2 = the tensor-core kernel wherever its shape constraints hold (output width a multiple of 64, <= 256).
+ * The weight-gradient products of the layer-wise backward run on mma.sync TF32 tiles (3-term split) unless 1.
  * HCG_CFG_AGG_PATH (neighbour aggregation of the layer-wise kernels): 0 = auto (whole-row kernel, with the
  * pooling fused into the last layer, when H >= 128, H % 4 == 0, H <= 512 and no edge weights / edge mask;
  * column-pass gather + k_pool otherwise), 1 = column-pass gather + k_pool only, 2 = the whole-row kernel
