@@ -329,7 +329,6 @@ __device__ __forceinline__ void agg_wide_tile(const int32_t* __restrict__ rowptr
 }
 
 constexpr int kAggTileRows = 8;   // rows per warp tile, row-parallel variant
-constexpr int kAggPoolRows = 4;   // rows per warp tile inside one graph (pooling variant: finer, for balance)
 
 template <int NV, bool EXACT, bool POOL>
 __global__ void __launch_bounds__(256)
@@ -354,13 +353,16 @@ k_agg_wide(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, 
   __shared__ float4 s_max[8][NV][32], s_sum[8][NV][32];
   const int64_t gid = blockIdx.x;
   const int n0 = graph_ptr[gid], n1 = graph_ptr[gid + 1];
-  for (int i0 = n0 + warp * kAggPoolRows; i0 < n1; i0 += 8 * kAggPoolRows)
-    agg_wide_tile<NV, kAggPoolRows, EXACT, true>(rowptr, col, dis, fill, T, i0, min(kAggPoolRows, n1 - i0), H, lane, b4, act,
+  // every warp takes a contiguous share of ceil(n / 8) rows (balanced to one row), walked in tiles of <= 8 rows
+  const int share = (n1 - n0 + 7) >> 3;
+  const int lo = n0 + warp * share, hi = min(n1, lo + share);
+  for (int i0 = lo; i0 < hi; i0 += kAggTileRows)
+    agg_wide_tile<NV, kAggTileRows, EXACT, true>(rowptr, col, dis, fill, T, i0, min(kAggTileRows, hi - i0), H, lane, b4, act,
                                                  slope, out, pmax, psum);
 #pragma unroll
   for (int v = 0; v < NV; ++v) { s_max[warp][v][lane] = pmax[v]; s_sum[warp][v][lane] = psum[v]; }
   __syncthreads();
-  // thread t combines column t of every 128-column chunk over the 8 warps in warp order (fixed order)
+  // thread t combines column t of every 128-column chunk over the 8 warps in warp order (= node order of the shares)
   const int n = n1 - n0;
   for (int c = threadIdx.x; c < NV * 128; c += 256) {
     const int v = c >> 7, cc = c & 127;

@@ -31,20 +31,28 @@ k_unpack_batch(const HcgPackedStore s, const int64_t* __restrict__ graph_ids, in
   const int64_t s0 = s.node_ptr[g], n = s.node_ptr[g + 1] - s0, d0 = out_ptr[b];
   const int64_t se0 = s.edge_ptr[g], e = s.edge_ptr[g + 1] - se0, de0 = out_eptr[b];
   // node features: consecutive threads write consecutive floats of the [n, F] block
-  const int64_t total = n * F;
-  for (int64_t t = tid; t < total; t += kUnpackThreads) {
-    const int64_t r = t / F;
-    const int c = (int)(t - r * F);
+  // (a single graph is far below 2^31 elements: 32-bit index arithmetic inside the graph)
+  const int total = (int)n * F;
+  const uint8_t* xu = s.xu8 + s0 * s.Fu;
+  const float* xf = s.xf32 + s0 * s.Ff;
+  float* xo = x + d0 * F;
+  int r = tid / F, c = tid - r * F;                      // element tid, then steps of kUnpackThreads
+  const int dr = kUnpackThreads / F, dc = kUnpackThreads - dr * F;
+  for (int t = tid; t < total; t += kUnpackThreads) {
     const int slot = s_slot[c];
-    x[d0 * F + t] = slot >= 0 ? (float)s.xu8[(s0 + r) * s.Fu + slot] : s.xf32[(s0 + r) * s.Ff + (~slot)];
+    xo[t] = slot >= 0 ? (float)xu[r * s.Fu + slot] : xf[r * s.Ff + (~slot)];
+    r += dr; c += dc;
+    if (c >= F) { c -= F; ++r; }
   }
   const ET* ed = static_cast<const ET*>(s.edges) + 2 * se0;
-  for (int64_t k = tid; k < e; k += kUnpackThreads) {
-    edge_index[de0 + k] = d0 + (int64_t)ed[2 * k];
-    edge_index[E_out + de0 + k] = d0 + (int64_t)ed[2 * k + 1];
+  int64_t* e_src = edge_index + de0;
+  int64_t* e_dst = edge_index + E_out + de0;
+  for (int k = tid; k < (int)e; k += kUnpackThreads) {
+    e_src[k] = d0 + (int64_t)ed[2 * k];
+    e_dst[k] = d0 + (int64_t)ed[2 * k + 1];
   }
   if (batch)
-    for (int64_t r = tid; r < n; r += kUnpackThreads) batch[d0 + r] = b;
+    for (int rr = tid; rr < (int)n; rr += kUnpackThreads) batch[d0 + rr] = b;
   if (y && tid == 0) y[b] = s.y[g];
 }
 

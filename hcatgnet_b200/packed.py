@@ -291,7 +291,7 @@ class DeviceGraphStore:
             n = ds.node_ptr[ids_np + 1] - ds.node_ptr[ids_np]
             e = ds.edge_ptr[ids_np + 1] - ds.edge_ptr[ids_np]
         B = int(n.size)
-        meta = torch.empty(3, B + 1, dtype=torch.int64).pin_memory() if dev.type == "cuda" else torch.empty(3, B + 1, dtype=torch.int64)
+        meta = torch.empty(3, B + 1, dtype=torch.int64, pin_memory=dev.type == "cuda")
         m = meta.numpy()
         m[0, 0] = m[1, 0] = 0
         np.cumsum(n, out=m[0, 1:])
