@@ -370,3 +370,11 @@ def create_store_loaders(store: DeviceGraphStore, opt):
             yield (StoreLoader(store, train, opt.batch_size, shuffle=True),
                    StoreLoader(store, proxy[inner], opt.batch_size, shuffle=False),
                    StoreLoader(store, folds[outer], opt.batch_size, shuffle=False))
+
+
+if __name__ == "__main__":  # python -m hcatgnet_b200.packed <processed_dir> <out.hcgp>
+    if len(sys.argv) != 3:
+        raise SystemExit("usage: python -m hcatgnet_b200.packed <reference processed/ directory> <out.hcgp>")
+    _ds = convert_processed_dir(sys.argv[1], sys.argv[2])
+    print(f"{_ds.G} graphs, {_ds.N} nodes, {_ds.E} directed edges, F={_ds.F} ({_ds.Fu} u8 + {_ds.Ff} f32 columns), "
+          f"{_ds.edge_kind}-byte endpoints -> {_ds.nbytes} bytes")
