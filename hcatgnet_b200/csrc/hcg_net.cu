@@ -411,7 +411,8 @@ static int launch_agg_wide(const int32_t* rowptr, const int32_t* col, const floa
   }
 #undef HCG_AGG_WIDE2
 #undef HCG_AGG_WIDE
-  HCG_LAUNCH_OK(st, "k_agg_wide");
+  if (emb) HCG_LAUNCH_OK(st, "k_agg_wide_pool");
+  else HCG_LAUNCH_OK(st, "k_agg_wide");
   return HCG_OK;
 }
 

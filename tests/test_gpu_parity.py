@@ -539,7 +539,10 @@ def test_wide_row_aggregation_forward_backward(hcg, agg_path, gemm_path, forward
     column chunks, partial chunks (H = 192, 136, 64), graphs from 1 to 300 nodes."""
     from hcatgnet_b200.synth import synth_batch
     b = synth_batch(B, n_features=F, seed=33, n_min=nmin, n_max=nmax)
-    sd = ref_gcn.init_state_dict(F, H, L, 2, 1, seed=4)
+    # seed 6: with seed 4 one readout pre-activation of the 700-graph case lands within 1e-7 of zero, and which
+    # side of the LeakyReLU kink it falls on depends on the rounding of the mean pooling (k_pool and the fp64
+    # oracle disagree there; profiles/experiments/agg_grad_probe.py) - a property of the data, not of a kernel
+    sd = ref_gcn.init_state_dict(F, H, L, 2, 1, seed=6)
     forward_path(1)
     backward_path(1)
     gemm_path(1)
@@ -563,8 +566,10 @@ def test_wide_row_aggregation_forward_backward(hcg, agg_path, gemm_path, forward
     assert _close(res[2][1].cpu(), res[1][1].cpu()) <= TOL
     args = (sd, b.x, b.edge_index, b.batch, b.num_graphs, b.y)
     _, g_ref, _ = _oracle_grads(*args)
-    _, g_res, _ = _cuda_grads(hcg, *args)
-    _assert_grads(g_res, g_ref)
+    for path in (2, 1):
+        agg_path(path)
+        _, g_res, _ = _cuda_grads(hcg, *args)
+        _assert_grads(g_res, g_ref)
 
 
 # ------------------------------------------------------------------------------------------
