@@ -213,6 +213,7 @@ def algorithmic_bytes(name: str, N: int, E: int, B: int, F: int, H: int):
         "k_fused_bwd": 8 * N * H + 4 * N * F + csr + 4 * N + 16 * B * H + 296 * 4 * (H * H + H * F + 2 * H),
         "k_agg": 4 * N * H + csr + 4 * N + 4 * N * H,        # read T once, CSR, dis, write h
         "k_agg_wide": 4 * N * H + csr + 4 * N + 4 * N * H,   # same contract as k_agg
+        "k_agg_narrow": 4 * N * H + csr + 4 * N + 4 * N * H,
         "k_agg_wide_pool": 4 * N * H + csr + 4 * N + 4 * (B + 1) + 8 * B * H,   # inference: rows are pooled, not stored
         "k_pool": 4 * N * H + 4 * (B + 1) + 8 * B * H,
         "k_count": 16 * E,                                     # + integer atomics into cnt (L2-resident)
@@ -479,7 +480,7 @@ def main():
     if kernels is not None and a.mode == "infer":
         N, E = int(np.mean(Ns)), int(np.mean(Es))
         agg_roofline = {}
-        for kname in ("k_agg_wide", "k_agg_wide_pool", "k_agg"):
+        for kname in ("k_agg_wide", "k_agg_wide_pool", "k_agg_narrow", "k_agg"):
             if kname in kernels:
                 ab = algorithmic_bytes(kname, N, E, a.batch, F_IN, a.hidden)
                 ach = ab / (kernels[kname]["ms_per_launch"] * 1e-3) / 1e9

@@ -292,6 +292,7 @@ __device__ __forceinline__ void agg_wide_tile(const int32_t* __restrict__ rowptr
   float wl = 0.f;
   if (beg0 + lane < end_all) { jl = __ldg(col + beg0 + lane); wl = __ldg(dis + jl); }
   const float* Tl = T + 4 * lane;
+  const int HH = EXACT ? NV * 128 : H;  // a compile-time row pitch turns every row address into one IMAD.WIDE
 #pragma unroll 1
   for (int r = 0; r < rows; ++r) {
     const int beg = __shfl_sync(kFull, rp, r), end = __shfl_sync(kFull, rp, r + 1);
@@ -299,26 +300,33 @@ __device__ __forceinline__ void agg_wide_tile(const int32_t* __restrict__ rowptr
     float4 acc[NV];
 #pragma unroll
     for (int v = 0; v < NV; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int cut = min(end, beg0 + 32);  // slots below it were preloaded (all of them for molecule-like rows)
+    int k = beg;
 #pragma unroll 2
-    for (int k = beg; k < end; ++k) {
-      const int sl = k - beg0;
-      int j;
-      float w;
-      if (sl < 32) { j = __shfl_sync(kFull, jl, sl); w = __shfl_sync(kFull, wl, sl); }   // warp-uniform branch
-      else { j = __ldg(col + k); w = __ldg(dis + j); }
-      agg_wide_fma<NV, EXACT>(acc, w * di, Tl + (int64_t)j * H, H, lane);
+    for (; k < cut; ++k) {
+      const int j = __shfl_sync(kFull, jl, k - beg0);
+      const float w = __shfl_sync(kFull, wl, k - beg0);
+      agg_wide_fma<NV, EXACT>(acc, w * di, Tl + (int64_t)j * HH, H, lane);
+    }
+    for (; k < end; ++k) {
+      const int j = __ldg(col + k);
+      const float w = __ldg(dis + j);
+      agg_wide_fma<NV, EXACT>(acc, w * di, Tl + (int64_t)j * HH, H, lane);
     }
     const int64_t i = i0 + r;
-    agg_wide_fma<NV, EXACT>(acc, (di * fill) * di, Tl + i * H, H, lane);
+    agg_wide_fma<NV, EXACT>(acc, (di * fill) * di, Tl + i * HH, H, lane);
 #pragma unroll
     for (int v = 0; v < NV; ++v)
       if (EXACT || 128 * v + 4 * lane < H) {
         acc[v].x += b4[v].x; acc[v].y += b4[v].y; acc[v].z += b4[v].z; acc[v].w += b4[v].w;
-        if (act) {
+        if (act == 2) {  // 0 <= slope <= 1: lrelu(v) = max(v, slope v), same bits, one instruction less
+          acc[v].x = fmaxf(acc[v].x, acc[v].x * slope); acc[v].y = fmaxf(acc[v].y, acc[v].y * slope);
+          acc[v].z = fmaxf(acc[v].z, acc[v].z * slope); acc[v].w = fmaxf(acc[v].w, acc[v].w * slope);
+        } else if (act) {
           acc[v].x = lrelu(acc[v].x, slope); acc[v].y = lrelu(acc[v].y, slope);
           acc[v].z = lrelu(acc[v].z, slope); acc[v].w = lrelu(acc[v].w, slope);
         }
-        if (!POOL || out) *reinterpret_cast<float4*>(out + i * H + 128 * v + 4 * lane) = acc[v];
+        if (!POOL || out) *reinterpret_cast<float4*>(out + i * HH + 128 * v + 4 * lane) = acc[v];
         if (POOL) {
           pmax[v].x = fmaxf(pmax[v].x, acc[v].x); pmax[v].y = fmaxf(pmax[v].y, acc[v].y);
           pmax[v].z = fmaxf(pmax[v].z, acc[v].z); pmax[v].w = fmaxf(pmax[v].w, acc[v].w);
@@ -378,12 +386,89 @@ k_agg_wide(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, 
   }
 }
 
-// HCG_CFG_AGG_PATH: 0 = wide-row kernels when H >= 128, 1 = k_agg / k_pool only, 2 = wide-row kernels for any H % 4 == 0
-static bool agg_wide_ok(const HcgGraph* g, int H, const float* T, const float* out) {
+// The same tile scheme for narrow layers (H <= 64, H even - the reference's default embedding_dim = 64): a lane
+// owns columns 2 lane, 2 lane + 1, so a 256-byte row of T is ONE coalesced 8-byte-per-lane access and all 32
+// lanes work (k_agg_wide would idle half of them).  Row-parallel only; k_pool follows.
+template <bool EXACT>
+__global__ void __launch_bounds__(256)
+k_agg_narrow(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ dis, float fill,
+             const float* __restrict__ T, const float* __restrict__ bias, float* __restrict__ out, int64_t N, int H, int act,
+             float slope) {
+  constexpr unsigned kFull = 0xffffffffu;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t i0 = ((int64_t)blockIdx.x * 8 + warp) * kAggTileRows;
+  if (i0 >= N) return;
+  const int rows = (int)min((int64_t)kAggTileRows, N - i0);
+  const bool on = EXACT || 2 * lane < H;
+  float2 b2 = make_float2(0.f, 0.f);
+  if (bias && on) b2 = __ldg(reinterpret_cast<const float2*>(bias + 2 * lane));
+  int rp = 0;
+  float drow = 0.f;
+  if (lane <= rows) rp = __ldg(rowptr + i0 + lane);
+  if (lane < rows) drow = __ldg(dis + i0 + lane);
+  const int beg0 = __shfl_sync(kFull, rp, 0), end_all = __shfl_sync(kFull, rp, rows);
+  int jl = 0;
+  float wl = 0.f;
+  if (beg0 + lane < end_all) { jl = __ldg(col + beg0 + lane); wl = __ldg(dis + jl); }
+  const float* Tl = T + 2 * lane;
+  const int HH = EXACT ? 64 : H;  // compile-time row pitch for the default width
+#pragma unroll 1
+  for (int r = 0; r < rows; ++r) {
+    const int beg = __shfl_sync(kFull, rp, r), end = __shfl_sync(kFull, rp, r + 1);
+    const float di = __shfl_sync(kFull, drow, r);
+    float2 acc = make_float2(0.f, 0.f);
+    const int cut = min(end, beg0 + 32);  // slots below it were preloaded
+    int k = beg;
+#pragma unroll 2
+    for (; k < cut; ++k) {
+      const int j = __shfl_sync(kFull, jl, k - beg0);
+      const float w = __shfl_sync(kFull, wl, k - beg0) * di;
+      if (on) {
+        const float2 t = __ldg(reinterpret_cast<const float2*>(Tl + (int64_t)j * HH));
+        acc.x = fmaf(w, t.x, acc.x); acc.y = fmaf(w, t.y, acc.y);
+      }
+    }
+    for (; k < end; ++k) {
+      const int j = __ldg(col + k);
+      const float w = __ldg(dis + j) * di;
+      if (on) {
+        const float2 t = __ldg(reinterpret_cast<const float2*>(Tl + (int64_t)j * HH));
+        acc.x = fmaf(w, t.x, acc.x); acc.y = fmaf(w, t.y, acc.y);
+      }
+    }
+    const int64_t i = i0 + r;
+    if (on) {
+      const float ws = (di * fill) * di;
+      const float2 t = __ldg(reinterpret_cast<const float2*>(Tl + i * HH));
+      acc.x = fmaf(ws, t.x, acc.x) + b2.x; acc.y = fmaf(ws, t.y, acc.y) + b2.y;
+      if (act == 2) { acc.x = fmaxf(acc.x, acc.x * slope); acc.y = fmaxf(acc.y, acc.y * slope); }
+      else if (act) { acc.x = lrelu(acc.x, slope); acc.y = lrelu(acc.y, slope); }
+      *reinterpret_cast<float2*>(out + i * HH + 2 * lane) = acc;
+    }
+  }
+}
+
+// HCG_CFG_AGG_PATH: 0 = tile kernels when H >= 128 (wide) or 32 <= H <= 64 (narrow), 1 = k_agg / k_pool only,
+// 2 = tile kernels whenever their constraints hold
+enum { AGG_ROWS = 0, AGG_WIDE = 1, AGG_NARROW = 2 };
+static int agg_kind(const HcgGraph* g, int H, const float* T, const float* out) {
   const int ap = config_get(HCG_CFG_AGG_PATH);
-  if (ap == 1 || (H & 3) != 0 || H > 512 || g->edge_mask != nullptr) return false;
-  if ((reinterpret_cast<uintptr_t>(T) | reinterpret_cast<uintptr_t>(out)) % 16 != 0) return false;
-  return ap == 2 || H >= 128;
+  if (ap == 1 || g->edge_mask != nullptr) return AGG_ROWS;
+  const uintptr_t al = reinterpret_cast<uintptr_t>(T) | reinterpret_cast<uintptr_t>(out);
+  if (H <= 64 && (H & 1) == 0 && al % 8 == 0 && (ap == 2 || H >= 32)) return AGG_NARROW;
+  if (H > 64 && (H & 3) == 0 && H <= 512 && al % 16 == 0 && (ap == 2 || H >= 128)) return AGG_WIDE;
+  return AGG_ROWS;
+}
+
+static int launch_agg_narrow(const int32_t* rowptr, const int32_t* col, const float* dis, float fill, const float* T,
+                             const float* bias, float* out, int64_t N, int H, int act, float slope, cudaStream_t st) {
+  if (N == 0) return HCG_OK;
+  if (act && slope >= 0.f && slope <= 1.f) act = 2;
+  const unsigned grid = (unsigned)cdiv(N, 8 * kAggTileRows);
+  if (H == 64) k_agg_narrow<true><<<grid, 256, 0, st>>>(rowptr, col, dis, fill, T, bias, out, N, H, act, slope);
+  else k_agg_narrow<false><<<grid, 256, 0, st>>>(rowptr, col, dis, fill, T, bias, out, N, H, act, slope);
+  HCG_LAUNCH_OK(st, "k_agg_narrow");
+  return HCG_OK;
 }
 
 // out may be NULL only with emb (pooling variant: grid = graphs); emb == NULL: grid = rows / 8
@@ -391,6 +476,7 @@ static int launch_agg_wide(const int32_t* rowptr, const int32_t* col, const floa
                            const float* bias, float* out, int64_t N, int H, int act, float slope,
                            const int32_t* graph_ptr, int64_t B, float* emb, cudaStream_t st) {
   if (N == 0 || (emb && B == 0)) return HCG_OK;
+  if (act && slope >= 0.f && slope <= 1.f) act = 2;
   const int nv = (H + 127) / 128;
   const unsigned grid = (unsigned)(emb ? B : cdiv(N, 8 * kAggTileRows));
   const bool exact = H % 128 == 0;
@@ -1145,12 +1231,15 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
     h_out = saved ? saved->acts[l] : w.act[l & 1];
     HCG_REQUIRE(h_out != nullptr, HCG_ERR_INVALID_ARG, "saved->acts[%d] is NULL", l);
     const bool weighted0 = (l == 0 && g->ew0 != nullptr);
-    if (!weighted0 && agg_wide_ok(g, H, w.T, h_out)) {
+    const int kind = weighted0 ? AGG_ROWS : agg_kind(g, H, w.T, h_out);
+    if (kind == AGG_WIDE) {
       // whole-row kernel; the last layer pools in its epilogue and keeps its rows only for a backward
       const bool last = l == p->L - 1 && B > 0;
       rc = launch_agg_wide(g->rowptr, g->col, g->dis, g->fill, w.T, p->conv_b[l], last && !saved ? nullptr : h_out, N, H, 1,
                            p->slope, g->graph_ptr, B, last ? emb : nullptr, st);
       pooled = last;
+    } else if (kind == AGG_NARROW) {
+      rc = launch_agg_narrow(g->rowptr, g->col, g->dis, g->fill, w.T, p->conv_b[l], h_out, N, H, 1, p->slope, st);
     } else {
       rc = launch_agg(g->rowptr, g->col, weighted0 ? g->dis0 : g->dis, weighted0 ? g->ew0 : nullptr,
                       weighted0 ? g->selfw0 : nullptr, g->fill, w.T, p->conv_b[l], h_out, N, H, 1, p->slope, st,
@@ -1308,9 +1397,12 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
       HCG_LAUNCH_OK(st, "k_edge_dot");
     }
     // gT = Â^T · gA  (transposed CSR; no bias, no activation)
-    if (!weighted0 && agg_wide_ok(g, H, w.gA, w.gT))
+    const int tkind = weighted0 ? AGG_ROWS : agg_kind(g, H, w.gA, w.gT);
+    if (tkind == AGG_WIDE)
       rc = launch_agg_wide(g->t_rowptr, g->t_col, g->dis, g->fill, w.gA, nullptr, w.gT, N, H, 0, p->slope, g->graph_ptr, B,
                            nullptr, st);
+    else if (tkind == AGG_NARROW)
+      rc = launch_agg_narrow(g->t_rowptr, g->t_col, g->dis, g->fill, w.gA, nullptr, w.gT, N, H, 0, p->slope, st);
     else
       rc = launch_agg(g->t_rowptr, g->t_col, weighted0 ? g->dis0 : g->dis, weighted0 ? g->t_ew0 : nullptr,
                       weighted0 ? g->selfw0 : nullptr, g->fill, w.gA, nullptr, w.gT, N, H, 0, p->slope, st,

@@ -167,10 +167,10 @@ int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts, int cap);
  * output widths 128/192/256 on batches of >= 8192 rows, fp32 FMA tiles otherwise), 1 = FMA tiles only,
  * 2 = the tensor-core kernel wherever its shape constraints hold (output width a multiple of 64, <= 256).
  * The weight-gradient products of the layer-wise backward run on mma.sync TF32 tiles (3-term split) unless 1.
- * HCG_CFG_AGG_PATH (neighbour aggregation of the layer-wise kernels): 0 = auto (whole-row kernel, with the
- * pooling fused into the last layer, when H >= 128, H % 4 == 0, H <= 512 and no edge weights / edge mask;
- * column-pass gather + k_pool otherwise), 1 = column-pass gather + k_pool only, 2 = the whole-row kernel
- * whenever its constraints hold (any H % 4 == 0).
+ * HCG_CFG_AGG_PATH (neighbour aggregation of the layer-wise kernels): 0 = auto (warp-tile kernels without edge
+ * weights / edge mask: whole-row kernel with the pooling fused into the last layer for H >= 128, H % 4 == 0,
+ * H <= 512; narrow kernel for even 32 <= H <= 64; column-pass gather + k_pool otherwise), 1 = column-pass
+ * gather + k_pool only, 2 = the warp-tile kernels whenever their shape constraints hold.
  * All are CUDA paths; there is no CPU path.  Returns the previous value, or -1 for a bad key.
  */
 enum { HCG_CFG_FORWARD_PATH = 0, HCG_CFG_BACKWARD_PATH = 1, HCG_CFG_GEMM_PATH = 2, HCG_CFG_AGG_PATH = 3, HCG_CFG_COUNT_ = 4 };

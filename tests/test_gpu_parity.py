@@ -531,12 +531,14 @@ def agg_path(hcg):
 
 
 @pytest.mark.parametrize("H,L,F,B,nmin,nmax", [(256, 4, 25, 33, 1, 50), (128, 2, 32, 700, 2, 60), (192, 3, 7, 64, 1, 40),
-                                               (64, 2, 25, 300, 1, 120), (136, 2, 9, 5, 1, 8), (256, 2, 25, 6, 100, 300)])
+                                               (64, 2, 25, 300, 1, 120), (136, 2, 9, 5, 1, 8), (256, 2, 25, 6, 100, 300),
+                                               (50, 2, 9, 40, 1, 30), (32, 3, 25, 100, 1, 80), (6, 2, 4, 9, 1, 12)])
 def test_wide_row_aggregation_forward_backward(hcg, agg_path, gemm_path, forward_path, backward_path, H, L, F, B,
                                                      nmin, nmax):
-    """k_agg_wide (a warp per whole row, pooled per graph in the last layer's epilogue, transposed CSR in the
-    backward) against k_agg + k_pool (same summation order: identical activations) and the oracle; 1..2
-    column chunks, partial chunks (H = 192, 136, 64), graphs from 1 to 300 nodes."""
+    """k_agg_wide (warp tiles of whole rows, pooled per graph in the last layer's epilogue, transposed CSR in the
+    backward) and k_agg_narrow (H <= 64) against k_agg + k_pool (same summation order: identical activations)
+    and the oracle; 1..2 column chunks, partial chunks (H = 192, 136), narrow widths 64 / 50 / 32 / 6, graphs
+    from 1 to 300 nodes."""
     from hcatgnet_b200.synth import synth_batch
     b = synth_batch(B, n_features=F, seed=33, n_min=nmin, n_max=nmax)
     # seed 6: with seed 4 one readout pre-activation of the 700-graph case lands within 1e-7 of zero, and which
