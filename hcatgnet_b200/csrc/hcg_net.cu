@@ -113,11 +113,12 @@ static int launch_gemm(const float* A, const float* Bm, float* C, int64_t M, int
                        const float* aux, float slope, cudaStream_t st, float* wimg = nullptr) {
   if (M == 0 || Nc == 0) return HCG_OK;
   {
-    // HCG_CFG_GEMM_PATH: 0 = tensor cores for wide layers on batches with enough row tiles, 1 = never, 2 = whenever applicable
+    // HCG_CFG_GEMM_PATH: 0 = tensor cores for output widths 64..256 on batches with enough row tiles (0.40 -> 0.23 ms at
+    // Nc = 64, 3.96 -> 0.99 ms at Nc = 256 for 1.31 M rows), 1 = never, 2 = whenever applicable
     const int gp = config_get(HCG_CFG_GEMM_PATH);
     const bool shape_ok = wimg != nullptr && (epi == EPI_NONE || epi == EPI_MASK) && tc_gemm_applicable(M, K, Nc) &&
                           (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (epi != EPI_MASK || (reinterpret_cast<uintptr_t>(aux) & 15) == 0);
-    if (shape_ok && (gp == 2 || (gp == 0 && Nc >= 128 && M >= 128 * 64)))
+    if (shape_ok && (gp == 2 || (gp == 0 && Nc >= 64 && M >= 128 * 64)))
       return launch_tc_gemm(A, Bm, C, M, K, Nc, !B_T, epi == EPI_MASK ? 1 : 0, aux, slope, wimg, st);
   }
   dim3 grid((unsigned)cdiv(M, GM), (unsigned)cdiv(Nc, GN));

@@ -164,7 +164,7 @@ int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts, int cap);
  * edge weights, a disjoint molecule-like batch and no gradient w.r.t. x is wanted; layer-wise kernels
  * otherwise), 1 = force layer-wise, 2 = force graph-resident (HCG_ERR_UNSUPPORTED if not applicable).
  * HCG_CFG_GEMM_PATH (dense X.W products of the layer-wise kernels): 0 = auto (split-TF32 tcgen05 kernel for
- * output widths 128/192/256 on batches of >= 8192 rows, fp32 FMA tiles otherwise), 1 = FMA tiles only,
+ * output widths 64/128/192/256 on batches of >= 8192 rows, fp32 FMA tiles otherwise), 1 = FMA tiles only,
  * 2 = the tensor-core kernel wherever its shape constraints hold (output width a multiple of 64, <= 256).
  * The weight-gradient products of the layer-wise backward run on mma.sync TF32 tiles (3-term split) unless 1.
  * HCG_CFG_AGG_PATH (neighbour aggregation of the layer-wise kernels): 0 = auto (warp-tile kernels without edge
