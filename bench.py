@@ -485,6 +485,7 @@ def main():
                 ab = algorithmic_bytes(kname, N, E, a.batch, F_IN, a.hidden)
                 ach = ab / (kernels[kname]["ms_per_launch"] * 1e-3) / 1e9
                 agg_roofline[kname] = {"achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                                       "traffic": measured_traffic(kname, a),
                                        "algorithmic_bytes_per_launch": ab, "ms_per_launch": kernels[kname]["ms_per_launch"]}
         agg_roofline = agg_roofline or None
 
