@@ -233,6 +233,25 @@ k_dis(const int32_t* __restrict__ rowptr, int64_t N, float fill, float* __restri
 // ------------------------------------------------------------------------------------------
 // 6. graph offsets from the sorted batch vector
 // ------------------------------------------------------------------------------------------
+// first edge e of [0, E) whose dst is >= `node` (edge lists grouped by graph make that predicate monotone;
+// on other inputs the result is some position in [0, E] and the per-edge checks of the graph-local
+// kernels refuse the batch; a node id outside [0, N] cannot reach here: graph_ptr holds offsets).  The search starts from the proportional guess node * E / N.
+__device__ __forceinline__ int32_t first_edge_at(const int64_t* __restrict__ dst, int64_t E, int64_t N, int64_t node) {
+  if (node <= 0) return 0;
+  int64_t lo = 0, hi = E;
+  constexpr int64_t kWin = 2048;
+  const int64_t guess = (int64_t)((double)node * (double)E / (double)N);
+  const int64_t a = guess - kWin, b = guess + kWin;
+  if (a > 0 && a < E && dst[a - 1] < node) lo = a;
+  if (b > 0 && b < E && dst[b] >= node) hi = b;
+  if (lo > hi) { lo = 0; hi = E; }
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (dst[mid] < node) lo = mid + 1; else hi = mid;
+  }
+  return (int32_t)lo;
+}
+
 __global__ void __launch_bounds__(256)
 k_graph_ptr(const int64_t* __restrict__ batch, int64_t N, int64_t B, int32_t* __restrict__ graph_ptr,
             int* __restrict__ status) {
@@ -245,6 +264,7 @@ k_graph_ptr(const int64_t* __restrict__ batch, int64_t N, int64_t B, int32_t* __
   if (i == N) {  // tail: graphs after the last node's graph are empty
     int64_t last = N > 0 ? batch[N - 1] : -1;
     if (last >= B) last = B - 1;
+    if (last < -1) last = -1;
     for (int64_t g = last + 1; g <= B; ++g) graph_ptr[g] = (int32_t)N;
     return;
   }
@@ -258,10 +278,21 @@ k_graph_ptr(const int64_t* __restrict__ batch, int64_t N, int64_t B, int32_t* __
   for (int64_t g = prev + 1; g <= b; ++g) graph_ptr[g] = (int32_t)i;
 }
 
+// eptr[g] = first edge whose dst belongs to graph g or a later one, eptr[B] = E: a thread per graph, one
+// wave of short searches instead of a scan of the whole edge list
+__global__ void __launch_bounds__(64)
+k_edge_ptr(const int64_t* __restrict__ dst, int64_t E, int64_t N, int64_t B, const int32_t* __restrict__ graph_ptr,
+           int32_t* __restrict__ eptr) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g > B) return;
+  eptr[g] = g == B ? (int32_t)E : first_edge_at(dst, E, N, graph_ptr[g]);
+}
+
 // ==========================================================================================
 // Graph-local fast path (HCG_COLLATE_GROUPED).  PyG's collate concatenates the edge lists graph
 // by graph, so the edges of graph g are one contiguous slice of edge_index: find the slices
-// (k_edge_ranges), then build each graph's CSR entirely in shared memory (k_collate_graph) and write
+// (k_edge_ptr: a search on dst per graph), then build each graph's CSR entirely in shared memory
+// (k_collate_graph_warp / k_collate_graph, which also check every edge against its slice) and write
 // it out coalesced.  Without dropped self-loops the CSR slots of graph g are exactly its edge slice,
 // so no batch-wide scan is needed.  Every precondition is checked on the device.
 // ==========================================================================================
@@ -270,29 +301,14 @@ constexpr int kGrpNodes = 1024;  // per-graph capacity of the shared-memory CSR 
 constexpr int kGrpEdges = 2048;
 constexpr int kGrpThreads = 128;
 
-// eptr[g] = first edge of graph g (graph of an edge = graph of its dst); eptr[B] = E
-__global__ void __launch_bounds__(256)
-k_edge_ranges(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, const int64_t* __restrict__ batch,
-              int64_t E, int64_t N, int64_t B, int32_t* __restrict__ eptr, int* __restrict__ status) {
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E; e += stride) {
-    const int64_t s = src[e], d = dst[e];
-    if (s < 0 || s >= N || d < 0 || d >= N) { atomicOr(status, kStatusBadIndex | kStatusNotGrouped); continue; }
-    if (s == d) { atomicOr(status, kStatusNotGrouped); continue; }  // dropped self-loops shift the slots
-    int64_t g = batch[d];
-    if (g < 0 || g >= B) { atomicOr(status, kStatusBadBatch | kStatusNotGrouped); continue; }
-    if (batch[s] != g) atomicOr(status, kStatusCrossEdge | kStatusNotGrouped);
-    int64_t gp = -1;
-    if (e > 0) {
-      const int64_t dp = dst[e - 1];
-      gp = (dp >= 0 && dp < N) ? batch[dp] : -1;
-      if (gp >= B) gp = -1;
-    }
-    if (g < gp) atomicOr(status, kStatusNotGrouped);
-    for (int64_t q = gp + 1; q <= g; ++q) eptr[q] = (int32_t)e;  // graphs without edges share the boundary
-    if (e == E - 1)
-      for (int64_t q = g + 1; q <= B; ++q) eptr[q] = (int32_t)E;
-  }
+// Per-edge check of the graph-local path, made by the thread that places the edge into its dst row: both
+// endpoints must be nodes of the graph whose slice [eptr[g], eptr[g+1]) holds the edge.  The slices
+// partition [0, E) (a non-monotone eptr is refused by the kernels below), so every edge is checked once.
+__device__ __forceinline__ void grp_check_edge(int64_t s, int64_t d, int n0, int n, int64_t N, int* status) {
+  if (s < 0 || s >= N || d < 0 || d >= N) { atomicOr(status, kStatusBadIndex | kStatusNotGrouped); return; }
+  if (s == d) { atomicOr(status, kStatusNotGrouped); return; }  // dropped self-loops shift the slots
+  if ((uint64_t)(d - n0) >= (uint64_t)n) { atomicOr(status, kStatusNotGrouped); return; }  // edge outside its graph's slice
+  if ((uint64_t)(s - n0) >= (uint64_t)n) atomicOr(status, kStatusCrossEdge | kStatusNotGrouped);
 }
 
 // block-wide exclusive scan of v[0..n) in shared memory (n <= kGrpNodes), kGrpThreads threads;
@@ -334,13 +350,13 @@ __device__ __forceinline__ void grp_build(const int64_t* __restrict__ rowkey, co
                                           int e_lo, int e_cnt, int n0, int n, int* cnt, int* rp, int* slot_eid,
                                           int* slot_val, int* warp_tot, int32_t* __restrict__ rowptr_out,
                                           int32_t* __restrict__ col_out, int32_t* __restrict__ eid_out,
-                                          float* __restrict__ dis_out, float fill) {
+                                          float* __restrict__ dis_out, float fill, int64_t N, int* check_status) {
   const int t = threadIdx.x;
   for (int i = t; i < n; i += kGrpThreads) cnt[i] = 0;
   __syncthreads();
   for (int k = t; k < e_cnt; k += kGrpThreads) {
-    const int r = (int)(rowkey[e_lo + k] - n0);
-    if ((unsigned)r < (unsigned)n) atomicAdd(&cnt[r], 1);  // out-of-graph keys were flagged by k_edge_ranges
+    const int64_t key = rowkey[e_lo + k];
+    if ((uint64_t)(key - n0) < (uint64_t)n) atomicAdd(&cnt[(int)(key - n0)], 1);
   }
   __syncthreads();
   grp_scan(cnt, n, rp, warp_tot);
@@ -355,11 +371,12 @@ __device__ __forceinline__ void grp_build(const int64_t* __restrict__ rowkey, co
   for (int i = t; i < n; i += kGrpThreads) cnt[i] = rp[i];  // cursors
   __syncthreads();
   for (int k = t; k < e_cnt; k += kGrpThreads) {
-    const int r = (int)(rowkey[e_lo + k] - n0);
-    if ((unsigned)r >= (unsigned)n) continue;
-    const int pos = atomicAdd(&cnt[r], 1);
+    const int64_t key = rowkey[e_lo + k], v = val[e_lo + k];
+    if (check_status) grp_check_edge(v, key, n0, n, N, check_status);  // by-dst pass: key = dst, v = src
+    if ((uint64_t)(key - n0) >= (uint64_t)n) continue;
+    const int pos = atomicAdd(&cnt[(int)(key - n0)], 1);
     slot_eid[pos] = e_lo + k;
-    slot_val[pos] = (int)val[e_lo + k];
+    slot_val[pos] = (int)v;
   }
   __syncthreads();
   for (int i = t; i < n; i += kGrpThreads) {  // insertion sort by edge id (rows are a handful of slots)
@@ -387,14 +404,15 @@ constexpr int kWgNodes = 256, kWgEdges = 512, kWgWarps = 4;
 __device__ __forceinline__ void wg_build(const int64_t* __restrict__ rowkey, const int64_t* __restrict__ val, int e_lo,
                                          int e_cnt, int n0, int n, int* cnt, int* rp, int* slot_eid, int* slot_val,
                                          int32_t* __restrict__ rowptr_out, int32_t* __restrict__ col_out,
-                                         int32_t* __restrict__ eid_out, float* __restrict__ dis_out, float fill) {
+                                         int32_t* __restrict__ eid_out, float* __restrict__ dis_out, float fill,
+                                         int64_t N, int* check_status) {
   const int lane = threadIdx.x & 31;
   constexpr int PER = kWgNodes / 32;
   for (int i = lane; i < n; i += 32) cnt[i] = 0;
   __syncwarp();
   for (int k = lane; k < e_cnt; k += 32) {
-    const int r = (int)(rowkey[e_lo + k] - n0);
-    if ((unsigned)r < (unsigned)n) atomicAdd(&cnt[r], 1);
+    const int64_t key = rowkey[e_lo + k];
+    if ((uint64_t)(key - n0) < (uint64_t)n) atomicAdd(&cnt[(int)(key - n0)], 1);
   }
   __syncwarp();
   int local[PER], sum = 0;
@@ -431,11 +449,12 @@ __device__ __forceinline__ void wg_build(const int64_t* __restrict__ rowkey, con
   for (int i = lane; i < n; i += 32) cnt[i] = rp[i];  // cursors
   __syncwarp();
   for (int k = lane; k < e_cnt; k += 32) {
-    const int r = (int)(rowkey[e_lo + k] - n0);
-    if ((unsigned)r >= (unsigned)n) continue;
-    const int pos = atomicAdd(&cnt[r], 1);
+    const int64_t key = rowkey[e_lo + k], v = val[e_lo + k];
+    if (check_status) grp_check_edge(v, key, n0, n, N, check_status);  // by-dst pass: key = dst, v = src
+    if ((uint64_t)(key - n0) >= (uint64_t)n) continue;
+    const int pos = atomicAdd(&cnt[(int)(key - n0)], 1);
     slot_eid[pos] = e_lo + k;
-    slot_val[pos] = (int)val[e_lo + k];
+    slot_val[pos] = (int)v;
   }
   __syncwarp();
   for (int i = lane; i < n; i += 32) {  // insertion sort by edge id inside each row
@@ -461,7 +480,8 @@ k_collate_graph_warp(const int64_t* __restrict__ src, const int64_t* __restrict_
                      const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ eptr, float fill,
                      int32_t* __restrict__ rowptr, int32_t* __restrict__ col, int32_t* __restrict__ eid,
                      float* __restrict__ dis, int32_t* __restrict__ t_rowptr, int32_t* __restrict__ t_col,
-                     int32_t* __restrict__ t_eid, int* __restrict__ big_count) {
+                     int32_t* __restrict__ t_eid, int* __restrict__ status) {
+  int* const big_count = status + 1;
   __shared__ int cnt[kWgWarps][kWgNodes], rp[kWgWarps][kWgNodes + 1], slot_eid[kWgWarps][kWgEdges], slot_val[kWgWarps][kWgEdges];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t stride = (int64_t)gridDim.x * kWgWarps;
@@ -477,9 +497,10 @@ k_collate_graph_warp(const int64_t* __restrict__ src, const int64_t* __restrict_
       if (lane == 0) atomicAdd(big_count, 1);  // left to the block-per-graph kernel
       continue;
     }
-    wg_build(dst, src, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot_eid[w], slot_val[w], rowptr, col, eid, dis, fill);
+    wg_build(dst, src, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot_eid[w], slot_val[w], rowptr, col, eid, dis, fill, N, status);
     if (t_rowptr)
-      wg_build(src, dst, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot_eid[w], slot_val[w], t_rowptr, t_col, t_eid, nullptr, fill);
+      wg_build(src, dst, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot_eid[w], slot_val[w], t_rowptr, t_col, t_eid, nullptr, fill,
+               N, nullptr);
   }
 }
 
@@ -501,9 +522,10 @@ k_collate_graph(const int64_t* __restrict__ src, const int64_t* __restrict__ dst
       if (threadIdx.x == 0) atomicOr(status, kStatusNotGrouped);
       continue;
     }
-    grp_build(dst, src, e_lo, e_cnt, n0, n, cnt, rp, slot_eid, slot_val, warp_tot, rowptr, col, eid, dis, fill);
+    grp_build(dst, src, e_lo, e_cnt, n0, n, cnt, rp, slot_eid, slot_val, warp_tot, rowptr, col, eid, dis, fill, N, status);
     if (t_rowptr)
-      grp_build(src, dst, e_lo, e_cnt, n0, n, cnt, rp, slot_eid, slot_val, warp_tot, t_rowptr, t_col, t_eid, nullptr, fill);
+      grp_build(src, dst, e_lo, e_cnt, n0, n, cnt, rp, slot_eid, slot_val, warp_tot, t_rowptr, t_col, t_eid, nullptr, fill,
+                N, nullptr);
   }
 }
 
@@ -588,16 +610,14 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
     note_other("memset(collate)", st);
     k_graph_ptr<<<(unsigned)cdiv(N + 1, 256), 256, 0, st>>>(batch, N, B, graph_ptr, w.status);
     HCG_LAUNCH_OK(st, "k_graph_ptr");
-    if (E > 0) {
-      int64_t eb = cdiv(E, 256);
-      if (eb > (int64_t)kNumSMs * 16) eb = (int64_t)kNumSMs * 16;
-      k_edge_ranges<<<(unsigned)eb, 256, 0, st>>>(src, dst, batch, E, N, B, w.eptr, w.status);
-      HCG_LAUNCH_OK(st, "k_edge_ranges");
+    if (E > 0) {  // E == 0 leaves the cleared eptr
+      k_edge_ptr<<<(unsigned)cdiv(B + 1, 64), 64, 0, st>>>(dst, E, N, B, graph_ptr, w.eptr);
+      HCG_LAUNCH_OK(st, "k_edge_ptr");
     }
     int64_t wb = cdiv(B, kWgWarps);
     if (wb > (int64_t)kNumSMs * 9) wb = (int64_t)kNumSMs * 9;
     k_collate_graph_warp<<<(unsigned)wb, kWgWarps * 32, 0, st>>>(src, dst, E, N, B, graph_ptr, w.eptr, fill, rowptr, col, eid, dis,
-                                                                transpose ? t_rowptr : nullptr, t_col, t_eid, w.status + 1);
+                                                                transpose ? t_rowptr : nullptr, t_col, t_eid, w.status);
     HCG_LAUNCH_OK(st, "k_collate_graph_warp");
     int64_t gb = B < (int64_t)kNumSMs * 8 ? B : (int64_t)kNumSMs * 8;
     k_collate_graph<<<(unsigned)gb, kGrpThreads, 0, st>>>(src, dst, E, N, B, graph_ptr, w.eptr, fill, rowptr, col, eid, dis,

@@ -557,56 +557,61 @@ k_pool(const float* __restrict__ h, const int32_t* __restrict__ graph_ptr, int64
 // Fused two-layer readout head (the default network: emb[B,128] -> 64 -> C), one launch:
 //   hid = lrelu(emb . W1^T + b1)   (optionally saved for the backward pass)
 //   out = hid . W2^T + b2
-// A block owns 64 graphs; 16 x 16 threads, each a 4 (graphs) x 4 (hidden units) micro-tile; the
-// k loop runs in ascending order like k_gemm, so both produce the same bits.
+// A block owns RO_FG = 32 graphs (512 blocks per 16384-graph batch: three to four resident per SM hide each
+// other's load -> barrier -> FMA chain); 16 x 16 threads, each a 2 (graphs) x 4 (hidden units) micro-tile;
+// the k loop runs in ascending order like k_gemm, so both produce the same bits.
 // ==========================================================================================
 constexpr int RO_G = 64, RO_IN = 128, RO_HID = 64, RO_KC = 32;
+constexpr int RO_FG = 32;  // graphs per block of the forward head (the backward keeps RO_G)
 
 __global__ void __launch_bounds__(256)
 k_readout2(const float* __restrict__ emb, const float* __restrict__ W1, const float* __restrict__ b1,
            const float* __restrict__ W2, const float* __restrict__ b2, float* __restrict__ hid_save,
            float* __restrict__ out, int64_t B, int C, float slope) {
-  __shared__ __align__(16) float Es[RO_KC][RO_G + 4];    // [k][graph]
+  __shared__ __align__(16) float Es[RO_KC][RO_FG + 4];   // [k][graph]
   __shared__ __align__(16) float Ws[RO_KC][RO_HID + 4];  // [k][unit]
-  __shared__ float Hs[RO_G][RO_HID + 1];
+  __shared__ float Hs[RO_FG][RO_HID + 1];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-  const int64_t g0 = (int64_t)blockIdx.x * RO_G;
-  float acc[4][4];
+  const int64_t g0 = (int64_t)blockIdx.x * RO_FG;
+  float acc[2][4];
 #pragma unroll
-  for (int a = 0; a < 4; ++a)
+  for (int a = 0; a < 2; ++a)
 #pragma unroll
     for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
   for (int k0 = 0; k0 < RO_IN; k0 += RO_KC) {
-    for (int idx = tid; idx < RO_G * RO_KC; idx += 256) {
+    for (int idx = tid; idx < RO_FG * RO_KC; idx += 256) {
       const int r = idx / RO_KC, c = idx % RO_KC;
       Es[c][r] = g0 + r < B ? emb[(g0 + r) * RO_IN + k0 + c] : 0.f;
-      Ws[c][r] = W1[r * RO_IN + k0 + c];  // r = hidden unit here (RO_HID == RO_G)
+    }
+    for (int idx = tid; idx < RO_HID * RO_KC; idx += 256) {
+      const int r = idx / RO_KC, c = idx % RO_KC;
+      Ws[c][r] = W1[r * RO_IN + k0 + c];
     }
     __syncthreads();
 #pragma unroll 8
     for (int kk = 0; kk < RO_KC; ++kk) {
-      const float4 e4 = *reinterpret_cast<const float4*>(&Es[kk][ty * 4]);
+      const float2 e2 = *reinterpret_cast<const float2*>(&Es[kk][ty * 2]);
       const float4 w4 = *reinterpret_cast<const float4*>(&Ws[kk][tx * 4]);
-      const float e[4] = {e4.x, e4.y, e4.z, e4.w}, w[4] = {w4.x, w4.y, w4.z, w4.w};
+      const float e[2] = {e2.x, e2.y}, w[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
-      for (int a = 0; a < 4; ++a)
+      for (int a = 0; a < 2; ++a)
 #pragma unroll
         for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(e[a], w[b], acc[a][b]);
     }
     __syncthreads();
   }
 #pragma unroll
-  for (int a = 0; a < 4; ++a)
+  for (int a = 0; a < 2; ++a)
 #pragma unroll
     for (int b = 0; b < 4; ++b) {
-      const int g = ty * 4 + a, o = tx * 4 + b;
+      const int g = ty * 2 + a, o = tx * 4 + b;
       const float v = lrelu(acc[a][b] + b1[o], slope);
       Hs[g][o] = v;
       if (hid_save && g0 + g < B) hid_save[(g0 + g) * RO_HID + o] = v;
     }
   __syncthreads();
-  for (int idx = tid; idx < RO_G * C; idx += 256) {
-    const int g = idx % RO_G, c = idx / RO_G;
+  for (int idx = tid; idx < RO_FG * C; idx += 256) {
+    const int g = idx % RO_FG, c = idx / RO_FG;
     if (g0 + g >= B) continue;
     float s = 0.f;
 #pragma unroll 8
@@ -1258,7 +1263,7 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
   if (p->R == 2 && 2 * H == RO_IN && B > 0) {  // the default head in one launch
     float* hs = saved ? saved->hid[0] : nullptr;
     if (saved) HCG_REQUIRE(hs != nullptr, HCG_ERR_INVALID_ARG, "saved->hid[0] is NULL");
-    k_readout2<<<(unsigned)cdiv(B, RO_G), 256, 0, st>>>(emb, p->ro_w[0], p->ro_b[0], p->ro_w[1], p->ro_b[1], hs, out, B,
+    k_readout2<<<(unsigned)cdiv(B, RO_FG), 256, 0, st>>>(emb, p->ro_w[0], p->ro_b[0], p->ro_w[1], p->ro_b[1], hs, out, B,
                                                         p->C, p->slope);
     HCG_LAUNCH_OK(st, "k_readout2");
     return HCG_OK;
