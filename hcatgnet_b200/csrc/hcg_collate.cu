@@ -401,17 +401,21 @@ __device__ __forceinline__ void grp_build(const int64_t* __restrict__ rowkey, co
 //      block-wide barriers, eight graphs in flight per CTA ----------------------------------------
 constexpr int kWgNodes = 256, kWgEdges = 512, kWgWarps = 4;
 
+// A slot is one word: (edge number inside the slice) << 16 | (value node - n0).  Both fit 16 bits for an
+// accepted graph (<= kWgEdges edges, <= kWgNodes nodes); sorting the words sorts a row by edge order.
 __device__ __forceinline__ void wg_build(const int64_t* __restrict__ rowkey, const int64_t* __restrict__ val, int e_lo,
-                                         int e_cnt, int n0, int n, int* cnt, int* rp, int* slot_eid, int* slot_val,
+                                         int e_cnt, int n0, int n, int* cnt, int* rp, unsigned* slot,
                                          int32_t* __restrict__ rowptr_out, int32_t* __restrict__ col_out,
                                          int32_t* __restrict__ eid_out, float* __restrict__ dis_out, float fill,
                                          int64_t N, int* check_status) {
   const int lane = threadIdx.x & 31;
   constexpr int PER = kWgNodes / 32;
+  const int64_t* __restrict__ rk = rowkey + e_lo;
+  const int64_t* __restrict__ vl = val + e_lo;
   for (int i = lane; i < n; i += 32) cnt[i] = 0;
   __syncwarp();
   for (int k = lane; k < e_cnt; k += 32) {
-    const int64_t key = rowkey[e_lo + k];
+    const int64_t key = rk[k];
     if ((uint64_t)(key - n0) < (uint64_t)n) atomicAdd(&cnt[(int)(key - n0)], 1);
   }
   __syncwarp();
@@ -444,45 +448,46 @@ __device__ __forceinline__ void wg_build(const int64_t* __restrict__ rowkey, con
       const float r = __fdiv_rn(1.0f, __fsqrt_rn((float)cnt[i] + fill));
       dis_out[n0 + i] = isinf(r) ? 0.f : r;
     }
+    cnt[i] = b;  // cursor of the row from here on
   }
   __syncwarp();
-  for (int i = lane; i < n; i += 32) cnt[i] = rp[i];  // cursors
-  __syncwarp();
   for (int k = lane; k < e_cnt; k += 32) {
-    const int64_t key = rowkey[e_lo + k], v = val[e_lo + k];
+    const int64_t key = rk[k], v = vl[k];
     if (check_status) grp_check_edge(v, key, n0, n, N, check_status);  // by-dst pass: key = dst, v = src
     if ((uint64_t)(key - n0) >= (uint64_t)n) continue;
     const int pos = atomicAdd(&cnt[(int)(key - n0)], 1);
-    slot_eid[pos] = e_lo + k;
-    slot_val[pos] = (int)v;
+    slot[pos] = ((unsigned)k << 16) | ((unsigned)(v - n0) & 0xffffu);
   }
   __syncwarp();
-  for (int i = lane; i < n; i += 32) {  // insertion sort by edge id inside each row
+  for (int i = lane; i < n; i += 32) {  // insertion sort by edge number inside each row
     const int b = rp[i], e = rp[i + 1];
     for (int a = b + 1; a < e; ++a) {
-      const int ke = slot_eid[a], kv = slot_val[a];
+      const unsigned ks = slot[a];
       int c = a - 1;
-      while (c >= b && slot_eid[c] > ke) { slot_eid[c + 1] = slot_eid[c]; slot_val[c + 1] = slot_val[c]; --c; }
-      slot_eid[c + 1] = ke; slot_val[c + 1] = kv;
+      while (c >= b && slot[c] > ks) { slot[c + 1] = slot[c]; --c; }
+      slot[c + 1] = ks;
     }
   }
   __syncwarp();
   const int kept = rp[n];
-  for (int k = lane; k < e_cnt; k += 32) {
-    eid_out[e_lo + k] = k < kept ? slot_eid[k] : 0;
-    col_out[e_lo + k] = k < kept ? slot_val[k] : 0;
+  for (int k = lane; k < e_cnt; k += 32) {  // kept == e_cnt unless the batch was flagged
+    const unsigned sv = k < kept ? slot[k] : 0u;
+    const int rel = (int)(sv & 0xffffu);
+    eid_out[e_lo + k] = k < kept ? e_lo + (int)(sv >> 16) : 0;
+    col_out[e_lo + k] = k < kept ? n0 + (rel < n ? rel : 0) : 0;  // a flagged batch stays memory-safe
   }
   __syncwarp();
 }
 
-__global__ void __launch_bounds__(kWgWarps * 32)
+__global__ void __launch_bounds__(kWgWarps * 32, 12)
 k_collate_graph_warp(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, int64_t E, int64_t N, int64_t B,
                      const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ eptr, float fill,
                      int32_t* __restrict__ rowptr, int32_t* __restrict__ col, int32_t* __restrict__ eid,
                      float* __restrict__ dis, int32_t* __restrict__ t_rowptr, int32_t* __restrict__ t_col,
                      int32_t* __restrict__ t_eid, int* __restrict__ status) {
   int* const big_count = status + 1;
-  __shared__ int cnt[kWgWarps][kWgNodes], rp[kWgWarps][kWgNodes + 1], slot_eid[kWgWarps][kWgEdges], slot_val[kWgWarps][kWgEdges];
+  __shared__ int cnt[kWgWarps][kWgNodes], rp[kWgWarps][kWgNodes + 1];
+  __shared__ unsigned slot[kWgWarps][kWgEdges];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t stride = (int64_t)gridDim.x * kWgWarps;
   for (int64_t g = (int64_t)blockIdx.x * kWgWarps + w; g < B; g += stride) {
@@ -497,10 +502,9 @@ k_collate_graph_warp(const int64_t* __restrict__ src, const int64_t* __restrict_
       if (lane == 0) atomicAdd(big_count, 1);  // left to the block-per-graph kernel
       continue;
     }
-    wg_build(dst, src, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot_eid[w], slot_val[w], rowptr, col, eid, dis, fill, N, status);
+    wg_build(dst, src, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot[w], rowptr, col, eid, dis, fill, N, status);
     if (t_rowptr)
-      wg_build(src, dst, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot_eid[w], slot_val[w], t_rowptr, t_col, t_eid, nullptr, fill,
-               N, nullptr);
+      wg_build(src, dst, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot[w], t_rowptr, t_col, t_eid, nullptr, fill, N, nullptr);
   }
 }
 
@@ -615,7 +619,7 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
       HCG_LAUNCH_OK(st, "k_edge_ptr");
     }
     int64_t wb = cdiv(B, kWgWarps);
-    if (wb > (int64_t)kNumSMs * 9) wb = (int64_t)kNumSMs * 9;
+    if (wb > (int64_t)kNumSMs * 12) wb = (int64_t)kNumSMs * 12;
     k_collate_graph_warp<<<(unsigned)wb, kWgWarps * 32, 0, st>>>(src, dst, E, N, B, graph_ptr, w.eptr, fill, rowptr, col, eid, dis,
                                                                 transpose ? t_rowptr : nullptr, t_col, t_eid, w.status);
     HCG_LAUNCH_OK(st, "k_collate_graph_warp");
