@@ -233,25 +233,6 @@ k_dis(const int32_t* __restrict__ rowptr, int64_t N, float fill, float* __restri
 // ------------------------------------------------------------------------------------------
 // 6. graph offsets from the sorted batch vector
 // ------------------------------------------------------------------------------------------
-// first edge e of [0, E) whose dst is >= `node` (edge lists grouped by graph make that predicate monotone;
-// on other inputs the result is some position in [0, E] and the per-edge checks of the graph-local
-// kernels refuse the batch; a node id outside [0, N] cannot reach here: graph_ptr holds offsets).  The search starts from the proportional guess node * E / N.
-__device__ __forceinline__ int32_t first_edge_at(const int64_t* __restrict__ dst, int64_t E, int64_t N, int64_t node) {
-  if (node <= 0) return 0;
-  int64_t lo = 0, hi = E;
-  constexpr int64_t kWin = 2048;
-  const int64_t guess = (int64_t)((double)node * (double)E / (double)N);
-  const int64_t a = guess - kWin, b = guess + kWin;
-  if (a > 0 && a < E && dst[a - 1] < node) lo = a;
-  if (b > 0 && b < E && dst[b] >= node) hi = b;
-  if (lo > hi) { lo = 0; hi = E; }
-  while (lo < hi) {
-    const int64_t mid = (lo + hi) >> 1;
-    if (dst[mid] < node) lo = mid + 1; else hi = mid;
-  }
-  return (int32_t)lo;
-}
-
 __global__ void __launch_bounds__(256)
 k_graph_ptr(const int64_t* __restrict__ batch, int64_t N, int64_t B, int32_t* __restrict__ graph_ptr,
             int* __restrict__ status) {
@@ -278,14 +259,49 @@ k_graph_ptr(const int64_t* __restrict__ batch, int64_t N, int64_t B, int32_t* __
   for (int64_t g = prev + 1; g <= b; ++g) graph_ptr[g] = (int32_t)i;
 }
 
-// eptr[g] = first edge whose dst belongs to graph g or a later one, eptr[B] = E: a thread per graph, one
-// wave of short searches instead of a scan of the whole edge list
-__global__ void __launch_bounds__(64)
+// eptr[g] = first edge whose dst belongs to graph g or a later one, eptr[B] = E.  A warp per graph runs a
+// 32-ary search: the lanes probe 32 evenly spaced positions of the current range at once, a ballot finds the
+// first probe at or past the graph, and the range shrinks 32-fold per step (3 dependent loads inside the
+// +-2048 window around the proportional guess node * E / N, 5 over a whole 4 M-edge list) instead of one load
+// per halving.  Edge lists grouped by graph make "dst[e] >= first node of g" monotone in e; on other inputs
+// the result is some position in [0, E] and the per-edge checks of the build kernels refuse the batch.
+__global__ void __launch_bounds__(256)
 k_edge_ptr(const int64_t* __restrict__ dst, int64_t E, int64_t N, int64_t B, const int32_t* __restrict__ graph_ptr,
            int32_t* __restrict__ eptr) {
-  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g > B) return;
-  eptr[g] = g == B ? (int32_t)E : first_edge_at(dst, E, N, graph_ptr[g]);
+  const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (g > B) return;  // whole warps leave together
+  if (g == B) { if (lane == 0) eptr[B] = (int32_t)E; return; }
+  const int64_t node = graph_ptr[g];
+  if (node <= 0) { if (lane == 0) eptr[g] = 0; return; }
+  int64_t lo = 0, hi = E;
+  {
+    constexpr int64_t kWin = 2048;
+    const int64_t guess = (int64_t)((double)node * (double)E / (double)N);
+    const int64_t a = guess - kWin, b = guess + kWin;
+    // lane 0 tests the lower fence, lane 1 the upper one
+    bool ok = false;
+    if (lane == 0) ok = a > 0 && a < E && dst[a - 1] < node;
+    if (lane == 1) ok = b > 0 && b < E && dst[b] >= node;
+    const unsigned m = __ballot_sync(0xffffffffu, ok);
+    if (m & 1u) lo = a;
+    if (m & 2u) hi = b;
+    if (lo > hi) { lo = 0; hi = E; }
+  }
+  while (hi > lo) {  // answer in [lo, hi]; dst[e] >= node is monotone on grouped input
+    const int64_t step = (hi - lo + 31) >> 5;
+    const int64_t pos = lo + (int64_t)lane * step;
+    const bool ge = pos >= hi ? true : dst[pos] >= node;
+    const unsigned m = __ballot_sync(0xffffffffu, ge);
+    const int f = m ? __ffs(m) - 1 : 32;  // first probe at or past the graph
+    if (f == 0) { hi = lo; break; }
+    const int64_t nlo = lo + (int64_t)(f - 1) * step + 1;
+    int64_t nhi = f < 32 ? lo + (int64_t)f * step : hi;
+    if (nhi > hi) nhi = hi;
+    lo = nlo < nhi ? nlo : nhi;
+    hi = nhi;
+  }
+  if (lane == 0) eptr[g] = (int32_t)lo;
 }
 
 // ==========================================================================================
@@ -615,7 +631,7 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
     k_graph_ptr<<<(unsigned)cdiv(N + 1, 256), 256, 0, st>>>(batch, N, B, graph_ptr, w.status);
     HCG_LAUNCH_OK(st, "k_graph_ptr");
     if (E > 0) {  // E == 0 leaves the cleared eptr
-      k_edge_ptr<<<(unsigned)cdiv(B + 1, 64), 64, 0, st>>>(dst, E, N, B, graph_ptr, w.eptr);
+      k_edge_ptr<<<(unsigned)cdiv((B + 1) * 32, 256), 256, 0, st>>>(dst, E, N, B, graph_ptr, w.eptr);
       HCG_LAUNCH_OK(st, "k_edge_ptr");
     }
     int64_t wb = cdiv(B, kWgWarps);
