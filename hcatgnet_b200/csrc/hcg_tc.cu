@@ -3,6 +3,7 @@
 #include "hcg_common.cuh"
 #include "hcg_fused.cuh"
 #include "hcg_tc.cuh"
+#include <stdlib.h>
 
 namespace hcg {
 
@@ -77,52 +78,66 @@ extern "C" int hcg_selftest_tc_gemm(const float* A, const float* W, int K, float
 // =================================================================================================
 // Graph-resident forward on the tensor cores.
 //
-// A CTA holds two independent "slots" of 128 threads; a slot walks its share of the batch one graph
-// at a time with thread r of the slot owning node r of the graph (= row r of the MMA tile = lane r
-// of tensor memory):
+// A CTA holds two independent "slots" of 256 threads; a slot walks its share of the batch one TILE at
+// a time.  A tile is 128 node rows = the M of one tcgen05.mma = the 128 lanes of tensor memory, and
+// holds ONE OR TWO whole reaction graphs (k_tile_desc pairs graphs of a small window of the batch
+// whose node counts fit together: at 40..120 atoms a tile carries 1.3 graphs and ~85 % of its rows are
+// real nodes instead of 62 %).  The adjacency of a tile is block diagonal, so nothing below cares
+// how many graphs it holds except the pooling.  Two threads own a row (half of the columns each):
 //
-//   prefetch   x rows, rowptr/col slice, deg^-1/2 of the NEXT graph: four bulk async copies
-//              (cp.async.bulk -> mbarrier), issued one graph ahead, double-buffered
-//   layer l    thread r gathers  a_r = sum_j norm_rj * h_j  (neighbours' rows from shared memory),
-//              splits it into TF32 hi/lo and stores it as row r of the A operand in tensor memory;
-//              one elected thread issues the split-TF32 tcgen05.mma chain against W_l^T (shared
-//              memory, swizzled) and commits to an mbarrier; every thread then pulls row r of the
-//              fp32 accumulator back (tcgen05.ld), adds bias, applies LeakyReLU and writes h_r to
-//              the slot's activation buffer (16-byte chunks XOR-swizzled by row: conflict-free for
-//              row-owner stores, column readers and neighbour gathers alike)
-//   pooling    column owners scan the last layer's rows: emb[g] = [max || mean]
+//   prefetch   x rows, rowptr / col slice, deg^-1/2 of the graphs of the NEXT tile: up to eight bulk
+//              async copies (cp.async.bulk -> mbarrier) issued by eight lanes of one warp a whole tile
+//              ahead, double-buffered
+//   layer 0    a_r = sum_j norm_rj x_j gathered straight from the copied x rows (scalar loads: the rows
+//              keep their F-float pitch, no re-pitch pass), norm_rj = dis_r dis_j computed on the fly;
+//              split into TF32 hi / lo and stored as row r of the A operand in tensor memory
+//   MMA        producers bar.arrive, the control warp bar.sync's, its first lane issues the split-TF32
+//              tcgen05.mma chain against W_l^T (shared memory, 128-byte swizzle) and commits to an
+//              mbarrier that every thread of the slot waits on
+//   epilogue   row r of the fp32 accumulator (tcgen05.ld) + bias, LeakyReLU -> activation buffer
+//   layer l>0  a_r = sum_j norm_rj h_j from the activation buffer (128-bit loads), as above
+//   pooling    column owners scan the last layer's rows of each graph of the tile; the eight row
+//              interleaves of a column sit in one warp and are combined by shuffles:
+//              emb[g] = [max || mean]
 //
-// The two slots of a CTA run out of phase, so one slot's gathers overlap the other's MMAs.
-// Nothing of size [N,H] touches HBM unless the caller wants the activations (training forward).
-// Graphs above the slot capacity (128 nodes / kTcEcap CSR slots) are appended to an overflow list
-// that the FMA graph-resident kernel processes afterwards.
+// Blocking synchronisation per tile: the stage mbarrier, per layer the MMA mbarrier and one slot-wide
+// barrier after the epilogue.  The two slots of a CTA run out of phase, so one slot's gathers overlap
+// the other's MMAs.  Nothing of size [N,H] touches HBM unless the caller wants the activations
+// (training forward).  Graphs above the tile capacity (128 nodes / kTcEcap CSR slots) are appended to
+// an overflow list that the FMA graph-resident kernel processes afterwards.
 // =================================================================================================
 namespace hcg {
 
-constexpr int kTcSlots = 2;           // independent graph pipelines per CTA (tensor memory: 256 columns each)
-constexpr int kTcSlotThreads = 256;  // two threads per node row: each owns half of the columns
-constexpr int kTcThreads = kTcSlots * kTcSlotThreads;
-constexpr int kTcNcap = 128;
-constexpr int kTcEcap = 640;
-constexpr int kTcHPitch = 68;        // floats per activation row: 8 consecutive rows cover all banks for 128-bit access
+constexpr int kTcDefaultTpr = 2;     // threads per tile row unless HCG_TC_TPR says otherwise
+constexpr int kTcSlots = 2;           // independent tile pipelines per CTA (tensor memory: 256 columns each)
+constexpr int kTcRows = 128;          // node rows per tile
+constexpr int kTcEcap = 640;          // CSR slots per tile
+constexpr int kTcHPitch = 68;         // floats per activation row: 8 consecutive rows cover all banks for 128-bit access
+constexpr int kTcWinMax = 8;          // graphs per pairing window (at most)
 constexpr int kStatusCrossEdgeTc = 4;
+constexpr int kTileManual = 1;        // TcTile.flags: a 16-byte granular copy window would leave an input array
 
-struct TcSlotMeta {
-  int n0, n, e0, e;
-  int lead_x, lead_rp, lead_cl, lead_ds;  // element offsets of the data inside the 16-byte aligned copies
-  int skip, pad0, pad1, pad2;
+struct __align__(16) TcTile {   // 64 bytes: one tile of the work list
+  int gA, n0A, nA, e0A;         // first graph: id, first node, nodes, first CSR slot
+  int gB, n0B, nB, e0B;         // second graph (gB < 0: none)
+  int eA, eB, flags, pad0;
+  int pad1[4];
 };
 
-struct TcStage {
-  float* x;       // [ncap*F + 4]
-  int32_t* rp;    // [ncap + 1 + 4]
-  int32_t* cl;    // [ecap + 4]
-  float* ds;      // [ncap + 4]
+struct __align__(16) TcMeta {   // a tile as the slot's threads see it
+  int gA, n0A, nA, e0A;
+  int gB, n0B, nB, e0B;
+  int eA, eB, flags, pad0;
+  int off[8];                   // [4 gb + q]: word offset, inside stage array q (0 x, 1 rowptr, 2 col, 3 dis),
+                                // of element 0 of graph gb's slice
 };
 
 struct TcArgs {
   FusedFwdArgs f;
-  const int4* gdesc;     // [B] {n0, n, e0, e}; e < 0: not for this kernel (on the overflow list)
+  const TcTile* tiles;      // [nslots][cap] dense per-slot work lists
+  const int* counts;        // [nslots]
+  int cap;
+  int64_t N, E;
 };
 
 // The 16-byte granular window [lo, lo + bytes) the bulk copy of `count` 4-byte elements at `p` reads.
@@ -132,64 +147,116 @@ __host__ __device__ __forceinline__ void copy_window(uintptr_t p, int count, uin
   *bytes = (uint32_t)(((p - *lo) + (uintptr_t)count * 4 + 15) & ~uintptr_t(15));
 }
 
-// Per-graph descriptor + routing: graphs above the slot capacity and graphs without nodes or edges go to
-// the overflow list (the FMA graph-resident kernel); everything else runs on the tensor-core kernel.
-// A graph whose 16-byte granular copy windows would reach past the end of an input array (the last
-// graph of a batch) is flagged (n stored negated): its slot fetches it with ordinary loads.
-__global__ void __launch_bounds__(256)
-k_graph_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
-             const float* __restrict__ dis, const float* __restrict__ x, int F, int64_t N, int64_t E, int64_t B,
-             int4* __restrict__ gdesc, int* __restrict__ overflow_count, int* __restrict__ overflow_list) {
-  int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= B) return;
-  const int n0 = graph_ptr[g], n = graph_ptr[g + 1] - n0;
-  const int e0 = rowptr[n0], e = rowptr[n0 + n] - e0;
-  const bool skip = n <= 0 || e <= 0 || n > kTcNcap || e > kTcEcap;
-  bool manual = false;  // a 16-byte granular copy window would reach past the end of an input array
-  if (!skip) {
-    uintptr_t lo; uint32_t bytes; int lead;
-    copy_window(reinterpret_cast<uintptr_t>(x + (int64_t)n0 * F), n * F, &lo, &bytes, &lead);
-    manual |= lo + bytes > reinterpret_cast<uintptr_t>(x + N * F);
-    copy_window(reinterpret_cast<uintptr_t>(rowptr + n0), n + 1, &lo, &bytes, &lead);
-    manual |= lo + bytes > reinterpret_cast<uintptr_t>(rowptr + N + 1);
-    copy_window(reinterpret_cast<uintptr_t>(col + e0), e, &lo, &bytes, &lead);
-    manual |= lo + bytes > reinterpret_cast<uintptr_t>(col + E);
-    copy_window(reinterpret_cast<uintptr_t>(dis + n0), n, &lo, &bytes, &lead);
-    manual |= lo + bytes > reinterpret_cast<uintptr_t>(dis + N);
+// ---- work list ----------------------------------------------------------------------------------
+// A warp per slot of the forward kernel; lane w takes the w-th window of W consecutive graphs that the slot
+// owns (windows are dealt round-robin to the slots), pairs its graphs greedily (first unpaired graph + the
+// largest later graph of the window that still fits the tile), and the lanes' tiles are written densely,
+// in window order, through a warp scan.  Graphs above the tile capacity and graphs without nodes or edges
+// go to the overflow list (the FMA graph-resident kernel).
+__global__ void __launch_bounds__(128)
+k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+            const float* __restrict__ dis, const float* __restrict__ x, int F, int64_t N, int64_t E, int64_t B, int W,
+            int nslots, int nwin, int cap, TcTile* __restrict__ tiles, int* __restrict__ counts,
+            int* __restrict__ overflow_count, int* __restrict__ overflow_list) {
+  const int slot = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int lane = threadIdx.x & 31;
+  if (slot >= nslots) return;  // whole warps leave together
+  TcTile* out = tiles + (size_t)slot * cap;
+  int total = 0;
+  const int wps = (nwin + nslots - 1) / nslots;
+  for (int w0 = 0; w0 < wps; w0 += 32) {
+    const int win = slot + (w0 + lane) * nslots;
+    int gp[kTcWinMax + 1], ee[kTcWinMax + 1];
+    const int64_t g0 = (int64_t)win * W;
+    const bool live = (w0 + lane) < wps && win < nwin;
+    int wcnt = 0;
+    if (live) wcnt = (int)((B - g0) < (int64_t)W ? (B - g0) : (int64_t)W);
+#pragma unroll
+    for (int k = 0; k <= kTcWinMax; ++k) gp[k] = (live && k <= wcnt) ? graph_ptr[g0 + k] : 0;
+#pragma unroll
+    for (int k = 0; k <= kTcWinMax; ++k) ee[k] = (live && k <= wcnt) ? rowptr[gp[k]] : 0;
+    unsigned used = 0, manual = 0;  // bit k: graph k of the window is not available / needs ordinary loads
+#pragma unroll
+    for (int k = 0; k < kTcWinMax; ++k) {
+      const int n = gp[k + 1] - gp[k], e = ee[k + 1] - ee[k];
+      if (k >= wcnt) { used |= 1u << k; continue; }
+      if (n <= 0 || e <= 0 || n > kTcRows || e > kTcEcap) {
+        used |= 1u << k;
+        overflow_list[atomicAdd(overflow_count, 1)] = (int)(g0 + k);
+        continue;
+      }
+      uintptr_t lo; uint32_t bytes; int lead;
+      bool m = false;
+      copy_window(reinterpret_cast<uintptr_t>(x + (int64_t)gp[k] * F), n * F, &lo, &bytes, &lead);
+      m |= lo + bytes > reinterpret_cast<uintptr_t>(x + N * F);
+      copy_window(reinterpret_cast<uintptr_t>(rowptr + gp[k]), n + 1, &lo, &bytes, &lead);
+      m |= lo + bytes > reinterpret_cast<uintptr_t>(rowptr + N + 1);
+      copy_window(reinterpret_cast<uintptr_t>(col + ee[k]), e, &lo, &bytes, &lead);
+      m |= lo + bytes > reinterpret_cast<uintptr_t>(col + E);
+      copy_window(reinterpret_cast<uintptr_t>(dis + gp[k]), n, &lo, &bytes, &lead);
+      m |= lo + bytes > reinterpret_cast<uintptr_t>(dis + N);
+      if (m) manual |= 1u << k;
+    }
+    // greedy pairing inside the window
+    unsigned leader = 0;
+    int partner[kTcWinMax];
+#pragma unroll
+    for (int a = 0; a < kTcWinMax; ++a) {
+      partner[a] = -1;
+      if (used & (1u << a)) continue;
+      used |= 1u << a;
+      leader |= 1u << a;
+      const int na = gp[a + 1] - gp[a], ea = ee[a + 1] - ee[a];
+      int best = -1, bn = 0;
+#pragma unroll
+      for (int b = a + 1; b < kTcWinMax; ++b) {
+        const int nb = gp[b + 1] - gp[b], eb = ee[b + 1] - ee[b];
+        if (!(used & (1u << b)) && na + nb <= kTcRows && ea + eb <= kTcEcap && nb > bn) { best = b; bn = nb; }
+      }
+      if (best >= 0) used |= 1u << best;
+      partner[a] = best;
+    }
+    const int cnt = __popc(leader);
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += u;
+    }
+    int pos = total + incl - cnt;
+    total += __shfl_sync(0xffffffffu, incl, 31);
+#pragma unroll
+    for (int a = 0; a < kTcWinMax; ++a) {
+      if (!(leader & (1u << a))) continue;
+      TcTile t;
+      t.gA = (int)(g0 + a); t.n0A = gp[a]; t.nA = gp[a + 1] - gp[a]; t.e0A = ee[a]; t.eA = ee[a + 1] - ee[a];
+      t.gB = -1; t.n0B = 0; t.nB = 0; t.e0B = 0; t.eB = 0;
+      t.flags = (manual >> a) & 1u ? kTileManual : 0;
+      const int b = partner[a];
+#pragma unroll
+      for (int k = 1; k < kTcWinMax; ++k) {
+        if (k == b) {
+          t.gB = (int)(g0 + k); t.n0B = gp[k]; t.nB = gp[k + 1] - gp[k]; t.e0B = ee[k]; t.eB = ee[k + 1] - ee[k];
+          if ((manual >> k) & 1u) t.flags |= kTileManual;
+        }
+      }
+      t.pad0 = 0; t.pad1[0] = t.pad1[1] = t.pad1[2] = t.pad1[3] = 0;
+      int4* o4 = reinterpret_cast<int4*>(out + pos);
+      o4[0] = make_int4(t.gA, t.n0A, t.nA, t.e0A);
+      o4[1] = make_int4(t.gB, t.n0B, t.nB, t.e0B);
+      o4[2] = make_int4(t.eA, t.eB, t.flags, 0);
+      ++pos;
+    }
   }
-  if (skip) overflow_list[atomicAdd(overflow_count, 1)] = (int)g;
-  gdesc[g] = make_int4(n0, manual ? -n : n, e0, skip ? -1 : e);
+  if (lane == 0) counts[slot] = total;
 }
 
-// thread 0 of a slot: start the four copies of one graph into a stage (branch-free for routed graphs)
-__device__ __forceinline__ void tc_prefetch(const TcArgs& a, int4 d, const TcStage& st, TcSlotMeta* meta, uint64_t* bar) {
-  meta->n0 = d.x; meta->n = d.y < 0 ? -d.y : d.y; meta->e0 = d.z; meta->e = d.w;
-  meta->skip = d.w < 0 ? 1 : (d.y < 0 ? 2 : 0);
-  meta->lead_x = meta->lead_rp = meta->lead_cl = meta->lead_ds = 0;
-  if (d.w < 0 || d.y < 0) {
-    ptx::mbar_arrive(bar);
-    return;
-  }
-  uintptr_t lo0, lo1, lo2, lo3;
-  uint32_t b0, b1, b2, b3;
-  int l0, l1, l2, l3;
-  copy_window(reinterpret_cast<uintptr_t>(a.f.x + (int64_t)d.x * a.f.F), d.y * a.f.F, &lo0, &b0, &l0);
-  copy_window(reinterpret_cast<uintptr_t>(a.f.rowptr + d.x), d.y + 1, &lo1, &b1, &l1);
-  copy_window(reinterpret_cast<uintptr_t>(a.f.col + d.z), d.w, &lo2, &b2, &l2);
-  copy_window(reinterpret_cast<uintptr_t>(a.f.dis + d.x), d.y, &lo3, &b3, &l3);
-  // the metadata must be in place before the arrival that can complete the phase (release/acquire)
-  meta->lead_x = l0; meta->lead_rp = l1; meta->lead_cl = l2; meta->lead_ds = l3;
-  ptx::mbar_expect_tx(bar, b0 + b1 + b2 + b3);  // the slot's single arrival for this phase + the bytes in flight
-  ptx::bulk_g2s(st.x, reinterpret_cast<const void*>(lo0), b0, bar);
-  ptx::bulk_g2s(st.rp, reinterpret_cast<const void*>(lo1), b1, bar);
-  ptx::bulk_g2s(st.cl, reinterpret_cast<const void*>(lo2), b2, bar);
-  ptx::bulk_g2s(st.ds, reinterpret_cast<const void*>(lo3), b3, bar);
-}
-
-// shared-memory carve-up, identical on host (size query) and device
+// shared-memory carve-up, identical on host (size query) and device; weights first, then per slot the
+// activation buffer and two input stages.  Offsets in BYTES from the 1024-aligned base; stage array sizes in
+// 4-byte words (multiples of 4, so every array is 16-byte aligned).
 struct TcSmemLayout {
-  uint32_t w0_hi, w0_lo, wl, bias, hbuf, wbuf, pool, stage;  // byte offsets from the 1024-aligned base
-  uint32_t x_bytes, rp_bytes, cl_bytes, ds_bytes, stage_bytes, total;
+  uint32_t w0_hi, w0_lo, wl, bias, hbuf, nbr, stage;
+  uint32_t xw, rw, cw, dw, stage_words, slot_bytes, total;
 };
 __host__ __device__ inline TcSmemLayout tc_layout(int F, int L) {
   TcSmemLayout y;
@@ -198,41 +265,19 @@ __host__ __device__ inline TcSmemLayout tc_layout(int F, int L) {
   y.w0_lo = p; p += tc::kN * 32 * 4;
   y.wl = p; p += (uint32_t)(L - 1) * 2 * tc::kN * 64 * 4;  // per layer: hi tile, lo tile
   y.bias = p; p += (uint32_t)L * 64 * 4;
-  y.hbuf = p; p += (uint32_t)kTcSlots * kTcNcap * kTcHPitch * 4;
-  y.wbuf = p; p += (uint32_t)kTcSlots * kTcEcap * 4;
-  y.pool = p; p += (uint32_t)kTcSlots * 4 * 128 * 4;
-  y.x_bytes = ((uint32_t)kTcNcap * F * 4 + 16 + 15) & ~15u;
-  y.rp_bytes = ((uint32_t)(kTcNcap + 1) * 4 + 16 + 15) & ~15u;
-  y.cl_bytes = ((uint32_t)kTcEcap * 4 + 16 + 15) & ~15u;
-  y.ds_bytes = ((uint32_t)kTcNcap * 4 + 16 + 15) & ~15u;
-  y.stage_bytes = y.x_bytes + y.rp_bytes + y.cl_bytes + y.ds_bytes;
-  y.stage = p; p += (uint32_t)kTcSlots * 2 * y.stage_bytes;
+  // two slices per array, each a 16-byte granular window: up to 12 + 15 bytes of slack per slice
+  y.xw = ((uint32_t)kTcRows * F + 16 + 3) & ~3u;
+  y.rw = ((uint32_t)kTcRows + 2 + 16 + 3) & ~3u;
+  y.cw = ((uint32_t)kTcEcap + 16 + 3) & ~3u;
+  y.dw = ((uint32_t)kTcRows + 16 + 3) & ~3u;
+  y.stage_words = y.xw + y.rw + y.cw + y.dw;
+  y.hbuf = p;
+  y.slot_bytes = (uint32_t)kTcRows * kTcHPitch * 4 + (uint32_t)kTcEcap * 8 + 2 * y.stage_words * 4;
+  y.nbr = p + (uint32_t)kTcRows * kTcHPitch * 4;    // slot 0's (tile row, norm) record per CSR slot
+  y.stage = y.nbr + (uint32_t)kTcEcap * 8;          // slot 0's first stage
+  p += (uint32_t)kTcSlots * y.slot_bytes;
   y.total = p + 1024;  // slack for the 1024-byte alignment of the base
   return y;
-}
-
-// One thread's share of a gather: NCH 16-byte chunks, starting at chunk q0, of the rows of `src` (pitch
-// P floats):  acc = sum_k w_k * src[j_k] over the row's CSR slots, then the self-loop (last, as in the
-// reference).  `jl` holds graph-local neighbour ids, `wn` the matching norm_ij (both per CSR slot).
-template <int NCH, int P, int NACC>
-__device__ __forceinline__ void gather_rows(float (&acc)[NACC], const float* src, const int32_t* jl,
-                                            const float* wn, int beg, int end, int i, float wself, int q0) {
-#pragma unroll
-  for (int c = 0; c < NACC; ++c) acc[c] = 0.f;
-  for (int kk = beg; kk <= end; ++kk) {
-    int j = i;
-    float w = wself;
-    if (kk < end) { j = jl[kk]; w = wn[kk]; }
-    const float4* row = reinterpret_cast<const float4*>(src + j * P) + q0;
-#pragma unroll
-    for (int q = 0; q < NCH; ++q) {
-      const float4 v = row[q];
-      acc[4 * q + 0] = fmaf(w, v.x, acc[4 * q + 0]);
-      acc[4 * q + 1] = fmaf(w, v.y, acc[4 * q + 1]);
-      acc[4 * q + 2] = fmaf(w, v.z, acc[4 * q + 2]);
-      acc[4 * q + 3] = fmaf(w, v.w, acc[4 * q + 3]);
-    }
-  }
 }
 
 #ifdef HCG_TC_TIMING
@@ -242,74 +287,95 @@ __device__ unsigned long long g_tc_timing[16];
 #define TC_TICK(slot_) do { } while (0)
 #endif
 
-// NQ = 16-byte chunks per re-pitched x row (7: F <= 28, 8: F <= 32); the pitch P keeps P/4 odd so that
-// eight consecutive rows cover all 32 banks for 128-bit reads.
-template <int NQ>
-__global__ void __launch_bounds__(kTcThreads, 1)
+// Layer-0 gather of one thread: acc[c] = sum_j w_j x[j][c] over its NC columns (NC < 0: `ncol` at run time), rows
+// walked as (tile row, norm) records; every lane takes `maxdeg` steps (a lane past its own degree adds
+// 0 x its own row), then the self-loop, last, as in the reference.  `xcol`: the thread's first column of tile row 0.
+template <int NC, int XW>
+__device__ __forceinline__ void gather_x(float (&acc)[XW], const float* xcol, int F, const int2* nbp, int deg, int maxdeg,
+                                         int iself, float wself, int ncol = 0) {
+  if (NC == 0) return;
+  auto row_fma = [&](int r, float w) {
+    const float* xr = xcol + r * F;
+#pragma unroll
+    for (int c = 0; c < XW; ++c)
+      if (NC < 0 ? c < ncol : c < NC) acc[c] = fmaf(w, xr[c], acc[c]);
+  };
+  int2 nb = 0 < deg ? nbp[0] : make_int2(iself, 0);
+  for (int t = 0; t < maxdeg; ++t) {
+    const int2 cur = nb;
+    nb = t + 1 < deg ? nbp[t + 1] : make_int2(iself, 0);
+    if (t < deg)   // (a lane past its own degree idles: fewer shared-memory wavefronts than adding 0 x its own row)
+      row_fma(cur.x, __int_as_float(cur.y));
+  }
+  row_fma(iself, wself);
+}
+
+// F_ = compile-time number of input features (25: the RhCAA featuriser, 32: biaryl) or 0 = run-time F <= 32.
+// TPR = threads per tile row (2 or 4): a row's columns are split over TPR threads that sit in TPR different
+// warps of the same lane quadrant; a slot has 128 TPR threads, the CTA 256 TPR.
+template <int F_, int TPR>
+__global__ void __launch_bounds__(kTcSlots * 128 * TPR, 1)
 k_tc_fwd(const TcArgs a) {
 #ifdef HCG_TC_TIMING
   long long t_prev = clock64();
 #endif
-  constexpr int P = (NQ & 1) ? 4 * NQ : 4 * NQ + 4;
   constexpr int HP = kTcHPitch;
+  constexpr int kSlotThreads = 128 * TPR, kThreads = kTcSlots * kSlotThreads, NW = 4 * TPR;
+  constexpr int CW = 64 / TPR;    // hidden columns per thread (gather of layers >= 1, epilogue)
+  constexpr int XW = 32 / TPR;    // input columns per thread (layer-0 gather)
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ uint64_t bar_stage[kTcSlots][2];
   __shared__ uint64_t bar_mma[kTcSlots];
   __shared__ uint32_t tmem_base_s;
-  __shared__ TcSlotMeta metas[kTcSlots][2];
+  __shared__ TcMeta metas[kTcSlots][2];
+  __shared__ int4 recs[kTcSlots][2][3];   // work-list records in flight (cp.async), two deep
 
   const int tid = threadIdx.x;
-  const int slot = tid / kTcSlotThreads, gt = tid % kTcSlotThreads;
-  const int half = gt >> 7;          // which half of the columns this thread works on
-  // Node (row of the graph) owned by this thread.  Its TMEM lane is fixed by the hardware (lane quadrant
-  // = warp id % 4 = the warp scheduler), and graphs fill rows from 0 up, so slot 1 maps its nodes in
-  // reverse: slot 0 loads schedulers 0,1 the most, slot 1 schedulers 3,2.
+  const int slot = tid / kSlotThreads, gt = tid % kSlotThreads;
+  const int cg = gt >> 7;            // which group of columns this thread works on
+  const int wslot = gt >> 5;         // warp inside the slot
+  // Tile row owned by this thread.  Its TMEM lane is fixed by the hardware (lane quadrant = warp id % 4 =
+  // the warp scheduler), and tiles fill rows from 0 up, so slot 1 maps its rows in reverse: slot 0 loads
+  // schedulers 0,1 the most, slot 1 schedulers 3,2.
   const int i = slot == 0 ? (gt & 127) : 127 - (gt & 127);
-  const int i_warp_min = slot == 0 ? (gt & 96) : 96 - (gt & 96);  // smallest node id owned by this warp
-  // the warp of each slot whose quadrant is filled last does the waiting and the MMA issue for the slot
-  const bool ctl_warp = (gt >> 5) == (slot == 0 ? 3 : 0);
+  const int i_warp_min = slot == 0 ? (gt & 96) : 96 - (gt & 96);  // smallest row owned by this warp
+  // the warp of each slot whose quadrant is filled last issues the MMAs; its sibling in the last column
+  // group feeds the slot (bulk copies of the next tile)
+  const bool ctl_warp = wslot == (slot == 0 ? 3 : 0);
+  const bool pf_warp = wslot == (slot == 0 ? NW - 1 : NW - 4);
   const int lane = tid & 31;
-  // the control warp's first lane also feeds the slot: it issues the next graph's bulk copies while the
-  // layer-0 MMAs run (it would only be polling their mbarrier), off the other warps' critical path
-  const bool pf_thread = ctl_warp && lane == 0;
-  const int F = a.f.F, L = a.f.L;
+  const int F = F_ > 0 ? F_ : a.f.F;
+  const int L = a.f.L;
 
-  // ---- carve shared memory (pointer arithmetic on the shared array only: keeps the address space) --
+  // ---- carve shared memory (one base pointer, word offsets: keeps every access an LDS / STS) -------
   const TcSmemLayout lay = tc_layout(F, L);
   unsigned char* base = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
+  float* smf = reinterpret_cast<float*>(base);
+  int32_t* smi = reinterpret_cast<int32_t*>(base);
   float* w0_hi = reinterpret_cast<float*>(base + lay.w0_hi);
   float* w0_lo = reinterpret_cast<float*>(base + lay.w0_lo);
   float* wl_base = reinterpret_cast<float*>(base + lay.wl);
   float* s_bias = reinterpret_cast<float*>(base + lay.bias);
-  float* Hbuf = reinterpret_cast<float*>(base + lay.hbuf) + (size_t)slot * kTcNcap * HP;
-  float* wn = reinterpret_cast<float*>(base + lay.wbuf) + (size_t)slot * kTcEcap;
-  float* s_pool = reinterpret_cast<float*>(base + lay.pool) + slot * 4 * 128;
-  unsigned char* stage0 = base + lay.stage + (size_t)slot * 2 * lay.stage_bytes;
-  auto stage_of = [&](int s) {
-    TcStage t;
-    unsigned char* q = stage0 + (size_t)s * lay.stage_bytes;
-    t.x = reinterpret_cast<float*>(q); q += lay.x_bytes;
-    t.rp = reinterpret_cast<int32_t*>(q); q += lay.rp_bytes;
-    t.cl = reinterpret_cast<int32_t*>(q); q += lay.cl_bytes;
-    t.ds = reinterpret_cast<float*>(q);
-    return t;
-  };
+  const int hb_w = (int)((lay.hbuf + (uint32_t)slot * lay.slot_bytes) >> 2);        // activation buffer, word offset
+  const int nb_w = (int)((lay.nbr + (uint32_t)slot * lay.slot_bytes) >> 2);         // neighbour records, word offset
+  const int st_w0 = (int)((lay.stage + (uint32_t)slot * lay.slot_bytes) >> 2);      // stage 0, word offset
+  const int xw = (int)lay.xw, rw = (int)lay.rw, cw = (int)lay.cw, stw = (int)lay.stage_words;
 
   // ---- one-time setup ----------------------------------------------------------------------------
   if (tid < 32) ptx::tmem_alloc(&tmem_base_s, 512);
   if (tid == 0) {
     for (int s = 0; s < kTcSlots; ++s) {
-      ptx::mbar_init(&bar_stage[s][0], 1);
-      ptx::mbar_init(&bar_stage[s][1], 1);
+      ptx::mbar_init(&bar_stage[s][0], 8);   // the eight feeding lanes: arrive (+ expect_tx) once per tile each
+      ptx::mbar_init(&bar_stage[s][1], 8);
       ptx::mbar_init(&bar_mma[s], 1);
     }
     ptx::fence_mbar_init();
   }
-  tc::prep_weight_tiles(a.f.conv_w[0], F, 32, w0_hi, w0_lo, tid, kTcThreads);
+  tc::prep_weight_tiles(a.f.conv_w[0], F, 32, w0_hi, w0_lo, tid, kThreads);
   for (int l = 1; l < L; ++l)
     tc::prep_weight_tiles(a.f.conv_w[l], 64, 64, wl_base + (size_t)(l - 1) * 2 * tc::kN * 64,
-                          wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64, tid, kTcThreads);
-  for (int idx = tid; idx < L * 64; idx += kTcThreads) s_bias[idx] = __ldg(a.f.conv_b[idx >> 6] + (idx & 63));
+                          wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64, tid, kThreads);
+  for (int idx = tid; idx < L * 64; idx += kThreads) s_bias[idx] = __ldg(a.f.conv_b[idx >> 6] + (idx & 63));
   ptx::fence_proxy_async_smem();
   ptx::tc_fence_before_sync();
   __syncthreads();
@@ -317,191 +383,321 @@ k_tc_fwd(const TcArgs a) {
 
   const uint32_t tbase = tmem_base_s + (uint32_t)slot * 256;  // accumulator | (free) | A hi | A lo, 64 columns each
   const uint32_t d_t = tbase, a_hi = tbase + 128, a_lo = tbase + 192;
-  const uint32_t trow = (uint32_t)(((gt >> 5) & 3) * 32) << 16;  // warps w and w+4 share a lane quadrant
-  const int bar_id = 1 + slot;
+  const uint32_t trow = (uint32_t)((wslot & 3) * 32) << 16;  // warps w, w + 4, ... share a lane quadrant
+  const int bar_full = 1 + slot;   // all threads of the slot
+  const int bar_aop = 3 + slot;    // A operand complete: the other warps arrive, the control warp waits
   const float slope = a.f.slope;
 
-  const int64_t first = (int64_t)blockIdx.x * kTcSlots + slot;
-  const int64_t stride = (int64_t)gridDim.x * kTcSlots;
-  int4 d_next = make_int4(0, 0, 0, -1);
-  if (pf_thread && first < a.f.B) {
-    tc_prefetch(a, a.gdesc[first], stage_of(0), &metas[slot][0], &bar_stage[slot][0]);
-    if (first + stride < a.f.B) d_next = a.gdesc[first + stride];
+  const int slot_id = blockIdx.x * kTcSlots + slot;
+  const int ntiles = a.counts[slot_id];
+  const TcTile* my_tiles = a.tiles + (size_t)slot_id * a.cap;
+
+  // Feeding lanes (lane < 8 of pf_warp): lane = 4 gb + q copies slice q (0 x, 1 rowptr, 2 col, 3 dis) of graph gb.
+  // The record of tile t travels global -> recs[t & 1] by cp.async (three lanes, 16 bytes each), a tile ahead.
+  auto fetch_rec = [&](int t) {
+    if (t < ntiles && lane < 3) ptx::cp_async16(&recs[slot][t & 1][lane], reinterpret_cast<const int4*>(my_tiles + t) + lane);
+  };
+  // issue the copies of tile t into stage t & 1 (or mark the stage as "no more tiles")
+  auto issue = [&](int t) {
+    const int s = t & 1;
+    TcMeta* m = &metas[slot][s];
+    uint64_t* bar = &bar_stage[slot][s];
+    ptx::cp_async_wait_all();   // this lane's part of the record ...
+    __syncwarp();               // ... and the other lanes'
+    if (lane >= 8) return;
+    if (t >= ntiles) {
+      if (lane == 0) m->gA = -1;
+      ptx::mbar_arrive(bar);
+      return;
+    }
+    const int4 r0 = recs[slot][s][0], r1 = recs[slot][s][1], r2 = recs[slot][s][2];
+    const int gb = lane >> 2, q = lane & 3;
+    const int n0 = gb ? r1.y : r0.y, n = gb ? r1.z : r0.z, e0 = gb ? r1.w : r0.w, e = gb ? r2.y : r2.x;
+    const bool have = gb == 0 || r1.x >= 0;
+    const bool manual = (r2.z & kTileManual) != 0;
+    // slice q of graph A too (every lane needs its window size: graph B's slice lands right behind it)
+    uintptr_t pA, pS;
+    int cA, cS;
+    if (q == 0) { pA = reinterpret_cast<uintptr_t>(a.f.x + (int64_t)r0.y * F); cA = r0.z * F;
+                  pS = reinterpret_cast<uintptr_t>(a.f.x + (int64_t)n0 * F); cS = n * F; }
+    else if (q == 1) { pA = reinterpret_cast<uintptr_t>(a.f.rowptr + r0.y); cA = r0.z + 1;
+                       pS = reinterpret_cast<uintptr_t>(a.f.rowptr + n0); cS = n + 1; }
+    else if (q == 2) { pA = reinterpret_cast<uintptr_t>(a.f.col + r0.w); cA = r2.x;
+                       pS = reinterpret_cast<uintptr_t>(a.f.col + e0); cS = e; }
+    else { pA = reinterpret_cast<uintptr_t>(a.f.dis + r0.y); cA = r0.z;
+           pS = reinterpret_cast<uintptr_t>(a.f.dis + n0); cS = n; }
+    uintptr_t loA, loS;
+    uint32_t bA, bS;
+    int leadA, leadS;
+    copy_window(pA, cA, &loA, &bA, &leadA);
+    copy_window(pS, cS, &loS, &bS, &leadS);
+    if (manual) { leadA = 0; leadS = 0; bA = (uint32_t)((cA * 4 + 15) & ~15); }   // ordinary loads place the slices themselves
+    const int arr_w = st_w0 + s * stw + (q == 0 ? 0 : q == 1 ? xw : q == 2 ? xw + rw : xw + rw + cw);
+    const int dst_w = arr_w + (gb ? (int)(bA >> 2) : 0);
+    if (lane == 0) {
+      m->gA = r0.x; m->n0A = r0.y; m->nA = r0.z; m->e0A = r0.w;
+      m->gB = r1.x; m->n0B = r1.y; m->nB = r1.x >= 0 ? r1.z : 0; m->e0B = r1.w;
+      m->eA = r2.x; m->eB = r2.y; m->flags = r2.z;
+    }
+    m->off[lane] = (gb ? (int)(bA >> 2) : 0) + leadS;
+    // the metadata must be in place before the arrival that can complete the phase (release / acquire)
+    if (!have || manual) {
+      ptx::mbar_arrive(bar);
+    } else {
+      ptx::mbar_expect_tx(bar, bS);   // this lane's arrival for the phase + its bytes in flight
+      ptx::bulk_g2s(smf + dst_w, reinterpret_cast<const void*>(loS), bS, bar);
+    }
+  };
+
+  // ---- pooling: warp w owns columns 4 w + cc (+ 32 with two threads per row), cc = lane & 3; the eight
+  //      lanes of a column take the rows of a graph eight apart (bank = 4 row + column: conflict-free)
+  //      and are combined by shuffles.  Runs one tile late, inside the next tile's layer-0 MMA window. ----
+  auto pool_tile = [&](int gA, int gB, int nA, int nB) {
+    constexpr int CPL = 64 / (4 * NW);   // columns per lane
+    const int cc = lane & 3, q = lane >> 2;
+    const int c0 = 4 * wslot + cc;
+    const float* hp = smf + hb_w + c0;
+    for (int gb = 0; gb < (nB > 0 ? 2 : 1); ++gb) {
+      const int rb = gb ? nA : 0, n = gb ? nB : nA;
+      float mx[CPL], sm[CPL];
+#pragma unroll
+      for (int u = 0; u < CPL; ++u) { mx[u] = -INFINITY; sm[u] = 0.f; }
+      int r = rb + q;
+      for (; r + 8 < rb + n; r += 16) {
+#pragma unroll
+        for (int u = 0; u < CPL; ++u) {
+          const float v0 = hp[r * HP + 32 * u], v1 = hp[(r + 8) * HP + 32 * u];
+          mx[u] = fmaxf(mx[u], fmaxf(v0, v1));
+          sm[u] += v0; sm[u] += v1;
+        }
+      }
+      if (r < rb + n) {
+#pragma unroll
+        for (int u = 0; u < CPL; ++u) {
+          const float v0 = hp[r * HP + 32 * u];
+          mx[u] = fmaxf(mx[u], v0);
+          sm[u] += v0;
+        }
+      }
+#pragma unroll
+      for (int o = 4; o < 32; o <<= 1) {
+#pragma unroll
+        for (int u = 0; u < CPL; ++u) {
+          mx[u] = fmaxf(mx[u], __shfl_xor_sync(0xffffffffu, mx[u], o));
+          sm[u] += __shfl_xor_sync(0xffffffffu, sm[u], o);
+        }
+      }
+      if (q == 0) {
+        float* eo = a.f.emb + (int64_t)(gb ? gB : gA) * 128;
+        const float inv = 1.f / (float)n;   // one division per graph; the mean is sum * (1 / n)
+#pragma unroll
+        for (int u = 0; u < CPL; ++u) {
+          eo[c0 + 32 * u] = mx[u];
+          eo[64 + c0 + 32 * u] = sm[u] * inv;
+        }
+      }
+    }
+  };
+  int p_gA = -1, p_gB = -1, p_nA = 0, p_nB = 0;   // the tile whose last-layer rows sit in the activation buffer, not yet pooled
+
+  if (pf_warp) {
+    fetch_rec(0);
+    issue(0);
+    fetch_rec(1);
   }
   uint32_t mma_phase = 0;
-  int k = 0;
-  for (int64_t gid = first; gid < a.f.B; gid += stride, ++k) {
+  for (int k = 0;; ++k) {
     const int s = k & 1;
-    // next graph -> the other stage; its readers finished with the previous iteration.  Issued by pf_thread
-    // either right here (this graph is skipped) or after the layer-0 MMAs have been committed.
-    auto issue_next = [&]() {
-      if (gid + stride < a.f.B) {
-        tc_prefetch(a, d_next, stage_of(s ^ 1), &metas[slot][s ^ 1], &bar_stage[slot][s ^ 1]);
-        if (gid + 2 * stride < a.f.B) d_next = a.gdesc[gid + 2 * stride];
-      }
-    };
     TC_TICK(0);
     ptx::mbar_wait(&bar_stage[slot][s], (uint32_t)(k >> 1) & 1u);
     TC_TICK(1);
-    const TcSlotMeta m = metas[slot][s];
-    if (m.skip == 1) {  // slot-uniform: this graph is on the overflow list
-      if (pf_thread) issue_next();
-      continue;
+    const TcMeta* mp = &metas[slot][s];
+    const int gA = mp->gA;
+    if (gA < 0) break;  // slot-uniform: no more tiles
+    // next tile -> the other stage: its readers (the precompute pass of tile k - 1) are long done, and its
+    // record slot recs[(k + 2) & 1] was read when tile k was issued
+    if (pf_warp) {
+      issue(k + 1);
+      fetch_rec(k + 2);
     }
-    const int n = m.n, n0 = m.n0, e0 = m.e0;
-    const TcStage st = stage_of(s);
-    if (m.skip == 2) {  // flagged graph: fetch the four slices with ordinary loads
-      for (int idx = gt; idx < n * F; idx += kTcSlotThreads) st.x[idx] = __ldg(a.f.x + (int64_t)n0 * F + idx);
-      for (int idx = gt; idx <= n; idx += kTcSlotThreads) st.rp[idx] = __ldg(a.f.rowptr + n0 + idx);
-      for (int idx = gt; idx < m.e; idx += kTcSlotThreads) st.cl[idx] = __ldg(a.f.col + e0 + idx);
-      for (int idx = gt; idx < n; idx += kTcSlotThreads) st.ds[idx] = __ldg(a.f.dis + n0 + idx);
-      ptx::named_bar_sync(bar_id, kTcSlotThreads);
-    }
-    const float* xs = st.x + m.lead_x;
-    const int32_t* rp = st.rp + m.lead_rp;
-    int32_t* cl = st.cl + m.lead_cl;
-    const float* ds = st.ds + m.lead_ds;
-    const bool row_ok = i < n;
-    const bool warp_ok = i_warp_min < n;  // this warp owns at least one node of the graph
-
-    // ---- re-pitch the x rows to P floats (zero padded) inside the idle activation buffer: a warp per
-    //      row, a lane per column ------------------------------------------------------------------------
-    for (int r0 = gt >> 5; r0 < n; r0 += 4 * (kTcSlotThreads / 32)) {  // four rows in flight per warp
-      float v[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int r = r0 + u * (kTcSlotThreads / 32);
-        v[u] = (r < n && lane < F) ? xs[r * F + lane] : 0.f;
+    const int nA = mp->nA, nB = mp->nB, gB = mp->gB, eA = mp->eA;   // (stage s's record is rewritten during tile k + 1)
+    const int ntot = nA + nB;
+    const int sx = st_w0 + s * stw, srp = sx + xw, scl = srp + rw, sds = scl + cw;
+    if (mp->flags & kTileManual) {  // flagged tile: fetch the slices with ordinary loads
+      for (int gb = 0; gb < (nB > 0 ? 2 : 1); ++gb) {
+        const int n0 = gb ? mp->n0B : mp->n0A, n = gb ? nB : nA, e0 = gb ? mp->e0B : mp->e0A, e = gb ? mp->eB : eA;
+        const int o0 = mp->off[4 * gb + 0], o1 = mp->off[4 * gb + 1], o2 = mp->off[4 * gb + 2], o3 = mp->off[4 * gb + 3];
+        for (int idx = gt; idx < n * F; idx += kSlotThreads) smf[sx + o0 + idx] = __ldg(a.f.x + (int64_t)n0 * F + idx);
+        for (int idx = gt; idx <= n; idx += kSlotThreads) smi[srp + o1 + idx] = __ldg(a.f.rowptr + n0 + idx);
+        for (int idx = gt; idx < e; idx += kSlotThreads) smi[scl + o2 + idx] = __ldg(a.f.col + e0 + idx);
+        for (int idx = gt; idx < n; idx += kSlotThreads) smf[sds + o3 + idx] = __ldg(a.f.dis + n0 + idx);
       }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int r = r0 + u * (kTcSlotThreads / 32);
-        if (r < n && lane < (P < 32 ? P : 32)) Hbuf[r * P + lane] = v[u];
-      }
+      ptx::named_bar_sync(bar_full, kSlotThreads);
     }
-    // ---- per CSR slot: graph-local neighbour id (in place) and norm_ij; the two threads of a row take
-    //      alternate slots --------------------------------------------------------------------------------
-    int beg = 0, end = -1;
+    // ---- this thread's row: which graph of the tile, where its slices start -------------------------
+    const bool row_ok = i < ntot;
+    const bool warp_ok = i_warp_min < ntot;  // this warp owns at least one row of the tile
+    const bool inB = row_ok && i >= nA;      // (rows past the tile use graph A's addresses and weight 0)
+    const int n0 = inB ? mp->n0B : mp->n0A, ng = inB ? nB : nA, e0 = inB ? mp->e0B : mp->e0A;
+    const int rowbase = inB ? nA : 0;
+    const int li = i - rowbase;               // row inside its graph
+    const int jb = n0 - rowbase;              // tile row of batch node j = j - jb
+    const int xt_o = sx + (inB ? mp->off[4] : mp->off[0]) - rowbase * F;   // x[tile row r][c] at smf[xt_o + r F + c]
+    const int rp_o = srp + (inB ? mp->off[5] : mp->off[1]);               // rowptr[n0 + r] at smi[rp_o + r]
+    const int cl_o = scl + (inB ? mp->off[6] : mp->off[2]) - e0;          // col[pos] at smi[cl_o + pos]
+    const int ds_o = sds + (inB ? mp->off[7] : mp->off[3]) - n0;          // dis[j] at smf[ds_o + j]
+    const int nbo = nb_w + 2 * ((inB ? eA : 0) - e0);                     // record of CSR slot pos at smi[nbo + 2 pos]
+    int beg = 0, deg = 0;
     float di = 0.f;
-    if (row_ok) {
-      beg = rp[i] - e0; end = rp[i + 1] - e0; di = ds[i];
-      for (int kk = beg + half; kk < end; kk += 2) {
-        int j = cl[kk] - n0;
-        const bool ok = (unsigned)j < (unsigned)n;
-        if (!ok) { if (a.f.status) atomicOr(a.f.status, kStatusCrossEdgeTc); j = i; }
-        cl[kk] = j;
-        wn[kk] = ok ? ds[j] * di : 0.f;
+    if (row_ok) { beg = smi[rp_o + li]; deg = smi[rp_o + li + 1] - beg; di = smf[ds_o + n0 + li]; }
+    const float wself = (di * a.f.fill) * di;
+    const int iself = row_ok ? i : 0;
+
+    // ---- per CSR slot: (tile row of the neighbour, norm_ij); the threads of a row take alternate slots ----
+    for (int t = cg; t < deg; t += TPR) {
+      const int j = smi[cl_o + beg + t];
+      const bool ok = (unsigned)(j - n0) < (unsigned)ng;
+      if (!ok && a.f.status) atomicOr(a.f.status, kStatusCrossEdgeTc);
+      const float w = ok ? smf[ds_o + (ok ? j : n0)] * di : 0.f;
+      *reinterpret_cast<int2*>(smi + nbo + 2 * (beg + t)) = make_int2(ok ? j - jb : i, __float_as_int(w));
+    }
+    TC_TICK(2);
+    ptx::named_bar_sync(bar_full, kSlotThreads);
+    TC_TICK(3);
+    // every lane of the warp walks the same number of neighbour steps (the warp's largest degree); a lane
+    // past its own degree adds 0 x its own row
+    const int maxdeg = __reduce_max_sync(0xffffffffu, deg);
+    const int2* nbp = reinterpret_cast<const int2*>(smi + nbo) + beg;
+    auto nb_at = [&](int t) { return t < deg ? nbp[t] : make_int2(iself, 0); };
+
+    // ---- layer 0: a_r = sum_j norm_rj x_j ; this thread's XW of the (up to) 32 columns ---------------
+    if (warp_ok) {
+      float acc[XW];
+#pragma unroll
+      for (int c = 0; c < XW; ++c) acc[c] = 0.f;
+      const int xc = xt_o + XW * cg;
+      const int ncol = F - XW * cg;    // columns of this thread that exist (<= 0: none)
+      if (F_ > 0) {
+        // compile-time column count of every column group: min(XW, F - XW g), dispatched on the (warp-uniform) group
+        constexpr int N0 = F_ < XW ? F_ : XW;
+        constexpr int N1 = F_ - XW < 0 ? 0 : (F_ - XW < XW ? F_ - XW : XW);
+        constexpr int N2 = F_ - 2 * XW < 0 ? 0 : (F_ - 2 * XW < XW ? F_ - 2 * XW : XW);
+        constexpr int N3 = F_ - 3 * XW < 0 ? 0 : (F_ - 3 * XW < XW ? F_ - 3 * XW : XW);
+        if (cg == 0) gather_x<N0, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
+        else if (cg == 1) gather_x<N1, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
+        else if (cg == 2) gather_x<N2, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
+        else gather_x<N3, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
+      } else if (ncol > 0) {
+        gather_x<-1, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself, ncol < XW ? ncol : XW);
+      }
+      if (TPR == 2) {
+        float v[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) v[c] = acc[c % XW];
+        tc::store_split16(v, a_hi, a_lo, trow, cg * 16);
+      } else {
+        float v[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) v[c] = acc[c % XW];
+        tc::store_split8(v, a_hi, a_lo, trow, cg * 8);
       }
     }
-    const float wself = (di * a.f.fill) * di;
-    TC_TICK(2);
-    ptx::named_bar_sync(bar_id, kTcSlotThreads);
-    TC_TICK(3);
-
-    // ---- layer 0: a_r = sum_j norm_rj x_j ; this thread's 16 of the (up to) 32 columns ---------------
-    if (warp_ok) {
-      float acc[16];
-      if (half == 0) gather_rows<(NQ < 4 ? NQ : 4), P, 16>(acc, Hbuf, cl, wn, beg, end, i, wself, 0);
-      else           gather_rows<(NQ > 4 ? NQ - 4 : 0), P, 16>(acc, Hbuf, cl, wn, beg, end, i, wself, 4);
-      tc::store_split16(acc, a_hi, a_lo, trow, half * 16);
-    }
+    TC_TICK(4);
 
     for (int l = 0; l < L; ++l) {
       const bool last = l == L - 1;
-      TC_TICK(4);
       ptx::tmem_wait_st();
-      TC_TICK(5);
       ptx::tc_fence_before_sync();
-      ptx::named_bar_sync(bar_id, kTcSlotThreads);  // A operand complete; previous readers of Hbuf / D are done
       if (ctl_warp) {
-       if (lane == 0) {
-        ptx::tc_fence_after_sync();
-        if (l == 0)
-          tc::issue_split_mma<4>(d_t, a_hi, a_lo, ptx::smem_u32(w0_hi), ptx::smem_u32(w0_lo));  // K = 32, zero padded
-        else
-          tc::issue_split_mma<8>(d_t, a_hi, a_lo, ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64),
-                                 ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64));
-        ptx::mma_commit(&bar_mma[slot]);
-        if (l == 0) issue_next();
-       }
-       __syncwarp();
-       ptx::mbar_wait(&bar_mma[slot], mma_phase);  // one warp polls; the others sleep in the barrier below
+        ptx::named_bar_sync(bar_aop, kSlotThreads);  // A operand complete; every reader of the activation buffer is done
+        if (lane == 0) {
+          ptx::tc_fence_after_sync();
+          if (l == 0)
+            tc::issue_split_mma<4>(d_t, a_hi, a_lo, ptx::smem_u32(w0_hi), ptx::smem_u32(w0_lo));  // K = 32, zero padded
+          else
+            tc::issue_split_mma<8>(d_t, a_hi, a_lo, ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64),
+                                   ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64));
+          ptx::mma_commit(&bar_mma[slot]);
+        }
+        __syncwarp();
+      } else {
+        ptx::named_bar_arrive(bar_aop, kSlotThreads);
       }
+      if (l == 0 && p_gA >= 0) pool_tile(p_gA, p_gB, p_nA, p_nB);   // the previous tile, while the MMAs run
+      if (ctl_warp) ptx::mbar_wait(&bar_mma[slot], mma_phase);      // one warp polls; the others sleep in the barrier below
       mma_phase ^= 1u;
-      TC_TICK(6);
-      ptx::named_bar_sync(bar_id, kTcSlotThreads);
+      TC_TICK(5);
+      ptx::named_bar_sync(bar_full, kSlotThreads);
       ptx::tc_fence_after_sync();
-      TC_TICK(7);
+      TC_TICK(6);
 
       // ---- epilogue: h_r = lrelu(D_r + b_l) -> activation buffer (+ optional save) ------------------
       if (warp_ok) {
-        float* save = a.f.save_act[l];
-        uint32_t r0[16], r1[16];
-        ptx::tmem_ld16(d_t + trow + half * 32, r0);
-        ptx::tmem_ld16(d_t + trow + half * 32 + 16, r1);
-        ptx::tmem_wait_ld();
+        float* save = (a.f.save_act[l] != nullptr && row_ok) ? a.f.save_act[l] + ((int64_t)n0 + li) * 64 : nullptr;
 #pragma unroll
-        for (int q4 = 0; q4 < 8; ++q4) {
-          const int c0 = half * 32 + 4 * q4;
-          const float4 b4 = *reinterpret_cast<const float4*>(s_bias + l * 64 + c0);
-          const uint32_t* rr = q4 < 4 ? &r0[4 * q4] : &r1[4 * (q4 - 4)];
-          float4 v;
-          v.x = __uint_as_float(rr[0]) + b4.x; v.x = fmaxf(v.x, v.x * slope);  // LeakyReLU, 0 <= slope <= 1
-          v.y = __uint_as_float(rr[1]) + b4.y; v.y = fmaxf(v.y, v.y * slope);
-          v.z = __uint_as_float(rr[2]) + b4.z; v.z = fmaxf(v.z, v.z * slope);
-          v.w = __uint_as_float(rr[3]) + b4.w; v.w = fmaxf(v.w, v.w * slope);
-          *reinterpret_cast<float4*>(Hbuf + i * HP + c0) = v;
-          if (save && row_ok) *reinterpret_cast<float4*>(save + ((int64_t)n0 + i) * 64 + c0) = v;
+        for (int part = 0; part < CW / 16; ++part) {
+          uint32_t q0[16];
+          ptx::tmem_ld16(d_t + trow + cg * CW + part * 16, q0);
+          ptx::tmem_wait_ld();
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            const int c0 = cg * CW + part * 16 + 4 * q4;
+            const float4 b4 = *reinterpret_cast<const float4*>(s_bias + l * 64 + c0);
+            float4 v;
+            v.x = __uint_as_float(q0[4 * q4 + 0]) + b4.x; v.x = fmaxf(v.x, v.x * slope);  // LeakyReLU, 0 <= slope <= 1
+            v.y = __uint_as_float(q0[4 * q4 + 1]) + b4.y; v.y = fmaxf(v.y, v.y * slope);
+            v.z = __uint_as_float(q0[4 * q4 + 2]) + b4.z; v.z = fmaxf(v.z, v.z * slope);
+            v.w = __uint_as_float(q0[4 * q4 + 3]) + b4.w; v.w = fmaxf(v.w, v.w * slope);
+            *reinterpret_cast<float4*>(smf + hb_w + i * HP + c0) = v;
+            if (save) *reinterpret_cast<float4*>(save + c0) = v;
+          }
         }
       }
-      TC_TICK(8);
+      TC_TICK(7);
       ptx::tc_fence_before_sync();
-      ptx::named_bar_sync(bar_id, kTcSlotThreads);  // h complete in shared memory; D may be overwritten
-      TC_TICK(9);
+      ptx::named_bar_sync(bar_full, kSlotThreads);  // h complete in shared memory; D may be overwritten
+      TC_TICK(8);
 
       if (!last && warp_ok) {
-        // ---- next layer's A operand: a_r = sum_j norm_rj h_j ; this thread's 32 of the 64 columns ----
-        float acc[32];
-        gather_rows<8, HP, 32>(acc, Hbuf, cl, wn, beg, end, i, wself, half * 8);
+        // ---- next layer's A operand: a_r = sum_j norm_rj h_j ; this thread's CW of the 64 columns -----
+        float acc[CW];
 #pragma unroll
-        for (int cc = 0; cc < 32; cc += 16) {
+        for (int c = 0; c < CW; ++c) acc[c] = 0.f;
+        const float* hcol = smf + hb_w + CW * cg;
+        auto row_fma = [&](int r, float w) {
+          const float4* row = reinterpret_cast<const float4*>(hcol + r * HP);
+#pragma unroll
+          for (int q = 0; q < CW / 4; ++q) {
+            const float4 v = row[q];
+            acc[4 * q + 0] = fmaf(w, v.x, acc[4 * q + 0]);
+            acc[4 * q + 1] = fmaf(w, v.y, acc[4 * q + 1]);
+            acc[4 * q + 2] = fmaf(w, v.z, acc[4 * q + 2]);
+            acc[4 * q + 3] = fmaf(w, v.w, acc[4 * q + 3]);
+          }
+        };
+        int2 nb = nb_at(0);
+        for (int t = 0; t < maxdeg; ++t) {
+          const int2 cur = nb;
+          nb = nb_at(t + 1);
+          if (t < deg)
+            row_fma(cur.x, __int_as_float(cur.y));
+        }
+        row_fma(iself, wself);
+#pragma unroll
+        for (int cc = 0; cc < CW; cc += 16) {
           float v[16];
 #pragma unroll
           for (int q = 0; q < 16; ++q) v[q] = acc[cc + q];
-          tc::store_split16(v, a_hi, a_lo, trow, half * 32 + cc);
+          tc::store_split16(v, a_hi, a_lo, trow, cg * CW + cc);
         }
       }
+      TC_TICK(9);
     }
 
-    // ---- pooling over the graph's rows (column owners; four interleaved quarters of the rows) ------
-    {
-      const int c = gt & 63, quarter = gt >> 6;
-      float mx = -INFINITY, sm = 0.f;
-      const float* hp = Hbuf + c;
-      int r = quarter;
-      for (; r + 12 < n; r += 16) {
-        const float v0 = hp[r * HP], v1 = hp[(r + 4) * HP], v2 = hp[(r + 8) * HP], v3 = hp[(r + 12) * HP];
-        mx = fmaxf(fmaxf(mx, v0), fmaxf(v1, fmaxf(v2, v3)));
-        sm += v0; sm += v1; sm += v2; sm += v3;
-      }
-      for (; r < n; r += 4) {
-        const float v0 = hp[r * HP];
-        mx = fmaxf(mx, v0);
-        sm += v0;
-      }
-      TC_TICK(10);
-      s_pool[quarter * 128 + c] = mx;
-      s_pool[quarter * 128 + 64 + c] = sm;
-      ptx::named_bar_sync(bar_id, kTcSlotThreads);
-      if (gt < 64) {
-        mx = fmaxf(fmaxf(s_pool[c], s_pool[128 + c]), fmaxf(s_pool[256 + c], s_pool[384 + c]));
-        sm = ((s_pool[64 + c] + s_pool[192 + c]) + s_pool[320 + c]) + s_pool[448 + c];
-        a.f.emb[gid * 128 + c] = mx;
-        a.f.emb[gid * 128 + 64 + c] = sm / (float)n;
-      }
-      TC_TICK(11);
-    }
+    p_gA = gA; p_gB = gB; p_nA = nA; p_nB = nB;
+    TC_TICK(10);
   }
+  if (p_gA >= 0) pool_tile(p_gA, p_gB, p_nA, p_nB);
 
   ptx::tc_fence_before_sync();
   __syncthreads();
@@ -514,8 +710,31 @@ size_t tc_fwd_smem_bytes(int F, int L) { return tc_layout(F, L).total; }
 
 namespace hcg {
 
+struct TcPlan {     // launch geometry of the work list for a batch of B graphs
+  int grid, nslots, W, nwin, cap;
+};
+
+static TcPlan tc_plan(int64_t B) {
+  TcPlan p{};
+  int64_t grid = cdiv(B, kTcSlots);
+  if (grid > kNumSMs) grid = kNumSMs;
+  if (grid < 1) grid = 1;
+  p.grid = (int)grid;
+  p.nslots = p.grid * kTcSlots;
+  // graphs per slot -> windows of at most kTcWinMax graphs, as equal as possible
+  const int64_t gps = cdiv(B, p.nslots);
+  const int64_t wins = cdiv(gps, kTcWinMax);
+  int64_t W = cdiv(gps, wins);
+  if (W < 1) W = 1;
+  p.W = (int)W;
+  p.nwin = (int)cdiv(B, W);
+  p.cap = (int)(cdiv(p.nwin, p.nslots) * W);
+  return p;
+}
+
 struct TcWs {
-  int4* gdesc;
+  TcTile* tiles;
+  int* counts;
   int* overflow_count;
   int* overflow_list;
   size_t bytes;
@@ -524,7 +743,9 @@ struct TcWs {
 static TcWs carve_tc(void* ws, int64_t B) {
   Carver c(ws, (size_t)-1);
   TcWs w{};
-  w.gdesc = c.take<int4>((size_t)B + 1);
+  const TcPlan p = tc_plan(B);
+  w.tiles = c.take<TcTile>((size_t)p.nslots * p.cap + 1);
+  w.counts = c.take<int>((size_t)p.nslots + 1);
   w.overflow_count = c.take<int>(64);
   w.overflow_list = c.take<int>((size_t)B + 1);
   w.bytes = c.off;
@@ -533,31 +754,65 @@ static TcWs carve_tc(void* ws, int64_t B) {
 
 size_t tc_fwd_workspace_bytes(int64_t B) { return carve_tc(nullptr, B).bytes; }
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-device setting
+template <typename K>
+static int ensure_smem(K kernel, size_t smem, size_t (&configured)[16]) {
+  int dev = 0;
+  HCG_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 16 || smem > configured[dev]) {
+    HCG_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (dev >= 0 && dev < 16) configured[dev] = smem;
+  }
+  return HCG_OK;
+}
+
+// launch-time choice of the threads-per-row variant (HCG_TC_TPR=2|4 in the environment overrides; tests / tuning)
+static int tc_tpr() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("HCG_TC_TPR");
+    v = (e && e[0] == '2') ? 2 : (e && e[0] == '4') ? 4 : kTcDefaultTpr;
+  }
+  return v;
+}
+
+template <int F_, int TPR>
+static int launch_tc_variant(const TcArgs& a, int grid, size_t smem, cudaStream_t st) {
+  static size_t configured[16];
+  int rc = ensure_smem(k_tc_fwd<F_, TPR>, smem, configured);
+  if (rc) return rc;
+  k_tc_fwd<F_, TPR><<<(unsigned)grid, kTcSlots * 128 * TPR, smem, st>>>(a);
+  return HCG_OK;
+}
+
 int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStream_t st) {
   if (f.B <= 0) return HCG_OK;
   TcWs w = carve_tc(ws, f.B);
+  const TcPlan p = tc_plan(f.B);
   const size_t smem = tc_fwd_smem_bytes(f.F, f.L);
-  static thread_local size_t configured[2] = {0, 0};
-  const int v = f.F <= 28 ? 0 : 1;
-  if (smem > configured[v]) {
-    HCG_CUDA_OK(cudaFuncSetAttribute(v == 0 ? k_tc_fwd<7> : k_tc_fwd<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured[v] = smem;
-  }
   HCG_CUDA_OK(cudaMemsetAsync(w.overflow_count, 0, sizeof(int), st));
-  k_graph_desc<<<(unsigned)cdiv(f.B, 256), 256, 0, st>>>(f.graph_ptr, f.rowptr, f.col, f.dis, f.x, f.F, N, E, f.B, w.gdesc,
-                                                         w.overflow_count, w.overflow_list);
-  HCG_LAUNCH_OK(st, "k_graph_desc");
+  k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(f.graph_ptr, f.rowptr, f.col, f.dis, f.x, f.F, N, E, f.B, p.W,
+                                                                          p.nslots, p.nwin, p.cap, w.tiles, w.counts,
+                                                                          w.overflow_count, w.overflow_list);
+  HCG_LAUNCH_OK(st, "k_tile_desc");
 
   TcArgs a{};
   a.f = f;
-  a.gdesc = w.gdesc;
-  int64_t grid = cdiv(f.B, kTcSlots);
-  if (grid > kNumSMs) grid = kNumSMs;
-  if (v == 0) k_tc_fwd<7><<<(unsigned)grid, kTcThreads, smem, st>>>(a);
-  else k_tc_fwd<8><<<(unsigned)grid, kTcThreads, smem, st>>>(a);
+  a.tiles = w.tiles;
+  a.counts = w.counts;
+  a.cap = p.cap;
+  a.N = N; a.E = E;
+  int rc;
+  if (tc_tpr() == 2)
+    rc = f.F == 25 ? launch_tc_variant<25, 2>(a, p.grid, smem, st) : f.F == 32 ? launch_tc_variant<32, 2>(a, p.grid, smem, st)
+                                                                               : launch_tc_variant<0, 2>(a, p.grid, smem, st);
+  else
+    rc = f.F == 25 ? launch_tc_variant<25, 4>(a, p.grid, smem, st) : f.F == 32 ? launch_tc_variant<32, 4>(a, p.grid, smem, st)
+                                                                               : launch_tc_variant<0, 4>(a, p.grid, smem, st);
+  if (rc) return rc;
   HCG_LAUNCH_OK(st, "k_tc_fwd");
 
-  // graphs above the slot capacity: the FMA graph-resident kernel walks the overflow list
+  // graphs above the tile capacity: the FMA graph-resident kernel walks the overflow list
   FusedFwdArgs o = f;
   o.list = w.overflow_list;
   o.list_count = w.overflow_count;

@@ -98,5 +98,17 @@ __device__ __forceinline__ void store_split16(const float (&v)[16], uint32_t a_h
   ptx::tmem_st16(a_lo + trow + col, l);
 }
 
+// Eight consecutive values: columns [col, col+8).
+__device__ __forceinline__ void store_split8(const float (&v)[8], uint32_t a_hi, uint32_t a_lo, uint32_t trow, int col) {
+  uint32_t h[8], l[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    h[q] = tf32_hi(v[q]);
+    l[q] = __float_as_uint(v[q] - __uint_as_float(h[q]));
+  }
+  ptx::tmem_st8(a_hi + trow + col, h);
+  ptx::tmem_st8(a_lo + trow + col, l);
+}
+
 }  // namespace tc
 }  // namespace hcg

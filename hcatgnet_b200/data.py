@@ -15,6 +15,10 @@ from typing import Iterable, Mapping, Sequence
 import torch
 
 
+# per-graph capacity of hcg_collate's graph-local path (csrc/hcg_collate.cu: kGrpNodes / kGrpEdges)
+GROUPED_MAX_NODES, GROUPED_MAX_EDGES = 1024, 2048
+
+
 def _field(g, name, default=None):
     if isinstance(g, Mapping):
         return g.get(name, default)
@@ -36,6 +40,10 @@ class Batch:
         self.max_graph_nodes = 0
         if ptr is not None and not ptr.is_cuda and ptr.numel() >= 2:
             self.max_graph_nodes = int((ptr[1:] - ptr[:-1]).max())
+        # optional: first edge of each graph (PyG keeps the same numbers in Batch._slice_dict['edge_index']) and
+        # the edge count of the largest graph, as a host integer; None / 0 = unknown
+        self.edge_ptr = None
+        self.max_graph_edges = 0
 
     @classmethod
     def from_data_list(cls, graphs: Sequence) -> "Batch":
@@ -54,7 +62,19 @@ class Batch:
             [torch.as_tensor(v, dtype=torch.float32).reshape(-1) for v in ys], 0)
         ids = [_field(g, "idx") for g in graphs]
         idx = None if any(v is None for v in ids) else torch.tensor([int(v) for v in ids], dtype=torch.int64)
-        return cls(x, edge_index, batch, ptr, y, idx, len(graphs), edges_grouped=True)
+        # The graph-local collate path (HCG_COLLATE_GROUPED) is only vouched for when the host has checked its
+        # preconditions: the edges are listed graph by graph by construction here; self-loop edges and graphs
+        # above the path's per-graph capacity are looked for explicitly (otherwise hcg_collate is left to
+        # try the path under `validate` and fall back by itself).
+        grouped = bool(edge_index.numel() == 0 or not bool((edge_index[0] == edge_index[1]).any()))
+        grouped = grouped and (not sizes or max(sizes) <= GROUPED_MAX_NODES) and \
+            (ecount.numel() == 0 or int(ecount.max()) <= GROUPED_MAX_EDGES)
+        out = cls(x, edge_index, batch, ptr, y, idx, len(graphs), edges_grouped=True if grouped else None)
+        out.edge_ptr = torch.zeros(len(graphs) + 1, dtype=torch.int64)
+        if ecount.numel():
+            out.edge_ptr[1:] = torch.cumsum(ecount, 0)
+        out.max_graph_edges = int(ecount.max()) if ecount.numel() else 0
+        return out
 
     @property
     def num_nodes(self) -> int:
@@ -64,7 +84,7 @@ class Batch:
         """In place, returning self (like PyG's ``Data.to``), so a collate plan cached on the
         object by the model survives ``batch = batch.to(device)`` when nothing moves."""
         moved = False
-        for name in ("x", "edge_index", "batch", "ptr", "y", "idx"):
+        for name in ("x", "edge_index", "batch", "ptr", "y", "idx", "edge_ptr"):
             t = getattr(self, name)
             if t is not None:
                 t2 = t.to(device, non_blocking=non_blocking)
@@ -75,7 +95,7 @@ class Batch:
         return self
 
     def pin_memory(self) -> "Batch":
-        for name in ("x", "edge_index", "batch", "ptr", "y", "idx"):
+        for name in ("x", "edge_index", "batch", "ptr", "y", "idx", "edge_ptr"):
             t = getattr(self, name)
             if t is not None and not t.is_cuda:
                 setattr(self, name, t.pin_memory())

@@ -183,10 +183,14 @@ def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edg
     """
     key = None
     if holder is not None and edge_weight is None:
-        key = (edge_index.data_ptr(), edge_index._version, tuple(edge_index.shape),
-               None if batch is None else batch.data_ptr(), int(num_nodes), int(num_graphs), str(device))
+        # Identity of the caller's tensors, not their addresses: the cache entry keeps references to them, so
+        # the allocator cannot hand the same storage to another graph's edge_index while the entry is alive
+        # (two same-shape molecules explained back to back would otherwise share one plan).
+        key = (edge_index._version, None if batch is None else batch._version, int(num_nodes), int(num_graphs),
+               str(device))
         hit = getattr(holder, "_hcg_plan", None)
-        if hit is not None and hit[0] == key and (hit[1].has_transpose or not transpose):
+        if hit is not None and hit[0] == key and hit[2] is edge_index and hit[3] is batch and \
+                (hit[1].has_transpose or not transpose):
             return hit[1]
     with torch.cuda.device(device):
         plan = collate(to_device(edge_index, device, torch.int64), to_device(batch, device, torch.int64),
@@ -195,7 +199,7 @@ def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edg
                        max_graph_nodes=max_graph_nodes, grouped=grouped)
     if key is not None:
         try:
-            object.__setattr__(holder, "_hcg_plan", (key, plan))
+            object.__setattr__(holder, "_hcg_plan", (key, plan, edge_index, batch))
         except (AttributeError, TypeError):
             pass
     return plan

@@ -17,9 +17,10 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 OUT = os.path.join(ROOT, "build", "libhcg_timing.so")
-PHASES = ["loop top + prefetch issue", "wait input stage", "re-pitch x", "barrier", "gather + split + tcgen05.st",
-          "tcgen05.wait::st", "barrier + MMA issue", "wait MMA", "epilogue (tcgen05.ld, bias, lrelu, sts)",
-          "barrier", "pooling partials", "pooling final + emb store"]
+PHASES = ["loop top", "wait input stage", "prefetch issue + row setup + (row, norm) records", "slot barrier",
+          "layer-0 gather + split + tcgen05.st", "tcgen05.wait::st + A-operand barrier (+ MMA issue)", "wait MMA",
+          "epilogue (tcgen05.ld, bias, lrelu, sts)", "slot barrier", "layer-1 gather + split + tcgen05.st",
+          "pooling + emb store"]
 
 if "--build" in sys.argv:
     from hcatgnet_b200 import build as b
@@ -51,8 +52,8 @@ with torch.no_grad():
     torch.cuda.synchronize()
 buf = (C.c_ulonglong * 16)()
 lib.hcg_debug_tc_timing(buf, 0)
-graphs = -(-16384 // (148 * 2))
-tot = sum(buf[:12])
-print(f"thread 0 / CTA 0: {graphs} graphs, {tot / graphs:.0f} cycles per graph")
+graphs = 16384 / (148 * 2)
+tot = sum(buf[:len(PHASES)])
+print(f"thread 0 / CTA 0: ~{graphs:.1f} graphs, {tot / graphs:.0f} cycles per graph")
 for i, name in enumerate(PHASES):
     print(f"  {i:2d} {name:42s} {buf[i] / graphs:8.0f} cyc/graph  {100 * buf[i] / tot:5.1f}%")
