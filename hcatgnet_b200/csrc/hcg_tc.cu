@@ -78,40 +78,42 @@ extern "C" int hcg_selftest_tc_gemm(const float* A, const float* W, int K, float
 // =================================================================================================
 // Graph-resident forward on the tensor cores.
 //
-// A CTA holds two independent "slots" of 256 threads; a slot walks its share of the batch one TILE at
-// a time.  A tile is 128 node rows = the M of one tcgen05.mma = the 128 lanes of tensor memory, and
-// holds ONE OR TWO whole reaction graphs (k_tile_desc pairs graphs of a small window of the batch
-// whose node counts fit together: at 40..120 atoms a tile carries 1.3 graphs and ~85 % of its rows are
+// A CTA holds two (or three) independent "slots" of 256 threads; a slot walks its share of the batch one
+// TILE at a time.  A tile is 128 node rows = the M of one tcgen05.mma = the 128 lanes of tensor memory,
+// and holds ONE OR TWO whole reaction graphs (k_tile_desc pairs graphs of a small window of the batch
+// whose node counts fit together: at 40..120 atoms a tile carries 1.37 graphs and ~85 % of its rows are
 // real nodes instead of 62 %).  The adjacency of a tile is block diagonal, so nothing below cares
 // how many graphs it holds except the pooling.  Two threads own a row (half of the columns each):
 //
-//   prefetch   x rows, rowptr / col slice, deg^-1/2 of the graphs of the NEXT tile: up to eight bulk
-//              async copies (cp.async.bulk -> mbarrier) issued by eight lanes of one warp a whole tile
-//              ahead, double-buffered
+//   prefetch   the small CSR slices (rowptr, col, deg^-1/2) of the NEXT tile go out a whole tile ahead
+//              into the other of two stages; its x rows, which have one buffer, as soon as this tile's
+//              layer-0 gather is over: up to eight bulk async copies (cp.async.bulk -> one mbarrier),
+//              issued by eight lanes of one warp; the work-list record itself arrives by cp.async
+//   records    per CSR slot (tile row of the neighbour, norm_rj = dis_r dis_j) -> shared memory, once per tile
 //   layer 0    a_r = sum_j norm_rj x_j gathered straight from the copied x rows (scalar loads: the rows
-//              keep their F-float pitch, no re-pitch pass), norm_rj = dis_r dis_j computed on the fly;
+//              keep their F-float pitch, no re-pitch pass); all lanes of a warp take the same number of
+//              neighbour steps (the warp's largest degree), a lane past its own degree idles;
 //              split into TF32 hi / lo and stored as row r of the A operand in tensor memory
 //   MMA        producers bar.arrive, the control warp bar.sync's, its first lane issues the split-TF32
 //              tcgen05.mma chain against W_l^T (shared memory, 128-byte swizzle) and commits to an
-//              mbarrier that every thread of the slot waits on
+//              mbarrier; the control warp polls it, the other warps sleep in a hardware barrier
 //   epilogue   row r of the fp32 accumulator (tcgen05.ld) + bias, LeakyReLU -> activation buffer
 //   layer l>0  a_r = sum_j norm_rj h_j from the activation buffer (128-bit loads), as above
 //   pooling    column owners scan the last layer's rows of each graph of the tile; the eight row
 //              interleaves of a column sit in one warp and are combined by shuffles:
-//              emb[g] = [max || mean]
+//              emb[g] = [max || mean].  Runs one tile late, inside the next tile's layer-0 MMA window.
 //
-// Blocking synchronisation per tile: the stage mbarrier, per layer the MMA mbarrier and one slot-wide
-// barrier after the epilogue.  The two slots of a CTA run out of phase, so one slot's gathers overlap
-// the other's MMAs.  Nothing of size [N,H] touches HBM unless the caller wants the activations
-// (training forward).  Graphs above the tile capacity (128 nodes / kTcEcap CSR slots) are appended to
-// an overflow list that the FMA graph-resident kernel processes afterwards.
+// The slots of a CTA run out of phase, so one slot's gathers overlap the other's MMAs.  Nothing of size
+// [N,H] touches HBM unless the caller wants the activations (training forward).  Graphs above the tile
+// capacity (128 nodes / kTcEcap CSR slots) are appended to an overflow list that the FMA graph-resident
+// kernel processes afterwards.
 // =================================================================================================
 namespace hcg {
 
-constexpr int kTcDefaultTpr = 2;     // threads per tile row unless HCG_TC_TPR says otherwise
-constexpr int kTcSlots = 2;           // independent tile pipelines per CTA (tensor memory: 256 columns each)
+constexpr int kTcDefaultSlots = 2;    // tile pipelines per CTA (HCG_TC_SLOTS=3 selects the three-slot variant: measured slower,
+                                      // 441 vs 398 us per 16384-graph batch - the kernel is bound by shared-memory throughput, not by latency)
 constexpr int kTcRows = 128;          // node rows per tile
-constexpr int kTcEcap = 640;          // CSR slots per tile
+constexpr int kTcEcap = 512;          // CSR slots per tile (4 per node row: molecules)
 constexpr int kTcHPitch = 68;         // floats per activation row: 8 consecutive rows cover all banks for 128-bit access
 constexpr int kTcWinMax = 8;          // graphs per pairing window (at most)
 constexpr int kStatusCrossEdgeTc = 4;
@@ -252,13 +254,14 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
 }
 
 // shared-memory carve-up, identical on host (size query) and device; weights first, then per slot the
-// activation buffer and two input stages.  Offsets in BYTES from the 1024-aligned base; stage array sizes in
-// 4-byte words (multiples of 4, so every array is 16-byte aligned).
+// activation buffer, the neighbour records, ONE x stage and two stages of the small CSR slices.  Offsets in
+// BYTES from the 1024-aligned base; stage array sizes in 4-byte words (multiples of 4, so every array is
+// 16-byte aligned).
 struct TcSmemLayout {
-  uint32_t w0_hi, w0_lo, wl, bias, hbuf, nbr, stage;
-  uint32_t xw, rw, cw, dw, stage_words, slot_bytes, total;
+  uint32_t w0_hi, w0_lo, wl, bias, hbuf, nbr, xst, cst;
+  uint32_t xw, rw, cw, dw, csr_words, slot_bytes, total;
 };
-__host__ __device__ inline TcSmemLayout tc_layout(int F, int L) {
+__host__ __device__ inline TcSmemLayout tc_layout(int F, int L, int nslots) {
   TcSmemLayout y;
   uint32_t p = 0;
   y.w0_hi = p; p += tc::kN * 32 * 4;
@@ -270,12 +273,13 @@ __host__ __device__ inline TcSmemLayout tc_layout(int F, int L) {
   y.rw = ((uint32_t)kTcRows + 2 + 16 + 3) & ~3u;
   y.cw = ((uint32_t)kTcEcap + 16 + 3) & ~3u;
   y.dw = ((uint32_t)kTcRows + 16 + 3) & ~3u;
-  y.stage_words = y.xw + y.rw + y.cw + y.dw;
+  y.csr_words = y.rw + y.cw + y.dw;
   y.hbuf = p;
-  y.slot_bytes = (uint32_t)kTcRows * kTcHPitch * 4 + (uint32_t)kTcEcap * 8 + 2 * y.stage_words * 4;
-  y.nbr = p + (uint32_t)kTcRows * kTcHPitch * 4;    // slot 0's (tile row, norm) record per CSR slot
-  y.stage = y.nbr + (uint32_t)kTcEcap * 8;          // slot 0's first stage
-  p += (uint32_t)kTcSlots * y.slot_bytes;
+  y.nbr = y.hbuf + (uint32_t)kTcRows * kTcHPitch * 4;   // slot 0's (tile row, norm) record per CSR slot
+  y.xst = y.nbr + (uint32_t)kTcEcap * 8;                // slot 0's x rows
+  y.cst = y.xst + y.xw * 4;                             // slot 0's first CSR stage (rowptr | col | dis)
+  y.slot_bytes = (y.cst - y.hbuf) + 2 * y.csr_words * 4;
+  p += (uint32_t)nslots * y.slot_bytes;
   y.total = p + 1024;  // slack for the 1024-byte alignment of the base
   return y;
 }
@@ -288,8 +292,9 @@ __device__ unsigned long long g_tc_timing[16];
 #endif
 
 // Layer-0 gather of one thread: acc[c] = sum_j w_j x[j][c] over its NC columns (NC < 0: `ncol` at run time), rows
-// walked as (tile row, norm) records; every lane takes `maxdeg` steps (a lane past its own degree adds
-// 0 x its own row), then the self-loop, last, as in the reference.  `xcol`: the thread's first column of tile row 0.
+// walked as (tile row, norm) records; every lane takes `maxdeg` steps (a lane past its own degree idles:
+// fewer shared-memory wavefronts than adding 0 x its own row), then the self-loop, last, as in the reference.
+// `xcol`: the thread's first column of tile row 0.
 template <int NC, int XW>
 __device__ __forceinline__ void gather_x(float (&acc)[XW], const float* xcol, int F, const int2* nbp, int deg, int maxdeg,
                                          int iself, float wself, int ncol = 0) {
@@ -304,51 +309,59 @@ __device__ __forceinline__ void gather_x(float (&acc)[XW], const float* xcol, in
   for (int t = 0; t < maxdeg; ++t) {
     const int2 cur = nb;
     nb = t + 1 < deg ? nbp[t + 1] : make_int2(iself, 0);
-    if (t < deg)   // (a lane past its own degree idles: fewer shared-memory wavefronts than adding 0 x its own row)
-      row_fma(cur.x, __int_as_float(cur.y));
+    if (t < deg) row_fma(cur.x, __int_as_float(cur.y));
   }
   row_fma(iself, wself);
 }
 
 // F_ = compile-time number of input features (25: the RhCAA featuriser, 32: biaryl) or 0 = run-time F <= 32.
-// TPR = threads per tile row (2 or 4): a row's columns are split over TPR threads that sit in TPR different
-// warps of the same lane quadrant; a slot has 128 TPR threads, the CTA 256 TPR.
-template <int F_, int TPR>
-__global__ void __launch_bounds__(kTcSlots * 128 * TPR, 1)
+// NS = tile pipelines ("slots") per CTA, 2 or 3.  Two threads own a tile row (32 of the 64 hidden columns each,
+// in two warps of the same lane quadrant), so a slot has 256 threads and the CTA 256 NS.
+//   NS = 2: 128 registers per thread; tensor memory per slot: accumulator 64 | - | A hi 64 | A lo 64 columns.
+//   NS = 3:  80 registers per thread; tensor memory per slot: accumulator 64 | A hi 32 | A lo 32 columns, so a
+//            64-wide layer runs as two K halves: the threads of column half 0 store their operand half and its
+//            MMAs are issued; the threads of half 1 (their gather ran meanwhile) wait for those MMAs to have
+//            read the operand (tcgen05.commit -> mbarrier), store theirs, and the second chain accumulates on top.
+template <int F_, int NS>
+__global__ void __launch_bounds__(NS * 256, 1)
 k_tc_fwd(const TcArgs a) {
 #ifdef HCG_TC_TIMING
   long long t_prev = clock64();
 #endif
   constexpr int HP = kTcHPitch;
-  constexpr int kSlotThreads = 128 * TPR, kThreads = kTcSlots * kSlotThreads, NW = 4 * TPR;
+  constexpr int TPR = 2;
+  constexpr int kSlotThreads = 128 * TPR, kThreads = NS * kSlotThreads, NW = 4 * TPR;
   constexpr int CW = 64 / TPR;    // hidden columns per thread (gather of layers >= 1, epilogue)
   constexpr int XW = 32 / TPR;    // input columns per thread (layer-0 gather)
+  constexpr bool KSPLIT = NS == 3;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  __shared__ uint64_t bar_stage[kTcSlots][2];
-  __shared__ uint64_t bar_mma[kTcSlots];
+  __shared__ uint64_t bar_stage[NS][2];
+  __shared__ uint64_t bar_mma[NS];
+  __shared__ uint64_t bar_free[NS];        // K-split: the first half's MMAs have read the A operand
   __shared__ uint32_t tmem_base_s;
-  __shared__ TcMeta metas[kTcSlots][2];
-  __shared__ int4 recs[kTcSlots][2][3];   // work-list records in flight (cp.async), two deep
+  __shared__ TcMeta metas[NS][2];
+  __shared__ int4 recs[NS][2][3];          // work-list records in flight (cp.async), two deep
 
   const int tid = threadIdx.x;
   const int slot = tid / kSlotThreads, gt = tid % kSlotThreads;
-  const int cg = gt >> 7;            // which group of columns this thread works on
+  const int cg = gt >> 7;            // which half of the columns this thread works on
   const int wslot = gt >> 5;         // warp inside the slot
   // Tile row owned by this thread.  Its TMEM lane is fixed by the hardware (lane quadrant = warp id % 4 =
-  // the warp scheduler), and tiles fill rows from 0 up, so slot 1 maps its rows in reverse: slot 0 loads
+  // the warp scheduler), and tiles fill rows from 0 up, so slot 1 maps its rows in reverse: slots 0 and 2 load
   // schedulers 0,1 the most, slot 1 schedulers 3,2.
-  const int i = slot == 0 ? (gt & 127) : 127 - (gt & 127);
-  const int i_warp_min = slot == 0 ? (gt & 96) : 96 - (gt & 96);  // smallest row owned by this warp
-  // the warp of each slot whose quadrant is filled last issues the MMAs; its sibling in the last column
-  // group feeds the slot (bulk copies of the next tile)
-  const bool ctl_warp = wslot == (slot == 0 ? 3 : 0);
-  const bool pf_warp = wslot == (slot == 0 ? NW - 1 : NW - 4);
+  const bool rev = slot == 1;
+  const int i = rev ? 127 - (gt & 127) : (gt & 127);
+  const int i_warp_min = rev ? 96 - (gt & 96) : (gt & 96);  // smallest row owned by this warp
+  // the warp of each slot whose quadrant is filled last issues the MMAs; its sibling in the other column
+  // half feeds the slot (bulk copies of the next tile)
+  const bool ctl_warp = wslot == (rev ? 0 : 3);
+  const bool pf_warp = wslot == (rev ? NW - 4 : NW - 1);
   const int lane = tid & 31;
   const int F = F_ > 0 ? F_ : a.f.F;
   const int L = a.f.L;
 
   // ---- carve shared memory (one base pointer, word offsets: keeps every access an LDS / STS) -------
-  const TcSmemLayout lay = tc_layout(F, L);
+  const TcSmemLayout lay = tc_layout(F, L, NS);
   unsigned char* base = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
   float* smf = reinterpret_cast<float*>(base);
   int32_t* smi = reinterpret_cast<int32_t*>(base);
@@ -356,18 +369,20 @@ k_tc_fwd(const TcArgs a) {
   float* w0_lo = reinterpret_cast<float*>(base + lay.w0_lo);
   float* wl_base = reinterpret_cast<float*>(base + lay.wl);
   float* s_bias = reinterpret_cast<float*>(base + lay.bias);
-  const int hb_w = (int)((lay.hbuf + (uint32_t)slot * lay.slot_bytes) >> 2);        // activation buffer, word offset
-  const int nb_w = (int)((lay.nbr + (uint32_t)slot * lay.slot_bytes) >> 2);         // neighbour records, word offset
-  const int st_w0 = (int)((lay.stage + (uint32_t)slot * lay.slot_bytes) >> 2);      // stage 0, word offset
-  const int xw = (int)lay.xw, rw = (int)lay.rw, cw = (int)lay.cw, stw = (int)lay.stage_words;
+  const int hb_w = (int)((lay.hbuf + (uint32_t)slot * lay.slot_bytes) >> 2);   // activation buffer, word offset
+  const int nb_w = (int)((lay.nbr + (uint32_t)slot * lay.slot_bytes) >> 2);    // neighbour records
+  const int sx = (int)((lay.xst + (uint32_t)slot * lay.slot_bytes) >> 2);      // x rows (one stage)
+  const int cs_w0 = (int)((lay.cst + (uint32_t)slot * lay.slot_bytes) >> 2);   // CSR stage 0
+  const int rw = (int)lay.rw, cw = (int)lay.cw, csw = (int)lay.csr_words;
 
   // ---- one-time setup ----------------------------------------------------------------------------
   if (tid < 32) ptx::tmem_alloc(&tmem_base_s, 512);
   if (tid == 0) {
-    for (int s = 0; s < kTcSlots; ++s) {
+    for (int s = 0; s < NS; ++s) {
       ptx::mbar_init(&bar_stage[s][0], 8);   // the eight feeding lanes: arrive (+ expect_tx) once per tile each
       ptx::mbar_init(&bar_stage[s][1], 8);
       ptx::mbar_init(&bar_mma[s], 1);
+      ptx::mbar_init(&bar_free[s], 1);
     }
     ptx::fence_mbar_init();
   }
@@ -381,14 +396,15 @@ k_tc_fwd(const TcArgs a) {
   __syncthreads();
   ptx::tc_fence_after_sync();
 
-  const uint32_t tbase = tmem_base_s + (uint32_t)slot * 256;  // accumulator | (free) | A hi | A lo, 64 columns each
-  const uint32_t d_t = tbase, a_hi = tbase + 128, a_lo = tbase + 192;
-  const uint32_t trow = (uint32_t)((wslot & 3) * 32) << 16;  // warps w, w + 4, ... share a lane quadrant
-  const int bar_full = 1 + slot;   // all threads of the slot
-  const int bar_aop = 3 + slot;    // A operand complete: the other warps arrive, the control warp waits
+  const uint32_t tbase = tmem_base_s + (uint32_t)slot * (KSPLIT ? 128 : 256);
+  const uint32_t d_t = tbase, a_hi = tbase + (KSPLIT ? 64 : 128), a_lo = tbase + (KSPLIT ? 96 : 192);
+  const uint32_t trow = (uint32_t)((wslot & 3) * 32) << 16;  // warps w and w + 4 share a lane quadrant
+  const int bar_full = 1 + slot;        // all threads of the slot
+  const int bar_aop = 1 + NS + slot;    // A operand complete: the other warps arrive, the control warp waits
+  const int bar_a1 = 1 + 2 * NS + slot; // K-split: second operand half complete (the warps of half 1 arrive)
   const float slope = a.f.slope;
 
-  const int slot_id = blockIdx.x * kTcSlots + slot;
+  const int slot_id = blockIdx.x * NS + slot;
   const int ntiles = a.counts[slot_id];
   const TcTile* my_tiles = a.tiles + (size_t)slot_id * a.cap;
 
@@ -397,16 +413,21 @@ k_tc_fwd(const TcArgs a) {
   auto fetch_rec = [&](int t) {
     if (t < ntiles && lane < 3) ptx::cp_async16(&recs[slot][t & 1][lane], reinterpret_cast<const int4*>(my_tiles + t) + lane);
   };
-  // issue the copies of tile t into stage t & 1 (or mark the stage as "no more tiles")
-  auto issue = [&](int t) {
+  // Issue the copies of tile t (or mark "no more tiles").  The small CSR slices are double-buffered and go out
+  // a whole tile ahead (want_x = false: the six lanes with q >= 1); the x rows have ONE buffer, so the two x
+  // lanes go later, once the previous tile's layer-0 gather is over (want_x = true).  All eight lanes arrive
+  // on the mbarrier of stage t & 1, each exactly once per tile.
+  auto issue = [&](int t, bool want_x) {
     const int s = t & 1;
     TcMeta* m = &metas[slot][s];
     uint64_t* bar = &bar_stage[slot][s];
-    ptx::cp_async_wait_all();   // this lane's part of the record ...
-    __syncwarp();               // ... and the other lanes'
-    if (lane >= 8) return;
+    if (!want_x) {
+      ptx::cp_async_wait_all();   // this lane's part of the record ...
+      __syncwarp();               // ... and the other lanes'
+    }
+    if (lane >= 8 || ((lane & 3) == 0) != want_x) return;
     if (t >= ntiles) {
-      if (lane == 0) m->gA = -1;
+      if (lane == 1) m->gA = -1;
       ptx::mbar_arrive(bar);
       return;
     }
@@ -432,9 +453,9 @@ k_tc_fwd(const TcArgs a) {
     copy_window(pA, cA, &loA, &bA, &leadA);
     copy_window(pS, cS, &loS, &bS, &leadS);
     if (manual) { leadA = 0; leadS = 0; bA = (uint32_t)((cA * 4 + 15) & ~15); }   // ordinary loads place the slices themselves
-    const int arr_w = st_w0 + s * stw + (q == 0 ? 0 : q == 1 ? xw : q == 2 ? xw + rw : xw + rw + cw);
+    const int arr_w = q == 0 ? sx : cs_w0 + s * csw + (q == 1 ? 0 : q == 2 ? rw : rw + cw);
     const int dst_w = arr_w + (gb ? (int)(bA >> 2) : 0);
-    if (lane == 0) {
+    if (lane == 1) {
       m->gA = r0.x; m->n0A = r0.y; m->nA = r0.z; m->e0A = r0.w;
       m->gB = r1.x; m->n0B = r1.y; m->nB = r1.x >= 0 ? r1.z : 0; m->e0B = r1.w;
       m->eA = r2.x; m->eB = r2.y; m->flags = r2.z;
@@ -449,9 +470,9 @@ k_tc_fwd(const TcArgs a) {
     }
   };
 
-  // ---- pooling: warp w owns columns 4 w + cc (+ 32 with two threads per row), cc = lane & 3; the eight
-  //      lanes of a column take the rows of a graph eight apart (bank = 4 row + column: conflict-free)
-  //      and are combined by shuffles.  Runs one tile late, inside the next tile's layer-0 MMA window. ----
+  // ---- pooling: warp w owns columns 4 w + cc and 32 + 4 w + cc, cc = lane & 3; the eight lanes of a column
+  //      take the rows of a graph eight apart (bank = 4 row + column: conflict-free) and are combined by
+  //      shuffles.  Runs one tile late, inside the next tile's layer-0 MMA window. ------------------------
   auto pool_tile = [&](int gA, int gB, int nA, int nB) {
     constexpr int CPL = 64 / (4 * NW);   // columns per lane
     const int cc = lane & 3, q = lane >> 2;
@@ -502,10 +523,11 @@ k_tc_fwd(const TcArgs a) {
 
   if (pf_warp) {
     fetch_rec(0);
-    issue(0);
+    issue(0, false);
+    issue(0, true);
     fetch_rec(1);
   }
-  uint32_t mma_phase = 0;
+  uint32_t mma_phase = 0, free_phase = 0;
   for (int k = 0;; ++k) {
     const int s = k & 1;
     TC_TICK(0);
@@ -514,15 +536,15 @@ k_tc_fwd(const TcArgs a) {
     const TcMeta* mp = &metas[slot][s];
     const int gA = mp->gA;
     if (gA < 0) break;  // slot-uniform: no more tiles
-    // next tile -> the other stage: its readers (the precompute pass of tile k - 1) are long done, and its
-    // record slot recs[(k + 2) & 1] was read when tile k was issued
+    // next tile's CSR slices -> the other CSR stage: its readers (the record pass of tile k - 1) are long done,
+    // and the record slot recs[(k + 2) & 1] was last read when tile k's x rows were issued
     if (pf_warp) {
-      issue(k + 1);
+      issue(k + 1, false);
       fetch_rec(k + 2);
     }
     const int nA = mp->nA, nB = mp->nB, gB = mp->gB, eA = mp->eA;   // (stage s's record is rewritten during tile k + 1)
     const int ntot = nA + nB;
-    const int sx = st_w0 + s * stw, srp = sx + xw, scl = srp + rw, sds = scl + cw;
+    const int srp = cs_w0 + s * csw, scl = srp + rw, sds = scl + cw;
     if (mp->flags & kTileManual) {  // flagged tile: fetch the slices with ordinary loads
       for (int gb = 0; gb < (nB > 0 ? 2 : 1); ++gb) {
         const int n0 = gb ? mp->n0B : mp->n0A, n = gb ? nB : nA, e0 = gb ? mp->e0B : mp->e0A, e = gb ? mp->eB : eA;
@@ -543,29 +565,29 @@ k_tc_fwd(const TcArgs a) {
     const int li = i - rowbase;               // row inside its graph
     const int jb = n0 - rowbase;              // tile row of batch node j = j - jb
     const int xt_o = sx + (inB ? mp->off[4] : mp->off[0]) - rowbase * F;   // x[tile row r][c] at smf[xt_o + r F + c]
-    const int rp_o = srp + (inB ? mp->off[5] : mp->off[1]);               // rowptr[n0 + r] at smi[rp_o + r]
-    const int cl_o = scl + (inB ? mp->off[6] : mp->off[2]) - e0;          // col[pos] at smi[cl_o + pos]
-    const int ds_o = sds + (inB ? mp->off[7] : mp->off[3]) - n0;          // dis[j] at smf[ds_o + j]
     const int nbo = nb_w + 2 * ((inB ? eA : 0) - e0);                     // record of CSR slot pos at smi[nbo + 2 pos]
     int beg = 0, deg = 0;
     float di = 0.f;
-    if (row_ok) { beg = smi[rp_o + li]; deg = smi[rp_o + li + 1] - beg; di = smf[ds_o + n0 + li]; }
+    {
+      const int rp_o = srp + (inB ? mp->off[5] : mp->off[1]);             // rowptr[n0 + r] at smi[rp_o + r]
+      const int cl_o = scl + (inB ? mp->off[6] : mp->off[2]) - e0;        // col[pos] at smi[cl_o + pos]
+      const int ds_o = sds + (inB ? mp->off[7] : mp->off[3]) - n0;        // dis[j] at smf[ds_o + j]
+      if (row_ok) { beg = smi[rp_o + li]; deg = smi[rp_o + li + 1] - beg; di = smf[ds_o + n0 + li]; }
+      // ---- per CSR slot: (tile row of the neighbour, norm_ij); the two threads of a row take alternate slots ----
+      for (int t = cg; t < deg; t += TPR) {
+        const int j = smi[cl_o + beg + t];
+        const bool ok = (unsigned)(j - n0) < (unsigned)ng;
+        if (!ok && a.f.status) atomicOr(a.f.status, kStatusCrossEdgeTc);
+        const float w = ok ? smf[ds_o + (ok ? j : n0)] * di : 0.f;
+        *reinterpret_cast<int2*>(smi + nbo + 2 * (beg + t)) = make_int2(ok ? j - jb : i, __float_as_int(w));
+      }
+    }
     const float wself = (di * a.f.fill) * di;
     const int iself = row_ok ? i : 0;
-
-    // ---- per CSR slot: (tile row of the neighbour, norm_ij); the threads of a row take alternate slots ----
-    for (int t = cg; t < deg; t += TPR) {
-      const int j = smi[cl_o + beg + t];
-      const bool ok = (unsigned)(j - n0) < (unsigned)ng;
-      if (!ok && a.f.status) atomicOr(a.f.status, kStatusCrossEdgeTc);
-      const float w = ok ? smf[ds_o + (ok ? j : n0)] * di : 0.f;
-      *reinterpret_cast<int2*>(smi + nbo + 2 * (beg + t)) = make_int2(ok ? j - jb : i, __float_as_int(w));
-    }
     TC_TICK(2);
     ptx::named_bar_sync(bar_full, kSlotThreads);
     TC_TICK(3);
-    // every lane of the warp walks the same number of neighbour steps (the warp's largest degree); a lane
-    // past its own degree adds 0 x its own row
+    // every lane of the warp walks the same number of neighbour steps (the warp's largest degree)
     const int maxdeg = __reduce_max_sync(0xffffffffu, deg);
     const int2* nbp = reinterpret_cast<const int2*>(smi + nbo) + beg;
     auto nb_at = [&](int t) { return t < deg ? nbp[t] : make_int2(iself, 0); };
@@ -581,47 +603,60 @@ k_tc_fwd(const TcArgs a) {
         // compile-time column count of every column group: min(XW, F - XW g), dispatched on the (warp-uniform) group
         constexpr int N0 = F_ < XW ? F_ : XW;
         constexpr int N1 = F_ - XW < 0 ? 0 : (F_ - XW < XW ? F_ - XW : XW);
-        constexpr int N2 = F_ - 2 * XW < 0 ? 0 : (F_ - 2 * XW < XW ? F_ - 2 * XW : XW);
-        constexpr int N3 = F_ - 3 * XW < 0 ? 0 : (F_ - 3 * XW < XW ? F_ - 3 * XW : XW);
         if (cg == 0) gather_x<N0, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
-        else if (cg == 1) gather_x<N1, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
-        else if (cg == 2) gather_x<N2, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
-        else gather_x<N3, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
+        else gather_x<N1, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
       } else if (ncol > 0) {
         gather_x<-1, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself, ncol < XW ? ncol : XW);
       }
-      if (TPR == 2) {
-        float v[16];
-#pragma unroll
-        for (int c = 0; c < 16; ++c) v[c] = acc[c % XW];
-        tc::store_split16(v, a_hi, a_lo, trow, cg * 16);
-      } else {
-        float v[8];
-#pragma unroll
-        for (int c = 0; c < 8; ++c) v[c] = acc[c % XW];
-        tc::store_split8(v, a_hi, a_lo, trow, cg * 8);
-      }
+      tc::store_split16(acc, a_hi, a_lo, trow, cg * 16);
     }
     TC_TICK(4);
 
     for (int l = 0; l < L; ++l) {
       const bool last = l == L - 1;
-      ptx::tmem_wait_st();
-      ptx::tc_fence_before_sync();
-      if (ctl_warp) {
-        ptx::named_bar_sync(bar_aop, kSlotThreads);  // A operand complete; every reader of the activation buffer is done
-        if (lane == 0) {
-          ptx::tc_fence_after_sync();
-          if (l == 0)
-            tc::issue_split_mma<4>(d_t, a_hi, a_lo, ptx::smem_u32(w0_hi), ptx::smem_u32(w0_lo));  // K = 32, zero padded
-          else
-            tc::issue_split_mma<8>(d_t, a_hi, a_lo, ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64),
-                                   ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64));
-          ptx::mma_commit(&bar_mma[slot]);
+      const uint32_t wt_hi = l == 0 ? ptx::smem_u32(w0_hi) : ptx::smem_u32(wl_base + (size_t)(l - 1) * 2 * tc::kN * 64);
+      const uint32_t wt_lo = l == 0 ? ptx::smem_u32(w0_lo) : wt_hi + tc::kN * 64 * 4;
+      if (!KSPLIT || l == 0) {
+        ptx::tmem_wait_st();
+        ptx::tc_fence_before_sync();
+        if (ctl_warp) {
+          ptx::named_bar_sync(bar_aop, kSlotThreads);  // A operand complete; every reader of the activation buffer is done
+          if (lane == 0) {
+            ptx::tc_fence_after_sync();
+            if (l == 0) tc::issue_split_mma<4>(d_t, a_hi, a_lo, wt_hi, wt_lo);  // K = 32, zero padded
+            else tc::issue_split_mma<8>(d_t, a_hi, a_lo, wt_hi, wt_lo);
+            ptx::mma_commit(&bar_mma[slot]);
+          }
+          __syncwarp();
+        } else {
+          ptx::named_bar_arrive(bar_aop, kSlotThreads);
         }
-        __syncwarp();
       } else {
-        ptx::named_bar_arrive(bar_aop, kSlotThreads);
+        // K-split layer: (the operand halves were gathered below, at the end of the previous layer)
+        if (cg == 0) {
+          ptx::tmem_wait_st();
+          ptx::tc_fence_before_sync();
+          if (ctl_warp) {
+            ptx::named_bar_sync(bar_aop, 128);   // the four warps of half 0
+            if (lane == 0) {
+              ptx::tc_fence_after_sync();
+              tc::issue_split_mma<4>(d_t, a_hi, a_lo, wt_hi, wt_lo);                         // k = 0..31
+              ptx::mma_commit(&bar_free[slot]);
+            }
+            __syncwarp();
+            ptx::named_bar_sync(bar_a1, 160);    // + the four warps of half 1
+            if (lane == 0) {
+              ptx::tc_fence_after_sync();
+              tc::issue_split_mma<4>(d_t, a_hi, a_lo, wt_hi + tc::kChunkFloats * 4, wt_lo + tc::kChunkFloats * 4, 1u);  // k = 32..63, on top
+              ptx::mma_commit(&bar_mma[slot]);
+            }
+            __syncwarp();
+          } else {
+            ptx::named_bar_arrive(bar_aop, 128);
+          }
+        } else {
+          ptx::named_bar_arrive(bar_a1, 160);    // (half 1 stored its operand inside the gather block below)
+        }
       }
       if (l == 0 && p_gA >= 0) pool_tile(p_gA, p_gB, p_nA, p_nB);   // the previous tile, while the MMAs run
       if (ctl_warp) ptx::mbar_wait(&bar_mma[slot], mma_phase);      // one warp polls; the others sleep in the barrier below
@@ -629,6 +664,7 @@ k_tc_fwd(const TcArgs a) {
       TC_TICK(5);
       ptx::named_bar_sync(bar_full, kSlotThreads);
       ptx::tc_fence_after_sync();
+      if (l == 0 && pf_warp) issue(k + 1, true);   // every layer-0 gather of the slot is over: the x stage is free
       TC_TICK(6);
 
       // ---- epilogue: h_r = lrelu(D_r + b_l) -> activation buffer (+ optional save) ------------------
@@ -658,42 +694,55 @@ k_tc_fwd(const TcArgs a) {
       ptx::named_bar_sync(bar_full, kSlotThreads);  // h complete in shared memory; D may be overwritten
       TC_TICK(8);
 
-      if (!last && warp_ok) {
+      if (!last) {
         // ---- next layer's A operand: a_r = sum_j norm_rj h_j ; this thread's CW of the 64 columns -----
         float acc[CW];
 #pragma unroll
         for (int c = 0; c < CW; ++c) acc[c] = 0.f;
-        const float* hcol = smf + hb_w + CW * cg;
-        auto row_fma = [&](int r, float w) {
-          const float4* row = reinterpret_cast<const float4*>(hcol + r * HP);
+        if (warp_ok) {
+          const float* hcol = smf + hb_w + CW * cg;
+          auto row_fma = [&](int r, float w) {
+            const float4* row = reinterpret_cast<const float4*>(hcol + r * HP);
 #pragma unroll
-          for (int q = 0; q < CW / 4; ++q) {
-            const float4 v = row[q];
-            acc[4 * q + 0] = fmaf(w, v.x, acc[4 * q + 0]);
-            acc[4 * q + 1] = fmaf(w, v.y, acc[4 * q + 1]);
-            acc[4 * q + 2] = fmaf(w, v.z, acc[4 * q + 2]);
-            acc[4 * q + 3] = fmaf(w, v.w, acc[4 * q + 3]);
+            for (int q = 0; q < CW / 4; ++q) {
+              const float4 v = row[q];
+              acc[4 * q + 0] = fmaf(w, v.x, acc[4 * q + 0]);
+              acc[4 * q + 1] = fmaf(w, v.y, acc[4 * q + 1]);
+              acc[4 * q + 2] = fmaf(w, v.z, acc[4 * q + 2]);
+              acc[4 * q + 3] = fmaf(w, v.w, acc[4 * q + 3]);
+            }
+          };
+          int2 nb = nb_at(0);
+#pragma unroll 1
+          for (int t = 0; t < maxdeg; ++t) {
+            const int2 cur = nb;
+            nb = nb_at(t + 1);
+            if (t < deg) row_fma(cur.x, __int_as_float(cur.y));
           }
-        };
-        int2 nb = nb_at(0);
-        for (int t = 0; t < maxdeg; ++t) {
-          const int2 cur = nb;
-          nb = nb_at(t + 1);
-          if (t < deg)
-            row_fma(cur.x, __int_as_float(cur.y));
+          row_fma(iself, wself);
         }
-        row_fma(iself, wself);
+        if (KSPLIT && cg == 1) {
+          // the first half's MMAs must have read the operand before it is overwritten
+          ptx::mbar_wait(&bar_free[slot], free_phase);
+          ptx::tc_fence_after_sync();
+        }
+        free_phase ^= 1u;
+        if (warp_ok) {
 #pragma unroll
-        for (int cc = 0; cc < CW; cc += 16) {
-          float v[16];
+          for (int cc = 0; cc < CW; cc += 16) {
+            float v[16];
 #pragma unroll
-          for (int q = 0; q < 16; ++q) v[q] = acc[cc + q];
-          tc::store_split16(v, a_hi, a_lo, trow, cg * CW + cc);
+            for (int q = 0; q < 16; ++q) v[q] = acc[cc + q];
+            tc::store_split16(v, a_hi, a_lo, trow, KSPLIT ? cc : cg * CW + cc);
+          }
+        }
+        if (KSPLIT && cg == 1) {
+          ptx::tmem_wait_st();
+          ptx::tc_fence_before_sync();
         }
       }
       TC_TICK(9);
     }
-
     p_gA = gA; p_gB = gB; p_nA = nA; p_nB = nB;
     TC_TICK(10);
   }
@@ -704,7 +753,7 @@ k_tc_fwd(const TcArgs a) {
   if (tid < 32) ptx::tmem_dealloc(tmem_base_s, 512);
 }
 
-size_t tc_fwd_smem_bytes(int F, int L) { return tc_layout(F, L).total; }
+size_t tc_fwd_smem_bytes(int F, int L) { return tc_layout(F, L, 2).total; }
 
 }  // namespace hcg
 
@@ -714,13 +763,13 @@ struct TcPlan {     // launch geometry of the work list for a batch of B graphs
   int grid, nslots, W, nwin, cap;
 };
 
-static TcPlan tc_plan(int64_t B) {
+static TcPlan tc_plan(int64_t B, int ns) {
   TcPlan p{};
-  int64_t grid = cdiv(B, kTcSlots);
+  int64_t grid = cdiv(B, ns);
   if (grid > kNumSMs) grid = kNumSMs;
   if (grid < 1) grid = 1;
   p.grid = (int)grid;
-  p.nslots = p.grid * kTcSlots;
+  p.nslots = p.grid * ns;
   // graphs per slot -> windows of at most kTcWinMax graphs, as equal as possible
   const int64_t gps = cdiv(B, p.nslots);
   const int64_t wins = cdiv(gps, kTcWinMax);
@@ -743,9 +792,10 @@ struct TcWs {
 static TcWs carve_tc(void* ws, int64_t B) {
   Carver c(ws, (size_t)-1);
   TcWs w{};
-  const TcPlan p = tc_plan(B);
-  w.tiles = c.take<TcTile>((size_t)p.nslots * p.cap + 1);
-  w.counts = c.take<int>((size_t)p.nslots + 1);
+  const TcPlan p2 = tc_plan(B, 2), p3 = tc_plan(B, 3);
+  const size_t t2 = (size_t)p2.nslots * p2.cap, t3 = (size_t)p3.nslots * p3.cap;
+  w.tiles = c.take<TcTile>((t2 > t3 ? t2 : t3) + 1);
+  w.counts = c.take<int>((size_t)3 * kNumSMs + 1);
   w.overflow_count = c.take<int>(64);
   w.overflow_list = c.take<int>((size_t)B + 1);
   w.bytes = c.off;
@@ -766,30 +816,34 @@ static int ensure_smem(K kernel, size_t smem, size_t (&configured)[16]) {
   return HCG_OK;
 }
 
-// launch-time choice of the threads-per-row variant (HCG_TC_TPR=2|4 in the environment overrides; tests / tuning)
-static int tc_tpr() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("HCG_TC_TPR");
-    v = (e && e[0] == '2') ? 2 : (e && e[0] == '4') ? 4 : kTcDefaultTpr;
+// slots per CTA: three when their shared memory fits (two conv layers), else two; HCG_TC_SLOTS=2|3 in the
+// environment overrides (tests / tuning)
+static int tc_slots(int F, int L) {
+  static int env = -1;
+  if (env < 0) {
+    const char* e = getenv("HCG_TC_SLOTS");
+    env = (e && e[0] == '2') ? 2 : (e && e[0] == '3') ? 3 : 0;
   }
-  return v;
+  const bool fits3 = tc_layout(F, L, 3).total <= 227 * 1024;
+  if (env == 2 || !fits3) return 2;
+  return env == 3 ? 3 : kTcDefaultSlots;
 }
 
-template <int F_, int TPR>
+template <int F_, int NS>
 static int launch_tc_variant(const TcArgs& a, int grid, size_t smem, cudaStream_t st) {
   static size_t configured[16];
-  int rc = ensure_smem(k_tc_fwd<F_, TPR>, smem, configured);
+  int rc = ensure_smem(k_tc_fwd<F_, NS>, smem, configured);
   if (rc) return rc;
-  k_tc_fwd<F_, TPR><<<(unsigned)grid, kTcSlots * 128 * TPR, smem, st>>>(a);
+  k_tc_fwd<F_, NS><<<(unsigned)grid, NS * 256, smem, st>>>(a);
   return HCG_OK;
 }
 
 int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStream_t st) {
   if (f.B <= 0) return HCG_OK;
   TcWs w = carve_tc(ws, f.B);
-  const TcPlan p = tc_plan(f.B);
-  const size_t smem = tc_fwd_smem_bytes(f.F, f.L);
+  const int ns = tc_slots(f.F, f.L);
+  const TcPlan p = tc_plan(f.B, ns);
+  const size_t smem = tc_layout(f.F, f.L, ns).total;
   HCG_CUDA_OK(cudaMemsetAsync(w.overflow_count, 0, sizeof(int), st));
   k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(f.graph_ptr, f.rowptr, f.col, f.dis, f.x, f.F, N, E, f.B, p.W,
                                                                           p.nslots, p.nwin, p.cap, w.tiles, w.counts,
@@ -803,12 +857,12 @@ int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStr
   a.cap = p.cap;
   a.N = N; a.E = E;
   int rc;
-  if (tc_tpr() == 2)
+  if (ns == 2)
     rc = f.F == 25 ? launch_tc_variant<25, 2>(a, p.grid, smem, st) : f.F == 32 ? launch_tc_variant<32, 2>(a, p.grid, smem, st)
                                                                                : launch_tc_variant<0, 2>(a, p.grid, smem, st);
   else
-    rc = f.F == 25 ? launch_tc_variant<25, 4>(a, p.grid, smem, st) : f.F == 32 ? launch_tc_variant<32, 4>(a, p.grid, smem, st)
-                                                                               : launch_tc_variant<0, 4>(a, p.grid, smem, st);
+    rc = f.F == 25 ? launch_tc_variant<25, 3>(a, p.grid, smem, st) : f.F == 32 ? launch_tc_variant<32, 3>(a, p.grid, smem, st)
+                                                                               : launch_tc_variant<0, 3>(a, p.grid, smem, st);
   if (rc) return rc;
   HCG_LAUNCH_OK(st, "k_tc_fwd");
 

@@ -56,7 +56,7 @@ __device__ __forceinline__ void prep_weight_tiles(const float* __restrict__ W, i
 // steps at full magnitude, not of 3 x ksteps.
 template <int KSTEPS>
 __device__ __forceinline__ void issue_split_mma(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi_smem,
-                                                uint32_t b_lo_smem) {
+                                                uint32_t b_lo_smem, uint32_t accumulate_first = 0u) {
   constexpr uint32_t idesc = ptx::make_idesc_tf32(kRows, kN);
   // descriptors of K-step s = descriptor of step 0 + a compile-time offset in its 14-bit address field
   // (16-byte units; shared-memory addresses are below 2^18, so the field never carries)
@@ -64,7 +64,7 @@ __device__ __forceinline__ void issue_split_mma(uint32_t d, uint32_t a_hi, uint3
 #pragma unroll
   for (int s = 0; s < KSTEPS; ++s) {
     const uint64_t boff = (uint64_t)(((s >> 2) * (kChunkFloats * 4) + (s & 3) * 32) >> 4);
-    ptx::mma_tf32_ts(d, a_lo + s * 8, bh + boff, idesc, s > 0 ? 1u : 0u);
+    ptx::mma_tf32_ts(d, a_lo + s * 8, bh + boff, idesc, s > 0 ? 1u : accumulate_first);  // (continues an earlier chain?)
     ptx::mma_tf32_ts(d, a_hi + s * 8, bl + boff, idesc, 1u);
   }
 #pragma unroll
