@@ -101,7 +101,7 @@ SIGNATURES = {
     "hcg_unpack_batch": (C.c_int, [C.POINTER(HcgPackedStore), _fp, C.c_int64, C.c_int64, _fp, _fp, _fp, _fp, C.c_int64,
                                    _fp, _fp, _fp]),
     "hcg_rmse_seed": (C.c_int, [_fp, _fp, C.c_int64, C.c_int, _fp, _fp, _fp]),
-    "hcg_adam_step": (C.c_int, [_fp, _fp, _fp, _fp, C.c_int64, _fp, C.c_float, C.c_float, C.c_float, C.c_float,
+    "hcg_adam_step": (C.c_int, [_fp, _fp, _fp, _fp, C.c_int64, _fp, C.c_double, C.c_double, C.c_double, C.c_double,
                                 C.c_int64, _fp, _fp]),
 }
 

@@ -539,7 +539,24 @@ k_collate_graph(const int64_t* __restrict__ src, const int64_t* __restrict__ dst
     if (n <= 0) continue;
     if (n <= kWgNodes && e_cnt <= kWgEdges && e_cnt >= 0 && e_lo >= 0 && (int64_t)e_lo + e_cnt <= E) continue;  // done by a warp
     if (n > kGrpNodes || e_cnt > kGrpEdges || e_cnt < 0 || e_lo < 0 || (int64_t)e_lo + e_cnt > E) {
+      // Refused graph: the status word says so and the caller is expected to collate again without the flag.  A
+      // caller that never reads the status (validate = false) must still stay in bounds: leave this graph's rows
+      // EMPTY (every row starts at the slice's first slot) and point the slice's column entries at the graph's own
+      // first node, instead of leaving uninitialised offsets behind.
       if (threadIdx.x == 0) atomicOr(status, kStatusNotGrouped);
+      const int64_t lo = e_lo < 0 ? 0 : (e_lo > E ? E : (int64_t)e_lo);
+      int64_t hi = (int64_t)e_lo + (e_cnt > 0 ? e_cnt : 0);
+      hi = hi < lo ? lo : (hi > E ? E : hi);
+      const float d1 = __fdiv_rn(1.0f, __fsqrt_rn(fill));
+      for (int i = threadIdx.x; i < n; i += kGrpThreads) {
+        rowptr[n0 + i] = (int32_t)lo;
+        dis[n0 + i] = isinf(d1) ? 0.f : d1;
+        if (t_rowptr) t_rowptr[n0 + i] = (int32_t)lo;
+      }
+      for (int64_t k = lo + threadIdx.x; k < hi; k += kGrpThreads) {
+        col[k] = n0; eid[k] = (int32_t)k;
+        if (t_rowptr) { t_col[k] = n0; t_eid[k] = (int32_t)k; }
+      }
       continue;
     }
     grp_build(dst, src, e_lo, e_cnt, n0, n, cnt, rp, slot_eid, slot_val, warp_tot, rowptr, col, eid, dis, fill, N, status);

@@ -44,6 +44,22 @@ int config_get(int key);                               // hcg_config_get
     if (!(cond)) return ::hcg::set_err(code, __VA_ARGS__);                            \
   } while (0)
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a PER-DEVICE setting: the "already configured" note is kept
+// per device (a process may drive several GPUs), indexed by cudaGetDevice().
+constexpr int kMaxDevices = 64;
+struct SmemConfigured { size_t bytes[kMaxDevices] = {}; };
+template <typename K>
+inline int ensure_dyn_smem(K kernel, size_t smem, SmemConfigured& done) {
+  int dev = 0;
+  HCG_CUDA_OK(cudaGetDevice(&dev));
+  const bool known = dev >= 0 && dev < kMaxDevices;
+  if (!known || smem > done.bytes[dev]) {
+    HCG_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (known) done.bytes[dev] = smem;
+  }
+  return HCG_OK;
+}
+
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 

@@ -291,11 +291,8 @@ size_t fused_fwd_smem_bytes(int F, int L, int ncap, int ecap) {
 
 int launch_fused_fwd(const FusedFwdArgs& a, size_t smem, cudaStream_t st) {
   if (a.B <= 0) return HCG_OK;
-  static thread_local size_t configured = 0;
-  if (smem > configured) {
-    HCG_CUDA_OK(cudaFuncSetAttribute(k_fused_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  static SmemConfigured configured;
+  if (int rc = ensure_dyn_smem(k_fused_fwd, smem, configured)) return rc;
   int per_sm = 0;
   HCG_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_fwd, kFusedThreads, smem));
   if (per_sm < 1) return set_err(HCG_ERR_UNSUPPORTED, "fused forward does not fit on an SM (%zu B smem)", smem);

@@ -314,11 +314,8 @@ size_t fused_bwd_scratch_elems(int64_t N, int64_t B) { return 3 * (size_t)(N + k
 int launch_fused_bwd(FusedBwdArgs a, int64_t N, float* g_w2, float* g_w1, float* g_b2, float* g_b1, cudaStream_t st) {
   if (a.B <= 0) return HCG_OK;
   const size_t smem = fused_bwd_smem_bytes();
-  static thread_local bool configured = false;
-  if (!configured) {
-    HCG_CUDA_OK(cudaFuncSetAttribute(k_fused_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
-  }
+  static SmemConfigured configured;
+  if (int rc = ensure_dyn_smem(k_fused_bwd, smem, configured)) return rc;
   a.scratch_stride = (int64_t)(N + kBwdSlack * a.B + kBwdSlack) * 64;
   const int grid = fused_bwd_grid(a.B);
   k_fused_bwd<<<grid, kBwdThreads, smem, st>>>(a);

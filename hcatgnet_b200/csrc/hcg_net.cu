@@ -1307,11 +1307,8 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
   if (g_out && w.ropartial != nullptr && config_get(HCG_CFG_BACKWARD_PATH) != 1) {
     // default head (128 -> 64 -> C): one kernel + one reduce
     const size_t smem = ro2_bwd_smem_bytes(p->C);
-    static thread_local size_t configured = 0;
-    if (smem > configured) {
-      HCG_CUDA_OK(cudaFuncSetAttribute(k_readout2_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      configured = smem;
-    }
+    static SmemConfigured configured;
+    if (int rc2 = ensure_dyn_smem(k_readout2_bwd, smem, configured)) return rc2;
     const int blocks = (int)cdiv(B, RO_G);
     k_readout2_bwd<<<blocks, 256, smem, st>>>(emb, saved->hid[0], g_out, g_emb, p->ro_w[0], p->ro_w[1], B, p->C, p->slope,
                                              w.gemb, w.ropartial);

@@ -69,7 +69,8 @@ extern "C" int hcg_selftest_tc_gemm(const float* A, const float* W, int K, float
   HCG_REQUIRE(A && W && D, HCG_ERR_INVALID_ARG, "NULL pointer");
   HCG_REQUIRE(K >= 1 && K <= 64, HCG_ERR_UNSUPPORTED, "K=%d outside [1,64]", K);
   const size_t smem = 2 * 64 * 64 * sizeof(float) + 1024;
-  HCG_CUDA_OK(cudaFuncSetAttribute(k_tc_selftest, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static SmemConfigured configured;
+  if (int rc = ensure_dyn_smem(k_tc_selftest, smem, configured)) return rc;
   k_tc_selftest<<<1, 128, smem, st>>>(A, W, K, D);
   HCG_LAUNCH_OK(st, "k_tc_selftest");
   return HCG_OK;
@@ -804,18 +805,6 @@ static TcWs carve_tc(void* ws, int64_t B) {
 
 size_t tc_fwd_workspace_bytes(int64_t B) { return carve_tc(nullptr, B).bytes; }
 
-// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-device setting
-template <typename K>
-static int ensure_smem(K kernel, size_t smem, size_t (&configured)[16]) {
-  int dev = 0;
-  HCG_CUDA_OK(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= 16 || smem > configured[dev]) {
-    HCG_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    if (dev >= 0 && dev < 16) configured[dev] = smem;
-  }
-  return HCG_OK;
-}
-
 // slots per CTA: three when their shared memory fits (two conv layers), else two; HCG_TC_SLOTS=2|3 in the
 // environment overrides (tests / tuning)
 static int tc_slots(int F, int L) {
@@ -831,9 +820,8 @@ static int tc_slots(int F, int L) {
 
 template <int F_, int NS>
 static int launch_tc_variant(const TcArgs& a, int grid, size_t smem, cudaStream_t st) {
-  static size_t configured[16];
-  int rc = ensure_smem(k_tc_fwd<F_, NS>, smem, configured);
-  if (rc) return rc;
+  static SmemConfigured configured;
+  if (int rc = ensure_dyn_smem(k_tc_fwd<F_, NS>, smem, configured)) return rc;
   k_tc_fwd<F_, NS><<<(unsigned)grid, NS * 256, smem, st>>>(a);
   return HCG_OK;
 }

@@ -223,13 +223,10 @@ int launch_tc_gemm(const float* A, const float* W, float* C, int64_t M, int K, i
   k_w_image<<<(unsigned)cdiv((int64_t)Nc * nkc * kGemmKC, 256), 256, 0, st>>>(W, Nc, K, transposed ? 1 : 0, nkc, img);
   HCG_LAUNCH_OK(st, "k_w_image");
   const size_t smem = 3 * 2 * (size_t)Nc * kGemmKC * 4 + 1024;
-  static thread_local size_t configured[2] = {0, 0};
+  static SmemConfigured configured[2];
   const int e = epi == TCG_EPI_MASK ? 1 : 0;
-  if (smem > configured[e]) {
-    HCG_CUDA_OK(cudaFuncSetAttribute(e ? k_tc_gemm<TCG_EPI_MASK> : k_tc_gemm<TCG_EPI_NONE>,
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured[e] = smem;
-  }
+  if (int rc = e ? ensure_dyn_smem(k_tc_gemm<TCG_EPI_MASK>, smem, configured[1])
+                 : ensure_dyn_smem(k_tc_gemm<TCG_EPI_NONE>, smem, configured[0])) return rc;
   int64_t grid = (M + 127) >> 7;
   if (grid > kNumSMs) grid = kNumSMs;
   if (e) k_tc_gemm<TCG_EPI_MASK><<<(unsigned)grid, kGemmThreads, smem, st>>>(A, img, C, M, K, Nc, nkc, aux, slope);

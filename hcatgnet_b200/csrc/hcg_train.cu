@@ -46,7 +46,7 @@ k_rmse_seed(const float* __restrict__ out, const float* __restrict__ y, int64_t 
 __global__ void __launch_bounds__(256)
 k_adam(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n,
        const float* __restrict__ tail, float one_minus_b1, float b2, float one_minus_b2, float step_size,
-       float inv_bc2_sqrt, float eps, float* __restrict__ loss_out) {
+       float bc2_sqrt, float eps, float* __restrict__ loss_out) {
   float scale = 1.f;
   if (tail) {
     const float sse = tail[0], cnt = tail[1];
@@ -58,10 +58,10 @@ k_adam(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m
   if (i >= n) return;
   const float gi = g[i] * scale;
   const float mi = m[i] + (gi - m[i]) * one_minus_b1;
-  const float vi = v[i] * b2 + one_minus_b2 * gi * gi;
+  const float vi = v[i] * b2 + one_minus_b2 * (gi * gi);
   m[i] = mi;
   v[i] = vi;
-  const float denom = sqrtf(vi) * inv_bc2_sqrt + eps;
+  const float denom = sqrtf(vi) / bc2_sqrt + eps;   // torch: (exp_avg_sq.sqrt() / bias_correction2_sqrt).add_(eps)
   p[i] = p[i] - step_size * (mi / denom);
 }
 
@@ -80,20 +80,20 @@ extern "C" int hcg_rmse_seed(const float* out, const float* y, int64_t B, int C,
 }
 
 extern "C" int hcg_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n,
-                             const float* tail, float lr, float beta1, float beta2, float eps, int64_t step,
+                             const float* tail, double lr, double beta1, double beta2, double eps, int64_t step,
                              float* loss_out, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   HCG_REQUIRE(param && grad && exp_avg && exp_avg_sq, HCG_ERR_INVALID_ARG, "NULL pointer");
   HCG_REQUIRE(n >= 0 && step >= 1, HCG_ERR_INVALID_ARG, "bad n=%lld / step=%lld", (long long)n, (long long)step);
   if (n == 0) return HCG_OK;
   // bias corrections in double on the host, exactly as torch's Python code computes them
-  const double bc1 = 1.0 - pow((double)beta1, (double)step);
-  const double bc2 = 1.0 - pow((double)beta2, (double)step);
-  const float step_size = (float)((double)lr / bc1);
-  const float inv_bc2_sqrt = (float)(1.0 / sqrt(bc2));
+  const double bc1 = 1.0 - pow(beta1, (double)step);
+  const double bc2 = 1.0 - pow(beta2, (double)step);
+  const float step_size = (float)(lr / bc1);
+  const float bc2_sqrt = (float)sqrt(bc2);
   note_region(st);
-  k_adam<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(param, grad, exp_avg, exp_avg_sq, n, tail, 1.f - beta1, beta2, 1.f - beta2,
-                                                 step_size, inv_bc2_sqrt, eps, loss_out);
+  k_adam<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(param, grad, exp_avg, exp_avg_sq, n, tail, (float)(1.0 - beta1), (float)beta2,
+                                                 (float)(1.0 - beta2), step_size, bc2_sqrt, (float)eps, loss_out);
   HCG_LAUNCH_OK(st, "k_adam");
   return HCG_OK;
 }

@@ -34,8 +34,9 @@ import numpy as np
 import torch
 
 from . import _lib
-from .data import Batch, _field
+from .data import GROUPED_MAX_EDGES, GROUPED_MAX_NODES, Batch, _field
 
+FLAG_GROUPABLE = 1      # header flag: the packer checked the preconditions of hcg_collate's graph-local path
 MAGIC = b"HCGPACK1"
 HEADER_BYTES = 128
 _ALIGN = 64
@@ -71,6 +72,11 @@ class PackedDataset:
             raise ValueError("not a packed graph image (bad magic)")
         h = blob[8:8 + 8 * 8].view(np.int64)
         self.G, self.N, self.E, self.F, self.Fu, self.Ff, self.edge_kind, self.max_graph_nodes = (int(v) for v in h)
+        h2 = blob[72:72 + 2 * 8].view(np.int64)
+        # written by from_arrays (zero in images of older writers): size of the largest edge list, and whether the
+        # packer verified what hcg_collate's graph-local path takes for granted (no self-loop edges; every graph
+        # within its per-graph capacity).  Unverified images leave the choice to hcg_collate's own device check.
+        self.max_graph_edges, self.flags = int(h2[0]), int(h2[1])
         self.layout, total = _layout(self.G, self.N, self.E, self.F, self.Fu, self.Ff, self.edge_kind)
         if blob.size < total:
             raise ValueError(f"packed graph image truncated: {blob.size} of {total} bytes")
@@ -111,6 +117,9 @@ class PackedDataset:
         blob = blob_t.numpy()
         blob[:8] = np.frombuffer(MAGIC, np.uint8)
         blob[8:72].view(np.int64)[:] = [G, N, E, F, Fu, Ff, ek, nmax]
+        emax = int(np.diff(edge_ptr).max()) if G else 0
+        groupable = (not E or not bool(np.any(ei[0] == ei[1]))) and nmax <= GROUPED_MAX_NODES and emax <= GROUPED_MAX_EDGES
+        blob[72:88].view(np.int64)[:] = [emax, FLAG_GROUPABLE if groupable else 0]
         self = cls(blob)
         self._owner = blob_t
         self.col_slot[:] = col_slot
@@ -166,7 +175,7 @@ class PackedDataset:
         batch = np.repeat(np.arange(ids.size, dtype=np.int64), n)
         return Batch(torch.from_numpy(x), torch.from_numpy(np.ascontiguousarray(ei)), torch.from_numpy(batch),
                      torch.from_numpy(ptr), torch.from_numpy(self.y[ids].copy()), torch.from_numpy(self.idx[ids].copy()),
-                     ids.size, edges_grouped=True)
+                     ids.size, edges_grouped=True if (self.flags & FLAG_GROUPABLE) else None)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -309,7 +318,7 @@ class DeviceGraphStore:
                 meta_d[0].data_ptr(), meta_d[1].data_ptr(), x.data_ptr(), ei.data_ptr(), E_out,
                 bvec.data_ptr() if bvec is not None else None, y.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
         idx = torch.from_numpy(ds.idx[ids_np].copy() if ids_np is not None else np.array(ds.idx))
-        out = Batch(x, ei, bvec, meta_d[0], y, idx, B, edges_grouped=True)
+        out = Batch(x, ei, bvec, meta_d[0], y, idx, B, edges_grouped=True if (ds.flags & FLAG_GROUPABLE) else None)
         out.max_graph_nodes = int(n.max()) if B else 0
         out._keepalive = meta_d
         return out

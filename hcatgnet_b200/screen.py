@@ -111,7 +111,7 @@ def predict_stream(model, batches: Iterable[Batch], return_embedding: bool = Fal
                     e_h = torch.empty(emb.shape, dtype=emb.dtype, pin_memory=True)
                     e_h.copy_(emb, non_blocking=True)
                 ev = torch.cuda.Event()
-                ev.record()
+                ev.record(torch.cuda.current_stream(out.device))   # the stream the copies above were queued on
                 pending.append((o_h, e_h, d._host, ev, (out, emb)))
                 if len(pending) > 1:  # hand back the previous batch: the GPU queue stays one step ahead
                     o, e, h, pev, _keep = pending.popleft()
@@ -187,7 +187,7 @@ def predict_ensemble_stream(models, batches: Iterable[Batch], device=None, depth
                 t_h.copy_(t, non_blocking=True)
                 hosts.append(t_h)
             ev = torch.cuda.Event()
-            ev.record()
+            ev.record(torch.cuda.current_stream(dev))
             pending.append((*hosts, d._host, ev, (pred, mean, std, plan, x)))
             if len(pending) > 1:
                 yield finish(pending.popleft())

@@ -43,6 +43,7 @@ class FusedTrainer:
         self.n = sum(sizes)
         f32 = dict(dtype=torch.float32, device=dev)
         self.flat = torch.empty(self.n, **f32)
+        self._offsets = [sum(sizes[:i]) for i in range(len(sizes))]
         off = 0
         with torch.no_grad():
             for p, k in zip(self.params, sizes):
@@ -55,11 +56,41 @@ class FusedTrainer:
         self.losses = torch.zeros(16, **f32)                    # ring of loss slots: a returned loss stays valid for 15 more steps
         self.steps = 0
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self.timing = None      # bench.py: a list here collects (start, end) CUDA events around every all-reduce
 
-    def step(self, batch) -> torch.Tensor:
-        """One optimisation step on ``batch`` (a device ``Batch``); returns the global RMSE (device scalar)."""
-        m, dev, dims = self.model, self.device, self.dims
+    def _bind(self):
+        """(Re-)point the module's parameters at views of the flat slab.  ``model.to(...)`` / ``load_state_dict``
+        with assignment re-allocate them (the reference's predict_network does ``model.to('cpu')``, reference
+        utils/utils_model.py:83): the slab would then be updated while forward reads detached copies."""
+        off = 0
+        with torch.no_grad():
+            for p in self.params:
+                k = p.numel()
+                view = self.flat[off:off + k].view(p.shape)
+                if p.data_ptr() != view.data_ptr():
+                    if p.device != self.device:
+                        raise RuntimeError("FusedTrainer: the model was moved off the trainer's device; move it back "
+                                           "(model.to(device)) before the next step")
+                    view.copy_(p.detach())          # keep whatever the caller loaded into the parameter
+                    p.data = view
+                off += k
+
+    def state_dict(self) -> dict:
+        """Optimizer state the module's own ``optimizer.state_dict()`` does not see (the moments live here)."""
+        return {"step": int(self.steps), "exp_avg": self.exp_avg.clone(), "exp_avg_sq": self.exp_avg_sq.clone()}
+
+    def load_state_dict(self, sd: dict) -> None:
+        self.steps = int(sd["step"])
+        self.exp_avg.copy_(sd["exp_avg"].to(self.device))
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"].to(self.device))
+
+    def accumulate(self, batch) -> None:
+        """Forward + loss seed + backward of ``batch`` into this rank's flat slab ``self.grad`` =
+        ``[parameter gradients of the shard's sum of squared errors | SSE | count]`` (shard-additive, see module doc)."""
+        dev, dims = self.device, self.dims
         lib = _lib.load()
+        if any(p.data_ptr() != self.flat.data_ptr() + 4 * o for p, o in zip(self.params, self._offsets)):
+            self._bind()
         x = ops.to_device(batch.x, dev, torch.float32)
         y = ops.to_device(batch.y, dev, torch.float32)
         B = int(batch.num_graphs)
@@ -74,16 +105,38 @@ class FusedTrainer:
             tail = self.grad[self.n:]
             _lib.check(lib.hcg_rmse_seed(out.data_ptr(), y.data_ptr(), B, dims.C, g_out.data_ptr(), tail.data_ptr(), st))
             ops.backward_raw(plan, x, dims, params, saved, emb, g_out, None, need_gx=False, flat_out=self.grad)
-            if self.world > 1:
-                dist.all_reduce(self.grad, op=dist.ReduceOp.SUM, group=self.group)
-            pg = m.optimizer.param_groups[0]
+
+    def reduce(self) -> None:
+        """Sum the slabs of all ranks (one NCCL all-reduce of 4 (n + 2) bytes); nothing to do with one rank."""
+        if self.world > 1:
+            if self.timing is not None:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            dist.all_reduce(self.grad, op=dist.ReduceOp.SUM, group=self.group)
+            if self.timing is not None:
+                e1.record()
+                self.timing.append((e0, e1))
+
+    def apply(self) -> torch.Tensor:
+        """``hcg_adam_step`` on the (reduced) slab: rescale by 1 / (2 count rmse), Adam update; returns the RMSE."""
+        lib = _lib.load()
+        with torch.cuda.device(self.device):
+            st = torch.cuda.current_stream(self.device).cuda_stream
+            pg = self.model.optimizer.param_groups[0]
             b1, b2 = pg["betas"]
             self.steps += 1
             loss = self.losses[self.steps % 16]
+            tail = self.grad[self.n:]
             _lib.check(lib.hcg_adam_step(self.flat.data_ptr(), self.grad.data_ptr(), self.exp_avg.data_ptr(),
                                          self.exp_avg_sq.data_ptr(), self.n, tail.data_ptr(), float(pg["lr"]), float(b1),
                                          float(b2), float(pg["eps"]), self.steps, loss.data_ptr(), st))
         return loss
+
+    def step(self, batch) -> torch.Tensor:
+        """One optimisation step on ``batch`` (a device ``Batch``); returns the global RMSE (device scalar)."""
+        self.accumulate(batch)
+        self.reduce()
+        return self.apply()
 
     def checksum(self) -> torch.Tensor:
         """Sum of the parameter slab (replicas of a data-parallel job must agree bit for bit)."""

@@ -293,10 +293,11 @@ int hcg_rmse_seed(const float* out, const float* y, int64_t B, int C, float* g_o
  * One Adam step (torch.optim.Adam semantics: amsgrad off, weight_decay 0) over a flat parameter slab.
  * tail: NULL, or the [sse, count] pair written by hcg_rmse_seed (summed over ranks): the gradient is then
  * scaled by 1 / (2 count sqrt(sse / count)) and the RMSE is written to loss_out (may be NULL).
- * step: 1-based step number (bias correction).
+ * step: 1-based step number (bias correction).  The hyper-parameters arrive as doubles, as torch holds them:
+ * 1 - beta and lr / bias_correction1 are formed in double and rounded to fp32 once (1.f - 0.999f is off by 1e-5).
  */
 int hcg_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n,
-                  const float* tail, float lr, float beta1, float beta2, float eps, int64_t step,
+                  const float* tail, double lr, double beta1, double beta2, double eps, int64_t step,
                   float* loss_out, void* stream);
 
 #ifdef __cplusplus

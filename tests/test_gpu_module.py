@@ -362,3 +362,29 @@ def test_store_loaders_match_host_loaders_in_nested_cv():
     assert dva._kept is not None and dtr._kept is None
     first = [id(b) for b in dva]
     assert first == [id(b) for b in dva]
+
+
+def test_explain_model_on_two_different_graphs_back_to_back(pkg):
+    """Two molecules of equal (N, E) through ONE GCN_explain, as the reference's explain loop feeds them
+    (scripts_experiments/explain_gnn.py:39-57): each call must use its own graph's topology (the plan cache is
+    keyed on the tensors' identity, not on their addresses, which the allocator reuses)."""
+    sd, graphs, _, _ = golden_io.rows_with_graphs("learning", 1, 2)
+    model = pkg.GCN_explain(pkg.default_options(), 25)
+    model.load_state_dict(sd, strict=True)
+    model = model.to("cuda").eval()
+    by_shape = {}
+    for g in graphs:
+        by_shape.setdefault((g["x"].shape[0], g["edge_index"].shape[1]), []).append(g)
+    pairs = [v for v in by_shape.values() if len(v) >= 2 and not torch.equal(v[0]["edge_index"], v[1]["edge_index"])]
+    assert pairs, "the fixture holds same-shape molecules with different bonds"
+    checked = 0
+    for group in pairs[:6]:
+        for g in group[:3]:
+            # fresh device tensors per call, freed right after: the next call's tensors land at the same addresses
+            with torch.no_grad():
+                out = model(x=g["x"].cuda(), edge_index=g["edge_index"].cuda(), batch_index=None).cpu()
+            ref_sd = {k: v for k, v in sd.items()}
+            o_ref, _ = ref_gcn.forward(ref_sd, g["x"], g["edge_index"], torch.zeros(g["x"].shape[0], dtype=torch.int64), 1)
+            assert float((out - o_ref).abs().max()) <= 1e-5 * max(1.0, float(o_ref.abs().max()))
+            checked += 1
+    assert checked >= 4
