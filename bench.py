@@ -361,7 +361,8 @@ def measure(cx: Ctx, mode: str, batch: int, hidden: int, convs: int, steps: int,
     for b in host:
         d = pkg.Batch(b.x.to(dev), b.edge_index.to(dev), b.batch.to(dev), b.ptr.to(dev), b.y.to(dev), None, b.num_graphs,
                       edges_grouped=True)
-        d.max_graph_nodes = b.max_graph_nodes   # what a PyG Batch knows on the host (ptr): sizes a kernel's capacity only
+        # what a PyG Batch knows on the host (ptr, _slice_dict): offsets of every graph and the size of the largest one
+        d.max_graph_nodes, d.max_graph_edges, d.edge_ptr = b.max_graph_nodes, b.max_graph_edges, b.edge_ptr.to(dev)
         devb.append(d)
     Ns = [b.num_nodes for b in host]
     Es = [int(b.edge_index.shape[1]) for b in host]
@@ -371,13 +372,14 @@ def measure(cx: Ctx, mode: str, batch: int, hidden: int, convs: int, steps: int,
         b = devb[i % POOL]
         if mode == "infer":
             plan = ops.collate(b.edge_index, b.batch, b.num_nodes, b.num_graphs, validate=False, grouped=True,
-                               max_graph_nodes=b.max_graph_nodes)
+                               max_graph_nodes=b.max_graph_nodes, ptr=b.ptr, edge_ptr=b.edge_ptr,
+                               max_graph_edges=b.max_graph_edges)
             with torch.no_grad():
                 out, _ = ops.gcn_apply(b.x, plan, dims, params)
             return out
         # a fresh batch object every step: the collate runs inside the step (no topology cache hit)
         fresh = pkg.Batch(b.x, b.edge_index, b.batch, b.ptr, b.y, None, b.num_graphs, edges_grouped=True)
-        fresh.max_graph_nodes = b.max_graph_nodes
+        fresh.max_graph_nodes, fresh.max_graph_edges, fresh.edge_ptr = b.max_graph_nodes, b.max_graph_edges, b.edge_ptr
         return trainer.step(fresh)
 
     def drain_losses(stream_of_losses):

@@ -32,6 +32,7 @@ class HcgGraph(C.Structure):
         ("ew0", _fp), ("t_ew0", _fp), ("selfw0", _fp), ("dis0", _fp),
         ("max_graph_nodes", C.c_int32), ("flags", C.c_int32),
         ("edge_mask", _fp),
+        ("max_graph_edges", C.c_int32), ("reserved0", C.c_int32),
     ]
 
 
@@ -90,6 +91,8 @@ SIGNATURES = {
     "hcg_collate": (C.c_int, [_fp, C.c_int64, _fp, C.c_int64, C.c_int64, C.c_float, _fp, C.c_float, C.c_int,
                               _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp,
                               _fp, C.c_size_t, _fp]),
+    "hcg_collate_offsets": (C.c_int, [_fp, C.c_int64, _fp, _fp, C.c_int64, C.c_int64, C.c_float, C.c_int, C.c_int32, C.c_int32,
+                                      _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, C.c_size_t, _fp]),
     "hcg_collate_status": (C.c_int, [_fp, _fp, C.POINTER(C.c_int32)]),
     "hcg_forward_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.POINTER(HcgParams)]),
     "hcg_gcn_forward": (C.c_int, [C.POINTER(HcgGraph), _fp, C.POINTER(HcgParams), _fp, _fp, C.POINTER(HcgSaved),

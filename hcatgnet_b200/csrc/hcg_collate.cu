@@ -304,6 +304,23 @@ k_edge_ptr(const int64_t* __restrict__ dst, int64_t E, int64_t N, int64_t B, con
   if (lane == 0) eptr[g] = (int32_t)lo;
 }
 
+// Offsets handed in by the caller (PyG's Batch carries them: `ptr` and `_slice_dict['edge_index']`): graph_ptr / eptr
+// are their int32 copies, clamped into range (a wrong offset is then caught by the per-edge checks of the build
+// kernels).  Without edge offsets the warp searches for its graph's slice exactly as k_edge_ptr does.
+__global__ void __launch_bounds__(256)
+k_offsets_from_ptr(const int64_t* __restrict__ node_ptr, const int64_t* __restrict__ edge_ptr, int64_t E, int64_t N, int64_t B,
+                   int32_t* __restrict__ graph_ptr, int32_t* __restrict__ eptr, int* __restrict__ status) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g == 0) { status[0] = 0; status[1] = 0; }   // (nothing else writes the status words in this kernel)
+  if (g > B) return;
+  int64_t n = node_ptr[g];
+  n = n < 0 ? 0 : (n > N ? N : n);
+  graph_ptr[g] = (int32_t)n;
+  int64_t e = edge_ptr[g];
+  e = e < 0 ? 0 : (e > E ? E : e);
+  eptr[g] = (int32_t)e;
+}
+
 // ==========================================================================================
 // Graph-local fast path (HCG_COLLATE_GROUPED).  PyG's collate concatenates the edge lists graph
 // by graph, so the edges of graph g are one contiguous slice of edge_index: find the slices
@@ -513,6 +530,7 @@ k_collate_graph_warp(const int64_t* __restrict__ src, const int64_t* __restrict_
       rowptr[N] = (int32_t)E;
       if (t_rowptr) t_rowptr[N] = (int32_t)E;
     }
+    if (n < 0 && lane == 0) atomicOr(status, kStatusBadBatch);   // offsets that do not ascend
     if (n <= 0) continue;
     if (n > kWgNodes || e_cnt > kWgEdges || e_cnt < 0 || e_lo < 0 || (int64_t)e_lo + e_cnt > E) {
       if (lane == 0) atomicAdd(big_count, 1);  // left to the block-per-graph kernel
@@ -706,6 +724,39 @@ extern "C" int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* 
   }
   k_graph_ptr<<<(unsigned)cdiv(N + 1, 256), 256, 0, st>>>(batch, N, B, graph_ptr, w.status);
   HCG_LAUNCH_OK(st, "k_graph_ptr");
+  return HCG_OK;
+}
+
+extern "C" int hcg_collate_offsets(const int64_t* edge_index, int64_t E, const int64_t* node_ptr, const int64_t* edge_ptr,
+                                   int64_t N, int64_t B, float fill, int flags, int32_t max_graph_nodes, int32_t max_graph_edges,
+                                   int32_t* rowptr, int32_t* col, int32_t* eid, float* dis, int32_t* graph_ptr,
+                                   int32_t* t_rowptr, int32_t* t_col, int32_t* t_eid, void* ws, size_t ws_bytes, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  HCG_REQUIRE(N > 0 && E > 0 && B > 0, HCG_ERR_INVALID_ARG, "hcg_collate_offsets needs N, E, B > 0");
+  HCG_REQUIRE(N < INT32_MAX && E < INT32_MAX && B < INT32_MAX, HCG_ERR_UNSUPPORTED, "sizes must fit int32");
+  HCG_REQUIRE(edge_index && node_ptr && edge_ptr && rowptr && col && eid && dis && graph_ptr && ws, HCG_ERR_INVALID_ARG, "NULL pointer");
+  const bool transpose = (flags & HCG_COLLATE_TRANSPOSE) != 0;
+  if (transpose) HCG_REQUIRE(t_rowptr && t_col && t_eid, HCG_ERR_INVALID_ARG, "NULL transposed outputs");
+  const size_t need = hcg_collate_workspace_bytes(N, E, B, flags | HCG_COLLATE_GROUPED);
+  HCG_REQUIRE(ws_bytes >= need, HCG_ERR_WORKSPACE, "collate workspace too small: %zu < %zu", ws_bytes, need);
+  CollateWs w = carve_collate(ws, N, E, B, flags);
+  note_region(st);
+  const int64_t* src = edge_index;
+  const int64_t* dst = edge_index + E;
+  k_offsets_from_ptr<<<(unsigned)cdiv(B + 1, 256), 256, 0, st>>>(node_ptr, edge_ptr, E, N, B, graph_ptr, w.eptr, w.status);
+  HCG_LAUNCH_OK(st, "k_offsets_from_ptr");
+  int64_t wb = cdiv(B, kWgWarps);
+  if (wb > (int64_t)kNumSMs * 12) wb = (int64_t)kNumSMs * 12;
+  k_collate_graph_warp<<<(unsigned)wb, kWgWarps * 32, 0, st>>>(src, dst, E, N, B, graph_ptr, w.eptr, fill, rowptr, col, eid, dis,
+                                                              transpose ? t_rowptr : nullptr, t_col, t_eid, w.status);
+  HCG_LAUNCH_OK(st, "k_collate_graph_warp");
+  // graphs the warp kernel leaves behind (above kWgNodes / kWgEdges): when the caller's hints say there are none, one
+  // CTA is enough to find that out (and to serve a wrong hint, slowly)
+  const bool none_big = max_graph_nodes > 0 && max_graph_nodes <= kWgNodes && max_graph_edges > 0 && max_graph_edges <= kWgEdges;
+  int64_t gb = none_big ? 1 : (B < (int64_t)kNumSMs * 8 ? B : (int64_t)kNumSMs * 8);
+  k_collate_graph<<<(unsigned)gb, kGrpThreads, 0, st>>>(src, dst, E, N, B, graph_ptr, w.eptr, fill, rowptr, col, eid, dis,
+                                                      transpose ? t_rowptr : nullptr, t_col, t_eid, w.status);
+  HCG_LAUNCH_OK(st, "k_collate_graph");
   return HCG_OK;
 }
 

@@ -289,7 +289,7 @@ size_t fused_fwd_smem_bytes(int F, int L, int ncap, int ecap) {
   return fl * 4;
 }
 
-int launch_fused_fwd(const FusedFwdArgs& a, size_t smem, cudaStream_t st) {
+int launch_fused_fwd(const FusedFwdArgs& a, size_t smem, cudaStream_t st, int64_t max_ctas) {
   if (a.B <= 0) return HCG_OK;
   static SmemConfigured configured;
   if (int rc = ensure_dyn_smem(k_fused_fwd, smem, configured)) return rc;
@@ -298,6 +298,7 @@ int launch_fused_fwd(const FusedFwdArgs& a, size_t smem, cudaStream_t st) {
   if (per_sm < 1) return set_err(HCG_ERR_UNSUPPORTED, "fused forward does not fit on an SM (%zu B smem)", smem);
   int64_t grid = (int64_t)kNumSMs * per_sm;
   if (grid > a.B) grid = a.B;
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
   k_fused_fwd<<<(unsigned)grid, kFusedThreads, smem, st>>>(a);
   HCG_LAUNCH_OK(st, "k_fused_fwd");
   return HCG_OK;

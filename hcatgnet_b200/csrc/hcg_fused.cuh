@@ -37,14 +37,18 @@ struct FusedFwdArgs {
 // bytes of dynamic shared memory the kernel needs for a given capacity
 size_t fused_fwd_smem_bytes(int F, int L, int ncap, int ecap);
 // launches the kernel; grid sized from the SM count and the achievable residency
-int launch_fused_fwd(const FusedFwdArgs& a, size_t smem, cudaStream_t st);
+// (max_ctas > 0 caps the grid: one CTA is enough to find an overflow list empty)
+int launch_fused_fwd(const FusedFwdArgs& a, size_t smem, cudaStream_t st, int64_t max_ctas = 0);
 
 // tensor-core graph-resident forward (hcg_tc.cu): H == 64, F <= 32
 size_t tc_fwd_smem_bytes(int F, int L);
 size_t tc_fwd_workspace_bytes(int64_t B);
+int tc_fwd_row_cap();    // tile capacity: node rows ...
+int tc_fwd_edge_cap();   // ... and CSR slots
 // `a.scratch_*`, `a.ncap/ecap` describe the FMA kernel that picks up the overflow list; ws holds
 // the per-graph descriptors and that list
-int launch_tc_fwd(const FusedFwdArgs& a, int64_t N, int64_t E, void* ws, cudaStream_t st);
+// all_fit: the caller's hints say that every graph fits a tile (the overflow pass then runs as a single CTA)
+int launch_tc_fwd(const FusedFwdArgs& a, int64_t N, int64_t E, void* ws, cudaStream_t st, bool all_fit = false);
 
 // ---- graph-resident backward (hcg_fused_bwd.cu): H == 64, two conv layers, F <= 32 ---------------
 struct FusedBwdArgs {

@@ -1215,7 +1215,9 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
       return set_err(HCG_ERR_UNSUPPORTED, "tensor-core forward needs F <= 32 and %d conv layers to fit in shared memory", p->L);
     const bool want_tc = path == 3 || (path == 0 && tc_ok && (g->max_graph_nodes == 0 || g->max_graph_nodes <= 128));
     if (want_tc) {
-      rc = launch_tc_fwd(a, N, g->E, w.tc, st);
+      const bool all_fit = g->max_graph_nodes > 0 && g->max_graph_nodes <= tc_fwd_row_cap() && g->max_graph_edges > 0 &&
+                           g->max_graph_edges <= tc_fwd_edge_cap();
+      rc = launch_tc_fwd(a, N, g->E, w.tc, st, all_fit);
       if (rc) return rc;
       fused_done = true;
     } else if (fma_fits) {

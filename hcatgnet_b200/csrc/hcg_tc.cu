@@ -755,6 +755,8 @@ k_tc_fwd(const TcArgs a) {
 }
 
 size_t tc_fwd_smem_bytes(int F, int L) { return tc_layout(F, L, 2).total; }
+int tc_fwd_row_cap() { return kTcRows; }
+int tc_fwd_edge_cap() { return kTcEcap; }
 
 }  // namespace hcg
 
@@ -826,7 +828,7 @@ static int launch_tc_variant(const TcArgs& a, int grid, size_t smem, cudaStream_
   return HCG_OK;
 }
 
-int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStream_t st) {
+int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStream_t st, bool all_fit) {
   if (f.B <= 0) return HCG_OK;
   TcWs w = carve_tc(ws, f.B);
   const int ns = tc_slots(f.F, f.L);
@@ -854,12 +856,13 @@ int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStr
   if (rc) return rc;
   HCG_LAUNCH_OK(st, "k_tc_fwd");
 
-  // graphs above the tile capacity: the FMA graph-resident kernel walks the overflow list
+  // graphs above the tile capacity: the FMA graph-resident kernel walks the overflow list.  When the caller's hints
+  // say that every graph fits, one CTA is enough to find the list empty (or to serve a wrong hint, slowly).
   FusedFwdArgs o = f;
   o.list = w.overflow_list;
   o.list_count = w.overflow_count;
   const size_t osmem = fused_fwd_smem_bytes(f.F, f.L, o.ncap, o.ecap);
-  return launch_fused_fwd(o, osmem, st);
+  return launch_fused_fwd(o, osmem, st, all_fit ? 1 : 0);
 }
 
 }  // namespace hcg

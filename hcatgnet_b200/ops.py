@@ -71,6 +71,7 @@ class GraphPlan:
     dis0: torch.Tensor | None = None
     flags: int = 0             # HCG_GRAPH_* bits reported by hcg_collate_status
     max_graph_nodes: int = 0   # hint (0 = unknown): sizes the smem capacity of the graph-resident kernel
+    max_graph_edges: int = 0   # hint (0 = unknown): edge count of the largest graph
     _keep: list = field(default_factory=list, repr=False)
 
     @property
@@ -86,13 +87,14 @@ class GraphPlan:
             self.N, self.E, self.B, _ptr(self.rowptr), _ptr(self.col), _ptr(self.eid), _ptr(self.dis),
             _ptr(self.graph_ptr), _ptr(self.t_rowptr), _ptr(self.t_col), _ptr(self.t_eid), self.fill,
             _ptr(self.ew0), _ptr(self.t_ew0), _ptr(self.selfw0), _ptr(self.dis0), int(self.max_graph_nodes), int(self.flags),
-            _ptr(edge_mask))
+            _ptr(edge_mask), int(self.max_graph_edges), 0)
 
 
 def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int, num_graphs: int,
             edge_weight: torch.Tensor | None = None, improved: bool = False, transpose: bool = False,
             fill: float = 1.0, validate: bool = True, max_graph_nodes: int = 0,
-            grouped: bool | None = None) -> GraphPlan:
+            grouped: bool | None = None, ptr: torch.Tensor | None = None, edge_ptr: torch.Tensor | None = None,
+            max_graph_edges: int = 0) -> GraphPlan:
     """COO ``edge_index`` [2,E] int64 + sorted ``batch`` [N] int64 -> :class:`GraphPlan`.
 
     Runs ``hcg_collate``.  ``improved`` only matters together with ``edge_weight`` (self-loop
@@ -103,6 +105,9 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
     graph by graph, as ``Batch.from_data_list`` / PyG's collate produce them; same outputs bit for bit):
     ``True`` = the caller vouches for it, ``None`` = try it when the status word is read back anyway
     (``validate``) and fall back to the general kernels if the device check refuses, ``False`` = never.
+    ``ptr`` / ``edge_ptr`` (int64 [B+1]: first node / first edge of every graph, as PyG's ``Batch.ptr`` and
+    ``Batch._slice_dict['edge_index']`` hold them): with both, the graph-local path takes its offsets from
+    them (``hcg_collate_offsets``) instead of deriving them from ``batch`` and searching the edge list.
     """
     device = _require_cuda() if not edge_index.is_cuda else edge_index.device
     lib = _lib.load()
@@ -116,16 +121,17 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
         raise ValueError(f"batch has {bt.numel()} entries for {N} nodes")
     if ew is not None and ew.numel() != E:
         raise ValueError(f"edge_weight has {ew.numel()} entries for {E} edges")
-    if bt is None and B > 1:
-        raise ValueError("batch vector required when num_graphs > 1")
+    if bt is None and B > 1 and (ptr is None or edge_ptr is None):
+        raise ValueError("batch vector (or ptr + edge_ptr) required when num_graphs > 1")
     i32 = dict(dtype=torch.int32, device=device)
     f32 = dict(dtype=torch.float32, device=device)
     with torch.cuda.device(device):
         plan = GraphPlan(N, E, B, torch.empty(N + 1, **i32), torch.empty(max(E, 1), **i32),
                          torch.empty(max(E, 1), **i32), torch.empty(max(N, 1), **f32), torch.empty(B + 1, **i32),
-                         fill=float(fill), max_graph_nodes=int(max_graph_nodes))
+                         fill=float(fill), max_graph_nodes=int(max_graph_nodes), max_graph_edges=int(max_graph_edges))
         flags = 0
-        use_grouped = bt is not None and ew is None and B > 0 and N > 0 and E > 0 and \
+        have_offsets = ptr is not None and edge_ptr is not None and ptr.numel() == B + 1 and edge_ptr.numel() == B + 1
+        use_grouped = (bt is not None or have_offsets) and ew is None and B > 0 and N > 0 and E > 0 and \
             (grouped is True or (grouped is None and validate))
         if use_grouped:
             flags |= _lib.HCG_COLLATE_GROUPED
@@ -142,18 +148,29 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
                 plan.t_ew0 = torch.empty(max(E, 1), **f32)
         ws = _workspace(lib.hcg_collate_workspace_bytes(N, E, B, flags), device)
         st = _stream(device)
-        _lib.check(lib.hcg_collate(
-            _ptr(ei), E, _ptr(bt), N, B, float(fill), _ptr(ew), 2.0 if improved else 1.0, flags,
-            _ptr(plan.rowptr), _ptr(plan.col), _ptr(plan.eid), _ptr(plan.dis), _ptr(plan.graph_ptr),
-            _ptr(plan.t_rowptr), _ptr(plan.t_col), _ptr(plan.t_eid),
-            _ptr(plan.ew0), _ptr(plan.t_ew0), _ptr(plan.selfw0), _ptr(plan.dis0),
-            _ptr(ws), ws.numel(), st))
+        if use_grouped and have_offsets:
+            ptr_d, eptr_d = to_device(ptr, device, torch.int64), to_device(edge_ptr, device, torch.int64)
+            _lib.check(lib.hcg_collate_offsets(
+                _ptr(ei), E, _ptr(ptr_d), _ptr(eptr_d), N, B, float(fill), flags & _lib.HCG_COLLATE_TRANSPOSE,
+                int(max_graph_nodes), int(max_graph_edges),
+                _ptr(plan.rowptr), _ptr(plan.col), _ptr(plan.eid), _ptr(plan.dis), _ptr(plan.graph_ptr),
+                _ptr(plan.t_rowptr), _ptr(plan.t_col), _ptr(plan.t_eid), _ptr(ws), ws.numel(), st))
+            plan._keep += [ptr_d, eptr_d]
+        else:
+            _lib.check(lib.hcg_collate(
+                _ptr(ei), E, _ptr(bt), N, B, float(fill), _ptr(ew), 2.0 if improved else 1.0, flags,
+                _ptr(plan.rowptr), _ptr(plan.col), _ptr(plan.eid), _ptr(plan.dis), _ptr(plan.graph_ptr),
+                _ptr(plan.t_rowptr), _ptr(plan.t_col), _ptr(plan.t_eid),
+                _ptr(plan.ew0), _ptr(plan.t_ew0), _ptr(plan.selfw0), _ptr(plan.dis0),
+                _ptr(ws), ws.numel(), st))
         if validate:
             gflags = C.c_int32(0)
             rc = lib.hcg_collate_status(_ptr(ws), st, C.byref(gflags))
             if rc == _lib.HCG_ERR_NOT_GROUPED and use_grouped:  # the device check refused the fast path
+                if bt is None and B > 1:
+                    bt = batch_from_ptr(to_device(ptr, device, torch.int64), N)
                 return collate(ei, bt, N, B, edge_weight=ew, improved=improved, transpose=transpose, fill=fill,
-                               validate=True, max_graph_nodes=max_graph_nodes, grouped=False)
+                               validate=True, max_graph_nodes=max_graph_nodes, grouped=False)   # (general kernels: no offsets)
             _lib.check(rc)
             plan.flags = int(gflags.value)
         else:
@@ -174,6 +191,15 @@ def batch_from_ptr(ptr: torch.Tensor, num_nodes: int) -> torch.Tensor:
 
 def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edge_weight=None,
                    improved=False, transpose=False, validate=True, max_graph_nodes=0, grouped=None) -> GraphPlan:
+    # graph offsets the batch object carries (ours do; so does PyG's Batch): spare hcg_collate the search for them
+    ptr, edge_ptr = getattr(holder, "ptr", None), getattr(holder, "edge_ptr", None)
+    max_graph_edges = int(getattr(holder, "max_graph_edges", 0) or 0)
+    return _cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edge_weight, improved, transpose,
+                           validate, max_graph_nodes, grouped, ptr, edge_ptr, max_graph_edges)
+
+
+def _cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edge_weight, improved, transpose, validate,
+                    max_graph_nodes, grouped, ptr, edge_ptr, max_graph_edges) -> GraphPlan:
     """``collate`` memoised on ``holder`` (the batch object the caller passed to ``forward``).
 
     The reference recomputes the normalisation inside every GCNConv call of every forward
@@ -196,7 +222,8 @@ def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edg
         plan = collate(to_device(edge_index, device, torch.int64), to_device(batch, device, torch.int64),
                        num_nodes, num_graphs, edge_weight=to_device(edge_weight, device, torch.float32),
                        improved=improved, transpose=transpose, validate=validate,
-                       max_graph_nodes=max_graph_nodes, grouped=grouped)
+                       max_graph_nodes=max_graph_nodes, grouped=grouped, ptr=ptr, edge_ptr=edge_ptr,
+                       max_graph_edges=max_graph_edges)
     if key is not None:
         try:
             object.__setattr__(holder, "_hcg_plan", (key, plan, edge_index, batch))

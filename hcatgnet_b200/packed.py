@@ -292,7 +292,7 @@ class DeviceGraphStore:
         """``ids``: sequence / numpy / CPU tensor of graph numbers (repeats allowed); None = all, in order."""
         ds, dev = self.ds, self.device
         if ids is None:
-            ids_np, n, e = None, np.diff(ds.node_ptr), np.diff(ds.edge_ptr)
+            return self._batch_all(with_batch_vector)
         else:
             ids_np = np.ascontiguousarray(np.asarray(ids, dtype=np.int64).reshape(-1))
             if ids_np.size and (ids_np.min() < 0 or ids_np.max() >= ds.G):
@@ -321,6 +321,44 @@ class DeviceGraphStore:
         out = Batch(x, ei, bvec, meta_d[0], y, idx, B, edges_grouped=True if (ds.flags & FLAG_GROUPABLE) else None)
         out.max_graph_nodes = int(n.max()) if B else 0
         out._keepalive = meta_d
+        return out
+
+
+    def _ptr_views(self):
+        """The image's own node_ptr / edge_ptr sections as device int64 tensors (no copy: views of the blob)."""
+        def view(name):
+            off, _dt, shape, nbytes = self.ds.layout[name]
+            return self.blob_dev[off:off + nbytes].view(torch.int64)
+        return view("node_ptr"), view("edge_ptr")
+
+    def _batch_all(self, with_batch_vector: bool) -> Batch:
+        """``batch(None)``: every graph of the image, in order (a wire-format chunk).  The exclusive prefix sums
+        hcg_unpack_batch needs ARE the image's node_ptr / edge_ptr sections, already on the device; sizes come
+        from the header.  Nothing is computed or allocated on the host per chunk (no pinned staging buffer, no
+        cumulative sums): the chunk costs its one PCIe copy and one kernel."""
+        ds, dev = self.ds, self.device
+        B, N_out, E_out = ds.G, ds.N, ds.E
+        node_ptr_d, edge_ptr_d = self._ptr_views()
+        x = torch.empty(N_out, ds.F, dtype=torch.float32, device=dev)
+        ei = torch.empty(2, E_out, dtype=torch.int64, device=dev)
+        bvec = torch.empty(N_out, dtype=torch.int64, device=dev) if with_batch_vector else None
+        y = torch.empty(B, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.load().hcg_unpack_batch(
+                C.byref(self.c_store), None, 0, B, node_ptr_d.data_ptr(), edge_ptr_d.data_ptr(), x.data_ptr(), ei.data_ptr(),
+                E_out, bvec.data_ptr() if bvec is not None else None, y.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+        idx = getattr(ds, "_idx_t", None)
+        if idx is None:
+            idx = torch.from_numpy(np.array(ds.idx))
+            try:
+                ds._idx_t = idx
+            except AttributeError:
+                pass
+        out = Batch(x, ei, bvec, node_ptr_d, y, idx, B, edges_grouped=True if (ds.flags & FLAG_GROUPABLE) else None)
+        out.max_graph_nodes = int(ds.max_graph_nodes)
+        out.max_graph_edges = int(ds.max_graph_edges)
+        out.edge_ptr = edge_ptr_d
+        out._keepalive = self.blob_dev
         return out
 
 

@@ -65,6 +65,8 @@ class DevicePrefetcher:
             d = Batch(mv(h.x), mv(h.edge_index), bt, ptr_d, mv(h.y), h.idx, h.num_graphs,
                       edges_grouped=getattr(h, "edges_grouped", None))
             d.max_graph_nodes = getattr(h, "max_graph_nodes", 0)
+            d.max_graph_edges = getattr(h, "max_graph_edges", 0)
+            d.edge_ptr = mv(getattr(h, "edge_ptr", None)) if ptr_d is not None else None
             ev = torch.cuda.Event()
             ev.record(self.copy_stream)
         self.queue.append((d, ev, h))
@@ -78,7 +80,7 @@ class DevicePrefetcher:
             cur = torch.cuda.current_stream(self.device)
             cur.wait_event(ev)
             store = getattr(d, "_store", None)
-            for t in (d.x, d.edge_index, d.batch, d.ptr, d.y, getattr(d, "_keepalive", None),
+            for t in (d.x, d.edge_index, d.batch, d.ptr, d.y, getattr(d, "edge_ptr", None), getattr(d, "_keepalive", None),
                       store.blob_dev if store is not None else None):
                 if t is not None and t.is_cuda:
                     t.record_stream(cur)

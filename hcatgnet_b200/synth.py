@@ -80,7 +80,9 @@ def synth_batch_numpy(num_graphs: int, n_features: int = 25, seed: int = 2023202
     elif features != "uniform":
         raise ValueError(f"unknown feature style {features!r}")
     y = (rng.standard_normal(B) * 8.0).astype(np.float32)
-    return {"x": x, "edge_index": edge_index, "batch": gid, "ptr": ptr, "y": y, "num_graphs": B}
+    edge_ptr = np.zeros(B + 1, dtype=np.int64)          # bonds are listed graph by graph: 2 directed edges per bond
+    np.cumsum(2 * np.bincount(bg, minlength=B), out=edge_ptr[1:])
+    return {"x": x, "edge_index": edge_index, "batch": gid, "ptr": ptr, "edge_ptr": edge_ptr, "y": y, "num_graphs": B}
 
 
 def synth_batch(num_graphs: int, n_features: int = 25, seed: int = 20232023, pin: bool = False, **kw) -> Batch:
@@ -88,4 +90,6 @@ def synth_batch(num_graphs: int, n_features: int = 25, seed: int = 20232023, pin
     b = Batch(torch.from_numpy(d["x"]), torch.from_numpy(d["edge_index"]), torch.from_numpy(d["batch"]),
               torch.from_numpy(d["ptr"]), torch.from_numpy(d["y"]),
               torch.arange(num_graphs, dtype=torch.int64), num_graphs, edges_grouped=True)
+    b.edge_ptr = torch.from_numpy(d["edge_ptr"])
+    b.max_graph_edges = int(np.diff(d["edge_ptr"]).max()) if num_graphs else 0
     return b.pin_memory() if pin else b

@@ -98,6 +98,9 @@ typedef struct HcgGraph {
    * (edge_mask_type='object'; reference scripts_experiments/explain_gnn.py:39-50).  Masked calls run on the
    * layer-wise kernels. */
   const float* edge_mask;
+  /* Optional hint like max_graph_nodes: directed edge count of the largest graph of the batch (0 = unknown). */
+  int32_t max_graph_edges;
+  int32_t reserved0;
 } HcgGraph;
 
 /*
@@ -210,6 +213,19 @@ int hcg_collate(const int64_t* edge_index, int64_t E, const int64_t* batch, int6
                 int32_t* t_rowptr, int32_t* t_col, int32_t* t_eid,
                 float* ew0, float* t_ew0, float* selfw0, float* dis0,
                 void* ws, size_t ws_bytes, void* stream);
+
+/*
+ * The graph-local path of hcg_collate (HCG_COLLATE_GROUPED: same preconditions, same device-side checks, same
+ * outputs bit for bit) for callers that hold the graph offsets: node_ptr int64 [B+1] (PyG `Batch.ptr`) and
+ * edge_ptr int64 [B+1] (first edge of each graph; PyG keeps it as `Batch._slice_dict['edge_index']`).  Nothing is
+ * derived from the N-entry batch vector or searched in the edge list: two kernels instead of five and two memsets.
+ * max_graph_nodes / max_graph_edges: sizes of the largest graph if known (0 = unknown); they only decide how many
+ * CTAs look for graphs the warp-per-graph kernel cannot take.  flags: HCG_COLLATE_TRANSPOSE or 0.
+ */
+int hcg_collate_offsets(const int64_t* edge_index, int64_t E, const int64_t* node_ptr, const int64_t* edge_ptr,
+                        int64_t N, int64_t B, float fill, int flags, int32_t max_graph_nodes, int32_t max_graph_edges,
+                        int32_t* rowptr, int32_t* col, int32_t* eid, float* dis, int32_t* graph_ptr,
+                        int32_t* t_rowptr, int32_t* t_col, int32_t* t_eid, void* ws, size_t ws_bytes, void* stream);
 
 /*
  * batch[i] = g for ptr[g] <= i < ptr[g+1]: rebuilds PyG's `Batch.batch` [N] from `Batch.ptr` [B+1] on the

@@ -1,4 +1,5 @@
 set -x
-nvidia-smi -L
-timeout 1500 python -m pytest tests/test_gpu_dp.py tests/test_gpu_invariance.py tests/test_gpu_module.py -q -m gpu 2>&1 | tail -8
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 30 --warmup 5 > gpurun_out/r2_bench_n2.json 2> gpurun_out/r2_bench_n2.err; tail -c 800 gpurun_out/r2_bench_n2.err
+for rep in 1 2; do
+(cd build/old_tree && timeout 600 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-profile 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('OLD infer',d['value'],'e2e',d['e2e']['value'],'packed',d['e2e_packed']['value'],'train',d['train']['value'],'train e2e',d['train']['e2e']['value'])")
+timeout 600 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-profile 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('NEW infer',d['value'],'e2e',d['e2e']['value'],'packed',d['e2e_packed']['value'],'train',d['train']['value'],'train e2e',d['train']['e2e']['value'])"
+done
