@@ -14,4 +14,11 @@ from .packed import (DeviceGraphStore, PackedDataset, StoreLoader, convert_proce
 from .screen import DevicePrefetcher, predict_ensemble_stream, predict_network_stream, predict_stream  # noqa: F401
 from .trainer import FusedTrainer  # noqa: F401
 
+
+def __getattr__(name):   # report.py needs pandas: imported on first use only
+    if name in ("write_report_csvs", "screen_ensemble_to_csv", "embeddings_frame"):
+        from . import report
+        return getattr(report, name)
+    raise AttributeError(name)
+
 __version__ = "0.1.0"

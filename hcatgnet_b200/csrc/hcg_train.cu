@@ -97,3 +97,88 @@ extern "C" int hcg_adam_step(float* param, const float* grad, float* exp_avg, fl
   HCG_LAUNCH_OK(st, "k_adam");
   return HCG_OK;
 }
+
+// ---- one whole optimisation step in ONE library call ----------------------------------------------------------
+// The reference's regime is tiny: 668 reactions in batches of 40 (reference scripts_experiments/train_GNN.py:73-111:
+// ~14 steps per epoch, ~100 epochs, 90 runs).  There a step is bound by the HOST: six C-ABI calls, ~25 tensor
+// allocations and their Python glue cost more than the ~14 kernels they launch.  hcg_train_step chains
+// collate -> forward -> loss seed -> backward -> Adam inside the library over one caller-owned workspace, so the
+// host pays for one call.  Single-rank only (with several ranks the all-reduce sits between backward and Adam:
+// use the separate entry points).
+namespace hcg {
+
+struct StepWs {
+  char* collate;
+  int32_t *rowptr, *col, *eid, *graph_ptr, *t_rowptr, *t_col, *t_eid;
+  float* dis;
+  char* fwd;
+  float* acts[HCG_MAX_CONV];
+  float* hid[HCG_MAX_READOUT];
+  float *out, *emb, *g_out;
+  char* bwd;
+  size_t collate_bytes, fwd_bytes, bwd_bytes, bytes;
+};
+
+static StepWs carve_step(void* ws, int64_t N, int64_t E, int64_t B, const HcgParams* p) {
+  Carver c(ws, (size_t)-1);
+  StepWs w{};
+  w.collate_bytes = hcg_collate_workspace_bytes(N, E, B, HCG_COLLATE_TRANSPOSE | HCG_COLLATE_GROUPED);
+  w.fwd_bytes = hcg_forward_workspace_bytes(N, E, B, p);
+  w.bwd_bytes = hcg_backward_workspace_bytes(N, E, B, p);
+  w.collate = c.take<char>(w.collate_bytes);
+  w.rowptr = c.take<int32_t>(N + 1); w.col = c.take<int32_t>(E + 1); w.eid = c.take<int32_t>(E + 1);
+  w.graph_ptr = c.take<int32_t>(B + 1);
+  w.t_rowptr = c.take<int32_t>(N + 1); w.t_col = c.take<int32_t>(E + 1); w.t_eid = c.take<int32_t>(E + 1);
+  w.dis = c.take<float>(N + 1);
+  w.fwd = c.take<char>(w.fwd_bytes);
+  for (int l = 0; l < p->L; ++l) w.acts[l] = c.take<float>((size_t)N * p->H + 4);
+  int d = 2 * p->H;
+  for (int k = 0; k < p->R - 1; ++k) { d /= 2; w.hid[k] = c.take<float>((size_t)B * d + 4); }
+  w.out = c.take<float>((size_t)B * p->C + 4);
+  w.emb = c.take<float>((size_t)B * 2 * p->H + 4);
+  w.g_out = c.take<float>((size_t)B * p->C + 4);
+  w.bwd = c.take<char>(w.bwd_bytes);
+  w.bytes = c.off;
+  return w;
+}
+
+}  // namespace hcg
+
+extern "C" size_t hcg_train_step_workspace_bytes(int64_t N, int64_t E, int64_t B, const HcgParams* p) {
+  if (!p || p->L < 1 || p->L > HCG_MAX_CONV || p->R < 1 || p->R > HCG_MAX_READOUT) return 0;
+  return carve_step(nullptr, N, E, B, p).bytes;
+}
+
+extern "C" int hcg_train_step(const float* x, const int64_t* edge_index, int64_t E, const int64_t* node_ptr,
+                              const int64_t* edge_ptr, const float* y, int64_t N, int64_t B, int32_t max_graph_nodes,
+                              int32_t max_graph_edges, float fill, const HcgParams* p, const HcgGrads* grads,
+                              float* param_slab, float* grad_slab, float* exp_avg, float* exp_avg_sq, int64_t n,
+                              double lr, double beta1, double beta2, double eps, int64_t step, float* loss_out,
+                              void* ws, size_t ws_bytes, void* stream) {
+  HCG_REQUIRE(x && edge_index && node_ptr && edge_ptr && y && p && grads && param_slab && grad_slab && exp_avg && exp_avg_sq && ws,
+              HCG_ERR_INVALID_ARG, "NULL pointer");
+  HCG_REQUIRE(N > 0 && E > 0 && B > 0 && n > 0, HCG_ERR_INVALID_ARG, "hcg_train_step needs N, E, B, n > 0");
+  HCG_REQUIRE(p->L >= 1 && p->L <= HCG_MAX_CONV && p->R >= 1 && p->R <= HCG_MAX_READOUT, HCG_ERR_UNSUPPORTED, "bad layer counts");
+  StepWs w = carve_step(ws, N, E, B, p);
+  HCG_REQUIRE(ws_bytes >= w.bytes, HCG_ERR_WORKSPACE, "train-step workspace too small: %zu < %zu", ws_bytes, w.bytes);
+  int rc = hcg_collate_offsets(edge_index, E, node_ptr, edge_ptr, N, B, fill, HCG_COLLATE_TRANSPOSE, max_graph_nodes,
+                               max_graph_edges, w.rowptr, w.col, w.eid, w.dis, w.graph_ptr, w.t_rowptr, w.t_col, w.t_eid,
+                               w.collate, w.collate_bytes, stream);
+  if (rc) return rc;
+  HcgGraph g{};
+  g.N = N; g.E = E; g.B = B;
+  g.rowptr = w.rowptr; g.col = w.col; g.eid = w.eid; g.dis = w.dis; g.graph_ptr = w.graph_ptr;
+  g.t_rowptr = w.t_rowptr; g.t_col = w.t_col; g.t_eid = w.t_eid;
+  g.fill = fill; g.max_graph_nodes = max_graph_nodes; g.max_graph_edges = max_graph_edges;
+  HcgSaved saved{};
+  for (int l = 0; l < p->L; ++l) saved.acts[l] = w.acts[l];
+  for (int k = 0; k < p->R - 1; ++k) saved.hid[k] = w.hid[k];
+  rc = hcg_gcn_forward(&g, x, p, w.out, w.emb, &saved, w.fwd, w.fwd_bytes, stream);
+  if (rc) return rc;
+  float* tail = grad_slab + n;
+  rc = hcg_rmse_seed(w.out, y, B, p->C, w.g_out, tail, stream);
+  if (rc) return rc;
+  rc = hcg_gcn_backward(&g, x, p, &saved, w.emb, w.g_out, nullptr, grads, nullptr, w.bwd, w.bwd_bytes, stream);
+  if (rc) return rc;
+  return hcg_adam_step(param_slab, grad_slab, exp_avg, exp_avg_sq, n, tail, lr, beta1, beta2, eps, step, loss_out, stream);
+}

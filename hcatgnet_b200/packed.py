@@ -308,6 +308,13 @@ class DeviceGraphStore:
         m[2, :B] = ids_np if ids_np is not None else 0
         N_out, E_out = int(m[0, B]), int(m[1, B])
         meta_d = meta.to(dev, non_blocking=True)
+        return self._assemble(meta_d, ids_np, B, N_out, E_out, int(n.max()) if B else 0, int(e.max()) if B else 0,
+                              with_batch_vector)
+
+    def _assemble(self, meta_d, ids_np, B, N_out, E_out, nmax, emax, with_batch_vector=True) -> Batch:
+        """The device half of ``batch(ids)``: ``meta_d`` int64 [3, B+1] on the device = (node offsets, edge offsets,
+        graph ids) of the selection.  One hcg_unpack_batch launch."""
+        ds, dev = self.ds, self.device
         x = torch.empty(N_out, ds.F, dtype=torch.float32, device=dev)
         ei = torch.empty(2, E_out, dtype=torch.int64, device=dev)
         bvec = torch.empty(N_out, dtype=torch.int64, device=dev) if with_batch_vector else None
@@ -319,9 +326,37 @@ class DeviceGraphStore:
                 bvec.data_ptr() if bvec is not None else None, y.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
         idx = torch.from_numpy(ds.idx[ids_np].copy() if ids_np is not None else np.array(ds.idx))
         out = Batch(x, ei, bvec, meta_d[0], y, idx, B, edges_grouped=True if (ds.flags & FLAG_GROUPABLE) else None)
-        out.max_graph_nodes = int(n.max()) if B else 0
+        out.max_graph_nodes, out.max_graph_edges = nmax, emax
+        out.edge_ptr = meta_d[1]
         out._keepalive = meta_d
         return out
+
+    def epoch_batches(self, order, batch_size: int):
+        """All mini-batches of one pass over ``order`` (graph ids, already shuffled): the offset / id tables of
+        EVERY batch are built in one go and cross PCIe as one pinned copy; per batch only views are sliced and one
+        kernel is launched.  (The reference's DataLoader does this work in Python per batch, reference
+        call_methods.py:41-46.)"""
+        ds, dev = self.ds, self.device
+        order = np.ascontiguousarray(np.asarray(order, dtype=np.int64).reshape(-1))
+        if order.size and (order.min() < 0 or order.max() >= ds.G):
+            raise IndexError(f"graph id out of range [0, {ds.G})")
+        n = ds.node_ptr[order + 1] - ds.node_ptr[order]
+        e = ds.edge_ptr[order + 1] - ds.edge_ptr[order]
+        starts = list(range(0, order.size, batch_size))
+        width = batch_size + 1
+        meta = torch.zeros(len(starts), 3, width, dtype=torch.int64, pin_memory=dev.type == "cuda")
+        m = meta.numpy()
+        sizes = []
+        for k, s0 in enumerate(starts):
+            B = min(batch_size, order.size - s0)
+            np.cumsum(n[s0:s0 + B], out=m[k, 0, 1:B + 1])
+            np.cumsum(e[s0:s0 + B], out=m[k, 1, 1:B + 1])
+            m[k, 2, :B] = order[s0:s0 + B]
+            sizes.append((B, int(m[k, 0, B]), int(m[k, 1, B]), int(n[s0:s0 + B].max()), int(e[s0:s0 + B].max())))
+        meta_d = meta.to(dev, non_blocking=True)
+        for k, s0 in enumerate(starts):
+            B, N_out, E_out, nmax, emax = sizes[k]
+            yield self._assemble(meta_d[k, :, :B + 1], order[s0:s0 + B], B, N_out, E_out, nmax, emax)   # (rows stay contiguous)
 
 
     def _ptr_views(self):
@@ -390,8 +425,7 @@ class StoreLoader:
         if self.shuffle:
             random.shuffle(order)
         kept = []
-        for s in range(0, len(order), self.batch_size):
-            b = self.store.batch(order[s:s + self.batch_size])
+        for b in self.store.epoch_batches(order, self.batch_size):
             if self.cache:
                 kept.append(b)
             yield b

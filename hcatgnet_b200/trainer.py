@@ -57,6 +57,7 @@ class FusedTrainer:
         self.steps = 0
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.timing = None      # bench.py: a list here collects (start, end) CUDA events around every all-reduce
+        self._pstruct = self._gstruct = self._ws = None   # hcg_train_step: cached parameter / gradient tables, workspace
 
     def _bind(self):
         """(Re-)point the module's parameters at views of the flat slab.  ``model.to(...)`` / ``load_state_dict``
@@ -132,8 +133,55 @@ class FusedTrainer:
                                          float(b2), float(pg["eps"]), self.steps, loss.data_ptr(), st))
         return loss
 
+    def _step_one_call(self, batch, x, y, ptr, edge_ptr) -> torch.Tensor:
+        """``hcg_train_step``: the whole step in one library call over a persistent workspace (single rank)."""
+        lib = _lib.load()
+        dev = self.device
+        ei = batch.edge_index
+        N, E, B = int(x.shape[0]), int(ei.shape[1]), int(batch.num_graphs)
+        if self._pstruct is None:
+            params = [p.data for p in self.params]
+            self._pstruct = ops._params_struct(self.dims, params)
+            gc, off = _lib.HcgGrads(), 0
+            ptrs = []
+            for p_ in params:
+                ptrs.append(self.grad.data_ptr() + 4 * off)
+                off += p_.numel()
+            L, R = self.dims.L, self.dims.R
+            for l in range(L):
+                gc.conv_w[l], gc.conv_b[l] = ptrs[2 * l], ptrs[2 * l + 1]
+            for k in range(R):
+                gc.ro_w[k], gc.ro_b[k] = ptrs[2 * L + 2 * k], ptrs[2 * L + 2 * k + 1]
+            self._gstruct = gc
+        import ctypes as C
+        need = int(lib.hcg_train_step_workspace_bytes(N, E, B, C.byref(self._pstruct)))
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(int(need * 1.25) + 256, dtype=torch.uint8, device=dev)
+        pg = self.model.optimizer.param_groups[0]
+        b1, b2 = pg["betas"]
+        self.steps += 1
+        loss = self.losses[self.steps % 16]
+        with torch.cuda.device(dev):
+            _lib.check(lib.hcg_train_step(
+                x.data_ptr(), ei.data_ptr(), E, ptr.data_ptr(), edge_ptr.data_ptr(), y.data_ptr(), N, B,
+                int(getattr(batch, "max_graph_nodes", 0) or 0), int(getattr(batch, "max_graph_edges", 0) or 0), 1.0,
+                C.byref(self._pstruct), C.byref(self._gstruct), self.flat.data_ptr(), self.grad.data_ptr(),
+                self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.n, float(pg["lr"]), float(b1), float(b2),
+                float(pg["eps"]), self.steps, loss.data_ptr(), self._ws.data_ptr(), self._ws.numel(),
+                torch.cuda.current_stream(dev).cuda_stream))
+        return loss
+
     def step(self, batch) -> torch.Tensor:
         """One optimisation step on ``batch`` (a device ``Batch``); returns the global RMSE (device scalar)."""
+        if self.world == 1 and not self.validate and getattr(batch, "edges_grouped", None) is True:
+            ptr, eptr, x, y, ei = batch.ptr, getattr(batch, "edge_ptr", None), batch.x, batch.y, batch.edge_index
+            dev = self.device
+            if all(t is not None and t.device == dev and t.is_contiguous() for t in (ptr, eptr, x, y, ei)) and \
+                    x.dtype == torch.float32 and y.dtype == torch.float32 and ei.dtype == torch.int64 and \
+                    ptr.dtype == torch.int64 and eptr.dtype == torch.int64 and ei.shape[1] > 0 and x.shape[0] > 0:
+                if any(p.data_ptr() != self.flat.data_ptr() + 4 * o for p, o in zip(self.params, self._offsets)):
+                    self._bind()
+                return self._step_one_call(batch, x, y, ptr, eptr)
         self.accumulate(batch)
         self.reduce()
         return self.apply()
@@ -152,7 +200,7 @@ class FusedTrainer:
         n = 0
         for batch in train_loader:
             batch = batch.to(dev)
-            acc += self.step(batch) * float(batch.num_graphs)
+            acc.add_(self.step(batch), alpha=float(batch.num_graphs))
             n += int(batch.num_graphs)
         total = len(train_loader.dataset) if hasattr(train_loader, "dataset") else n
         return float(acc.item()) / max(total, 1)
@@ -187,9 +235,11 @@ class FusedTrainer:
         m = self.model
         hist = {"train": [], "val": [], "test": [], "best_epoch": 0, "best_val": float("inf"), "best_state_dict": None}
         strikes = 0
+        hist["epochs_run"] = 0
         for epoch in range(epochs):
             if strikes > early_stopping:
                 break
+            hist["epochs_run"] = epoch + 1
             train_loss = self.train_network(train_loader)
             val_loss = self.eval_network(val_loader)
             test_loss = self.eval_network(test_loader) if test_loader is not None else float("nan")

@@ -316,6 +316,20 @@ int hcg_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
                   const float* tail, double lr, double beta1, double beta2, double eps, int64_t step,
                   float* loss_out, void* stream);
 
+/*
+ * One whole optimisation step of the reference's train loop (utils/utils_model.py:60-66) in ONE call: collate
+ * (hcg_collate_offsets with the transposed CSR) -> forward -> hcg_rmse_seed -> backward -> hcg_adam_step, over one
+ * caller-owned workspace (hcg_train_step_workspace_bytes).  For the reference's own regime (batches of 40 reactions)
+ * the step is bound by the host's per-call cost, not by the kernels.  `p` / `grads` point into `param_slab` /
+ * `grad_slab` (n floats + the [SSE, count] tail).  Single rank; preconditions of the graph-local collate apply.
+ */
+size_t hcg_train_step_workspace_bytes(int64_t N, int64_t E, int64_t B, const HcgParams* p);
+int hcg_train_step(const float* x, const int64_t* edge_index, int64_t E, const int64_t* node_ptr, const int64_t* edge_ptr,
+                   const float* y, int64_t N, int64_t B, int32_t max_graph_nodes, int32_t max_graph_edges, float fill,
+                   const HcgParams* p, const HcgGrads* grads, float* param_slab, float* grad_slab, float* exp_avg,
+                   float* exp_avg_sq, int64_t n, double lr, double beta1, double beta2, double eps, int64_t step,
+                   float* loss_out, void* ws, size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -388,3 +388,32 @@ def test_explain_model_on_two_different_graphs_back_to_back(pkg):
             assert float((out - o_ref).abs().max()) <= 1e-5 * max(1.0, float(o_ref.abs().max()))
             checked += 1
     assert checked >= 4
+
+
+def test_report_csvs_reproduce_the_reference_files(pkg, tmp_path):
+    """embeddings.csv / predictions_test_set.csv written through the CUDA path: same columns as the reference's
+    network_report (utils/utils_model.py:199-205) and the same numbers as the shipped files (the golden fixture IS the
+    reference's embeddings.csv of this run), row for row."""
+    import pandas as pd
+    sd, rows = golden_io.load_model("final_test", 1, 2)
+    model = pkg.make_network("GCN", pkg.default_options(), 25)
+    model.load_state_dict(sd, strict=True)
+    model = model.to("cuda").eval()
+    learn, final = golden_io.graphs_by_idx("rhcaa_learning"), golden_io.graphs_by_idx("rhcaa_final_test")
+    sets = {"training": [], "val": [], "test": []}
+    for r in range(len(rows["index"])):
+        name = str(rows["set"][r])
+        sets[name].append((final if name == "test" else learn)[int(rows["index"][r])])
+    loaders = [pkg.DataLoader(sets[k], batch_size=40) for k in ("training", "val", "test")]
+    pkg.write_report_csvs(str(tmp_path), model, loaders)
+    emb = pd.read_csv(tmp_path / "embeddings.csv", index_col=0)
+    assert list(emb.columns) == [str(i) for i in range(128)] + ["ddG_exp", "ddG_pred", "index", "set"]
+    assert len(emb) == len(rows["index"]) and list(emb["set"]) == [str(v) for v in rows["set"]]
+    assert np.array_equal(emb["index"].to_numpy(), rows["index"])
+    assert np.abs(emb[[str(i) for i in range(128)]].to_numpy() - rows["emb"]).max() <= 1e-5 * max(1.0, np.abs(rows["emb"]).max())
+    assert np.abs(emb["ddG_pred"].to_numpy() - rows["ddG_pred"]).max() <= 2e-5
+    pred = pd.read_csv(tmp_path / "predictions_test_set.csv", index_col=0)
+    assert list(pred.columns) == ["real_ddG", "predicted_ddG", "index"] and len(pred) == len(sets["test"])
+    ens = pkg.screen_ensemble_to_csv(str(tmp_path / "screen"), [model, model], pkg.DataLoader(sets["test"], batch_size=16))
+    assert np.allclose(ens["mean_predicted_ddG"].to_numpy(), pred["predicted_ddG"].to_numpy(), atol=1e-6)
+    assert float(ens["std_predicted_ddG"].abs().max()) == 0.0
