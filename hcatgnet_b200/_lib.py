@@ -83,6 +83,7 @@ SIGNATURES = {
     "hcg_config_set": (C.c_int, [C.c_int, C.c_int]),
     "hcg_config_get": (C.c_int, [C.c_int]),
     "hcg_selftest_tc_gemm": (C.c_int, [_fp, _fp, C.c_int, _fp, _fp]),
+    "hcg_selftest_tc_xty": (C.c_int, [_fp, _fp, C.c_int, _fp, _fp]),
     "hcg_sizeof_graph": (C.c_size_t, []),
     "hcg_sizeof_params": (C.c_size_t, []),
     "hcg_sizeof_grads": (C.c_size_t, []),

@@ -65,6 +65,9 @@ struct FusedBwdArgs {
   float* scratch;                 // 3 planes of [(N + 16 B + 16), 64] for graphs above the smem capacity
   int64_t scratch_stride;         // floats between the planes (set by launch_fused_bwd)
   float* partial;                 // [grid][64*64 + 64*F + 128] per-CTA partial parameter gradients
+  const int* only;                // optional per-graph flags: only graphs with only[g] != 0 are processed (the tensor-core
+  const int* only_count;          // kernel's overflow graphs; a fixed graph -> CTA assignment keeps the sums reproducible) ...
+                                  // ... and their number (device-resident): 0 = nothing to do
   int64_t B;
   int F;
   float slope, fill;
@@ -73,6 +76,15 @@ int fused_bwd_grid(int64_t B);
 size_t fused_bwd_partial_elems(int64_t B, int F);
 size_t fused_bwd_scratch_elems(int64_t N, int64_t B);
 // writes g_w2 [64,64], g_w1 [64,F], g_b2 [64], g_b1 [64]
-int launch_fused_bwd(FusedBwdArgs a, int64_t N, float* g_w2, float* g_w1, float* g_b2, float* g_b1, cudaStream_t st);
+// max_ctas > 0 caps the grid; the reduce kernel sums `extra_rows` rows starting at reduce_base (the tensor-core kernel's
+// partials, reduce_base + extra_rows * row == a.partial) followed by this kernel's own rows
+int launch_fused_bwd(FusedBwdArgs a, int64_t N, float* g_w2, float* g_w1, float* g_b2, float* g_b1, cudaStream_t st,
+                     int max_ctas = 0, const float* reduce_base = nullptr, int extra_rows = 0);
+
+// ---- tensor-core graph-resident backward (hcg_tc_bwd.cu): same contract, tiles of one or two graphs ----------------
+int tc_bwd_grid(int64_t B);
+size_t tc_bwd_workspace_bytes(int64_t B);
+int launch_tc_bwd(FusedBwdArgs a, int64_t N, int64_t E, void* ws, bool all_fit, float* g_w2, float* g_w1, float* g_b2, float* g_b1,
+                  cudaStream_t st);
 
 }  // namespace hcg

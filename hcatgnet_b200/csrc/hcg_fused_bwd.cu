@@ -220,7 +220,9 @@ k_fused_bwd(const FusedBwdArgs a) {
   for (int idx = tid; idx < 3 * kBwdNcap * 64; idx += kBwdThreads) smem_b[idx] = 0.f;
   __syncthreads();
 
-  for (int64_t gid = blockIdx.x; gid < a.B; gid += gridDim.x) {
+  const int64_t total = (a.only && *a.only_count == 0) ? 0 : a.B;
+  for (int64_t gid = blockIdx.x; gid < total; gid += gridDim.x) {
+    if (a.only && a.only[gid] == 0) continue;  // block-uniform
     const int n0 = a.graph_ptr[gid];
     const int n = a.graph_ptr[gid + 1] - n0;
     if (n <= 0) continue;  // block-uniform
@@ -307,21 +309,26 @@ int fused_bwd_grid(int64_t B) {
   return (int)(grid < B ? grid : (B > 0 ? B : 1));
 }
 
-size_t fused_bwd_partial_elems(int64_t B, int F) { return (size_t)fused_bwd_grid(B) * (size_t)(64 * 64 + 64 * F + 128); }
+size_t fused_bwd_partial_elems(int64_t B, int F) {
+  return (size_t)(fused_bwd_grid(B) + tc_bwd_grid(B)) * (size_t)(64 * 64 + 64 * F + 128);   // + the tensor-core kernel's rows
+}
 
 size_t fused_bwd_scratch_elems(int64_t N, int64_t B) { return 3 * (size_t)(N + kBwdSlack * B + kBwdSlack) * 64; }
 
-int launch_fused_bwd(FusedBwdArgs a, int64_t N, float* g_w2, float* g_w1, float* g_b2, float* g_b1, cudaStream_t st) {
+int launch_fused_bwd(FusedBwdArgs a, int64_t N, float* g_w2, float* g_w1, float* g_b2, float* g_b1, cudaStream_t st,
+                     int max_ctas, const float* reduce_base, int extra_rows) {
   if (a.B <= 0) return HCG_OK;
   const size_t smem = fused_bwd_smem_bytes();
   static SmemConfigured configured;
   if (int rc = ensure_dyn_smem(k_fused_bwd, smem, configured)) return rc;
   a.scratch_stride = (int64_t)(N + kBwdSlack * a.B + kBwdSlack) * 64;
-  const int grid = fused_bwd_grid(a.B);
+  int grid = fused_bwd_grid(a.B);
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
   k_fused_bwd<<<grid, kBwdThreads, smem, st>>>(a);
   HCG_LAUNCH_OK(st, "k_fused_bwd");
   const int pe = 64 * 64 + 64 * a.F + 128;
-  k_fused_bwd_reduce<<<(unsigned)cdiv(pe, 256), 256, 0, st>>>(a.partial, grid, a.F, g_w2, g_w1, g_b2, g_b1);
+  k_fused_bwd_reduce<<<(unsigned)cdiv(pe, 256), 256, 0, st>>>(reduce_base ? reduce_base : a.partial, grid + extra_rows, a.F, g_w2,
+                                                             g_w1, g_b2, g_b1);
   HCG_LAUNCH_OK(st, "k_fused_bwd_reduce");
   return HCG_OK;
 }

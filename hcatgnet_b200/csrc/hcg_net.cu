@@ -1099,6 +1099,7 @@ static FwdWs carve_fwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
 }
 
 struct BwdWs {
+  char* tcb;                   // tensor-core graph-resident backward: tile work list
   float *gA, *gT, *partial, *gz[2], *gemb;
   float *fpartial, *fscratch;  // graph-resident backward: per-CTA partials, oversize-graph scratch
   float *ropartial;            // fused readout backward: per-block partials
@@ -1121,6 +1122,7 @@ static BwdWs carve_bwd(void* ws, int64_t N, int64_t B, const HcgParams* p) {
   if (fshape) {
     w.fscratch = c.take<float>(fused_bwd_scratch_elems(N, B) + 4);
     w.fpartial = c.take<float>(fused_bwd_partial_elems(B, p->F) + 4);
+    w.tcb = c.take<char>(tc_bwd_workspace_bytes(B));
     w.gA = w.fscratch;
     w.gT = w.fscratch + (size_t)N * p->H + 64;
   } else {
@@ -1360,7 +1362,7 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
   {
     const int bpath = config_get(HCG_CFG_BACKWARD_PATH);
     const bool ok = fused_bwd_shape_ok(g, p) && g_x == nullptr && w.fscratch != nullptr;
-    if (bpath == 2 && !ok)
+    if ((bpath == 2 || bpath == 3) && !ok)
       return set_err(HCG_ERR_UNSUPPORTED, "graph-resident backward needs H == %d, L == 2, F <= 32, no edge weights, a disjoint batch and g_x == NULL", kFusedH);
     if (ok && bpath != 1) {
       FusedBwdArgs a{};
@@ -1368,6 +1370,12 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
       a.x = x; a.h1 = saved->acts[0]; a.h2 = saved->acts[1]; a.emb = emb; a.gemb = gemb_total;
       a.w2 = p->conv_w[1]; a.scratch = w.fscratch; a.partial = w.fpartial;
       a.B = B; a.F = p->F; a.slope = p->slope; a.fill = g->fill;
+      // bpath 3 = the mma.sync kernel only; otherwise the tcgen05 kernel takes every graph that fits a tile
+      if (bpath != 3 && w.tcb != nullptr) {
+        const bool all_fit = g->max_graph_nodes > 0 && g->max_graph_nodes <= tc_fwd_row_cap() && g->max_graph_edges > 0 &&
+                             g->max_graph_edges <= tc_fwd_edge_cap();
+        return launch_tc_bwd(a, N, g->E, w.tcb, all_fit, grads->conv_w[1], grads->conv_w[0], grads->conv_b[1], grads->conv_b[0], st);
+      }
       return launch_fused_bwd(a, N, grads->conv_w[1], grads->conv_w[0], grads->conv_b[1], grads->conv_b[0], st);
     }
   }

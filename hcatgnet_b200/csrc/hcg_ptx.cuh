@@ -123,6 +123,15 @@ __device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, ui
       "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// both operands from shared memory through matrix descriptors
+__device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // all MMAs issued so far by this thread -> one arrival on `bar` when they have completed
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -142,10 +151,31 @@ __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
   return d;
 }
 
+// Shared-memory matrix descriptor of an MN-major TF32 operand (the M / N index is the contiguous one).  For 32-bit
+// elements the only MN-major layout is "128-byte swizzle with 32-byte base" (layout type 1): atoms of 32 MN-elements
+// (128 bytes) x 4 K-rows = 512 bytes, the 32-byte unit index of a row XORed with (K-row & 3); leading byte offset =
+// distance between atoms along MN, stride byte offset = distance between atoms along K (two of them per K = 8 MMA).
+// (CUTLASS cute/atom/mma_traits_sm100.hpp: Layout_MN_SW128_32B_Atom = Swizzle<2,5,2> o (1024 bits, 4):(1, 1024 bits);
+//  cutlass/gemm/collective/builders/sm100_common.inl:92 "for mn-major tf32 operands, SW128_32B is the only available
+//  smem layout".)
+__device__ __forceinline__ uint64_t make_mnmajor_tf32_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3fff);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3fff) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3fff) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(1) << 61;   // SWIZZLE_128B_BASE32B
+  return d;
+}
+
 // Instruction descriptor: D = F32 (bits [4,6) = 1), A = B = TF32 (bits [7,10) = [10,13) = 2), both
 // K-major (bits 15, 16 = 0), N >> 3 at [17,23), M >> 4 at [24,29)
 __host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N) {
   return (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
+}
+// the same with MN-major operands: bit 15 = A is MN-major, bit 16 = B is MN-major
+__host__ __device__ constexpr uint32_t make_idesc_tf32_mn(int M, int N, bool a_mn, bool b_mn) {
+  return make_idesc_tf32(M, N) | (a_mn ? (1u << 15) : 0u) | (b_mn ? (1u << 16) : 0u);
 }
 
 }  // namespace ptx

@@ -3,6 +3,8 @@
 #include "hcg_common.cuh"
 #include "hcg_fused.cuh"
 #include "hcg_tc.cuh"
+#include "hcg_tcbwd_blocks.cuh"
+#include "hcg_tc_tiles.cuh"
 #include <stdlib.h>
 
 namespace hcg {
@@ -60,9 +62,75 @@ k_tc_selftest(const float* __restrict__ A, const float* __restrict__ W, int K, f
   if (warp == 0) ptx::tmem_dealloc(tbase, 256);
 }
 
+// ---- self-test: G[64, 64] = X[128, 64]^T . Y[128, 64] (the node index is the reduction index) through MN-major
+//      shared-memory operands; rows >= K of X and Y are zero ------------------------------------------------------
+__global__ void __launch_bounds__(128, 1)
+k_tc_selftest_xty(const float* __restrict__ X, const float* __restrict__ Y, int K, float* __restrict__ G) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  __shared__ uint64_t bar_mma;
+  __shared__ uint32_t tmem_base_s;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  float* base = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // X hi | X lo | (two junk planes = the Y tiles below serve as the A operand's atoms 2, 3) ... keep it simple:
+  float* x_hi = base;                          // 2 planes
+  float* pad = x_hi + 2 * tcb::kPlaneFloats;   // 2 planes read as atoms 2, 3 of X hi (zeroed)
+  float* x_lo = pad + 2 * tcb::kPlaneFloats;
+  float* pad2 = x_lo + 2 * tcb::kPlaneFloats;  // atoms 2, 3 of X lo (zeroed)
+  float* y_hi = pad2 + 2 * tcb::kPlaneFloats;
+  float* y_lo = y_hi + 2 * tcb::kPlaneFloats;
+  if (warp == 0) ptx::tmem_alloc(&tmem_base_s, 64);
+  if (tid == 0) {
+    ptx::mbar_init(&bar_mma, 1);
+    ptx::fence_mbar_init();
+  }
+  for (int idx = tid; idx < 128 * 64; idx += 128) {
+    const int r = idx >> 6, c = idx & 63;
+    const float xv = r < K ? X[idx] : 0.f, yv = r < K ? Y[idx] : 0.f;
+    const int o = tcb::plane_off(r, c);
+    x_hi[o] = xv; x_lo[o] = xv - tcb::tf32_trunc(xv);
+    y_hi[o] = yv; y_lo[o] = yv - tcb::tf32_trunc(yv);
+    pad[o] = 0.f; pad2[o] = 0.f;
+  }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  ptx::tc_fence_after_sync();
+  const uint32_t d_t = tmem_base_s;
+  if (tid == 0) {
+    tcb::issue_xty<64>(d_t, ptx::smem_u32(x_hi), ptx::smem_u32(x_lo), ptx::smem_u32(y_hi), ptx::smem_u32(y_lo), 16, 0u);
+    ptx::mma_commit(&bar_mma);
+  }
+  ptx::mbar_wait(&bar_mma, 0);
+  ptx::tc_fence_after_sync();
+  const uint32_t trow = (uint32_t)(warp * 32) << 16;
+  for (int c0 = 0; c0 < 64; c0 += 16) {
+    float r[16];
+    tc::load_acc16(d_t, trow, c0, r);
+    if (tid < 64) {
+#pragma unroll
+      for (int q = 0; q < 16; ++q) G[tid * 64 + c0 + q] = r[q];
+    }
+  }
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) ptx::tmem_dealloc(tmem_base_s, 64);
+}
+
 }  // namespace hcg
 
 using namespace hcg;
+
+extern "C" int hcg_selftest_tc_xty(const float* X, const float* Y, int K, float* G, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  HCG_REQUIRE(X && Y && G, HCG_ERR_INVALID_ARG, "NULL pointer");
+  HCG_REQUIRE(K >= 1 && K <= 128, HCG_ERR_UNSUPPORTED, "K=%d outside [1,128]", K);
+  const size_t smem = 12 * (size_t)tcb::kPlaneBytes + 1024;
+  static SmemConfigured configured;
+  if (int rc = ensure_dyn_smem(k_tc_selftest_xty, smem, configured)) return rc;
+  k_tc_selftest_xty<<<1, 128, smem, st>>>(X, Y, K, G);
+  HCG_LAUNCH_OK(st, "k_tc_selftest_xty");
+  return HCG_OK;
+}
 
 extern "C" int hcg_selftest_tc_gemm(const float* A, const float* W, int K, float* D, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -113,28 +181,6 @@ namespace hcg {
 
 constexpr int kTcDefaultSlots = 2;    // tile pipelines per CTA (HCG_TC_SLOTS=3 selects the three-slot variant: measured slower,
                                       // 441 vs 398 us per 16384-graph batch - the kernel is bound by shared-memory throughput, not by latency)
-constexpr int kTcRows = 128;          // node rows per tile
-constexpr int kTcEcap = 512;          // CSR slots per tile (4 per node row: molecules)
-constexpr int kTcHPitch = 68;         // floats per activation row: 8 consecutive rows cover all banks for 128-bit access
-constexpr int kTcWinMax = 8;          // graphs per pairing window (at most)
-constexpr int kStatusCrossEdgeTc = 4;
-constexpr int kTileManual = 1;        // TcTile.flags: a 16-byte granular copy window would leave an input array
-
-struct __align__(16) TcTile {   // 64 bytes: one tile of the work list
-  int gA, n0A, nA, e0A;         // first graph: id, first node, nodes, first CSR slot
-  int gB, n0B, nB, e0B;         // second graph (gB < 0: none)
-  int eA, eB, flags, pad0;
-  int pad1[4];
-};
-
-struct __align__(16) TcMeta {   // a tile as the slot's threads see it
-  int gA, n0A, nA, e0A;
-  int gB, n0B, nB, e0B;
-  int eA, eB, flags, pad0;
-  int off[8];                   // [4 gb + q]: word offset, inside stage array q (0 x, 1 rowptr, 2 col, 3 dis),
-                                // of element 0 of graph gb's slice
-};
-
 struct TcArgs {
   FusedFwdArgs f;
   const TcTile* tiles;      // [nslots][cap] dense per-slot work lists
@@ -142,13 +188,6 @@ struct TcArgs {
   int cap;
   int64_t N, E;
 };
-
-// The 16-byte granular window [lo, lo + bytes) the bulk copy of `count` 4-byte elements at `p` reads.
-__host__ __device__ __forceinline__ void copy_window(uintptr_t p, int count, uintptr_t* lo, uint32_t* bytes, int* lead) {
-  *lo = p & ~uintptr_t(15);
-  *lead = (int)((p - *lo) >> 2);
-  *bytes = (uint32_t)(((p - *lo) + (uintptr_t)count * 4 + 15) & ~uintptr_t(15));
-}
 
 // ---- work list ----------------------------------------------------------------------------------
 // A warp per slot of the forward kernel; lane w takes the w-th window of W consecutive graphs that the slot
@@ -160,7 +199,7 @@ __global__ void __launch_bounds__(128)
 k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
             const float* __restrict__ dis, const float* __restrict__ x, int F, int64_t N, int64_t E, int64_t B, int W,
             int nslots, int nwin, int cap, TcTile* __restrict__ tiles, int* __restrict__ counts,
-            int* __restrict__ overflow_count, int* __restrict__ overflow_list) {
+            int* __restrict__ overflow_count, int* __restrict__ overflow_list, int* __restrict__ overflow_flag) {
   const int slot = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   const int lane = threadIdx.x & 31;
   if (slot >= nslots) return;  // whole warps leave together
@@ -183,7 +222,9 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
     for (int k = 0; k < kTcWinMax; ++k) {
       const int n = gp[k + 1] - gp[k], e = ee[k + 1] - ee[k];
       if (k >= wcnt) { used |= 1u << k; continue; }
-      if (n <= 0 || e <= 0 || n > kTcRows || e > kTcEcap) {
+      const bool over = n <= 0 || e <= 0 || n > kTcRows || e > kTcEcap;
+      if (overflow_flag) overflow_flag[g0 + k] = over ? 1 : 0;   // (a per-graph flag: an order that does not depend on timing)
+      if (over) {
         used |= 1u << k;
         overflow_list[atomicAdd(overflow_count, 1)] = (int)(g0 + k);
         continue;
@@ -287,7 +328,7 @@ __host__ __device__ inline TcSmemLayout tc_layout(int F, int L, int nslots) {
 
 #ifdef HCG_TC_TIMING
 __device__ unsigned long long g_tc_timing[16];
-#define TC_TICK(slot_) do { if (tid == 0) { long long t_ = clock64(); g_tc_timing[slot_] += (unsigned long long)(t_ - t_prev); t_prev = t_; } } while (0)
+#define TC_TICK(slot_) do { if (tid == 0 && blockIdx.x == 0) { long long t_ = clock64(); g_tc_timing[slot_] += (unsigned long long)(t_ - t_prev); t_prev = t_; } } while (0)
 #else
 #define TC_TICK(slot_) do { } while (0)
 #endif
@@ -762,11 +803,7 @@ int tc_fwd_edge_cap() { return kTcEcap; }
 
 namespace hcg {
 
-struct TcPlan {     // launch geometry of the work list for a batch of B graphs
-  int grid, nslots, W, nwin, cap;
-};
-
-static TcPlan tc_plan(int64_t B, int ns) {
+TcPlan tc_plan(int64_t B, int ns) {
   TcPlan p{};
   int64_t grid = cdiv(B, ns);
   if (grid > kNumSMs) grid = kNumSMs;
@@ -784,6 +821,27 @@ static TcPlan tc_plan(int64_t B, int ns) {
   return p;
 }
 
+size_t tc_tiles_capacity(int64_t B) {
+  size_t best = 0;
+  for (int ns = 1; ns <= 3; ++ns) {
+    const TcPlan p = tc_plan(B, ns);
+    const size_t t = (size_t)p.nslots * p.cap;
+    best = t > best ? t : best;
+  }
+  return best + 1;
+}
+
+int launch_tile_desc(const int32_t* graph_ptr, const int32_t* rowptr, const int32_t* col, const float* dis, const float* x, int F,
+                     int64_t N, int64_t E, int64_t B, const TcPlan& p, TcTile* tiles, int* counts, int* overflow_count,
+                     int* overflow_list, cudaStream_t st, int* overflow_flag) {
+  HCG_CUDA_OK(cudaMemsetAsync(overflow_count, 0, sizeof(int), st));
+  k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(graph_ptr, rowptr, col, dis, x, F, N, E, B, p.W, p.nslots,
+                                                                          p.nwin, p.cap, tiles, counts, overflow_count, overflow_list,
+                                                                          overflow_flag);
+  HCG_LAUNCH_OK(st, "k_tile_desc");
+  return HCG_OK;
+}
+
 struct TcWs {
   TcTile* tiles;
   int* counts;
@@ -795,9 +853,7 @@ struct TcWs {
 static TcWs carve_tc(void* ws, int64_t B) {
   Carver c(ws, (size_t)-1);
   TcWs w{};
-  const TcPlan p2 = tc_plan(B, 2), p3 = tc_plan(B, 3);
-  const size_t t2 = (size_t)p2.nslots * p2.cap, t3 = (size_t)p3.nslots * p3.cap;
-  w.tiles = c.take<TcTile>((t2 > t3 ? t2 : t3) + 1);
+  w.tiles = c.take<TcTile>(tc_tiles_capacity(B));
   w.counts = c.take<int>((size_t)3 * kNumSMs + 1);
   w.overflow_count = c.take<int>(64);
   w.overflow_list = c.take<int>((size_t)B + 1);
@@ -834,11 +890,8 @@ int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStr
   const int ns = tc_slots(f.F, f.L);
   const TcPlan p = tc_plan(f.B, ns);
   const size_t smem = tc_layout(f.F, f.L, ns).total;
-  HCG_CUDA_OK(cudaMemsetAsync(w.overflow_count, 0, sizeof(int), st));
-  k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(f.graph_ptr, f.rowptr, f.col, f.dis, f.x, f.F, N, E, f.B, p.W,
-                                                                          p.nslots, p.nwin, p.cap, w.tiles, w.counts,
-                                                                          w.overflow_count, w.overflow_list);
-  HCG_LAUNCH_OK(st, "k_tile_desc");
+  if (int rc = launch_tile_desc(f.graph_ptr, f.rowptr, f.col, f.dis, f.x, f.F, N, E, f.B, p, w.tiles, w.counts, w.overflow_count,
+                                w.overflow_list, st)) return rc;
 
   TcArgs a{};
   a.f = f;

@@ -1,0 +1,50 @@
+// Tile work list shared by the tensor-core graph-resident kernels (forward: hcg_tc.cu, backward: hcg_tc_bwd.cu):
+// a tile is 128 node rows holding one or two whole graphs; k_tile_desc (hcg_tc.cu) builds one dense list per slot.
+#pragma once
+
+#include "hcg_common.cuh"
+
+namespace hcg {
+
+constexpr int kTcRows = 128;          // node rows per tile
+constexpr int kTcEcap = 512;          // CSR slots per tile (4 per node row: molecules)
+constexpr int kTcHPitch = 68;         // floats per activation row: 8 consecutive rows cover all banks for 128-bit access
+constexpr int kTcWinMax = 8;          // graphs per pairing window (at most)
+constexpr int kStatusCrossEdgeTc = 4;
+constexpr int kTileManual = 1;        // TcTile.flags: a 16-byte granular copy window would leave an input array
+
+struct __align__(16) TcTile {   // 64 bytes: one tile of the work list
+  int gA, n0A, nA, e0A;         // first graph: id, first node, nodes, first CSR slot
+  int gB, n0B, nB, e0B;         // second graph (gB < 0: none)
+  int eA, eB, flags, pad0;
+  int pad1[4];
+};
+
+struct __align__(16) TcMeta {   // a tile as the slot's threads see it
+  int gA, n0A, nA, e0A;
+  int gB, n0B, nB, e0B;
+  int eA, eB, flags, pad0;
+  int off[8];                   // [4 gb + q]: word offset, inside stage array q (0 x, 1 rowptr, 2 col, 3 dis),
+                                // of element 0 of graph gb's slice
+};
+
+// The 16-byte granular window [lo, lo + bytes) the bulk copy of `count` 4-byte elements at `p` reads.
+__host__ __device__ __forceinline__ void copy_window(uintptr_t p, int count, uintptr_t* lo, uint32_t* bytes, int* lead) {
+  *lo = p & ~uintptr_t(15);
+  *lead = (int)((p - *lo) >> 2);
+  *bytes = (uint32_t)(((p - *lo) + (uintptr_t)count * 4 + 15) & ~uintptr_t(15));
+}
+
+struct TcPlan {     // launch geometry of the work list for a batch of B graphs
+  int grid, nslots, W, nwin, cap;
+};
+// ns = tile pipelines per CTA; at most max_grid CTAs (the SM count)
+TcPlan tc_plan(int64_t B, int ns);
+// element count of the TcTile array a batch of B graphs can need for any ns in 1..3
+size_t tc_tiles_capacity(int64_t B);
+// builds the per-slot tile lists + overflow list (rowptr / col: the CSR the kernel will copy slices of)
+int launch_tile_desc(const int32_t* graph_ptr, const int32_t* rowptr, const int32_t* col, const float* dis, const float* x, int F,
+                     int64_t N, int64_t E, int64_t B, const TcPlan& p, TcTile* tiles, int* counts, int* overflow_count,
+                     int* overflow_list, cudaStream_t st, int* overflow_flag = nullptr);   // flag[g] = 1: graph g is on the list
+
+}  // namespace hcg

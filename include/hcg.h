@@ -165,7 +165,9 @@ int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts, int cap);
  * tensor-core (HCG_ERR_UNSUPPORTED if not applicable).
  * HCG_CFG_BACKWARD_PATH: 0 = auto (the graph-resident backward kernel when H == 64, L == 2, F <= 32, no
  * edge weights, a disjoint molecule-like batch and no gradient w.r.t. x is wanted; layer-wise kernels
- * otherwise), 1 = force layer-wise, 2 = force graph-resident (HCG_ERR_UNSUPPORTED if not applicable).
+ * otherwise), 1 = force layer-wise, 2 = force graph-resident (HCG_ERR_UNSUPPORTED if not applicable), 3 = force the
+ * graph-resident mma.sync kernel for every graph (the default graph-resident path runs the tcgen05 kernel and leaves
+ * only graphs above its tile capacity to the mma.sync kernel).
  * HCG_CFG_GEMM_PATH (dense X.W products of the layer-wise kernels): 0 = auto (split-TF32 tcgen05 kernel for
  * output widths 64/128/192/256 on batches of >= 8192 rows, fp32 FMA tiles otherwise), 1 = FMA tiles only,
  * 2 = the tensor-core kernel wherever its shape constraints hold (output width a multiple of 64, <= 256).
@@ -185,6 +187,9 @@ int hcg_config_get(int key);
  * memory): D[128,64] = A[128,K] . W[64,K]^T, 1 <= K <= 64, fp32 in / fp32 out.  Test-suite only.
  */
 int hcg_selftest_tc_gemm(const float* A, const float* W, int K, float* D, void* stream);
+/* The weight-gradient building block: G[64,64] = X[K,64]^T . Y[K,64], 1 <= K <= 128 (node rows), both operands read from
+ * row-per-node shared-memory tiles as MN-major tcgen05 operands, split-TF32.  Test-suite only. */
+int hcg_selftest_tc_xty(const float* X, const float* Y, int K, float* G, void* stream);
 
 /* sizeof() of the structs above, for bindings that mirror them (ctypes, cgo, JNI ...) */
 size_t hcg_sizeof_graph(void);

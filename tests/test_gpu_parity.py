@@ -428,7 +428,7 @@ def backward_path(hcg):
         _lib.config_set(_lib.HCG_CFG_BACKWARD_PATH, prev[0])
 
 
-@pytest.mark.parametrize("path", [1, 2])
+@pytest.mark.parametrize("path", [1, 2, 3])   # layer-wise / graph-resident (tcgen05 tiles + overflow) / graph-resident mma.sync only
 @pytest.mark.parametrize("rset,outer,inner,count", [("learning", 1, 2, 668), ("biaryl", 5, 6, 485), ("final_test", 8, 10, 52)])
 def test_backward_paths_match_oracle(hcg, backward_path, path, rset, outer, inner, count):
     """Whole datasets in one batch: more graphs than CTAs (each CTA accumulates several graphs), biaryl
@@ -450,12 +450,13 @@ def test_graph_resident_backward_shapes(hcg, backward_path, F, nmin, nmax, B):
     sd = ref_gcn.init_state_dict(F, 64, 2, 2, 1, seed=5)
     args = (sd, b.x, b.edge_index, b.batch, b.num_graphs, b.y)
     _, g_ref, _ = _oracle_grads(*args)
-    backward_path(2)
-    _, g_fused, _ = _cuda_grads(hcg, *args)
-    _assert_grads(g_fused, g_ref)
-    _, g_again, _ = _cuda_grads(hcg, *args)
-    for k in g_fused:  # no floating-point atomics: run-to-run identical bits
-        assert torch.equal(g_fused[k], g_again[k]), k
+    for path in (2, 3):     # the tcgen05 kernel (+ overflow list), then the mma.sync kernel alone
+        backward_path(path)
+        _, g_fused, _ = _cuda_grads(hcg, *args)
+        _assert_grads(g_fused, g_ref)
+        _, g_again, _ = _cuda_grads(hcg, *args)
+        for k in g_fused:  # no floating-point atomics: run-to-run identical bits
+            assert torch.equal(g_fused[k], g_again[k]), k
     backward_path(1)
     _, g_layer, _ = _cuda_grads(hcg, *args)
     _assert_grads(g_layer, g_ref)

@@ -26,3 +26,22 @@ def test_tc_split_tf32_tile_product(K):
     print(f"K={K}: max |D - ref| / (|A| |W|^T) = {err:.3e}")
     # fp32-class accuracy (a plain TF32 pass would sit at 2^-11 ~ 5e-4)
     assert err <= 5e-7, err
+
+
+@pytest.mark.parametrize("K", [128, 80, 41, 8])
+def test_tc_split_tf32_xty_product(K):
+    """G = X^T Y with the node index as the reduction index (MN-major shared-memory operands): the building block
+    of the weight gradients g_W = gT^T h on the tensor cores."""
+    from hcatgnet_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(100 + K)
+    X = (torch.randn(128, 64, generator=g) * 2).cuda()
+    Y = torch.randn(128, 64, generator=g).cuda()
+    G = torch.full((64, 64), float("nan"), device="cuda")
+    _lib.check(lib.hcg_selftest_tc_xty(X.data_ptr(), Y.data_ptr(), K, G.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    ref = X[:K].double().cpu().t() @ Y[:K].double().cpu()
+    scale = (X[:K].double().abs().cpu().t() @ Y[:K].double().abs().cpu()).clamp(min=1e-30)
+    err = ((G.double().cpu() - ref).abs() / scale).max().item()
+    print(f"K={K}: max |G - ref| / (|X|^T |Y|) = {err:.3e}")
+    assert err <= 1e-6, err
