@@ -149,7 +149,7 @@ class _GCNBase(BaseNetwork):
         need_grad = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params) or
                                                  (edge_mask is not None and edge_mask.requires_grad))
         if edge_weight is not None and edge_weight.requires_grad and torch.is_grad_enabled():
-            raise NotImplementedError("gradients w.r.t. edge_weight are not provided by libhcg yet")
+            return self._run_edge_weight_grad(x, edge_index, batch, num_graphs, edge_weight, home, device)
         plan = ops.cached_collate(cache_on, edge_index, batch, x.shape[0], num_graphs, device,
                                   edge_weight=edge_weight, improved=bool(self.improved), transpose=need_grad,
                                   validate=self.validate_inputs, max_graph_nodes=_max_nodes_hint(cache_on),
@@ -158,6 +158,60 @@ class _GCNBase(BaseNetwork):
         pd = [ops.to_device(p, device, torch.float32) for p in params]
         md = ops.to_device(edge_mask, device, torch.float32)
         out, emb = ops.gcn_apply(xd, plan, self._dims(), pd, edge_mask=md)
+        if home != device:
+            out, emb = out.to(home), emb.to(home)
+        return out, emb
+
+
+    def _run_edge_weight_grad(self, x, edge_index, batch, num_graphs, edge_weight, home, device):
+        """Gradient w.r.t. ``edge_weight`` (reference model/gcn.py:124-127 hands it to conv1 only).
+        The weights enter conv1's NORMALISATION (weighted degrees), so their derivative is not a per-edge dot product
+        the aggregation kernels could emit: conv1 is written here with differentiable torch operations on the GPU
+        (gcn_norm with weights: existing self-loops keep their weight, added ones get 2.0 when ``improved``; transform,
+        weighted sum to dst, bias) and everything after it - the remaining conv layers, pooling, readout - runs in
+        libhcg on conv1's output, whose backward returns the gradient w.r.t. that input.  A path for explainers; it
+        is never taken when ``edge_weight`` does not require grad."""
+        xd = ops.to_device(x, device, torch.float32)
+        ei = ops.to_device(edge_index, device, torch.int64)
+        bt = ops.to_device(batch, device, torch.int64)
+        ew = edge_weight if edge_weight.device == device else edge_weight.to(device)
+        n = xd.shape[0]
+        row, col = ei[0], ei[1]
+        loop = row == col
+        keep = ~loop
+        w_loop = torch.full((n,), 2.0 if self.improved else 1.0, dtype=torch.float32, device=device)
+        if bool(loop.any()):
+            w_loop = w_loop.index_put((row[loop],), ew[loop].to(torch.float32))     # an existing self-loop keeps its weight
+        ar = torch.arange(n, dtype=torch.int64, device=device)
+        w = torch.cat([ew[keep].to(torch.float32), w_loop])
+        row2, col2 = torch.cat([row[keep], ar]), torch.cat([col[keep], ar])
+        deg = torch.zeros(n, dtype=torch.float32, device=device).index_add(0, col2, w)
+        dis = deg.pow(-0.5)
+        dis = dis.masked_fill(dis == float("inf"), 0.0)
+        norm = dis[row2] * w * dis[col2]
+        params = [ops.to_device(p, device, torch.float32) for p in self._flat_params()]
+        t = xd @ params[0].t()
+        z1 = torch.zeros(n, self.embedding_dim, dtype=torch.float32, device=device).index_add(0, col2, t[row2] * norm[:, None]) + params[1]
+        h1 = torch.nn.functional.leaky_relu(z1, self.relu1.negative_slope)
+        dims = self._dims()
+        if dims.L > 1:
+            plan = ops.collate(ei, bt, n, num_graphs, transpose=True, validate=self.validate_inputs)
+            sub = ops.NetDims(F=dims.H, H=dims.H, L=dims.L - 1, R=dims.R, C=dims.C, slope=dims.slope)
+            out, emb = ops.gcn_apply(h1, plan, sub, params[2:])
+        else:
+            b = bt if bt is not None else torch.zeros(n, dtype=torch.int64, device=device)
+            idx = b[:, None].expand(-1, h1.shape[1])
+            mx = torch.full((num_graphs, h1.shape[1]), float("-inf"), device=device).scatter_reduce(0, idx, h1, reduce="amax", include_self=False)
+            cnt = torch.zeros(num_graphs, device=device).index_add(0, b, torch.ones(n, device=device)).clamp(min=1)
+            mean = torch.zeros(num_graphs, h1.shape[1], device=device).index_add(0, b, h1) / cnt[:, None]
+            emb = torch.cat([mx, mean], dim=1)
+            z = emb
+            for k in range(dims.R):
+                wk, bk = params[2 * dims.L + 2 * k], params[2 * dims.L + 2 * k + 1]
+                z = z @ wk.t() + bk
+                if k < dims.R - 1:
+                    z = torch.nn.functional.leaky_relu(z, dims.slope)
+            out = z
         if home != device:
             out, emb = out.to(home), emb.to(home)
         return out, emb

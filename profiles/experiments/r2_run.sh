@@ -1,4 +1,16 @@
 set -x
-timeout 900 python -m pytest tests/test_gpu_parity.py -q -m gpu -x -k "backward" 2>&1 | tail -4
-timeout 600 python bench.py --mode train --steps 30 --warmup 5 --no-cpu-baseline 2>gpurun_out/tb.err | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('train', d['value'], d['ms_per_step'], {k:round(v['ms_per_launch']*1e3,1) for k,v in d['kernels'].items()})"; tail -3 gpurun_out/tb.err
-HCG_LIB_PATH=build/libhcg_timing.so python profiles/tb_phase_timing.py 2>&1 | tail -17
+timeout 600 python -m pytest tests/test_gpu_dp.py -q -m gpu -x -k emulated 2>&1 | grep -E "^>|^E  " | head -12
+python - <<'PY'
+import sys; sys.path.insert(0,'.'); sys.path.insert(0,'tests')
+import torch, hcatgnet_b200 as pkg
+import tests.test_gpu_dp as T
+whole, sh_a, sh_b = T._shards(pkg)
+sd0 = {k: v.clone() for k, v in T._fresh(pkg).state_dict().items()}
+one = pkg.FusedTrainer(T._fresh(pkg, sd0)); ra, rb = pkg.FusedTrainer(T._fresh(pkg, sd0)), pkg.FusedTrainer(T._fresh(pkg, sd0))
+for it in range(4):
+    l1 = one.step(whole.to("cuda")); ra.accumulate(sh_a.to("cuda")); rb.accumulate(sh_b.to("cuda"))
+    total = ra.grad + rb.grad
+    gd = (total[:-2]-one.grad[:-2]).abs().max().item(); gm = one.grad[:-2].abs().max().item()
+    ra.grad.copy_(total); rb.grad.copy_(total); la, lb = ra.apply(), rb.apply()
+    print(it, 'grad diff', gd, 'max', gm, 'sse', total[-2].item(), one.grad[-2].item(), 'loss', float(la), float(l1), 'param diff', (ra.flat-one.flat).abs().max().item())
+PY

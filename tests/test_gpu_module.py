@@ -417,3 +417,32 @@ def test_report_csvs_reproduce_the_reference_files(pkg, tmp_path):
     ens = pkg.screen_ensemble_to_csv(str(tmp_path / "screen"), [model, model], pkg.DataLoader(sets["test"], batch_size=16))
     assert np.allclose(ens["mean_predicted_ddG"].to_numpy(), pred["predicted_ddG"].to_numpy(), atol=1e-6)
     assert float(ens["std_predicted_ddG"].abs().max()) == 0.0
+
+
+def test_gradient_wrt_edge_weight_matches_oracle(pkg):
+    """GCN_explain.forward(x, edge_index, batch_index, edge_weight) with edge_weight.requires_grad (reference
+    model/gcn.py:124-127: the weights reach conv1 only, through its weighted normalisation): d out / d edge_weight and
+    d out / d x against the fp64 oracle's autograd, with and without `improved`, including an existing self-loop."""
+    sd, graphs, _, _ = golden_io.rows_with_graphs("learning", 1, 2)
+    b = ref_gcn.collate(graphs[:7])
+    ei = torch.cat([b["edge_index"], torch.tensor([[3], [3]])], dim=1)       # one self-loop edge with its own weight
+    g = torch.Generator().manual_seed(4)
+    ew0 = torch.rand(ei.shape[1], generator=g) + 0.25
+    for improved in (True, False):
+        opt = pkg.default_options(improved=improved)
+        model = pkg.GCN_explain(opt, 25)
+        model.load_state_dict(sd, strict=True)
+        model = model.to("cuda").eval()
+        ew = ew0.clone().cuda().requires_grad_(True)
+        x = b["x"].clone().cuda().requires_grad_(True)
+        out = model(x=x, edge_index=ei.cuda(), batch_index=b["batch"].cuda(), edge_weight=ew)
+        out.sum().backward()
+        sd64 = {k: v.double() for k, v in sd.items()}
+        ew_r = ew0.double().requires_grad_(True)
+        x_r = b["x"].double().requires_grad_(True)
+        o_ref, _ = ref_gcn.forward(sd64, x_r, ei, b["batch"], 7, edge_weight=ew_r, improved=improved)
+        o_ref.sum().backward()
+        assert float((out.detach().cpu().double() - o_ref.detach()).abs().max()) <= 1e-5 * max(1.0, float(o_ref.abs().max()))
+        for got, ref in ((ew.grad, ew_r.grad), (x.grad, x_r.grad)):
+            scale = max(float(ref.abs().max()), 1e-12)
+            assert float((got.cpu().double() - ref).abs().max()) <= 1e-4 * scale
