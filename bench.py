@@ -258,6 +258,7 @@ def algorithmic_bytes(name: str, N: int, E: int, B: int, F: int, H: int):
         "k_fused_fwd": 4 * N * F + csr + 4 * N + 8 * B * H + 4 * (B + 1),
         # graph-resident backward: saved h1, h2, x, transposed CSR, dis, emb + its gradient in; per-CTA partials out
         "k_fused_bwd": 8 * N * H + 4 * N * F + csr + 4 * N + 16 * B * H + 296 * 4 * (H * H + H * F + 2 * H),
+        "k_tc_bwd": 8 * N * H + 4 * N * F + csr + 4 * N + 16 * B * H + 64 * B + 148 * 4 * (H * H + H * F + 2 * H),
         "k_agg": 4 * N * H + csr + 4 * N + 4 * N * H,        # read T once, CSR, dis, write h
         "k_agg_wide": 4 * N * H + csr + 4 * N + 4 * N * H,   # same contract as k_agg
         "k_agg_narrow": 4 * N * H + csr + 4 * N + 4 * N * H,

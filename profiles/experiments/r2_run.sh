@@ -1,16 +1,10 @@
 set -x
-timeout 600 python -m pytest tests/test_gpu_dp.py -q -m gpu -x -k emulated 2>&1 | grep -E "^>|^E  " | head -12
-python - <<'PY'
-import sys; sys.path.insert(0,'.'); sys.path.insert(0,'tests')
-import torch, hcatgnet_b200 as pkg
-import tests.test_gpu_dp as T
-whole, sh_a, sh_b = T._shards(pkg)
-sd0 = {k: v.clone() for k, v in T._fresh(pkg).state_dict().items()}
-one = pkg.FusedTrainer(T._fresh(pkg, sd0)); ra, rb = pkg.FusedTrainer(T._fresh(pkg, sd0)), pkg.FusedTrainer(T._fresh(pkg, sd0))
-for it in range(4):
-    l1 = one.step(whole.to("cuda")); ra.accumulate(sh_a.to("cuda")); rb.accumulate(sh_b.to("cuda"))
-    total = ra.grad + rb.grad
-    gd = (total[:-2]-one.grad[:-2]).abs().max().item(); gm = one.grad[:-2].abs().max().item()
-    ra.grad.copy_(total); rb.grad.copy_(total); la, lb = ra.apply(), rb.apply()
-    print(it, 'grad diff', gd, 'max', gm, 'sse', total[-2].item(), one.grad[-2].item(), 'loss', float(la), float(l1), 'param diff', (ra.flat-one.flat).abs().max().item())
-PY
+python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-profile --no-sub > gpurun_out/plain.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -s 40 -c 200 --csv --log-file gpurun_out/r2_launches_infer.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-profile --no-sub > gpurun_out/ncu1.log 2>&1
+python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-profile --no-sub > gpurun_out/plain.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:k_tc_fwd -s 4 -c 1 -o gpurun_out/r2_tc_fwd_final -f python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-profile --no-sub > gpurun_out/ncu2.log 2>&1
+python bench.py --mode train --steps 3 --warmup 3 --no-cpu-baseline --no-profile > gpurun_out/plain.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:k_tc_bwd -s 4 -c 1 -o gpurun_out/r2_tc_bwd -f python bench.py --mode train --steps 3 --warmup 3 --no-cpu-baseline --no-profile > gpurun_out/ncu3.log 2>&1
+python bench.py --mode train --steps 3 --warmup 3 --no-cpu-baseline --no-profile > gpurun_out/plain.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -s 60 -c 200 --csv --log-file gpurun_out/r2_launches_train.csv python bench.py --mode train --steps 3 --warmup 3 --no-cpu-baseline --no-profile > gpurun_out/ncu4.log 2>&1
+tail -2 gpurun_out/ncu2.log | cut -c1-150; tail -2 gpurun_out/ncu3.log | cut -c1-150
