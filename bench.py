@@ -255,6 +255,8 @@ def algorithmic_bytes(name: str, N: int, E: int, B: int, F: int, H: int):
     table = {
         # whole conv stack + pooling of a batch: x, CSR, deg^-1/2 in; embedding + per-graph descriptor out/in
         "k_tc_fwd": 4 * N * F + csr + 4 * N + 8 * B * H + 64 * B,   # (+ one 64-byte work-list record per tile, <= B tiles)
+        # the same from the raw edge list: x, int64 (src, dst) per edge, work-list record per tile in; embedding out
+        "k_tc_fwd_coo": 4 * N * F + 16 * E + 8 * B * H + 64 * B,
         "k_fused_fwd": 4 * N * F + csr + 4 * N + 8 * B * H + 4 * (B + 1),
         # graph-resident backward: saved h1, h2, x, transposed CSR, dis, emb + its gradient in; per-CTA partials out
         "k_fused_bwd": 8 * N * H + 4 * N * F + csr + 4 * N + 16 * B * H + 296 * 4 * (H * H + H * F + 2 * H),
@@ -364,13 +366,21 @@ def measure(cx: Ctx, mode: str, batch: int, hidden: int, convs: int, steps: int,
                       edges_grouped=True)
         # what a PyG Batch knows on the host (ptr, _slice_dict): offsets of every graph and the size of the largest one
         d.max_graph_nodes, d.max_graph_edges, d.edge_ptr = b.max_graph_nodes, b.max_graph_edges, b.edge_ptr.to(dev)
+        d.max_in_degree = b.max_in_degree
         devb.append(d)
+    # inference straight from the edge list (hcg_gcn_forward_coo: the conv kernel builds the neighbour lists) when the
+    # batches' host-side size facts allow it; HCG_BENCH_CSR=1 forces hcg_collate + hcg_gcn_forward (the round-1/2 path)
+    edge_list = mode == "infer" and os.environ.get("HCG_BENCH_CSR", "0") != "1" and all(ops.edge_list_hints_ok(d) for d in devb)
     Ns = [b.num_nodes for b in host]
     Es = [int(b.edge_index.shape[1]) for b in host]
     N, E = int(np.mean(Ns)), int(np.mean(Es))
 
     def step_device(i):
         b = devb[i % POOL]
+        if edge_list:
+            res = ops.forward_edge_list(b.x, b.edge_index, b.ptr, b.edge_ptr, dims, params, validate=False)
+            if res is not None:
+                return res[0]
         if mode == "infer":
             plan = ops.collate(b.edge_index, b.batch, b.num_nodes, b.num_graphs, validate=False, grouped=True,
                                max_graph_nodes=b.max_graph_nodes, ptr=b.ptr, edge_ptr=b.edge_ptr,
@@ -405,7 +415,7 @@ def measure(cx: Ctx, mode: str, batch: int, hidden: int, convs: int, steps: int,
         else:
             drain_losses(trainer.step(d) for d in pkg.DevicePrefetcher(stream, device=dev))
 
-    rec = {"mode": mode, "batch_per_gpu": batch, "hidden": hidden, "n_convolutions": convs, "steps": steps, "warmup": warmup,
+    rec = {"mode": mode, "path": "edge_list (hcg_gcn_forward_coo)" if edge_list else "collate + forward", "batch_per_gpu": batch, "hidden": hidden, "n_convolutions": convs, "steps": steps, "warmup": warmup,
            "mean_nodes_per_batch": N, "mean_edges_per_batch": E}
 
     # ---- device-resident number --------------------------------------------------------------

@@ -50,6 +50,18 @@ int tc_fwd_edge_cap();   // ... and CSR slots
 // all_fit: the caller's hints say that every graph fits a tile (the overflow pass then runs as a single CTA)
 int launch_tc_fwd(const FusedFwdArgs& a, int64_t N, int64_t E, void* ws, cudaStream_t st, bool all_fit = false);
 
+// COO variant: the kernel builds each tile's neighbour lists from the raw edge list (edge_index int64 [2, E], every
+// graph's edges contiguous; node_ptr / edge_ptr: int64 [B + 1] offsets).  No fallback kernel: input it cannot take
+// (a graph above the tile capacity, an in-degree above tc_fwd_coo_degree_cap(), a self-loop, an edge that leaves its
+// graph) is reported through tc_fwd_coo_flags and the embeddings of the call are then unspecified (finite memory
+// accesses only).  a.rowptr / col / dis / graph_ptr / scratch are not used.
+size_t tc_fwd_coo_smem_bytes(int F, int L);
+size_t tc_fwd_coo_workspace_bytes(int64_t B);
+int tc_fwd_coo_degree_cap();
+int launch_tc_fwd_coo(const FusedFwdArgs& a, const int64_t* edge_index, const int64_t* node_ptr, const int64_t* edge_ptr, int64_t N,
+                      int64_t E, void* ws, cudaStream_t st);
+int tc_fwd_coo_flags(const void* ws, int64_t B, cudaStream_t st, int* flags);
+
 // ---- graph-resident backward (hcg_fused_bwd.cu): H == 64, two conv layers, F <= 32 ---------------
 struct FusedBwdArgs {
   const int32_t* t_rowptr;        // transposed (src-sorted) CSR

@@ -1167,6 +1167,30 @@ extern "C" size_t hcg_backward_workspace_bytes(int64_t N, int64_t E, int64_t B, 
   return carve_bwd(nullptr, N, B, p).bytes;
 }
 
+// readout MLP on the pooled embeddings: the default head (128 -> 64 -> C) in one launch, anything else layer by layer
+static int run_readout(const HcgParams* p, const float* emb, float* out, const HcgSaved* saved, float* const* hid_ws, int64_t B,
+                       cudaStream_t st) {
+  if (p->R == 2 && 2 * p->H == RO_IN && B > 0) {
+    float* hs = saved ? saved->hid[0] : nullptr;
+    if (saved) HCG_REQUIRE(hs != nullptr, HCG_ERR_INVALID_ARG, "saved->hid[0] is NULL");
+    k_readout2<<<(unsigned)cdiv(B, RO_FG), 256, 0, st>>>(emb, p->ro_w[0], p->ro_b[0], p->ro_w[1], p->ro_b[1], hs, out, B,
+                                                        p->C, p->slope);
+    HCG_LAUNCH_OK(st, "k_readout2");
+    return HCG_OK;
+  }
+  const float* z = emb;
+  for (int k = 0; k < p->R; ++k) {
+    const bool last = k == p->R - 1;
+    float* zo = last ? out : (saved ? saved->hid[k] : hid_ws[k]);
+    HCG_REQUIRE(zo != nullptr, HCG_ERR_INVALID_ARG, "saved->hid[%d] is NULL", k);
+    const int rc = launch_gemm<true>(z, p->ro_w[k], zo, B, ro_in_dim(p, k), ro_out_dim(p, k),
+                                     last ? EPI_BIAS : EPI_BIAS_LRELU, p->ro_b[k], p->slope, st);
+    if (rc) return rc;
+    z = zo;
+  }
+  return HCG_OK;
+}
+
 extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParams* p, float* out, float* emb,
                                const HcgSaved* saved, void* ws, size_t ws_bytes, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -1264,25 +1288,67 @@ extern "C" int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParam
     k_pool<<<(unsigned)cdiv(B, 256 / lpr), 256, 0, st>>>(h_out, g->graph_ptr, B, H, lpr, emb);
     HCG_LAUNCH_OK(st, "k_pool");
   }
-  if (p->R == 2 && 2 * H == RO_IN && B > 0) {  // the default head in one launch
-    float* hs = saved ? saved->hid[0] : nullptr;
-    if (saved) HCG_REQUIRE(hs != nullptr, HCG_ERR_INVALID_ARG, "saved->hid[0] is NULL");
-    k_readout2<<<(unsigned)cdiv(B, RO_FG), 256, 0, st>>>(emb, p->ro_w[0], p->ro_b[0], p->ro_w[1], p->ro_b[1], hs, out, B,
-                                                        p->C, p->slope);
-    HCG_LAUNCH_OK(st, "k_readout2");
-    return HCG_OK;
-  }
-  const float* z = emb;
-  for (int k = 0; k < p->R; ++k) {
-    const bool last = k == p->R - 1;
-    float* zo = last ? out : (saved ? saved->hid[k] : w.hid[k]);
-    HCG_REQUIRE(zo != nullptr, HCG_ERR_INVALID_ARG, "saved->hid[%d] is NULL", k);
-    rc = launch_gemm<true>(z, p->ro_w[k], zo, B, ro_in_dim(p, k), ro_out_dim(p, k),
-                           last ? EPI_BIAS : EPI_BIAS_LRELU, p->ro_b[k], p->slope, st);
-    if (rc) return rc;
-    z = zo;
-  }
-  return HCG_OK;
+  return run_readout(p, emb, out, saved, w.hid, B, st);
+}
+
+// ---- forward from the raw edge list (no collate) ---------------------------------------------------
+struct CooWs {
+  char* tc;
+  float* hid[HCG_MAX_READOUT];
+  size_t bytes;
+};
+
+static CooWs carve_coo(void* ws, int64_t B, const HcgParams* p) {
+  Carver c(ws, (size_t)-1);
+  CooWs w{};
+  w.tc = c.take<char>(tc_fwd_coo_workspace_bytes(B));   // first: hcg_forward_coo_status finds the flags from B alone
+  for (int k = 0; k < p->R - 1; ++k) w.hid[k] = c.take<float>((size_t)B * ro_out_dim(p, k) + 4);
+  w.bytes = c.off;
+  return w;
+}
+
+extern "C" int hcg_forward_coo_supported(const HcgParams* p) {
+  if (!p || check_params(p)) return 0;
+  return p->H == kFusedH && p->F <= 32 && p->slope >= 0.f && p->slope <= 1.f && tc_fwd_coo_smem_bytes(p->F, p->L) <= 227 * 1024;
+}
+
+extern "C" size_t hcg_forward_coo_workspace_bytes(int64_t B, const HcgParams* p) {
+  if (!p || check_params(p) || B < 0) return 0;
+  return carve_coo(nullptr, B, p).bytes;
+}
+
+extern "C" int hcg_gcn_forward_coo(const float* x, const int64_t* edge_index, const int64_t* node_ptr, const int64_t* edge_ptr,
+                                   int64_t N, int64_t E, int64_t B, float fill, const HcgParams* p, float* out, float* emb,
+                                   void* ws, size_t ws_bytes, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = check_params(p);
+  if (rc) return rc;
+  HCG_REQUIRE(N >= 0 && E >= 0 && B >= 0 && N < INT32_MAX && E < INT32_MAX, HCG_ERR_INVALID_ARG, "bad sizes N=%lld E=%lld B=%lld",
+              (long long)N, (long long)E, (long long)B);
+  HCG_REQUIRE(out && emb && ws, HCG_ERR_INVALID_ARG, "NULL out/emb/workspace");
+  HCG_REQUIRE((N == 0 || x) && (E == 0 || edge_index) && node_ptr && edge_ptr, HCG_ERR_INVALID_ARG, "NULL x/edge_index/offsets");
+  if (!hcg_forward_coo_supported(p))
+    return set_err(HCG_ERR_UNSUPPORTED, "edge-list forward needs H == %d, F <= 32, 0 <= slope <= 1 and conv layers that fit shared memory", kFusedH);
+  CooWs w = carve_coo(ws, B, p);
+  HCG_REQUIRE(ws_bytes >= w.bytes, HCG_ERR_WORKSPACE, "edge-list forward workspace too small: %zu < %zu", ws_bytes, w.bytes);
+  if (B == 0) return HCG_OK;
+  note_region(st);
+  FusedFwdArgs a{};
+  a.x = x;
+  for (int l = 0; l < p->L; ++l) { a.conv_w[l] = p->conv_w[l]; a.conv_b[l] = p->conv_b[l]; }
+  a.emb = emb;
+  a.B = B; a.F = p->F; a.Fp = (p->F + 3) / 4 * 4; a.L = p->L; a.slope = p->slope; a.fill = fill;
+  rc = launch_tc_fwd_coo(a, edge_index, node_ptr, edge_ptr, N, E, w.tc, st);
+  if (rc) return rc;
+  return run_readout(p, emb, out, nullptr, w.hid, B, st);
+}
+
+extern "C" int hcg_forward_coo_status(const void* ws, int64_t B, void* stream, int32_t* flags) {
+  HCG_REQUIRE(ws && flags && B >= 0, HCG_ERR_INVALID_ARG, "NULL workspace / flags");
+  int f = 0;
+  const int rc = tc_fwd_coo_flags(ws, B, static_cast<cudaStream_t>(stream), &f);   // (the tile work list opens the workspace)
+  *flags = f;
+  return rc;
 }
 
 extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgParams* p, const HcgSaved* saved,

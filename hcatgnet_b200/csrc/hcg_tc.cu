@@ -187,6 +187,9 @@ struct TcArgs {
   const int* counts;        // [nslots]
   int cap;
   int64_t N, E;
+  // COO variant (k_tc_fwd<.., COO = true>): the raw edge list instead of the CSR of f.rowptr / f.col / f.dis
+  const int64_t* ei;        // [2, E]: row 0 sources, row 1 targets, grouped by graph
+  int* kflags;              // [nslots]: per-slot refusal flags (plain stores, no memset needed)
 };
 
 // ---- work list ----------------------------------------------------------------------------------
@@ -199,10 +202,17 @@ __global__ void __launch_bounds__(128)
 k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
             const float* __restrict__ dis, const float* __restrict__ x, int F, int64_t N, int64_t E, int64_t B, int W,
             int nslots, int nwin, int cap, TcTile* __restrict__ tiles, int* __restrict__ counts,
-            int* __restrict__ overflow_count, int* __restrict__ overflow_list, int* __restrict__ overflow_flag) {
+            int* __restrict__ overflow_count, int* __restrict__ overflow_list, int* __restrict__ overflow_flag,
+            const int64_t* __restrict__ node_ptr64, const int64_t* __restrict__ edge_ptr64, const int64_t* __restrict__ ei,
+            int* __restrict__ dflags, float* __restrict__ emb) {
   const int slot = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   const int lane = threadIdx.x & 31;
   if (slot >= nslots) return;  // whole warps leave together
+  // COO mode (ei != NULL): node / edge offsets come from the batch's own int64 offset vectors, a graph may have
+  // no edges, the copy windows are those of the two edge_index rows, and a graph that does not fit a tile is
+  // REFUSED (flag in dflags[slot], embedding row zeroed) - there is no fallback kernel behind this path.
+  const bool coo = ei != nullptr;
+  int refused = 0;
   TcTile* out = tiles + (size_t)slot * cap;
   int total = 0;
   const int wps = (nwin + nslots - 1) / nslots;
@@ -214,25 +224,60 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
     int wcnt = 0;
     if (live) wcnt = (int)((B - g0) < (int64_t)W ? (B - g0) : (int64_t)W);
 #pragma unroll
-    for (int k = 0; k <= kTcWinMax; ++k) gp[k] = (live && k <= wcnt) ? graph_ptr[g0 + k] : 0;
+    for (int k = 0; k <= kTcWinMax; ++k) {
+      gp[k] = 0;
+      if (live && k <= wcnt) {
+        if (coo) {
+          const int64_t v = node_ptr64[g0 + k];
+          gp[k] = (int)v;
+          if (v < 0 || v > N) { gp[k] = 0; refused |= kCooBadOffsets; }
+        } else {
+          gp[k] = graph_ptr[g0 + k];
+        }
+      }
+    }
 #pragma unroll
-    for (int k = 0; k <= kTcWinMax; ++k) ee[k] = (live && k <= wcnt) ? rowptr[gp[k]] : 0;
+    for (int k = 0; k <= kTcWinMax; ++k) {
+      ee[k] = 0;
+      if (live && k <= wcnt) {
+        if (coo) {
+          const int64_t v = edge_ptr64[g0 + k];
+          ee[k] = (int)v;
+          if (v < 0 || v > E) { ee[k] = 0; refused |= kCooBadOffsets; }
+        } else {
+          ee[k] = rowptr[gp[k]];
+        }
+      }
+    }
     unsigned used = 0, manual = 0;  // bit k: graph k of the window is not available / needs ordinary loads
 #pragma unroll
     for (int k = 0; k < kTcWinMax; ++k) {
       const int n = gp[k + 1] - gp[k], e = ee[k + 1] - ee[k];
       if (k >= wcnt) { used |= 1u << k; continue; }
-      const bool over = n <= 0 || e <= 0 || n > kTcRows || e > kTcEcap;
+      const bool over = n <= 0 || (coo ? e < 0 : e <= 0) || n > kTcRows || e > kTcEcap;
       if (overflow_flag) overflow_flag[g0 + k] = over ? 1 : 0;   // (a per-graph flag: an order that does not depend on timing)
       if (over) {
         used |= 1u << k;
-        overflow_list[atomicAdd(overflow_count, 1)] = (int)(g0 + k);
+        if (coo) {
+          refused |= kCooTooLarge;
+          if (emb) for (int c = 0; c < 128; ++c) emb[(g0 + k) * 128 + c] = 0.f;
+        } else {
+          overflow_list[atomicAdd(overflow_count, 1)] = (int)(g0 + k);
+        }
         continue;
       }
       uintptr_t lo; uint32_t bytes; int lead;
       bool m = false;
       copy_window(reinterpret_cast<uintptr_t>(x + (int64_t)gp[k] * F), n * F, &lo, &bytes, &lead);
       m |= lo + bytes > reinterpret_cast<uintptr_t>(x + N * F);
+      if (coo) {   // slices of the two edge_index rows, as 4-byte words
+        copy_window(reinterpret_cast<uintptr_t>(ei + ee[k]), 2 * e, &lo, &bytes, &lead);
+        m |= lo + bytes > reinterpret_cast<uintptr_t>(ei + 2 * E);
+        copy_window(reinterpret_cast<uintptr_t>(ei + E + ee[k]), 2 * e, &lo, &bytes, &lead);
+        m |= lo + bytes > reinterpret_cast<uintptr_t>(ei + 2 * E);
+        if (m) manual |= 1u << k;
+        continue;
+      }
       copy_window(reinterpret_cast<uintptr_t>(rowptr + gp[k]), n + 1, &lo, &bytes, &lead);
       m |= lo + bytes > reinterpret_cast<uintptr_t>(rowptr + N + 1);
       copy_window(reinterpret_cast<uintptr_t>(col + ee[k]), e, &lo, &bytes, &lead);
@@ -293,6 +338,11 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
     }
   }
   if (lane == 0) counts[slot] = total;
+  if (dflags) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) refused |= __shfl_xor_sync(0xffffffffu, refused, o);
+    if (lane == 0) dflags[slot] = refused;
+  }
 }
 
 // shared-memory carve-up, identical on host (size query) and device; weights first, then per slot the
@@ -300,10 +350,13 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
 // BYTES from the 1024-aligned base; stage array sizes in 4-byte words (multiples of 4, so every array is
 // 16-byte aligned).
 struct TcSmemLayout {
-  uint32_t w0_hi, w0_lo, wl, bias, hbuf, nbr, xst, cst;
+  uint32_t w0_hi, w0_lo, wl, bias, hbuf, nbr, deg, xst, cst;
   uint32_t xw, rw, cw, dw, csr_words, slot_bytes, total;
 };
-__host__ __device__ inline TcSmemLayout tc_layout(int F, int L, int nslots) {
+// coo: the stage arrays are the int64 source / target slices (2 words per edge) and there is no dis array; the
+// neighbour records are kTcCooDeg planes of kTcRows (record t of row r at [t][r]) and a per-row in-degree
+// counter follows them.
+__host__ __device__ inline TcSmemLayout tc_layout(int F, int L, int nslots, bool coo = false) {
   TcSmemLayout y;
   uint32_t p = 0;
   y.w0_hi = p; p += tc::kN * 32 * 4;
@@ -312,13 +365,14 @@ __host__ __device__ inline TcSmemLayout tc_layout(int F, int L, int nslots) {
   y.bias = p; p += (uint32_t)L * 64 * 4;
   // two slices per array, each a 16-byte granular window: up to 12 + 15 bytes of slack per slice
   y.xw = ((uint32_t)kTcRows * F + 16 + 3) & ~3u;
-  y.rw = ((uint32_t)kTcRows + 2 + 16 + 3) & ~3u;
-  y.cw = ((uint32_t)kTcEcap + 16 + 3) & ~3u;
-  y.dw = ((uint32_t)kTcRows + 16 + 3) & ~3u;
+  y.rw = coo ? (2u * kTcEcap + 16) : (((uint32_t)kTcRows + 2 + 16 + 3) & ~3u);
+  y.cw = coo ? (2u * kTcEcap + 16) : (((uint32_t)kTcEcap + 16 + 3) & ~3u);
+  y.dw = coo ? 0u : (((uint32_t)kTcRows + 16 + 3) & ~3u);
   y.csr_words = y.rw + y.cw + y.dw;
   y.hbuf = p;
   y.nbr = y.hbuf + (uint32_t)kTcRows * kTcHPitch * 4;   // slot 0's (tile row, norm) record per CSR slot
-  y.xst = y.nbr + (uint32_t)kTcEcap * 8;                // slot 0's x rows
+  y.deg = y.nbr + (coo ? (uint32_t)kTcCooDeg * kTcRows * 8 : (uint32_t)kTcEcap * 8);   // coo: in-degree per tile row
+  y.xst = y.deg + (coo ? (uint32_t)kTcRows * 4 : 0u);   // slot 0's x rows
   y.cst = y.xst + y.xw * 4;                             // slot 0's first CSR stage (rowptr | col | dis)
   y.slot_bytes = (y.cst - y.hbuf) + 2 * y.csr_words * 4;
   p += (uint32_t)nslots * y.slot_bytes;
@@ -337,7 +391,8 @@ __device__ unsigned long long g_tc_timing[16];
 // walked as (tile row, norm) records; every lane takes `maxdeg` steps (a lane past its own degree idles:
 // fewer shared-memory wavefronts than adding 0 x its own row), then the self-loop, last, as in the reference.
 // `xcol`: the thread's first column of tile row 0.
-template <int NC, int XW>
+// NBS: distance, in records, between consecutive records of a row (1: CSR slots; kTcRows: COO planes).
+template <int NC, int XW, int NBS>
 __device__ __forceinline__ void gather_x(float (&acc)[XW], const float* xcol, int F, const int2* nbp, int deg, int maxdeg,
                                          int iself, float wself, int ncol = 0) {
   if (NC == 0) return;
@@ -350,10 +405,16 @@ __device__ __forceinline__ void gather_x(float (&acc)[XW], const float* xcol, in
   int2 nb = 0 < deg ? nbp[0] : make_int2(iself, 0);
   for (int t = 0; t < maxdeg; ++t) {
     const int2 cur = nb;
-    nb = t + 1 < deg ? nbp[t + 1] : make_int2(iself, 0);
+    nb = t + 1 < deg ? nbp[(t + 1) * NBS] : make_int2(iself, 0);
     if (t < deg) row_fma(cur.x, __int_as_float(cur.y));
   }
   row_fma(iself, wself);
+}
+
+// compare-exchange of two (edge number << 8 | tile row) keys
+__device__ __forceinline__ void key_cx(int& p, int& q) {
+  const int lo = min(p, q), hi = max(p, q);
+  p = lo; q = hi;
 }
 
 // F_ = compile-time number of input features (25: the RhCAA featuriser, 32: biaryl) or 0 = run-time F <= 32.
@@ -364,7 +425,19 @@ __device__ __forceinline__ void gather_x(float (&acc)[XW], const float* xcol, in
 //            64-wide layer runs as two K halves: the threads of column half 0 store their operand half and its
 //            MMAs are issued; the threads of half 1 (their gather ran meanwhile) wait for those MMAs to have
 //            read the operand (tcgen05.commit -> mbarrier), store theirs, and the second chain accumulates on top.
-template <int F_, int NS>
+//
+// COO = true: the kernel reads the raw edge list (a.ei: int64 [2, E], each graph's edges contiguous, located by the
+// work list) instead of a collated CSR, and builds the tile's neighbour records itself:
+//   A. every staged edge (s, d) claims the next record of row d (shared-memory atomic on the row's in-degree counter)
+//      and leaves (tile row of s, edge number) there;
+//   B. the row's first thread orders its records by edge number (sorting network in registers on the packed keys
+//      edge number << 8 | tile row: the claim order is arbitrary, the summation order must not be) and rewrites
+//      them as (tile row, norm_ij), norm from the two
+//      in-degrees through a small table of (deg + fill)^-1/2 - IEEE sqrt and divide, as hcg_collate computes them.
+// The records of a row are kTcRows apart (plane t holds record t of every row): the gathers' record loads are
+// conflict-free.  Same arithmetic in the same order as the CSR variant on hcg_collate's output: identical bits.
+// Refused input (kCoo* flags): see k_tile_desc; the caller falls back to hcg_collate + hcg_gcn_forward.
+template <int F_, int NS, bool COO = false>
 __global__ void __launch_bounds__(NS * 256, 1)
 k_tc_fwd(const TcArgs a) {
 #ifdef HCG_TC_TIMING
@@ -376,6 +449,9 @@ k_tc_fwd(const TcArgs a) {
   constexpr int CW = 64 / TPR;    // hidden columns per thread (gather of layers >= 1, epilogue)
   constexpr int XW = 32 / TPR;    // input columns per thread (layer-0 gather)
   constexpr bool KSPLIT = NS == 3;
+  constexpr int NBS = COO ? kTcRows : 1;   // records between consecutive neighbour records of a row
+  __shared__ float s_lut[32];              // COO: (deg + fill)^-1/2 for deg = 0..31
+  __shared__ int s_bad[NS];                // COO: refusal flags of the slot
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ uint64_t bar_stage[NS][2];
   __shared__ uint64_t bar_mma[NS];
@@ -403,7 +479,7 @@ k_tc_fwd(const TcArgs a) {
   const int L = a.f.L;
 
   // ---- carve shared memory (one base pointer, word offsets: keeps every access an LDS / STS) -------
-  const TcSmemLayout lay = tc_layout(F, L, NS);
+  const TcSmemLayout lay = tc_layout(F, L, NS, COO);
   unsigned char* base = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
   float* smf = reinterpret_cast<float*>(base);
   int32_t* smi = reinterpret_cast<int32_t*>(base);
@@ -413,6 +489,7 @@ k_tc_fwd(const TcArgs a) {
   float* s_bias = reinterpret_cast<float*>(base + lay.bias);
   const int hb_w = (int)((lay.hbuf + (uint32_t)slot * lay.slot_bytes) >> 2);   // activation buffer, word offset
   const int nb_w = (int)((lay.nbr + (uint32_t)slot * lay.slot_bytes) >> 2);    // neighbour records
+  const int dg_w = (int)((lay.deg + (uint32_t)slot * lay.slot_bytes) >> 2);    // COO: in-degree counters
   const int sx = (int)((lay.xst + (uint32_t)slot * lay.slot_bytes) >> 2);      // x rows (one stage)
   const int cs_w0 = (int)((lay.cst + (uint32_t)slot * lay.slot_bytes) >> 2);   // CSR stage 0
   const int rw = (int)lay.rw, cw = (int)lay.cw, csw = (int)lay.csr_words;
@@ -433,6 +510,14 @@ k_tc_fwd(const TcArgs a) {
     tc::prep_weight_tiles(a.f.conv_w[l], 64, 64, wl_base + (size_t)(l - 1) * 2 * tc::kN * 64,
                           wl_base + (size_t)(l - 1) * 2 * tc::kN * 64 + tc::kN * 64, tid, kThreads);
   for (int idx = tid; idx < L * 64; idx += kThreads) s_bias[idx] = __ldg(a.f.conv_b[idx >> 6] + (idx & 63));
+  if (COO) {
+    if (tid < 32) {
+      const float r = __fdiv_rn(1.0f, __fsqrt_rn((float)tid + a.f.fill));
+      s_lut[tid] = isinf(r) ? 0.f : r;
+    }
+    if (tid < NS) s_bad[tid] = 0;
+    if (gt < kTcRows) smi[dg_w + gt] = 0;
+  }
   ptx::fence_proxy_async_smem();
   ptx::tc_fence_before_sync();
   __syncthreads();
@@ -483,6 +568,12 @@ k_tc_fwd(const TcArgs a) {
     int cA, cS;
     if (q == 0) { pA = reinterpret_cast<uintptr_t>(a.f.x + (int64_t)r0.y * F); cA = r0.z * F;
                   pS = reinterpret_cast<uintptr_t>(a.f.x + (int64_t)n0 * F); cS = n * F; }
+    else if (COO) {
+      // q = 1: sources, q = 2: targets of the graph's edges (int64: two words each); q = 3 has nothing to copy
+      const int64_t* row = a.ei + (q == 2 ? a.E : 0);
+      pA = reinterpret_cast<uintptr_t>(row + r0.w); cA = 2 * r2.x;
+      pS = reinterpret_cast<uintptr_t>(row + e0); cS = 2 * e;
+    }
     else if (q == 1) { pA = reinterpret_cast<uintptr_t>(a.f.rowptr + r0.y); cA = r0.z + 1;
                        pS = reinterpret_cast<uintptr_t>(a.f.rowptr + n0); cS = n + 1; }
     else if (q == 2) { pA = reinterpret_cast<uintptr_t>(a.f.col + r0.w); cA = r2.x;
@@ -504,7 +595,7 @@ k_tc_fwd(const TcArgs a) {
     }
     m->off[lane] = (gb ? (int)(bA >> 2) : 0) + leadS;
     // the metadata must be in place before the arrival that can complete the phase (release / acquire)
-    if (!have || manual) {
+    if (!have || manual || (COO && (q == 3 || cS == 0))) {
       ptx::mbar_arrive(bar);
     } else {
       ptx::mbar_expect_tx(bar, bS);   // this lane's arrival for the phase + its bytes in flight
@@ -592,6 +683,15 @@ k_tc_fwd(const TcArgs a) {
         const int n0 = gb ? mp->n0B : mp->n0A, n = gb ? nB : nA, e0 = gb ? mp->e0B : mp->e0A, e = gb ? mp->eB : eA;
         const int o0 = mp->off[4 * gb + 0], o1 = mp->off[4 * gb + 1], o2 = mp->off[4 * gb + 2], o3 = mp->off[4 * gb + 3];
         for (int idx = gt; idx < n * F; idx += kSlotThreads) smf[sx + o0 + idx] = __ldg(a.f.x + (int64_t)n0 * F + idx);
+        if (COO) {
+          const int2* es = reinterpret_cast<const int2*>(a.ei + e0);
+          const int2* ed = reinterpret_cast<const int2*>(a.ei + a.E + e0);
+          for (int idx = gt; idx < e; idx += kSlotThreads) {
+            *reinterpret_cast<int2*>(smi + srp + o1 + 2 * idx) = __ldg(es + idx);
+            *reinterpret_cast<int2*>(smi + scl + o2 + 2 * idx) = __ldg(ed + idx);
+          }
+          continue;
+        }
         for (int idx = gt; idx <= n; idx += kSlotThreads) smi[srp + o1 + idx] = __ldg(a.f.rowptr + n0 + idx);
         for (int idx = gt; idx < e; idx += kSlotThreads) smi[scl + o2 + idx] = __ldg(a.f.col + e0 + idx);
         for (int idx = gt; idx < n; idx += kSlotThreads) smf[sds + o3 + idx] = __ldg(a.f.dis + n0 + idx);
@@ -607,10 +707,73 @@ k_tc_fwd(const TcArgs a) {
     const int li = i - rowbase;               // row inside its graph
     const int jb = n0 - rowbase;              // tile row of batch node j = j - jb
     const int xt_o = sx + (inB ? mp->off[4] : mp->off[0]) - rowbase * F;   // x[tile row r][c] at smf[xt_o + r F + c]
-    const int nbo = nb_w + 2 * ((inB ? eA : 0) - e0);                     // record of CSR slot pos at smi[nbo + 2 pos]
+    const int nbo = COO ? nb_w + 2 * i                                    // COO: record t of this row at smi[nbo + 2 t kTcRows]
+                        : nb_w + 2 * ((inB ? eA : 0) - e0);               // record of CSR slot pos at smi[nbo + 2 pos]
     int beg = 0, deg = 0;
     float di = 0.f;
-    {
+    if (COO) {
+      // ---- A. every edge claims a record of its target row -------------------------------------------
+      int bad = 0;
+      const int etot = eA + mp->eB;
+      for (int k = gt; k < etot; k += kSlotThreads) {
+        const int eb = k >= eA;                    // edge of graph B
+        const int kk = eb ? k - eA : k;
+        const int2 sv = *reinterpret_cast<const int2*>(smi + srp + mp->off[4 * eb + 1] + 2 * kk);
+        const int2 dv = *reinterpret_cast<const int2*>(smi + scl + mp->off[4 * eb + 2] + 2 * kk);
+        const int gn0 = eb ? mp->n0B : mp->n0A, gn = eb ? nB : nA, rb = eb ? nA : 0;
+        const int ts = sv.x - gn0, td = dv.x - gn0;
+        if (sv.y != 0 || dv.y != 0 || (unsigned)ts >= (unsigned)gn || (unsigned)td >= (unsigned)gn || ts == td) {
+          bad |= kCooBadEdge;     // (a self-loop would be dropped and replaced by the fill-weight one: not handled here)
+          continue;
+        }
+        const int pos = atomicAdd(smi + dg_w + rb + td, 1);
+        if (pos < kTcCooDeg) smi[nb_w + 2 * (pos * kTcRows + rb + td)] = (k << 8) | (rb + ts);   // key: edge number, then the source's tile row
+        else bad |= kCooDegree;
+      }
+      if (bad) atomicOr(&s_bad[slot], bad);
+      ptx::named_bar_sync(bar_full, kSlotThreads);
+      // ---- B. order the row's records by edge number, attach the norms ----------------------------------
+      const int dtrue = row_ok ? smi[dg_w + i] : 0;
+      deg = dtrue < kTcCooDeg ? dtrue : kTcCooDeg;
+      di = row_ok ? s_lut[dtrue < 31 ? dtrue : 31] : 0.f;
+      const int wmax = __reduce_max_sync(0xffffffffu, deg);
+      if (cg == 0 && wmax > 0) {
+        int* kp = smi + nbo;                        // key of record t at kp[2 t kTcRows]
+        auto finish = [&](int t, int key) {        // (tile row of the source, norm)
+          const int j = key & 0xff;
+          const int dj = smi[dg_w + j];
+          const float w = s_lut[dj < 31 ? dj : 31] * di;
+          *reinterpret_cast<int2*>(kp + 2 * t * kTcRows) = make_int2(j, __float_as_int(w));
+        };
+        if (wmax <= 8) {   // sorting network in registers, sized by the warp's largest row
+          int r[8];
+#pragma unroll
+          for (int t = 0; t < 8; ++t) r[t] = (t < deg && (t < 4 || wmax > 4)) ? kp[2 * t * kTcRows] : 0x7fffffff;
+          if (wmax <= 4) {
+            key_cx(r[0], r[1]); key_cx(r[2], r[3]); key_cx(r[0], r[2]); key_cx(r[1], r[3]); key_cx(r[1], r[2]);
+          } else {         // 19 exchanges for eight keys
+            key_cx(r[0], r[1]); key_cx(r[2], r[3]); key_cx(r[4], r[5]); key_cx(r[6], r[7]);
+            key_cx(r[0], r[2]); key_cx(r[1], r[3]); key_cx(r[4], r[6]); key_cx(r[5], r[7]);
+            key_cx(r[1], r[2]); key_cx(r[5], r[6]); key_cx(r[0], r[4]); key_cx(r[3], r[7]);
+            key_cx(r[1], r[5]); key_cx(r[2], r[6]);
+            key_cx(r[1], r[4]); key_cx(r[3], r[6]);
+            key_cx(r[2], r[4]); key_cx(r[3], r[5]);
+            key_cx(r[3], r[4]);
+          }
+#pragma unroll
+          for (int t = 0; t < 8; ++t)
+            if (t < deg) finish(t, r[t]);
+        } else {           // a row with 9..16 records somewhere in the warp: insertion sort in place
+          for (int u = 1; u < deg; ++u) {
+            const int key = kp[2 * u * kTcRows];
+            int c = u - 1;
+            while (c >= 0 && kp[2 * c * kTcRows] > key) { kp[2 * (c + 1) * kTcRows] = kp[2 * c * kTcRows]; --c; }
+            kp[2 * (c + 1) * kTcRows] = key;
+          }
+          for (int t = 0; t < deg; ++t) finish(t, kp[2 * t * kTcRows]);
+        }
+      }
+    } else {
       const int rp_o = srp + (inB ? mp->off[5] : mp->off[1]);             // rowptr[n0 + r] at smi[rp_o + r]
       const int cl_o = scl + (inB ? mp->off[6] : mp->off[2]) - e0;        // col[pos] at smi[cl_o + pos]
       const int ds_o = sds + (inB ? mp->off[7] : mp->off[3]) - n0;        // dis[j] at smf[ds_o + j]
@@ -628,11 +791,12 @@ k_tc_fwd(const TcArgs a) {
     const int iself = row_ok ? i : 0;
     TC_TICK(2);
     ptx::named_bar_sync(bar_full, kSlotThreads);
+    if (COO && cg == 0) smi[dg_w + i] = 0;   // every norm has been taken: counters ready for the next tile
     TC_TICK(3);
     // every lane of the warp walks the same number of neighbour steps (the warp's largest degree)
     const int maxdeg = __reduce_max_sync(0xffffffffu, deg);
     const int2* nbp = reinterpret_cast<const int2*>(smi + nbo) + beg;
-    auto nb_at = [&](int t) { return t < deg ? nbp[t] : make_int2(iself, 0); };
+    auto nb_at = [&](int t) { return t < deg ? nbp[t * NBS] : make_int2(iself, 0); };
 
     // ---- layer 0: a_r = sum_j norm_rj x_j ; this thread's XW of the (up to) 32 columns ---------------
     if (warp_ok) {
@@ -645,10 +809,10 @@ k_tc_fwd(const TcArgs a) {
         // compile-time column count of every column group: min(XW, F - XW g), dispatched on the (warp-uniform) group
         constexpr int N0 = F_ < XW ? F_ : XW;
         constexpr int N1 = F_ - XW < 0 ? 0 : (F_ - XW < XW ? F_ - XW : XW);
-        if (cg == 0) gather_x<N0, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
-        else gather_x<N1, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
+        if (cg == 0) gather_x<N0, XW, NBS>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
+        else gather_x<N1, XW, NBS>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself);
       } else if (ncol > 0) {
-        gather_x<-1, XW>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself, ncol < XW ? ncol : XW);
+        gather_x<-1, XW, NBS>(acc, smf + xc, F, nbp, deg, maxdeg, iself, wself, ncol < XW ? ncol : XW);
       }
       tc::store_split16(acc, a_hi, a_lo, trow, cg * 16);
     }
@@ -792,6 +956,7 @@ k_tc_fwd(const TcArgs a) {
 
   ptx::tc_fence_before_sync();
   __syncthreads();
+  if (COO && a.kflags && gt == 0) a.kflags[slot_id] = s_bad[slot];
   if (tid < 32) ptx::tmem_dealloc(tmem_base_s, 512);
 }
 
@@ -837,7 +1002,7 @@ int launch_tile_desc(const int32_t* graph_ptr, const int32_t* rowptr, const int3
   HCG_CUDA_OK(cudaMemsetAsync(overflow_count, 0, sizeof(int), st));
   k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(graph_ptr, rowptr, col, dis, x, F, N, E, B, p.W, p.nslots,
                                                                           p.nwin, p.cap, tiles, counts, overflow_count, overflow_list,
-                                                                          overflow_flag);
+                                                                          overflow_flag, nullptr, nullptr, nullptr, nullptr, nullptr);
   HCG_LAUNCH_OK(st, "k_tile_desc");
   return HCG_OK;
 }
@@ -876,11 +1041,11 @@ static int tc_slots(int F, int L) {
   return env == 3 ? 3 : kTcDefaultSlots;
 }
 
-template <int F_, int NS>
+template <int F_, int NS, bool COO = false>
 static int launch_tc_variant(const TcArgs& a, int grid, size_t smem, cudaStream_t st) {
   static SmemConfigured configured;
-  if (int rc = ensure_dyn_smem(k_tc_fwd<F_, NS>, smem, configured)) return rc;
-  k_tc_fwd<F_, NS><<<(unsigned)grid, NS * 256, smem, st>>>(a);
+  if (int rc = ensure_dyn_smem(k_tc_fwd<F_, NS, COO>, smem, configured)) return rc;
+  k_tc_fwd<F_, NS, COO><<<(unsigned)grid, NS * 256, smem, st>>>(a);
   return HCG_OK;
 }
 
@@ -916,6 +1081,71 @@ int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStr
   o.list_count = w.overflow_count;
   const size_t osmem = fused_fwd_smem_bytes(f.F, f.L, o.ncap, o.ecap);
   return launch_fused_fwd(o, osmem, st, all_fit ? 1 : 0);
+}
+
+// ---- COO variant: edge list in, embeddings out --------------------------------------------------------
+struct TcCooWs {
+  TcTile* tiles;
+  int* counts;
+  int* dflags;     // refusal flags of k_tile_desc, one per slot
+  int* kflags;     // refusal flags of k_tc_fwd, one per slot
+  size_t bytes;
+};
+
+static TcCooWs carve_tc_coo(void* ws, int64_t B) {
+  Carver c(ws, (size_t)-1);
+  TcCooWs w{};
+  w.tiles = c.take<TcTile>(tc_tiles_capacity(B));
+  w.counts = c.take<int>((size_t)3 * kNumSMs + 1);
+  w.dflags = c.take<int>((size_t)3 * kNumSMs + 1);
+  w.kflags = c.take<int>((size_t)3 * kNumSMs + 1);
+  w.bytes = c.off;
+  return w;
+}
+
+size_t tc_fwd_coo_workspace_bytes(int64_t B) { return carve_tc_coo(nullptr, B).bytes; }
+size_t tc_fwd_coo_smem_bytes(int F, int L) { return tc_layout(F, L, 2, true).total; }
+int tc_fwd_coo_degree_cap() { return kTcCooDeg; }
+
+int launch_tc_fwd_coo(const FusedFwdArgs& f, const int64_t* edge_index, const int64_t* node_ptr, const int64_t* edge_ptr, int64_t N,
+                      int64_t E, void* ws, cudaStream_t st) {
+  if (f.B <= 0) return HCG_OK;
+  TcCooWs w = carve_tc_coo(ws, f.B);
+  const TcPlan p = tc_plan(f.B, 2);
+  const size_t smem = tc_layout(f.F, f.L, 2, true).total;
+  k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(nullptr, nullptr, nullptr, nullptr, f.x, f.F, N, E, f.B, p.W,
+                                                                          p.nslots, p.nwin, p.cap, w.tiles, w.counts, nullptr, nullptr,
+                                                                          nullptr, node_ptr, edge_ptr, edge_index, w.dflags, f.emb);
+  HCG_LAUNCH_OK(st, "k_tile_desc");
+  TcArgs a{};
+  a.f = f;
+  a.tiles = w.tiles;
+  a.counts = w.counts;
+  a.cap = p.cap;
+  a.N = N; a.E = E;
+  a.ei = edge_index;
+  a.kflags = w.kflags;
+  const int rc = f.F == 25 ? launch_tc_variant<25, 2, true>(a, p.grid, smem, st)
+               : f.F == 32 ? launch_tc_variant<32, 2, true>(a, p.grid, smem, st)
+                           : launch_tc_variant<0, 2, true>(a, p.grid, smem, st);
+  if (rc) return rc;
+  HCG_LAUNCH_OK(st, "k_tc_fwd_coo");
+  return HCG_OK;
+}
+
+// OR of the refusal flags the last launch_tc_fwd_coo with this workspace left (synchronises the stream)
+int tc_fwd_coo_flags(const void* ws, int64_t B, cudaStream_t st, int* flags) {
+  *flags = 0;
+  if (B <= 0) return HCG_OK;
+  TcCooWs w = carve_tc_coo(const_cast<void*>(ws), B);
+  const TcPlan p = tc_plan(B, 2);
+  static thread_local int host[2 * (3 * kNumSMs + 1)];
+  // dflags and kflags are adjacent up to the carver's alignment: two copies keep this independent of it
+  HCG_CUDA_OK(cudaMemcpyAsync(host, w.dflags, sizeof(int) * p.nslots, cudaMemcpyDeviceToHost, st));
+  HCG_CUDA_OK(cudaMemcpyAsync(host + p.nslots, w.kflags, sizeof(int) * p.nslots, cudaMemcpyDeviceToHost, st));
+  HCG_CUDA_OK(cudaStreamSynchronize(st));
+  for (int k = 0; k < 2 * p.nslots; ++k) *flags |= host[k];
+  return HCG_OK;
 }
 
 }  // namespace hcg

@@ -11,6 +11,12 @@ constexpr int kTcEcap = 512;          // CSR slots per tile (4 per node row: mol
 constexpr int kTcHPitch = 68;         // floats per activation row: 8 consecutive rows cover all banks for 128-bit access
 constexpr int kTcWinMax = 8;          // graphs per pairing window (at most)
 constexpr int kStatusCrossEdgeTc = 4;
+// COO variant of the forward kernel: refusal flags (HCG_COO_* of include/hcg.h)
+constexpr int kTcCooDeg = 16;         // neighbour records per node row (in-degree cap)
+constexpr int kCooTooLarge = 1;       // a graph has no nodes, more than kTcRows nodes or more than kTcEcap edges
+constexpr int kCooBadEdge = 2;        // an edge leaves its graph's node range, or is a self-loop
+constexpr int kCooDegree = 4;         // a node has more than kTcCooDeg incoming edges
+constexpr int kCooBadOffsets = 8;     // node / edge offsets outside [0, N] / [0, E]
 constexpr int kTileManual = 1;        // TcTile.flags: a 16-byte granular copy window would leave an input array
 
 struct __align__(16) TcTile {   // 64 bytes: one tile of the work list

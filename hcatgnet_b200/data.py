@@ -44,6 +44,9 @@ class Batch:
         # the edge count of the largest graph, as a host integer; None / 0 = unknown
         self.edge_ptr = None
         self.max_graph_edges = 0
+        # largest number of incoming edges of any node (host integer), None = unknown: with the sizes above it lets
+        # inference run straight from the edge list (hcg_gcn_forward_coo: no collate)
+        self.max_in_degree = None
 
     @classmethod
     def from_data_list(cls, graphs: Sequence) -> "Batch":
@@ -74,6 +77,8 @@ class Batch:
         if ecount.numel():
             out.edge_ptr[1:] = torch.cumsum(ecount, 0)
         out.max_graph_edges = int(ecount.max()) if ecount.numel() else 0
+        out.max_in_degree = int(torch.bincount(edge_index[1]).max()) if edge_index.numel() and int(edge_index.min()) >= 0 else \
+            (0 if not edge_index.numel() else None)
         return out
 
     @property

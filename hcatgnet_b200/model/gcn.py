@@ -19,7 +19,7 @@ import math
 import torch
 import torch.nn as nn
 
-from .. import ops
+from .. import _lib, ops
 from .networks import BaseNetwork
 
 
@@ -150,6 +150,18 @@ class _GCNBase(BaseNetwork):
                                                  (edge_mask is not None and edge_mask.requires_grad))
         if edge_weight is not None and edge_weight.requires_grad and torch.is_grad_enabled():
             return self._run_edge_weight_grad(x, edge_index, batch, num_graphs, edge_weight, home, device)
+        if not need_grad and edge_weight is None and edge_mask is None and x.is_cuda and edge_index.is_cuda and \
+                getattr(cache_on, "_hcg_plan", None) is None and ops.edge_list_hints_ok(cache_on) and \
+                cache_on.ptr.is_cuda and cache_on.edge_ptr.is_cuda and x.dtype == torch.float32 and \
+                edge_index.dtype == torch.int64 and cache_on.ptr.dtype == torch.int64 and \
+                _lib.load().hcg_config_get(_lib.HCG_CFG_FORWARD_PATH) == _lib.PATH_AUTO:
+            # inference on a batch that carries its offsets and size facts: no collate, the conv kernel reads the
+            # edge list itself (refused -> None -> the general path below)
+            pd = [ops.to_device(p, device, torch.float32) for p in params]
+            res = ops.forward_edge_list(x.contiguous(), edge_index.contiguous(), cache_on.ptr, cache_on.edge_ptr,
+                                        self._dims(), pd, validate=self.validate_inputs)
+            if res is not None:
+                return res
         plan = ops.cached_collate(cache_on, edge_index, batch, x.shape[0], num_graphs, device,
                                   edge_weight=edge_weight, improved=bool(self.improved), transpose=need_grad,
                                   validate=self.validate_inputs, max_graph_nodes=_max_nodes_hint(cache_on),

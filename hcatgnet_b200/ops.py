@@ -317,6 +317,59 @@ def forward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, save: b
     return out, emb, saved_t
 
 
+# capacity of hcg_gcn_forward_coo (include/hcg.h): nodes / edges per graph, incoming edges per node
+COO_MAX_NODES, COO_MAX_EDGES, COO_MAX_IN_DEGREE = 128, 512, 16
+
+
+def edge_list_hints_ok(holder) -> bool:
+    """The batch object vouches (host-side integers, no device read) for what ``hcg_gcn_forward_coo`` requires."""
+    if holder is None or getattr(holder, "edges_grouped", None) is not True:
+        return False
+    if getattr(holder, "ptr", None) is None or getattr(holder, "edge_ptr", None) is None:
+        return False
+    nmax, emax = int(getattr(holder, "max_graph_nodes", 0) or 0), int(getattr(holder, "max_graph_edges", 0) or 0)
+    dmax = getattr(holder, "max_in_degree", None)
+    return 0 < nmax <= COO_MAX_NODES and emax <= COO_MAX_EDGES and dmax is not None and 0 <= int(dmax) <= COO_MAX_IN_DEGREE
+
+
+def forward_edge_list(x: torch.Tensor, edge_index: torch.Tensor, ptr: torch.Tensor, edge_ptr: torch.Tensor, dims: NetDims,
+                      params, fill: float = 1.0, validate: bool = True):
+    """Inference straight from the batch's edge list: one ``hcg_gcn_forward_coo`` call, no collate, no ``GraphPlan``
+    (the conv kernel builds each graph's normalised neighbour lists in shared memory).  Same bits as
+    ``collate`` + ``forward_raw``.  Returns ``(out, emb)``, or ``None`` when the network's shape cannot take the path
+    or - with ``validate`` (one small read-back, a stream sync) - when the device refused the batch (oversize graph,
+    in-degree above 16, self-loop, edge between graphs): the caller then goes through ``collate``.  Without
+    ``validate`` the caller vouches for the batch (``edge_list_hints_ok``)."""
+    lib = _lib.load()
+    device = x.device
+    _check_param_shapes(dims, params)
+    pstruct = _params_struct(dims, params)
+    if not lib.hcg_forward_coo_supported(C.byref(pstruct)):
+        return None
+    if edge_index.dim() != 2 or edge_index.shape[0] != 2 or edge_index.dtype != torch.int64 or not edge_index.is_contiguous():
+        raise ValueError("edge_index must be a contiguous int64 [2, E] tensor")
+    B, N, E = int(ptr.numel()) - 1, int(x.shape[0]), int(edge_index.shape[1])
+    if x.shape != (N, dims.F) or x.dtype != torch.float32 or not x.is_contiguous():
+        raise ValueError(f"x must be a contiguous float32 [N, {dims.F}] tensor")
+    if edge_ptr.numel() != B + 1 or ptr.dtype != torch.int64 or edge_ptr.dtype != torch.int64:
+        raise ValueError("ptr / edge_ptr must be int64 [B + 1]")
+    f32 = dict(dtype=torch.float32, device=device)
+    with torch.cuda.device(device):
+        out = torch.empty(B, dims.C, **f32)
+        emb = torch.empty(B, 2 * dims.H, **f32)
+        ws = _workspace(lib.hcg_forward_coo_workspace_bytes(B, C.byref(pstruct)), device)
+        st = _stream(device)
+        _lib.check(lib.hcg_gcn_forward_coo(_ptr(x), _ptr(edge_index), _ptr(ptr), _ptr(edge_ptr), N, E, B, float(fill),
+                                           C.byref(pstruct), _ptr(out), _ptr(emb), _ptr(ws), ws.numel(), st))
+        ws.record_stream(torch.cuda.current_stream(device))
+        if validate:
+            flags = C.c_int32(0)
+            _lib.check(lib.hcg_forward_coo_status(_ptr(ws), B, st, C.byref(flags)))
+            if flags.value:
+                return None
+    return out, emb
+
+
 def backward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, saved_t, emb, g_out, g_emb, need_gx: bool,
                  flat_out: torch.Tensor | None = None, edge_mask=None, need_gmask: bool = False):
     """One ``hcg_gcn_backward`` call.  Returns (g_x or None, list of parameter grads) — and the gradient

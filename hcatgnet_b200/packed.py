@@ -77,6 +77,10 @@ class PackedDataset:
         # packer verified what hcg_collate's graph-local path takes for granted (no self-loop edges; every graph
         # within its per-graph capacity).  Unverified images leave the choice to hcg_collate's own device check.
         self.max_graph_edges, self.flags = int(h2[0]), int(h2[1])
+        # 1 + the largest in-degree of any node (0 in images of older writers: unknown)
+        self.max_in_degree = int(blob[88:96].view(np.int64)[0]) - 1
+        if self.max_in_degree < 0:
+            self.max_in_degree = None
         self.layout, total = _layout(self.G, self.N, self.E, self.F, self.Fu, self.Ff, self.edge_kind)
         if blob.size < total:
             raise ValueError(f"packed graph image truncated: {blob.size} of {total} bytes")
@@ -120,6 +124,7 @@ class PackedDataset:
         emax = int(np.diff(edge_ptr).max()) if G else 0
         groupable = (not E or not bool(np.any(ei[0] == ei[1]))) and nmax <= GROUPED_MAX_NODES and emax <= GROUPED_MAX_EDGES
         blob[72:88].view(np.int64)[:] = [emax, FLAG_GROUPABLE if groupable else 0]
+        blob[88:96].view(np.int64)[:] = [1 + (int(np.bincount(ei[1]).max()) if E else 0)]
         self = cls(blob)
         self._owner = blob_t
         self.col_slot[:] = col_slot
@@ -327,6 +332,7 @@ class DeviceGraphStore:
         idx = torch.from_numpy(ds.idx[ids_np].copy() if ids_np is not None else np.array(ds.idx))
         out = Batch(x, ei, bvec, meta_d[0], y, idx, B, edges_grouped=True if (ds.flags & FLAG_GROUPABLE) else None)
         out.max_graph_nodes, out.max_graph_edges = nmax, emax
+        out.max_in_degree = ds.max_in_degree
         out.edge_ptr = meta_d[1]
         out._keepalive = meta_d
         return out
@@ -392,6 +398,7 @@ class DeviceGraphStore:
         out = Batch(x, ei, bvec, node_ptr_d, y, idx, B, edges_grouped=True if (ds.flags & FLAG_GROUPABLE) else None)
         out.max_graph_nodes = int(ds.max_graph_nodes)
         out.max_graph_edges = int(ds.max_graph_edges)
+        out.max_in_degree = ds.max_in_degree
         out.edge_ptr = edge_ptr_d
         out._keepalive = self.blob_dev
         return out

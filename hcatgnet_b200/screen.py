@@ -66,6 +66,7 @@ class DevicePrefetcher:
                       edges_grouped=getattr(h, "edges_grouped", None))
             d.max_graph_nodes = getattr(h, "max_graph_nodes", 0)
             d.max_graph_edges = getattr(h, "max_graph_edges", 0)
+            d.max_in_degree = getattr(h, "max_in_degree", None)
             d.edge_ptr = mv(getattr(h, "edge_ptr", None)) if ptr_d is not None else None
             ev = torch.cuda.Event()
             ev.record(self.copy_stream)

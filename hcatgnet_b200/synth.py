@@ -92,4 +92,5 @@ def synth_batch(num_graphs: int, n_features: int = 25, seed: int = 20232023, pin
               torch.arange(num_graphs, dtype=torch.int64), num_graphs, edges_grouped=True)
     b.edge_ptr = torch.from_numpy(d["edge_ptr"])
     b.max_graph_edges = int(np.diff(d["edge_ptr"]).max()) if num_graphs else 0
+    b.max_in_degree = int(np.bincount(d["edge_index"][1]).max()) if d["edge_index"].size else 0
     return b.pin_memory() if pin else b

@@ -283,6 +283,35 @@ int hcg_gcn_forward(const HcgGraph* g, const float* x, const HcgParams* p,
                     float* out, float* emb, const HcgSaved* saved,
                     void* ws, size_t ws_bytes, void* stream);
 
+/*
+ * Inference straight from the batch as torch_geometric holds it (`Batch.x`, `Batch.edge_index`, `Batch.ptr`; the
+ * call of the reference this replaces is `model(batch)` under torch.no_grad, utils/utils_model.py:83-96): no
+ * hcg_collate, no HcgGraph.  The conv kernel stages each graph's slice of the int64 edge list and builds the
+ * normalised neighbour lists in shared memory (add_remaining_self_loops + the symmetric degree norm of
+ * GCNConv.forward), so the CSR never exists in HBM.  Results carry the same bits as hcg_collate + hcg_gcn_forward.
+ *
+ * edge_index: int64 [2, E], the edges of graph g contiguous at [edge_ptr[g], edge_ptr[g+1]) (what
+ *             Batch.from_data_list produces);  node_ptr, edge_ptr: int64 [B + 1] device arrays.
+ * Preconditions, checked ON THE DEVICE and reported by hcg_forward_coo_status as HCG_COO_* bits: every graph has
+ * 1..128 nodes and at most 512 edges, every node at most 16 incoming edges, no self-loops in the input, no edge
+ * between two graphs.  When a bit is set the outputs of that call are unspecified (all memory accesses stay in
+ * bounds): run hcg_collate + hcg_gcn_forward instead.  hcg_forward_coo_supported: 1 when the network's shape
+ * (H = 64, F <= 32, conv layers that fit shared memory) can take this path at all.
+ */
+enum {
+  HCG_COO_TOO_LARGE = 1,    /* a graph without nodes, with more than 128 nodes or more than 512 edges */
+  HCG_COO_BAD_EDGE = 2,     /* self-loop, or an endpoint outside the graph that owns the edge slice */
+  HCG_COO_DEGREE = 4,       /* a node with more than 16 incoming edges */
+  HCG_COO_BAD_OFFSETS = 8   /* node_ptr / edge_ptr entry outside [0, N] / [0, E] */
+};
+int hcg_forward_coo_supported(const HcgParams* p);
+size_t hcg_forward_coo_workspace_bytes(int64_t B, const HcgParams* p);
+int hcg_gcn_forward_coo(const float* x, const int64_t* edge_index, const int64_t* node_ptr, const int64_t* edge_ptr,
+                        int64_t N, int64_t E, int64_t B, float fill, const HcgParams* p, float* out, float* emb,
+                        void* ws, size_t ws_bytes, void* stream);
+/* Synchronises `stream` and ORs the HCG_COO_* bits of the last hcg_gcn_forward_coo that used `ws` into *flags. */
+int hcg_forward_coo_status(const void* ws, int64_t B, void* stream, int32_t* flags);
+
 /* ---- backward (replaces autograd over the ops above) -------------------------------------- */
 
 size_t hcg_backward_workspace_bytes(int64_t N, int64_t E, int64_t B, const HcgParams* p);

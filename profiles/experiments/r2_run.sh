@@ -1,10 +1,12 @@
 set -x
-python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-profile --no-sub > gpurun_out/plain.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -s 40 -c 200 --csv --log-file gpurun_out/r2_launches_infer.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-profile --no-sub > gpurun_out/ncu1.log 2>&1
-python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-profile --no-sub > gpurun_out/plain.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:k_tc_fwd -s 4 -c 1 -o gpurun_out/r2_tc_fwd_final -f python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-profile --no-sub > gpurun_out/ncu2.log 2>&1
-python bench.py --mode train --steps 3 --warmup 3 --no-cpu-baseline --no-profile > gpurun_out/plain.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:k_tc_bwd -s 4 -c 1 -o gpurun_out/r2_tc_bwd -f python bench.py --mode train --steps 3 --warmup 3 --no-cpu-baseline --no-profile > gpurun_out/ncu3.log 2>&1
-python bench.py --mode train --steps 3 --warmup 3 --no-cpu-baseline --no-profile > gpurun_out/plain.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -s 60 -c 200 --csv --log-file gpurun_out/r2_launches_train.csv python bench.py --mode train --steps 3 --warmup 3 --no-cpu-baseline --no-profile > gpurun_out/ncu4.log 2>&1
-tail -2 gpurun_out/ncu2.log | cut -c1-150; tail -2 gpurun_out/ncu3.log | cut -c1-150
+for k in 1 2; do
+timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-sub 2>&1 | tail -1 > gpurun_out/b$k.json
+done
+HCG_BENCH_CSR=1 timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-sub 2>&1 | tail -1 > gpurun_out/b3.json
+timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-sub --no-profile 2>&1 | tail -1 > gpurun_out/b4.json
+python - <<'PY'
+import json
+for k in (1,2,3,4):
+    r=json.loads(open(f"gpurun_out/b{k}.json").read())
+    print(k, r["value"], r["e2e"]["value"], r["e2e"].get("wall_ms_per_step"), r.get("e2e_packed",{}).get("value"), r.get("e2e_packed",{}).get("ms_per_step"))
+PY

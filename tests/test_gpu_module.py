@@ -73,13 +73,20 @@ def test_plan_is_cached_on_batch_and_eval_needs_no_grad(pkg):
     model = pkg.make_network("GCN", pkg.default_options(), 25).to("cuda").eval()
     batch = pkg.Batch.from_data_list(graphs).to("cuda")
     with torch.no_grad():
-        a = model(batch)
+        a0 = model(batch)   # inference on a batch that carries its offsets and size facts: straight from the edge list, no plan
+    assert not hasattr(batch, "_hcg_plan")
+    c = model(batch)  # grad mode on (reference eval_network has no no_grad): collate with the transpose, plan cached
     plan = batch._hcg_plan[1]
+    assert plan.has_transpose and torch.equal(a0, c.detach())
     with torch.no_grad():
+        a = model(batch)    # a cached plan is reused by later inference calls
         b = model(batch)
-    assert batch._hcg_plan[1] is plan and torch.equal(a, b)
-    c = model(batch)  # grad mode on (reference eval_network has no no_grad): plan upgraded with transpose
-    assert batch._hcg_plan[1].has_transpose and torch.equal(a, c.detach())
+    assert batch._hcg_plan[1] is plan and torch.equal(a, b) and torch.equal(a, a0)
+    # a batch without the host-side size facts (e.g. built by hand): inference collates, and caches the plan
+    bare = pkg.Batch(batch.x, batch.edge_index, batch.batch, None, batch.y, None, batch.num_graphs)
+    with torch.no_grad():
+        d = model(bare)
+    assert hasattr(bare, "_hcg_plan") and torch.equal(d, a0)
 
 
 def test_explain_signature_and_pickle(pkg):
