@@ -102,6 +102,8 @@ SIGNATURES = {
     "hcg_forward_coo_workspace_bytes": (C.c_size_t, [C.c_int64, C.POINTER(HcgParams)]),
     "hcg_gcn_forward_coo": (C.c_int, [_fp, _fp, _fp, _fp, C.c_int64, C.c_int64, C.c_int64, C.c_float, C.POINTER(HcgParams),
                                       _fp, _fp, _fp, C.c_size_t, _fp]),
+    "hcg_gcn_forward_coo_static": (C.c_int, [_fp, _fp, _fp, _fp, C.c_int64, C.c_int64, C.c_int64, C.c_float, C.POINTER(HcgParams),
+                                             _fp, _fp, C.POINTER(C.c_int32), _fp]),
     "hcg_forward_coo_status": (C.c_int, [_fp, C.c_int64, _fp, C.POINTER(C.c_int32)]),
     "hcg_backward_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.POINTER(HcgParams)]),
     "hcg_gcn_backward": (C.c_int, [C.POINTER(HcgGraph), _fp, C.POINTER(HcgParams), C.POINTER(HcgSaved), _fp, _fp, _fp,

@@ -8,6 +8,8 @@
 // Â = D^-1/2 (A + I) D^-1/2 lives in the dst-sorted CSR built by hcg_collate; every reduction
 // (neighbour sum, segment max/mean, weight-gradient sums) walks its operands in a fixed order,
 // so there are no floating-point atomics and results are run-to-run identical.
+#include <atomic>
+
 #include "hcg_common.cuh"
 #include "hcg_fused.cuh"
 #include "hcg_mma.cuh"
@@ -1349,6 +1351,57 @@ extern "C" int hcg_forward_coo_status(const void* ws, int64_t B, void* stream, i
   const int rc = tc_fwd_coo_flags(ws, B, static_cast<cudaStream_t>(stream), &f);   // (the tile work list opens the workspace)
   *flags = f;
   return rc;
+}
+
+// ---- the same forward with NO caller workspace and no allocation of any kind -------------------------
+// (no counterpart in the reference: added for callers that cannot allocate -
+//  code under CUDA graph capture, tight serving loops.)  The scratch of hcg_gcn_forward_coo - the tile work list
+// k_tile_desc writes and k_tc_fwd reads, the per-slot refusal flags, the hidden rows of a readout deeper than the
+// default - lives in one file-scope device array.  Every GPU that loads the library holds its kCooStaticBytes until
+// exit.  The array is shared by every call on a device and keeps the last call's contents: nothing in it has to start
+// at zero (every word a call reads, that call's own kernels have written first), but two calls that overlap on the
+// GPU (different streams, no ordering between them) race on it.
+constexpr int64_t kCooStaticMaxGraphs = 16384;
+constexpr size_t kCooStaticBytes = 6u << 20;     // 6 MiB: a 16384-graph batch of the default network needs 5.1 MiB
+static __device__ __align__(256) unsigned char g_coo_static_scratch[kCooStaticBytes];
+
+// Device address of the array on the CURRENT device (in host code the array's name is only a handle for
+// cudaGetSymbolAddress, not an address a kernel could use); looked up once per device.
+static int coo_static_scratch(void** out) {
+  constexpr int kMaxDevices = 64;
+  static std::atomic<void*> cache[kMaxDevices];
+  int dev = 0;
+  HCG_CUDA_OK(cudaGetDevice(&dev));
+  HCG_REQUIRE(dev >= 0 && dev < kMaxDevices, HCG_ERR_UNSUPPORTED, "device ordinal %d outside [0, %d)", dev, kMaxDevices);
+  void* ptr = cache[dev].load(std::memory_order_acquire);
+  if (ptr == nullptr) {
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_coo_static_scratch);
+    if (e != cudaSuccess || ptr == nullptr)
+      return set_err(HCG_ERR_CUDA, "cudaGetSymbolAddress(static scratch) on device %d failed: %s", dev, cudaGetErrorString(e));
+    cache[dev].store(ptr, std::memory_order_release);   // (two threads racing here store the same address)
+  }
+  *out = ptr;
+  return HCG_OK;
+}
+
+extern "C" int hcg_gcn_forward_coo_static(const float* x, const int64_t* edge_index, const int64_t* node_ptr,
+                                          const int64_t* edge_ptr, int64_t N, int64_t E, int64_t B, float fill,
+                                          const HcgParams* p, float* out, float* emb, int32_t* flags, void* stream) {
+  int rc = check_params(p);
+  if (rc) return rc;
+  HCG_REQUIRE(B >= 0 && B <= kCooStaticMaxGraphs, HCG_ERR_WORKSPACE,
+              "hcg_gcn_forward_coo_static takes at most %lld graphs per call, got %lld (use hcg_gcn_forward_coo with a workspace)",
+              (long long)kCooStaticMaxGraphs, (long long)B);
+  const size_t need = carve_coo(nullptr, B, p).bytes;
+  HCG_REQUIRE(need <= kCooStaticBytes, HCG_ERR_WORKSPACE,
+              "hcg_gcn_forward_coo_static: this network needs %zu bytes of scratch for %lld graphs, the static array holds %zu",
+              need, (long long)B, kCooStaticBytes);
+  void* scratch = nullptr;
+  rc = coo_static_scratch(&scratch);
+  if (rc) return rc;
+  rc = hcg_gcn_forward_coo(x, edge_index, node_ptr, edge_ptr, N, E, B, fill, p, out, emb, scratch, kCooStaticBytes, stream);
+  if (rc || flags == nullptr) return rc;
+  return hcg_forward_coo_status(scratch, B, stream, flags);
 }
 
 extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgParams* p, const HcgSaved* saved,

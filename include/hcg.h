@@ -312,6 +312,25 @@ int hcg_gcn_forward_coo(const float* x, const int64_t* edge_index, const int64_t
 /* Synchronises `stream` and ORs the HCG_COO_* bits of the last hcg_gcn_forward_coo that used `ws` into *flags. */
 int hcg_forward_coo_status(const void* ws, int64_t B, void* stream, int32_t* flags);
 
+/*
+ * hcg_gcn_forward_coo for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and results as hcg_gcn_forward_coo, but no workspace argument: the scratch (tile work list,
+ * refusal flags, hidden rows of a deeper readout) is a file-scope device array of 6 MiB inside the library, held by
+ * every GPU that loads it until the process exits.  The call performs no cudaMalloc / cudaFree and calls no
+ * allocating library routine (with hcg_profile_enable off, the default).
+ * Limits: B <= 16384 graphs per call and a scratch need (hcg_forward_coo_workspace_bytes) of at most 6 MiB - the
+ * default network at 16384 graphs needs 5.1 MiB; beyond either the call returns HCG_ERR_WORKSPACE.
+ * The array is shared by all calls on a device and keeps the last call's contents (nothing in it needs clearing:
+ * each call writes every word it later reads); calls that OVERLAP on the GPU - different streams without an
+ * ordering between them - race on it: serialise them or use hcg_gcn_forward_coo with one workspace per stream.
+ * flags: NULL (no read-back, fully asynchronous), or a host pointer that receives the HCG_COO_* bits of this call
+ * (synchronises `stream`).
+ */
+int hcg_gcn_forward_coo_static(const float* x, const int64_t* edge_index, const int64_t* node_ptr,
+                               const int64_t* edge_ptr, int64_t N, int64_t E, int64_t B, float fill,
+                               const HcgParams* p, float* out, float* emb, int32_t* flags, void* stream);
+
 /* ---- backward (replaces autograd over the ops above) -------------------------------------- */
 
 size_t hcg_backward_workspace_bytes(int64_t N, int64_t E, int64_t B, const HcgParams* p);
