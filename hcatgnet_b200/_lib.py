@@ -57,6 +57,12 @@ class HcgSaved(C.Structure):
     _fields_ = [("acts", _fp * HCG_MAX_CONV), ("hid", _fp * HCG_MAX_READOUT)]
 
 
+class HcgEnsemble(C.Structure):
+    _fields_ = [("M", C.c_int32), ("F", C.c_int32), ("H", C.c_int32), ("C", C.c_int32), ("slope", C.c_float),
+                ("reserved0", C.c_int32), ("conv_w0", _fp), ("conv_b0", _fp), ("conv_w1", _fp), ("conv_b1", _fp),
+                ("ro_w0", _fp), ("ro_b0", _fp), ("ro_w1", _fp), ("ro_b1", _fp)]
+
+
 class HcgError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"libhcg error {code} ({ERR_NAMES.get(code, '?')}): {msg}")
@@ -88,6 +94,10 @@ SIGNATURES = {
     "hcg_sizeof_params": (C.c_size_t, []),
     "hcg_sizeof_grads": (C.c_size_t, []),
     "hcg_sizeof_saved": (C.c_size_t, []),
+    "hcg_sizeof_ensemble": (C.c_size_t, []),
+    "hcg_ensemble_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int32]),
+    "hcg_gcn_forward_coo_ensemble": (C.c_int, [_fp, _fp, _fp, _fp, C.c_int64, C.c_int64, C.c_int64, C.c_float,
+                                               C.POINTER(HcgEnsemble), _fp, _fp, _fp, C.c_size_t, _fp]),
     "hcg_collate_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.c_int]),
     "hcg_collate": (C.c_int, [_fp, C.c_int64, _fp, C.c_int64, C.c_int64, C.c_float, _fp, C.c_float, C.c_int,
                               _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp,

@@ -62,6 +62,15 @@ int launch_tc_fwd_coo(const FusedFwdArgs& a, const int64_t* edge_index, const in
                       int64_t E, void* ws, cudaStream_t st);
 int tc_fwd_coo_flags(const void* ws, int64_t B, cudaStream_t st, int* flags);
 
+// one-pass ensemble variant (hcg_tc_ens.cu): M models (stacked conv weights: w0 [M,64,F], b0 [M,64], w1 [M,64,64],
+// b1 [M,64]) over one batch; emb [M,B,128]; wimg: scratch of tc_fwd_ens_image_floats(M) floats; ws as the COO variant's
+// (tc_fwd_coo_workspace_bytes, flags by tc_fwd_coo_flags).  Two conv layers, H = 64, F <= 32.
+size_t tc_fwd_ens_smem_bytes(int F);
+size_t tc_fwd_ens_image_floats(int M);
+int launch_tc_fwd_ens(const float* x, const int64_t* edge_index, const int64_t* node_ptr, const int64_t* edge_ptr, int64_t N, int64_t E,
+                      int64_t B, int M, int F, float slope, float fill, const float* w0, const float* b0, const float* w1,
+                      const float* b1, float* wimg, float* emb, void* ws, cudaStream_t st);
+
 // ---- graph-resident backward (hcg_fused_bwd.cu): H == 64, two conv layers, F <= 32 ---------------
 struct FusedBwdArgs {
   const int32_t* t_rowptr;        // transposed (src-sorted) CSR

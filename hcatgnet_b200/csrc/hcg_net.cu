@@ -566,10 +566,10 @@ k_pool(const float* __restrict__ h, const int32_t* __restrict__ graph_ptr, int64
 constexpr int RO_G = 64, RO_IN = 128, RO_HID = 64, RO_KC = 32;
 constexpr int RO_FG = 32;  // graphs per block of the forward head (the backward keeps RO_G)
 
-__global__ void __launch_bounds__(256)
-k_readout2(const float* __restrict__ emb, const float* __restrict__ W1, const float* __restrict__ b1,
-           const float* __restrict__ W2, const float* __restrict__ b2, float* __restrict__ hid_save,
-           float* __restrict__ out, int64_t B, int C, float slope) {
+__device__ __forceinline__ void
+readout2_block(const float* __restrict__ emb, const float* __restrict__ W1, const float* __restrict__ b1,
+               const float* __restrict__ W2, const float* __restrict__ b2, float* __restrict__ hid_save,
+               float* __restrict__ out, int64_t B, int C, float slope) {
   __shared__ __align__(16) float Es[RO_KC][RO_FG + 4];   // [k][graph]
   __shared__ __align__(16) float Ws[RO_KC][RO_HID + 4];  // [k][unit]
   __shared__ float Hs[RO_FG][RO_HID + 1];
@@ -620,6 +620,23 @@ k_readout2(const float* __restrict__ emb, const float* __restrict__ W1, const fl
     for (int o = 0; o < RO_HID; ++o) s = fmaf(Hs[g][o], W2[c * RO_HID + o], s);
     out[(g0 + g) * C + c] = s + b2[c];
   }
+}
+
+__global__ void __launch_bounds__(256)
+k_readout2(const float* __restrict__ emb, const float* __restrict__ W1, const float* __restrict__ b1,
+           const float* __restrict__ W2, const float* __restrict__ b2, float* __restrict__ hid_save,
+           float* __restrict__ out, int64_t B, int C, float slope) {
+  readout2_block(emb, W1, b1, W2, b2, hid_save, out, B, C, slope);
+}
+
+// the same head for the M models of an ensemble in one launch: blockIdx.y = model; stacked weights
+// (W1 [M,64,128], b1 [M,64], W2 [M,C,64], b2 [M,C]), emb [M,B,128], out [M,B,C]
+__global__ void __launch_bounds__(256)
+k_readout2_ens(const float* __restrict__ emb, const float* __restrict__ W1, const float* __restrict__ b1,
+               const float* __restrict__ W2, const float* __restrict__ b2, float* __restrict__ out, int64_t B, int C, float slope) {
+  const int64_t m = blockIdx.y;
+  readout2_block(emb + m * B * RO_IN, W1 + m * RO_HID * RO_IN, b1 + m * RO_HID, W2 + m * C * RO_HID, b2 + m * C, nullptr,
+                 out + m * B * C, B, C, slope);
 }
 
 // ==========================================================================================
@@ -1351,6 +1368,61 @@ extern "C" int hcg_forward_coo_status(const void* ws, int64_t B, void* stream, i
   const int rc = tc_fwd_coo_flags(ws, B, static_cast<cudaStream_t>(stream), &f);   // (the tile work list opens the workspace)
   *flags = f;
   return rc;
+}
+
+// ---- one-pass ensemble forward ------------------------------------------------
+struct EnsWs {
+  char* tc;
+  float* wimg;
+  size_t bytes;
+};
+static EnsWs carve_ens(void* ws, int64_t B, int M) {
+  Carver c(ws, (size_t)-1);
+  EnsWs w{};
+  w.tc = c.take<char>(tc_fwd_coo_workspace_bytes(B));   // first: hcg_forward_coo_status finds the flags from B alone
+  w.wimg = c.take<float>(tc_fwd_ens_image_floats(M) + 4);
+  w.bytes = c.off;
+  return w;
+}
+
+static int check_ensemble(const HcgEnsemble* e) {
+  HCG_REQUIRE(e != nullptr, HCG_ERR_INVALID_ARG, "ensemble is NULL");
+  HCG_REQUIRE(e->M >= 1 && e->M <= 4096, HCG_ERR_INVALID_ARG, "ensemble of %d models", (int)e->M);
+  HCG_REQUIRE(e->H == kFusedH && e->F >= 1 && e->F <= 32 && e->C >= 1 && e->C <= 64, HCG_ERR_UNSUPPORTED,
+              "one-pass ensemble forward needs H == %d, F <= 32, C <= 64 (got H=%d F=%d C=%d)", kFusedH, (int)e->H, (int)e->F, (int)e->C);
+  HCG_REQUIRE(e->slope >= 0.f && e->slope <= 1.f, HCG_ERR_UNSUPPORTED, "LeakyReLU slope %g outside [0, 1]", (double)e->slope);
+  HCG_REQUIRE(e->conv_w0 && e->conv_b0 && e->conv_w1 && e->conv_b1 && e->ro_w0 && e->ro_b0 && e->ro_w1 && e->ro_b1,
+              HCG_ERR_INVALID_ARG, "NULL weight pointer in the ensemble");
+  return HCG_OK;
+}
+
+extern "C" size_t hcg_ensemble_workspace_bytes(int64_t B, int32_t M) {
+  if (B < 0 || M < 1) return 0;
+  return carve_ens(nullptr, B, M).bytes;
+}
+
+extern "C" int hcg_gcn_forward_coo_ensemble(const float* x, const int64_t* edge_index, const int64_t* node_ptr,
+                                            const int64_t* edge_ptr, int64_t N, int64_t E, int64_t B, float fill,
+                                            const HcgEnsemble* ens, float* out, float* emb, void* ws, size_t ws_bytes,
+                                            void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = check_ensemble(ens);
+  if (rc) return rc;
+  HCG_REQUIRE(N >= 0 && E >= 0 && B >= 0 && N < INT32_MAX && E < INT32_MAX, HCG_ERR_INVALID_ARG, "bad sizes N=%lld E=%lld B=%lld",
+              (long long)N, (long long)E, (long long)B);
+  HCG_REQUIRE(out && emb && ws, HCG_ERR_INVALID_ARG, "NULL out/emb/workspace");
+  HCG_REQUIRE((N == 0 || x) && (E == 0 || edge_index) && node_ptr && edge_ptr, HCG_ERR_INVALID_ARG, "NULL x/edge_index/offsets");
+  EnsWs w = carve_ens(ws, B, ens->M);
+  HCG_REQUIRE(ws_bytes >= w.bytes, HCG_ERR_WORKSPACE, "ensemble workspace too small: %zu < %zu", ws_bytes, w.bytes);
+  if (B == 0) return HCG_OK;
+  note_region(st);
+  rc = launch_tc_fwd_ens(x, edge_index, node_ptr, edge_ptr, N, E, B, ens->M, ens->F, ens->slope, fill, ens->conv_w0, ens->conv_b0,
+                         ens->conv_w1, ens->conv_b1, w.wimg, emb, w.tc, st);
+  if (rc) return rc;
+  k_readout2_ens<<<dim3((unsigned)cdiv(B, RO_FG), (unsigned)ens->M), 256, 0, st>>>(emb, ens->ro_w0, ens->ro_b0, ens->ro_w1, ens->ro_b1,
+                                                                                  out, B, ens->C, ens->slope);
+  HCG_LAUNCH_OK(st, "k_readout2_ens");
+  return HCG_OK;
 }
 
 // ---- the same forward with NO caller workspace and no allocation of any kind -------------------------

@@ -143,3 +143,4 @@ extern "C" size_t hcg_sizeof_graph(void) { return sizeof(HcgGraph); }
 extern "C" size_t hcg_sizeof_params(void) { return sizeof(HcgParams); }
 extern "C" size_t hcg_sizeof_grads(void) { return sizeof(HcgGrads); }
 extern "C" size_t hcg_sizeof_saved(void) { return sizeof(HcgSaved); }
+extern "C" size_t hcg_sizeof_ensemble(void) { return sizeof(HcgEnsemble); }

@@ -181,17 +181,6 @@ namespace hcg {
 
 constexpr int kTcDefaultSlots = 2;    // tile pipelines per CTA (HCG_TC_SLOTS=3 selects the three-slot variant: measured slower,
                                       // 441 vs 398 us per 16384-graph batch - the kernel is bound by shared-memory throughput, not by latency)
-struct TcArgs {
-  FusedFwdArgs f;
-  const TcTile* tiles;      // [nslots][cap] dense per-slot work lists
-  const int* counts;        // [nslots]
-  int cap;
-  int64_t N, E;
-  // COO variant (k_tc_fwd<.., COO = true>): the raw edge list instead of the CSR of f.rowptr / f.col / f.dis
-  const int64_t* ei;        // [2, E]: row 0 sources, row 1 targets, grouped by graph
-  int* kflags;              // [nslots]: per-slot refusal flags (plain stores, no memset needed)
-};
-
 // ---- work list ----------------------------------------------------------------------------------
 // A warp per slot of the forward kernel; lane w takes the w-th window of W consecutive graphs that the slot
 // owns (windows are dealt round-robin to the slots), pairs its graphs greedily (first unpaired graph + the
@@ -386,36 +375,6 @@ __device__ unsigned long long g_tc_timing[16];
 #else
 #define TC_TICK(slot_) do { } while (0)
 #endif
-
-// Layer-0 gather of one thread: acc[c] = sum_j w_j x[j][c] over its NC columns (NC < 0: `ncol` at run time), rows
-// walked as (tile row, norm) records; every lane takes `maxdeg` steps (a lane past its own degree idles:
-// fewer shared-memory wavefronts than adding 0 x its own row), then the self-loop, last, as in the reference.
-// `xcol`: the thread's first column of tile row 0.
-// NBS: distance, in records, between consecutive records of a row (1: CSR slots; kTcRows: COO planes).
-template <int NC, int XW, int NBS>
-__device__ __forceinline__ void gather_x(float (&acc)[XW], const float* xcol, int F, const int2* nbp, int deg, int maxdeg,
-                                         int iself, float wself, int ncol = 0) {
-  if (NC == 0) return;
-  auto row_fma = [&](int r, float w) {
-    const float* xr = xcol + r * F;
-#pragma unroll
-    for (int c = 0; c < XW; ++c)
-      if (NC < 0 ? c < ncol : c < NC) acc[c] = fmaf(w, xr[c], acc[c]);
-  };
-  int2 nb = 0 < deg ? nbp[0] : make_int2(iself, 0);
-  for (int t = 0; t < maxdeg; ++t) {
-    const int2 cur = nb;
-    nb = t + 1 < deg ? nbp[(t + 1) * NBS] : make_int2(iself, 0);
-    if (t < deg) row_fma(cur.x, __int_as_float(cur.y));
-  }
-  row_fma(iself, wself);
-}
-
-// compare-exchange of two (edge number << 8 | tile row) keys
-__device__ __forceinline__ void key_cx(int& p, int& q) {
-  const int lo = min(p, q), hi = max(p, q);
-  p = lo; q = hi;
-}
 
 // F_ = compile-time number of input features (25: the RhCAA featuriser, 32: biaryl) or 0 = run-time F <= 32.
 // NS = tile pipelines ("slots") per CTA, 2 or 3.  Two threads own a tile row (32 of the 64 hidden columns each,
@@ -1084,15 +1043,7 @@ int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStr
 }
 
 // ---- COO variant: edge list in, embeddings out --------------------------------------------------------
-struct TcCooWs {
-  TcTile* tiles;
-  int* counts;
-  int* dflags;     // refusal flags of k_tile_desc, one per slot
-  int* kflags;     // refusal flags of k_tc_fwd, one per slot
-  size_t bytes;
-};
-
-static TcCooWs carve_tc_coo(void* ws, int64_t B) {
+TcCooWs carve_tc_coo(void* ws, int64_t B) {
   Carver c(ws, (size_t)-1);
   TcCooWs w{};
   w.tiles = c.take<TcTile>(tc_tiles_capacity(B));
@@ -1107,16 +1058,22 @@ size_t tc_fwd_coo_workspace_bytes(int64_t B) { return carve_tc_coo(nullptr, B).b
 size_t tc_fwd_coo_smem_bytes(int F, int L) { return tc_layout(F, L, 2, true).total; }
 int tc_fwd_coo_degree_cap() { return kTcCooDeg; }
 
+int launch_tile_desc_coo(const float* x, int F, const int64_t* edge_index, const int64_t* node_ptr, const int64_t* edge_ptr, int64_t N,
+                         int64_t E, int64_t B, const TcPlan& p, const TcCooWs& w, float* emb, int emb_zero_cols, cudaStream_t st) {
+  k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(nullptr, nullptr, nullptr, nullptr, x, F, N, E, B, p.W, p.nslots,
+                                                                          p.nwin, p.cap, w.tiles, w.counts, nullptr, nullptr, nullptr,
+                                                                          node_ptr, edge_ptr, edge_index, w.dflags, emb_zero_cols > 0 ? emb : nullptr);
+  HCG_LAUNCH_OK(st, "k_tile_desc");
+  return HCG_OK;
+}
+
 int launch_tc_fwd_coo(const FusedFwdArgs& f, const int64_t* edge_index, const int64_t* node_ptr, const int64_t* edge_ptr, int64_t N,
                       int64_t E, void* ws, cudaStream_t st) {
   if (f.B <= 0) return HCG_OK;
   TcCooWs w = carve_tc_coo(ws, f.B);
   const TcPlan p = tc_plan(f.B, 2);
   const size_t smem = tc_layout(f.F, f.L, 2, true).total;
-  k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(nullptr, nullptr, nullptr, nullptr, f.x, f.F, N, E, f.B, p.W,
-                                                                          p.nslots, p.nwin, p.cap, w.tiles, w.counts, nullptr, nullptr,
-                                                                          nullptr, node_ptr, edge_ptr, edge_index, w.dflags, f.emb);
-  HCG_LAUNCH_OK(st, "k_tile_desc");
+  if (int rc = launch_tile_desc_coo(f.x, f.F, edge_index, node_ptr, edge_ptr, N, E, f.B, p, w, f.emb, 128, st)) return rc;
   TcArgs a{};
   a.f = f;
   a.tiles = w.tiles;

@@ -370,6 +370,62 @@ def forward_edge_list(x: torch.Tensor, edge_index: torch.Tensor, ptr: torch.Tens
     return out, emb
 
 
+class EnsembleWeights:
+    """The conv / readout weights of M same-architecture networks stacked along a new first axis (what
+    ``hcg_gcn_forward_coo_ensemble`` takes).  Built once per ensemble from the models' flat parameter lists
+    (``_GCNBase._flat_params`` order: conv1 w, b, conv2 w, b, readout0 w, b, readout1 w, b)."""
+
+    def __init__(self, dims: NetDims, params_per_model, device):
+        if dims.L != 2 or dims.R != 2 or dims.H != 64 or dims.F > 32:
+            raise ValueError("one-pass ensemble needs the default architecture (2 conv layers, H = 64, readout 128-64-C, F <= 32)")
+        for ps in params_per_model:
+            _check_param_shapes(dims, ps)
+        self.dims, self.M = dims, len(params_per_model)
+        self.stacked = [torch.stack([to_device(ps[k].detach(), device, torch.float32) for ps in params_per_model]).contiguous()
+                        for k in range(8)]
+
+    @staticmethod
+    def supported(dims: NetDims) -> bool:
+        return dims.L == 2 and dims.R == 2 and dims.H == 64 and dims.F <= 32 and dims.C <= 64 and 0.0 <= dims.slope <= 1.0
+
+    def c_struct(self) -> _lib.HcgEnsemble:
+        e = _lib.HcgEnsemble()
+        e.M, e.F, e.H, e.C, e.slope = self.M, self.dims.F, self.dims.H, self.dims.C, float(self.dims.slope)
+        (e.conv_w0, e.conv_b0, e.conv_w1, e.conv_b1, e.ro_w0, e.ro_b0, e.ro_w1, e.ro_b1) = (t.data_ptr() for t in self.stacked)
+        return e
+
+
+def forward_edge_list_ensemble(x, edge_index, ptr, edge_ptr, weights: EnsembleWeights, fill: float = 1.0, validate: bool = True):
+    """M networks over one batch in ONE pass (``hcg_gcn_forward_coo_ensemble``): returns ``(out[M,B,C], emb[M,B,2H])``
+    or ``None`` when the device refused the batch (``validate``; see ``forward_edge_list``).  Per model the same bits as
+    ``forward_edge_list``."""
+    lib = _lib.load()
+    device, dims = x.device, weights.dims
+    if edge_index.dim() != 2 or edge_index.shape[0] != 2 or edge_index.dtype != torch.int64 or not edge_index.is_contiguous():
+        raise ValueError("edge_index must be a contiguous int64 [2, E] tensor")
+    B, N, E = int(ptr.numel()) - 1, int(x.shape[0]), int(edge_index.shape[1])
+    if x.shape != (N, dims.F) or x.dtype != torch.float32 or not x.is_contiguous():
+        raise ValueError(f"x must be a contiguous float32 [N, {dims.F}] tensor")
+    if edge_ptr.numel() != B + 1 or ptr.dtype != torch.int64 or edge_ptr.dtype != torch.int64:
+        raise ValueError("ptr / edge_ptr must be int64 [B + 1]")
+    f32 = dict(dtype=torch.float32, device=device)
+    with torch.cuda.device(device):
+        out = torch.empty(weights.M, B, dims.C, **f32)
+        emb = torch.empty(weights.M, B, 2 * dims.H, **f32)
+        ws = _workspace(lib.hcg_ensemble_workspace_bytes(B, weights.M), device)
+        st = _stream(device)
+        e = weights.c_struct()
+        _lib.check(lib.hcg_gcn_forward_coo_ensemble(_ptr(x), _ptr(edge_index), _ptr(ptr), _ptr(edge_ptr), N, E, B, float(fill),
+                                                    C.byref(e), _ptr(out), _ptr(emb), _ptr(ws), ws.numel(), st))
+        ws.record_stream(torch.cuda.current_stream(device))
+        if validate:
+            flags = C.c_int32(0)
+            _lib.check(lib.hcg_forward_coo_status(_ptr(ws), B, st, C.byref(flags)))
+            if flags.value:
+                return None
+    return out, emb
+
+
 def backward_raw(plan: GraphPlan, x: torch.Tensor, dims: NetDims, params, saved_t, emb, g_out, g_emb, need_gx: bool,
                  flat_out: torch.Tensor | None = None, edge_mask=None, need_gmask: bool = False):
     """One ``hcg_gcn_backward`` call.  Returns (g_x or None, list of parameter grads) — and the gradient

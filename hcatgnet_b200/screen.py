@@ -148,15 +148,19 @@ def predict_network_stream(model, loader: Iterable[Batch], return_emb: bool = Fa
     return cat(y_pred), cat(y_true), cat(idx)
 
 
-def predict_ensemble_stream(models, batches: Iterable[Batch], device=None, depth: int = 2, validate: bool = False):
+def predict_ensemble_stream(models, batches: Iterable[Batch], device=None, depth: int = 2, validate: bool = False,
+                            return_embedding: bool = False, one_pass: bool | None = None):
     """Ensemble screening — the intended ``scripts_experiments/predict.py`` (reference :11-60, dead code
     there): every model of ``models`` (e.g. the 90 ``model_params.pth`` of a nested cross-validation,
     reference scripts_experiments/train_GNN.py:48-137) is run over every batch of the stream.
 
-    A batch crosses PCIe ONCE and is collated ONCE (the topology plan is shared by all models); only the
-    network kernel runs per model, so the screen is bound by the device, not by the host link.
-    Yields ``(pred[M, B, C], mean[B, C], std[B, C], host_batch)`` per batch as pinned HOST tensors
-    (``std`` is the population standard deviation over the ensemble)."""
+    A batch crosses PCIe ONCE.  For the default architecture on batches that carry their offsets and size facts
+    the whole ensemble then runs in ONE pass over the batch (``hcg_gcn_forward_coo_ensemble``: graphs staged, neighbour
+    lists built and the layer-0 aggregation done once per tile, the models' weights streamed through shared memory);
+    otherwise the batch is collated once and the network kernel runs per model.  ``one_pass``: ``None`` = when
+    possible, ``False`` = never, ``True`` = raise if not possible.  Same bits per model either way.
+    Yields ``(pred[M, B, C], mean[B, C], std[B, C], host_batch)`` per batch as pinned HOST tensors (``std`` is the
+    population standard deviation over the ensemble); with ``return_embedding`` a fifth item ``emb[M, B, 2H]``."""
     models = list(models)
     if not models:
         raise ValueError("predict_ensemble_stream needs at least one model")
@@ -166,32 +170,49 @@ def predict_ensemble_stream(models, batches: Iterable[Batch], device=None, depth
             raise ValueError("all models of an ensemble must share one architecture")
     dev = torch.device(device) if device is not None else ops._require_cuda()
     params = [[ops.to_device(p.detach(), dev, torch.float32) for p in m._flat_params()] for m in models]
+    stacked = ops.EnsembleWeights(dims0, params, dev) if one_pass is not False and ops.EnsembleWeights.supported(dims0) else None
+    if one_pass is True and stacked is None:
+        raise ValueError("one_pass=True: this architecture has no one-pass ensemble kernel")
     pending: deque = deque()
 
     def finish(item):
-        p_h, m_h, s_h, h, ev, _keep = item
+        hosts, h, ev, _keep = item
         ev.synchronize()
-        return p_h, m_h, s_h, h
+        return (*hosts, h) if not return_embedding else (*hosts[:3], h, hosts[3])
 
     with torch.no_grad():
         for d in DevicePrefetcher(batches, device=dev, depth=depth):
-            plan = ops.cached_collate(d, d.edge_index, d.batch, d.x.shape[0], d.num_graphs, dev, transpose=False,
-                                      validate=validate, max_graph_nodes=int(getattr(d, "max_graph_nodes", 0) or 0),
-                                      grouped=getattr(d, "edges_grouped", None))
             x = ops.to_device(d.x, dev, torch.float32)
-            pred = torch.empty(len(models), d.num_graphs, dims0.C, dtype=torch.float32, device=dev)
-            for k, ps in enumerate(params):
-                out, _, _ = ops.forward_raw(plan, x, dims0, ps, save=False)
-                pred[k].copy_(out)
+            res, plan = None, None
+            if stacked is not None and (ops.edge_list_hints_ok(d) or validate or one_pass is True) and \
+                    getattr(d, "ptr", None) is not None and getattr(d, "edge_ptr", None) is not None and \
+                    d.edge_index.dtype == torch.int64:
+                res = ops.forward_edge_list_ensemble(x.contiguous(), d.edge_index.contiguous(), d.ptr, d.edge_ptr, stacked,
+                                                     validate=validate or not ops.edge_list_hints_ok(d))
+                if res is None and one_pass is True:
+                    raise ValueError("one_pass=True: the device refused the batch (oversize graph, in-degree above 16, self-loop)")
+            if res is not None:
+                pred, emb = res
+            else:
+                plan = ops.cached_collate(d, d.edge_index, d.batch, d.x.shape[0], d.num_graphs, dev, transpose=False,
+                                          validate=validate, max_graph_nodes=int(getattr(d, "max_graph_nodes", 0) or 0),
+                                          grouped=getattr(d, "edges_grouped", None))
+                pred = torch.empty(len(models), d.num_graphs, dims0.C, dtype=torch.float32, device=dev)
+                emb = torch.empty(len(models), d.num_graphs, 2 * dims0.H, dtype=torch.float32, device=dev) if return_embedding else None
+                for k, ps in enumerate(params):
+                    out, e_k, _ = ops.forward_raw(plan, x, dims0, ps, save=False)
+                    pred[k].copy_(out)
+                    if emb is not None:
+                        emb[k].copy_(e_k)
             mean, std = pred.mean(0), pred.std(0, unbiased=False)
             hosts = []
-            for t in (pred, mean, std):
+            for t in (pred, mean, std) + ((emb,) if return_embedding else ()):
                 t_h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
                 t_h.copy_(t, non_blocking=True)
                 hosts.append(t_h)
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream(dev))
-            pending.append((*hosts, d._host, ev, (pred, mean, std, plan, x)))
+            pending.append((hosts, d._host, ev, (pred, mean, std, emb, plan, x)))
             if len(pending) > 1:
                 yield finish(pending.popleft())
         while pending:

@@ -313,6 +313,38 @@ int hcg_gcn_forward_coo(const float* x, const int64_t* edge_index, const int64_t
 int hcg_forward_coo_status(const void* ws, int64_t B, void* stream, int32_t* flags);
 
 /*
+ * One-pass ENSEMBLE inference (replaces the loop over trained models of scripts_experiments/predict_test.py:47-70, each
+ * iteration a whole predict_network, utils/utils_model.py:82-111; the reference's own ensemble script
+ * scripts_experiments/predict.py:11-60 is dead code): M networks of one architecture (the default one: two conv layers,
+ * H = 64, readout 128 -> 64 -> C) over one batch in ONE pass.  Per tile of the batch the kernel stages the graphs,
+ * builds the normalised neighbour lists and gathers the layer-0 operand A.x once, then streams the models' weights
+ * through shared memory; per model only the two tensor-core products, the 64-wide gather and the pooling remain.
+ * Weights are the state_dict tensors of the M models STACKED along a new first axis.  Per model the results carry the
+ * same bits as hcg_gcn_forward_coo.  Input preconditions and HCG_COO_* flags as hcg_gcn_forward_coo
+ * (hcg_forward_coo_status on the same `ws`).
+ * out: [M, B, C];  emb: [M, B, 2H].
+ */
+typedef struct HcgEnsemble {
+  int32_t M, F, H, C;
+  float slope;
+  int32_t reserved0;
+  const float* conv_w0;   /* [M, H, F]   conv1.lin.weight            */
+  const float* conv_b0;   /* [M, H]      conv1.bias                  */
+  const float* conv_w1;   /* [M, H, H]   conv_layers.0.lin.weight    */
+  const float* conv_b1;   /* [M, H]      conv_layers.0.bias          */
+  const float* ro_w0;     /* [M, H, 2H]  readout.0.0.weight          */
+  const float* ro_b0;     /* [M, H]      readout.0.0.bias            */
+  const float* ro_w1;     /* [M, C, H]   readout.1.weight            */
+  const float* ro_b1;     /* [M, C]      readout.1.bias              */
+} HcgEnsemble;
+size_t hcg_sizeof_ensemble(void);   /* sizeof(HcgEnsemble), for bindings */
+size_t hcg_ensemble_workspace_bytes(int64_t B, int32_t M);
+int hcg_gcn_forward_coo_ensemble(const float* x, const int64_t* edge_index, const int64_t* node_ptr,
+                                 const int64_t* edge_ptr, int64_t N, int64_t E, int64_t B, float fill,
+                                 const HcgEnsemble* ens, float* out, float* emb, void* ws, size_t ws_bytes,
+                                 void* stream);
+
+/*
  * hcg_gcn_forward_coo for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
  * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
  * Same inputs, outputs and results as hcg_gcn_forward_coo, but no workspace argument: the scratch (tile work list,

@@ -1,3 +1,3 @@
 set -x
-timeout 300 python -m pytest tests/test_zz_no_alloc.py -x -q 2>&1 | tail -6
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+PYTHONPATH=. timeout 600 python profiles/experiments/ensemble_rate.py 2>&1 | tail -12
+timeout 600 python -m pytest tests/test_gpu_ensemble.py tests/test_gpu_module.py -x -q 2>&1 | tail -5

@@ -37,7 +37,7 @@ def test_struct_layouts_match_header_sizes():
     from hcatgnet_b200 import _lib
     lib = _lib.load()
     for name, cls in (("HcgGraph", _lib.HcgGraph), ("HcgParams", _lib.HcgParams),
-                      ("HcgGrads", _lib.HcgGrads), ("HcgSaved", _lib.HcgSaved)):
+                      ("HcgGrads", _lib.HcgGrads), ("HcgSaved", _lib.HcgSaved), ("HcgEnsemble", _lib.HcgEnsemble)):
         fn = getattr(lib, "hcg_sizeof_" + name.lower()[3:])
         fn.restype = ctypes.c_size_t
         assert fn() == ctypes.sizeof(cls), name
