@@ -4,16 +4,18 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--mode infer|train] [--batch B]
     python bench.py --impl reference ...      # the CPU restatement of the reference's PyG path
 
-With no --mode the line's headline is BASELINE.json configs[1] (screening inference) and it carries two
+With no --mode the line's headline is BASELINE.json configs[1] (screening inference) and it carries three
 sub-records measured in the same run: `train` (configs[2]: data-parallel training, batch 4096 per GPU,
-FusedTrainer.step with the NCCL all-reduce of the gradient slab, `allreduce_us` timed on its own) and
-`stress` (configs[4]: H = 256, 4 conv layers, the layer-wise kernels with their `aggregation_roofline`).
+FusedTrainer.step with the NCCL all-reduce of the gradient slab, `allreduce_us` timed on its own),
+`stress` (configs[4]: H = 256, 4 conv layers, the layer-wise kernels with their `aggregation_roofline`) and
+`ensemble` (16 models over the screening batch in one pass vs 16 single-model forwards).
 
 A step = one pass of the hot path over one synthetic batch delivered as PyG would deliver it
-(x fp32 [N,25], edge_index int64 [2,E], batch int64 [N]): hcg_collate (dst-sorted CSR, deg^-1/2,
-graph offsets) + hcg_gcn_forward (2 x GCNConv + LeakyReLU, max||mean pooling, readout MLP); in
---mode train additionally hcg_gcn_backward, the NCCL all-reduce of the flat gradient (N > 1)
-and the Adam step.  Default workload = BASELINE.json configs[1]: screening inference, ~80-atom
+(x fp32 [N,25], edge_index int64 [2,E], ptr / edge offsets int64 [B+1]).  Inference: hcg_gcn_forward_coo (the conv
+kernel builds the normalised neighbour lists from the edge list itself; 2 x GCNConv + LeakyReLU, max||mean pooling,
+readout MLP) - HCG_BENCH_CSR=1 selects the earlier hcg_collate (dst-sorted CSR, deg^-1/2, graph offsets) +
+hcg_gcn_forward pair.  --mode train: hcg_collate + forward + hcg_gcn_backward, the NCCL all-reduce of the flat
+gradient (N > 1) and the Adam step.  Default workload = BASELINE.json configs[1]: screening inference, ~80-atom
 graphs, batch 16384 per GPU, 62 steps ~ 1 M graphs.
 
 `value` times the device-resident path with CUDA events (barrier + synchronize on both sides,
@@ -290,6 +292,47 @@ def measured_traffic(name: str, mode: str, batch: int, hidden: int, convs: int):
         return None
     rec = t.get(f"{name}|{mode}|batch{batch}|H{hidden}|L{convs}")
     return None if rec is None else rec["dram_bytes"]
+
+
+# ----------------------------------------------------------------------------------------------
+def measure_ensemble(cx, batch: int, n_models: int, steps: int):
+    """`n_models` networks over the screening batch in ONE pass (hcg_gcn_forward_coo_ensemble)
+    against the same models as `n_models` single-model edge-list forwards; device-resident, CUDA events, 4 batches cycled.
+    `value` counts graph x model evaluations per second over all ranks."""
+    import hcatgnet_b200 as pkg
+    from hcatgnet_b200 import _lib, ops
+    from hcatgnet_b200.synth import synth_batch
+    dev = cx.dev
+    pool = [synth_batch(batch, F_IN, seed=20232023 + 1000 * cx.rank + i).to(dev) for i in range(POOL)]
+    models = []
+    for k in range(n_models):
+        torch.manual_seed(100 + k)
+        models.append(pkg.make_network("GCN", pkg.default_options(embedding_dim=HID, n_convolutions=N_CONV), F_IN).to(dev).eval())
+    dims = models[0]._dims()
+    params = [[p.detach() for p in m._flat_params()] for m in models]
+    w = ops.EnsembleWeights(dims, params, dev)
+
+    def one_pass(i):
+        b = pool[i % POOL]
+        return ops.forward_edge_list_ensemble(b.x, b.edge_index, b.ptr, b.edge_ptr, w, validate=False)
+
+    def per_model(i):
+        b = pool[i % POOL]
+        for ps in params:
+            ops.forward_edge_list(b.x, b.edge_index, b.ptr, b.edge_ptr, dims, ps, validate=False)
+
+    for i in range(3):
+        one_pass(i); per_model(i)
+    l0 = _lib.launch_count()
+    ms1 = cx.timed(one_pass, steps)
+    launches = int(_lib.launch_count() - l0)
+    msm = cx.timed(per_model, steps)
+    del pool
+    return {"models": n_models, "batch_per_gpu": batch, "steps": steps,
+            "value": n_models * batch * steps * cx.world / (ms1 * 1e-3), "unit": "graph-model evaluations/s",
+            "ms_per_step": ms1 / steps, "ms_per_step_per_model_launches": msm / steps,
+            "per_model_cost_vs_single_forward": (ms1 / steps) / (msm / steps), "gpu_launches": launches,
+            "api": "hcg_gcn_forward_coo_ensemble (one pass) vs n_models x hcg_gcn_forward_coo"}
 
 
 # ----------------------------------------------------------------------------------------------
@@ -602,6 +645,10 @@ def main():
         train, _ = measure(cx, "train", 4096, HID, N_CONV, sub, max(3, a.warmup), want_packed=False,
                            want_profile=not a.no_profile, want_clocks=False)
 
+    ensemble = None
+    if default_cfg and not a.no_sub:
+        ensemble = measure_ensemble(cx, a.batch, 16, max(3, int(a.sub_steps) // 4))
+
     cpu_baseline = None
     if cx.rank == 0 and cx.world == 1 and not a.no_cpu_baseline:
         v, cores, sample = cpu_oracle_rate(a.hidden, a.convs, 2048, 12.0, a.mode)
@@ -616,7 +663,7 @@ def main():
             "clocks": head.get("clocks"), "e2e": head.get("e2e"), "e2e_packed": head.get("e2e_packed"),
             "gpu_launches": head["gpu_launches"], "roofline": head["roofline"],
             "aggregation_roofline": head["aggregation_roofline"], "kernels": head["kernels"], "cpu_baseline": cpu_baseline,
-            "train": train, "stress": stress,
+            "train": train, "stress": stress, "ensemble": ensemble,
         }
         if a.mode == "train":
             line["allreduce_us"] = head.get("allreduce_us")

@@ -1,3 +1,9 @@
 set -x
-PYTHONPATH=. timeout 600 python profiles/experiments/ensemble_rate.py 2>&1 | tail -12
-timeout 600 python -m pytest tests/test_gpu_ensemble.py tests/test_gpu_module.py -x -q 2>&1 | tail -5
+timeout 900 python bench.py 2>&1 | tail -1 > gpurun_out/bench_default.json
+python - <<'PY'
+import json
+r=json.loads(open("gpurun_out/bench_default.json").read())
+print(r["value"], r["ms_per_step"], r["e2e"]["value"], r.get("e2e_packed",{}).get("value"), r["gpu_launches"], r["roofline"])
+print(r["kernels"])
+print(r["train"]["value"], r["stress"]["value"], r["ensemble"])
+PY
