@@ -827,6 +827,7 @@ k_tc_fwd(const TcArgs a) {
       if (ctl_warp) ptx::mbar_wait(&bar_mma[slot], mma_phase);      // one warp polls; the others sleep in the barrier below
       mma_phase ^= 1u;
       TC_TICK(5);
+      if (cg == 0) ptx::bulk_wait_read();   // (training forward) the saved rows have left the activation buffer
       ptx::named_bar_sync(bar_full, kSlotThreads);
       ptx::tc_fence_after_sync();
       if (l == 0 && pf_warp) issue(k + 1, true);   // every layer-0 gather of the slot is over: the x stage is free
@@ -834,7 +835,7 @@ k_tc_fwd(const TcArgs a) {
 
       // ---- epilogue: h_r = lrelu(D_r + b_l) -> activation buffer (+ optional save) ------------------
       if (warp_ok) {
-        float* save = (a.f.save_act[l] != nullptr && row_ok) ? a.f.save_act[l] + ((int64_t)n0 + li) * 64 : nullptr;
+        // (training forward: the finished row goes out below, as ONE bulk copy per row from the activation buffer)
 #pragma unroll
         for (int part = 0; part < CW / 16; ++part) {
           uint32_t q0[16];
@@ -850,13 +851,18 @@ k_tc_fwd(const TcArgs a) {
             v.z = __uint_as_float(q0[4 * q4 + 2]) + b4.z; v.z = fmaxf(v.z, v.z * slope);
             v.w = __uint_as_float(q0[4 * q4 + 3]) + b4.w; v.w = fmaxf(v.w, v.w * slope);
             *reinterpret_cast<float4*>(smf + hb_w + i * HP + c0) = v;
-            if (save) *reinterpret_cast<float4*>(save + c0) = v;
           }
         }
       }
       TC_TICK(7);
+      const bool saving = a.f.save_act[l] != nullptr;
+      if (saving) ptx::fence_proxy_async_smem();   // the rows are read by the bulk copies below (async proxy)
       ptx::tc_fence_before_sync();
       ptx::named_bar_sync(bar_full, kSlotThreads);  // h complete in shared memory; D may be overwritten
+      if (saving && cg == 0 && row_ok) {
+        ptx::bulk_s2g(a.f.save_act[l] + ((int64_t)n0 + li) * 64, smf + hb_w + i * HP, 256);
+        ptx::bulk_commit();
+      }
       TC_TICK(8);
 
       if (!last) {
@@ -912,6 +918,7 @@ k_tc_fwd(const TcArgs a) {
     TC_TICK(10);
   }
   if (p_gA >= 0) pool_tile(p_gA, p_gB, p_nA, p_nB);
+  ptx::bulk_wait_all();
 
   ptx::tc_fence_before_sync();
   __syncthreads();

@@ -1,9 +1,9 @@
 set -x
-timeout 900 python bench.py 2>&1 | tail -1 > gpurun_out/bench_default.json
+timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_module.py tests/test_gpu_tc.py -x -q 2>&1 | tail -4
+timeout 600 python bench.py --mode train --batch 4096 --steps 30 --warmup 5 --no-cpu-baseline 2>&1 | tail -1 > gpurun_out/train.json
 python - <<'PY'
 import json
-r=json.loads(open("gpurun_out/bench_default.json").read())
-print(r["value"], r["ms_per_step"], r["e2e"]["value"], r.get("e2e_packed",{}).get("value"), r["gpu_launches"], r["roofline"])
-print(r["kernels"])
-print(r["train"]["value"], r["stress"]["value"], r["ensemble"])
+r=json.loads(open("gpurun_out/train.json").read())
+print(r["value"], r["ms_per_step"], r["e2e"]["value"])
+print({n:round(v["ms_per_launch"]*1e3,1) for n,v in r["kernels"].items()})
 PY
