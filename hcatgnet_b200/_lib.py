@@ -74,7 +74,7 @@ class HcgPackedStore(C.Structure):
     _fields_ = [("G", C.c_int64), ("N", C.c_int64), ("E", C.c_int64),
                 ("F", C.c_int32), ("Fu", C.c_int32), ("Ff", C.c_int32), ("edge_kind", C.c_int32),
                 ("col_slot", _fp), ("node_ptr", _fp), ("edge_ptr", _fp), ("y", _fp), ("xu8", _fp), ("xf32", _fp),
-                ("edges", _fp)]
+                ("edges", _fp), ("Fb", C.c_int32), ("bit_stride", C.c_int32), ("xbits", _fp)]
 
 
 _lib = None

@@ -14,6 +14,7 @@ namespace hcg {
 
 constexpr int kUnpackThreads = 128;
 constexpr int kUnpackMaxF = 256;
+constexpr int kBitSlot0 = 65536;   // col_slot values from here on name a bit of the node's xbits row
 
 template <typename ET>
 __global__ void __launch_bounds__(kUnpackThreads)
@@ -35,12 +36,20 @@ k_unpack_batch(const HcgPackedStore s, const int64_t* __restrict__ graph_ids, in
   const int total = (int)n * F;
   const uint8_t* xu = s.xu8 + s0 * s.Fu;
   const float* xf = s.xf32 + s0 * s.Ff;
+  const uint8_t* xb = s.xbits + s0 * s.bit_stride;
   float* xo = x + d0 * F;
   int r = tid / F, c = tid - r * F;                      // element tid, then steps of kUnpackThreads
   const int dr = kUnpackThreads / F, dc = kUnpackThreads - dr * F;
   for (int t = tid; t < total; t += kUnpackThreads) {
     const int slot = s_slot[c];
-    xo[t] = slot >= 0 ? (float)xu[r * s.Fu + slot] : xf[r * s.Ff + (~slot)];
+    float v;
+    if (slot >= kBitSlot0) {
+      const int k = slot - kBitSlot0;
+      v = (float)((xb[r * s.bit_stride + (k >> 3)] >> (k & 7)) & 1);
+    } else {
+      v = slot >= 0 ? (float)xu[r * s.Fu + slot] : xf[r * s.Ff + (~slot)];
+    }
+    xo[t] = v;
     r += dr; c += dc;
     if (c >= F) { c -= F; ++r; }
   }
@@ -69,8 +78,10 @@ extern "C" int hcg_unpack_batch(const HcgPackedStore* store, const int64_t* grap
   if (B == 0) return HCG_OK;
   HCG_REQUIRE(graph_ids != nullptr || first + B <= store->G, HCG_ERR_INVALID_ARG, "graphs [%lld, %lld) outside the store (G=%lld)",
               (long long)first, (long long)(first + B), (long long)store->G);
-  HCG_REQUIRE(store->F >= 1 && store->F <= kUnpackMaxF && store->Fu + store->Ff == store->F, HCG_ERR_INVALID_ARG,
-              "bad feature split F=%d Fu=%d Ff=%d", store->F, store->Fu, store->Ff);
+  HCG_REQUIRE(store->F >= 1 && store->F <= kUnpackMaxF && store->Fb >= 0 && store->Fu + store->Ff + store->Fb == store->F,
+              HCG_ERR_INVALID_ARG, "bad feature split F=%d Fu=%d Ff=%d Fb=%d", store->F, store->Fu, store->Ff, store->Fb);
+  HCG_REQUIRE(store->Fb == 0 || (store->xbits && store->bit_stride * 8 >= store->Fb), HCG_ERR_INVALID_ARG,
+              "bit columns without a bit section (Fb=%d, bit_stride=%d)", store->Fb, store->bit_stride);
   HCG_REQUIRE(store->node_ptr && store->edge_ptr && store->col_slot && store->y && out_ptr && out_eptr && x,
               HCG_ERR_INVALID_ARG, "NULL pointer");
   HCG_REQUIRE((store->Fu == 0 || store->xu8) && (store->Ff == 0 || store->xf32) && (E_out == 0 || (store->edges && edge_index)),

@@ -46,6 +46,22 @@ def _stream(device) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
 
+def bucketed_empty(shape, dtype, device) -> torch.Tensor:
+    """``torch.empty(shape)`` whose allocation is rounded up to one of eight sizes per power of two.  Batches of a
+    stream differ in size by a few per cent; with exact sizes torch's caching allocator misses on most of them (a
+    cudaMalloc of 100+ MB per tensor and step until every size has been seen), with buckets the second batch already
+    reuses the first one's blocks.  At most 12.5 % of slack, never touched."""
+    shape = tuple(int(v) for v in shape)
+    numel = 1
+    for v in shape:
+        numel *= v
+    if numel < (1 << 16):
+        return torch.empty(shape, dtype=dtype, device=device)
+    step = 1 << (numel.bit_length() - 4)
+    cap = (numel + step - 1) // step * step
+    return torch.empty(cap, dtype=dtype, device=device)[:numel].view(shape)
+
+
 def _workspace(nbytes: int, device) -> torch.Tensor:
     return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
 

@@ -6,14 +6,15 @@ data/datasets.py:74-78, data/rhcaa.py:90-92) and collates with Python per batch
 batch of 100 B per node + 16 B per directed edge.  Here the whole set is ONE binary image:
 
     header (128 B) | col_slot i32[F] | node_ptr i64[G+1] | edge_ptr i64[G+1] | y f32[G] | idx i64[G] |
-    fold i32[G] | xu8 u8[N, Fu] | xf32 f32[N, Ff] | edges uK[E, 2]          (every section 64-byte aligned)
+    fold i32[G] | xu8 u8[N, Fu] | xf32 f32[N, Ff] | edges uK[E, 2] | xbits u8[N, ceil(Fb / 8)]
+                                                                          (every section 64-byte aligned)
 
-* node features are split per COLUMN: a column whose values are all integers in 0..255 (the one-hot / count
-  columns of the featuriser, reference data/rhcaa.py:112-150) is stored as u8, the others (temperature)
-  stay f32 — lossless by construction, checked at pack time;
+* node features are split per COLUMN: a column whose every value is 0 or 1 (the one-hot and flag columns of the
+  featuriser, reference data/rhcaa.py:112-150) takes ONE BIT per node, a column of integers in 0..255 (counts) one
+  byte, the others (temperature) stay f32 — lossless by construction, checked at pack time;
 * edges are (src, dst) pairs LOCAL to their graph in u8 (graphs <= 256 nodes), u16 or i32, graph by graph.
 
-RhCAA-shaped graphs take ~2.7 KB instead of ~11.9 KB.  The image is consumed on the GPU:
+RhCAA-shaped graphs take ~1.0 KB instead of ~11.9 KB (2.7 KB before the bit columns).  The image is consumed on the GPU:
 ``DeviceGraphStore`` keeps it resident (the 10 M-graph screening set is ~27 GB of 180 GB HBM) and
 ``batch(ids)`` assembles any selection of graphs — a shuffled mini-batch, a cross-validation fold — with one
 kernel (``hcg_unpack_batch``, csrc/hcg_packed.cu) into exactly the tensors PyG's collate would have produced
@@ -33,7 +34,7 @@ from typing import Sequence
 import numpy as np
 import torch
 
-from . import _lib
+from . import _lib, ops
 from .data import GROUPED_MAX_EDGES, GROUPED_MAX_NODES, Batch, _field
 
 FLAG_GROUPABLE = 1      # header flag: the packer checked the preconditions of hcg_collate's graph-local path
@@ -47,16 +48,21 @@ def _aligned(n: int) -> int:
     return (n + _ALIGN - 1) // _ALIGN * _ALIGN
 
 
-def _sections(G: int, N: int, E: int, F: int, Fu: int, Ff: int, ek: int):
-    """(name, dtype, shape) in file order."""
+BIT_SLOT0 = 65536       # col_slot values from here on: bit (slot - BIT_SLOT0) of the node's xbits row
+
+
+def _sections(G: int, N: int, E: int, F: int, Fu: int, Ff: int, ek: int, Fb: int = 0):
+    """(name, dtype, shape) in file order.  ``xbits`` (columns whose every value is 0 or 1, one bit each) comes last:
+    images of writers that did not know it (Fb = 0 in the header) keep their layout."""
     return [("col_slot", np.int32, (F,)), ("node_ptr", np.int64, (G + 1,)), ("edge_ptr", np.int64, (G + 1,)),
             ("y", np.float32, (G,)), ("idx", np.int64, (G,)), ("fold", np.int32, (G,)),
-            ("xu8", np.uint8, (N, Fu)), ("xf32", np.float32, (N, Ff)), ("edges", _EDGE_DTYPES[ek], (E, 2))]
+            ("xu8", np.uint8, (N, Fu)), ("xf32", np.float32, (N, Ff)), ("edges", _EDGE_DTYPES[ek], (E, 2)),
+            ("xbits", np.uint8, (N, (Fb + 7) // 8))]
 
 
-def _layout(G, N, E, F, Fu, Ff, ek):
+def _layout(G, N, E, F, Fu, Ff, ek, Fb=0):
     off, out = HEADER_BYTES, {}
-    for name, dt, shape in _sections(G, N, E, F, Fu, Ff, ek):
+    for name, dt, shape in _sections(G, N, E, F, Fu, Ff, ek, Fb):
         nbytes = int(np.prod(shape, dtype=np.int64)) * np.dtype(dt).itemsize
         out[name] = (off, dt, shape, nbytes)
         off = _aligned(off + nbytes)
@@ -81,7 +87,8 @@ class PackedDataset:
         self.max_in_degree = int(blob[88:96].view(np.int64)[0]) - 1
         if self.max_in_degree < 0:
             self.max_in_degree = None
-        self.layout, total = _layout(self.G, self.N, self.E, self.F, self.Fu, self.Ff, self.edge_kind)
+        self.Fb = int(blob[96:104].view(np.int64)[0])       # bit columns (0 in images of older writers)
+        self.layout, total = _layout(self.G, self.N, self.E, self.F, self.Fu, self.Ff, self.edge_kind, self.Fb)
         if blob.size < total:
             raise ValueError(f"packed graph image truncated: {blob.size} of {total} bytes")
         self.blob = blob[:total]
@@ -90,7 +97,8 @@ class PackedDataset:
 
     # ------------------------------------------------------------------ construction
     @classmethod
-    def from_arrays(cls, x, edge_index, ptr, y=None, idx=None, fold=None, pinned: bool = False) -> "PackedDataset":
+    def from_arrays(cls, x, edge_index, ptr, y=None, idx=None, fold=None, pinned: bool = False,
+                    bits: bool = True) -> "PackedDataset":
         """From a collated set: ``x[N,F]`` f32, ``edge_index[2,E]`` with GLOBAL node numbers listed graph by
         graph (what ``Batch.from_data_list`` / PyG's collate produce), ``ptr[G+1]``."""
         x = np.ascontiguousarray(np.asarray(x, dtype=np.float32))
@@ -107,14 +115,22 @@ class PackedDataset:
         sizes = np.diff(ptr)
         nmax = int(sizes.max()) if G else 0
         ek = 1 if nmax <= 256 else 2 if nmax <= 65536 else 4
-        # lossless column split
-        as_u8 = np.array([bool(np.all((x[:, c] >= 0) & (x[:, c] <= 255) & (x[:, c] == np.floor(x[:, c])))) for c in range(F)],
-                         dtype=bool) if N else np.ones(F, bool)
-        Fu, Ff = int(as_u8.sum()), int((~as_u8).sum())
+        # lossless column split: one bit (every value 0 or 1: one-hot / flag columns), one byte (integers 0..255), f32
+        # (-0.0 compares equal to 0 but would come back as +0.0: such a column stays f32)
+        as_bit = np.array([bool(np.all(((x[:, c] == 0) & ~np.signbit(x[:, c])) | (x[:, c] == 1))) for c in range(F)],
+                          dtype=bool) if N else np.ones(F, bool)
+        if not bits:
+            as_bit[:] = False
+        as_u8 = np.array([bool(np.all((x[:, c] >= 0) & (x[:, c] <= 255) & (x[:, c] == np.floor(x[:, c])) & ~np.signbit(x[:, c])))
+                          for c in range(F)], dtype=bool) if N else np.zeros(F, bool)
+        as_u8 &= ~as_bit
+        as_f32 = ~(as_bit | as_u8)
+        Fb, Fu, Ff = int(as_bit.sum()), int(as_u8.sum()), int(as_f32.sum())
         col_slot = np.empty(F, np.int32)
+        col_slot[as_bit] = BIT_SLOT0 + np.arange(Fb, dtype=np.int32)
         col_slot[as_u8] = np.arange(Fu, dtype=np.int32)
-        col_slot[~as_u8] = ~np.arange(Ff, dtype=np.int32)      # negative: ~slot in the f32 block
-        layout, total = _layout(G, N, E, F, Fu, Ff, ek)
+        col_slot[as_f32] = ~np.arange(Ff, dtype=np.int32)      # negative: ~slot in the f32 block
+        layout, total = _layout(G, N, E, F, Fu, Ff, ek, Fb)
         blob_t = torch.zeros(total, dtype=torch.uint8)
         if pinned:
             blob_t = blob_t.pin_memory()
@@ -125,6 +141,7 @@ class PackedDataset:
         groupable = (not E or not bool(np.any(ei[0] == ei[1]))) and nmax <= GROUPED_MAX_NODES and emax <= GROUPED_MAX_EDGES
         blob[72:88].view(np.int64)[:] = [emax, FLAG_GROUPABLE if groupable else 0]
         blob[88:96].view(np.int64)[:] = [1 + (int(np.bincount(ei[1]).max()) if E else 0)]
+        blob[96:104].view(np.int64)[:] = [Fb]
         self = cls(blob)
         self._owner = blob_t
         self.col_slot[:] = col_slot
@@ -134,7 +151,9 @@ class PackedDataset:
         self.idx[:] = np.arange(G) if idx is None else np.asarray(idx, np.int64).reshape(-1)
         self.fold[:] = -1 if fold is None else np.asarray(fold, np.int32).reshape(-1)
         self.xu8[:] = x[:, as_u8].astype(np.uint8)
-        self.xf32[:] = x[:, ~as_u8]
+        self.xf32[:] = x[:, as_f32]
+        if Fb:
+            self.xbits[:] = np.packbits(x[:, as_bit].astype(np.uint8), axis=1, bitorder="little")
         if E:
             self.edges[:, 0] = (ei[0] - ptr[gsrc]).astype(self.edges.dtype)
             self.edges[:, 1] = (ei[1] - ptr[gsrc]).astype(self.edges.dtype)
@@ -173,9 +192,13 @@ class PackedDataset:
         rows = np.concatenate([np.arange(self.node_ptr[g], self.node_ptr[g + 1]) for g in ids]) if ids.size else np.zeros(0, np.int64)
         slots = np.concatenate([np.arange(self.edge_ptr[g], self.edge_ptr[g + 1]) for g in ids]) if ids.size else np.zeros(0, np.int64)
         x = np.empty((rows.size, self.F), np.float32)
-        u8c = self.col_slot >= 0
+        bitc = self.col_slot >= BIT_SLOT0
+        u8c = (self.col_slot >= 0) & ~bitc
+        f32c = self.col_slot < 0
         x[:, u8c] = self.xu8[rows][:, self.col_slot[u8c]]
-        x[:, ~u8c] = self.xf32[rows][:, ~self.col_slot[~u8c]]
+        x[:, f32c] = self.xf32[rows][:, ~self.col_slot[f32c]]
+        if self.Fb:
+            x[:, bitc] = np.unpackbits(self.xbits[rows], axis=1, bitorder="little")[:, self.col_slot[bitc] - BIT_SLOT0]
         ei = self.edges[slots].astype(np.int64).T + np.repeat(ptr[:-1], e)[None, :]
         batch = np.repeat(np.arange(ids.size, dtype=np.int64), n)
         return Batch(torch.from_numpy(x), torch.from_numpy(np.ascontiguousarray(ei)), torch.from_numpy(batch),
@@ -281,7 +304,8 @@ class DeviceGraphStore:
         s = _lib.HcgPackedStore()
         s.G, s.N, s.E = self.ds.G, self.ds.N, self.ds.E
         s.F, s.Fu, s.Ff, s.edge_kind = self.ds.F, self.ds.Fu, self.ds.Ff, self.ds.edge_kind
-        for name in ("col_slot", "node_ptr", "edge_ptr", "y", "xu8", "xf32", "edges"):
+        s.Fb, s.bit_stride = self.ds.Fb, (self.ds.Fb + 7) // 8
+        for name in ("col_slot", "node_ptr", "edge_ptr", "y", "xu8", "xf32", "edges", "xbits"):
             setattr(s, name, base + self.ds.layout[name][0])
         self.c_store = s
 
@@ -320,9 +344,9 @@ class DeviceGraphStore:
         """The device half of ``batch(ids)``: ``meta_d`` int64 [3, B+1] on the device = (node offsets, edge offsets,
         graph ids) of the selection.  One hcg_unpack_batch launch."""
         ds, dev = self.ds, self.device
-        x = torch.empty(N_out, ds.F, dtype=torch.float32, device=dev)
-        ei = torch.empty(2, E_out, dtype=torch.int64, device=dev)
-        bvec = torch.empty(N_out, dtype=torch.int64, device=dev) if with_batch_vector else None
+        x = ops.bucketed_empty((N_out, ds.F), torch.float32, dev)
+        ei = ops.bucketed_empty((2, E_out), torch.int64, dev)
+        bvec = ops.bucketed_empty((N_out,), torch.int64, dev) if with_batch_vector else None
         y = torch.empty(B, dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             _lib.check(_lib.load().hcg_unpack_batch(
@@ -380,9 +404,9 @@ class DeviceGraphStore:
         ds, dev = self.ds, self.device
         B, N_out, E_out = ds.G, ds.N, ds.E
         node_ptr_d, edge_ptr_d = self._ptr_views()
-        x = torch.empty(N_out, ds.F, dtype=torch.float32, device=dev)
-        ei = torch.empty(2, E_out, dtype=torch.int64, device=dev)
-        bvec = torch.empty(N_out, dtype=torch.int64, device=dev) if with_batch_vector else None
+        x = ops.bucketed_empty((N_out, ds.F), torch.float32, dev)
+        ei = ops.bucketed_empty((2, E_out), torch.int64, dev)
+        bvec = ops.bucketed_empty((N_out,), torch.int64, dev) if with_batch_vector else None
         y = torch.empty(B, dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             _lib.check(_lib.load().hcg_unpack_batch(

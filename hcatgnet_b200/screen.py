@@ -45,7 +45,9 @@ class DevicePrefetcher:
             with torch.cuda.stream(self.copy_stream):
                 owner = getattr(h, "_owner", None)     # the pinned torch buffer behind an image packed with pinned=True
                 blob_h = owner[:h.nbytes] if owner is not None else torch.from_numpy(h.blob)
-                store = DeviceGraphStore.from_blob(h, blob_h.to(self.device, non_blocking=True))
+                blob_d = ops.bucketed_empty((blob_h.numel(),), torch.uint8, self.device)
+                blob_d.copy_(blob_h, non_blocking=True)
+                store = DeviceGraphStore.from_blob(h, blob_d)
                 d = store.batch(None)
                 d._store = store
                 ev = torch.cuda.Event()
@@ -53,7 +55,13 @@ class DevicePrefetcher:
             self.queue.append((d, ev, h))
             return True
         with torch.cuda.stream(self.copy_stream):
-            mv = lambda t: None if t is None else t.to(self.device, non_blocking=True)  # noqa: E731
+            def mv(t):
+                if t is None or t.is_cuda:
+                    return t
+                t_d = ops.bucketed_empty(t.shape, t.dtype, self.device)     # (size buckets: see ops.bucketed_empty)
+                t_d.copy_(t, non_blocking=True)
+                return t_d
+
             ptr = getattr(h, "ptr", None)
             if ptr is not None and not ptr.is_cuda and ptr.numel() == h.num_graphs + 1 and h.x is not None:
                 # `batch` and `ptr` carry the same information: ship the (B+1)-entry ptr and rebuild the

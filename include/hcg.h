@@ -245,15 +245,17 @@ int hcg_batch_from_ptr(const int64_t* ptr, int64_t B, int64_t N, int64_t* batch,
  */
 typedef struct HcgPackedStore {
   int64_t G, N, E;            /* graphs, nodes, directed edges in the image */
-  int32_t F, Fu, Ff;          /* feature columns: total, stored as u8, stored as f32 (Fu + Ff == F) */
+  int32_t F, Fu, Ff;          /* feature columns: total, stored as u8, stored as f32 (Fu + Ff + Fb == F) */
   int32_t edge_kind;          /* bytes per local edge endpoint: 1, 2 or 4 */
-  const int32_t* col_slot;    /* [F]  >= 0: column of xu8;  < 0: ~column of xf32 */
+  const int32_t* col_slot;    /* [F]  0 .. 65535: column of xu8;  >= 65536: bit (slot - 65536) of the node's xbits row;  < 0: ~column of xf32 */
   const int64_t* node_ptr;    /* [G+1] */
   const int64_t* edge_ptr;    /* [G+1] */
   const float* y;             /* [G] */
   const uint8_t* xu8;         /* [N, Fu] */
   const float* xf32;          /* [N, Ff] */
   const void* edges;          /* [E, 2] (src, dst) local to the graph */
+  int32_t Fb, bit_stride;     /* columns whose every value is 0 or 1, stored as one bit each; bytes per node of xbits ((Fb + 7) / 8) */
+  const uint8_t* xbits;       /* [N, bit_stride]  bit k of a node: byte k / 8, bit k % 8 */
 } HcgPackedStore;
 
 /*

@@ -329,6 +329,16 @@ def test_device_graph_store_large_and_wire_format():
     ds16 = pkg.PackedDataset.from_arrays(big.x.numpy(), big.edge_index.numpy(), big.ptr.numpy(), big.y.numpy())
     assert ds16.edge_kind == 2 and ds16.Fu == 0
     _assert_same_batch(pkg.DeviceGraphStore(ds16, "cuda").batch([2, 0]), ds16.unpack_host([2, 0]))
+    # bit columns (one-hot / flag columns of the featuriser: one bit per node and column), mixed with byte and f32 columns
+    fb = synth_batch(500, n_features=25, seed=78, features="featuriser")
+    xm = fb.x.clone()
+    xm[:, 3] *= 5.0                     # 0 / 5: a byte column between the bit columns
+    dsb = pkg.PackedDataset.from_arrays(xm.numpy(), fb.edge_index.numpy(), fb.ptr.numpy(), fb.y.numpy())
+    assert (dsb.Fb, dsb.Fu, dsb.Ff) == (23, 1, 1)
+    sel = np.random.default_rng(2).permutation(500)[:123]
+    got = pkg.DeviceGraphStore(dsb, "cuda").batch(sel)
+    _assert_same_batch(got, dsb.unpack_host(sel))
+    assert torch.equal(got.x.cpu(), torch.cat([xm[fb.ptr[g]:fb.ptr[g + 1]] for g in sel]))
     # wire format: the same predictions as the f32 / i64 host batch
     opt = pkg.default_options()
     torch.manual_seed(0)

@@ -159,10 +159,14 @@ def test_packed_image_round_trip_real_graphs(tmp_path):
     graphs = _real_graphs()
     ds = PackedDataset.from_graphs(graphs)
     assert ds.G == len(graphs) and ds.edge_kind == 1
-    # the featuriser's one-hot columns go to u8, lossless: the image is several times smaller than the tensors
+    # the featuriser's one-hot / flag columns take one bit each, lossless: the image is many times smaller than the tensors
     full = Batch.from_data_list(graphs)
-    assert ds.Fu >= ds.F - 2
-    assert ds.nbytes * 3 < full.x.numel() * 4 + full.edge_index.numel() * 8
+    assert ds.Fb + ds.Fu >= ds.F - 2 and ds.Fb >= ds.F - 4
+    assert ds.nbytes * 6 < full.x.numel() * 4 + full.edge_index.numel() * 8
+    old = PackedDataset.from_arrays(full.x.numpy(), full.edge_index.numpy(), full.ptr.numpy(), full.y.numpy(), full.idx.numpy(),
+                                    bits=False)   # the byte-per-value split of round 1
+    assert old.Fb == 0 and old.Fu == ds.Fb + ds.Fu and ds.nbytes < old.nbytes
+    _same_batch(old.unpack_host(), full)
     _same_batch(ds.unpack_host(), full)
     ids = [7, 3, 3, 39, 0, 12]
     _same_batch(ds.unpack_host(ids), Batch.from_data_list([graphs[i] for i in ids]))
@@ -191,7 +195,19 @@ def test_packed_image_column_and_edge_kinds():
         graphs.append({"x": torch.from_numpy(x), "edge_index": torch.from_numpy(e.astype(np.int64)), "y": torch.tensor([float(n)]),
                        "idx": n, "fold": n % 3})
     ds = PackedDataset.from_graphs(graphs)
-    assert ds.edge_kind == 2 and ds.Fu == 2 and ds.Ff == 3 and ds.max_graph_nodes == 300
+    assert ds.edge_kind == 2 and ds.Fu == 2 and ds.Ff == 3 and ds.Fb == 0 and ds.max_graph_nodes == 300
+    # bit columns: every value 0 or 1; a column holding -0.0 must stay f32 (the sign would be lost); 11 bit columns
+    # need two bytes per node
+    xb = (gen.random((40, 14)) < 0.4).astype(np.float32)
+    xb[:, 12] *= 7.0                       # 0 / 7: a byte column
+    xb[3, 13] = -0.0                       # compares equal to 0
+    xb[:, 5] = gen.random(40).astype(np.float32)
+    gb = [{"x": torch.from_numpy(xb[:25]), "edge_index": torch.tensor([[0, 1], [1, 0]]), "y": torch.tensor([1.0])},
+          {"x": torch.from_numpy(xb[25:]), "edge_index": torch.zeros(2, 0, dtype=torch.int64), "y": torch.tensor([2.0])}]
+    dsb = PackedDataset.from_graphs(gb)
+    assert (dsb.Fb, dsb.Fu, dsb.Ff) == (11, 1, 2) and dsb.xbits.shape == (40, 2)
+    back = dsb.unpack_host()
+    assert np.array_equal(back.x.numpy().view(np.uint32), xb.view(np.uint32))      # bit patterns, -0.0 included
     assert list(ds.fold) == [0, 1, 2] and list(ds.idx) == sizes
     from hcatgnet_b200.data import Batch
     _same_batch(ds.unpack_host([2, 0, 1, 0]), Batch.from_data_list([graphs[i] for i in (2, 0, 1, 0)]))
