@@ -29,7 +29,7 @@ class Batch:
     """A disjoint union of graphs: nodes concatenated, edge indices offset per graph."""
 
     def __init__(self, x, edge_index, batch, ptr=None, y=None, idx=None, num_graphs=None, edges_grouped=None):
-        self.x, self.edge_index, self.batch, self.ptr, self.y, self.idx = x, edge_index, batch, ptr, y, idx
+        self.x, self.edge_index, self._batch, self.ptr, self.y, self.idx = x, edge_index, batch, ptr, y, idx
         # True when edge_index is known to list the edges graph by graph (this module's own collate
         # does); lets hcg_collate take its graph-local path without a status read-back
         self.edges_grouped = edges_grouped
@@ -82,6 +82,23 @@ class Batch:
         return out
 
     @property
+    def batch(self):
+        """The N-entry graph id of every node.  It says what ``ptr`` says; loaders that ship ``ptr`` leave it out and it
+        is rebuilt here on first use (on the device: ``hcg_batch_from_ptr``) - the kernels themselves work from ``ptr``."""
+        if self._batch is None and self.ptr is not None and self.x is not None:
+            if self.ptr.is_cuda:
+                from . import ops
+                self._batch = ops.batch_from_ptr(self.ptr, int(self.x.shape[0]))
+            else:
+                self._batch = torch.repeat_interleave(torch.arange(self.ptr.numel() - 1, dtype=torch.int64),
+                                                      self.ptr[1:] - self.ptr[:-1])
+        return self._batch
+
+    @batch.setter
+    def batch(self, value):
+        self._batch = value
+
+    @property
     def num_nodes(self) -> int:
         return int(self.x.shape[0])
 
@@ -89,7 +106,7 @@ class Batch:
         """In place, returning self (like PyG's ``Data.to``), so a collate plan cached on the
         object by the model survives ``batch = batch.to(device)`` when nothing moves."""
         moved = False
-        for name in ("x", "edge_index", "batch", "ptr", "y", "idx", "edge_ptr"):
+        for name in ("x", "edge_index", "_batch", "ptr", "y", "idx", "edge_ptr"):
             t = getattr(self, name)
             if t is not None:
                 t2 = t.to(device, non_blocking=non_blocking)
@@ -100,7 +117,7 @@ class Batch:
         return self
 
     def pin_memory(self) -> "Batch":
-        for name in ("x", "edge_index", "batch", "ptr", "y", "idx", "edge_ptr"):
+        for name in ("x", "edge_index", "_batch", "ptr", "y", "idx", "edge_ptr"):
             t = getattr(self, name)
             if t is not None and not t.is_cuda:
                 setattr(self, name, t.pin_memory())

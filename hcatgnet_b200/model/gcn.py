@@ -233,7 +233,9 @@ class GCN(_GCNBase):
     """reference model/gcn.py:9-76."""
 
     def forward(self, reaction_graph, return_graph_embedding=False):
-        x, edge_index, batch = reaction_graph.x, reaction_graph.edge_index, reaction_graph.batch
+        x, edge_index = reaction_graph.x, reaction_graph.edge_index
+        # (our Batch builds its batch vector lazily from ptr: the kernels work from ptr, so leave it alone if it is not there yet)
+        batch = ops.batch_vector_if_built(reaction_graph)
         # edge_weight is None on this path, so `improved` does not change the normalisation
         # (self-loop weight 1.0) — the behaviour the shipped golden outputs pin (SURVEY.md fact 4)
         out, graph_emb = self._run(x, edge_index, batch, _num_graphs_of(reaction_graph, batch, x.shape[0]),

@@ -137,8 +137,8 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
         raise ValueError(f"batch has {bt.numel()} entries for {N} nodes")
     if ew is not None and ew.numel() != E:
         raise ValueError(f"edge_weight has {ew.numel()} entries for {E} edges")
-    if bt is None and B > 1 and (ptr is None or edge_ptr is None):
-        raise ValueError("batch vector (or ptr + edge_ptr) required when num_graphs > 1")
+    if bt is None and B > 1 and ptr is None:
+        raise ValueError("batch vector (or ptr) required when num_graphs > 1")
     i32 = dict(dtype=torch.int32, device=device)
     f32 = dict(dtype=torch.float32, device=device)
     with torch.cuda.device(device):
@@ -173,6 +173,8 @@ def collate(edge_index: torch.Tensor, batch: torch.Tensor | None, num_nodes: int
                 _ptr(plan.t_rowptr), _ptr(plan.t_col), _ptr(plan.t_eid), _ptr(ws), ws.numel(), st))
             plan._keep += [ptr_d, eptr_d]
         else:
+            if bt is None and B > 1:       # the general kernels work from the N-entry batch vector
+                bt = batch_from_ptr(to_device(ptr, device, torch.int64), N)
             _lib.check(lib.hcg_collate(
                 _ptr(ei), E, _ptr(bt), N, B, float(fill), _ptr(ew), 2.0 if improved else 1.0, flags,
                 _ptr(plan.rowptr), _ptr(plan.col), _ptr(plan.eid), _ptr(plan.dis), _ptr(plan.graph_ptr),
@@ -203,6 +205,14 @@ def batch_from_ptr(ptr: torch.Tensor, num_nodes: int) -> torch.Tensor:
     with torch.cuda.device(ptr.device):
         _lib.check(_lib.load().hcg_batch_from_ptr(_ptr(ptr), int(ptr.numel()) - 1, int(num_nodes), _ptr(out), _stream(ptr.device)))
     return out
+
+
+def batch_vector_if_built(holder):
+    """``holder.batch`` unless the holder is one of our lazily-built batches that carries ``ptr`` / ``edge_ptr`` and has
+    not built its N-entry batch vector yet (the collate kernels then work from the offsets: no need to build it)."""
+    if hasattr(holder, "_batch") and getattr(holder, "ptr", None) is not None and getattr(holder, "edge_ptr", None) is not None:
+        return holder._batch
+    return holder.batch
 
 
 def cached_collate(holder, edge_index, batch, num_nodes, num_graphs, device, edge_weight=None,

@@ -48,7 +48,7 @@ class DevicePrefetcher:
                 blob_d = ops.bucketed_empty((blob_h.numel(),), torch.uint8, self.device)
                 blob_d.copy_(blob_h, non_blocking=True)
                 store = DeviceGraphStore.from_blob(h, blob_d)
-                d = store.batch(None)
+                d = store.batch(None, with_batch_vector=False)    # (Batch.batch rebuilds it from ptr if anybody asks)
                 d._store = store
                 ev = torch.cuda.Event()
                 ev.record(self.copy_stream)
@@ -67,7 +67,7 @@ class DevicePrefetcher:
                 # `batch` and `ptr` carry the same information: ship the (B+1)-entry ptr and rebuild the
                 # N-entry batch vector on the device (5 % fewer bytes over PCIe for a reaction graph)
                 ptr_d = mv(ptr)
-                bt = ops.batch_from_ptr(ptr_d, int(h.x.shape[0]))
+                bt = None          # (Batch.batch rebuilds it on the device if anybody asks)
             else:
                 ptr_d, bt = None, mv(h.batch)
             d = Batch(mv(h.x), mv(h.edge_index), bt, ptr_d, mv(h.y), h.idx, h.num_graphs,
@@ -89,7 +89,7 @@ class DevicePrefetcher:
             cur = torch.cuda.current_stream(self.device)
             cur.wait_event(ev)
             store = getattr(d, "_store", None)
-            for t in (d.x, d.edge_index, d.batch, d.ptr, d.y, getattr(d, "edge_ptr", None), getattr(d, "_keepalive", None),
+            for t in (d.x, d.edge_index, d._batch, d.ptr, d.y, getattr(d, "edge_ptr", None), getattr(d, "_keepalive", None),
                       store.blob_dev if store is not None else None):
                 if t is not None and t.is_cuda:
                     t.record_stream(cur)

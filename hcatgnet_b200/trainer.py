@@ -95,7 +95,7 @@ class FusedTrainer:
         x = ops.to_device(batch.x, dev, torch.float32)
         y = ops.to_device(batch.y, dev, torch.float32)
         B = int(batch.num_graphs)
-        plan = ops.cached_collate(batch, batch.edge_index, batch.batch, x.shape[0], B, dev, transpose=True,
+        plan = ops.cached_collate(batch, batch.edge_index, ops.batch_vector_if_built(batch), x.shape[0], B, dev, transpose=True,
                                   validate=self.validate, max_graph_nodes=int(getattr(batch, "max_graph_nodes", 0) or 0),
                                   grouped=getattr(batch, "edges_grouped", None))
         params = [p.data for p in self.params]

@@ -109,8 +109,8 @@ def test_predict_ensemble_stream_one_pass_equals_per_model_launches(pkg):
     for a, b in zip(runs[True], runs[False]):
         for u, v in zip(a, b):
             assert torch.equal(u, v)
-    # per batch: k_batch_from_ptr (prefetcher), k_ens_prep, k_tile_desc, k_tc_fwd_ens, k_readout2_ens
-    assert runs[True, "launches"] == 5 * len(batches)
+    # per batch: k_ens_prep, k_tile_desc, k_tc_fwd_ens, k_readout2_ens (the batch vector is never built)
+    assert runs[True, "launches"] == 4 * len(batches)
     assert runs[False, "launches"] > runs[True, "launches"]
 
 
