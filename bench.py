@@ -506,9 +506,9 @@ def measure(cx: Ctx, mode: str, batch: int, hidden: int, convs: int, steps: int,
                       if mode == "infer" else "hcatgnet_b200.DevicePrefetcher + FusedTrainer.step"}
 
     # ---- the same, with the batches in the packed wire format ----------
-    # Node features with the block structure of the reference featuriser (24 one-hot / binary columns -> u8,
-    # temperature -> f32), endpoints local to their graph in u8: ~4x fewer bytes over PCIe, expanded on the
-    # device by hcg_unpack_batch into the very tensors PyG's collate would produce.  Same graphs as `host`.
+    # Node features with the block structure of the reference featuriser (24 one-hot / binary columns -> one bit
+    # each, temperature -> f32), endpoints local to their graph in u8: ~11x fewer bytes over PCIe, consumed as they
+    # are by hcg_gcn_forward_packed (the conv kernel expands a tile's rows in shared memory).  Same graphs as `host`.
     if want_packed and mode == "infer":
         packed = []
         for i in range(POOL):
@@ -524,8 +524,9 @@ def measure(cx: Ctx, mode: str, batch: int, hidden: int, convs: int, steps: int,
         ms_p = cx.timed(run_packed, steps, whole=True)
         rec["e2e_packed"] = {"value": graphs_total / (ms_p * 1e-3), "unit": UNIT, "ms_per_step": ms_p / steps,
                              "h2d_bytes_per_step": int(np.mean([p.nbytes for p in packed])), "d2h_bytes_per_step": d2h,
-                             "api": "hcatgnet_b200.predict_stream over PackedDataset chunks (one image copy + hcg_unpack_batch per step)",
-                             "x": "featuriser-shaped: 24 one-hot/binary columns as u8 + 1 f32 column (lossless)"}
+                             "api": "hcatgnet_b200.predict_stream over PackedDataset chunks (one image copy per step, "
+                                    "hcg_gcn_forward_packed straight from the image: no unpack, no collate)",
+                             "x": "featuriser-shaped: 24 one-hot/binary columns as one bit each + 1 f32 column (lossless)"}
         del packed
     elif want_packed:
         # training from a device-resident packed store: shuffled mini-batches are assembled on the GPU

@@ -121,6 +121,9 @@ SIGNATURES = {
     "hcg_batch_from_ptr": (C.c_int, [_fp, C.c_int64, C.c_int64, _fp, _fp]),
     "hcg_unpack_batch": (C.c_int, [C.POINTER(HcgPackedStore), _fp, C.c_int64, C.c_int64, _fp, _fp, _fp, _fp, C.c_int64,
                                    _fp, _fp, _fp]),
+    "hcg_forward_packed_supported": (C.c_int, [C.POINTER(HcgPackedStore), C.POINTER(HcgParams)]),
+    "hcg_gcn_forward_packed": (C.c_int, [C.POINTER(HcgPackedStore), C.c_int64, C.c_int64, C.c_float, C.POINTER(HcgParams),
+                                         _fp, _fp, _fp, C.c_size_t, _fp]),
     "hcg_rmse_seed": (C.c_int, [_fp, _fp, C.c_int64, C.c_int, _fp, _fp, _fp]),
     "hcg_train_step_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.POINTER(HcgParams)]),
     "hcg_train_step": (C.c_int, [_fp, _fp, C.c_int64, _fp, _fp, _fp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_float,

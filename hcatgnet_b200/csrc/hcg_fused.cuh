@@ -62,6 +62,11 @@ int launch_tc_fwd_coo(const FusedFwdArgs& a, const int64_t* edge_index, const in
                       int64_t E, void* ws, cudaStream_t st);
 int tc_fwd_coo_flags(const void* ws, int64_t B, cudaStream_t st, int* flags);
 
+// packed-image variant: graphs [first, first + a.B) of a packed image resident in device memory (a.x is not used);
+// same workspace and flags as the COO variant.  tc_fwd_packed_fits: the image's per-node bytes fit the kernel's stage.
+bool tc_fwd_packed_fits(const HcgPackedStore& pk);
+int launch_tc_fwd_packed(const FusedFwdArgs& a, const HcgPackedStore& pk, int64_t first, void* ws, cudaStream_t st);
+
 // one-pass ensemble variant (hcg_tc_ens.cu): M models (stacked conv weights: w0 [M,64,F], b0 [M,64], w1 [M,64,64],
 // b1 [M,64]) over one batch; emb [M,B,128]; wimg: scratch of tc_fwd_ens_image_floats(M) floats; ws as the COO variant's
 // (tc_fwd_coo_workspace_bytes, flags by tc_fwd_coo_flags).  Two conv layers, H = 64, F <= 32.

@@ -1370,6 +1370,41 @@ extern "C" int hcg_forward_coo_status(const void* ws, int64_t B, void* stream, i
   return rc;
 }
 
+// ---- forward straight from a packed graph image (the on-disk / on-wire format) -------------
+extern "C" int hcg_forward_packed_supported(const HcgPackedStore* store, const HcgParams* p) {
+  if (!store || !hcg_forward_coo_supported(p)) return 0;
+  if (store->F != p->F || store->Fb < 0 || store->Fu + store->Ff + store->Fb != store->F) return 0;
+  if (store->Fb > 0 && (store->xbits == nullptr || store->bit_stride * 8 < store->Fb)) return 0;
+  return tc_fwd_packed_fits(*store) ? 1 : 0;
+}
+
+extern "C" int hcg_gcn_forward_packed(const HcgPackedStore* store, int64_t first, int64_t B, float fill, const HcgParams* p,
+                                      float* out, float* emb, void* ws, size_t ws_bytes, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = check_params(p);
+  if (rc) return rc;
+  HCG_REQUIRE(store != nullptr && out && emb && ws, HCG_ERR_INVALID_ARG, "NULL store/out/emb/workspace");
+  HCG_REQUIRE(first >= 0 && B >= 0 && first + B <= store->G, HCG_ERR_INVALID_ARG, "graphs [%lld, %lld) outside the image (G=%lld)",
+              (long long)first, (long long)(first + B), (long long)store->G);
+  HCG_REQUIRE(store->N < INT32_MAX && store->E < INT32_MAX, HCG_ERR_UNSUPPORTED, "image above 2^31 nodes or edges");
+  if (!hcg_forward_packed_supported(store, p))
+    return set_err(HCG_ERR_UNSUPPORTED, "packed forward needs the edge-list forward's network shape, byte edge endpoints, F == the "
+                                        "image's F <= 32 and at most ~50 packed bytes per node (use hcg_unpack_batch + hcg_gcn_forward_coo)");
+  HCG_REQUIRE(store->node_ptr && store->edge_ptr && store->col_slot && (store->E == 0 || store->edges) &&
+              (store->Fu == 0 || store->xu8) && (store->Ff == 0 || store->xf32), HCG_ERR_INVALID_ARG, "NULL section pointer");
+  CooWs w = carve_coo(ws, B, p);
+  HCG_REQUIRE(ws_bytes >= w.bytes, HCG_ERR_WORKSPACE, "packed forward workspace too small: %zu < %zu", ws_bytes, w.bytes);
+  if (B == 0) return HCG_OK;
+  note_region(st);
+  FusedFwdArgs a{};
+  for (int l = 0; l < p->L; ++l) { a.conv_w[l] = p->conv_w[l]; a.conv_b[l] = p->conv_b[l]; }
+  a.emb = emb;
+  a.B = B; a.F = p->F; a.Fp = (p->F + 3) / 4 * 4; a.L = p->L; a.slope = p->slope; a.fill = fill;
+  rc = launch_tc_fwd_packed(a, *store, first, w.tc, st);
+  if (rc) return rc;
+  return run_readout(p, emb, out, nullptr, w.hid, B, st);
+}
+
 // ---- one-pass ensemble forward ------------------------------------------------
 struct EnsWs {
   char* tc;

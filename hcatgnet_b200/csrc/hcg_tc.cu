@@ -193,14 +193,16 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
             int nslots, int nwin, int cap, TcTile* __restrict__ tiles, int* __restrict__ counts,
             int* __restrict__ overflow_count, int* __restrict__ overflow_list, int* __restrict__ overflow_flag,
             const int64_t* __restrict__ node_ptr64, const int64_t* __restrict__ edge_ptr64, const int64_t* __restrict__ ei,
-            int* __restrict__ dflags, float* __restrict__ emb) {
+            int* __restrict__ dflags, float* __restrict__ emb, int packed) {
   const int slot = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   const int lane = threadIdx.x & 31;
   if (slot >= nslots) return;  // whole warps leave together
   // COO mode (ei != NULL): node / edge offsets come from the batch's own int64 offset vectors, a graph may have
   // no edges, the copy windows are those of the two edge_index rows, and a graph that does not fit a tile is
   // REFUSED (flag in dflags[slot], embedding row zeroed) - there is no fallback kernel behind this path.
-  const bool coo = ei != nullptr;
+  // packed mode: the same, for the kernel variant that reads a packed graph image (byte-granular slices of 64-byte
+  // aligned sections: no copy window can leave the image, no tile is flagged for ordinary loads)
+  const bool coo = ei != nullptr || packed != 0;
   int refused = 0;
   TcTile* out = tiles + (size_t)slot * cap;
   int total = 0;
@@ -255,6 +257,7 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
         }
         continue;
       }
+      if (packed) continue;
       uintptr_t lo; uint32_t bytes; int lead;
       bool m = false;
       copy_window(reinterpret_cast<uintptr_t>(x + (int64_t)gp[k] * F), n * F, &lo, &bytes, &lead);
@@ -396,9 +399,15 @@ __device__ unsigned long long g_tc_timing[16];
 // The records of a row are kTcRows apart (plane t holds record t of every row): the gathers' record loads are
 // conflict-free.  Same arithmetic in the same order as the CSR variant on hcg_collate's output: identical bits.
 // Refused input (kCoo* flags): see k_tile_desc; the caller falls back to hcg_collate + hcg_gcn_forward.
-template <int F_, int NS, bool COO = false>
+//
+// MODE 2 (PK): the same from a PACKED graph image resident in device memory (hcatgnet_b200/packed.py; a.pk): the
+// feeding lanes copy each graph's slices of the bit / byte / f32 feature sections and of the local byte edge pairs
+// (a few bytes per node instead of 4 F) into the stage, the slot expands them to fp32 rows in its x buffer (what
+// hcg_unpack_batch would have written to HBM and this kernel read back), and the records come from the byte pairs.
+template <int F_, int NS, int MODE = 0>
 __global__ void __launch_bounds__(NS * 256, 1)
 k_tc_fwd(const TcArgs a) {
+  constexpr bool COO = MODE != 0, PK = MODE == 2;
 #ifdef HCG_TC_TIMING
   long long t_prev = clock64();
 #endif
@@ -411,6 +420,7 @@ k_tc_fwd(const TcArgs a) {
   constexpr int NBS = COO ? kTcRows : 1;   // records between consecutive neighbour records of a row
   __shared__ float s_lut[32];              // COO: (deg + fill)^-1/2 for deg = 0..31
   __shared__ int s_bad[NS];                // COO: refusal flags of the slot
+  __shared__ int s_slot[32];               // PK: where column c of x lives in the image (HcgPackedStore.col_slot)
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ uint64_t bar_stage[NS][2];
   __shared__ uint64_t bar_mma[NS];
@@ -476,6 +486,7 @@ k_tc_fwd(const TcArgs a) {
     }
     if (tid < NS) s_bad[tid] = 0;
     if (gt < kTcRows) smi[dg_w + gt] = 0;
+    if (PK && tid < 32) s_slot[tid] = tid < F ? a.pk.col_slot[tid] : 0;
   }
   ptx::fence_proxy_async_smem();
   ptx::tc_fence_before_sync();
@@ -494,6 +505,12 @@ k_tc_fwd(const TcArgs a) {
   const int ntiles = a.counts[slot_id];
   const TcTile* my_tiles = a.tiles + (size_t)slot_id * a.cap;
 
+  // PK: byte offsets, inside a stage, of the four staged arrays (q = 1 edge pairs | 0 bit rows | 2 byte rows | 3 f32 rows);
+  // every region leaves room for the 16-byte granular windows of two slices
+  const int pk_bs = PK ? a.pk.bit_stride : 0, pk_fu = PK ? a.pk.Fu : 0, pk_ff = PK ? a.pk.Ff : 0;
+  const int pk_ob = 2 * kTcEcap + 64;     // (two windows: up to 15 bytes of lead and 15 of rounding each)
+  const int pk_ou = pk_ob + ((kTcRows * pk_bs + 79) & ~15);
+  const int pk_of = pk_ou + ((kTcRows * pk_fu + 79) & ~15);
   // Feeding lanes (lane < 8 of pf_warp): lane = 4 gb + q copies slice q (0 x, 1 rowptr, 2 col, 3 dis) of graph gb.
   // The record of tile t travels global -> recs[t & 1] by cp.async (three lanes, 16 bytes each), a tile ahead.
   auto fetch_rec = [&](int t) {
@@ -511,7 +528,7 @@ k_tc_fwd(const TcArgs a) {
       ptx::cp_async_wait_all();   // this lane's part of the record ...
       __syncwarp();               // ... and the other lanes'
     }
-    if (lane >= 8 || ((lane & 3) == 0) != want_x) return;
+    if (lane >= 8 || (PK ? want_x : ((lane & 3) == 0) != want_x)) return;   // (PK: nothing waits for the x buffer: all eight go out early)
     if (t >= ntiles) {
       if (lane == 1) m->gA = -1;
       ptx::mbar_arrive(bar);
@@ -522,6 +539,31 @@ k_tc_fwd(const TcArgs a) {
     const int n0 = gb ? r1.y : r0.y, n = gb ? r1.z : r0.z, e0 = gb ? r1.w : r0.w, e = gb ? r2.y : r2.x;
     const bool have = gb == 0 || r1.x >= 0;
     const bool manual = (r2.z & kTileManual) != 0;
+    if (PK) {
+      // byte slices of the image: q = 0 bit rows, 1 local (src, dst) byte pairs, 2 byte rows, 3 f32 rows
+      const unsigned char* arr = q == 0 ? a.pk.xbits : q == 1 ? static_cast<const unsigned char*>(a.pk.edges)
+                               : q == 2 ? a.pk.xu8 : reinterpret_cast<const unsigned char*>(a.pk.xf32);
+      const int64_t unit = q == 0 ? pk_bs : q == 1 ? 2 : q == 2 ? pk_fu : 4 * pk_ff;
+      const uintptr_t pA = reinterpret_cast<uintptr_t>(arr) + (uintptr_t)((q == 1 ? (int64_t)r0.w : (int64_t)r0.y) * unit);
+      const uintptr_t pS = reinterpret_cast<uintptr_t>(arr) + (uintptr_t)((q == 1 ? (int64_t)e0 : (int64_t)n0) * unit);
+      const uint32_t cA = (uint32_t)((q == 1 ? r2.x : r0.z) * unit), cS = (uint32_t)((q == 1 ? e : n) * unit);
+      const uintptr_t loA = pA & ~uintptr_t(15), loS = pS & ~uintptr_t(15);
+      const uint32_t bA = (uint32_t)((pA - loA) + cA + 15) & ~15u, bS = (uint32_t)((pS - loS) + cS + 15) & ~15u;
+      const int reg = q == 0 ? pk_ob : q == 1 ? 0 : q == 2 ? pk_ou : pk_of;
+      if (lane == 1) {
+        m->gA = r0.x; m->n0A = r0.y; m->nA = r0.z; m->e0A = r0.w;
+        m->gB = r1.x; m->n0B = r1.y; m->nB = r1.x >= 0 ? r1.z : 0; m->e0B = r1.w;
+        m->eA = r2.x; m->eB = r2.y; m->flags = 0;
+      }
+      m->off[lane] = reg + (gb ? (int)bA : 0) + (int)(pS - loS);     // BYTES from the stage's start to element 0 of the slice
+      if (!have || cS == 0) {
+        ptx::mbar_arrive(bar);
+      } else {
+        ptx::mbar_expect_tx(bar, bS);
+        ptx::bulk_g2s(reinterpret_cast<unsigned char*>(smf + cs_w0 + s * csw) + reg + (gb ? bA : 0u), reinterpret_cast<const void*>(loS), bS, bar);
+      }
+      return;
+    }
     // slice q of graph A too (every lane needs its window size: graph B's slice lands right behind it)
     uintptr_t pA, pS;
     int cA, cS;
@@ -657,6 +699,40 @@ k_tc_fwd(const TcArgs a) {
       }
       ptx::named_bar_sync(bar_full, kSlotThreads);
     }
+    if (PK) {
+      // ---- the tile's x rows, expanded from the staged bit / byte / f32 slices into dense fp32 rows ---------
+      // (two threads per row, half of the columns each; a thread's columns are walked from a row-dependent start so
+      //  that the lanes of a warp - consecutive rows, pitch F floats - write different banks for any F)
+      const unsigned char* st8 = reinterpret_cast<const unsigned char*>(smf + srp);
+      const int r = gt & 127, half = gt >> 7;
+      if (r < ntot) {
+        const int gb = r >= nA, lr = gb ? r - nA : r;
+        const unsigned char* pb = st8 + mp->off[4 * gb + 0] + lr * pk_bs;
+        uint32_t bits = 0;                       // F <= 32: at most 32 bit columns, four bytes
+        for (int q = 0; q < pk_bs; ++q) bits |= (uint32_t)pb[q] << (8 * q);
+        const unsigned char* pu = st8 + mp->off[4 * gb + 2] + lr * pk_fu;
+        const float* pf = reinterpret_cast<const float*>(st8 + mp->off[4 * gb + 3]) + lr * pk_ff;
+        const int c0 = half ? (F + 1) >> 1 : 0, w = half ? F - ((F + 1) >> 1) : (F + 1) >> 1;
+        float* xo = smf + sx + r * F + c0;
+        const int cs = r % (w > 0 ? w : 1);
+        constexpr int WMAX = F_ > 0 ? (F_ + 1) / 2 : 16;
+        int sl[WMAX];
+#pragma unroll
+        for (int j = 0; j < WMAX; ++j) {          // (unrolled: the table reads, then the data reads, go out together)
+          int c = cs + j; c = c >= w ? c - w : c;
+          sl[j] = j < w ? s_slot[c0 + c] : 65536;
+        }
+        float v[WMAX];
+#pragma unroll
+        for (int j = 0; j < WMAX; ++j)
+          v[j] = sl[j] >= 65536 ? (float)((bits >> ((sl[j] - 65536) & 31)) & 1u) : sl[j] >= 0 ? (float)pu[sl[j]] : pf[~sl[j]];
+#pragma unroll
+        for (int j = 0; j < WMAX; ++j) {
+          int c = cs + j; c = c >= w ? c - w : c;
+          if (j < w) xo[c] = v[j];
+        }
+      }
+    }
     // ---- this thread's row: which graph of the tile, where its slices start -------------------------
     const bool row_ok = i < ntot;
     const bool warp_ok = i_warp_min < ntot;  // this warp owns at least one row of the tile
@@ -665,7 +741,7 @@ k_tc_fwd(const TcArgs a) {
     const int rowbase = inB ? nA : 0;
     const int li = i - rowbase;               // row inside its graph
     const int jb = n0 - rowbase;              // tile row of batch node j = j - jb
-    const int xt_o = sx + (inB ? mp->off[4] : mp->off[0]) - rowbase * F;   // x[tile row r][c] at smf[xt_o + r F + c]
+    const int xt_o = PK ? sx : sx + (inB ? mp->off[4] : mp->off[0]) - rowbase * F;   // x[tile row r][c] at smf[xt_o + r F + c]
     const int nbo = COO ? nb_w + 2 * i                                    // COO: record t of this row at smi[nbo + 2 t kTcRows]
                         : nb_w + 2 * ((inB ? eA : 0) - e0);               // record of CSR slot pos at smi[nbo + 2 pos]
     int beg = 0, deg = 0;
@@ -677,9 +753,17 @@ k_tc_fwd(const TcArgs a) {
       for (int k = gt; k < etot; k += kSlotThreads) {
         const int eb = k >= eA;                    // edge of graph B
         const int kk = eb ? k - eA : k;
-        const int2 sv = *reinterpret_cast<const int2*>(smi + srp + mp->off[4 * eb + 1] + 2 * kk);
-        const int2 dv = *reinterpret_cast<const int2*>(smi + scl + mp->off[4 * eb + 2] + 2 * kk);
-        const int gn0 = eb ? mp->n0B : mp->n0A, gn = eb ? nB : nA, rb = eb ? nA : 0;
+        int2 sv, dv;
+        int gn0 = eb ? mp->n0B : mp->n0A;
+        const int gn = eb ? nB : nA, rb = eb ? nA : 0;
+        if (PK) {     // a pair of bytes local to the graph
+          const unsigned short pr = *reinterpret_cast<const unsigned short*>(reinterpret_cast<const unsigned char*>(smf + srp) +
+                                                                             mp->off[4 * eb + 1] + 2 * kk);
+          sv = make_int2(pr & 0xff, 0); dv = make_int2(pr >> 8, 0); gn0 = 0;
+        } else {
+          sv = *reinterpret_cast<const int2*>(smi + srp + mp->off[4 * eb + 1] + 2 * kk);
+          dv = *reinterpret_cast<const int2*>(smi + scl + mp->off[4 * eb + 2] + 2 * kk);
+        }
         const int ts = sv.x - gn0, td = dv.x - gn0;
         if (sv.y != 0 || dv.y != 0 || (unsigned)ts >= (unsigned)gn || (unsigned)td >= (unsigned)gn || ts == td) {
           bad |= kCooBadEdge;     // (a self-loop would be dropped and replaced by the fill-weight one: not handled here)
@@ -968,7 +1052,7 @@ int launch_tile_desc(const int32_t* graph_ptr, const int32_t* rowptr, const int3
   HCG_CUDA_OK(cudaMemsetAsync(overflow_count, 0, sizeof(int), st));
   k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(graph_ptr, rowptr, col, dis, x, F, N, E, B, p.W, p.nslots,
                                                                           p.nwin, p.cap, tiles, counts, overflow_count, overflow_list,
-                                                                          overflow_flag, nullptr, nullptr, nullptr, nullptr, nullptr);
+                                                                          overflow_flag, nullptr, nullptr, nullptr, nullptr, nullptr, 0);
   HCG_LAUNCH_OK(st, "k_tile_desc");
   return HCG_OK;
 }
@@ -1007,11 +1091,11 @@ static int tc_slots(int F, int L) {
   return env == 3 ? 3 : kTcDefaultSlots;
 }
 
-template <int F_, int NS, bool COO = false>
+template <int F_, int NS, int MODE = 0>
 static int launch_tc_variant(const TcArgs& a, int grid, size_t smem, cudaStream_t st) {
   static SmemConfigured configured;
-  if (int rc = ensure_dyn_smem(k_tc_fwd<F_, NS, COO>, smem, configured)) return rc;
-  k_tc_fwd<F_, NS, COO><<<(unsigned)grid, NS * 256, smem, st>>>(a);
+  if (int rc = ensure_dyn_smem(k_tc_fwd<F_, NS, MODE>, smem, configured)) return rc;
+  k_tc_fwd<F_, NS, MODE><<<(unsigned)grid, NS * 256, smem, st>>>(a);
   return HCG_OK;
 }
 
@@ -1069,7 +1153,8 @@ int launch_tile_desc_coo(const float* x, int F, const int64_t* edge_index, const
                          int64_t E, int64_t B, const TcPlan& p, const TcCooWs& w, float* emb, int emb_zero_cols, cudaStream_t st) {
   k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(nullptr, nullptr, nullptr, nullptr, x, F, N, E, B, p.W, p.nslots,
                                                                           p.nwin, p.cap, w.tiles, w.counts, nullptr, nullptr, nullptr,
-                                                                          node_ptr, edge_ptr, edge_index, w.dflags, emb_zero_cols > 0 ? emb : nullptr);
+                                                                          node_ptr, edge_ptr, edge_index, w.dflags, emb_zero_cols > 0 ? emb : nullptr,
+                                                                          edge_index == nullptr ? 1 : 0);
   HCG_LAUNCH_OK(st, "k_tile_desc");
   return HCG_OK;
 }
@@ -1089,11 +1174,44 @@ int launch_tc_fwd_coo(const FusedFwdArgs& f, const int64_t* edge_index, const in
   a.N = N; a.E = E;
   a.ei = edge_index;
   a.kflags = w.kflags;
-  const int rc = f.F == 25 ? launch_tc_variant<25, 2, true>(a, p.grid, smem, st)
-               : f.F == 32 ? launch_tc_variant<32, 2, true>(a, p.grid, smem, st)
-                           : launch_tc_variant<0, 2, true>(a, p.grid, smem, st);
+  const int rc = f.F == 25 ? launch_tc_variant<25, 2, 1>(a, p.grid, smem, st)
+               : f.F == 32 ? launch_tc_variant<32, 2, 1>(a, p.grid, smem, st)
+                           : launch_tc_variant<0, 2, 1>(a, p.grid, smem, st);
   if (rc) return rc;
   HCG_LAUNCH_OK(st, "k_tc_fwd_coo");
+  return HCG_OK;
+}
+
+// ---- packed-image variant ------------------------------------------------------------------------------
+// the staged slices of a tile must fit one stage: edge pairs + bit rows + byte rows + f32 rows, each with window slack
+bool tc_fwd_packed_fits(const HcgPackedStore& pk) {
+  const int ob = 2 * kTcEcap + 64;
+  const int ou = ob + ((kTcRows * pk.bit_stride + 79) & ~15);
+  const int of = ou + ((kTcRows * pk.Fu + 79) & ~15);
+  const int end = of + ((kTcRows * pk.Ff * 4 + 79) & ~15);
+  return pk.edge_kind == 1 && pk.F >= 1 && pk.F <= 32 && end <= (int)tc_layout(pk.F, 2, 2, true).csr_words * 4;
+}
+
+int launch_tc_fwd_packed(const FusedFwdArgs& f, const HcgPackedStore& pk, int64_t first, void* ws, cudaStream_t st) {
+  if (f.B <= 0) return HCG_OK;
+  TcCooWs w = carve_tc_coo(ws, f.B);
+  const TcPlan p = tc_plan(f.B, 2);
+  const size_t smem = tc_layout(f.F, f.L, 2, true).total;
+  if (int rc = launch_tile_desc_coo(nullptr, f.F, nullptr, pk.node_ptr + first, pk.edge_ptr + first, pk.N, pk.E, f.B, p, w, f.emb, 128, st))
+    return rc;
+  TcArgs a{};
+  a.f = f;
+  a.tiles = w.tiles;
+  a.counts = w.counts;
+  a.cap = p.cap;
+  a.N = pk.N; a.E = pk.E;
+  a.kflags = w.kflags;
+  a.pk = pk;
+  const int rc = f.F == 25 ? launch_tc_variant<25, 2, 2>(a, p.grid, smem, st)
+               : f.F == 32 ? launch_tc_variant<32, 2, 2>(a, p.grid, smem, st)
+                           : launch_tc_variant<0, 2, 2>(a, p.grid, smem, st);
+  if (rc) return rc;
+  HCG_LAUNCH_OK(st, "k_tc_fwd_packed");
   return HCG_OK;
 }
 

@@ -51,6 +51,7 @@ struct TcArgs {
   // edge-list variants (k_tc_fwd<.., COO = true>, k_tc_fwd_ens): the raw edge list instead of the CSR of f.rowptr / f.col / f.dis
   const int64_t* ei;        // [2, E]: row 0 sources, row 1 targets, grouped by graph
   int* kflags;              // [nslots]: per-slot refusal flags (plain stores, no memset needed)
+  HcgPackedStore pk;        // packed-image variant (k_tc_fwd<.., 2>): the image the graphs are read from
 };
 
 struct TcPlan {     // launch geometry of the work list for a batch of B graphs

@@ -233,6 +233,17 @@ class GCN(_GCNBase):
     """reference model/gcn.py:9-76."""
 
     def forward(self, reaction_graph, return_graph_embedding=False):
+        store = getattr(reaction_graph, "_packed_store", None)
+        if store is not None and not torch.is_grad_enabled() and getattr(reaction_graph, "_real", None) is None and \
+                _lib.load().hcg_config_get(_lib.HCG_CFG_FORWARD_PATH) == _lib.PATH_AUTO and \
+                (self.validate_inputs or ops.edge_list_hints_ok(reaction_graph)):
+            # a device-resident packed image that nobody has unpacked: inference straight from it
+            dev = reaction_graph.ptr.device
+            pd = [ops.to_device(p, dev, torch.float32) for p in self._flat_params()]
+            res = ops.forward_packed(store.c_store, 0, reaction_graph.num_graphs, self._dims(), pd, dev,
+                                     validate=self.validate_inputs)
+            if res is not None:
+                return res if return_graph_embedding == True else res[0]  # noqa: E712
         x, edge_index = reaction_graph.x, reaction_graph.edge_index
         # (our Batch builds its batch vector lazily from ptr: the kernels work from ptr, so leave it alone if it is not there yet)
         batch = ops.batch_vector_if_built(reaction_graph)

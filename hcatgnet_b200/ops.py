@@ -396,6 +396,32 @@ def forward_edge_list(x: torch.Tensor, edge_index: torch.Tensor, ptr: torch.Tens
     return out, emb
 
 
+def forward_packed(c_store, first: int, B: int, dims: NetDims, params, device, fill: float = 1.0, validate: bool = True):
+    """Inference on graphs ``[first, first + B)`` of a packed image resident on ``device`` (``hcg_gcn_forward_packed``: no
+    unpack, no collate; x and edge_index never exist in HBM).  Returns ``(out, emb)`` or ``None`` when the image / network
+    cannot take the path or - with ``validate`` - the device refused the graphs: unpack and go through the other paths."""
+    lib = _lib.load()
+    _check_param_shapes(dims, params)
+    pstruct = _params_struct(dims, params)
+    if not lib.hcg_forward_packed_supported(C.byref(c_store), C.byref(pstruct)):
+        return None
+    f32 = dict(dtype=torch.float32, device=device)
+    with torch.cuda.device(device):
+        out = torch.empty(B, dims.C, **f32)
+        emb = torch.empty(B, 2 * dims.H, **f32)
+        ws = _workspace(lib.hcg_forward_coo_workspace_bytes(B, C.byref(pstruct)), device)
+        st = _stream(device)
+        _lib.check(lib.hcg_gcn_forward_packed(C.byref(c_store), int(first), int(B), float(fill), C.byref(pstruct), _ptr(out), _ptr(emb),
+                                              _ptr(ws), ws.numel(), st))
+        ws.record_stream(torch.cuda.current_stream(device))
+        if validate:
+            flags = C.c_int32(0)
+            _lib.check(lib.hcg_forward_coo_status(_ptr(ws), B, st, C.byref(flags)))
+            if flags.value:
+                return None
+    return out, emb
+
+
 class EnsembleWeights:
     """The conv / readout weights of M same-architecture networks stacked along a new first axis (what
     ``hcg_gcn_forward_coo_ensemble`` takes).  Built once per ensemble from the models' flat parameter lists

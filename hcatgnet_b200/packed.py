@@ -396,6 +396,21 @@ class DeviceGraphStore:
             return self.blob_dev[off:off + nbytes].view(torch.int64)
         return view("node_ptr"), view("edge_ptr")
 
+    def _idx_tensor(self) -> torch.Tensor:
+        ds = self.ds
+        idx = getattr(ds, "_idx_t", None)
+        if idx is None:
+            idx = torch.from_numpy(np.array(ds.idx))
+            try:
+                ds._idx_t = idx
+            except AttributeError:
+                pass
+        return idx
+
+    def lazy_batch(self) -> "LazyPackedBatch":
+        """Every graph of the image, in order, unpacked only on demand (see ``LazyPackedBatch``)."""
+        return LazyPackedBatch(self)
+
     def _batch_all(self, with_batch_vector: bool) -> Batch:
         """``batch(None)``: every graph of the image, in order (a wire-format chunk).  The exclusive prefix sums
         hcg_unpack_batch needs ARE the image's node_ptr / edge_ptr sections, already on the device; sizes come
@@ -412,13 +427,7 @@ class DeviceGraphStore:
             _lib.check(_lib.load().hcg_unpack_batch(
                 C.byref(self.c_store), None, 0, B, node_ptr_d.data_ptr(), edge_ptr_d.data_ptr(), x.data_ptr(), ei.data_ptr(),
                 E_out, bvec.data_ptr() if bvec is not None else None, y.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
-        idx = getattr(ds, "_idx_t", None)
-        if idx is None:
-            idx = torch.from_numpy(np.array(ds.idx))
-            try:
-                ds._idx_t = idx
-            except AttributeError:
-                pass
+        idx = self._idx_tensor()
         out = Batch(x, ei, bvec, node_ptr_d, y, idx, B, edges_grouped=True if (ds.flags & FLAG_GROUPABLE) else None)
         out.max_graph_nodes = int(ds.max_graph_nodes)
         out.max_graph_edges = int(ds.max_graph_edges)
@@ -426,6 +435,50 @@ class DeviceGraphStore:
         out.edge_ptr = edge_ptr_d
         out._keepalive = self.blob_dev
         return out
+
+
+class LazyPackedBatch(Batch):
+    """Every graph of a device-resident packed image as a batch whose ``x`` / ``edge_index`` / ``y`` are only unpacked
+    (``hcg_unpack_batch``) if somebody reads them: inference through ``GCN.forward`` runs straight from the image
+    (``hcg_gcn_forward_packed``) and never does."""
+
+    def __init__(self, store: "DeviceGraphStore"):
+        ds = store.ds
+        self._packed_store, self._real = store, None
+        self.ptr, self.edge_ptr = store._ptr_views()
+        self._batch = None
+        self.num_graphs = int(ds.G)
+        self.idx = store._idx_tensor()
+        self.edges_grouped = True if (ds.flags & FLAG_GROUPABLE) else None
+        self.max_graph_nodes, self.max_graph_edges = int(ds.max_graph_nodes), int(ds.max_graph_edges)
+        self.max_in_degree = ds.max_in_degree
+        self._keepalive = store.blob_dev
+
+    def _materialise(self) -> Batch:
+        if self._real is None:
+            self._real = self._packed_store._batch_all(False)
+        return self._real
+
+    x = property(lambda self: self._materialise().x)
+    edge_index = property(lambda self: self._materialise().edge_index)
+    y = property(lambda self: self._materialise().y)
+
+    @property
+    def num_nodes(self) -> int:
+        return int(self._packed_store.ds.N)
+
+    def to(self, device, non_blocking: bool = False):
+        dev = torch.device(device)
+        if dev.type == "cuda" and (dev.index is None or dev.index == self.ptr.device.index):
+            return self
+        return self._materialise().to(device, non_blocking=non_blocking)
+
+    def pin_memory(self):
+        return self
+
+    def __repr__(self):
+        ds = self._packed_store.ds
+        return f"LazyPackedBatch(num_graphs={ds.G}, nodes={ds.N}, edges={ds.E}, unpacked={self._real is not None})"
 
 
 class StoreLoader:

@@ -19,21 +19,33 @@ from .data import Batch
 from .packed import DeviceGraphStore, PackedDataset
 
 
+_COPY_STREAMS: dict = {}
+
+
 class DevicePrefetcher:
     """Iterates an iterable of host ``Batch`` objects as device batches, ``depth`` copies ahead.
-    An item may also be a ``PackedDataset`` chunk (packed wire format, ~4x fewer bytes per graph): its image
-    crosses PCIe as ONE copy and is expanded on the device by ``hcg_unpack_batch``.
+    An item may also be a ``PackedDataset`` chunk (packed wire format, ~11x fewer bytes per graph): its image
+    crosses PCIe as ONE copy and is expanded on the device by ``hcg_unpack_batch`` - or, with ``lazy_packed``, consumed
+    as it is by ``hcg_gcn_forward_packed``.
 
     Copies are issued on a private stream (pinned host memory makes them truly asynchronous);
     the consumer's current stream is made to wait on each batch's copy event when it is handed
     out, and the device tensors are marked as used by that stream for the caching allocator.
     """
 
-    def __init__(self, batches: Iterable[Batch], device=None, depth: int = 2):
+    def __init__(self, batches: Iterable[Batch], device=None, depth: int = 2, lazy_packed: bool = False):
         self.device = torch.device(device) if device is not None else ops._require_cuda()
+        # lazy_packed: a PackedDataset chunk is handed out as a LazyPackedBatch (unpacked only when x / edge_index are
+        # read): what inference wants; training reads x and y anyway
+        self.lazy_packed = bool(lazy_packed)
         self.batches = iter(batches)
         self.depth = max(1, int(depth))
-        self.copy_stream = torch.cuda.Stream(self.device)
+        # ONE copy stream per device for the whole process: torch's caching allocator keeps a pool per stream, so a new
+        # stream per prefetcher would strand the previous one's staging buffers and cudaMalloc its own again
+        key = (self.device.type, self.device.index if self.device.index is not None else torch.cuda.current_device())
+        if key not in _COPY_STREAMS:
+            _COPY_STREAMS[key] = torch.cuda.Stream(self.device)
+        self.copy_stream = _COPY_STREAMS[key]
         self.queue: deque = deque()
 
     def _stage_one(self) -> bool:
@@ -48,7 +60,8 @@ class DevicePrefetcher:
                 blob_d = ops.bucketed_empty((blob_h.numel(),), torch.uint8, self.device)
                 blob_d.copy_(blob_h, non_blocking=True)
                 store = DeviceGraphStore.from_blob(h, blob_d)
-                d = store.batch(None, with_batch_vector=False)    # (Batch.batch rebuilds it from ptr if anybody asks)
+                # unpacked only if somebody reads x / edge_index: inference runs straight from the image
+                d = store.lazy_batch() if self.lazy_packed else store.batch(None, with_batch_vector=False)
                 d._store = store
                 ev = torch.cuda.Event()
                 ev.record(self.copy_stream)
@@ -89,8 +102,10 @@ class DevicePrefetcher:
             cur = torch.cuda.current_stream(self.device)
             cur.wait_event(ev)
             store = getattr(d, "_store", None)
-            for t in (d.x, d.edge_index, d._batch, d.ptr, d.y, getattr(d, "edge_ptr", None), getattr(d, "_keepalive", None),
-                      store.blob_dev if store is not None else None):
+            lazy = getattr(d, "_packed_store", None) is not None
+            for t in ((None, None, None) if lazy else (d.x, d.edge_index, d.y)) + \
+                    (d._batch, d.ptr, getattr(d, "edge_ptr", None), getattr(d, "_keepalive", None),
+                     store.blob_dev if store is not None else None):
                 if t is not None and t.is_cuda:
                     t.record_stream(cur)
             self._stage_one()  # refill behind the batch being handed out
@@ -113,7 +128,7 @@ def predict_stream(model, batches: Iterable[Batch], return_embedding: bool = Fal
     pending: deque = deque()
     try:
         with torch.no_grad():
-            for d in DevicePrefetcher(batches, device=device, depth=depth):
+            for d in DevicePrefetcher(batches, device=device, depth=depth, lazy_packed=True):
                 out, emb = model(d, True)
                 o_h = torch.empty(out.shape, dtype=out.dtype, pin_memory=True)
                 o_h.copy_(out, non_blocking=True)

@@ -268,6 +268,21 @@ int hcg_unpack_batch(const HcgPackedStore* store, const int64_t* graph_ids, int6
                      const int64_t* out_ptr, const int64_t* out_eptr, float* x, int64_t* edge_index, int64_t E_out,
                      int64_t* batch, float* y, void* stream);
 
+/*
+ * Inference straight from the packed image: graphs [first, first + B) of `store`, in order, through the edge-list
+ * forward without hcg_unpack_batch - the conv kernel stages each graph's bit / byte / f32 feature slices and its local
+ * byte edge pairs (a few bytes per node instead of 4 F + 16 per edge) and expands them in shared memory, so x and
+ * edge_index never exist in HBM.  Same bits as hcg_unpack_batch + hcg_gcn_forward_coo.  Workspace:
+ * hcg_forward_coo_workspace_bytes(B, p); refusal flags (HCG_COO_*): hcg_forward_coo_status on the same `ws`.
+ * hcg_forward_packed_supported: 1 when the network (as hcg_forward_coo_supported) and the image (byte edge endpoints,
+ * F == p->F <= 32, at most ~50 packed bytes per node) can take this path; otherwise unpack first.
+ * Replaces, for a resident or streamed screening set: DataLoader collate (call_methods.py:41-46) + model(batch)
+ * (utils/utils_model.py:83-96).
+ */
+int hcg_forward_packed_supported(const HcgPackedStore* store, const HcgParams* p);
+int hcg_gcn_forward_packed(const HcgPackedStore* store, int64_t first, int64_t B, float fill, const HcgParams* p,
+                           float* out, float* emb, void* ws, size_t ws_bytes, void* stream);
+
 /* Synchronises `stream`, reads the status word of the last hcg_collate that used `ws`.  Returns
  * HCG_ERR_BAD_INDEX / HCG_ERR_BAD_BATCH for unusable input; `graph_flags` (may be NULL) receives
  * the HCG_GRAPH_* bits to put into HcgGraph.flags. */

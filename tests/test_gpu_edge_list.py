@@ -2,6 +2,7 @@
 normalised neighbour lists itself) against hcg_collate + hcg_gcn_forward on the same batch: identical bits, and against
 the CPU oracle.  Reference call replaced: `model(batch)` under no_grad, utils/utils_model.py:83-96 -> model/gcn.py:52-76."""
 import numpy as np
+import numpy as np
 import pytest
 import torch
 
@@ -145,3 +146,63 @@ def test_module_takes_the_edge_list_path_for_inference_only(pkg):
     out2 = model(b)
     assert hasattr(b, "_hcg_plan")
     assert torch.equal(out, out2.detach())
+
+
+# ---- hcg_gcn_forward_packed: the same forward straight from a device-resident packed image (no unpack) ----------------
+def _packed_pair(pkg, ds, first, count, F, seed=5):
+    from hcatgnet_b200 import ops
+    torch.manual_seed(seed)
+    model = pkg.make_network("GCN", pkg.default_options(), F).cuda().eval()
+    params = [p.detach() for p in model._flat_params()]
+    store = pkg.DeviceGraphStore(ds, "cuda")
+    got = ops.forward_packed(store.c_store, first, count, model._dims(), params, torch.device("cuda", 0), validate=True)
+    b = store.batch(np.arange(first, first + count))
+    want = ops.forward_edge_list(b.x, b.edge_index, b.ptr, b.edge_ptr, model._dims(), params, validate=True)
+    return got, want, model, store
+
+
+@pytest.mark.parametrize("n_graphs,F,style", [(1, 25, "featuriser"), (700, 25, "featuriser"), (3001, 25, "uniform"), (257, 32, "mixed"),
+                                              (64, 9, "mixed")])
+def test_packed_forward_equals_unpack_plus_edge_list_forward(pkg, n_graphs, F, style):
+    from hcatgnet_b200.synth import synth_batch
+    b = synth_batch(n_graphs, F, seed=900 + n_graphs, features="featuriser" if style == "featuriser" else "uniform")
+    x = b.x.clone()
+    if style == "mixed":                      # bit, byte and f32 columns interleaved
+        x[:, 0::3] = (x[:, 0::3] < 0.4).float()
+        x[:, 1::3] = torch.floor(x[:, 1::3] * 7)
+    ds = pkg.PackedDataset.from_arrays(x.numpy(), b.edge_index.numpy(), b.ptr.numpy(), b.y.numpy())
+    if style == "mixed":
+        assert ds.Fb > 0 and ds.Fu > 0 and ds.Ff > 0
+    if style == "uniform" and F == 25:        # 25 f32 columns = 100 packed bytes per node: above the kernel's stage
+        got, want, _, _ = _packed_pair(pkg, ds, 0, n_graphs, F)
+        assert got is None and want is not None
+        return
+    for first, count in ((0, n_graphs), (n_graphs // 3, n_graphs - n_graphs // 3)):
+        got, want, _, _ = _packed_pair(pkg, ds, first, count, F)
+        assert got is not None and want is not None
+        assert torch.equal(got[1], want[1]) and torch.equal(got[0], want[0])
+
+
+def test_predict_stream_runs_packed_chunks_without_unpacking(pkg):
+    from hcatgnet_b200 import _lib
+    from hcatgnet_b200.synth import synth_batch
+    chunks, hosts = [], []
+    for k in range(3):
+        b = synth_batch(400 + 37 * k, 25, seed=70 + k, features="featuriser")
+        chunks.append(pkg.PackedDataset.from_arrays(b.x.numpy(), b.edge_index.numpy(), b.ptr.numpy(), b.y.numpy(), pinned=True))
+        hosts.append(b)
+    torch.manual_seed(3)
+    model = pkg.make_network("GCN", pkg.default_options(), 25).cuda().eval()
+    want = [(o.clone(), e.clone()) for o, e, _ in pkg.predict_stream(model, hosts, return_embedding=True)]
+    n0 = _lib.launch_count()
+    got = [(o.clone(), e.clone()) for o, e, _ in pkg.predict_stream(model, chunks, return_embedding=True)]
+    assert _lib.launch_count() - n0 == 3 * len(chunks)          # k_tile_desc, k_tc_fwd_packed, k_readout2: no k_unpack_batch
+    for (o, e), (ow, ew) in zip(got, want):
+        assert torch.equal(o, ow) and torch.equal(e, ew)
+    # the lazy batch unpacks itself when somebody reads it (training, or a model that takes another path)
+    store = pkg.DeviceGraphStore(chunks[0], "cuda")
+    lazy = store.lazy_batch()
+    assert lazy._real is None and lazy.num_graphs == 400
+    assert torch.equal(lazy.x.cpu(), hosts[0].x) and torch.equal(lazy.edge_index.cpu(), hosts[0].edge_index)
+    out = model(lazy)                                            # grad mode: the collate path, on the unpacked tensors
+    assert torch.allclose(out.detach().cpu(), want[0][0], rtol=1e-5, atol=1e-6)
