@@ -407,7 +407,8 @@ __device__ unsigned long long g_tc_timing[16];
 template <int F_, int NS, int MODE = 0>
 __global__ void __launch_bounds__(NS * 256, 1)
 k_tc_fwd(const TcArgs a) {
-  constexpr bool COO = MODE != 0, PK = MODE == 2;
+  constexpr bool COO = MODE == 1 || MODE == 2, PK = MODE == 2;
+  constexpr bool SAVE = MODE == 3;   // MODE 3: the CSR variant of the training forward (every layer's rows are saved)
 #ifdef HCG_TC_TIMING
   long long t_prev = clock64();
 #endif
@@ -911,7 +912,7 @@ k_tc_fwd(const TcArgs a) {
       if (ctl_warp) ptx::mbar_wait(&bar_mma[slot], mma_phase);      // one warp polls; the others sleep in the barrier below
       mma_phase ^= 1u;
       TC_TICK(5);
-      if (cg == 0) ptx::bulk_wait_read();   // (training forward) the saved rows have left the activation buffer
+      if (SAVE && cg == 0) ptx::bulk_wait_read();   // (training forward) the saved rows have left the activation buffer
       ptx::named_bar_sync(bar_full, kSlotThreads);
       ptx::tc_fence_after_sync();
       if (l == 0 && pf_warp) issue(k + 1, true);   // every layer-0 gather of the slot is over: the x stage is free
@@ -939,7 +940,7 @@ k_tc_fwd(const TcArgs a) {
         }
       }
       TC_TICK(7);
-      const bool saving = a.f.save_act[l] != nullptr;
+      const bool saving = SAVE && a.f.save_act[l] != nullptr;
       if (saving) ptx::fence_proxy_async_smem();   // the rows are read by the bulk copies below (async proxy)
       ptx::tc_fence_before_sync();
       ptx::named_bar_sync(bar_full, kSlotThreads);  // h complete in shared memory; D may be overwritten
@@ -1002,7 +1003,7 @@ k_tc_fwd(const TcArgs a) {
     TC_TICK(10);
   }
   if (p_gA >= 0) pool_tile(p_gA, p_gB, p_nA, p_nB);
-  ptx::bulk_wait_all();
+  if (SAVE) ptx::bulk_wait_all();
 
   ptx::tc_fence_before_sync();
   __syncthreads();
@@ -1114,10 +1115,18 @@ int launch_tc_fwd(const FusedFwdArgs& f, int64_t N, int64_t E, void* ws, cudaStr
   a.counts = w.counts;
   a.cap = p.cap;
   a.N = N; a.E = E;
+  bool save = false;    // training forward: MODE 3 (the inference instantiations carry no trace of the row saving)
+  for (int l = 0; l < f.L; ++l) save |= f.save_act[l] != nullptr;
   int rc;
-  if (ns == 2)
+  if (ns == 2 && save)
+    rc = f.F == 25 ? launch_tc_variant<25, 2, 3>(a, p.grid, smem, st) : f.F == 32 ? launch_tc_variant<32, 2, 3>(a, p.grid, smem, st)
+                                                                                  : launch_tc_variant<0, 2, 3>(a, p.grid, smem, st);
+  else if (ns == 2)
     rc = f.F == 25 ? launch_tc_variant<25, 2>(a, p.grid, smem, st) : f.F == 32 ? launch_tc_variant<32, 2>(a, p.grid, smem, st)
                                                                                : launch_tc_variant<0, 2>(a, p.grid, smem, st);
+  else if (save)
+    rc = f.F == 25 ? launch_tc_variant<25, 3, 3>(a, p.grid, smem, st) : f.F == 32 ? launch_tc_variant<32, 3, 3>(a, p.grid, smem, st)
+                                                                                  : launch_tc_variant<0, 3, 3>(a, p.grid, smem, st);
   else
     rc = f.F == 25 ? launch_tc_variant<25, 3>(a, p.grid, smem, st) : f.F == 32 ? launch_tc_variant<32, 3>(a, p.grid, smem, st)
                                                                                : launch_tc_variant<0, 3>(a, p.grid, smem, st);
