@@ -206,3 +206,28 @@ def test_predict_stream_runs_packed_chunks_without_unpacking(pkg):
     assert torch.equal(lazy.x.cpu(), hosts[0].x) and torch.equal(lazy.edge_index.cpu(), hosts[0].edge_index)
     out = model(lazy)                                            # grad mode: the collate path, on the unpacked tensors
     assert torch.allclose(out.detach().cpu(), want[0][0], rtol=1e-5, atol=1e-6)
+
+
+def test_packed_forward_on_edgeless_graphs_single_nodes_and_all_bit_columns(pkg):
+    """Graphs without edges, one-node graphs, shuffled edge order; an image whose columns are ALL bit columns (no byte, no
+    f32 section) and one with f32 columns only."""
+    g = torch.Generator().manual_seed(23)
+    for F, kind in ((12, "bits"), (9, "f32")):
+        graphs = []
+        for k in range(97):
+            n = 1 if k % 11 == 0 else int(torch.randint(2, 129, (1,), generator=g))
+            if k % 7 == 0 or n == 1:
+                ei = torch.zeros(2, 0, dtype=torch.int64)
+            else:
+                src = torch.randint(0, n, (3 * n,), generator=g)
+                dst = (src + 1 + torch.randint(0, n - 1, (3 * n,), generator=g)) % n        # never a self-loop
+                key = torch.unique(dst * n + src)[:500]                                      # simple graph
+                ei = torch.stack([key % n, key // n])[:, torch.randperm(key.numel(), generator=g)]
+                ei = ei[:, torch.bincount(ei[1], minlength=n)[ei[1]] <= 16]                  # in-degree cap of the gather kernel
+            x = (torch.rand(n, F, generator=g) < 0.3).float() if kind == "bits" else torch.randn(n, F, generator=g)
+            graphs.append({"x": x, "edge_index": ei, "y": torch.zeros(1), "idx": k})
+        ds = pkg.PackedDataset.from_graphs(graphs)
+        assert (ds.Fb, ds.Fu, ds.Ff) == ((F, 0, 0) if kind == "bits" else (0, 0, F))
+        got, want, _, _ = _packed_pair(pkg, ds, 0, len(graphs), F)
+        assert got is not None and want is not None
+        assert torch.equal(got[1], want[1]) and torch.equal(got[0], want[0])
