@@ -1,7 +1,5 @@
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-timeout 600 python bench.py --mode train --batch 4096 --steps 30 --warmup 5 --no-cpu-baseline 2>&1 | tail -1 > gpurun_out/train.json
-python - <<'PY'
-import json
-r=json.loads(open("gpurun_out/train.json").read())
-print(r["value"], r["ms_per_step"], {n:round(v["ms_per_launch"]*1e3,1) for n,v in r["kernels"].items()})
-PY
+export PYTHONPATH=.
+HCG_LIB_PATH=build/libhcg_prev.so python profiles/experiments/coo_ab.py 2>&1 | tail -1
+python profiles/experiments/coo_ab.py 2>&1 | tail -1
+HCG_LIB_PATH=build/libhcg_prev.so python profiles/experiments/coo_ab.py 2>&1 | tail -1
+python profiles/experiments/coo_ab.py 2>&1 | tail -1
