@@ -434,6 +434,7 @@ def measure(cx: Ctx, mode: str, batch: int, hidden: int, convs: int, steps: int,
         # a fresh batch object every step: the collate runs inside the step (no topology cache hit)
         fresh = pkg.Batch(b.x, b.edge_index, b.batch, b.ptr, b.y, None, b.num_graphs, edges_grouped=True)
         fresh.max_graph_nodes, fresh.max_graph_edges, fresh.edge_ptr = b.max_graph_nodes, b.max_graph_edges, b.edge_ptr
+        fresh.max_in_degree = b.max_in_degree
         return trainer.step(fresh)
 
     def drain_losses(stream_of_losses):

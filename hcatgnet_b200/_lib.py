@@ -126,7 +126,7 @@ SIGNATURES = {
                                          _fp, _fp, _fp, C.c_size_t, _fp]),
     "hcg_rmse_seed": (C.c_int, [_fp, _fp, C.c_int64, C.c_int, _fp, _fp, _fp]),
     "hcg_train_step_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.POINTER(HcgParams)]),
-    "hcg_train_step": (C.c_int, [_fp, _fp, C.c_int64, _fp, _fp, _fp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_float,
+    "hcg_train_step": (C.c_int, [_fp, _fp, C.c_int64, _fp, _fp, _fp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_float,
                                  C.POINTER(HcgParams), C.POINTER(HcgGrads), _fp, _fp, _fp, _fp, C.c_int64,
                                  C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64, _fp, _fp, C.c_size_t, _fp]),
     "hcg_adam_step": (C.c_int, [_fp, _fp, _fp, _fp, C.c_int64, _fp, C.c_double, C.c_double, C.c_double, C.c_double,

@@ -62,6 +62,15 @@ int launch_tc_fwd_coo(const FusedFwdArgs& a, const int64_t* edge_index, const in
                       int64_t E, void* ws, cudaStream_t st);
 int tc_fwd_coo_flags(const void* ws, int64_t B, cudaStream_t st, int* flags);
 
+// hcg_gcn_forward_coo with the activations saved for the backward pass (hcg_net.cu; used by hcg_train_step)
+int gcn_forward_coo_saved(const float* x, const int64_t* edge_index, const int64_t* node_ptr, const int64_t* edge_ptr, int64_t N,
+                          int64_t E, int64_t B, float fill, const HcgParams* p, float* out, float* emb, const HcgSaved* saved,
+                          void* ws, size_t ws_bytes, void* stream);
+
+// the next hcg_gcn_backward of the calling thread makes its stream wait for `ev` after the readout part, before the
+// first kernel that reads the graph arrays (rowptr / col / dis / transposed CSR)
+void set_backward_prereq(cudaEvent_t ev);
+
 // packed-image variant: graphs [first, first + a.B) of a packed image resident in device memory (a.x is not used);
 // same workspace and flags as the COO variant.  tc_fwd_packed_fits: the image's per-node bytes fit the kernel's stage.
 bool tc_fwd_packed_fits(const HcgPackedStore& pk);

@@ -1339,6 +1339,13 @@ extern "C" size_t hcg_forward_coo_workspace_bytes(int64_t B, const HcgParams* p)
 extern "C" int hcg_gcn_forward_coo(const float* x, const int64_t* edge_index, const int64_t* node_ptr, const int64_t* edge_ptr,
                                    int64_t N, int64_t E, int64_t B, float fill, const HcgParams* p, float* out, float* emb,
                                    void* ws, size_t ws_bytes, void* stream) {
+  return gcn_forward_coo_saved(x, edge_index, node_ptr, edge_ptr, N, E, B, fill, p, out, emb, nullptr, ws, ws_bytes, stream);
+}
+
+// the same with the activations saved for hcg_gcn_backward (the training step's forward: hcg_train.cu)
+int hcg::gcn_forward_coo_saved(const float* x, const int64_t* edge_index, const int64_t* node_ptr, const int64_t* edge_ptr, int64_t N,
+                               int64_t E, int64_t B, float fill, const HcgParams* p, float* out, float* emb, const HcgSaved* saved,
+                               void* ws, size_t ws_bytes, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = check_params(p);
   if (rc) return rc;
@@ -1354,12 +1361,16 @@ extern "C" int hcg_gcn_forward_coo(const float* x, const int64_t* edge_index, co
   note_region(st);
   FusedFwdArgs a{};
   a.x = x;
-  for (int l = 0; l < p->L; ++l) { a.conv_w[l] = p->conv_w[l]; a.conv_b[l] = p->conv_b[l]; }
+  for (int l = 0; l < p->L; ++l) {
+    a.conv_w[l] = p->conv_w[l]; a.conv_b[l] = p->conv_b[l];
+    a.save_act[l] = saved ? saved->acts[l] : nullptr;
+    if (saved) HCG_REQUIRE(saved->acts[l] != nullptr, HCG_ERR_INVALID_ARG, "saved->acts[%d] is NULL", l);
+  }
   a.emb = emb;
   a.B = B; a.F = p->F; a.Fp = (p->F + 3) / 4 * 4; a.L = p->L; a.slope = p->slope; a.fill = fill;
   rc = launch_tc_fwd_coo(a, edge_index, node_ptr, edge_ptr, N, E, w.tc, st);
   if (rc) return rc;
-  return run_readout(p, emb, out, nullptr, w.hid, B, st);
+  return run_readout(p, emb, out, saved, w.hid, B, st);
 }
 
 extern "C" int hcg_forward_coo_status(const void* ws, int64_t B, void* stream, int32_t* flags) {
@@ -1511,6 +1522,10 @@ extern "C" int hcg_gcn_forward_coo_static(const float* x, const int64_t* edge_in
   return hcg_forward_coo_status(scratch, B, stream, flags);
 }
 
+// event the NEXT hcg_gcn_backward of this thread waits for before it reads the graph arrays (set by hcg_train_step)
+static thread_local cudaEvent_t g_backward_prereq = nullptr;
+void hcg::set_backward_prereq(cudaEvent_t ev) { g_backward_prereq = ev; }
+
 extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgParams* p, const HcgSaved* saved,
                                 const float* emb, const float* g_out, const float* g_emb,
                                 const HcgGrads* grads, float* g_x, void* ws, size_t ws_bytes, void* stream) {
@@ -1584,6 +1599,11 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
     }
   }
 
+  // (hcg_train_step builds the transposed CSR on a second stream while the readout part above runs: join it here)
+  if (g_backward_prereq != nullptr) {
+    HCG_CUDA_OK(cudaStreamWaitEvent(st, g_backward_prereq, 0));
+    g_backward_prereq = nullptr;
+  }
   // ---- graph-resident path: pooling backward + both conv layers in one kernel ----------------
   {
     const int bpath = config_get(HCG_CFG_BACKWARD_PATH);

@@ -407,8 +407,8 @@ __device__ unsigned long long g_tc_timing[16];
 template <int F_, int NS, int MODE = 0>
 __global__ void __launch_bounds__(NS * 256, 1)
 k_tc_fwd(const TcArgs a) {
-  constexpr bool COO = MODE == 1 || MODE == 2, PK = MODE == 2;
-  constexpr bool SAVE = MODE == 3;   // MODE 3: the CSR variant of the training forward (every layer's rows are saved)
+  constexpr bool COO = MODE == 1 || MODE == 2 || MODE == 4, PK = MODE == 2;
+  constexpr bool SAVE = MODE == 3 || MODE == 4;   // the training forward (every layer's rows are saved): 3 from the CSR, 4 from the edge list
 #ifdef HCG_TC_TIMING
   long long t_prev = clock64();
 #endif
@@ -1183,9 +1183,14 @@ int launch_tc_fwd_coo(const FusedFwdArgs& f, const int64_t* edge_index, const in
   a.N = N; a.E = E;
   a.ei = edge_index;
   a.kflags = w.kflags;
-  const int rc = f.F == 25 ? launch_tc_variant<25, 2, 1>(a, p.grid, smem, st)
-               : f.F == 32 ? launch_tc_variant<32, 2, 1>(a, p.grid, smem, st)
-                           : launch_tc_variant<0, 2, 1>(a, p.grid, smem, st);
+  bool save = false;
+  for (int l = 0; l < f.L; ++l) save |= f.save_act[l] != nullptr;
+  const int rc = save ? (f.F == 25 ? launch_tc_variant<25, 2, 4>(a, p.grid, smem, st)
+                       : f.F == 32 ? launch_tc_variant<32, 2, 4>(a, p.grid, smem, st)
+                                   : launch_tc_variant<0, 2, 4>(a, p.grid, smem, st))
+                      : (f.F == 25 ? launch_tc_variant<25, 2, 1>(a, p.grid, smem, st)
+                       : f.F == 32 ? launch_tc_variant<32, 2, 1>(a, p.grid, smem, st)
+                                   : launch_tc_variant<0, 2, 1>(a, p.grid, smem, st));
   if (rc) return rc;
   HCG_LAUNCH_OK(st, "k_tc_fwd_coo");
   return HCG_OK;

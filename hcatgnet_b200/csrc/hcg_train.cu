@@ -10,7 +10,10 @@
 // 2 (out - y), the flat gradient travels with the tail through ONE all-reduce, and the rescale happens
 // inside the optimizer kernel.  With one rank the same code gives the reference's single-device step.
 // Also here: the fused backward of the default two-layer readout head.
+#include <mutex>
+
 #include "hcg_common.cuh"
+#include "hcg_fused.cuh"
 
 namespace hcg {
 
@@ -116,7 +119,8 @@ struct StepWs {
   float* hid[HCG_MAX_READOUT];
   float *out, *emb, *g_out;
   char* bwd;
-  size_t collate_bytes, fwd_bytes, bwd_bytes, bytes;
+  char* coo;
+  size_t collate_bytes, fwd_bytes, bwd_bytes, coo_bytes, bytes;
 };
 
 static StepWs carve_step(void* ws, int64_t N, int64_t E, int64_t B, const HcgParams* p) {
@@ -138,8 +142,33 @@ static StepWs carve_step(void* ws, int64_t N, int64_t E, int64_t B, const HcgPar
   w.emb = c.take<float>((size_t)B * 2 * p->H + 4);
   w.g_out = c.take<float>((size_t)B * p->C + 4);
   w.bwd = c.take<char>(w.bwd_bytes);
+  w.coo_bytes = hcg_forward_coo_workspace_bytes(B, p);
+  w.coo = c.take<char>(w.coo_bytes);
   w.bytes = c.off;
   return w;
+}
+
+// A second stream (and two events) per device for the part of the step that the forward does not depend on.
+struct SideStream {
+  cudaStream_t st = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+};
+static int side_stream(SideStream** out) {
+  constexpr int kMaxDevices = 64;
+  static SideStream side[kMaxDevices];
+  static std::mutex mu;
+  int dev = 0;
+  HCG_CUDA_OK(cudaGetDevice(&dev));
+  HCG_REQUIRE(dev >= 0 && dev < kMaxDevices, HCG_ERR_UNSUPPORTED, "device ordinal %d outside [0, %d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(mu);
+  SideStream& s = side[dev];
+  if (s.st == nullptr) {
+    HCG_CUDA_OK(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+    HCG_CUDA_OK(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
+    HCG_CUDA_OK(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
+  }
+  *out = &s;
+  return HCG_OK;
 }
 
 }  // namespace hcg
@@ -151,7 +180,7 @@ extern "C" size_t hcg_train_step_workspace_bytes(int64_t N, int64_t E, int64_t B
 
 extern "C" int hcg_train_step(const float* x, const int64_t* edge_index, int64_t E, const int64_t* node_ptr,
                               const int64_t* edge_ptr, const float* y, int64_t N, int64_t B, int32_t max_graph_nodes,
-                              int32_t max_graph_edges, float fill, const HcgParams* p, const HcgGrads* grads,
+                              int32_t max_graph_edges, int32_t max_in_degree, float fill, const HcgParams* p, const HcgGrads* grads,
                               float* param_slab, float* grad_slab, float* exp_avg, float* exp_avg_sq, int64_t n,
                               double lr, double beta1, double beta2, double eps, int64_t step, float* loss_out,
                               void* ws, size_t ws_bytes, void* stream) {
@@ -161,10 +190,12 @@ extern "C" int hcg_train_step(const float* x, const int64_t* edge_index, int64_t
   HCG_REQUIRE(p->L >= 1 && p->L <= HCG_MAX_CONV && p->R >= 1 && p->R <= HCG_MAX_READOUT, HCG_ERR_UNSUPPORTED, "bad layer counts");
   StepWs w = carve_step(ws, N, E, B, p);
   HCG_REQUIRE(ws_bytes >= w.bytes, HCG_ERR_WORKSPACE, "train-step workspace too small: %zu < %zu", ws_bytes, w.bytes);
-  int rc = hcg_collate_offsets(edge_index, E, node_ptr, edge_ptr, N, B, fill, HCG_COLLATE_TRANSPOSE, max_graph_nodes,
-                               max_graph_edges, w.rowptr, w.col, w.eid, w.dis, w.graph_ptr, w.t_rowptr, w.t_col, w.t_eid,
-                               w.collate, w.collate_bytes, stream);
-  if (rc) return rc;
+  // When the caller's (host-verified) size facts allow the edge-list forward, the forward does not need the collate:
+  // the collate (whose transposed CSR only the backward reads) leaves the critical path (see below).
+  const bool coo_fwd = hcg_forward_coo_supported(p) && max_graph_nodes > 0 && max_graph_nodes <= 128 && max_graph_edges >= 0 &&
+                       max_graph_edges <= 512 && max_in_degree >= 0 && max_in_degree <= 16 &&
+                       hcg_config_get(HCG_CFG_FORWARD_PATH) == 0;
+  cudaStream_t main_st = static_cast<cudaStream_t>(stream);
   HcgGraph g{};
   g.N = N; g.E = E; g.B = B;
   g.rowptr = w.rowptr; g.col = w.col; g.eid = w.eid; g.dis = w.dis; g.graph_ptr = w.graph_ptr;
@@ -173,12 +204,42 @@ extern "C" int hcg_train_step(const float* x, const int64_t* edge_index, int64_t
   HcgSaved saved{};
   for (int l = 0; l < p->L; ++l) saved.acts[l] = w.acts[l];
   for (int k = 0; k < p->R - 1; ++k) saved.hid[k] = w.hid[k];
-  rc = hcg_gcn_forward(&g, x, p, w.out, w.emb, &saved, w.fwd, w.fwd_bytes, stream);
-  if (rc) return rc;
+  int rc;
+  if (coo_fwd) {
+    // forward first, on the caller's stream; then the collate on the second stream, beside the loss seed and the readout
+    // part of the backward (small kernels that leave most of the GPU idle); hcg_gcn_backward joins it before its conv part
+    SideStream* side = nullptr;
+    if (int rc0 = side_stream(&side)) return rc0;
+    rc = gcn_forward_coo_saved(x, edge_index, node_ptr, edge_ptr, N, E, B, fill, p, w.out, w.emb, &saved, w.coo, w.coo_bytes, stream);
+    if (rc) return rc;
+    HCG_CUDA_OK(cudaEventRecord(side->fork, main_st));     // (orders the side stream behind the previous step's backward, too)
+    HCG_CUDA_OK(cudaStreamWaitEvent(side->st, side->fork, 0));
+    rc = hcg_collate_offsets(edge_index, E, node_ptr, edge_ptr, N, B, fill, HCG_COLLATE_TRANSPOSE, max_graph_nodes, max_graph_edges,
+                             w.rowptr, w.col, w.eid, w.dis, w.graph_ptr, w.t_rowptr, w.t_col, w.t_eid, w.collate, w.collate_bytes,
+                             side->st);
+    HCG_CUDA_OK(cudaEventRecord(side->join, side->st));
+    if (rc) {
+      cudaStreamWaitEvent(main_st, side->join, 0);          // nothing of this call may outlive it out of stream order
+      return rc;
+    }
+    set_backward_prereq(side->join);
+  } else {
+    rc = hcg_collate_offsets(edge_index, E, node_ptr, edge_ptr, N, B, fill, HCG_COLLATE_TRANSPOSE, max_graph_nodes, max_graph_edges,
+                             w.rowptr, w.col, w.eid, w.dis, w.graph_ptr, w.t_rowptr, w.t_col, w.t_eid, w.collate, w.collate_bytes, stream);
+    if (rc) return rc;
+    rc = hcg_gcn_forward(&g, x, p, w.out, w.emb, &saved, w.fwd, w.fwd_bytes, stream);
+    if (rc) return rc;
+  }
+  // (error paths below: drop the pending join and let both streams drain, so that nothing of this call is still
+  //  running out of stream order when it returns)
+  auto bail = [&](int code) {
+    if (coo_fwd) { set_backward_prereq(nullptr); cudaDeviceSynchronize(); }
+    return code;
+  };
   float* tail = grad_slab + n;
   rc = hcg_rmse_seed(w.out, y, B, p->C, w.g_out, tail, stream);
-  if (rc) return rc;
+  if (rc) return bail(rc);
   rc = hcg_gcn_backward(&g, x, p, &saved, w.emb, w.g_out, nullptr, grads, nullptr, w.bwd, w.bwd_bytes, stream);
-  if (rc) return rc;
+  if (rc) return bail(rc);
   return hcg_adam_step(param_slab, grad_slab, exp_avg, exp_avg_sq, n, tail, lr, beta1, beta2, eps, step, loss_out, stream);
 }

@@ -164,7 +164,8 @@ class FusedTrainer:
         with torch.cuda.device(dev):
             _lib.check(lib.hcg_train_step(
                 x.data_ptr(), ei.data_ptr(), E, ptr.data_ptr(), edge_ptr.data_ptr(), y.data_ptr(), N, B,
-                int(getattr(batch, "max_graph_nodes", 0) or 0), int(getattr(batch, "max_graph_edges", 0) or 0), 1.0,
+                int(getattr(batch, "max_graph_nodes", 0) or 0), int(getattr(batch, "max_graph_edges", 0) or 0),
+                -1 if getattr(batch, "max_in_degree", None) is None else int(batch.max_in_degree), 1.0,
                 C.byref(self._pstruct), C.byref(self._gstruct), self.flat.data_ptr(), self.grad.data_ptr(),
                 self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.n, float(pg["lr"]), float(b1), float(b2),
                 float(pg["eps"]), self.steps, loss.data_ptr(), self._ws.data_ptr(), self._ws.numel(),

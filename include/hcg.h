@@ -424,10 +424,15 @@ int hcg_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
  * caller-owned workspace (hcg_train_step_workspace_bytes).  For the reference's own regime (batches of 40 reactions)
  * the step is bound by the host's per-call cost, not by the kernels.  `p` / `grads` point into `param_slab` /
  * `grad_slab` (n floats + the [SSE, count] tail).  Single rank; preconditions of the graph-local collate apply.
+ * max_graph_nodes / max_graph_edges / max_in_degree: host-verified facts about the batch (0 / 0 / -1 = unknown).  When
+ * they show that the edge-list forward applies (<= 128 nodes and <= 512 edges per graph, in-degree <= 16), the forward
+ * runs straight from the edge list and the collate - whose transposed CSR only the backward reads - runs beside it on
+ * a second, library-owned stream that is joined into `stream` before the backward: same results, bit for bit.
  */
 size_t hcg_train_step_workspace_bytes(int64_t N, int64_t E, int64_t B, const HcgParams* p);
 int hcg_train_step(const float* x, const int64_t* edge_index, int64_t E, const int64_t* node_ptr, const int64_t* edge_ptr,
-                   const float* y, int64_t N, int64_t B, int32_t max_graph_nodes, int32_t max_graph_edges, float fill,
+                   const float* y, int64_t N, int64_t B, int32_t max_graph_nodes, int32_t max_graph_edges,
+                   int32_t max_in_degree, float fill,
                    const HcgParams* p, const HcgGrads* grads, float* param_slab, float* grad_slab, float* exp_avg,
                    float* exp_avg_sq, int64_t n, double lr, double beta1, double beta2, double eps, int64_t step,
                    float* loss_out, void* ws, size_t ws_bytes, void* stream);
