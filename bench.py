@@ -486,7 +486,8 @@ def measure(cx: Ctx, mode: str, batch: int, hidden: int, convs: int, steps: int,
             torch.cuda.synchronize()
             us = [e0.elapsed_time(e1) * 1e3 for e0, e1 in trainer.timing]
             trainer.timing = None
-            t = torch.tensor([float(np.mean(us))], device=dev)
+            # median: a rank that enters this pass late (rank 0 has just read the clocks) makes the others wait once
+            t = torch.tensor([float(np.median(us))], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             rec["allreduce_us"] = float(t.item())
             rec["allreduce_bytes"] = int(trainer.grad.numel() * 4)

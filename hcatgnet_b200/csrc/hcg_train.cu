@@ -184,8 +184,8 @@ extern "C" int hcg_train_step(const float* x, const int64_t* edge_index, int64_t
                               float* param_slab, float* grad_slab, float* exp_avg, float* exp_avg_sq, int64_t n,
                               double lr, double beta1, double beta2, double eps, int64_t step, float* loss_out,
                               void* ws, size_t ws_bytes, void* stream) {
-  HCG_REQUIRE(x && edge_index && node_ptr && edge_ptr && y && p && grads && param_slab && grad_slab && exp_avg && exp_avg_sq && ws,
-              HCG_ERR_INVALID_ARG, "NULL pointer");
+  HCG_REQUIRE(x && edge_index && node_ptr && edge_ptr && y && p && grads && grad_slab && ws, HCG_ERR_INVALID_ARG, "NULL pointer");
+  HCG_REQUIRE(step <= 0 || (param_slab && exp_avg && exp_avg_sq), HCG_ERR_INVALID_ARG, "NULL optimizer state");
   HCG_REQUIRE(N > 0 && E > 0 && B > 0 && n > 0, HCG_ERR_INVALID_ARG, "hcg_train_step needs N, E, B, n > 0");
   HCG_REQUIRE(p->L >= 1 && p->L <= HCG_MAX_CONV && p->R >= 1 && p->R <= HCG_MAX_READOUT, HCG_ERR_UNSUPPORTED, "bad layer counts");
   StepWs w = carve_step(ws, N, E, B, p);
@@ -241,5 +241,6 @@ extern "C" int hcg_train_step(const float* x, const int64_t* edge_index, int64_t
   if (rc) return bail(rc);
   rc = hcg_gcn_backward(&g, x, p, &saved, w.emb, w.g_out, nullptr, grads, nullptr, w.bwd, w.bwd_bytes, stream);
   if (rc) return bail(rc);
+  if (step <= 0) return HCG_OK;   // gradients only: data-parallel ranks all-reduce grad_slab, then call hcg_adam_step
   return hcg_adam_step(param_slab, grad_slab, exp_avg, exp_avg_sq, n, tail, lr, beta1, beta2, eps, step, loss_out, stream);
 }

@@ -133,8 +133,9 @@ class FusedTrainer:
                                          float(b2), float(pg["eps"]), self.steps, loss.data_ptr(), st))
         return loss
 
-    def _step_one_call(self, batch, x, y, ptr, edge_ptr) -> torch.Tensor:
-        """``hcg_train_step``: the whole step in one library call over a persistent workspace (single rank)."""
+    def _step_one_call(self, batch, x, y, ptr, edge_ptr, adam: bool = True):
+        """``hcg_train_step``: the whole step in one library call over a persistent workspace; ``adam=False`` stops
+        after the backward (data-parallel ranks: ``reduce()`` and ``apply()`` follow)."""
         lib = _lib.load()
         dev = self.device
         ei = batch.edge_index
@@ -159,7 +160,8 @@ class FusedTrainer:
             self._ws = torch.empty(int(need * 1.25) + 256, dtype=torch.uint8, device=dev)
         pg = self.model.optimizer.param_groups[0]
         b1, b2 = pg["betas"]
-        self.steps += 1
+        if adam:
+            self.steps += 1
         loss = self.losses[self.steps % 16]
         with torch.cuda.device(dev):
             _lib.check(lib.hcg_train_step(
@@ -168,13 +170,13 @@ class FusedTrainer:
                 -1 if getattr(batch, "max_in_degree", None) is None else int(batch.max_in_degree), 1.0,
                 C.byref(self._pstruct), C.byref(self._gstruct), self.flat.data_ptr(), self.grad.data_ptr(),
                 self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.n, float(pg["lr"]), float(b1), float(b2),
-                float(pg["eps"]), self.steps, loss.data_ptr(), self._ws.data_ptr(), self._ws.numel(),
+                float(pg["eps"]), self.steps if adam else 0, loss.data_ptr(), self._ws.data_ptr(), self._ws.numel(),
                 torch.cuda.current_stream(dev).cuda_stream))
-        return loss
+        return loss if adam else None
 
     def step(self, batch) -> torch.Tensor:
         """One optimisation step on ``batch`` (a device ``Batch``); returns the global RMSE (device scalar)."""
-        if self.world == 1 and not self.validate and getattr(batch, "edges_grouped", None) is True:
+        if not self.validate and getattr(batch, "edges_grouped", None) is True:
             ptr, eptr, x, y, ei = batch.ptr, getattr(batch, "edge_ptr", None), batch.x, batch.y, batch.edge_index
             dev = self.device
             if all(t is not None and t.device == dev and t.is_contiguous() for t in (ptr, eptr, x, y, ei)) and \
@@ -182,7 +184,11 @@ class FusedTrainer:
                     ptr.dtype == torch.int64 and eptr.dtype == torch.int64 and ei.shape[1] > 0 and x.shape[0] > 0:
                 if any(p.data_ptr() != self.flat.data_ptr() + 4 * o for p, o in zip(self.params, self._offsets)):
                     self._bind()
-                return self._step_one_call(batch, x, y, ptr, eptr)
+                if self.world == 1:
+                    return self._step_one_call(batch, x, y, ptr, eptr)
+                self._step_one_call(batch, x, y, ptr, eptr, adam=False)     # gradients of this rank's shard
+                self.reduce()
+                return self.apply()
         self.accumulate(batch)
         self.reduce()
         return self.apply()

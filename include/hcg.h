@@ -424,6 +424,8 @@ int hcg_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
  * caller-owned workspace (hcg_train_step_workspace_bytes).  For the reference's own regime (batches of 40 reactions)
  * the step is bound by the host's per-call cost, not by the kernels.  `p` / `grads` point into `param_slab` /
  * `grad_slab` (n floats + the [SSE, count] tail).  Single rank; preconditions of the graph-local collate apply.
+ * step = 0: stop after the backward (grad_slab = [gradient of the shard's SSE | SSE | count]; no optimizer state needed):
+ * data-parallel ranks all-reduce grad_slab and call hcg_adam_step themselves.
  * max_graph_nodes / max_graph_edges / max_in_degree: host-verified facts about the batch (0 / 0 / -1 = unknown).  When
  * they show that the edge-list forward applies (<= 128 nodes and <= 512 edges per graph, in-degree <= 16), the forward
  * runs straight from the edge list and the collate - whose transposed CSR only the backward reads - runs beside it on
