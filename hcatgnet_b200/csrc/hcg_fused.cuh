@@ -69,7 +69,8 @@ int gcn_forward_coo_saved(const float* x, const int64_t* edge_index, const int64
 
 // the next hcg_gcn_backward of the calling thread makes its stream wait for `ev` after the readout part, before the
 // first kernel that reads the graph arrays (rowptr / col / dis / transposed CSR)
-void set_backward_prereq(cudaEvent_t ev);
+// (`side`: the stream `ev` was recorded on; the tensor-core backward builds its work list there too and re-records `ev`)
+void set_backward_prereq(cudaEvent_t ev, cudaStream_t side = nullptr);
 
 // packed-image variant: graphs [first, first + a.B) of a packed image resident in device memory (a.x is not used);
 // same workspace and flags as the COO variant.  tc_fwd_packed_fits: the image's per-node bytes fit the kernel's stage.
@@ -120,6 +121,6 @@ int launch_fused_bwd(FusedBwdArgs a, int64_t N, float* g_w2, float* g_w1, float*
 int tc_bwd_grid(int64_t B);
 size_t tc_bwd_workspace_bytes(int64_t B);
 int launch_tc_bwd(FusedBwdArgs a, int64_t N, int64_t E, void* ws, bool all_fit, float* g_w2, float* g_w1, float* g_b2, float* g_b1,
-                  cudaStream_t st);
+                  cudaStream_t st, cudaStream_t desc_st = nullptr, cudaEvent_t desc_ev = nullptr);
 
 }  // namespace hcg

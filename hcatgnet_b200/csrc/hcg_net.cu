@@ -1524,7 +1524,8 @@ extern "C" int hcg_gcn_forward_coo_static(const float* x, const int64_t* edge_in
 
 // event the NEXT hcg_gcn_backward of this thread waits for before it reads the graph arrays (set by hcg_train_step)
 static thread_local cudaEvent_t g_backward_prereq = nullptr;
-void hcg::set_backward_prereq(cudaEvent_t ev) { g_backward_prereq = ev; }
+static thread_local cudaStream_t g_backward_side = nullptr;
+void hcg::set_backward_prereq(cudaEvent_t ev, cudaStream_t side) { g_backward_prereq = ev; g_backward_side = ev ? side : nullptr; }
 
 extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgParams* p, const HcgSaved* saved,
                                 const float* emb, const float* g_out, const float* g_emb,
@@ -1599,17 +1600,24 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
     }
   }
 
-  // (hcg_train_step builds the transposed CSR on a second stream while the readout part above runs: join it here)
-  if (g_backward_prereq != nullptr) {
-    HCG_CUDA_OK(cudaStreamWaitEvent(st, g_backward_prereq, 0));
-    g_backward_prereq = nullptr;
-  }
+  // (hcg_train_step builds the transposed CSR on a second stream while the readout part above runs: it is joined here,
+  //  or - tensor-core path - after the backward's work list has been built on that stream as well)
+  const cudaEvent_t side_ev = g_backward_prereq;
+  const cudaStream_t side_st = g_backward_side;
+  g_backward_prereq = nullptr; g_backward_side = nullptr;
+  bool joined = side_ev == nullptr;
+  auto join_side = [&]() -> int {
+    if (!joined) { joined = true; HCG_CUDA_OK(cudaStreamWaitEvent(st, side_ev, 0)); }
+    return HCG_OK;
+  };
   // ---- graph-resident path: pooling backward + both conv layers in one kernel ----------------
   {
     const int bpath = config_get(HCG_CFG_BACKWARD_PATH);
     const bool ok = fused_bwd_shape_ok(g, p) && g_x == nullptr && w.fscratch != nullptr;
-    if ((bpath == 2 || bpath == 3) && !ok)
+    if ((bpath == 2 || bpath == 3) && !ok) {
+      join_side();
       return set_err(HCG_ERR_UNSUPPORTED, "graph-resident backward needs H == %d, L == 2, F <= 32, no edge weights, a disjoint batch and g_x == NULL", kFusedH);
+    }
     if (ok && bpath != 1) {
       FusedBwdArgs a{};
       a.t_rowptr = g->t_rowptr; a.t_col = g->t_col; a.dis = g->dis; a.graph_ptr = g->graph_ptr;
@@ -1620,11 +1628,18 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
       if (bpath != 3 && w.tcb != nullptr) {
         const bool all_fit = g->max_graph_nodes > 0 && g->max_graph_nodes <= tc_fwd_row_cap() && g->max_graph_edges > 0 &&
                              g->max_graph_edges <= tc_fwd_edge_cap();
+        if (!joined) {   // the work list goes out on the second stream, behind the collate; `st` joins after it
+          joined = true;
+          return launch_tc_bwd(a, N, g->E, w.tcb, all_fit, grads->conv_w[1], grads->conv_w[0], grads->conv_b[1], grads->conv_b[0], st,
+                               side_st, side_ev);
+        }
         return launch_tc_bwd(a, N, g->E, w.tcb, all_fit, grads->conv_w[1], grads->conv_w[0], grads->conv_b[1], grads->conv_b[0], st);
       }
+      if (int rcj = join_side()) return rcj;
       return launch_fused_bwd(a, N, grads->conv_w[1], grads->conv_w[0], grads->conv_b[1], grads->conv_b[0], st);
     }
   }
+  if (int rcj = join_side()) return rcj;
 
   // ---- pooling backward (+ LeakyReLU' of the last conv layer) -----------------------------
   if (N > 0) {  // nodes of no graph
