@@ -72,6 +72,15 @@ int gcn_forward_coo_saved(const float* x, const int64_t* edge_index, const int64
 // (`side`: the stream `ev` was recorded on; the tensor-core backward builds its work list there too and re-records `ev`)
 void set_backward_prereq(cudaEvent_t ev, cudaStream_t side = nullptr);
 
+// The head of a training step in one kernel + reduce (hcg_net.cu): forward of the default readout, loss seed
+// (tail = [sum (out - y)^2, B C]) and its backward: g_emb [B, 2H] and the readout gradients into `grads`.
+// partial: readout2_train_partial_floats(B, C) floats of scratch.
+bool readout2_train_supported(const HcgParams* p);
+size_t readout2_train_partial_floats(int64_t B, int C);
+int launch_readout2_train(const float* emb, const HcgParams* p, const float* y, int64_t B, float* g_emb, float* partial,
+                          const HcgGrads* grads, float* tail, cudaStream_t st);
+void set_backward_keep_readout_grads(bool keep);
+
 // packed-image variant: graphs [first, first + a.B) of a packed image resident in device memory (a.x is not used);
 // same workspace and flags as the COO variant.  tc_fwd_packed_fits: the image's per-node bytes fit the kernel's stage.
 bool tc_fwd_packed_fits(const HcgPackedStore& pk);

@@ -651,39 +651,98 @@ constexpr int RB_P = 68;  // pitch of the 64-wide shared tiles
 
 __host__ __device__ inline int ro2_partial_elems(int C) { return RO_HID * RO_IN + RO_HID + C * RO_HID + C; }
 __host__ __device__ inline int ro2_partial_stride(int C) { return (ro2_partial_elems(C) + 3) & ~3; }  // 16-byte aligned blocks
-static inline size_t ro2_bwd_smem_bytes(int C) {
-  return sizeof(float) * (size_t)(RO_HID * RO_IN + RO_G * RO_IN + 2 * RO_G * RB_P + RO_G * C);
+constexpr int RO_W1P = RO_IN + 4;  // pitch of the W1 tile: the head's forward product reads it by columns (bank = 4 j + k)
+static inline size_t ro2_bwd_smem_bytes(int C, bool train = false) {
+  return sizeof(float) * (size_t)(RO_HID * RO_W1P + RO_G * RO_IN + 2 * RO_G * RB_P + RO_G * C + (train ? RO_G * (RO_HID + 1) + 256 : 0));
 }
 
+// TRAIN = true: the whole head of a training step in one kernel - its forward (hid = lrelu(emb W1^T + b1),
+// out = hid W2^T + b2, the arithmetic and order of k_readout2), the loss seed (g_out = 2 (out - y), the block's share of
+// sum (out - y)^2 -> sse_partial[block]; hcg_rmse_seed) and the backward below, with hid and g_out kept in shared
+// memory (`hid`, `g_out` are not read).
+template <bool TRAIN>
 __global__ void __launch_bounds__(256)
 k_readout2_bwd(const float* __restrict__ emb, const float* __restrict__ hid, const float* __restrict__ g_out,
                const float* __restrict__ g_emb_extra, const float* __restrict__ W1, const float* __restrict__ W2,
-               int64_t B, int C, float slope, float* __restrict__ g_emb, float* __restrict__ partial) {
+               int64_t B, int C, float slope, float* __restrict__ g_emb, float* __restrict__ partial,
+               const float* __restrict__ b1, const float* __restrict__ b2, const float* __restrict__ y,
+               float* __restrict__ sse_partial) {
   extern __shared__ __align__(16) float ro_smem[];
-  float* W1s = ro_smem;                    // [64][128]  (unit j, input k)
-  float* Es = W1s + RO_HID * RO_IN;        // [64][128]  (graph g, input k)
+  float* W1s = ro_smem;                    // [64][132]  (unit j, input k)
+  float* Es = W1s + RO_HID * RO_W1P;       // [64][128]  (graph g, input k)
   float* G = Es + RO_G * RO_IN;            // [64][68]   gpre1[g][j]
   float* GT = G + RO_G * RB_P;             // [64][68]   gpre1[j][g]
   float* Go = GT + RO_G * RB_P;            // [64][C]    g_out tile
+  float* Hs = Go + RO_G * C;               // TRAIN: [64][65] hid tile, then 256 floats of reduction scratch
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int64_t g0 = (int64_t)blockIdx.x * RO_G;
   float* part = partial + (int64_t)blockIdx.x * ro2_partial_stride(C);
 
-  for (int idx = tid; idx < RO_HID * RO_IN / 4; idx += 256)
-    reinterpret_cast<float4*>(W1s)[idx] = ldg4(W1 + 4 * idx);
+  for (int idx = tid; idx < RO_HID * RO_IN / 4; idx += 256) {
+    const int j = idx / (RO_IN / 4), k4 = idx - j * (RO_IN / 4);
+    *reinterpret_cast<float4*>(W1s + j * RO_W1P + 4 * k4) = ldg4(W1 + 4 * idx);
+  }
   for (int idx = tid; idx < RO_G * RO_IN / 4; idx += 256) {
     const int g = idx / (RO_IN / 4);
     reinterpret_cast<float4*>(Es)[idx] = g0 + g < B ? ldg4(emb + g0 * RO_IN + 4 * (int64_t)idx) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  for (int idx = tid; idx < RO_G * C; idx += 256) Go[idx] = g0 + idx / C < B ? g_out[g0 * C + idx] : 0.f;
+  if (!TRAIN)
+    for (int idx = tid; idx < RO_G * C; idx += 256) Go[idx] = g0 + idx / C < B ? g_out[g0 * C + idx] : 0.f;
   __syncthreads();
+  if (TRAIN) {
+    // forward head: thread = graphs 4 ty .. + 3, units tx + 16 b; k ascending with one fmaf chain per output, as k_readout2
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < RO_IN; ++k) {
+      float e[4], w[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) e[a] = Es[(4 * ty + a) * RO_IN + k];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) w[b] = W1s[(tx + 16 * b) * RO_W1P + k];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(e[a], w[b], acc[a][b]);
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int j = tx + 16 * b;
+        Hs[(4 * ty + a) * (RO_HID + 1) + j] = lrelu(acc[a][b] + __ldg(b1 + j), slope);
+      }
+    __syncthreads();
+    float sq = 0.f;
+    for (int idx = tid; idx < RO_G * C; idx += 256) {
+      const int g = idx / C, c = idx - g * C;
+      float o = 0.f;
+#pragma unroll 8
+      for (int j = 0; j < RO_HID; ++j) o = fmaf(Hs[g * (RO_HID + 1) + j], __ldg(W2 + c * RO_HID + j), o);
+      o += __ldg(b2 + c);
+      const float d = g0 + g < B ? o - __ldg(y + g0 + g) : 0.f;
+      Go[idx] = 2.f * d;
+      sq = fmaf(d, d, sq);
+    }
+    float* red = Hs + RO_G * (RO_HID + 1);
+    red[tid] = sq;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+      if (tid < w) red[tid] += red[tid + w];
+      __syncthreads();
+    }
+    if (tid == 0) sse_partial[blockIdx.x] = red[0];
+  }
 
   // gpre1 (both orientations)
   for (int idx = tid; idx < RO_G * RO_HID; idx += 256) {
     const int g = idx >> 6, j = idx & 63;
     float s = 0.f;
     for (int c = 0; c < C; ++c) s = fmaf(Go[g * C + c], __ldg(W2 + c * RO_HID + j), s);
-    const float h = g0 + g < B ? hid[(g0 + g) * RO_HID + j] : 0.f;
+    const float h = TRAIN ? Hs[g * (RO_HID + 1) + j] : (g0 + g < B ? hid[(g0 + g) * RO_HID + j] : 0.f);
     s *= lrelu_grad_from_out(h, slope);
     G[g * RB_P + j] = s;
     GT[j * RB_P + g] = s;
@@ -698,7 +757,7 @@ k_readout2_bwd(const float* __restrict__ emb, const float* __restrict__ hid, con
     for (int c = 0; c < C; ++c) {
       float w = 0.f;
       for (int g = 0; g < RO_G; ++g)
-        if (g0 + g < B) w = fmaf(Go[g * C + c], hid[(g0 + g) * RO_HID + tid], w);
+        if (g0 + g < B) w = fmaf(Go[g * C + c], TRAIN ? Hs[g * (RO_HID + 1) + tid] : hid[(g0 + g) * RO_HID + tid], w);
       part[RO_HID * RO_IN + RO_HID + c * RO_HID + tid] = w;
     }
   } else if (tid < RO_HID + C) {
@@ -718,8 +777,8 @@ k_readout2_bwd(const float* __restrict__ emb, const float* __restrict__ hid, con
 #pragma unroll 4
     for (int j = 0; j < RO_HID; ++j) {
       const float4 a4 = *reinterpret_cast<const float4*>(GT + j * RB_P + 4 * ty);
-      const float4 w0 = *reinterpret_cast<const float4*>(W1s + j * RO_IN + 8 * tx);
-      const float4 w1 = *reinterpret_cast<const float4*>(W1s + j * RO_IN + 8 * tx + 4);
+      const float4 w0 = *reinterpret_cast<const float4*>(W1s + j * RO_W1P + 8 * tx);
+      const float4 w1 = *reinterpret_cast<const float4*>(W1s + j * RO_W1P + 8 * tx + 4);
       const float av[4] = {a4.x, a4.y, a4.z, a4.w};
       const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
 #pragma unroll
@@ -773,9 +832,16 @@ k_readout2_bwd(const float* __restrict__ emb, const float* __restrict__ hid, con
 
 __global__ void __launch_bounds__(256)
 k_readout2_bwd_reduce(const float* __restrict__ partial, int blocks, int C, float* __restrict__ gW1, float* __restrict__ gb1,
-                      float* __restrict__ gW2, float* __restrict__ gb2) {
+                      float* __restrict__ gW2, float* __restrict__ gb2, const float* __restrict__ sse_partial = nullptr,
+                      float* __restrict__ tail = nullptr, float count = 0.f) {
   const int pe = ro2_partial_stride(C);
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (sse_partial != nullptr && e == 0) {   // the training head's loss seed: [sum of squared errors, count], blocks in order
+    float s = 0.f;
+    for (int k = 0; k < blocks; ++k) s += sse_partial[k];
+    tail[0] = s;
+    tail[1] = count;
+  }
   if (e >= ro2_partial_elems(C)) return;
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
   int k = 0;
@@ -1351,7 +1417,7 @@ int hcg::gcn_forward_coo_saved(const float* x, const int64_t* edge_index, const 
   if (rc) return rc;
   HCG_REQUIRE(N >= 0 && E >= 0 && B >= 0 && N < INT32_MAX && E < INT32_MAX, HCG_ERR_INVALID_ARG, "bad sizes N=%lld E=%lld B=%lld",
               (long long)N, (long long)E, (long long)B);
-  HCG_REQUIRE(out && emb && ws, HCG_ERR_INVALID_ARG, "NULL out/emb/workspace");
+  HCG_REQUIRE((out || saved) && emb && ws, HCG_ERR_INVALID_ARG, "NULL out/emb/workspace");
   HCG_REQUIRE((N == 0 || x) && (E == 0 || edge_index) && node_ptr && edge_ptr, HCG_ERR_INVALID_ARG, "NULL x/edge_index/offsets");
   if (!hcg_forward_coo_supported(p))
     return set_err(HCG_ERR_UNSUPPORTED, "edge-list forward needs H == %d, F <= 32, 0 <= slope <= 1 and conv layers that fit shared memory", kFusedH);
@@ -1369,8 +1435,29 @@ int hcg::gcn_forward_coo_saved(const float* x, const int64_t* edge_index, const 
   a.emb = emb;
   a.B = B; a.F = p->F; a.Fp = (p->F + 3) / 4 * 4; a.L = p->L; a.slope = p->slope; a.fill = fill;
   rc = launch_tc_fwd_coo(a, edge_index, node_ptr, edge_ptr, N, E, w.tc, st);
-  if (rc) return rc;
+  if (rc || out == nullptr) return rc;     // (out == NULL: embeddings only - the training step runs the head itself)
   return run_readout(p, emb, out, saved, w.hid, B, st);
+}
+
+// ---- the training step's head in one kernel (+ the reduce): forward, loss seed, backward of the default readout ------
+bool hcg::readout2_train_supported(const HcgParams* p) { return p->R == 2 && 2 * p->H == RO_IN && p->C >= 1 && p->C <= 16; }
+size_t hcg::readout2_train_partial_floats(int64_t B, int C) {
+  return (size_t)cdiv(B, RO_G) * (size_t)ro2_partial_stride(C) + (size_t)cdiv(B, RO_G) + 8;
+}
+int hcg::launch_readout2_train(const float* emb, const HcgParams* p, const float* y, int64_t B, float* g_emb, float* partial,
+                               const HcgGrads* grads, float* tail, cudaStream_t st) {
+  const size_t smem = ro2_bwd_smem_bytes(p->C, true);
+  static SmemConfigured configured;
+  if (int rc = ensure_dyn_smem(k_readout2_bwd<true>, smem, configured)) return rc;
+  const int blocks = (int)cdiv(B, RO_G);
+  float* sse_partial = partial + (size_t)blocks * ro2_partial_stride(p->C);
+  k_readout2_bwd<true><<<blocks, 256, smem, st>>>(emb, nullptr, nullptr, nullptr, p->ro_w[0], p->ro_w[1], B, p->C, p->slope, g_emb,
+                                                 partial, p->ro_b[0], p->ro_b[1], y, sse_partial);
+  HCG_LAUNCH_OK(st, "k_readout2_train");
+  k_readout2_bwd_reduce<<<(unsigned)cdiv(ro2_partial_elems(p->C), 256), 256, 0, st>>>(
+      partial, blocks, p->C, grads->ro_w[0], grads->ro_b[0], grads->ro_w[1], grads->ro_b[1], sse_partial, tail, (float)(B * p->C));
+  HCG_LAUNCH_OK(st, "k_readout2_bwd_reduce");
+  return HCG_OK;
 }
 
 extern "C" int hcg_forward_coo_status(const void* ws, int64_t B, void* stream, int32_t* flags) {
@@ -1525,6 +1612,9 @@ extern "C" int hcg_gcn_forward_coo_static(const float* x, const int64_t* edge_in
 // event the NEXT hcg_gcn_backward of this thread waits for before it reads the graph arrays (set by hcg_train_step)
 static thread_local cudaEvent_t g_backward_prereq = nullptr;
 static thread_local cudaStream_t g_backward_side = nullptr;
+static thread_local bool g_backward_keep_readout = false;
+// the next hcg_gcn_backward of this thread (called with g_out == NULL) leaves the readout gradients as they are
+void hcg::set_backward_keep_readout_grads(bool keep) { g_backward_keep_readout = keep; }
 void hcg::set_backward_prereq(cudaEvent_t ev, cudaStream_t side) { g_backward_prereq = ev; g_backward_side = ev ? side : nullptr; }
 
 extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgParams* p, const HcgSaved* saved,
@@ -1549,15 +1639,17 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
   note_region(st);
 
   // ---- readout MLP backward -------------------------------------------------------------
+  const bool keep_readout_grads = g_backward_keep_readout;
+  g_backward_keep_readout = false;
   const float* gemb_total = g_emb;
   if (g_out && w.ropartial != nullptr && config_get(HCG_CFG_BACKWARD_PATH) != 1) {
     // default head (128 -> 64 -> C): one kernel + one reduce
     const size_t smem = ro2_bwd_smem_bytes(p->C);
     static SmemConfigured configured;
-    if (int rc2 = ensure_dyn_smem(k_readout2_bwd, smem, configured)) return rc2;
+    if (int rc2 = ensure_dyn_smem(k_readout2_bwd<false>, smem, configured)) return rc2;
     const int blocks = (int)cdiv(B, RO_G);
-    k_readout2_bwd<<<blocks, 256, smem, st>>>(emb, saved->hid[0], g_out, g_emb, p->ro_w[0], p->ro_w[1], B, p->C, p->slope,
-                                             w.gemb, w.ropartial);
+    k_readout2_bwd<false><<<blocks, 256, smem, st>>>(emb, saved->hid[0], g_out, g_emb, p->ro_w[0], p->ro_w[1], B, p->C, p->slope,
+                                                    w.gemb, w.ropartial, nullptr, nullptr, nullptr, nullptr);
     HCG_LAUNCH_OK(st, "k_readout2_bwd");
     k_readout2_bwd_reduce<<<(unsigned)cdiv(ro2_partial_elems(p->C), 256), 256, 0, st>>>(
         w.ropartial, blocks, p->C, grads->ro_w[0], grads->ro_b[0], grads->ro_w[1], grads->ro_b[1]);
@@ -1593,7 +1685,7 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
       gz = gin;
     }
     gemb_total = w.gemb;
-  } else {
+  } else if (!keep_readout_grads) {
     for (int k = 0; k < p->R; ++k) {
       HCG_CUDA_OK(cudaMemsetAsync(grads->ro_w[k], 0, sizeof(float) * (size_t)ro_in_dim(p, k) * ro_out_dim(p, k), st));
       HCG_CUDA_OK(cudaMemsetAsync(grads->ro_b[k], 0, sizeof(float) * (size_t)ro_out_dim(p, k), st));

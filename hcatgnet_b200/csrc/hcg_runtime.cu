@@ -32,6 +32,7 @@ static std::atomic<int> g_prof_on{0};
 struct Mark {
   const char* name;  // string literal; nullptr = region start (not attributed)
   cudaEvent_t ev;
+  cudaStream_t st;   // a mark is timed against the previous mark of the SAME stream (hcg_train_step uses two)
 };
 
 struct Profiler {
@@ -51,7 +52,7 @@ struct Profiler {
     }
     cudaEvent_t e = pool[next++];
     cudaEventRecord(e, st);
-    marks.push_back({name, e});
+    marks.push_back({name, e, st});
   }
   void reset() {
     std::lock_guard<std::mutex> lk(mu);
@@ -101,10 +102,16 @@ extern "C" int hcg_profile_read(char* name_buf, float* total_ms, int64_t* counts
   if (!p.marks.empty()) HCG_CUDA_OK(cudaEventSynchronize(p.marks.back().ev));
   std::map<std::string, std::pair<double, int64_t>> agg;
   std::vector<std::string> order;
-  for (size_t i = 1; i < p.marks.size(); ++i) {
-    if (p.marks[i].name == nullptr) continue;
+  if (!p.marks.empty()) HCG_CUDA_OK(cudaDeviceSynchronize());   // (marks of every stream)
+  std::map<cudaStream_t, size_t> last;   // index of the previous mark of each stream
+  for (size_t i = 0; i < p.marks.size(); ++i) {
+    const auto prev = last.find(p.marks[i].st);
+    const bool have_prev = prev != last.end();
+    const size_t j = have_prev ? prev->second : 0;
+    last[p.marks[i].st] = i;
+    if (p.marks[i].name == nullptr || !have_prev) continue;
     float ms = 0.f;
-    HCG_CUDA_OK(cudaEventElapsedTime(&ms, p.marks[i - 1].ev, p.marks[i].ev));
+    HCG_CUDA_OK(cudaEventElapsedTime(&ms, p.marks[j].ev, p.marks[i].ev));
     auto it = agg.find(p.marks[i].name);
     if (it == agg.end()) {
       order.push_back(p.marks[i].name);

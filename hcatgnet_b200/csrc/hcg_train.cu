@@ -120,6 +120,7 @@ struct StepWs {
   float *out, *emb, *g_out;
   char* bwd;
   char* coo;
+  float *head_gemb, *head_partial;
   size_t collate_bytes, fwd_bytes, bwd_bytes, coo_bytes, bytes;
 };
 
@@ -144,6 +145,8 @@ static StepWs carve_step(void* ws, int64_t N, int64_t E, int64_t B, const HcgPar
   w.bwd = c.take<char>(w.bwd_bytes);
   w.coo_bytes = hcg_forward_coo_workspace_bytes(B, p);
   w.coo = c.take<char>(w.coo_bytes);
+  w.head_gemb = c.take<float>((size_t)B * 2 * p->H + 4);
+  w.head_partial = c.take<float>(readout2_train_partial_floats(B, p->C > 0 ? p->C : 1));
   w.bytes = c.off;
   return w;
 }
@@ -205,12 +208,15 @@ extern "C" int hcg_train_step(const float* x, const int64_t* edge_index, int64_t
   for (int l = 0; l < p->L; ++l) saved.acts[l] = w.acts[l];
   for (int k = 0; k < p->R - 1; ++k) saved.hid[k] = w.hid[k];
   int rc;
+  bool fused_head = false;   // forward head + loss seed + backward head in ONE kernel (default readout)
   if (coo_fwd) {
     // forward first, on the caller's stream; then the collate on the second stream, beside the loss seed and the readout
     // part of the backward (small kernels that leave most of the GPU idle); hcg_gcn_backward joins it before its conv part
     SideStream* side = nullptr;
     if (int rc0 = side_stream(&side)) return rc0;
-    rc = gcn_forward_coo_saved(x, edge_index, node_ptr, edge_ptr, N, E, B, fill, p, w.out, w.emb, &saved, w.coo, w.coo_bytes, stream);
+    fused_head = readout2_train_supported(p);
+    rc = gcn_forward_coo_saved(x, edge_index, node_ptr, edge_ptr, N, E, B, fill, p, fused_head ? nullptr : w.out, w.emb, &saved, w.coo,
+                               w.coo_bytes, stream);
     if (rc) return rc;
     HCG_CUDA_OK(cudaEventRecord(side->fork, main_st));     // (orders the side stream behind the previous step's backward, too)
     HCG_CUDA_OK(cudaStreamWaitEvent(side->st, side->fork, 0));
@@ -237,9 +243,17 @@ extern "C" int hcg_train_step(const float* x, const int64_t* edge_index, int64_t
     return code;
   };
   float* tail = grad_slab + n;
-  rc = hcg_rmse_seed(w.out, y, B, p->C, w.g_out, tail, stream);
-  if (rc) return bail(rc);
-  rc = hcg_gcn_backward(&g, x, p, &saved, w.emb, w.g_out, nullptr, grads, nullptr, w.bwd, w.bwd_bytes, stream);
+  if (fused_head) {
+    rc = launch_readout2_train(w.emb, p, y, B, w.head_gemb, w.head_partial, grads, tail, main_st);
+    if (rc) return bail(rc);
+    set_backward_keep_readout_grads(true);
+    rc = hcg_gcn_backward(&g, x, p, &saved, w.emb, nullptr, w.head_gemb, grads, nullptr, w.bwd, w.bwd_bytes, stream);
+    set_backward_keep_readout_grads(false);
+  } else {
+    rc = hcg_rmse_seed(w.out, y, B, p->C, w.g_out, tail, stream);
+    if (rc) return bail(rc);
+    rc = hcg_gcn_backward(&g, x, p, &saved, w.emb, w.g_out, nullptr, grads, nullptr, w.bwd, w.bwd_bytes, stream);
+  }
   if (rc) return bail(rc);
   if (step <= 0) return HCG_OK;   // gradients only: data-parallel ranks all-reduce grad_slab, then call hcg_adam_step
   return hcg_adam_step(param_slab, grad_slab, exp_avg, exp_avg_sq, n, tail, lr, beta1, beta2, eps, step, loss_out, stream);
