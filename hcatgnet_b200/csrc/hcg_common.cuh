@@ -86,4 +86,31 @@ __device__ __forceinline__ float lrelu_grad_from_out(float h, float slope) { ret
 
 __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
+#ifdef __CUDACC__
+// Deterministic column sum of `rows` partial rows of pitch `pe` for a block of 32 consecutive elements: 256 threads =
+// 8 row slices x 32 elements (coalesced 128-byte loads); slice q adds rows q, q + 8, ... in order into two interleaved
+// sums, the eight slices are combined in a fixed order.  ~rows / 16 dependent loads instead of rows / 4.
+// Returns the sum for element blockIdx.x * 32 + (threadIdx.x & 31) in the threads of slice 0 (others: undefined).
+__device__ __forceinline__ float det_colsum32(const float* __restrict__ partial, int rows, int pe, int e, bool valid, float* s_red) {
+  const int q = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float s0 = 0.f, s1 = 0.f;
+  if (valid) {
+    int k = q;
+    for (; k + 8 < rows; k += 16) {
+      s0 += partial[(int64_t)k * pe + e];
+      s1 += partial[(int64_t)(k + 8) * pe + e];
+    }
+    if (k < rows) s0 += partial[(int64_t)k * pe + e];
+  }
+  s_red[q * 32 + lane] = s0 + s1;
+  __syncthreads();
+  float v = 0.f;
+  if (q == 0) {
+    v = ((s_red[lane] + s_red[32 + lane]) + (s_red[64 + lane] + s_red[96 + lane])) +
+        ((s_red[128 + lane] + s_red[160 + lane]) + (s_red[192 + lane] + s_red[224 + lane]));
+  }
+  return v;
+}
+#endif
+
 }  // namespace hcg

@@ -277,23 +277,15 @@ k_fused_bwd(const FusedBwdArgs a) {
   }
 }
 
-// grads = sum over CTAs (in CTA order, four interleaved running sums) of the partials
+// grads = sum over CTAs of the partials, in a fixed order (det_colsum32)
 __global__ void __launch_bounds__(256)
 k_fused_bwd_reduce(const float* __restrict__ partial, int ctas, int F, float* __restrict__ g_w2, float* __restrict__ g_w1,
                    float* __restrict__ g_b2, float* __restrict__ g_b1) {
+  __shared__ float s_red[256];
   const int pe = 64 * 64 + 64 * F + 128;
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= pe) return;
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-  int k = 0;
-  for (; k + 4 <= ctas; k += 4) {
-    s0 += partial[(int64_t)k * pe + e];
-    s1 += partial[(int64_t)(k + 1) * pe + e];
-    s2 += partial[(int64_t)(k + 2) * pe + e];
-    s3 += partial[(int64_t)(k + 3) * pe + e];
-  }
-  for (; k < ctas; ++k) s0 += partial[(int64_t)k * pe + e];
-  const float v = (s0 + s1) + (s2 + s3);
+  const int e = blockIdx.x * 32 + (threadIdx.x & 31);
+  const float v = det_colsum32(partial, ctas, pe, e, e < pe, s_red);
+  if (e >= pe || threadIdx.x >= 32) return;
   if (e < 64 * 64) g_w2[e] = v;
   else if (e < 64 * 64 + 64 * F) g_w1[e - 64 * 64] = v;
   else if (e < 64 * 64 + 64 * F + 64) g_b2[e - 64 * 64 - 64 * F] = v;
@@ -327,7 +319,7 @@ int launch_fused_bwd(FusedBwdArgs a, int64_t N, float* g_w2, float* g_w1, float*
   k_fused_bwd<<<grid, kBwdThreads, smem, st>>>(a);
   HCG_LAUNCH_OK(st, "k_fused_bwd");
   const int pe = 64 * 64 + 64 * a.F + 128;
-  k_fused_bwd_reduce<<<(unsigned)cdiv(pe, 256), 256, 0, st>>>(reduce_base ? reduce_base : a.partial, grid + extra_rows, a.F, g_w2,
+  k_fused_bwd_reduce<<<(unsigned)cdiv(pe, 32), 256, 0, st>>>(reduce_base ? reduce_base : a.partial, grid + extra_rows, a.F, g_w2,
                                                              g_w1, g_b2, g_b1);
   HCG_LAUNCH_OK(st, "k_fused_bwd_reduce");
   return HCG_OK;

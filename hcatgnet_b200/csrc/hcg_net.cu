@@ -835,24 +835,16 @@ k_readout2_bwd_reduce(const float* __restrict__ partial, int blocks, int C, floa
                       float* __restrict__ gW2, float* __restrict__ gb2, const float* __restrict__ sse_partial = nullptr,
                       float* __restrict__ tail = nullptr, float count = 0.f) {
   const int pe = ro2_partial_stride(C);
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (sse_partial != nullptr && e == 0) {   // the training head's loss seed: [sum of squared errors, count], blocks in order
+  const int e = blockIdx.x * 32 + (threadIdx.x & 31);
+  if (sse_partial != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {   // the training head's loss seed: [sum of squared errors, count], blocks in order
     float s = 0.f;
     for (int k = 0; k < blocks; ++k) s += sse_partial[k];
     tail[0] = s;
     tail[1] = count;
   }
-  if (e >= ro2_partial_elems(C)) return;
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-  int k = 0;
-  for (; k + 4 <= blocks; k += 4) {
-    s0 += partial[(int64_t)k * pe + e];
-    s1 += partial[(int64_t)(k + 1) * pe + e];
-    s2 += partial[(int64_t)(k + 2) * pe + e];
-    s3 += partial[(int64_t)(k + 3) * pe + e];
-  }
-  for (; k < blocks; ++k) s0 += partial[(int64_t)k * pe + e];
-  const float v = (s0 + s1) + (s2 + s3);
+  __shared__ float s_red[256];
+  const float v = det_colsum32(partial, blocks, pe, e, e < ro2_partial_elems(C), s_red);
+  if (e >= ro2_partial_elems(C) || threadIdx.x >= 32) return;
   const int n1 = RO_HID * RO_IN;
   if (e < n1) gW1[e] = v;
   else if (e < n1 + RO_HID) gb1[e - n1] = v;
@@ -1454,7 +1446,7 @@ int hcg::launch_readout2_train(const float* emb, const HcgParams* p, const float
   k_readout2_bwd<true><<<blocks, 256, smem, st>>>(emb, nullptr, nullptr, nullptr, p->ro_w[0], p->ro_w[1], B, p->C, p->slope, g_emb,
                                                  partial, p->ro_b[0], p->ro_b[1], y, sse_partial);
   HCG_LAUNCH_OK(st, "k_readout2_train");
-  k_readout2_bwd_reduce<<<(unsigned)cdiv(ro2_partial_elems(p->C), 256), 256, 0, st>>>(
+  k_readout2_bwd_reduce<<<(unsigned)cdiv(ro2_partial_elems(p->C), 32), 256, 0, st>>>(
       partial, blocks, p->C, grads->ro_w[0], grads->ro_b[0], grads->ro_w[1], grads->ro_b[1], sse_partial, tail, (float)(B * p->C));
   HCG_LAUNCH_OK(st, "k_readout2_bwd_reduce");
   return HCG_OK;
@@ -1651,7 +1643,7 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
     k_readout2_bwd<false><<<blocks, 256, smem, st>>>(emb, saved->hid[0], g_out, g_emb, p->ro_w[0], p->ro_w[1], B, p->C, p->slope,
                                                     w.gemb, w.ropartial, nullptr, nullptr, nullptr, nullptr);
     HCG_LAUNCH_OK(st, "k_readout2_bwd");
-    k_readout2_bwd_reduce<<<(unsigned)cdiv(ro2_partial_elems(p->C), 256), 256, 0, st>>>(
+    k_readout2_bwd_reduce<<<(unsigned)cdiv(ro2_partial_elems(p->C), 32), 256, 0, st>>>(
         w.ropartial, blocks, p->C, grads->ro_w[0], grads->ro_b[0], grads->ro_w[1], grads->ro_b[1]);
     HCG_LAUNCH_OK(st, "k_readout2_bwd_reduce");
     gemb_total = w.gemb;
