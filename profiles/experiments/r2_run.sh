@@ -1,7 +1,7 @@
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-timeout 600 python bench.py --mode train --batch 4096 --steps 30 --warmup 5 --no-cpu-baseline 2>&1 | tail -1 > gpurun_out/train.json
+timeout 900 python bench.py 2>&1 | tail -1 > gpurun_out/r2_final_bench.json
 python - <<'PY'
 import json
-r=json.loads(open("gpurun_out/train.json").read())
-print(r["value"], r["ms_per_step"], r["e2e"]["value"], {n:round(v["ms_per_launch"]*1e3,1) for n,v in r["kernels"].items()})
+r=json.loads(open("gpurun_out/r2_final_bench.json").read())
+print(r["value"], r["ms_per_step"], r["e2e"]["value"], r["e2e_packed"]["value"], r["train"]["value"], r["train"]["e2e"]["value"], r["stress"]["value"], r["ensemble"]["value"])
+print(r["train"]["kernels"])
 PY
