@@ -1,7 +1,8 @@
-timeout 900 python bench.py 2>&1 | tail -1 > gpurun_out/r2_final_bench.json
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+for k in 1 2; do timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-sub 2>&1 | tail -1 > gpurun_out/b$k.json; done
 python - <<'PY'
 import json
-r=json.loads(open("gpurun_out/r2_final_bench.json").read())
-print(r["value"], r["ms_per_step"], r["e2e"]["value"], r["e2e_packed"]["value"], r["train"]["value"], r["train"]["e2e"]["value"], r["stress"]["value"], r["ensemble"]["value"])
-print(r["train"]["kernels"])
+for k in (1,2):
+    r=json.loads(open(f"gpurun_out/b{k}.json").read())
+    print(r["value"], r["ms_per_step"], {n:round(v["ms_per_launch"]*1e3,1) for n,v in r["kernels"].items()}, r["e2e_packed"]["value"], r["gpu_launches"])
 PY
