@@ -13,7 +13,6 @@
 #include "hcg_common.cuh"
 #include "hcg_fused.cuh"
 #include "hcg_mma.cuh"
-#include "hcg_readout.cuh"
 
 namespace hcg {
 
@@ -567,17 +566,60 @@ k_pool(const float* __restrict__ h, const int32_t* __restrict__ graph_ptr, int64
 constexpr int RO_G = 64, RO_IN = 128, RO_HID = 64, RO_KC = 32;
 constexpr int RO_FG = 32;  // graphs per block of the forward head (the backward keeps RO_G)
 
-// a block = 32 consecutive graphs through ro::head_tile (hcg_readout.cuh)
 __device__ __forceinline__ void
 readout2_block(const float* __restrict__ emb, const float* __restrict__ W1, const float* __restrict__ b1,
                const float* __restrict__ W2, const float* __restrict__ b2, float* __restrict__ hid_save,
                float* __restrict__ out, int64_t B, int C, float slope) {
-  __shared__ __align__(16) float sm[ro::kSmemFloats];
+  __shared__ __align__(16) float Es[RO_KC][RO_FG + 4];   // [k][graph]
+  __shared__ __align__(16) float Ws[RO_KC][RO_HID + 4];  // [k][unit]
+  __shared__ float Hs[RO_FG][RO_HID + 1];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int64_t g0 = (int64_t)blockIdx.x * RO_FG;
-  const int64_t left = B - g0;
-  const int n = left < RO_FG ? (int)left : RO_FG;
-  ro::head_tile(emb, W1, b1, W2, b2, hid_save, out, n, [g0](int r) { return g0 + r; }, C, slope, sm, (int)threadIdx.x,
-                [] { __syncthreads(); });
+  float acc[2][4];
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+  for (int k0 = 0; k0 < RO_IN; k0 += RO_KC) {
+    for (int idx = tid; idx < RO_FG * RO_KC; idx += 256) {
+      const int r = idx / RO_KC, c = idx % RO_KC;
+      Es[c][r] = g0 + r < B ? emb[(g0 + r) * RO_IN + k0 + c] : 0.f;
+    }
+    for (int idx = tid; idx < RO_HID * RO_KC; idx += 256) {
+      const int r = idx / RO_KC, c = idx % RO_KC;
+      Ws[c][r] = W1[r * RO_IN + k0 + c];
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int kk = 0; kk < RO_KC; ++kk) {
+      const float2 e2 = *reinterpret_cast<const float2*>(&Es[kk][ty * 2]);
+      const float4 w4 = *reinterpret_cast<const float4*>(&Ws[kk][tx * 4]);
+      const float e[2] = {e2.x, e2.y}, w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+      for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(e[a], w[b], acc[a][b]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int g = ty * 2 + a, o = tx * 4 + b;
+      const float v = lrelu(acc[a][b] + b1[o], slope);
+      Hs[g][o] = v;
+      if (hid_save && g0 + g < B) hid_save[(g0 + g) * RO_HID + o] = v;
+    }
+  __syncthreads();
+  for (int idx = tid; idx < RO_FG * C; idx += 256) {
+    const int g = idx % RO_FG, c = idx / RO_FG;
+    if (g0 + g >= B) continue;
+    float s = 0.f;
+#pragma unroll 8
+    for (int o = 0; o < RO_HID; ++o) s = fmaf(Hs[g][o], W2[c * RO_HID + o], s);
+    out[(g0 + g) * C + c] = s + b2[c];
+  }
 }
 
 __global__ void __launch_bounds__(256)
