@@ -1,4 +1,5 @@
 N=${HCG_N:-2}
+timeout 600 python -m pytest tests/test_gpu_dp.py tests/test_zz_no_alloc.py -x -q 2>&1 | tail -2
 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 20 --warmup 5 2>&1 | tail -1 > gpurun_out/scale$N.json
 python - <<'PY'
 import json, os
