@@ -656,6 +656,45 @@ k_tc_fwd(const TcArgs a) {
   };
   int p_gA = -1, p_gB = -1, p_nA = 0, p_nB = 0;   // the tile whose last-layer rows sit in the activation buffer, not yet pooled
 
+  // PK: the x rows of a tile, expanded from the staged bit / byte / f32 slices of stage `st` into dense fp32 rows of the
+  // slot's x buffer.  Runs at the top of a tile, or - from the second conv layer on - a tile EARLY, inside the previous
+  // tile's layer-1 MMA window (the x buffer is free once that tile's layer-0 gather is over).
+  bool pre_expanded = false;
+  auto expand_x = [&](const TcMeta* m, int st) {
+      // ---- the tile's x rows, expanded from the staged bit / byte / f32 slices into dense fp32 rows ---------
+      // (two threads per row, half of the columns each; a thread's columns are walked from a row-dependent start so
+      //  that the lanes of a warp - consecutive rows, pitch F floats - write different banks for any F)
+      const unsigned char* st8 = reinterpret_cast<const unsigned char*>(smf + cs_w0 + st * csw);
+      const int r = gt & 127, half = gt >> 7;
+      if (r < m->nA + m->nB) {
+        const int gb = r >= m->nA, lr = gb ? r - m->nA : r;
+        const unsigned char* pb = st8 + m->off[4 * gb + 0] + lr * pk_bs;
+        uint32_t bits = 0;                       // F <= 32: at most 32 bit columns, four bytes
+        for (int q = 0; q < pk_bs; ++q) bits |= (uint32_t)pb[q] << (8 * q);
+        const unsigned char* pu = st8 + m->off[4 * gb + 2] + lr * pk_fu;
+        const float* pf = reinterpret_cast<const float*>(st8 + m->off[4 * gb + 3]) + lr * pk_ff;
+        const int c0 = half ? (F + 1) >> 1 : 0, w = half ? F - ((F + 1) >> 1) : (F + 1) >> 1;
+        float* xo = smf + sx + r * F + c0;
+        const int cs = r % (w > 0 ? w : 1);
+        constexpr int WMAX = F_ > 0 ? (F_ + 1) / 2 : 16;
+        int sl[WMAX];
+#pragma unroll
+        for (int j = 0; j < WMAX; ++j) {          // (unrolled: the table reads, then the data reads, go out together)
+          int c = cs + j; c = c >= w ? c - w : c;
+          sl[j] = j < w ? s_slot[c0 + c] : 65536;
+        }
+        float v[WMAX];
+#pragma unroll
+        for (int j = 0; j < WMAX; ++j)
+          v[j] = sl[j] >= 65536 ? (float)((bits >> ((sl[j] - 65536) & 31)) & 1u) : sl[j] >= 0 ? (float)pu[sl[j]] : pf[~sl[j]];
+#pragma unroll
+        for (int j = 0; j < WMAX; ++j) {
+          int c = cs + j; c = c >= w ? c - w : c;
+          if (j < w) xo[c] = v[j];
+        }
+      }
+  };
+
   if (pf_warp) {
     fetch_rec(0);
     issue(0, false);
@@ -700,40 +739,8 @@ k_tc_fwd(const TcArgs a) {
       }
       ptx::named_bar_sync(bar_full, kSlotThreads);
     }
-    if (PK) {
-      // ---- the tile's x rows, expanded from the staged bit / byte / f32 slices into dense fp32 rows ---------
-      // (two threads per row, half of the columns each; a thread's columns are walked from a row-dependent start so
-      //  that the lanes of a warp - consecutive rows, pitch F floats - write different banks for any F)
-      const unsigned char* st8 = reinterpret_cast<const unsigned char*>(smf + srp);
-      const int r = gt & 127, half = gt >> 7;
-      if (r < ntot) {
-        const int gb = r >= nA, lr = gb ? r - nA : r;
-        const unsigned char* pb = st8 + mp->off[4 * gb + 0] + lr * pk_bs;
-        uint32_t bits = 0;                       // F <= 32: at most 32 bit columns, four bytes
-        for (int q = 0; q < pk_bs; ++q) bits |= (uint32_t)pb[q] << (8 * q);
-        const unsigned char* pu = st8 + mp->off[4 * gb + 2] + lr * pk_fu;
-        const float* pf = reinterpret_cast<const float*>(st8 + mp->off[4 * gb + 3]) + lr * pk_ff;
-        const int c0 = half ? (F + 1) >> 1 : 0, w = half ? F - ((F + 1) >> 1) : (F + 1) >> 1;
-        float* xo = smf + sx + r * F + c0;
-        const int cs = r % (w > 0 ? w : 1);
-        constexpr int WMAX = F_ > 0 ? (F_ + 1) / 2 : 16;
-        int sl[WMAX];
-#pragma unroll
-        for (int j = 0; j < WMAX; ++j) {          // (unrolled: the table reads, then the data reads, go out together)
-          int c = cs + j; c = c >= w ? c - w : c;
-          sl[j] = j < w ? s_slot[c0 + c] : 65536;
-        }
-        float v[WMAX];
-#pragma unroll
-        for (int j = 0; j < WMAX; ++j)
-          v[j] = sl[j] >= 65536 ? (float)((bits >> ((sl[j] - 65536) & 31)) & 1u) : sl[j] >= 0 ? (float)pu[sl[j]] : pf[~sl[j]];
-#pragma unroll
-        for (int j = 0; j < WMAX; ++j) {
-          int c = cs + j; c = c >= w ? c - w : c;
-          if (j < w) xo[c] = v[j];
-        }
-      }
-    }
+    if (PK && !pre_expanded) expand_x(mp, s);
+    pre_expanded = false;
     // ---- this thread's row: which graph of the tile, where its slices start -------------------------
     const bool row_ok = i < ntot;
     const bool warp_ok = i_warp_min < ntot;  // this warp owns at least one row of the tile
@@ -909,6 +916,12 @@ k_tc_fwd(const TcArgs a) {
         }
       }
       if (l == 0 && p_gA >= 0) pool_tile(p_gA, p_gB, p_nA, p_nB);   // the previous tile, while the MMAs run
+      if (PK && l == 1) {   // the NEXT tile's x rows, while this layer's MMAs run
+        ptx::mbar_wait(&bar_stage[slot][(k + 1) & 1], (uint32_t)((k + 1) >> 1) & 1u);
+        const TcMeta* m2 = &metas[slot][(k + 1) & 1];
+        if (m2->gA >= 0) expand_x(m2, (k + 1) & 1);
+        pre_expanded = true;
+      }
       if (ctl_warp) ptx::mbar_wait(&bar_mma[slot], mma_phase);      // one warp polls; the others sleep in the barrier below
       mma_phase ^= 1u;
       TC_TICK(5);

@@ -1,3 +1,2 @@
-export PYTHONPATH=.
-python profiles/experiments/stress_ab.py 2>&1 | tail -4
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+timeout 600 python -m pytest tests/test_gpu_edge_list.py -x -q 2>&1 | tail -3
+PYTHONPATH=. timeout 300 python profiles/experiments/packed_fwd_time.py 2>&1 | tail -3
