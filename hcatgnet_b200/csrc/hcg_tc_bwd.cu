@@ -22,7 +22,7 @@
 // never compounds over the batch); per-CTA sums go to `partial` and are summed in CTA order by k_fused_bwd_reduce:
 // no floating-point atomics, run-to-run identical.
 //
-// One CTA of 256 threads per SM (two threads per tile row, one 32-column plane each); shared memory holds five
+// One CTA of 512 threads per SM (four threads per tile row, 16 columns each); shared memory holds five
 // two-plane tiles (gT hi / lo, h1-or-x hi / lo, gA), W2^T tiles, the neighbour records and two CSR stages: ~207 KB.
 // Graphs above the tile capacity are flagged and served by the mma.sync kernel of hcg_fused_bwd.cu.
 #include "hcg_fused.cuh"
@@ -32,7 +32,17 @@
 
 namespace hcg {
 
-constexpr int kTbThreads = 256;
+#ifndef HCG_TB_THREADS
+#define HCG_TB_THREADS 512
+#endif
+constexpr int kTbThreads = HCG_TB_THREADS;     // 256 or 512
+constexpr int kTbTpr = kTbThreads / 128;        // threads per tile row
+constexpr int kTbCw = 64 / kTbTpr;              // columns per thread (32 or 16): units of 8 floats inside one 32-column plane
+constexpr int kTbUnits = kTbCw / 8;
+constexpr int kTbPq = kTbThreads / 64;          // row groups of the column owners (P1, P5)
+constexpr int kTbLd = 2048 / kTbThreads;        // 16-byte chunks of a 128 x 64 tile per thread
+constexpr int kTbLx = 4096 / kTbThreads;        // elements of a 128 x 32 x tile per thread
+static_assert(kTbThreads == 256 || kTbThreads == 512, "k_tc_bwd: two or four threads per tile row");
 
 #ifdef HCG_TC_TIMING
 __device__ unsigned long long g_tb_timing[16];
@@ -71,7 +81,7 @@ __host__ __device__ inline TbSmem tb_layout() {
   y.dw = ((uint32_t)kTcRows + 16 + 3) & ~3u;
   y.csr_words = y.rw + y.cw + y.dw;
   y.cst = o; o += 2 * y.csr_words * 4;
-  y.misc = o; o += (2 * 3 * 64 + 2 * 4 * 64 + 2 * 4 * 64) * 4;   // [gb][mx | gmax | gmean/n][64], tie counts [gb][4][64], column sums [2][4][64]
+  y.misc = o; o += (2 * 3 * 64 + 2 * kTbPq * 64 + 2 * kTbPq * 64) * 4;   // [gb][mx | gmax | gmean/n][64], tie counts [gb][kTbPq][64], column sums [2][kTbPq][64]
   y.total = o + 1024;
   return y;
 }
@@ -102,7 +112,9 @@ k_tc_bwd(const TbArgs a) {
   __shared__ int4 recs[2][3];
 
   const int tid = threadIdx.x, lane = tid & 31, wslot = tid >> 5;
-  const int cg = tid >> 7;            // column half = plane of the two-plane tiles
+  const int cg = tid >> 7;            // column group: columns kTbCw cg .. + kTbCw - 1
+  const int pl = (cg * kTbCw) >> 5;   // ... which sit in plane pl of the two-plane tiles,
+  const int ub = ((cg * kTbCw) & 31) >> 3;   // ... from 8-float unit ub on
   const int i = tid & 127;            // tile row
   const int i_warp_min = tid & 96;
   const bool ctl_warp = wslot == 3, pf_warp = wslot == 7;
@@ -123,8 +135,8 @@ k_tc_bwd(const TbArgs a) {
   const int nb_w = (int)(lay.nbr >> 2), cs_w0 = (int)(lay.cst >> 2);
   const int rw = (int)lay.rw, cw = (int)lay.cw, csw = (int)lay.csr_words;
   float* s_pool = reinterpret_cast<float*>(base + lay.misc);          // [gb][3][64]
-  int* s_cnt = reinterpret_cast<int*>(s_pool + 2 * 3 * 64);           // [gb][4][64]
-  float* s_red = reinterpret_cast<float*>(s_cnt + 2 * 4 * 64);        // [2][4][64]
+  int* s_cnt = reinterpret_cast<int*>(s_pool + 2 * 3 * 64);           // [gb][kTbPq][64]
+  float* s_red = reinterpret_cast<float*>(s_cnt + 2 * kTbPq * 64);    // [2][kTbPq][64]
 
   // ---- one-time setup: every byte of shared memory initialised (don't-care operand rows must never hold NaN) ----
   for (int idx = tid; idx < (int)(lay.total - 1024) / 4; idx += kTbThreads) smf[idx] = 0.f;
@@ -204,27 +216,29 @@ k_tc_bwd(const TbArgs a) {
   };
 
   // per-thread running sums over the tiles of this CTA
-  float acc_w2[32], acc_w1[16];
+  float acc_w2[kTbCw], acc_w1[16];      // (g_W1: the column groups below 32 only)
 #pragma unroll
-  for (int q = 0; q < 32; ++q) acc_w2[q] = 0.f;
+  for (int q = 0; q < kTbCw; ++q) acc_w2[q] = 0.f;
 #pragma unroll
   for (int q = 0; q < 16; ++q) acc_w1[q] = 0.f;
-  float b2acc = 0.f, b1acc = 0.f;      // column (tid & 63), rows (tid >> 6) mod 4
+  float b2acc = 0.f, b1acc = 0.f;      // column (tid & 63), rows (tid >> 6) mod kTbPq
   const int pc = tid & 63, pq = tid >> 6;
 
   // adds the finished weight-gradient accumulators of a tile to the register sums (rows 0..63 = TMEM lanes 0..63)
   auto take_w2 = [&]() {
     if (wrow) {
-      uint32_t r0[16], r1[16];
-      ptx::tmem_ld16(d_w2 + trow + cg * 32, r0);
-      ptx::tmem_ld16(d_w2 + trow + cg * 32 + 16, r1);
-      ptx::tmem_wait_ld();
 #pragma unroll
-      for (int q = 0; q < 16; ++q) { acc_w2[q] += __uint_as_float(r0[q]); acc_w2[16 + q] += __uint_as_float(r1[q]); }
+      for (int part = 0; part < kTbCw / 16; ++part) {
+        uint32_t r0[16];
+        ptx::tmem_ld16(d_w2 + trow + cg * kTbCw + part * 16, r0);
+        ptx::tmem_wait_ld();
+#pragma unroll
+        for (int q = 0; q < 16; ++q) acc_w2[part * 16 + q] += __uint_as_float(r0[q]);
+      }
     }
   };
   auto take_w1 = [&]() {
-    if (wrow) {
+    if (wrow && cg < 2) {
       uint32_t r0[16];
       ptx::tmem_ld16(d_w1 + trow + cg * 16, r0);
       ptx::tmem_wait_ld();
@@ -267,15 +281,15 @@ k_tc_bwd(const TbArgs a) {
     }
     // ---- h2 -> P (16-byte chunks, coalesced), per-graph pooling data -> shared memory -------------------------------
     {   // all (up to eight) loads of a thread in flight at once: one memory latency per tile, not eight
-      float4 v[8];
+      float4 v[kTbLd];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
+      for (int u = 0; u < kTbLd; ++u) {
         const int idx = tid + u * kTbThreads, r = idx >> 4, q = idx & 15;
         const int64_t grow = r < nA ? (int64_t)n0A + r : (int64_t)n0B + (r - nA);
         if (r < ntot) v[u] = ldg4(a.b.h2 + grow * 64 + 4 * q);
       }
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
+      for (int u = 0; u < kTbLd; ++u) {
         const int idx = tid + u * kTbThreads, r = idx >> 4, q = idx & 15;
         if (r < ntot) *reinterpret_cast<float4*>(P + tcb::plane_chunk_off(r, q)) = v[u];
       }
@@ -295,9 +309,9 @@ k_tc_bwd(const TbArgs a) {
     TB_TICK(3);
 
     // h1 of this tile: the loads go out now and are consumed after P1 (their latency hides under the records and P1)
-    float4 h1v[8];
+    float4 h1v[kTbLd];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
+    for (int u = 0; u < kTbLd; ++u) {
       const int idx = tid + u * kTbThreads, r = idx >> 4, q = idx & 15;
       const int64_t grow = r < nA ? (int64_t)n0A + r : (int64_t)n0B + (r - nA);
       if (r < ntot) h1v[u] = ldg4(a.b.h1 + grow * 64 + 4 * q);
@@ -317,7 +331,7 @@ k_tc_bwd(const TbArgs a) {
       const int cl_o = scl + (inB ? mp->off[6] : mp->off[2]) - e0;
       const int ds_o = sds + (inB ? mp->off[7] : mp->off[3]) - n0;
       if (row_ok) { beg = smi[rp_o + li]; deg = smi[rp_o + li + 1] - beg; di = smf[ds_o + n0 + li]; }
-      for (int t = cg; t < deg; t += 2) {
+      for (int t = cg; t < deg; t += kTbTpr) {
         const int j = smi[cl_o + beg + t];
         const bool ok = (unsigned)(j - n0) < (unsigned)ng;
         if (!ok && a.status) atomicOr(a.status, kStatusCrossEdgeTc);
@@ -329,38 +343,39 @@ k_tc_bwd(const TbArgs a) {
     const int iself = row_ok ? i : 0;
 
     // ---- P1: pooling backward . lrelu'(h2), in place in P; bias gradient of layer 2 (column owners) ---------------
-    // (a column owner's rows are four apart, so (row & 3) - the swizzle key of the planes - is one constant per
-    //  loop: element (r, pc) sits at col_at(r & 3) + 32 r)
+    // (a column owner's rows are kTbPq (4 or 8) apart, so (row & 3) - the swizzle key of the planes - is one constant
+    //  per loop: element (r, pc) sits at col_at(r & 3) + 32 r)
     auto col_at = [&](int r3) { return P + (pc >> 5) * tcb::kPlaneFloats + (((((pc & 31) >> 3) ^ r3) << 3) | (pc & 7)); };
     for (int gb = 0; gb < (nB > 0 ? 2 : 1); ++gb) {
       const int rb = gb ? nA : 0, n = gb ? nB : nA;
       const float mx = s_pool[(gb * 3 + 0) * 64 + pc];
       const float* pcol = col_at((rb + pq) & 3);
       int ties = 0, r = rb + pq;
-      for (; r + 12 < rb + n; r += 16) {
-        const float v0 = pcol[r * 32], v1 = pcol[(r + 4) * 32], v2 = pcol[(r + 8) * 32], v3 = pcol[(r + 12) * 32];
+      for (; r + 3 * kTbPq < rb + n; r += 4 * kTbPq) {
+        const float v0 = pcol[r * 32], v1 = pcol[(r + kTbPq) * 32], v2 = pcol[(r + 2 * kTbPq) * 32], v3 = pcol[(r + 3 * kTbPq) * 32];
         ties += (v0 == mx) + (v1 == mx) + (v2 == mx) + (v3 == mx);
       }
-      for (; r < rb + n; r += 4) ties += (pcol[r * 32] == mx) ? 1 : 0;
-      s_cnt[(gb * 4 + pq) * 64 + pc] = ties;
+      for (; r < rb + n; r += kTbPq) ties += (pcol[r * 32] == mx) ? 1 : 0;
+      s_cnt[(gb * kTbPq + pq) * 64 + pc] = ties;
     }
     __syncthreads();   // tie counts complete; the records above are visible
     for (int gb = 0; gb < (nB > 0 ? 2 : 1); ++gb) {
       const int rb = gb ? nA : 0, n = gb ? nB : nA;
       const float mx = s_pool[(gb * 3 + 0) * 64 + pc], gmax = s_pool[(gb * 3 + 1) * 64 + pc], gmean = s_pool[(gb * 3 + 2) * 64 + pc];
-      const int ties = s_cnt[(gb * 4 + 0) * 64 + pc] + s_cnt[(gb * 4 + 1) * 64 + pc] + s_cnt[(gb * 4 + 2) * 64 + pc] +
-                       s_cnt[(gb * 4 + 3) * 64 + pc];
+      int ties = 0;
+#pragma unroll
+      for (int u = 0; u < kTbPq; ++u) ties += s_cnt[(gb * kTbPq + u) * 64 + pc];
       const float gm = ties > 0 ? gmax / (float)ties : 0.f;
       float* pcol = col_at((rb + pq) & 3);
       int r = rb + pq;
-      for (; r + 4 < rb + n; r += 8) {
-        const float v0 = pcol[r * 32], v1 = pcol[(r + 4) * 32];
+      for (; r + kTbPq < rb + n; r += 2 * kTbPq) {
+        const float v0 = pcol[r * 32], v1 = pcol[(r + kTbPq) * 32];
         const float g0 = (gmean + (v0 == mx ? gm : 0.f)) * lrelu_grad_from_out(v0, slope);
         const float g1 = (gmean + (v1 == mx ? gm : 0.f)) * lrelu_grad_from_out(v1, slope);
-        pcol[r * 32] = g0; pcol[(r + 4) * 32] = g1;
+        pcol[r * 32] = g0; pcol[(r + kTbPq) * 32] = g1;
         b2acc += g0; b2acc += g1;
       }
-      for (; r < rb + n; r += 4) {
+      for (; r < rb + n; r += kTbPq) {
         const float v = pcol[r * 32];
         const float gg = (gmean + (v == mx ? gm : 0.f)) * lrelu_grad_from_out(v, slope);
         pcol[r * 32] = gg;
@@ -379,7 +394,7 @@ k_tc_bwd(const TbArgs a) {
     // ---- h1 -> Hh (raw) and Hl (residual of the TF32 truncation): the B operand of P3, and lrelu'(h1) for P4 -------
     {
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
+      for (int u = 0; u < kTbLd; ++u) {
         const int idx = tid + u * kTbThreads, r = idx >> 4, q = idx & 15;
         if (r < ntot) {
           const float4 v = h1v[u];
@@ -397,18 +412,18 @@ k_tc_bwd(const TbArgs a) {
     const int maxdeg = __reduce_max_sync(0xffffffffu, deg);
     const int2* nbp = reinterpret_cast<const int2*>(smi + nbo) + beg;
     auto nb_at = [&](int t) { return t < deg ? nbp[t] : make_int2(iself, 0); };
-    // gT = Â^T g over the records: this thread's 32 columns (= plane cg) of row i; self-loop last
-    auto gather_plane = [&](float (&acc)[32]) {
+    // gT = Â^T g over the records: this thread's kTbCw columns (units ub .. of plane pl) of row i; self-loop last
+    auto gather_plane = [&](float (&acc)[kTbCw]) {
 #pragma unroll
-      for (int c = 0; c < 32; ++c) acc[c] = 0.f;
+      for (int c = 0; c < kTbCw; ++c) acc[c] = 0.f;
       if (!warp_ok) return;
-      const float* src = P + cg * tcb::kPlaneFloats;
+      const float* src = P + pl * tcb::kPlaneFloats;
       auto row_fma = [&](int r, float w) {
         const float* row = src + r * 32;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {     // 32-byte units, permuted by (row & 3)
-          const float4 v0 = *reinterpret_cast<const float4*>(row + ((u ^ (r & 3)) << 3));
-          const float4 v1 = *reinterpret_cast<const float4*>(row + ((u ^ (r & 3)) << 3) + 4);
+        for (int u = 0; u < kTbUnits; ++u) {     // 32-byte units, permuted by (row & 3)
+          const float4 v0 = *reinterpret_cast<const float4*>(row + (((ub + u) ^ (r & 3)) << 3));
+          const float4 v1 = *reinterpret_cast<const float4*>(row + (((ub + u) ^ (r & 3)) << 3) + 4);
           acc[8 * u + 0] = fmaf(w, v0.x, acc[8 * u + 0]); acc[8 * u + 1] = fmaf(w, v0.y, acc[8 * u + 1]);
           acc[8 * u + 2] = fmaf(w, v0.z, acc[8 * u + 2]); acc[8 * u + 3] = fmaf(w, v0.w, acc[8 * u + 3]);
           acc[8 * u + 4] = fmaf(w, v1.x, acc[8 * u + 4]); acc[8 * u + 5] = fmaf(w, v1.y, acc[8 * u + 5]);
@@ -424,14 +439,14 @@ k_tc_bwd(const TbArgs a) {
       }
       row_fma(iself, wself);
     };
-    // row i, plane cg of an operand tile pair (raw, residual) <- acc
-    auto store_planes = [&](const float (&acc)[32]) {
+    // row i, this thread's units of an operand tile pair (raw, residual) <- acc
+    auto store_planes = [&](const float (&acc)[kTbCw]) {
       if (!warp_ok) return;
-      float* qh = Qh + cg * tcb::kPlaneFloats + i * 32;
-      float* ql = Ql + cg * tcb::kPlaneFloats + i * 32;
+      float* qh = Qh + pl * tcb::kPlaneFloats + i * 32;
+      float* ql = Ql + pl * tcb::kPlaneFloats + i * 32;
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int o = (u ^ (i & 3)) << 3;
+      for (int u = 0; u < kTbUnits; ++u) {
+        const int o = ((ub + u) ^ (i & 3)) << 3;
         *reinterpret_cast<float4*>(qh + o) = make_float4(acc[8 * u], acc[8 * u + 1], acc[8 * u + 2], acc[8 * u + 3]);
         *reinterpret_cast<float4*>(qh + o + 4) = make_float4(acc[8 * u + 4], acc[8 * u + 5], acc[8 * u + 6], acc[8 * u + 7]);
         *reinterpret_cast<float4*>(ql + o) = make_float4(acc[8 * u] - tcb::tf32_trunc(acc[8 * u]), acc[8 * u + 1] - tcb::tf32_trunc(acc[8 * u + 1]),
@@ -443,16 +458,16 @@ k_tc_bwd(const TbArgs a) {
 
     // ---- P2: gT2 = Â^T gA2 -> Q tiles (P3's A operand) and tensor memory (P4's A operand) ---------------------------
     {
-      float acc[32];
+      float acc[kTbCw];
       gather_plane(acc);
       store_planes(acc);
       if (warp_ok) {
 #pragma unroll
-        for (int cc = 0; cc < 32; cc += 16) {
+        for (int cc = 0; cc < kTbCw; cc += 16) {
           float v[16];
 #pragma unroll
           for (int q = 0; q < 16; ++q) v[q] = acc[cc + q];
-          tc::store_split16(v, a_hi, a_lo, trow, cg * 32 + cc);
+          tc::store_split16(v, a_hi, a_lo, trow, cg * kTbCw + cc);
         }
       }
     }
@@ -478,16 +493,16 @@ k_tc_bwd(const TbArgs a) {
 
     // ---- P4 epilogue: gA1 = (gT2 W2) . lrelu'(h1) -> P (own row: every gather from P is over) -------------------------
     if (warp_ok) {
-      float* prow = P + cg * tcb::kPlaneFloats + i * 32;
-      const float* hrow = Hh + cg * tcb::kPlaneFloats + i * 32;
+      float* prow = P + pl * tcb::kPlaneFloats + i * 32;
+      const float* hrow = Hh + pl * tcb::kPlaneFloats + i * 32;
 #pragma unroll
-      for (int part = 0; part < 2; ++part) {
+      for (int part = 0; part < kTbCw / 16; ++part) {
         uint32_t q0[16];
-        ptx::tmem_ld16(d_g + trow + cg * 32 + part * 16, q0);
+        ptx::tmem_ld16(d_g + trow + cg * kTbCw + part * 16, q0);
         ptx::tmem_wait_ld();
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-          const int o = (((2 * part + u) ^ (i & 3)) << 3);
+          const int o = (((ub + 2 * part + u) ^ (i & 3)) << 3);
           const float4 h0 = *reinterpret_cast<const float4*>(hrow + o), h1v = *reinterpret_cast<const float4*>(hrow + o + 4);
           float4 g0, g1;
           g0.x = __uint_as_float(q0[8 * u + 0]) * lrelu_grad_from_out(h0.x, slope);
@@ -509,9 +524,9 @@ k_tc_bwd(const TbArgs a) {
     __syncthreads();   // gA1 complete in P
 
     // x of this tile: the loads go out now and are consumed once P3 has released the H tiles
-    float xv[16];
+    float xv[kTbLx];
 #pragma unroll
-    for (int u = 0; u < 16; ++u) {
+    for (int u = 0; u < kTbLx; ++u) {
       const int idx = tid + u * kTbThreads, r = idx >> 5, c = idx & 31;
       const int64_t grow = r < nA ? (int64_t)n0A + r : (int64_t)n0B + (r - nA);
       xv[u] = (r < ntot && c < F) ? __ldg(a.b.x + grow * F + c) : 0.f;
@@ -521,10 +536,10 @@ k_tc_bwd(const TbArgs a) {
       const float* pcol = col_at(pq & 3);
       int r = pq;
       float s0 = 0.f, s1 = 0.f;
-      for (; r + 12 < ntot; r += 16) {
-        s0 += pcol[r * 32]; s1 += pcol[(r + 4) * 32]; s0 += pcol[(r + 8) * 32]; s1 += pcol[(r + 12) * 32];
+      for (; r + 3 * kTbPq < ntot; r += 4 * kTbPq) {
+        s0 += pcol[r * 32]; s1 += pcol[(r + kTbPq) * 32]; s0 += pcol[(r + 2 * kTbPq) * 32]; s1 += pcol[(r + 3 * kTbPq) * 32];
       }
-      for (; r < ntot; r += 4) s0 += pcol[r * 32];
+      for (; r < ntot; r += kTbPq) s0 += pcol[r * 32];
       b1acc += s0 + s1;
     }
 
@@ -538,7 +553,7 @@ k_tc_bwd(const TbArgs a) {
     TB_TICK(12);
     // ---- x -> Hh plane 0 (columns >= F zero) and Hl: the B operand of P7 -----------------------------------------------
 #pragma unroll
-    for (int u = 0; u < 16; ++u) {
+    for (int u = 0; u < kTbLx; ++u) {
       const int idx = tid + u * kTbThreads, r = idx >> 5, c = idx & 31;
       if (r < ntot) {
         const int o = tcb::plane_off(r, c);
@@ -549,7 +564,7 @@ k_tc_bwd(const TbArgs a) {
     TB_TICK(13);
     // ---- P6: gT1 = Â^T gA1 -> Q tiles --------------------------------------------------------------------------------
     {
-      float acc[32];
+      float acc[kTbCw];
       gather_plane(acc);
       store_planes(acc);
     }
@@ -575,21 +590,24 @@ k_tc_bwd(const TbArgs a) {
   const int pe = 64 * 64 + 64 * F + 128;
   float* out = a.b.partial + (int64_t)blockIdx.x * pe;
   if (wrow) {
-    float* o2 = out + i * 64 + cg * 32;
+    float* o2 = out + i * 64 + cg * kTbCw;
 #pragma unroll
-    for (int q = 0; q < 32; q += 4) *reinterpret_cast<float4*>(o2 + q) = make_float4(acc_w2[q], acc_w2[q + 1], acc_w2[q + 2], acc_w2[q + 3]);
+    for (int q = 0; q < kTbCw; q += 4) *reinterpret_cast<float4*>(o2 + q) = make_float4(acc_w2[q], acc_w2[q + 1], acc_w2[q + 2], acc_w2[q + 3]);
     float* o1 = out + 64 * 64 + i * F + cg * 16;
 #pragma unroll
     for (int q = 0; q < 16; ++q)
-      if (cg * 16 + q < F) o1[q] = acc_w1[q];
+      if (cg < 2 && cg * 16 + q < F) o1[q] = acc_w1[q];
   }
   __syncthreads();
   s_red[pq * 64 + pc] = b2acc;
-  s_red[256 + pq * 64 + pc] = b1acc;
+  s_red[kTbPq * 64 + pq * 64 + pc] = b1acc;
   __syncthreads();
   if (tid < 128) {
-    const float* p = s_red + (tid >> 6) * 256 + (tid & 63);
-    out[64 * 64 + 64 * F + tid] = ((p[0] + p[64]) + p[128]) + p[192];  // [b2 (64) | b1 (64)]
+    const float* p = s_red + (tid >> 6) * kTbPq * 64 + (tid & 63);
+    float sum = p[0];
+#pragma unroll
+    for (int u = 1; u < kTbPq; ++u) sum += p[u * 64];
+    out[64 * 64 + 64 * F + tid] = sum;  // [b2 (64) | b1 (64)]
   }
   ptx::tc_fence_before_sync();
   __syncthreads();
