@@ -42,6 +42,13 @@ constexpr int kTbUnits = kTbCw / 8;
 constexpr int kTbPq = kTbThreads / 64;          // row groups of the column owners (P1, P5)
 constexpr int kTbLd = 2048 / kTbThreads;        // 16-byte chunks of a 128 x 64 tile per thread
 constexpr int kTbLx = 4096 / kTbThreads;        // elements of a 128 x 32 x tile per thread
+// The gA tile (P) is no MMA operand: plain rows with a pitch of 68 floats.  A warp whose lanes are 32 consecutive rows, or
+// 32 consecutive columns of one row, reads and writes it without bank conflicts, and random neighbour rows spread over
+// eight 16-byte bank groups instead of the four 32-byte slots of the operand layout.
+#ifndef HCG_TB_PPITCH
+#define HCG_TB_PPITCH 68
+#endif
+constexpr int kTbPp = HCG_TB_PPITCH;
 static_assert(kTbThreads == 256 || kTbThreads == 512, "k_tc_bwd: two or four threads per tile row");
 
 #ifdef HCG_TC_TIMING
@@ -72,7 +79,7 @@ __host__ __device__ inline TbSmem tb_layout() {
   y.q_lo = o; o += 2 * tcb::kPlaneBytes;
   y.hx_hi = o; o += 2 * tcb::kPlaneBytes;
   y.hx_lo = o; o += 2 * tcb::kPlaneBytes;
-  y.p = o; o += 2 * tcb::kPlaneBytes;
+  y.p = o; o += (uint32_t)kTcRows * kTbPp * 4;
   y.w_hi = o; o += tc::kN * 64 * 4;
   y.w_lo = o; o += tc::kN * 64 * 4;
   y.nbr = o; o += (uint32_t)kTcEcap * 8;
@@ -115,6 +122,7 @@ k_tc_bwd(const TbArgs a) {
   const int cg = tid >> 7;            // column group: columns kTbCw cg .. + kTbCw - 1
   const int pl = (cg * kTbCw) >> 5;   // ... which sit in plane pl of the two-plane tiles,
   const int ub = ((cg * kTbCw) & 31) >> 3;   // ... from 8-float unit ub on
+  const bool hswap = ((tid >> 2) & 1) != 0;  // row-owner accesses of operand tiles: 16-byte halves in swapped order
   const int i = tid & 127;            // tile row
   const int i_warp_min = tid & 96;
   const bool ctl_warp = wslot == 3, pf_warp = wslot == 7;
@@ -291,7 +299,7 @@ k_tc_bwd(const TbArgs a) {
 #pragma unroll
       for (int u = 0; u < kTbLd; ++u) {
         const int idx = tid + u * kTbThreads, r = idx >> 4, q = idx & 15;
-        if (r < ntot) *reinterpret_cast<float4*>(P + tcb::plane_chunk_off(r, q)) = v[u];
+        if (r < ntot) *reinterpret_cast<float4*>(P + r * kTbPp + 4 * q) = v[u];
       }
     }
     if (tid < 128) {
@@ -343,19 +351,17 @@ k_tc_bwd(const TbArgs a) {
     const int iself = row_ok ? i : 0;
 
     // ---- P1: pooling backward . lrelu'(h2), in place in P; bias gradient of layer 2 (column owners) ---------------
-    // (a column owner's rows are kTbPq (4 or 8) apart, so (row & 3) - the swizzle key of the planes - is one constant
-    //  per loop: element (r, pc) sits at col_at(r & 3) + 32 r)
-    auto col_at = [&](int r3) { return P + (pc >> 5) * tcb::kPlaneFloats + (((((pc & 31) >> 3) ^ r3) << 3) | (pc & 7)); };
+    // (column owner pc: element (r, pc) sits at pcol[r kTbPp]; a warp = 32 consecutive columns of one row)
+    float* const pcol = P + pc;
     for (int gb = 0; gb < (nB > 0 ? 2 : 1); ++gb) {
       const int rb = gb ? nA : 0, n = gb ? nB : nA;
       const float mx = s_pool[(gb * 3 + 0) * 64 + pc];
-      const float* pcol = col_at((rb + pq) & 3);
       int ties = 0, r = rb + pq;
       for (; r + 3 * kTbPq < rb + n; r += 4 * kTbPq) {
-        const float v0 = pcol[r * 32], v1 = pcol[(r + kTbPq) * 32], v2 = pcol[(r + 2 * kTbPq) * 32], v3 = pcol[(r + 3 * kTbPq) * 32];
+        const float v0 = pcol[r * kTbPp], v1 = pcol[(r + kTbPq) * kTbPp], v2 = pcol[(r + 2 * kTbPq) * kTbPp], v3 = pcol[(r + 3 * kTbPq) * kTbPp];
         ties += (v0 == mx) + (v1 == mx) + (v2 == mx) + (v3 == mx);
       }
-      for (; r < rb + n; r += kTbPq) ties += (pcol[r * 32] == mx) ? 1 : 0;
+      for (; r < rb + n; r += kTbPq) ties += (pcol[r * kTbPp] == mx) ? 1 : 0;
       s_cnt[(gb * kTbPq + pq) * 64 + pc] = ties;
     }
     __syncthreads();   // tie counts complete; the records above are visible
@@ -366,19 +372,18 @@ k_tc_bwd(const TbArgs a) {
 #pragma unroll
       for (int u = 0; u < kTbPq; ++u) ties += s_cnt[(gb * kTbPq + u) * 64 + pc];
       const float gm = ties > 0 ? gmax / (float)ties : 0.f;
-      float* pcol = col_at((rb + pq) & 3);
       int r = rb + pq;
       for (; r + kTbPq < rb + n; r += 2 * kTbPq) {
-        const float v0 = pcol[r * 32], v1 = pcol[(r + kTbPq) * 32];
+        const float v0 = pcol[r * kTbPp], v1 = pcol[(r + kTbPq) * kTbPp];
         const float g0 = (gmean + (v0 == mx ? gm : 0.f)) * lrelu_grad_from_out(v0, slope);
         const float g1 = (gmean + (v1 == mx ? gm : 0.f)) * lrelu_grad_from_out(v1, slope);
-        pcol[r * 32] = g0; pcol[(r + kTbPq) * 32] = g1;
+        pcol[r * kTbPp] = g0; pcol[(r + kTbPq) * kTbPp] = g1;
         b2acc += g0; b2acc += g1;
       }
       for (; r < rb + n; r += kTbPq) {
-        const float v = pcol[r * 32];
+        const float v = pcol[r * kTbPp];
         const float gg = (gmean + (v == mx ? gm : 0.f)) * lrelu_grad_from_out(v, slope);
-        pcol[r * 32] = gg;
+        pcol[r * kTbPp] = gg;
         b2acc += gg;
       }
     }
@@ -417,13 +422,13 @@ k_tc_bwd(const TbArgs a) {
 #pragma unroll
       for (int c = 0; c < kTbCw; ++c) acc[c] = 0.f;
       if (!warp_ok) return;
-      const float* src = P + pl * tcb::kPlaneFloats;
+      const float* src = P + cg * kTbCw;
       auto row_fma = [&](int r, float w) {
-        const float* row = src + r * 32;
+        const float* row = src + r * kTbPp;
 #pragma unroll
-        for (int u = 0; u < kTbUnits; ++u) {     // 32-byte units, permuted by (row & 3)
-          const float4 v0 = *reinterpret_cast<const float4*>(row + (((ub + u) ^ (r & 3)) << 3));
-          const float4 v1 = *reinterpret_cast<const float4*>(row + (((ub + u) ^ (r & 3)) << 3) + 4);
+        for (int u = 0; u < kTbUnits; ++u) {
+          const float4 v0 = *reinterpret_cast<const float4*>(row + 8 * u);
+          const float4 v1 = *reinterpret_cast<const float4*>(row + 8 * u + 4);
           acc[8 * u + 0] = fmaf(w, v0.x, acc[8 * u + 0]); acc[8 * u + 1] = fmaf(w, v0.y, acc[8 * u + 1]);
           acc[8 * u + 2] = fmaf(w, v0.z, acc[8 * u + 2]); acc[8 * u + 3] = fmaf(w, v0.w, acc[8 * u + 3]);
           acc[8 * u + 4] = fmaf(w, v1.x, acc[8 * u + 4]); acc[8 * u + 5] = fmaf(w, v1.y, acc[8 * u + 5]);
@@ -444,15 +449,21 @@ k_tc_bwd(const TbArgs a) {
       if (!warp_ok) return;
       float* qh = Qh + pl * tcb::kPlaneFloats + i * 32;
       float* ql = Ql + pl * tcb::kPlaneFloats + i * 32;
+      // rows i and i + 4 of a quarter warp share a 32-byte slot of the operand layout: the upper one writes the two
+      // 16-byte halves in the opposite order, so the eight lanes of a store cover eight different bank groups
 #pragma unroll
       for (int u = 0; u < kTbUnits; ++u) {
         const int o = ((ub + u) ^ (i & 3)) << 3;
-        *reinterpret_cast<float4*>(qh + o) = make_float4(acc[8 * u], acc[8 * u + 1], acc[8 * u + 2], acc[8 * u + 3]);
-        *reinterpret_cast<float4*>(qh + o + 4) = make_float4(acc[8 * u + 4], acc[8 * u + 5], acc[8 * u + 6], acc[8 * u + 7]);
-        *reinterpret_cast<float4*>(ql + o) = make_float4(acc[8 * u] - tcb::tf32_trunc(acc[8 * u]), acc[8 * u + 1] - tcb::tf32_trunc(acc[8 * u + 1]),
-                                                         acc[8 * u + 2] - tcb::tf32_trunc(acc[8 * u + 2]), acc[8 * u + 3] - tcb::tf32_trunc(acc[8 * u + 3]));
-        *reinterpret_cast<float4*>(ql + o + 4) = make_float4(acc[8 * u + 4] - tcb::tf32_trunc(acc[8 * u + 4]), acc[8 * u + 5] - tcb::tf32_trunc(acc[8 * u + 5]),
-                                                             acc[8 * u + 6] - tcb::tf32_trunc(acc[8 * u + 6]), acc[8 * u + 7] - tcb::tf32_trunc(acc[8 * u + 7]));
+        const float4 lo4 = make_float4(acc[8 * u], acc[8 * u + 1], acc[8 * u + 2], acc[8 * u + 3]);
+        const float4 hi4 = make_float4(acc[8 * u + 4], acc[8 * u + 5], acc[8 * u + 6], acc[8 * u + 7]);
+        const float4 f0 = hswap ? hi4 : lo4, f1 = hswap ? lo4 : hi4;
+        const int o0 = o + (hswap ? 4 : 0), o1 = o + (hswap ? 0 : 4);
+        *reinterpret_cast<float4*>(qh + o0) = f0;
+        *reinterpret_cast<float4*>(qh + o1) = f1;
+        *reinterpret_cast<float4*>(ql + o0) = make_float4(f0.x - tcb::tf32_trunc(f0.x), f0.y - tcb::tf32_trunc(f0.y),
+                                                          f0.z - tcb::tf32_trunc(f0.z), f0.w - tcb::tf32_trunc(f0.w));
+        *reinterpret_cast<float4*>(ql + o1) = make_float4(f1.x - tcb::tf32_trunc(f1.x), f1.y - tcb::tf32_trunc(f1.y),
+                                                          f1.z - tcb::tf32_trunc(f1.z), f1.w - tcb::tf32_trunc(f1.w));
       }
     };
 
@@ -493,7 +504,7 @@ k_tc_bwd(const TbArgs a) {
 
     // ---- P4 epilogue: gA1 = (gT2 W2) . lrelu'(h1) -> P (own row: every gather from P is over) -------------------------
     if (warp_ok) {
-      float* prow = P + pl * tcb::kPlaneFloats + i * 32;
+      float* prow = P + i * kTbPp + cg * kTbCw;
       const float* hrow = Hh + pl * tcb::kPlaneFloats + i * 32;
 #pragma unroll
       for (int part = 0; part < kTbCw / 16; ++part) {
@@ -503,7 +514,9 @@ k_tc_bwd(const TbArgs a) {
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           const int o = (((ub + 2 * part + u) ^ (i & 3)) << 3);
-          const float4 h0 = *reinterpret_cast<const float4*>(hrow + o), h1v = *reinterpret_cast<const float4*>(hrow + o + 4);
+          const float4 ha = *reinterpret_cast<const float4*>(hrow + o + (hswap ? 4 : 0));   // (half order: see store_planes)
+          const float4 hb = *reinterpret_cast<const float4*>(hrow + o + (hswap ? 0 : 4));
+          const float4 h0 = hswap ? hb : ha, h1v = hswap ? ha : hb;
           float4 g0, g1;
           g0.x = __uint_as_float(q0[8 * u + 0]) * lrelu_grad_from_out(h0.x, slope);
           g0.y = __uint_as_float(q0[8 * u + 1]) * lrelu_grad_from_out(h0.y, slope);
@@ -514,8 +527,8 @@ k_tc_bwd(const TbArgs a) {
           g1.z = __uint_as_float(q0[8 * u + 6]) * lrelu_grad_from_out(h1v.z, slope);
           g1.w = __uint_as_float(q0[8 * u + 7]) * lrelu_grad_from_out(h1v.w, slope);
           if (!row_ok) { g0 = make_float4(0.f, 0.f, 0.f, 0.f); g1 = g0; }
-          *reinterpret_cast<float4*>(prow + o) = g0;
-          *reinterpret_cast<float4*>(prow + o + 4) = g1;
+          *reinterpret_cast<float4*>(prow + 8 * (2 * part + u)) = g0;
+          *reinterpret_cast<float4*>(prow + 8 * (2 * part + u) + 4) = g1;
         }
       }
     }
@@ -533,13 +546,12 @@ k_tc_bwd(const TbArgs a) {
     }
     // ---- P5: bias gradient of layer 1 (column owners) ----------------------------------------------------------------
     {
-      const float* pcol = col_at(pq & 3);
       int r = pq;
       float s0 = 0.f, s1 = 0.f;
       for (; r + 3 * kTbPq < ntot; r += 4 * kTbPq) {
-        s0 += pcol[r * 32]; s1 += pcol[(r + kTbPq) * 32]; s0 += pcol[(r + 2 * kTbPq) * 32]; s1 += pcol[(r + 3 * kTbPq) * 32];
+        s0 += pcol[r * kTbPp]; s1 += pcol[(r + kTbPq) * kTbPp]; s0 += pcol[(r + 2 * kTbPq) * kTbPp]; s1 += pcol[(r + 3 * kTbPq) * kTbPp];
       }
-      for (; r < ntot; r += kTbPq) s0 += pcol[r * 32];
+      for (; r < ntot; r += kTbPq) s0 += pcol[r * kTbPp];
       b1acc += s0 + s1;
     }
 
