@@ -559,57 +559,77 @@ k_pool(const float* __restrict__ h, const int32_t* __restrict__ graph_ptr, int64
 // Fused two-layer readout head (the default network: emb[B,128] -> 64 -> C), one launch:
 //   hid = lrelu(emb . W1^T + b1)   (optionally saved for the backward pass)
 //   out = hid . W2^T + b2
-// A block owns RO_FG = 32 graphs (512 blocks per 16384-graph batch: three to four resident per SM hide each
-// other's load -> barrier -> FMA chain); 16 x 16 threads, each a 2 (graphs) x 4 (hidden units) micro-tile;
-// the k loop runs in ascending order like k_gemm, so both produce the same bits.
+// A block owns RO_FG = 64 graphs and keeps the whole problem in shared memory - its embedding rows [64][128], W1
+// [64][132] and, afterwards, the hidden tile: one round of coalesced 16-byte loads and ONE barrier before the product
+// (the first version walked k in four load -> barrier -> FMA -> barrier rounds of 32 and was latency-bound at 27 us per
+// 16384 graphs).  16 x 16 threads, each a 4 (graphs 4 ty ..) x 4 (hidden units tx + 16 b) micro-tile fed by 16-byte
+// shared-memory reads along k; per output the k loop is ONE fmaf chain in ascending order, like k_gemm and the head of
+// k_readout2_bwd<true>, so all of them produce the same bits.
 // ==========================================================================================
 constexpr int RO_G = 64, RO_IN = 128, RO_HID = 64, RO_KC = 32;
-constexpr int RO_FG = 32;  // graphs per block of the forward head (the backward keeps RO_G)
+constexpr int RO_FG = 64;            // graphs per block of the forward head
+constexpr int RO_FW1P = RO_IN + 4;   // pitch of its W1 tile: 16-byte reads of rows tx + 16 b hit eight different bank groups
+static inline size_t ro2_fwd_smem_bytes() { return sizeof(float) * (size_t)(RO_HID * RO_FW1P + RO_FG * RO_IN + RO_FG * (RO_HID + 1)); }
 
 __device__ __forceinline__ void
 readout2_block(const float* __restrict__ emb, const float* __restrict__ W1, const float* __restrict__ b1,
                const float* __restrict__ W2, const float* __restrict__ b2, float* __restrict__ hid_save,
                float* __restrict__ out, int64_t B, int C, float slope) {
-  __shared__ __align__(16) float Es[RO_KC][RO_FG + 4];   // [k][graph]
-  __shared__ __align__(16) float Ws[RO_KC][RO_HID + 4];  // [k][unit]
-  __shared__ float Hs[RO_FG][RO_HID + 1];
+  extern __shared__ __align__(16) float rof_smem[];
+  float* W1s = rof_smem;                   // [64][132]  (unit j, input k)
+  float* Es = W1s + RO_HID * RO_FW1P;      // [64][128]  (graph g, input k)
+  float* Hs = Es + RO_FG * RO_IN;          // [64][65]   hidden tile
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int64_t g0 = (int64_t)blockIdx.x * RO_FG;
-  float acc[2][4];
+  {   // all sixteen 16-byte loads of a thread in flight at once: one memory latency, not sixteen
+    constexpr int NL = RO_HID * RO_IN / 4 / 256;   // = RO_FG * RO_IN / 4 / 256 = 8
+    static_assert(RO_FG == RO_HID, "one load count for both tiles");
+    float4 wv[NL], ev[NL];
 #pragma unroll
-  for (int a = 0; a < 2; ++a)
+    for (int u = 0; u < NL; ++u) wv[u] = ldg4(W1 + 4 * (tid + 256 * u));
+#pragma unroll
+    for (int u = 0; u < NL; ++u) {
+      const int idx = tid + 256 * u;
+      ev[u] = g0 + idx / (RO_IN / 4) < B ? ldg4(emb + g0 * RO_IN + 4 * (int64_t)idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < NL; ++u) {
+      const int idx = tid + 256 * u, j = idx / (RO_IN / 4), k4 = idx - j * (RO_IN / 4);
+      *reinterpret_cast<float4*>(W1s + j * RO_FW1P + 4 * k4) = wv[u];
+    }
+#pragma unroll
+    for (int u = 0; u < NL; ++u) reinterpret_cast<float4*>(Es)[tid + 256 * u] = ev[u];
+  }
+  __syncthreads();
+  float acc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
 #pragma unroll
     for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
-  for (int k0 = 0; k0 < RO_IN; k0 += RO_KC) {
-    for (int idx = tid; idx < RO_FG * RO_KC; idx += 256) {
-      const int r = idx / RO_KC, c = idx % RO_KC;
-      Es[c][r] = g0 + r < B ? emb[(g0 + r) * RO_IN + k0 + c] : 0.f;
-    }
-    for (int idx = tid; idx < RO_HID * RO_KC; idx += 256) {
-      const int r = idx / RO_KC, c = idx % RO_KC;
-      Ws[c][r] = W1[r * RO_IN + k0 + c];
-    }
-    __syncthreads();
-#pragma unroll 8
-    for (int kk = 0; kk < RO_KC; ++kk) {
-      const float2 e2 = *reinterpret_cast<const float2*>(&Es[kk][ty * 2]);
-      const float4 w4 = *reinterpret_cast<const float4*>(&Ws[kk][tx * 4]);
-      const float e[2] = {e2.x, e2.y}, w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll 2
+  for (int k = 0; k < RO_IN; k += 4) {
+    float4 e[4], w[4];
 #pragma unroll
-      for (int a = 0; a < 2; ++a)
+    for (int a = 0; a < 4; ++a) e[a] = *reinterpret_cast<const float4*>(Es + (4 * ty + a) * RO_IN + k);
 #pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(e[a], w[b], acc[a][b]);
-    }
-    __syncthreads();
+    for (int b = 0; b < 4; ++b) w[b] = *reinterpret_cast<const float4*>(W1s + (tx + 16 * b) * RO_FW1P + k);
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        float v = acc[a][b];
+        v = fmaf(e[a].x, w[b].x, v); v = fmaf(e[a].y, w[b].y, v); v = fmaf(e[a].z, w[b].z, v); v = fmaf(e[a].w, w[b].w, v);
+        acc[a][b] = v;
+      }
   }
 #pragma unroll
-  for (int a = 0; a < 2; ++a)
+  for (int a = 0; a < 4; ++a)
 #pragma unroll
     for (int b = 0; b < 4; ++b) {
-      const int g = ty * 2 + a, o = tx * 4 + b;
-      const float v = lrelu(acc[a][b] + b1[o], slope);
-      Hs[g][o] = v;
-      if (hid_save && g0 + g < B) hid_save[(g0 + g) * RO_HID + o] = v;
+      const int g = 4 * ty + a, j = tx + 16 * b;
+      const float v = lrelu(acc[a][b] + __ldg(b1 + j), slope);
+      Hs[g * (RO_HID + 1) + j] = v;
+      if (hid_save && g0 + g < B) hid_save[(g0 + g) * RO_HID + j] = v;
     }
   __syncthreads();
   for (int idx = tid; idx < RO_FG * C; idx += 256) {
@@ -617,8 +637,8 @@ readout2_block(const float* __restrict__ emb, const float* __restrict__ W1, cons
     if (g0 + g >= B) continue;
     float s = 0.f;
 #pragma unroll 8
-    for (int o = 0; o < RO_HID; ++o) s = fmaf(Hs[g][o], W2[c * RO_HID + o], s);
-    out[(g0 + g) * C + c] = s + b2[c];
+    for (int o = 0; o < RO_HID; ++o) s = fmaf(Hs[g * (RO_HID + 1) + o], __ldg(W2 + c * RO_HID + o), s);
+    out[(g0 + g) * C + c] = s + __ldg(b2 + c);
   }
 }
 
@@ -1250,8 +1270,10 @@ static int run_readout(const HcgParams* p, const float* emb, float* out, const H
   if (p->R == 2 && 2 * p->H == RO_IN && B > 0) {
     float* hs = saved ? saved->hid[0] : nullptr;
     if (saved) HCG_REQUIRE(hs != nullptr, HCG_ERR_INVALID_ARG, "saved->hid[0] is NULL");
-    k_readout2<<<(unsigned)cdiv(B, RO_FG), 256, 0, st>>>(emb, p->ro_w[0], p->ro_b[0], p->ro_w[1], p->ro_b[1], hs, out, B,
-                                                        p->C, p->slope);
+    static SmemConfigured configured;
+    if (int rc = ensure_dyn_smem(k_readout2, ro2_fwd_smem_bytes(), configured)) return rc;
+    k_readout2<<<(unsigned)cdiv(B, RO_FG), 256, ro2_fwd_smem_bytes(), st>>>(emb, p->ro_w[0], p->ro_b[0], p->ro_w[1], p->ro_b[1], hs,
+                                                                           out, B, p->C, p->slope);
     HCG_LAUNCH_OK(st, "k_readout2");
     return HCG_OK;
   }
@@ -1544,8 +1566,10 @@ extern "C" int hcg_gcn_forward_coo_ensemble(const float* x, const int64_t* edge_
   rc = launch_tc_fwd_ens(x, edge_index, node_ptr, edge_ptr, N, E, B, ens->M, ens->F, ens->slope, fill, ens->conv_w0, ens->conv_b0,
                          ens->conv_w1, ens->conv_b1, w.wimg, emb, w.tc, st);
   if (rc) return rc;
-  k_readout2_ens<<<dim3((unsigned)cdiv(B, RO_FG), (unsigned)ens->M), 256, 0, st>>>(emb, ens->ro_w0, ens->ro_b0, ens->ro_w1, ens->ro_b1,
-                                                                                  out, B, ens->C, ens->slope);
+  static SmemConfigured ro_configured;
+  if (int rc2 = ensure_dyn_smem(k_readout2_ens, ro2_fwd_smem_bytes(), ro_configured)) return rc2;
+  k_readout2_ens<<<dim3((unsigned)cdiv(B, RO_FG), (unsigned)ens->M), 256, ro2_fwd_smem_bytes(), st>>>(
+      emb, ens->ro_w0, ens->ro_b0, ens->ro_w1, ens->ro_b1, out, B, ens->C, ens->slope);
   HCG_LAUNCH_OK(st, "k_readout2_ens");
   return HCG_OK;
 }

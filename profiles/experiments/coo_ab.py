@@ -23,3 +23,7 @@ for rep in range(3):
     e1.record(); torch.cuda.synchronize()
     res.append(e0.elapsed_time(e1) / 40)
 print(os.environ.get("HCG_LIB_PATH", "default"), ["%.4f" % r for r in res])
+_lib.profile_enable(True)
+for i in range(8): fn(i)
+torch.cuda.synchronize()
+print({k: round(v[0] / v[1] * 1e3, 1) for k, v in _lib.profile_read().items()})
