@@ -698,13 +698,24 @@ k_readout2_bwd(const float* __restrict__ emb, const float* __restrict__ hid, con
   const int64_t g0 = (int64_t)blockIdx.x * RO_G;
   float* part = partial + (int64_t)blockIdx.x * ro2_partial_stride(C);
 
-  for (int idx = tid; idx < RO_HID * RO_IN / 4; idx += 256) {
-    const int j = idx / (RO_IN / 4), k4 = idx - j * (RO_IN / 4);
-    *reinterpret_cast<float4*>(W1s + j * RO_W1P + 4 * k4) = ldg4(W1 + 4 * idx);
-  }
-  for (int idx = tid; idx < RO_G * RO_IN / 4; idx += 256) {
-    const int g = idx / (RO_IN / 4);
-    reinterpret_cast<float4*>(Es)[idx] = g0 + g < B ? ldg4(emb + g0 * RO_IN + 4 * (int64_t)idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+  {   // all sixteen 16-byte loads of a thread in flight at once: one memory latency, not sixteen
+    constexpr int NL = RO_HID * RO_IN / 4 / 256;   // = RO_G * RO_IN / 4 / 256 = 8
+    static_assert(RO_G == RO_HID, "one load count for both tiles");
+    float4 wv[NL], ev[NL];
+#pragma unroll
+    for (int u = 0; u < NL; ++u) wv[u] = ldg4(W1 + 4 * (tid + 256 * u));
+#pragma unroll
+    for (int u = 0; u < NL; ++u) {
+      const int idx = tid + 256 * u;
+      ev[u] = g0 + idx / (RO_IN / 4) < B ? ldg4(emb + g0 * RO_IN + 4 * (int64_t)idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < NL; ++u) {
+      const int idx = tid + 256 * u, j = idx / (RO_IN / 4), k4 = idx - j * (RO_IN / 4);
+      *reinterpret_cast<float4*>(W1s + j * RO_W1P + 4 * k4) = wv[u];
+    }
+#pragma unroll
+    for (int u = 0; u < NL; ++u) reinterpret_cast<float4*>(Es)[tid + 256 * u] = ev[u];
   }
   if (!TRAIN)
     for (int idx = tid; idx < RO_G * C; idx += 256) Go[idx] = g0 + idx / C < B ? g_out[g0 * C + idx] : 0.f;
@@ -716,17 +727,21 @@ k_readout2_bwd(const float* __restrict__ emb, const float* __restrict__ hid, con
     for (int a = 0; a < 4; ++a)
 #pragma unroll
       for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
-#pragma unroll 4
-    for (int k = 0; k < RO_IN; ++k) {
-      float e[4], w[4];
+#pragma unroll 2
+    for (int k = 0; k < RO_IN; k += 4) {   // 16-byte reads along k; per output still one chain in ascending k
+      float4 e[4], w[4];
 #pragma unroll
-      for (int a = 0; a < 4; ++a) e[a] = Es[(4 * ty + a) * RO_IN + k];
+      for (int a = 0; a < 4; ++a) e[a] = *reinterpret_cast<const float4*>(Es + (4 * ty + a) * RO_IN + k);
 #pragma unroll
-      for (int b = 0; b < 4; ++b) w[b] = W1s[(tx + 16 * b) * RO_W1P + k];
+      for (int b = 0; b < 4; ++b) w[b] = *reinterpret_cast<const float4*>(W1s + (tx + 16 * b) * RO_W1P + k);
 #pragma unroll
       for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(e[a], w[b], acc[a][b]);
+        for (int b = 0; b < 4; ++b) {
+          float v = acc[a][b];
+          v = fmaf(e[a].x, w[b].x, v); v = fmaf(e[a].y, w[b].y, v); v = fmaf(e[a].z, w[b].z, v); v = fmaf(e[a].w, w[b].w, v);
+          acc[a][b] = v;
+        }
     }
 #pragma unroll
     for (int a = 0; a < 4; ++a)
