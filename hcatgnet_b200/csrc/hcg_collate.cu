@@ -434,22 +434,23 @@ __device__ __forceinline__ void grp_build(const int64_t* __restrict__ rowkey, co
 //      block-wide barriers, eight graphs in flight per CTA ----------------------------------------
 constexpr int kWgNodes = 256, kWgEdges = 512, kWgWarps = 4;
 
-// A slot is one word: (edge number inside the slice) << 16 | (value node - n0).  Both fit 16 bits for an
-// accepted graph (<= kWgEdges edges, <= kWgNodes nodes); sorting the words sorts a row by edge order.
-__device__ __forceinline__ void wg_build(const int64_t* __restrict__ rowkey, const int64_t* __restrict__ val, int e_lo,
-                                         int e_cnt, int n0, int n, int* cnt, int* rp, unsigned* slot,
-                                         int32_t* __restrict__ rowptr_out, int32_t* __restrict__ col_out,
-                                         int32_t* __restrict__ eid_out, float* __restrict__ dis_out, float fill,
-                                         int64_t N, int* check_status) {
+// The graph's edges are staged ONCE in registers (lane l holds edges l, l + 32, ...; sixteen 64-bit loads in flight
+// at a time instead of one per loop trip) as words (dst - n0) << 16 | (src - n0) with a bit per edge for "key inside the
+// graph"; both CSR directions are then built from the registers.
+constexpr int kWgPer = kWgEdges / 32;   // staged edges per lane
+
+__device__ __forceinline__ void wg_build(const unsigned (&pk)[kWgPer], unsigned okmask, bool by_src, int e_lo, int e_cnt, int n0,
+                                         int n, int* cnt, int* rp, unsigned* slot, int32_t* __restrict__ rowptr_out,
+                                         int32_t* __restrict__ col_out, int32_t* __restrict__ eid_out,
+                                         float* __restrict__ dis_out, float fill) {
   const int lane = threadIdx.x & 31;
   constexpr int PER = kWgNodes / 32;
-  const int64_t* __restrict__ rk = rowkey + e_lo;
-  const int64_t* __restrict__ vl = val + e_lo;
   for (int i = lane; i < n; i += 32) cnt[i] = 0;
   __syncwarp();
-  for (int k = lane; k < e_cnt; k += 32) {
-    const int64_t key = rk[k];
-    if ((uint64_t)(key - n0) < (uint64_t)n) atomicAdd(&cnt[(int)(key - n0)], 1);
+#pragma unroll
+  for (int q = 0; q < kWgPer; ++q) {
+    const int key = by_src ? (int)(pk[q] & 0xffffu) : (int)(pk[q] >> 16);
+    if (lane + 32 * q < e_cnt && (okmask >> q & 1u)) atomicAdd(&cnt[key], 1);
   }
   __syncwarp();
   int local[PER], sum = 0;
@@ -484,12 +485,16 @@ __device__ __forceinline__ void wg_build(const int64_t* __restrict__ rowkey, con
     cnt[i] = b;  // cursor of the row from here on
   }
   __syncwarp();
-  for (int k = lane; k < e_cnt; k += 32) {
-    const int64_t key = rk[k], v = vl[k];
-    if (check_status) grp_check_edge(v, key, n0, n, N, check_status);  // by-dst pass: key = dst, v = src
-    if ((uint64_t)(key - n0) >= (uint64_t)n) continue;
-    const int pos = atomicAdd(&cnt[(int)(key - n0)], 1);
-    slot[pos] = ((unsigned)k << 16) | ((unsigned)(v - n0) & 0xffffu);
+  // A slot is one word: (edge number inside the slice) << 16 | (value node - n0).  Both fit 16 bits for an
+  // accepted graph (<= kWgEdges edges, <= kWgNodes nodes); sorting the words sorts a row by edge order.
+#pragma unroll
+  for (int q = 0; q < kWgPer; ++q) {
+    const int k = lane + 32 * q;
+    if (k >= e_cnt || !(okmask >> q & 1u)) continue;
+    const int key = by_src ? (int)(pk[q] & 0xffffu) : (int)(pk[q] >> 16);
+    const unsigned v = by_src ? pk[q] >> 16 : pk[q] & 0xffffu;
+    const int pos = atomicAdd(&cnt[key], 1);
+    slot[pos] = ((unsigned)k << 16) | v;
   }
   __syncwarp();
   for (int i = lane; i < n; i += 32) {  // insertion sort by edge number inside each row
@@ -512,7 +517,7 @@ __device__ __forceinline__ void wg_build(const int64_t* __restrict__ rowkey, con
   __syncwarp();
 }
 
-__global__ void __launch_bounds__(kWgWarps * 32, 12)
+__global__ void __launch_bounds__(kWgWarps * 32, 8)
 k_collate_graph_warp(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, int64_t E, int64_t N, int64_t B,
                      const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ eptr, float fill,
                      int32_t* __restrict__ rowptr, int32_t* __restrict__ col, int32_t* __restrict__ eid,
@@ -536,9 +541,31 @@ k_collate_graph_warp(const int64_t* __restrict__ src, const int64_t* __restrict_
       if (lane == 0) atomicAdd(big_count, 1);  // left to the block-per-graph kernel
       continue;
     }
-    wg_build(dst, src, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot[w], rowptr, col, eid, dis, fill, N, status);
-    if (t_rowptr)
-      wg_build(src, dst, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot[w], t_rowptr, t_col, t_eid, nullptr, fill, N, nullptr);
+    unsigned pk[kWgPer], okd = 0u, oks = 0u;
+#pragma unroll
+    for (int h = 0; h < kWgPer; h += 8) {   // eight edges of the lane = sixteen loads in flight
+      int64_t sv[8], dv[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const int k = lane + 32 * (h + q);
+        sv[q] = k < e_cnt ? __ldg(src + e_lo + k) : 0;
+        dv[q] = k < e_cnt ? __ldg(dst + e_lo + k) : 0;
+      }
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const int k = lane + 32 * (h + q);
+        pk[h + q] = 0u;
+        if (k < e_cnt) {
+          grp_check_edge(sv[q], dv[q], n0, n, N, status);
+          const int64_t sr = sv[q] - n0, dr = dv[q] - n0;
+          if ((uint64_t)dr < (uint64_t)n) okd |= 1u << (h + q);
+          if ((uint64_t)sr < (uint64_t)n) oks |= 1u << (h + q);
+          pk[h + q] = ((unsigned)dr & 0xffffu) << 16 | ((unsigned)sr & 0xffffu);
+        }
+      }
+    }
+    wg_build(pk, okd, false, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot[w], rowptr, col, eid, dis, fill);
+    if (t_rowptr) wg_build(pk, oks, true, e_lo, e_cnt, n0, n, cnt[w], rp[w], slot[w], t_rowptr, t_col, t_eid, nullptr, fill);
   }
 }
 
