@@ -37,13 +37,23 @@ __device__ __forceinline__ int w_tile_offset(int n, int k) {
 // padded to Kpad (32 or 64).  Cooperative over `nthreads` threads; tiles must be 1024-B aligned.
 __device__ __forceinline__ void prep_weight_tiles(const float* __restrict__ W, int Kin, int Kpad, float* s_hi,
                                                   float* s_lo, int tid, int nthreads) {
-  for (int idx = tid; idx < kN * Kpad; idx += nthreads) {
-    const int n = idx / Kpad, k = idx - n * Kpad;
-    const float v = k < Kin ? __ldg(W + n * Kin + k) : 0.f;
-    const uint32_t hi = tf32_hi(v), lo = tf32_lo(v, hi);
-    const int off = w_tile_offset(n, k);
-    s_hi[off] = __uint_as_float(hi);
-    s_lo[off] = __uint_as_float(lo);
+  constexpr int U = 4;   // loads of a thread in flight at once (the loop is a chain of memory latencies otherwise)
+  for (int base = tid; base < kN * Kpad; base += U * nthreads) {
+    float v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int idx = base + u * nthreads, n = idx / Kpad, k = idx - n * Kpad;
+      v[u] = idx < kN * Kpad && k < Kin ? __ldg(W + n * Kin + k) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int idx = base + u * nthreads, n = idx / Kpad, k = idx - n * Kpad;
+      if (idx >= kN * Kpad) break;
+      const uint32_t hi = tf32_hi(v[u]), lo = tf32_lo(v[u], hi);
+      const int off = w_tile_offset(n, k);
+      s_hi[off] = __uint_as_float(hi);
+      s_lo[off] = __uint_as_float(lo);
+    }
   }
 }
 

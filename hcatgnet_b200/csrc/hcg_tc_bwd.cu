@@ -96,13 +96,20 @@ __host__ __device__ inline TbSmem tb_layout() {
 // W: global [64][64] (state_dict layout [out o][in i]).  Tiles of W^T for  D[r][i] = sum_o A[r][o] W[o][i]:
 // tile element (n = i, k = o) = W[o][i].
 __device__ __forceinline__ void prep_weight_tiles_t(const float* __restrict__ W, float* s_hi, float* s_lo, int tid, int nthreads) {
-  for (int idx = tid; idx < 64 * 64; idx += nthreads) {
-    const int o = idx >> 6, i = idx & 63;            // coalesced read of W[o][i]
-    const float v = __ldg(W + idx);
-    const uint32_t hi = tc::tf32_hi(v), lo = tc::tf32_lo(v, hi);
-    const int off = tc::w_tile_offset(i, o);
-    s_hi[off] = __uint_as_float(hi);
-    s_lo[off] = __uint_as_float(lo);
+  constexpr int U = 4;   // loads of a thread in flight at once
+  for (int base = tid; base < 64 * 64; base += U * nthreads) {
+    float v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = base + u * nthreads < 64 * 64 ? __ldg(W + base + u * nthreads) : 0.f;   // coalesced read of W[o][i]
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int idx = base + u * nthreads, o = idx >> 6, i = idx & 63;
+      if (idx >= 64 * 64) break;
+      const uint32_t hi = tc::tf32_hi(v[u]), lo = tc::tf32_lo(v[u], hi);
+      const int off = tc::w_tile_offset(i, o);
+      s_hi[off] = __uint_as_float(hi);
+      s_lo[off] = __uint_as_float(lo);
+    }
   }
 }
 
