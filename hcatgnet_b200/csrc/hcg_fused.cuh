@@ -70,7 +70,9 @@ int gcn_forward_coo_saved(const float* x, const int64_t* edge_index, const int64
 // the next hcg_gcn_backward of the calling thread makes its stream wait for `ev` after the readout part, before the
 // first kernel that reads the graph arrays (rowptr / col / dis / transposed CSR)
 // (`side`: the stream `ev` was recorded on; the tensor-core backward builds its work list there too and re-records `ev`)
-void set_backward_prereq(cudaEvent_t ev, cudaStream_t side = nullptr);
+// (`node_ptr` / `edge_ptr`: the batch's int64 offset vectors; with them the tensor-core backward builds its work list on its
+//  own stream before it waits for `ev` - the list then needs nothing the other stream produces)
+void set_backward_prereq(cudaEvent_t ev, cudaStream_t side = nullptr, const int64_t* node_ptr = nullptr, const int64_t* edge_ptr = nullptr);
 
 // The head of a training step in one kernel + reduce (hcg_net.cu): forward of the default readout, loss seed
 // (tail = [sum (out - y)^2, B C]) and its backward: g_emb [B, 2H] and the readout gradients into `grads`.
@@ -130,6 +132,7 @@ int launch_fused_bwd(FusedBwdArgs a, int64_t N, float* g_w2, float* g_w1, float*
 int tc_bwd_grid(int64_t B);
 size_t tc_bwd_workspace_bytes(int64_t B);
 int launch_tc_bwd(FusedBwdArgs a, int64_t N, int64_t E, void* ws, bool all_fit, float* g_w2, float* g_w1, float* g_b2, float* g_b1,
-                  cudaStream_t st, cudaStream_t desc_st = nullptr, cudaEvent_t desc_ev = nullptr);
+                  cudaStream_t st, cudaStream_t desc_st = nullptr, cudaEvent_t desc_ev = nullptr, const int64_t* node_ptr64 = nullptr,
+                  const int64_t* edge_ptr64 = nullptr);
 
 }  // namespace hcg

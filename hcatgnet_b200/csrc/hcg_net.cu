@@ -1643,10 +1643,15 @@ extern "C" int hcg_gcn_forward_coo_static(const float* x, const int64_t* edge_in
 // event the NEXT hcg_gcn_backward of this thread waits for before it reads the graph arrays (set by hcg_train_step)
 static thread_local cudaEvent_t g_backward_prereq = nullptr;
 static thread_local cudaStream_t g_backward_side = nullptr;
+static thread_local const int64_t* g_backward_node_ptr = nullptr;   // the batch's int64 offset vectors (training step)
+static thread_local const int64_t* g_backward_edge_ptr = nullptr;
 static thread_local bool g_backward_keep_readout = false;
 // the next hcg_gcn_backward of this thread (called with g_out == NULL) leaves the readout gradients as they are
 void hcg::set_backward_keep_readout_grads(bool keep) { g_backward_keep_readout = keep; }
-void hcg::set_backward_prereq(cudaEvent_t ev, cudaStream_t side) { g_backward_prereq = ev; g_backward_side = ev ? side : nullptr; }
+void hcg::set_backward_prereq(cudaEvent_t ev, cudaStream_t side, const int64_t* node_ptr, const int64_t* edge_ptr) {
+  g_backward_prereq = ev; g_backward_side = ev ? side : nullptr;
+  g_backward_node_ptr = ev ? node_ptr : nullptr; g_backward_edge_ptr = ev ? edge_ptr : nullptr;
+}
 
 extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgParams* p, const HcgSaved* saved,
                                 const float* emb, const float* g_out, const float* g_emb,
@@ -1727,7 +1732,9 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
   //  or - tensor-core path - after the backward's work list has been built on that stream as well)
   const cudaEvent_t side_ev = g_backward_prereq;
   const cudaStream_t side_st = g_backward_side;
-  g_backward_prereq = nullptr; g_backward_side = nullptr;
+  const int64_t* const np64 = g_backward_node_ptr;
+  const int64_t* const ep64 = g_backward_edge_ptr;
+  g_backward_prereq = nullptr; g_backward_side = nullptr; g_backward_node_ptr = nullptr; g_backward_edge_ptr = nullptr;
   bool joined = side_ev == nullptr;
   auto join_side = [&]() -> int {
     if (!joined) { joined = true; HCG_CUDA_OK(cudaStreamWaitEvent(st, side_ev, 0)); }
@@ -1754,7 +1761,7 @@ extern "C" int hcg_gcn_backward(const HcgGraph* g, const float* x, const HcgPara
         if (!joined) {   // the work list goes out on the second stream, behind the collate; `st` joins after it
           joined = true;
           return launch_tc_bwd(a, N, g->E, w.tcb, all_fit, grads->conv_w[1], grads->conv_w[0], grads->conv_b[1], grads->conv_b[0], st,
-                               side_st, side_ev);
+                               side_st, side_ev, np64, ep64);
         }
         return launch_tc_bwd(a, N, g->E, w.tcb, all_fit, grads->conv_w[1], grads->conv_w[0], grads->conv_b[1], grads->conv_b[0], st);
       }

@@ -203,6 +203,10 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
   // packed mode: the same, for the kernel variant that reads a packed graph image (byte-granular slices of 64-byte
   // aligned sections: no copy window can leave the image, no tile is flagged for ordinary loads)
   const bool coo = ei != nullptr || packed != 0;
+  // CSR mode with the batch's int64 offset vectors (the training step's backward): the same tiles as from graph_ptr and
+  // rowptr[graph_ptr[g]] - for a batch the collate accepts they hold the same numbers - without reading the collate's
+  // outputs, so the work list does not have to wait for the collate
+  const bool ptr64 = !coo && node_ptr64 != nullptr && edge_ptr64 != nullptr;
   int refused = 0;
   TcTile* out = tiles + (size_t)slot * cap;
   int total = 0;
@@ -218,7 +222,7 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
     for (int k = 0; k <= kTcWinMax; ++k) {
       gp[k] = 0;
       if (live && k <= wcnt) {
-        if (coo) {
+        if (coo || ptr64) {
           const int64_t v = node_ptr64[g0 + k];
           gp[k] = (int)v;
           if (v < 0 || v > N) { gp[k] = 0; refused |= kCooBadOffsets; }
@@ -231,7 +235,7 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
     for (int k = 0; k <= kTcWinMax; ++k) {
       ee[k] = 0;
       if (live && k <= wcnt) {
-        if (coo) {
+        if (coo || ptr64) {
           const int64_t v = edge_ptr64[g0 + k];
           ee[k] = (int)v;
           if (v < 0 || v > E) { ee[k] = 0; refused |= kCooBadOffsets; }
@@ -1062,11 +1066,11 @@ size_t tc_tiles_capacity(int64_t B) {
 
 int launch_tile_desc(const int32_t* graph_ptr, const int32_t* rowptr, const int32_t* col, const float* dis, const float* x, int F,
                      int64_t N, int64_t E, int64_t B, const TcPlan& p, TcTile* tiles, int* counts, int* overflow_count,
-                     int* overflow_list, cudaStream_t st, int* overflow_flag) {
+                     int* overflow_list, cudaStream_t st, int* overflow_flag, const int64_t* node_ptr64, const int64_t* edge_ptr64) {
   HCG_CUDA_OK(cudaMemsetAsync(overflow_count, 0, sizeof(int), st));
   k_tile_desc<<<(unsigned)cdiv((int64_t)p.nslots * 32, 128), 128, 0, st>>>(graph_ptr, rowptr, col, dis, x, F, N, E, B, p.W, p.nslots,
                                                                           p.nwin, p.cap, tiles, counts, overflow_count, overflow_list,
-                                                                          overflow_flag, nullptr, nullptr, nullptr, nullptr, nullptr, 0);
+                                                                          overflow_flag, node_ptr64, edge_ptr64, nullptr, nullptr, nullptr, 0);
   HCG_LAUNCH_OK(st, "k_tile_desc");
   return HCG_OK;
 }

@@ -648,7 +648,7 @@ size_t tc_bwd_workspace_bytes(int64_t B) {
 // `a.partial` has room for tc_bwd_grid(B) + fused_bwd_grid(B) rows of 64*64 + 64*F + 128 floats: the tensor-core CTAs
 // write the first rows, the overflow kernel the rest; both are summed by k_fused_bwd_reduce.
 int launch_tc_bwd(FusedBwdArgs a, int64_t N, int64_t E, void* ws, bool all_fit, float* g_w2, float* g_w1, float* g_b2, float* g_b1,
-                  cudaStream_t st, cudaStream_t desc_st, cudaEvent_t desc_ev) {
+                  cudaStream_t st, cudaStream_t desc_st, cudaEvent_t desc_ev, const int64_t* node_ptr64, const int64_t* edge_ptr64) {
   if (a.B <= 0) return HCG_OK;
   Carver c(ws, (size_t)-1);
   TcTile* tiles = c.take<TcTile>(tc_tiles_capacity(a.B));
@@ -657,10 +657,14 @@ int launch_tc_bwd(FusedBwdArgs a, int64_t N, int64_t E, void* ws, bool all_fit, 
   int* overflow_list = c.take<int>((size_t)a.B + 1);
   int* overflow_flag = c.take<int>((size_t)a.B + 1);
   const TcPlan p = tc_plan(a.B, 1);
-  // desc_st / desc_ev: the work list is built on another stream (the one that produced the transposed CSR), `st` joins it
-  const bool side = desc_st != nullptr && desc_ev != nullptr;
+  // desc_st / desc_ev: the work list is built on another stream (the one that produced the transposed CSR), `st` joins it.
+  // With the batch's int64 offset vectors the work list needs nothing of the collate: it goes out on `st` BEFORE `st`
+  // waits for the other stream (desc_ev), i.e. beside the collate instead of behind it.
+  const bool ptr64 = node_ptr64 != nullptr && edge_ptr64 != nullptr;
+  const bool side = !ptr64 && desc_st != nullptr && desc_ev != nullptr;
   const int rc_desc = launch_tile_desc(a.graph_ptr, a.t_rowptr, a.t_col, a.dis, a.x, a.F, N, E, a.B, p, tiles, counts, overflow_count,
-                                       overflow_list, side ? desc_st : st, overflow_flag);
+                                       overflow_list, side ? desc_st : st, overflow_flag, ptr64 ? node_ptr64 : nullptr,
+                                       ptr64 ? edge_ptr64 : nullptr);
   if (side) {
     HCG_CUDA_OK(cudaEventRecord(desc_ev, desc_st));
     HCG_CUDA_OK(cudaStreamWaitEvent(st, desc_ev, 0));

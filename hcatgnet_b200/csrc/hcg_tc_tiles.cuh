@@ -64,7 +64,8 @@ size_t tc_tiles_capacity(int64_t B);
 // builds the per-slot tile lists + overflow list (rowptr / col: the CSR the kernel will copy slices of)
 int launch_tile_desc(const int32_t* graph_ptr, const int32_t* rowptr, const int32_t* col, const float* dis, const float* x, int F,
                      int64_t N, int64_t E, int64_t B, const TcPlan& p, TcTile* tiles, int* counts, int* overflow_count,
-                     int* overflow_list, cudaStream_t st, int* overflow_flag = nullptr);   // flag[g] = 1: graph g is on the list
+                     int* overflow_list, cudaStream_t st, int* overflow_flag = nullptr,   // flag[g] = 1: graph g is on the list
+                     const int64_t* node_ptr64 = nullptr, const int64_t* edge_ptr64 = nullptr);   // offsets from the batch's own vectors
 
 // workspace of the edge-list variants: work list + per-slot refusal flags
 struct TcCooWs {

@@ -228,7 +228,7 @@ extern "C" int hcg_train_step(const float* x, const int64_t* edge_index, int64_t
       cudaStreamWaitEvent(main_st, side->join, 0);          // nothing of this call may outlive it out of stream order
       return rc;
     }
-    set_backward_prereq(side->join, side->st);
+    set_backward_prereq(side->join, side->st, node_ptr, edge_ptr);
   } else {
     rc = hcg_collate_offsets(edge_index, E, node_ptr, edge_ptr, N, B, fill, HCG_COLLATE_TRANSPOSE, max_graph_nodes, max_graph_edges,
                              w.rowptr, w.col, w.eid, w.dis, w.graph_ptr, w.t_rowptr, w.t_col, w.t_eid, w.collate, w.collate_bytes, stream);
