@@ -929,7 +929,6 @@ k_tc_fwd(const TcArgs a) {
       if (ctl_warp) ptx::mbar_wait(&bar_mma[slot], mma_phase);      // one warp polls; the others sleep in the barrier below
       mma_phase ^= 1u;
       TC_TICK(5);
-      if (SAVE && cg == 0) ptx::bulk_wait_read();   // (training forward) the saved rows have left the activation buffer
       ptx::named_bar_sync(bar_full, kSlotThreads);
       ptx::tc_fence_after_sync();
       if (l == 0 && pf_warp) issue(k + 1, true);   // every layer-0 gather of the slot is over: the x stage is free
@@ -958,12 +957,20 @@ k_tc_fwd(const TcArgs a) {
       }
       TC_TICK(7);
       const bool saving = SAVE && a.f.save_act[l] != nullptr;
-      if (saving) ptx::fence_proxy_async_smem();   // the rows are read by the bulk copies below (async proxy)
       ptx::tc_fence_before_sync();
       ptx::named_bar_sync(bar_full, kSlotThreads);  // h complete in shared memory; D may be overwritten
-      if (saving && cg == 0 && row_ok) {
-        ptx::bulk_s2g(a.f.save_act[l] + ((int64_t)n0 + li) * 64, smf + hb_w + i * HP, 256);
-        ptx::bulk_commit();
+      if (saving) {
+        // (training forward) the finished rows -> global memory in 16-byte chunks, sixteen lanes per row: a warp writes two
+        // whole rows per instruction.  (One 256-byte bulk copy per row costs ~21 issue cycles in the copy engine - 2 700
+        // per layer and tile, shared by the two slots; these are eight plain loads and stores per thread.)  The activation
+        // buffer is next WRITTEN by the following epilogue, after a barrier every thread passes behind this loop.
+        float* const dst = a.f.save_act[l];
+        const int n0A_s = mp->n0A, n0B_s = mp->n0B;
+        for (int idx = gt; idx < ntot * 16; idx += kSlotThreads) {
+          const int r = idx >> 4, q = idx & 15;
+          const int64_t grow = r < nA ? (int64_t)n0A_s + r : (int64_t)n0B_s + (r - nA);
+          __stcs(reinterpret_cast<float4*>(dst + grow * 64 + 4 * q), *reinterpret_cast<const float4*>(smf + hb_w + r * HP + 4 * q));
+        }
       }
       TC_TICK(8);
 
@@ -1020,7 +1027,6 @@ k_tc_fwd(const TcArgs a) {
     TC_TICK(10);
   }
   if (p_gA >= 0) pool_tile(p_gA, p_gB, p_nA, p_nB);
-  if (SAVE) ptx::bulk_wait_all();
 
   ptx::tc_fence_before_sync();
   __syncthreads();

@@ -20,4 +20,4 @@ _lib.profile_enable(True)
 for i in range(8): trainer.step(pool[i % 4])
 torch.cuda.synchronize()
 pr = _lib.profile_read()
-print(os.environ.get("HCG_LIB_PATH", "default"), ["%.4f" % r for r in res], {k: round(v[0] / v[1] * 1e3) for k, v in pr.items() if "bwd" in k or "readout" in k or "collate" in k})
+print(os.environ.get("HCG_LIB_PATH", "default"), ["%.4f" % r for r in res], {k: round(v[0] / v[1] * 1e3) for k, v in pr.items() if "tc_" in k or "readout" in k or "collate" in k})
