@@ -659,6 +659,21 @@ k_tc_fwd(const TcArgs a) {
     }
   };
   int p_gA = -1, p_gB = -1, p_nA = 0, p_nB = 0;   // the tile whose last-layer rows sit in the activation buffer, not yet pooled
+  int p_n0A = 0, p_n0B = 0;
+  // (training forward) the rows of a finished layer -> global memory, from the activation buffer, in 16-byte chunks with
+  // sixteen lanes per row: a warp writes two whole rows per instruction.  (One 256-byte bulk copy per row costs ~21 issue
+  // cycles in the copy engine - 2 700 per layer and tile, shared by the two slots.)  Runs one MMA window late, like the
+  // pooling: the buffer keeps the rows until the next epilogue, which every thread reaches through a barrier behind this.
+  auto save_rows = [&](int layer, int nA_, int nB_, int n0A_, int n0B_) {
+    float* const dst = a.f.save_act[layer];
+    if (dst == nullptr) return;
+    const int nt = nA_ + nB_;
+    for (int idx = gt; idx < nt * 16; idx += kSlotThreads) {
+      const int r = idx >> 4, q = idx & 15;
+      const int64_t grow = r < nA_ ? (int64_t)n0A_ + r : (int64_t)n0B_ + (r - nA_);
+      __stcs(reinterpret_cast<float4*>(dst + grow * 64 + 4 * q), *reinterpret_cast<const float4*>(smf + hb_w + r * HP + 4 * q));
+    }
+  };
 
   // PK: the x rows of a tile, expanded from the staged bit / byte / f32 slices of stage `st` into dense fp32 rows of the
   // slot's x buffer.  Runs at the top of a tile, or - from the second conv layer on - a tile EARLY, inside the previous
@@ -721,6 +736,7 @@ k_tc_fwd(const TcArgs a) {
       fetch_rec(k + 2);
     }
     const int nA = mp->nA, nB = mp->nB, gB = mp->gB, eA = mp->eA;   // (stage s's record is rewritten during tile k + 1)
+    const int n0A_t = mp->n0A, n0B_t = mp->n0B;
     const int ntot = nA + nB;
     const int srp = cs_w0 + s * csw, scl = srp + rw, sds = scl + cw;
     if (mp->flags & kTileManual) {  // flagged tile: fetch the slices with ordinary loads
@@ -919,6 +935,10 @@ k_tc_fwd(const TcArgs a) {
           ptx::named_bar_arrive(bar_a1, 160);    // (half 1 stored its operand inside the gather block below)
         }
       }
+      if (SAVE) {   // the rows the activation buffer holds: this tile's previous layer, or the previous tile's last one
+        if (l > 0) save_rows(l - 1, nA, nB, n0A_t, n0B_t);
+        else if (p_gA >= 0) save_rows(L - 1, p_nA, p_nB, p_n0A, p_n0B);
+      }
       if (l == 0 && p_gA >= 0) pool_tile(p_gA, p_gB, p_nA, p_nB);   // the previous tile, while the MMAs run
       if (PK && l == 1) {   // the NEXT tile's x rows, while this layer's MMAs run
         ptx::mbar_wait(&bar_stage[slot][(k + 1) & 1], (uint32_t)((k + 1) >> 1) & 1u);
@@ -956,22 +976,8 @@ k_tc_fwd(const TcArgs a) {
         }
       }
       TC_TICK(7);
-      const bool saving = SAVE && a.f.save_act[l] != nullptr;
       ptx::tc_fence_before_sync();
       ptx::named_bar_sync(bar_full, kSlotThreads);  // h complete in shared memory; D may be overwritten
-      if (saving) {
-        // (training forward) the finished rows -> global memory in 16-byte chunks, sixteen lanes per row: a warp writes two
-        // whole rows per instruction.  (One 256-byte bulk copy per row costs ~21 issue cycles in the copy engine - 2 700
-        // per layer and tile, shared by the two slots; these are eight plain loads and stores per thread.)  The activation
-        // buffer is next WRITTEN by the following epilogue, after a barrier every thread passes behind this loop.
-        float* const dst = a.f.save_act[l];
-        const int n0A_s = mp->n0A, n0B_s = mp->n0B;
-        for (int idx = gt; idx < ntot * 16; idx += kSlotThreads) {
-          const int r = idx >> 4, q = idx & 15;
-          const int64_t grow = r < nA ? (int64_t)n0A_s + r : (int64_t)n0B_s + (r - nA);
-          __stcs(reinterpret_cast<float4*>(dst + grow * 64 + 4 * q), *reinterpret_cast<const float4*>(smf + hb_w + r * HP + 4 * q));
-        }
-      }
       TC_TICK(8);
 
       if (!last) {
@@ -1023,9 +1029,10 @@ k_tc_fwd(const TcArgs a) {
       }
       TC_TICK(9);
     }
-    p_gA = gA; p_gB = gB; p_nA = nA; p_nB = nB;
+    p_gA = gA; p_gB = gB; p_nA = nA; p_nB = nB; p_n0A = n0A_t; p_n0B = n0B_t;
     TC_TICK(10);
   }
+  if (SAVE && p_gA >= 0) save_rows(L - 1, p_nA, p_nB, p_n0A, p_n0B);
   if (p_gA >= 0) pool_tile(p_gA, p_gB, p_nA, p_nB);
 
   ptx::tc_fence_before_sync();
