@@ -22,8 +22,9 @@
 // never compounds over the batch); per-CTA sums go to `partial` and are summed in CTA order by k_fused_bwd_reduce:
 // no floating-point atomics, run-to-run identical.
 //
-// One CTA of 512 threads per SM (four threads per tile row, 16 columns each); shared memory holds five
-// two-plane tiles (gT hi / lo, h1-or-x hi / lo, gA), W2^T tiles, the neighbour records and two CSR stages: ~207 KB.
+// One CTA of 512 threads per SM (four threads per tile row, 16 columns each); shared memory holds four two-plane
+// operand tiles (gT hi / lo, h1-or-x hi / lo), the gA tile in plain rows (pitch 68 floats), W2^T tiles, the neighbour
+// records and two CSR stages: ~215 KB.
 // Graphs above the tile capacity are flagged and served by the mma.sync kernel of hcg_fused_bwd.cu.
 #include "hcg_fused.cuh"
 #include "hcg_tc.cuh"
