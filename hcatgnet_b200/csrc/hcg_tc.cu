@@ -7,6 +7,10 @@
 #include "hcg_tc_tiles.cuh"
 #include <stdlib.h>
 
+#ifndef HCG_TC_DYNAMIC
+#define HCG_TC_DYNAMIC 1   // 0: every slot walks its own list (the first scheduling; kept for A/B builds)
+#endif
+
 namespace hcg {
 
 // ---- self-test: D[128,64] = A[128,K] . W[64,K]^T through TMEM-resident A and tcgen05.mma -------
@@ -197,6 +201,7 @@ k_tile_desc(const int32_t* __restrict__ graph_ptr, const int32_t* __restrict__ r
   const int slot = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   const int lane = threadIdx.x & 31;
   if (slot >= nslots) return;  // whole warps leave together
+  if (slot == 0 && lane == 0) counts[nslots] = 0;   // the tile queue of the kernel that walks the lists (k_tc_fwd)
   // COO mode (ei != NULL): node / edge offsets come from the batch's own int64 offset vectors, a graph may have
   // no edges, the copy windows are those of the two edge_index rows, and a graph that does not fit a tile is
   // REFUSED (flag in dflags[slot], embedding row zeroed) - there is no fallback kernel behind this path.
@@ -433,6 +438,10 @@ k_tc_fwd(const TcArgs a) {
   __shared__ uint32_t tmem_base_s;
   __shared__ TcMeta metas[NS][2];
   __shared__ int4 recs[NS][2][3];          // work-list records in flight (cp.async), two deep
+#if HCG_TC_DYNAMIC
+  __shared__ int s_pref[3 * kNumSMs + 1];  // exclusive prefix sums of the per-slot list lengths: tile g of the launch is
+  __shared__ int s_rec_ok[NS][2];          //   entry g - s_pref[l] of list l; s_rec_ok: the record in flight is a tile
+#endif
 
   const int tid = threadIdx.x;
   const int slot = tid / kSlotThreads, gt = tid % kSlotThreads;
@@ -507,8 +516,35 @@ k_tc_fwd(const TcArgs a) {
   const float slope = a.f.slope;
 
   const int slot_id = blockIdx.x * NS + slot;
+#if HCG_TC_DYNAMIC
+  // The work list is per-slot lists of tiles (k_tile_desc).  Walking only its own list leaves a slot with the largest
+  // graphs (or one window more) working alone at the end: with 16384 graphs of 40..120 nodes the longest list has 52
+  // tiles against 44.4 on average.  No result depends on which slot computes a tile, so the slots take tiles from ONE
+  // queue over all lists instead: a global counter (zeroed by k_tile_desc, behind the list lengths) hands out tile
+  // numbers; the feeding warp finds the list by a binary search in the prefix sums and fetches the record two tiles ahead.
+  const int nslots_all = (int)gridDim.x * NS;
+  if (tid < 32) {
+    int run = 0;
+    for (int b0 = 0; b0 < nslots_all; b0 += 32) {
+      const int v = b0 + lane < nslots_all ? a.counts[b0 + lane] : 0;
+      int incl = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += u;
+      }
+      if (b0 + lane < nslots_all) s_pref[b0 + lane] = run + incl - v;
+      run += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 0) s_pref[nslots_all] = run;
+  }
+  __syncthreads();
+  const int total_tiles = s_pref[nslots_all];
+  int* const queue = const_cast<int*>(a.counts) + nslots_all;
+#else
   const int ntiles = a.counts[slot_id];
   const TcTile* my_tiles = a.tiles + (size_t)slot_id * a.cap;
+#endif
 
   // PK: byte offsets, inside a stage, of the four staged arrays (q = 1 edge pairs | 0 bit rows | 2 byte rows | 3 f32 rows);
   // every region leaves room for the 16-byte granular windows of two slices
@@ -518,9 +554,28 @@ k_tc_fwd(const TcArgs a) {
   const int pk_of = pk_ou + ((kTcRows * pk_fu + 79) & ~15);
   // Feeding lanes (lane < 8 of pf_warp): lane = 4 gb + q copies slice q (0 x, 1 rowptr, 2 col, 3 dis) of graph gb.
   // The record of tile t travels global -> recs[t & 1] by cp.async (three lanes, 16 bytes each), a tile ahead.
+#if HCG_TC_DYNAMIC
+  auto fetch_rec = [&](int t) {   // (whole feeding warp)
+    int g = 0;
+    if (lane == 0) g = atomicAdd(queue, 1);
+    g = __shfl_sync(0xffffffffu, g, 0);
+    const bool ok = g < total_tiles;
+    if (ok) {
+      int lo = 0, hi = nslots_all;          // largest l with s_pref[l] <= g (empty lists repeat their prefix: never chosen)
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (s_pref[mid] <= g) lo = mid; else hi = mid;
+      }
+      const TcTile* src = a.tiles + (size_t)lo * a.cap + (g - s_pref[lo]);
+      if (lane < 3) ptx::cp_async16(&recs[slot][t & 1][lane], reinterpret_cast<const int4*>(src) + lane);
+    }
+    if (lane == 0) s_rec_ok[slot][t & 1] = ok ? 1 : 0;
+  };
+#else
   auto fetch_rec = [&](int t) {
     if (t < ntiles && lane < 3) ptx::cp_async16(&recs[slot][t & 1][lane], reinterpret_cast<const int4*>(my_tiles + t) + lane);
   };
+#endif
   // Issue the copies of tile t (or mark "no more tiles").  The small CSR slices are double-buffered and go out
   // a whole tile ahead (want_x = false: the six lanes with q >= 1); the x rows have ONE buffer, so the two x
   // lanes go later, once the previous tile's layer-0 gather is over (want_x = true).  All eight lanes arrive
@@ -534,7 +589,11 @@ k_tc_fwd(const TcArgs a) {
       __syncwarp();               // ... and the other lanes'
     }
     if (lane >= 8 || (PK ? want_x : ((lane & 3) == 0) != want_x)) return;   // (PK: nothing waits for the x buffer: all eight go out early)
+#if HCG_TC_DYNAMIC
+    if (!s_rec_ok[slot][s]) {
+#else
     if (t >= ntiles) {
+#endif
       if (lane == 1) m->gA = -1;
       ptx::mbar_arrive(bar);
       return;
